@@ -1,0 +1,224 @@
+"""ctypes mirror of include/avr.h (POD structs only).  No compute here."""
+import ctypes as C
+
+import numpy as np
+
+NSPEC = 471
+
+f32p = C.POINTER(C.c_float)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(f32p) if a is not None else None
+
+
+class avr_grid_desc(C.Structure):
+    _fields_ = [
+        ("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32),
+        ("density", f32p), ("temperature", f32p), ("lescale", f32p),
+        ("le_norm", C.c_float),
+        ("p0", C.c_float * 3), ("p1", C.c_float * 3),
+        ("render_from_medium", C.c_float * 16), ("medium_from_render", C.c_float * 16),
+        ("sigma_a", f32p), ("sigma_s", f32p), ("le", f32p),
+        ("sigma_scale", C.c_float), ("g", C.c_float),
+        ("temperature_offset", C.c_float), ("temperature_scale", C.c_float),
+        ("majorant_res", C.c_int32 * 3),
+    ]
+
+
+class avr_rgbgrid_desc(C.Structure):
+    _fields_ = [
+        ("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32),
+        ("sigma_a", f32p), ("sigma_s", f32p), ("le", f32p), ("le_illuminant", f32p),
+        ("le_scale", C.c_float),
+        ("p0", C.c_float * 3), ("p1", C.c_float * 3),
+        ("render_from_medium", C.c_float * 16), ("medium_from_render", C.c_float * 16),
+        ("sigma_scale", C.c_float), ("g", C.c_float),
+        ("majorant_res", C.c_int32 * 3),
+    ]
+
+
+class avr_render_desc(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("pixel_bounds", C.c_int32 * 4),
+        ("spp", C.c_int32), ("sample_begin", C.c_int32), ("sample_end", C.c_int32),
+        ("max_depth", C.c_int32), ("sampler_seed", C.c_int32), ("exact_math", C.c_int32),
+        ("filter_radius", C.c_float * 2),
+        ("camera_from_raster", C.c_float * 16), ("render_from_camera", C.c_float * 16),
+        ("light_dir", C.c_float * 3),
+        ("light_spectrum", f32p),
+        ("scene_radius", C.c_float),
+        ("boundary_type", C.c_int32),
+        ("boundary", C.c_float * 6),
+        ("sensor_rgb", f32p),
+        ("imaging_ratio", C.c_float),
+        ("output_rgb_from_sensor", C.c_float * 9),
+        ("max_component_value", C.c_float),
+        ("rank", C.c_int32), ("world", C.c_int32),
+    ]
+
+
+class avr_render_stats(C.Structure):
+    _fields_ = [
+        ("camera_rays", C.c_int64), ("camera_fetches", C.c_int64), ("shadow_fetches", C.c_int64),
+        ("segments", C.c_int64), ("scatter_events", C.c_int64),
+        ("kernel_ms", C.c_float), ("launches", C.c_int32),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+TMAJ_DTYPE = np.dtype([
+    ("T_maj", np.float32, 4), ("Tr", np.float32, 4), ("r_u", np.float32, 4), ("r_l", np.float32, 4),
+    ("t_event", np.float32), ("event", np.int32), ("n_fetch", np.int32), ("n_seg", np.int32),
+])
+assert TMAJ_DTYPE.itemsize == 80
+
+
+def _set_arr(dst, src):
+    src = np.asarray(src, dtype=np.float64).ravel()
+    for i in range(len(dst)):
+        dst[i] = float(src[i])
+
+
+IDENTITY16 = np.eye(4, dtype=np.float32).ravel()
+
+
+class GridDesc:
+    """Parameters of MakeNamedMedium "uniformgrid" (reference media.cpp:249-330), keeping the numpy
+    buffers alive for the lifetime of the ctypes struct."""
+
+    def __init__(self, density, sigma_a, sigma_s, *, temperature=None, lescale=None, le=None, le_norm=1.0,
+                 p0=(0, 0, 0), p1=(1, 1, 1), render_from_medium=None, medium_from_render=None, scale=1.0, g=0.0,
+                 temperature_offset=0.0, temperature_scale=1.0, majorant_res=(16, 16, 16)):
+        self.density = _f32(density)
+        assert self.density.ndim == 3, "density must be [nz, ny, nx]"
+        nz, ny, nx = self.density.shape
+        self.temperature = None if temperature is None else _f32(temperature)
+        self.lescale = None if lescale is None else _f32(lescale)
+        self.sigma_a = _f32(np.broadcast_to(sigma_a, (NSPEC,)))
+        self.sigma_s = _f32(np.broadcast_to(sigma_s, (NSPEC,)))
+        self.le = None if le is None else _f32(np.broadcast_to(le, (NSPEC,)))
+        self.majorant_res = tuple(int(r) for r in majorant_res)
+        m = IDENTITY16 if render_from_medium is None else _f32(render_from_medium).ravel()
+        if medium_from_render is None:
+            mi = np.linalg.inv(np.asarray(m, dtype=np.float64).reshape(4, 4)).astype(np.float32).ravel()
+        else:
+            mi = _f32(medium_from_render).ravel()
+        self.m, self.minv = m, mi
+        c = avr_grid_desc()
+        c.nx, c.ny, c.nz = nx, ny, nz
+        c.density = _ptr(self.density)
+        c.temperature = _ptr(self.temperature)
+        c.lescale = _ptr(self.lescale)
+        c.le_norm = le_norm
+        _set_arr(c.p0, p0); _set_arr(c.p1, p1)
+        _set_arr(c.render_from_medium, m); _set_arr(c.medium_from_render, mi)
+        c.sigma_a = _ptr(self.sigma_a); c.sigma_s = _ptr(self.sigma_s); c.le = _ptr(self.le)
+        c.sigma_scale = scale; c.g = g
+        c.temperature_offset = temperature_offset; c.temperature_scale = temperature_scale
+        for i in range(3):
+            c.majorant_res[i] = self.majorant_res[i]
+        self.c = c
+        self.p0 = np.asarray(p0, dtype=np.float32); self.p1 = np.asarray(p1, dtype=np.float32)
+
+
+class RGBGridDesc:
+    """Parameters of MakeNamedMedium "rgbgrid" (reference media.cpp:380-453); voxels are
+    {scale,c0,c1,c2} as produced by RGBUnboundedSpectrum(cs, rgb)."""
+
+    def __init__(self, sigma_a=None, sigma_s=None, *, le=None, le_illuminant=None, le_scale=1.0, p0=(0, 0, 0),
+                 p1=(1, 1, 1), render_from_medium=None, medium_from_render=None, scale=1.0, g=0.0,
+                 majorant_res=(16, 16, 16)):
+        self.sigma_a = None if sigma_a is None else _f32(sigma_a)
+        self.sigma_s = None if sigma_s is None else _f32(sigma_s)
+        self.le = None if le is None else _f32(le)
+        self.le_illuminant = None if le_illuminant is None else _f32(le_illuminant)
+        ref = self.sigma_a if self.sigma_a is not None else self.sigma_s
+        assert ref is not None and ref.ndim == 4 and ref.shape[3] == 4, "voxels must be [nz, ny, nx, 4]"
+        nz, ny, nx, _ = ref.shape
+        self.majorant_res = tuple(int(r) for r in majorant_res)
+        m = IDENTITY16 if render_from_medium is None else _f32(render_from_medium).ravel()
+        if medium_from_render is None:
+            mi = np.linalg.inv(np.asarray(m, dtype=np.float64).reshape(4, 4)).astype(np.float32).ravel()
+        else:
+            mi = _f32(medium_from_render).ravel()
+        self.m, self.minv = m, mi
+        c = avr_rgbgrid_desc()
+        c.nx, c.ny, c.nz = nx, ny, nz
+        c.sigma_a = _ptr(self.sigma_a); c.sigma_s = _ptr(self.sigma_s)
+        c.le = _ptr(self.le); c.le_illuminant = _ptr(self.le_illuminant)
+        c.le_scale = le_scale
+        _set_arr(c.p0, p0); _set_arr(c.p1, p1)
+        _set_arr(c.render_from_medium, m); _set_arr(c.medium_from_render, mi)
+        c.sigma_scale = scale; c.g = g
+        for i in range(3):
+            c.majorant_res[i] = self.majorant_res[i]
+        self.c = c
+        self.p0 = np.asarray(p0, dtype=np.float32); self.p1 = np.asarray(p1, dtype=np.float32)
+
+
+class RenderDesc:
+    """Camera / light / film / sampler parameters of one volpath render (see avr_render_desc)."""
+
+    def __init__(self, width, height, spp, *, camera_from_raster, render_from_camera, light_dir, light_spectrum,
+                 scene_radius, boundary_type, boundary, sensor_rgb, max_depth=5, sampler_seed=0, exact_math=1,
+                 filter_radius=(0.5, 0.5), imaging_ratio=1.0, output_rgb_from_sensor=None,
+                 max_component_value=float("inf"), pixel_bounds=None, sample_begin=0, sample_end=0, rank=0, world=1):
+        self.light_spectrum = _f32(np.broadcast_to(light_spectrum, (NSPEC,)))
+        self.sensor_rgb = _f32(sensor_rgb).reshape(3, NSPEC)
+        c = avr_render_desc()
+        c.width, c.height, c.spp = width, height, spp
+        pb = pixel_bounds if pixel_bounds is not None else (0, 0, width, height)
+        for i in range(4):
+            c.pixel_bounds[i] = int(pb[i])
+        c.sample_begin, c.sample_end = sample_begin, sample_end
+        c.max_depth, c.sampler_seed, c.exact_math = max_depth, sampler_seed, exact_math
+        _set_arr(c.filter_radius, filter_radius)
+        _set_arr(c.camera_from_raster, camera_from_raster)
+        _set_arr(c.render_from_camera, render_from_camera)
+        ld = np.asarray(light_dir, dtype=np.float64)
+        ld = (ld / np.linalg.norm(ld)).astype(np.float32)
+        _set_arr(c.light_dir, ld)
+        c.light_spectrum = _ptr(self.light_spectrum)
+        c.scene_radius = scene_radius
+        c.boundary_type = boundary_type
+        b = list(boundary) + [0.0] * (6 - len(boundary))
+        _set_arr(c.boundary, b)
+        c.sensor_rgb = _ptr(self.sensor_rgb)
+        c.imaging_ratio = imaging_ratio
+        _set_arr(c.output_rgb_from_sensor, np.eye(3).ravel() if output_rgb_from_sensor is None
+                 else output_rgb_from_sensor)
+        c.max_component_value = max_component_value
+        c.rank, c.world = rank, world
+        self.c = c
+
+    def ranges(self):
+        c = self.c
+        x0, y0, x1, y1 = list(c.pixel_bounds)
+        if (x0, y0, x1, y1) == (0, 0, 0, 0):
+            x1, y1 = c.width, c.height
+        s0, s1 = c.sample_begin, c.sample_end
+        if s0 == 0 and s1 == 0:
+            s1 = c.spp
+        return x0, y0, x1, y1, s0, s1
+
+    def with_(self, **kw):
+        """Shallow variant with some scalar fields of the C struct replaced."""
+        import copy
+        r = copy.copy(self)
+        r.c = avr_render_desc()
+        C.memmove(C.byref(r.c), C.byref(self.c), C.sizeof(avr_render_desc))
+        for k, v in kw.items():
+            if k == "pixel_bounds":
+                for i in range(4):
+                    r.c.pixel_bounds[i] = int(v[i])
+            else:
+                setattr(r.c, k, v)
+        return r

@@ -1,0 +1,281 @@
+/*
+ * avr.h — C ABI of libavr_b200.so: the B200-native (sm_100a) volumetric hot path of
+ * tsvdh/AcceleratedVolRenderer (a pbrt-v4 fork).
+ *
+ * Every entry point names the reference interface it replaces (file:line relative to the
+ * reference tree).  Plain C: pointers, sizes, POD structs.  No C++/torch types cross this boundary.
+ * Every call returns avr_status; nothing in the library exits or aborts (the reference's
+ * ErrorExit/CHECK behaviour, util/error.h + util/check.h:36, is re-created by the host adapter,
+ * which maps a non-zero status to ErrorExit).  There is NO CPU fallback: with no CUDA device every
+ * compute entry point returns AVR_ERR_CUDA.
+ *
+ * Spectra cross the boundary the way the reference stores them after construction:
+ * DenselySampledSpectrum tables (util/spectrum.h:374), AVR_NSPEC = 471 fp32 values for
+ * lambda = 360..830 nm.
+ */
+#ifndef AVR_H
+#define AVR_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AVR_NSPEC 471      /* Lambda_min=360 .. Lambda_max=830, util/spectrum.h:30-33 */
+#define AVR_NLAMBDA 4      /* NSpectrumSamples, util/spectrum.h:36 */
+
+typedef int avr_status;
+enum {
+    AVR_OK = 0,
+    AVR_ERR_BAD_ARG = 1,
+    AVR_ERR_OOM = 2,
+    AVR_ERR_CUDA = 3,
+    AVR_ERR_UNSUPPORTED = 4
+};
+
+typedef struct avr_ctx avr_ctx;
+typedef struct avr_medium avr_medium;
+typedef struct avr_graph avr_graph;
+
+/* ---- context -------------------------------------------------------------------------------- */
+/* One context per GPU/process.  Owns streams, scratch and the last error string. */
+avr_status avr_ctx_create(int device, avr_ctx **out);
+void avr_ctx_destroy(avr_ctx *ctx);
+/* Last error message of the context (or of the failed avr_ctx_create when ctx == NULL). */
+const char *avr_last_error(const avr_ctx *ctx);
+/* Library version / build string ("avr_b200 <n> sm_100a ..."). */
+const char *avr_version(void);
+
+/* ---- media ---------------------------------------------------------------------------------- */
+/* HBM layouts for scalar grids.  All three give the same SampledGrid::Lookup tap values
+ * (util/containers.h:804-835); the octet layouts store, per interpolation cell, its 8 corner taps
+ * contiguously (one 32-byte sector for fp32, one 16-byte vector for fp16) in 4x4x4-cell bricks. */
+enum {
+    AVR_LAYOUT_DENSE_F32 = 0,  /* reference layout: values[(z*ny+y)*nx+x], 8 bounds-checked taps */
+    AVR_LAYOUT_OCTET_F32 = 1,  /* bit-identical taps, 1 sector per fetch                       */
+    AVR_LAYOUT_OCTET_F16 = 2   /* taps rounded to fp16 (perf option; NOT per-ray bit-parity)   */
+};
+
+/* Replaces GridMedium::Create + ctor, media.cpp:212-336 ("uniformgrid").  Host pointers; the
+ * library copies at create time (reference copies into pstd::vector, util/containers.h:771-774). */
+typedef struct avr_grid_desc {
+    int32_t nx, ny, nz;
+    const float *density;      /* nx*ny*nz, x fastest                                         */
+    const float *temperature;  /* NULL or nx*ny*nz ("temperature", media.cpp:250)             */
+    const float *lescale;      /* NULL or nx*ny*nz ("Lescale", media.cpp:295), NOT yet *LeNorm */
+    float le_norm;             /* LeNorm = 1/SpectrumToPhotometric(Le) or 1 (media.cpp:288-292) */
+    float p0[3], p1[3];        /* medium-space bounds ("p0","p1")                             */
+    float render_from_medium[16]; /* Transform::m,    row-major                               */
+    float medium_from_render[16]; /* Transform::mInv, row-major                               */
+    const float *sigma_a;      /* AVR_NSPEC, unscaled (ctor applies sigma_scale, media.cpp:229) */
+    const float *sigma_s;      /* AVR_NSPEC                                                   */
+    const float *le;           /* NULL or AVR_NSPEC ("Le")                                    */
+    float sigma_scale;         /* "scale"                                                     */
+    float g;                   /* HG asymmetry "g"                                            */
+    float temperature_offset;  /* "temperatureoffset"                                         */
+    float temperature_scale;   /* "temperaturescale"                                          */
+    int32_t majorant_res[3];   /* {16,16,16} for uniformgrid (media.cpp:229); {64,64,64} is what
+                                  NanoVDBMedium uses (media.cpp:521); 0 -> 16                  */
+} avr_grid_desc;
+
+/* Replaces RGBGridMedium::Create + ctor, media.cpp:339-459 ("rgbgrid").  Voxels arrive already
+ * converted by the host with RGBUnboundedSpectrum(cs, rgb) (util/spectrum.cpp:236-240) as
+ * {scale, c0, c1, c2} fp32x4 per voxel. */
+typedef struct avr_rgbgrid_desc {
+    int32_t nx, ny, nz;
+    const float *sigma_a;      /* NULL or nx*ny*nz*4                                          */
+    const float *sigma_s;      /* NULL or nx*ny*nz*4                                          */
+    const float *le;           /* NULL or nx*ny*nz*4 (scale,c0,c1,c2 of RGBIlluminantSpectrum) */
+    const float *le_illuminant;/* AVR_NSPEC: the colour space's illuminant, needed iff le      */
+    float le_scale;            /* "Lescale"                                                   */
+    float p0[3], p1[3];
+    float render_from_medium[16];
+    float medium_from_render[16];
+    float sigma_scale, g;
+    int32_t majorant_res[3];
+} avr_rgbgrid_desc;
+
+avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid_desc *desc, int layout,
+                                         avr_medium **out);
+avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_desc *desc, avr_medium **out);
+void avr_medium_destroy(avr_medium *m);
+
+/* Medium::IsEmissive, media.h:284/374. */
+int avr_medium_is_emissive(const avr_medium *m);
+/* Bytes of HBM held by the medium's grids (the STAT_MEMORY_COUNTER "Memory/Volume grids"). */
+int64_t avr_medium_bytes(const avr_medium *m);
+
+/* Copies the device-built MajorantGrid (media.h:105-133; built as in media.cpp:240-246 /
+ * :364-377) to host: out has res[0]*res[1]*res[2] floats, x fastest.  Bit-exact contract. */
+avr_status avr_medium_majorants(avr_medium *m, float *out, int32_t res[3]);
+
+/* SampledGrid<Float>::Lookup(Point3f), util/containers.h:804-819, on the medium's density grid.
+ * p in grid-normalised [0,1]^3 coordinates (after bounds.Offset), 3 floats per point. */
+avr_status avr_medium_lookup_density(avr_medium *m, const float *p, int64_t n, float *out);
+
+/* MediumProperties Medium::SamplePoint(p, lambda), media.h:287-319 / :377-401.  p in render space,
+ * lambda: 4 wavelengths shared by all points.  out: 12 floats per point {sigma_a[4], sigma_s[4],
+ * Le[4]}. */
+avr_status avr_medium_sample_point(avr_medium *m, const float *p, int64_t n, const float lambda[4],
+                                   float *out);
+
+/* ---- kernel 2: DDA traversal ------------------------------------------------------------------ */
+/* DDAMajorantIterator ctor + Next(), media.h:141-203.  rays: 8 floats each {o.xyz, d.xyz, tMin,
+ * tMax} in MEDIUM space (what GridMedium::SampleRay hands the iterator after ApplyInverse + slab
+ * test, media.h:322-337).  Emits up to max_per_ray segments per ray:
+ *   seg_t[(i*max_per_ray+k)*2 + {0,1}] = tMin,tMax ; seg_sigma[...] = sigma_t * grid(voxel) ;
+ *   seg_voxel[...] = x + res.x*(y + res.y*z) ;  counts[i] = number of segments the reference
+ * iterator yields (may exceed max_per_ray; extra segments are counted, not stored).
+ * Bit-exact with the reference (integer voxels, fp32 t values). */
+avr_status avr_dda_segments(avr_medium *m, const float *rays, int64_t n, float sigma_t,
+                            int32_t max_per_ray, int32_t *counts, float *seg_t, float *seg_sigma,
+                            int32_t *seg_voxel);
+
+/* {Grid,RGBGrid}Medium::SampleRay prologue, media.h:322-337: Transform::ApplyInverse(Ray,&tMax)
+ * (util/transform.h:420-433, interval-arithmetic origin offset) + Bounds3::IntersectP slab test.
+ * rays: 7 floats {o.xyz, d.xyz, tMax} render space.  out: 9 floats {o.xyz, d.xyz, tMin, tMax,
+ * hit(0/1)} medium space. */
+avr_status avr_medium_ray_to_medium(avr_medium *m, const float *rays, int64_t n, float *out);
+
+/* ---- kernel 1a: majorant free-flight / transmittance sampling -------------------------------- */
+enum {
+    /* ratio tracking, channel 0: util::SampleTransmittance, src/graph/util.h:344-366 */
+    AVR_TMAJ_RATIO = 0,
+    /* delta tracking to the first real event: util::SampleScatter, src/graph/util.h:368-403, and
+       GraphIntegrator::Li's callback, src/graph/graph_integrator.cpp:201-230 */
+    AVR_TMAJ_DELTA = 1,
+    /* chromatic ratio tracking with Russian roulette: the shadow-ray loop of
+       VolPathIntegrator::SampleLd, cpu/integrators.cpp:1352-1380 */
+    AVR_TMAJ_SHADOW = 2
+};
+
+typedef struct avr_tmaj_result {
+    float T_maj[4];     /* return value of SampleT_maj (media.h:741-806)                        */
+    float Tr[4];        /* RATIO: Tr in [0]; SHADOW: T_ray[4]; DELTA: unused (1)                 */
+    float r_u[4];       /* SHADOW: r_u ; else 1                                                  */
+    float r_l[4];       /* SHADOW: r_l ; else 1                                                  */
+    float t_event;      /* DELTA: ray parameter t of the terminating event (normalised ray), else -1 */
+    int32_t event;      /* DELTA: 0 absorbed, 1 scattered, 2 escaped ; else 2                    */
+    int32_t n_fetch;    /* number of SamplePoint calls (density fetches) made                    */
+    int32_t n_seg;      /* number of majorant segments consumed                                  */
+} avr_tmaj_result;
+
+/* SampleT_maj<GridMedium>(ray, tMax, u, rng, lambda, callback), media.h:741-806.
+ * rays: 7 floats {o.xyz, d.xyz (not necessarily normalised), tMax}, render space.
+ * rng: 2 uint64 per ray {sequenceIndex, seed} -> RNG(seq, seed) (util/rng.h:124-130);
+ * u: first exponential sample per ray; lambda: 4 wavelengths, shared by the batch. */
+avr_status avr_sample_tmaj(avr_medium *m, int mode, const float *rays, int64_t n,
+                           const uint64_t *rng, const float *u, const float lambda[4],
+                           avr_tmaj_result *out);
+
+/* ---- kernel 1b: volumetric path tracing -------------------------------------------------------- */
+/* Replaces Integrator::Create("volpath"/"volpathcustom") + ImageTileIntegrator::Render
+ * (cpu/integrators.cpp:72-232), RayIntegrator::EvaluatePixelSample (:235-298),
+ * VolPathIntegrator::Li volume branch (:962-1106) and SampleLd (:1282-1399) for the scene class the
+ * fork's graph pipeline accepts (src/graph/util.h:61-132): ONE grid medium inside ONE convex
+ * boundary shape with Material "interface", ONE distant light, perspective camera, box pixel filter,
+ * Sampler "independent". */
+enum { AVR_BOUNDARY_SPHERE = 0, AVR_BOUNDARY_BOX = 1 };
+
+typedef struct avr_render_desc {
+    int32_t width, height;           /* full film resolution                                   */
+    int32_t pixel_bounds[4];         /* x0,y0,x1,y1 (exclusive); all 0 -> full frame           */
+    int32_t spp;                     /* samplesPerPixel                                        */
+    int32_t sample_begin, sample_end;/* sample-index range rendered by this call (multi-GPU
+                                        sharding by sample index); both 0 -> [0, spp)          */
+    int32_t max_depth;               /* "maxdepth" (default 5, cpu/integrators.cpp:1410)       */
+    int32_t sampler_seed;            /* IndependentSampler seed, samplers.h:442-476            */
+    int32_t exact_math;              /* 1: restated CPU FastExp/logf/IEEE div (parity mode);
+                                        0: ex2.approx / lg2.approx (reference's own GPU branch,
+                                        util/math.h:451-452)                                   */
+    float filter_radius[2];          /* box filter radius (default 0.5)                        */
+    float camera_from_raster[16];    /* PerspectiveCamera, cameras.cpp:404-460                 */
+    float render_from_camera[16];
+    float light_dir[3];              /* direction TOWARDS the distant light (wi), render space */
+    const float *light_spectrum;     /* AVR_NSPEC, already multiplied by the light's scale     */
+    float scene_radius;              /* DistantLight::Preprocess sceneRadius, lights.h:284-291 */
+    int32_t boundary_type;
+    float boundary[6];               /* sphere: cx,cy,cz,r ; box: min xyz, max xyz (render sp.) */
+    const float *sensor_rgb;         /* 3*AVR_NSPEC: r_bar,g_bar,b_bar of PixelSensor, film.h:95 */
+    float imaging_ratio;
+    float output_rgb_from_sensor[9]; /* row-major 3x3 (film.h:257-275)                         */
+    float max_component_value;       /* RGBFilm clamp, film.h:246                              */
+    int32_t rank, world;             /* tile/sample partition: this call renders work items
+                                        with (item % world) == rank; world 0 -> 1              */
+} avr_render_desc;
+
+typedef struct avr_render_stats {
+    int64_t camera_rays;       /* pixel samples evaluated                                       */
+    int64_t camera_fetches;    /* "Integrator/Volume interactions" (cpu/integrators.cpp:958,997) */
+    int64_t shadow_fetches;    /* SamplePoint calls on NEE shadow rays                           */
+    int64_t segments;          /* DDA segments consumed (camera + shadow)                        */
+    int64_t scatter_events;    /* real scattering events                                         */
+    float kernel_ms;           /* device time of the render kernel(s), CUDA events              */
+    int32_t launches;          /* kernels launched by this call                                 */
+} avr_render_stats;
+
+/* film: width*height*4 doubles {rgbSum[3], weightSum} per pixel (RGBFilm::Pixel, film.h:302-307),
+ * host memory.  The call ADDS into film (so sample shards/ranks can be accumulated). */
+avr_status avr_render_volpath(avr_ctx *ctx, avr_medium *m, const avr_render_desc *desc,
+                              double *film, avr_render_stats *stats);
+/* Same, film is a DEVICE pointer (for NCCL reduction by the caller); asynchronous on `stream`
+ * (a cudaStream_t passed as void*, NULL = the context's stream).  stats may be NULL. */
+avr_status avr_render_volpath_device(avr_ctx *ctx, avr_medium *m, const avr_render_desc *desc,
+                                     double *film_dev, void *stream, avr_render_stats *stats);
+/* Per-sample radiance dump for parity tests: L[4] + lambda[4] + pdf[4] per (pixel, sample) in
+ * pixel_bounds x [sample_begin, sample_end), pixel-major.  Host memory, 12 floats per sample. */
+avr_status avr_render_volpath_samples(avr_ctx *ctx, avr_medium *m, const avr_render_desc *desc,
+                                      float *out, avr_render_stats *stats);
+/* RGBFilm::GetPixelRGB, film.h:257-275: rgb = outputRGBFromSensorRGB * rgbSum/weightSum. */
+avr_status avr_film_resolve(const avr_render_desc *desc, const double *film, float *rgb);
+
+/* ---- kernel 3: radiance-graph propagation ----------------------------------------------------- */
+/* Replaces LightingCalculator::GetTransportMatrix (src/graph/lighting_calculator.cpp:61-82): the
+ * host hands over CSR (row = vertex, col = out-edge target, val = edge.samples/vertex.samples;
+ * duplicates already summed as Eigen::setFromTriplets does). */
+avr_status avr_graph_create(avr_ctx *ctx, int32_t n_vertices, int64_t nnz, const int64_t *rowptr,
+                            const int32_t *col, const float *val, avr_graph **out);
+void avr_graph_destroy(avr_graph *g);
+
+/* LightingCalculator::ComputeFinalLight (src/graph/lighting_calculator.cpp:23-59):
+ * total = L0; cur = L0; repeat `bounces`: cur = T*cur; stop BEFORE adding if any NaN/Inf;
+ * total += cur.  iters_done = the function's return value. */
+avr_status avr_graph_propagate(avr_graph *g, const float *L0, int32_t bounces, float *total,
+                               int32_t *iters_done);
+/* Row-range shard of one iteration on device pointers, for the multi-GPU path (caller all-gathers
+ * `cur_out` rows with NCCL): cur_out[r] = sum_j T[r,j]*cur_in[j], total[r] += cur_out[r] unless
+ * *bad_flag is raised; rows [row_begin,row_end).  Asynchronous on `stream`. */
+avr_status avr_graph_spmv_rows_device(avr_graph *g, const float *cur_in_dev, float *cur_out_dev,
+                                      int32_t row_begin, int32_t row_end, int32_t *bad_flag_dev,
+                                      void *stream);
+avr_status avr_graph_axpy_rows_device(avr_graph *g, const float *cur_dev, float *total_dev,
+                                      int32_t row_begin, int32_t row_end, const int32_t *bad_flag_dev,
+                                      void *stream);
+
+/* Vertex data for rendering (what FreeGraph::ReadFromDisk yields, src/graph/graph.cpp:657 +
+ * GraphIntegrator::Initialize, src/graph/graph_integrator.cpp:24-81): positions (world space),
+ * lightScalar, optional renderSearchRange; builds the device spatial index. */
+avr_status avr_graph_set_vertices(avr_graph *g, const float *pos, const float *light_scalar,
+                                  const float *search_range /* or NULL */, float vertex_radius);
+/* GraphIntegrator::ConnectToGraph, src/graph/graph_integrator.cpp:249-280: radius search with the
+ * perc99 / max fallbacks and 1/dist^2 weighted mean.  points in WORLD space, 3 floats each. */
+avr_status avr_graph_connect(avr_graph *g, const float *points, int64_t n, float *out);
+/* GraphIntegrator::Li free-graph branch (src/graph/graph_integrator.cpp:180-244) rendered over the
+ * same scene class as avr_render_volpath; world_from_render: 16 floats row-major. */
+avr_status avr_render_graph(avr_ctx *ctx, avr_medium *m, avr_graph *g, const avr_render_desc *desc,
+                            const float *world_from_render, double *film, avr_render_stats *stats);
+
+/* LightingCalculator::GetLightVector inner estimator (src/graph/lighting_calculator.cpp:84-155 via
+ * ComputeRaysToSphere, src/graph/util.h:814-839): for each ray, `iterations` ratio-tracking
+ * estimates with IndependentSampler streams StartPixelSample({x,y}, i) and
+ * tMax_i = start_scatter_t + dist_in_sphere * Get1D(); out[i] = mean transmittance.
+ * rays: 6 floats {o, d}; pixel: 2 ints per ray; ts: 2 floats {start_scatter_t, dist_in_sphere}. */
+avr_status avr_graph_light_rays(avr_medium *m, const float *rays, const int32_t *pixel,
+                                const float *ts, int64_t n, int32_t iterations, int32_t sampler_seed,
+                                const float lambda[4], float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AVR_H */

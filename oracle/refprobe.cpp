@@ -1,0 +1,384 @@
+// oracle/refprobe.cpp — TEST INFRASTRUCTURE ONLY.
+//
+// Thin probe over the REFERENCE'S OWN hot-path code, compiled from the sources where they lie under
+// /root/reference (never copied): this file only #includes reference headers and calls into them;
+// oracle/Makefile adds the reference's media.cpp, util/{pstd,transform,math,sampling,vecmath}.cpp.
+// Output: oracle/_ref/libavr_refprobe.so (git-ignored, travels to the GPU box).
+//
+// It exports the same flat signatures as oracle/oracle_capi.cpp with a ref_ prefix, so that
+// tests can check the restatement against the real GridMedium / RGBGridMedium / SampleT_maj<> /
+// DDAMajorantIterator / SampledGrid / RNG / Hash / FastExp / SampleDiscrete / HG / Transform code.
+// Built with -fno-access-control solely to fill RGBUnboundedSpectrum coefficients (the reference
+// builds them from its generated rgb2spec tables, which need its cmake build).
+#include <pbrt/media.h>
+#include <pbrt/samplers.h>
+#include <pbrt/util/hash.h>
+#include <pbrt/util/rng.h>
+#include <pbrt/util/sampling.h>
+#include <pbrt/util/scattering.h>
+#include <pbrt/util/spectrum.h>
+#include <pbrt/util/transform.h>
+
+#include <Eigen/Sparse>
+
+#include "../include/avr.h"
+
+using namespace pbrt;
+
+namespace {
+Transform make_xf(const float *m, const float *minv) {
+    SquareMatrix<4> M, MI;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            M[i][j] = m[4 * i + j];
+            MI[i][j] = minv[4 * i + j];
+        }
+    return Transform(M, MI);
+}
+SampledWavelengths make_lambda(const float l[4]) {
+    SampledWavelengths swl;
+    for (int i = 0; i < 4; ++i) {
+        swl.lambda[i] = l[i];
+        swl.pdf[i] = 1;
+    }
+    return swl;
+}
+struct RefMedium {
+    Medium medium;
+    GridMedium *grid = nullptr;
+    RGBGridMedium *rgb = nullptr;
+    std::vector<DenselySampledSpectrum *> keep;
+};
+DenselySampledSpectrum *dense_from(const float *tab) {
+    auto *d = new DenselySampledSpectrum(
+        DenselySampledSpectrum::SampleFunction([&](Float l) { return tab[int(l) - 360]; }));
+    return d;
+}
+}  // namespace
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+const char *ref_kind() { return "reference"; }
+
+void ref_fast_exp(const float *x, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = FastExp(x[i]);
+}
+void ref_mix_bits(const uint64_t *x, int64_t n, uint64_t *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = MixBits(x[i]);
+}
+void ref_hash_float(const float *x, int64_t n, uint64_t *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = Hash(x[i]);
+}
+void ref_hash_point3(const float *x, int64_t n, uint64_t *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = Hash(Point3f(x[3 * i], x[3 * i + 1], x[3 * i + 2]));
+}
+void ref_rng_stream(uint64_t seq, uint64_t seed, int use_seed, int64_t adv, int64_t n, uint32_t *out_u32,
+                    float *out_f) {
+    RNG r;
+    if (use_seed) r.SetSequence(seq, seed); else r.SetSequence(seq);
+    r.Advance(adv);
+    RNG r2 = r;
+    for (int64_t i = 0; i < n; ++i) out_u32[i] = r.Uniform<uint32_t>();
+    for (int64_t i = 0; i < n; ++i) out_f[i] = r2.Uniform<Float>();
+}
+void ref_independent_sampler(int px, int py, int seed, int sampleIndex, int dim, int64_t n, float *out) {
+    IndependentSampler s(1, seed);
+    s.StartPixelSample(Point2i(px, py), sampleIndex, dim);
+    for (int64_t i = 0; i < n; ++i) out[i] = s.Get1D();
+}
+void ref_sample_discrete3(const float *w, const float *u, int64_t n, int32_t *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = SampleDiscrete({w[3 * i], w[3 * i + 1], w[3 * i + 2]}, u[i]);
+}
+void ref_sample_exponential(const float *u, const float *a, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = SampleExponential(u[i], a[i]);
+}
+void ref_hg_sample(const float *wo, float g, const float *u, int64_t n, float *wi, float *pdf) {
+    HGPhaseFunction hg(g);
+    for (int64_t i = 0; i < n; ++i) {
+        auto ps = hg.Sample_p(Vector3f(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), Point2f(u[2 * i], u[2 * i + 1]));
+        wi[3 * i] = ps->wi.x; wi[3 * i + 1] = ps->wi.y; wi[3 * i + 2] = ps->wi.z;
+        pdf[i] = ps->pdf;
+    }
+}
+void ref_hg_p(const float *cosTheta, float g, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = HenyeyGreenstein(cosTheta[i], g);
+}
+void ref_sample_wavelengths(const float *u, int64_t n, float *lambda_pdf) {
+    for (int64_t i = 0; i < n; ++i) {
+        SampledWavelengths l = SampledWavelengths::SampleVisible(u[i]);
+        for (int k = 0; k < 4; ++k) { lambda_pdf[8 * i + k] = l[k]; lambda_pdf[8 * i + 4 + k] = l.PDF()[k]; }
+    }
+}
+void ref_blackbody(const float *T, int64_t n, const float lambda[4], float *out) {
+    SampledWavelengths swl = make_lambda(lambda);
+    for (int64_t i = 0; i < n; ++i) {
+        SampledSpectrum s = BlackbodySpectrum(T[i]).Sample(swl);
+        for (int k = 0; k < 4; ++k) out[4 * i + k] = s[k];
+    }
+}
+void ref_grid_lookup(const float *grid, int nx, int ny, int nz, const float *p, int64_t n, float *out) {
+    SampledGrid<Float> g(pstd::span<const Float>(grid, size_t(nx) * ny * nz), nx, ny, nz, Allocator());
+    for (int64_t i = 0; i < n; ++i) out[i] = g.Lookup(Point3f(p[3 * i], p[3 * i + 1], p[3 * i + 2]));
+}
+void ref_dda(const float *bounds, const int32_t *res, const float *vox, const float *rays, int64_t n,
+             float sigma_t, int32_t max_per_ray, int32_t *counts, float *seg_t, float *seg_sigma,
+             int32_t *seg_voxel) {
+    MajorantGrid g(Bounds3f(Point3f(bounds[0], bounds[1], bounds[2]), Point3f(bounds[3], bounds[4], bounds[5])),
+                   Point3i(res[0], res[1], res[2]), Allocator());
+    // a second grid whose values are the voxel's own linear index recovers the traversed voxel
+    MajorantGrid gi = g;
+    for (size_t i = 0; i < g.voxels.size(); ++i) { g.voxels[i] = vox[i]; gi.voxels[i] = Float(i); }
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 8 * i;
+        Ray ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5]));
+        DDAMajorantIterator it(ray, r[6], r[7], &g, SampledSpectrum(sigma_t));
+        DDAMajorantIterator iti(ray, r[6], r[7], &gi, SampledSpectrum(1.f));
+        int k = 0;
+        while (auto s = it.Next()) {
+            auto si = iti.Next();
+            if (k < max_per_ray) {
+                size_t j = size_t(i) * max_per_ray + k;
+                seg_t[2 * j] = s->tMin; seg_t[2 * j + 1] = s->tMax;
+                seg_sigma[j] = s->sigma_maj[0];
+                seg_voxel[j] = int(si->sigma_maj[0]);
+            }
+            ++k;
+            if (k > 100000) break;
+        }
+        counts[i] = k;
+    }
+}
+void ref_apply_inverse_ray(const float *m, const float *minv, const float *rays7, int64_t n, float *out7) {
+    Transform t = make_xf(m, minv);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays7 + 7 * i;
+        Float tMax = r[6];
+        Ray ray = t.ApplyInverse(Ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5])), &tMax);
+        float *q = out7 + 7 * i;
+        q[0] = ray.o.x; q[1] = ray.o.y; q[2] = ray.o.z; q[3] = ray.d.x; q[4] = ray.d.y; q[5] = ray.d.z; q[6] = tMax;
+    }
+}
+void ref_apply_ray(const float *m, const float *minv, const float *rays7, int64_t n, float *out7) {
+    Transform t = make_xf(m, minv);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays7 + 7 * i;
+        Float tMax = r[6];
+        Ray ray = t(Ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5])), &tMax);
+        float *q = out7 + 7 * i;
+        q[0] = ray.o.x; q[1] = ray.o.y; q[2] = ray.o.z; q[3] = ray.d.x; q[4] = ray.d.y; q[5] = ray.d.z; q[6] = tMax;
+    }
+}
+
+// ---- media: the reference's real constructors ----------------------------------------------------
+void *ref_medium_create_uniformgrid(const avr_grid_desc *d) {
+    Allocator alloc;
+    RefMedium *rm = new RefMedium();
+    size_t n = size_t(d->nx) * d->ny * d->nz;
+    SampledGrid<Float> density(pstd::span<const Float>(d->density, n), d->nx, d->ny, d->nz, alloc);
+    pstd::optional<SampledGrid<Float>> temperature;
+    if (d->temperature)
+        temperature = SampledGrid<Float>(pstd::span<const Float>(d->temperature, n), d->nx, d->ny, d->nz, alloc);
+    // LeScale grid as GridMedium::Create builds it, media.cpp:293-306
+    SampledGrid<Float> LeGrid(alloc);
+    if (!d->lescale) {
+        std::vector<Float> one = {d->le_norm};
+        LeGrid = SampledGrid<Float>(one, 1, 1, 1, alloc);
+    } else {
+        std::vector<Float> ls(d->lescale, d->lescale + n);
+        for (size_t i = 0; i < n; ++i) ls[i] *= d->le_norm;
+        LeGrid = SampledGrid<Float>(ls, d->nx, d->ny, d->nz, alloc);
+    }
+    DenselySampledSpectrum *sa = dense_from(d->sigma_a), *ss = dense_from(d->sigma_s);
+    rm->keep = {sa, ss};
+    Spectrum Le;
+    if (d->le) {
+        DenselySampledSpectrum *le = dense_from(d->le);
+        rm->keep.push_back(le);
+        Le = le;
+    } else
+        Le = new ConstantSpectrum(0.f);
+    Transform xf = make_xf(d->render_from_medium, d->medium_from_render);
+    rm->grid = new GridMedium(Bounds3f(Point3f(d->p0[0], d->p0[1], d->p0[2]), Point3f(d->p1[0], d->p1[1], d->p1[2])),
+                              xf, sa, ss, d->sigma_scale, d->g, std::move(density), std::move(temperature),
+                              d->temperature_scale, d->temperature_offset, Le, std::move(LeGrid), alloc);
+    rm->medium = rm->grid;
+    return rm;
+}
+void *ref_medium_create_rgbgrid(const avr_rgbgrid_desc *d) {
+    Allocator alloc;
+    RefMedium *rm = new RefMedium();
+    size_t n = size_t(d->nx) * d->ny * d->nz;
+    auto mk = [&](const float *v) {
+        std::vector<RGBUnboundedSpectrum> s(n);
+        for (size_t i = 0; i < n; ++i) {
+            s[i].scale = v[4 * i];
+            s[i].rsp = RGBSigmoidPolynomial(v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        }
+        return SampledGrid<RGBUnboundedSpectrum>(s, d->nx, d->ny, d->nz, alloc);
+    };
+    pstd::optional<SampledGrid<RGBUnboundedSpectrum>> ga, gs;
+    pstd::optional<SampledGrid<RGBIlluminantSpectrum>> gle;
+    if (d->sigma_a) ga = mk(d->sigma_a);
+    if (d->sigma_s) gs = mk(d->sigma_s);
+    if (d->le) {
+        DenselySampledSpectrum *ill = dense_from(d->le_illuminant);
+        rm->keep.push_back(ill);
+        std::vector<RGBIlluminantSpectrum> s(n);
+        for (size_t i = 0; i < n; ++i) {
+            s[i].scale = d->le[4 * i];
+            s[i].rsp = RGBSigmoidPolynomial(d->le[4 * i + 1], d->le[4 * i + 2], d->le[4 * i + 3]);
+            s[i].illuminant = ill;
+        }
+        gle = SampledGrid<RGBIlluminantSpectrum>(s, d->nx, d->ny, d->nz, alloc);
+    }
+    Transform xf = make_xf(d->render_from_medium, d->medium_from_render);
+    rm->rgb = new RGBGridMedium(Bounds3f(Point3f(d->p0[0], d->p0[1], d->p0[2]), Point3f(d->p1[0], d->p1[1], d->p1[2])),
+                                xf, d->g, std::move(ga), std::move(gs), d->sigma_scale, std::move(gle), d->le_scale,
+                                alloc);
+    rm->medium = rm->rgb;
+    return rm;
+}
+void ref_medium_destroy(void *m) { delete (RefMedium *)m; }
+int ref_medium_is_emissive(void *m) { return ((RefMedium *)m)->medium.IsEmissive() ? 1 : 0; }
+void ref_medium_majorants(void *mp, float *out, int32_t res[3]) {
+    RefMedium *rm = (RefMedium *)mp;
+    const MajorantGrid &g = rm->grid ? rm->grid->majorantGrid : rm->rgb->majorantGrid;
+    for (int i = 0; i < 3; ++i) res[i] = g.res[i];
+    for (size_t i = 0; i < g.voxels.size(); ++i) out[i] = g.voxels[i];
+}
+void ref_medium_sample_point(void *mp, const float *p, int64_t n, const float lambda[4], float *out) {
+    RefMedium *rm = (RefMedium *)mp;
+    SampledWavelengths swl = make_lambda(lambda);
+    for (int64_t i = 0; i < n; ++i) {
+        MediumProperties q = rm->medium.SamplePoint(Point3f(p[3 * i], p[3 * i + 1], p[3 * i + 2]), swl);
+        for (int k = 0; k < 4; ++k) {
+            out[12 * i + k] = q.sigma_a[k];
+            out[12 * i + 4 + k] = q.sigma_s[k];
+            out[12 * i + 8 + k] = q.Le[k];
+        }
+    }
+}
+// SampleRay prologue exactly as media.h:322-337 writes it (ApplyInverse + IntersectP)
+void ref_medium_ray_to_medium(void *mp, const float *rays, int64_t n, float *out) {
+    RefMedium *rm = (RefMedium *)mp;
+    const Transform &xf = rm->grid ? rm->grid->renderFromMedium : rm->rgb->renderFromMedium;
+    const Bounds3f &b = rm->grid ? rm->grid->bounds : rm->rgb->bounds;
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 7 * i;
+        Float raytMax = r[6];
+        Ray ray = xf.ApplyInverse(Ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5])), &raytMax);
+        Float t0 = 0, t1 = 0;
+        bool hit = b.IntersectP(ray.o, ray.d, raytMax, &t0, &t1);
+        float *q = out + 9 * i;
+        q[0] = ray.o.x; q[1] = ray.o.y; q[2] = ray.o.z; q[3] = ray.d.x; q[4] = ray.d.y; q[5] = ray.d.z;
+        q[6] = hit ? t0 : 0; q[7] = hit ? t1 : 0; q[8] = hit ? 1.f : 0.f;
+    }
+}
+
+// SampleT_maj (media.h:730-806) driven with the three callbacks the fork uses (bodies follow
+// src/graph/util.h:344-403 and cpu/integrators.cpp:1352-1380 statement by statement).
+void ref_sample_tmaj(void *mp, int mode, const float *rays, int64_t n, const uint64_t *rngs, const float *u,
+                     const float lambda[4], avr_tmaj_result *out) {
+    RefMedium *rm = (RefMedium *)mp;
+    SampledWavelengths swl = make_lambda(lambda);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 7 * i;
+        Ray ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5]), 0.f, rm->medium);
+        RNG rng(rngs[2 * i], rngs[2 * i + 1]);
+        avr_tmaj_result res;
+        res.t_event = -1;
+        res.event = 2;
+        res.n_fetch = 0;
+        res.n_seg = -1;  // the reference iterator does not expose a segment count
+        SampledSpectrum T_ray(1.f), r_l(1.f), r_u(1.f), T;
+        Vector3f dn = Normalize(ray.d);
+        if (mode == 0) {
+            float Tr = 1;
+            T = SampleT_maj(ray, r[6], u[i], rng, swl,
+                            [&](Point3f p, MediumProperties mp, SampledSpectrum sigma_maj, SampledSpectrum T_maj) {
+                                res.n_fetch++;
+                                SampledSpectrum sigma_n = ClampZero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                Tr *= sigma_n[0] / sigma_maj[0];
+                                if (Tr == 0) return false;
+                                return true;
+                            });
+            T_ray[0] = Tr;
+        } else if (mode == 1) {
+            T = SampleT_maj(ray, r[6], u[i], rng, swl,
+                            [&](Point3f p, MediumProperties mp, SampledSpectrum sigma_maj, SampledSpectrum T_maj) {
+                                res.n_fetch++;
+                                Float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                                Float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                                Float pNull = std::max<Float>(0, 1 - pAbsorb - pScatter);
+                                Float um = rng.Uniform<Float>();
+                                int md = SampleDiscrete({pAbsorb, pScatter, pNull}, um);
+                                if (md == 0 || md == 1) {
+                                    res.event = md;
+                                    // recover t from p = o + dn*t along the dominant axis
+                                    int ax = std::abs(dn.x) > std::abs(dn.y) ? (std::abs(dn.x) > std::abs(dn.z) ? 0 : 2)
+                                                                             : (std::abs(dn.y) > std::abs(dn.z) ? 1 : 2);
+                                    res.t_event = (p[ax] - ray.o[ax]) / dn[ax];
+                                    return false;
+                                }
+                                return true;
+                            });
+        } else {
+            T = SampleT_maj(ray, r[6], u[i], rng, swl,
+                            [&](Point3f p, MediumProperties mp, SampledSpectrum sigma_maj, SampledSpectrum T_maj) {
+                                res.n_fetch++;
+                                SampledSpectrum sigma_n = ClampZero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                Float pdf = T_maj[0] * sigma_maj[0];
+                                T_ray *= T_maj * sigma_n / pdf;
+                                r_l *= T_maj * sigma_maj / pdf;
+                                r_u *= T_maj * sigma_n / pdf;
+                                SampledSpectrum Tr = T_ray / (r_l + r_u).Average();
+                                if (Tr.MaxComponentValue() < 0.05f) {
+                                    Float q = 0.75f;
+                                    if (rng.Uniform<Float>() < q) T_ray = SampledSpectrum(0.);
+                                    else T_ray /= 1 - q;
+                                }
+                                if (!T_ray) return false;
+                                return true;
+                            });
+            T_ray *= T / T[0];
+            r_l *= T / T[0];
+            r_u *= T / T[0];
+        }
+        for (int k = 0; k < 4; ++k) { res.T_maj[k] = T[k]; res.Tr[k] = T_ray[k]; res.r_u[k] = r_u[k]; res.r_l[k] = r_l[k]; }
+        out[i] = res;
+    }
+}
+
+// Eigen SpMV exactly as LightingCalculator::ComputeFinalLight drives it
+// (src/graph/lighting_calculator.cpp:23-59, types from lighting_calculator.h).
+int ref_graph_propagate(int32_t n, int64_t nnz, const int64_t *rowptr, const int32_t *col, const float *val,
+                        const float *L0, int32_t bounces, float *total) {
+    using SparseMat = Eigen::SparseMatrix<float>;
+    using SparseVec = Eigen::SparseVector<float>;
+    std::vector<Eigen::Triplet<float>> entries;
+    for (int r = 0; r < n; ++r)
+        for (int64_t k = rowptr[r]; k < rowptr[r + 1]; ++k) entries.emplace_back(r, col[k], val[k]);
+    SparseMat T(n, n);
+    T.setFromTriplets(entries.begin(), entries.end());
+    SparseVec lightVec(n);
+    for (int i = 0; i < n; ++i) lightVec.coeffRef(i) = L0[i];
+    SparseVec totalLight(lightVec);
+    int curIteration = 0;
+    if (bounces > 0) {
+        SparseVec curLight = totalLight;
+        for (; curIteration < bounces; ++curIteration) {
+            curLight = T * curLight;
+            bool invalidNumbers = false;
+            for (int i = 0; i < n; ++i)
+                if (IsNaN(curLight.coeff(i)) || IsInf(curLight.coeff(i))) { invalidNumbers = true; break; }
+            if (invalidNumbers) break;
+            totalLight += curLight;
+        }
+    }
+    for (int i = 0; i < n; ++i) total[i] = totalLight.coeff(i);
+    return curIteration;
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

@@ -1,0 +1,34 @@
+// oracle/refprobe_stubs.cpp — TEST INFRASTRUCTURE ONLY.
+// Link-time stand-ins for the handful of reference symbols the hot-path templates reference but never
+// reach from the probe's entry points (logging, stats registry, a spectrum type the probe does not
+// construct).  Everything on the measured/parity path is the reference's own object code.
+#include <pbrt/util/log.h>
+#include <pbrt/util/print.h>
+#include <pbrt/util/spectrum.h>
+#include <pbrt/util/stats.h>
+
+#include <cstdio>
+#include <cstdlib>
+
+namespace pbrt {
+void LogFatal(LogLevel, const char *file, int line, const char *s) {
+    std::fprintf(stderr, "refprobe: reference CHECK failed at %s:%d: %s\n", file, line, s);
+    std::abort();
+}
+StatRegisterer::StatRegisterer(AccumFunc, PixelAccumFunc) {}
+void StatsAccumulator::ReportMemoryCounter(const char *, int64_t) {}
+Float PiecewiseLinearSpectrum::operator()(Float) const {
+    std::fprintf(stderr, "refprobe: PiecewiseLinearSpectrum is not part of the probe\n");
+    std::abort();
+}
+namespace detail {
+// only reached from ToString()/StringPrintf on error paths
+std::string FloatToString(float v) { return std::to_string(v); }
+void stringPrintfRecursive(std::string *s, const char *fmt) { *s += fmt; }
+std::string copyToFormatString(const char **fmt_ptr, std::string *s) {
+    *s += *fmt_ptr;
+    while (**fmt_ptr) ++*fmt_ptr;
+    return "%s";
+}
+}  // namespace detail
+}  // namespace pbrt

@@ -1,0 +1,247 @@
+// oracle/restate_volpath.hpp — TEST INFRASTRUCTURE ONLY (see restate.hpp header).
+// Volume-only subset of VolPathIntegrator (cpu/integrators.cpp:962-1106, :1282-1399),
+// RayIntegrator::EvaluatePixelSample (:235-298), GetCameraSample (samplers.h:797-814),
+// PerspectiveCamera::GenerateRayDifferential (cameras.cpp:429-460), PixelSensor::ToSensorRGB
+// (film.h:95-100) and RGBFilm::AddSample (film.h:239-255) for the scene class of include/avr.h
+// (one grid medium inside one convex "interface" boundary, one distant light).
+//
+// PARITY UNPINNED for Li/SampleLd as a whole (the reference's integrators.cpp cannot be compiled
+// without its cmake build); the primitives it is made of are pinned individually.
+// Deliberate restatement choices where the reference goes through its BVH / shape code:
+//  * boundary hits are analytic (sphere: quadratic in double; box: slab test) and the ray is
+//    re-spawned at o + d*tHit without pbrt's error-bound offset (interaction.cpp:91-97);
+//  * "IsInf(L.y(lambda))" (cpu/integrators.cpp:277) is evaluated as "any component of L is inf".
+#pragma once
+#include "restate_tmaj.hpp"
+
+namespace avro {
+
+struct Scene {
+    int width = 0, height = 0, spp = 1, max_depth = 5, sampler_seed = 0;
+    float filter_radius[2] = {0.5f, 0.5f};
+    Xform camera_from_raster, render_from_camera;  // only .m is used
+    V3 light_dir;                                  // wi towards the light, normalised
+    std::vector<float> light_spec;                 // NSPEC, includes scale
+    float scene_radius = 1;
+    int boundary_type = 0;
+    float boundary[6];
+    std::vector<float> sensor_rgb;  // 3*NSPEC
+    float imaging_ratio = 1;
+    float max_component = kInf;
+};
+
+struct RenderCounters {
+    int64_t camera_rays = 0, camera_fetches = 0, shadow_fetches = 0, segments = 0, scatter_events = 0;
+};
+
+// Distance range [t0,t1] of the ray inside the boundary; false if missed.
+inline bool boundary_hit(const Scene &sc, V3 o, V3 d, float *t0, float *t1) {
+    if (sc.boundary_type == 0) {
+        double ox = double(o.x) - sc.boundary[0], oy = double(o.y) - sc.boundary[1], oz = double(o.z) - sc.boundary[2];
+        double r = sc.boundary[3];
+        double a = double(d.x) * d.x + double(d.y) * d.y + double(d.z) * d.z;
+        double b = 2 * (ox * d.x + oy * d.y + oz * d.z);
+        double c = ox * ox + oy * oy + oz * oz - r * r;
+        double disc = b * b - 4 * a * c;
+        if (!(disc >= 0) || a == 0) return false;
+        double s = std::sqrt(disc);
+        double q = (b < 0) ? -0.5 * (b - s) : -0.5 * (b + s);
+        double ta = q / a, tb = (q != 0) ? c / q : ta;
+        if (ta > tb) std::swap(ta, tb);
+        *t0 = (float)ta;
+        *t1 = (float)tb;
+        return true;
+    }
+    float a0 = -kInf, a1 = kInf;
+    for (int i = 0; i < 3; ++i) {
+        float inv = 1 / d[i];
+        float tn = (sc.boundary[i] - o[i]) * inv, tf = (sc.boundary[3 + i] - o[i]) * inv;
+        if (tn > tf) std::swap(tn, tf);
+        a0 = tn > a0 ? tn : a0;
+        a1 = tf < a1 ? tf : a1;
+        if (a0 > a1) return false;
+    }
+    *t0 = a0;
+    *t1 = a1;
+    return true;
+}
+
+// VolPathIntegrator::SampleLd, medium-interaction branch, cpu/integrators.cpp:1282-1399
+inline Spec4 sample_ld(const Scene &sc, const Medium &med, V3 p, V3 wo, const float lambda[4],
+                       IndependentSampler &sampler, Spec4 beta, Spec4 r_p, RenderCounters *rc) {
+    float u = sampler.get1d();  // light choice: single light, p = 1
+    (void)u;
+    sampler.get1d();  // uLight
+    sampler.get1d();
+    // DistantLight::SampleLi, lights.h:284-291
+    V3 wi = sc.light_dir;
+    V3 pLight = p + wi * (2 * sc.scene_radius);
+    Spec4 Ll = sample_dense(sc.light_spec.data(), lambda);
+    if (!nonzero(Ll)) return spec(0.f);
+    float p_l = 1.f * 1.f;
+    float ph = henyey_greenstein(dot(wo, wi), med.g);  // HGPhaseFunction::p, media.h:51
+    Spec4 f_hat = spec(ph);
+    float scatterPDF = ph;
+    (void)scatterPDF;
+    if (!nonzero(f_hat)) return spec(0.f);
+    // Interaction::SpawnRayTo(pLight): medium interaction has n = 0 and exact pi -> o = p, d = pLight - p
+    V3 ro = p, rd = pLight - p;
+    Spec4 T_ray = spec(1.f), r_l = spec(1.f), r_u = spec(1.f);
+    RNG rng(hash_v3(ro), hash_v3(rd));
+    if (!(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
+        float t0, t1;
+        float tMax = 1 - kShadowEps;
+        if (boundary_hit(sc, ro, rd, &t0, &t1) && t1 > 0 && t1 < tMax) tMax = t1;
+        float uu = rng.uniform();
+        TmajCounters cnt;
+        Spec4 T_maj = sample_tmaj(med, ro, rd, tMax, uu, rng, lambda,
+                                  [&](V3, float, const MediumProps &mp, Spec4 sigma_maj, Spec4 T_maj) {
+                                      Spec4 sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                      float pdf = T_maj[0] * sigma_maj[0];
+                                      T_ray = T_ray * (T_maj * sigma_n / pdf);
+                                      r_l = r_l * (T_maj * sigma_maj / pdf);
+                                      r_u = r_u * (T_maj * sigma_n / pdf);
+                                      Spec4 Tr = T_ray / average(r_l + r_u);
+                                      if (max_component(Tr) < 0.05f) {
+                                          float q = 0.75f;
+                                          if (rng.uniform() < q) T_ray = spec(0.f);
+                                          else T_ray = T_ray / (1 - q);
+                                      }
+                                      return nonzero(T_ray);
+                                  }, &cnt);
+        if (rc) { rc->shadow_fetches += cnt.n_fetch; rc->segments += cnt.n_seg; }
+        T_ray = T_ray * (T_maj / T_maj[0]);
+        r_l = r_l * (T_maj / T_maj[0]);
+        r_u = r_u * (T_maj / T_maj[0]);
+        if (!nonzero(T_ray)) return spec(0.f);
+    }
+    r_l = r_l * (r_p * p_l);
+    // delta light: beta * f_hat * T_ray * ls->L / r_l.Average()
+    return beta * f_hat * T_ray * Ll / average(r_l);
+}
+
+// VolPathIntegrator::Li, cpu/integrators.cpp:962-1106, for a ray that starts outside the boundary.
+inline Spec4 volpath_li(const Scene &sc, const Medium &med, V3 ro, V3 rd, const float lambda[4],
+                        IndependentSampler &sampler, RenderCounters *rc) {
+    Spec4 L = spec(0.f), beta = spec(1.f), r_u = spec(1.f), r_l = spec(1.f);
+    int depth = 0;
+    float t0, t1;
+    if (!boundary_hit(sc, ro, rd, &t0, &t1) || t1 <= 0) return L;
+    if (t0 > 0) ro = ro + rd * t0;  // SkipIntersection at the entry hit
+    while (true) {
+        float tMax = kInf;
+        if (boundary_hit(sc, ro, rd, &t0, &t1) && t1 > 0) tMax = t1; else return L;
+        bool scattered = false, terminated = false;
+        uint64_t hash0 = hash_float(sampler.get1d());
+        uint64_t hash1 = hash_float(sampler.get1d());
+        RNG rng(hash0, hash1);
+        float u0 = sampler.get1d();
+        TmajCounters cnt;
+        V3 nro = ro, nrd = rd;
+        Spec4 T_maj = sample_tmaj(
+            med, ro, rd, tMax, u0, rng, lambda,
+            [&](V3 p, float, const MediumProps &mp, Spec4 sigma_maj, Spec4 T_maj) {
+                if (!nonzero(beta)) { terminated = true; return false; }
+                if (rc) rc->camera_fetches++;
+                if (depth < sc.max_depth && nonzero(mp.Le)) {
+                    float pdf = sigma_maj[0] * T_maj[0];
+                    Spec4 betap = beta * T_maj / pdf;
+                    Spec4 r_e = r_u * sigma_maj * T_maj / pdf;
+                    if (nonzero(r_e)) L = L + betap * mp.sigma_a * mp.Le / average(r_e);
+                }
+                float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                float pNull = std::max<float>(0, 1 - pAbsorb - pScatter);
+                float um = rng.uniform();
+                float w[3] = {pAbsorb, pScatter, pNull};
+                int mode = sample_discrete(w, 3, um);
+                if (mode == 0) { terminated = true; return false; }
+                if (mode == 1) {
+                    if (depth++ >= sc.max_depth) { terminated = true; return false; }
+                    float pdf = T_maj[0] * mp.sigma_s[0];
+                    beta = beta * (T_maj * mp.sigma_s / pdf);
+                    r_u = r_u * (T_maj * mp.sigma_s / pdf);
+                    if (nonzero(beta) && nonzero(r_u)) {
+                        if (rc) rc->scatter_events++;
+                        V3 wo = -rd;  // ray.d is the normalised direction inside SampleT_maj's caller
+                        L = L + sample_ld(sc, med, p, wo, lambda, sampler, beta, r_u, rc);
+                        float ua = sampler.get1d(), ub = sampler.get1d();
+                        float pdfp;
+                        V3 wi = sample_hg(wo, med.g, ua, ub, &pdfp);
+                        if (pdfp == 0) terminated = true;
+                        else {
+                            beta = beta * (pdfp / pdfp);  // ps->p / ps->pdf, both = pdf
+                            r_l = r_u / pdfp;
+                            scattered = true;
+                            nro = p;
+                            nrd = wi;
+                        }
+                    }
+                    return false;
+                }
+                Spec4 sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                float pdf = T_maj[0] * sigma_n[0];
+                beta = beta * (T_maj * sigma_n / pdf);
+                if (pdf == 0) beta = spec(0.f);
+                r_u = r_u * (T_maj * sigma_n / pdf);
+                r_l = r_l * (T_maj * sigma_maj / pdf);
+                return nonzero(beta) && nonzero(r_u);
+            }, &cnt);
+        if (rc) rc->segments += cnt.n_seg;
+        if (terminated || !nonzero(beta) || !nonzero(r_u)) return L;
+        if (scattered) { ro = nro; rd = nrd; continue; }
+        beta = beta * (T_maj / T_maj[0]);
+        r_u = r_u * (T_maj / T_maj[0]);
+        r_l = r_l * (T_maj / T_maj[0]);
+        // ray leaves the boundary: no infinite lights (a DistantLight is not one) -> done
+        break;
+    }
+    return L;
+}
+
+struct PixelSampleOut {
+    Spec4 L;
+    Lambda4 lambda;
+    float rgb[3];
+    float weight;
+};
+
+// RayIntegrator::EvaluatePixelSample, cpu/integrators.cpp:235-298
+inline PixelSampleOut evaluate_pixel_sample(const Scene &sc, const Medium &med, int px, int py, int sampleIndex,
+                                            RenderCounters *rc) {
+    IndependentSampler sampler;
+    sampler.seed = sc.sampler_seed;
+    sampler.start_pixel_sample(px, py, sampleIndex);
+    float lu = sampler.get1d();
+    PixelSampleOut out;
+    out.lambda = sample_visible_wavelengths(lu);
+    // GetCameraSample with BoxFilter::Sample (filters.h:67-70)
+    float f0 = sampler.get1d(), f1 = sampler.get1d();
+    float fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
+    float fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
+    float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
+    sampler.get1d();  // time
+    sampler.get1d();  // lens
+    sampler.get1d();
+    out.weight = 1;
+    V3 pCamera = apply_point(sc.camera_from_raster, {pfx, pfy, 0});
+    V3 dir = normalize(pCamera);
+    V3 ro, rd;
+    apply_ray(sc.render_from_camera, {0, 0, 0}, dir, nullptr, &ro, &rd);
+    if (rc) rc->camera_rays++;
+    Spec4 L = volpath_li(sc, med, ro, rd, out.lambda.lambda, sampler, rc);
+    if (has_nans(L)) L = spec(0.f);
+    else if (std::isinf(L[0]) || std::isinf(L[1]) || std::isinf(L[2]) || std::isinf(L[3])) L = spec(0.f);
+    out.L = L;
+    // PixelSensor::ToSensorRGB film.h:95-100
+    Spec4 pdf = {{out.lambda.pdf[0], out.lambda.pdf[1], out.lambda.pdf[2], out.lambda.pdf[3]}};
+    Spec4 Ld = safe_div(L, pdf);
+    for (int c = 0; c < 3; ++c)
+        out.rgb[c] = sc.imaging_ratio * average(sample_dense(sc.sensor_rgb.data() + c * NSPEC, out.lambda.lambda) * Ld);
+    // RGBFilm::AddSample clamp film.h:244-247
+    float m = std::max({out.rgb[0], out.rgb[1], out.rgb[2]});
+    if (m > sc.max_component) for (int c = 0; c < 3; ++c) out.rgb[c] *= sc.max_component / m;
+    return out;
+}
+
+}  // namespace avro

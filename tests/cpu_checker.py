@@ -1,0 +1,242 @@
+"""ctypes bindings for the CPU checkers (TEST INFRASTRUCTURE ONLY).
+
+`Checker("orc")` loads oracle/liboracle.so (the CPU restatement, always available after
+`make -C oracle`); `Checker("ref")` loads oracle/_ref/libavr_refprobe.so (the reference's own
+templates compiled from /root/reference; present in the build container and shipped to the GPU box
+as a built artefact).  Both export the same flat signatures (orc_* / ref_*).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from acceleratedvolrenderer_b200._abi import GridDesc, RGBGridDesc, RenderDesc, TMAJ_DTYPE
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORC_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
+REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libavr_refprobe.so")
+
+f32p = C.POINTER(C.c_float)
+i32p = C.POINTER(C.c_int32)
+u32p = C.POINTER(C.c_uint32)
+u64p = C.POINTER(C.c_uint64)
+i64p = C.POINTER(C.c_int64)
+f64p = C.POINTER(C.c_double)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+def f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def have_ref():
+    return os.path.exists(REF_PATH)
+
+
+class Checker:
+    def __init__(self, kind="orc"):
+        self.kind = kind
+        path = ORC_PATH if kind == "orc" else REF_PATH
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} missing: run `make -C oracle`")
+        self.lib = C.CDLL(path)
+        self.pfx = kind + "_"
+        for name in ("medium_create_uniformgrid", "medium_create_rgbgrid"):
+            getattr(self.lib, self.pfx + name).restype = C.c_void_p
+        self.fn("kind").restype = C.c_char_p
+
+    def fn(self, name):
+        return getattr(self.lib, self.pfx + name)
+
+    def has(self, name):
+        return hasattr(self.lib, self.pfx + name)
+
+    # ---- primitives ------------------------------------------------------------------------------
+    def fast_exp(self, x):
+        x = f32(x); out = np.empty_like(x)
+        self.fn("fast_exp")(_p(x, f32p), C.c_int64(x.size), _p(out, f32p))
+        return out
+
+    def mix_bits(self, x):
+        x = np.ascontiguousarray(x, dtype=np.uint64); out = np.empty_like(x)
+        self.fn("mix_bits")(_p(x, u64p), C.c_int64(x.size), _p(out, u64p))
+        return out
+
+    def hash_float(self, x):
+        x = f32(x); out = np.empty(x.size, dtype=np.uint64)
+        self.fn("hash_float")(_p(x, f32p), C.c_int64(x.size), _p(out, u64p))
+        return out
+
+    def hash_point3(self, x):
+        x = f32(x); n = x.size // 3; out = np.empty(n, dtype=np.uint64)
+        self.fn("hash_point3")(_p(x, f32p), C.c_int64(n), _p(out, u64p))
+        return out
+
+    def rng_stream(self, seq, seed, use_seed, adv, n):
+        u = np.empty(n, dtype=np.uint32); f = np.empty(n, dtype=np.float32)
+        self.fn("rng_stream")(C.c_uint64(seq), C.c_uint64(seed), C.c_int(use_seed), C.c_int64(adv), C.c_int64(n),
+                              _p(u, u32p), _p(f, f32p))
+        return u, f
+
+    def independent_sampler(self, px, py, seed, sample_index, dim, n):
+        out = np.empty(n, dtype=np.float32)
+        self.fn("independent_sampler")(C.c_int(px), C.c_int(py), C.c_int(seed), C.c_int(sample_index), C.c_int(dim),
+                                       C.c_int64(n), _p(out, f32p))
+        return out
+
+    def sample_discrete3(self, w, u):
+        w = f32(w); u = f32(u); out = np.empty(u.size, dtype=np.int32)
+        self.fn("sample_discrete3")(_p(w, f32p), _p(u, f32p), C.c_int64(u.size), _p(out, i32p))
+        return out
+
+    def sample_exponential(self, u, a):
+        u = f32(u); a = f32(a); out = np.empty_like(u)
+        self.fn("sample_exponential")(_p(u, f32p), _p(a, f32p), C.c_int64(u.size), _p(out, f32p))
+        return out
+
+    def hg_sample(self, wo, g, u):
+        wo = f32(wo); u = f32(u); n = wo.size // 3
+        wi = np.empty((n, 3), dtype=np.float32); pdf = np.empty(n, dtype=np.float32)
+        self.fn("hg_sample")(_p(wo, f32p), C.c_float(g), _p(u, f32p), C.c_int64(n), _p(wi, f32p), _p(pdf, f32p))
+        return wi, pdf
+
+    def hg_p(self, cos_theta, g):
+        c = f32(cos_theta); out = np.empty_like(c)
+        self.fn("hg_p")(_p(c, f32p), C.c_float(g), C.c_int64(c.size), _p(out, f32p))
+        return out
+
+    def sample_wavelengths(self, u):
+        u = f32(u); out = np.empty((u.size, 8), dtype=np.float32)
+        self.fn("sample_wavelengths")(_p(u, f32p), C.c_int64(u.size), _p(out, f32p))
+        return out
+
+    def blackbody(self, T, lam):
+        T = f32(T); lam = f32(lam); out = np.empty((T.size, 4), dtype=np.float32)
+        self.fn("blackbody")(_p(T, f32p), C.c_int64(T.size), _p(lam, f32p), _p(out, f32p))
+        return out
+
+    def grid_lookup(self, grid, p):
+        grid = f32(grid); p = f32(p); nz, ny, nx = grid.shape; n = p.size // 3
+        out = np.empty(n, dtype=np.float32)
+        self.fn("grid_lookup")(_p(grid, f32p), C.c_int(nx), C.c_int(ny), C.c_int(nz), _p(p, f32p), C.c_int64(n),
+                               _p(out, f32p))
+        return out
+
+    def dda(self, bounds, res, vox, rays, sigma_t=1.0, max_per_ray=200):
+        bounds = f32(bounds); res = np.ascontiguousarray(res, dtype=np.int32); vox = f32(vox); rays = f32(rays)
+        n = rays.size // 8
+        counts = np.zeros(n, dtype=np.int32)
+        seg_t = np.zeros((n, max_per_ray, 2), dtype=np.float32)
+        seg_s = np.zeros((n, max_per_ray), dtype=np.float32)
+        seg_v = np.full((n, max_per_ray), -1, dtype=np.int32)
+        self.fn("dda")(_p(bounds, f32p), _p(res, i32p), _p(vox, f32p), _p(rays, f32p), C.c_int64(n),
+                       C.c_float(sigma_t), C.c_int32(max_per_ray), _p(counts, i32p), _p(seg_t, f32p),
+                       _p(seg_s, f32p), _p(seg_v, i32p))
+        return counts, seg_t, seg_s, seg_v
+
+    def apply_inverse_ray(self, m, minv, rays7):
+        return self._xf_ray("apply_inverse_ray", m, minv, rays7)
+
+    def apply_ray(self, m, minv, rays7):
+        return self._xf_ray("apply_ray", m, minv, rays7)
+
+    def _xf_ray(self, name, m, minv, rays7):
+        m = f32(m); minv = f32(minv); rays7 = f32(rays7); n = rays7.size // 7
+        out = np.empty((n, 7), dtype=np.float32)
+        self.fn(name)(_p(m, f32p), _p(minv, f32p), _p(rays7, f32p), C.c_int64(n), _p(out, f32p))
+        return out
+
+    # ---- media -----------------------------------------------------------------------------------
+    def medium_uniformgrid(self, desc: GridDesc):
+        h = self.fn("medium_create_uniformgrid")(C.byref(desc.c))
+        return CheckerMedium(self, h, desc)
+
+    def medium_rgbgrid(self, desc: RGBGridDesc):
+        h = self.fn("medium_create_rgbgrid")(C.byref(desc.c))
+        return CheckerMedium(self, h, desc)
+
+    # ---- graph -----------------------------------------------------------------------------------
+    def graph_propagate(self, rowptr, col, val, L0, bounces):
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64); col = np.ascontiguousarray(col, dtype=np.int32)
+        val = f32(val); L0 = f32(L0); n = L0.size
+        total = np.empty(n, dtype=np.float32)
+        self.fn("graph_propagate").restype = C.c_int
+        it = self.fn("graph_propagate")(C.c_int32(n), C.c_int64(col.size), _p(rowptr, i64p), _p(col, i32p),
+                                        _p(val, f32p), _p(L0, f32p), C.c_int32(bounces), _p(total, f32p))
+        return total, it
+
+    def graph_connect(self, pos, light, search_range, vertex_radius, points):
+        pos = f32(pos); light = f32(light); points = f32(points); n = light.size; npts = points.size // 3
+        rng = None if search_range is None else f32(search_range)
+        out = np.empty(npts, dtype=np.float32)
+        self.fn("graph_connect")(C.c_int32(n), _p(pos, f32p), _p(light, f32p),
+                                 _p(rng, f32p) if rng is not None else None, C.c_float(vertex_radius),
+                                 _p(points, f32p), C.c_int64(npts), _p(out, f32p))
+        return out
+
+
+class CheckerMedium:
+    def __init__(self, ck, handle, desc):
+        self.ck, self.h, self.desc = ck, C.c_void_p(handle), desc
+
+    def close(self):
+        if self.h:
+            self.ck.fn("medium_destroy")(self.h)
+            self.h = None
+
+    def is_emissive(self):
+        return bool(self.ck.fn("medium_is_emissive")(self.h))
+
+    def majorants(self):
+        res = np.zeros(3, dtype=np.int32)
+        mr = self.desc.majorant_res
+        out = np.empty(max(int(np.prod(mr)), 4096), dtype=np.float32)
+        self.ck.fn("medium_majorants")(self.h, _p(out, f32p), _p(res, i32p))
+        return out[: int(np.prod(res))].reshape(res[2], res[1], res[0])
+
+    def sample_point(self, p, lam):
+        p = f32(p); lam = f32(lam); n = p.size // 3
+        out = np.empty((n, 12), dtype=np.float32)
+        self.ck.fn("medium_sample_point")(self.h, _p(p, f32p), C.c_int64(n), _p(lam, f32p), _p(out, f32p))
+        return out
+
+    def ray_to_medium(self, rays7):
+        rays7 = f32(rays7); n = rays7.size // 7
+        out = np.empty((n, 9), dtype=np.float32)
+        self.ck.fn("medium_ray_to_medium")(self.h, _p(rays7, f32p), C.c_int64(n), _p(out, f32p))
+        return out
+
+    def sample_tmaj(self, mode, rays7, rng, u, lam):
+        rays7 = f32(rays7); rng = np.ascontiguousarray(rng, dtype=np.uint64); u = f32(u); lam = f32(lam)
+        n = rays7.size // 7
+        out = np.zeros(n, dtype=TMAJ_DTYPE)
+        self.ck.fn("sample_tmaj")(self.h, C.c_int(mode), _p(rays7, f32p), C.c_int64(n), _p(rng, u64p), _p(u, f32p),
+                                  _p(lam, f32p), out.ctypes.data_as(C.c_void_p))
+        return out
+
+    # oracle-only (the reference's integrators.cpp cannot be built here)
+    def render_samples(self, rdesc: RenderDesc):
+        x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+        n = (x1 - x0) * (y1 - y0) * (s1 - s0)
+        out = np.empty((n, 12), dtype=np.float32)
+        stats = np.zeros(5, dtype=np.int64)
+        self.ck.fn("render_volpath_samples")(self.h, C.byref(rdesc.c), _p(out, f32p), _p(stats, i64p))
+        return out, stats
+
+    def render(self, rdesc: RenderDesc, threads=1, film=None):
+        if film is None:
+            film = np.zeros((rdesc.c.height, rdesc.c.width, 4), dtype=np.float64)
+        stats = np.zeros(5, dtype=np.int64)
+        self.ck.fn("render_volpath")(self.h, C.byref(rdesc.c), _p(film, f64p), C.c_int(threads), _p(stats, i64p))
+        return film, stats
+
+    def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):
+        rays6 = f32(rays6); pixel = np.ascontiguousarray(pixel, dtype=np.int32); ts = f32(ts); lam = f32(lam)
+        n = rays6.size // 6
+        out = np.empty(n, dtype=np.float32)
+        self.ck.fn("graph_light_rays")(self.h, _p(rays6, f32p), _p(pixel, i32p), _p(ts, f32p), C.c_int64(n),
+                                       C.c_int32(iterations), C.c_int32(seed), _p(lam, f32p), _p(out, f32p))
+        return out

@@ -1,0 +1,294 @@
+"""Host-side mirror of the reference's medium / integrator interface over the C ABI (include/avr.h).
+
+Names follow the reference: `Context.create_medium("uniformgrid" | "rgbgrid", ...)` is
+Medium::Create (media.cpp:667-689); `Medium.sample_point / sample_ray_segments / sample_t_maj`
+are Medium::SamplePoint / SampleRay+DDAMajorantIterator::Next / SampleT_maj (media.h);
+`Context.render("volpath" | "graph", ...)` is Integrator::Create(name)->Render()
+(cpu/integrators.cpp:3658-3700); `Graph.compute_final_light` is LightingCalculator::ComputeFinalLight.
+Every call goes through libavr_b200.so; a missing library or a non-zero avr_status raises
+(the reference ErrorExit()s) — nothing here computes on the CPU.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, RenderDesc, RGBGridDesc, avr_grid_desc, avr_render_desc,
+                   avr_render_stats, avr_rgbgrid_desc)
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
+
+LAYOUTS = {"dense": 0, "octet32": 1, "octet16": 2}
+TMAJ_RATIO, TMAJ_DELTA, TMAJ_SHADOW = 0, 1, 2
+
+f32p = C.POINTER(C.c_float)
+f64p = C.POINTER(C.c_double)
+i32p = C.POINTER(C.c_int32)
+i64p = C.POINTER(C.c_int64)
+u64p = C.POINTER(C.c_uint64)
+
+_lib = None
+
+# every symbol include/avr.h declares (tests check that the .so exports all of them)
+ABI_SYMBOLS = [
+    "avr_ctx_create", "avr_ctx_destroy", "avr_last_error", "avr_version",
+    "avr_medium_create_uniformgrid", "avr_medium_create_rgbgrid", "avr_medium_destroy", "avr_medium_is_emissive",
+    "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
+    "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
+    "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
+    "avr_graph_create", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
+    "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
+    "avr_render_graph", "avr_graph_light_rays",
+]
+
+
+class AvrError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"avr_status {status}: {msg}")
+        self.status = status
+
+
+def load_library():
+    """dlopen libavr_b200.so.  Raises if it has not been built — there is no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(make -C acceleratedvolrenderer_b200/csrc). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.avr_last_error.restype = C.c_char_p
+    lib.avr_last_error.argtypes = [C.c_void_p]
+    lib.avr_version.restype = C.c_char_p
+    lib.avr_medium_bytes.restype = C.c_int64
+    for name in ABI_SYMBOLS:
+        fn = getattr(lib, name)
+        if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
+                        "avr_graph_destroy"):
+            fn.restype = C.c_int
+    lib.avr_ctx_destroy.restype = None
+    lib.avr_medium_destroy.restype = None
+    lib.avr_graph_destroy.restype = None
+    _lib = lib
+    return lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _p(a, t=f32p):
+    return a.ctypes.data_as(t)
+
+
+class Context:
+    """One per GPU/process (avr_ctx)."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        st = self.lib.avr_ctx_create(C.c_int(device), C.byref(h))
+        if st != 0:
+            raise AvrError(st, self.lib.avr_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def check(self, st):
+        if st != 0:
+            raise AvrError(st, self.lib.avr_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.avr_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # Medium::Create(name, params...) — media.cpp:667-689
+    def create_medium(self, name, desc, layout="dense"):
+        h = C.c_void_p()
+        if name == "uniformgrid":
+            assert isinstance(desc, GridDesc)
+            self.check(self.lib.avr_medium_create_uniformgrid(self.h, C.byref(desc.c), C.c_int(LAYOUTS[layout]),
+                                                              C.byref(h)))
+        elif name == "rgbgrid":
+            assert isinstance(desc, RGBGridDesc)
+            self.check(self.lib.avr_medium_create_rgbgrid(self.h, C.byref(desc.c), C.byref(h)))
+        else:
+            # the reference: ErrorExit(loc, "%s: medium unknown.", name)
+            raise AvrError(1, f"{name}: medium unknown.")
+        return Medium(self, h, desc)
+
+    # Integrator::Create("volpath") -> Render(): returns the film [H, W, 4] float64 (rgbSum, weightSum)
+    def render_volpath(self, medium, rdesc: RenderDesc, film=None):
+        if film is None:
+            film = np.zeros((rdesc.c.height, rdesc.c.width, 4), dtype=np.float64)
+        stats = avr_render_stats()
+        self.check(self.lib.avr_render_volpath(self.h, medium.h, C.byref(rdesc.c), _p(film, f64p), C.byref(stats)))
+        return film, stats.as_dict()
+
+    def render_volpath_device(self, medium, rdesc: RenderDesc, film_dev_ptr, stream=None, want_stats=True):
+        stats = avr_render_stats()
+        self.check(self.lib.avr_render_volpath_device(self.h, medium.h, C.byref(rdesc.c), C.c_void_p(film_dev_ptr),
+                                                      C.c_void_p(stream or 0),
+                                                      C.byref(stats) if want_stats else None))
+        return stats.as_dict()
+
+    def render_volpath_samples(self, medium, rdesc: RenderDesc):
+        x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+        n = (x1 - x0) * (y1 - y0) * (s1 - s0)
+        out = np.zeros((n, 12), dtype=np.float32)
+        stats = avr_render_stats()
+        self.check(self.lib.avr_render_volpath_samples(self.h, medium.h, C.byref(rdesc.c), _p(out), C.byref(stats)))
+        return out, stats.as_dict()
+
+    def render_graph(self, medium, graph, rdesc: RenderDesc, world_from_render=None):
+        film = np.zeros((rdesc.c.height, rdesc.c.width, 4), dtype=np.float64)
+        wfr = _f32(np.eye(4) if world_from_render is None else world_from_render).ravel()
+        stats = avr_render_stats()
+        self.check(self.lib.avr_render_graph(self.h, medium.h, graph.h, C.byref(rdesc.c), _p(wfr), _p(film, f64p),
+                                             C.byref(stats)))
+        return film, stats.as_dict()
+
+    def film_resolve(self, rdesc: RenderDesc, film):
+        rgb = np.zeros((rdesc.c.height, rdesc.c.width, 3), dtype=np.float32)
+        film = np.ascontiguousarray(film, dtype=np.float64)
+        st = self.lib.avr_film_resolve(C.byref(rdesc.c), _p(film, f64p), _p(rgb))
+        if st != 0:
+            raise AvrError(st, "avr_film_resolve: bad argument")
+        return rgb
+
+    def create_graph(self, rowptr, col, val):
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        col = np.ascontiguousarray(col, dtype=np.int32)
+        val = _f32(val)
+        h = C.c_void_p()
+        self.check(self.lib.avr_graph_create(self.h, C.c_int32(rowptr.size - 1), C.c_int64(col.size), _p(rowptr, i64p),
+                                             _p(col, i32p), _p(val), C.byref(h)))
+        return Graph(self, h, rowptr.size - 1, col.size)
+
+
+class Medium:
+    def __init__(self, ctx, h, desc):
+        self.ctx, self.h, self.desc = ctx, h, desc
+        self.lib = ctx.lib
+
+    def close(self):
+        if self.h:
+            self.lib.avr_medium_destroy(self.h)
+            self.h = None
+
+    def is_emissive(self):  # Medium::IsEmissive
+        return bool(self.lib.avr_medium_is_emissive(self.h))
+
+    def bytes(self):
+        return int(self.lib.avr_medium_bytes(self.h))
+
+    def majorants(self):
+        mr = self.desc.majorant_res
+        out = np.empty(int(np.prod(mr)), dtype=np.float32)
+        res = np.zeros(3, dtype=np.int32)
+        self.ctx.check(self.lib.avr_medium_majorants(self.h, _p(out), _p(res, i32p)))
+        return out.reshape(res[2], res[1], res[0])
+
+    def lookup_density(self, p):
+        p = _f32(p); n = p.size // 3
+        out = np.empty(n, dtype=np.float32)
+        self.ctx.check(self.lib.avr_medium_lookup_density(self.h, _p(p), C.c_int64(n), _p(out)))
+        return out
+
+    def sample_point(self, p, lam):  # Medium::SamplePoint
+        p = _f32(p); lam = _f32(lam); n = p.size // 3
+        out = np.empty((n, 12), dtype=np.float32)
+        self.ctx.check(self.lib.avr_medium_sample_point(self.h, _p(p), C.c_int64(n), _p(lam), _p(out)))
+        return out
+
+    def ray_to_medium(self, rays7):
+        rays7 = _f32(rays7); n = rays7.size // 7
+        out = np.empty((n, 9), dtype=np.float32)
+        self.ctx.check(self.lib.avr_medium_ray_to_medium(self.h, _p(rays7), C.c_int64(n), _p(out)))
+        return out
+
+    def dda_segments(self, rays8, sigma_t=1.0, max_per_ray=200):  # DDAMajorantIterator
+        rays8 = _f32(rays8); n = rays8.size // 8
+        counts = np.zeros(n, dtype=np.int32)
+        seg_t = np.zeros((n, max_per_ray, 2), dtype=np.float32)
+        seg_s = np.zeros((n, max_per_ray), dtype=np.float32)
+        seg_v = np.full((n, max_per_ray), -1, dtype=np.int32)
+        self.ctx.check(self.lib.avr_dda_segments(self.h, _p(rays8), C.c_int64(n), C.c_float(sigma_t),
+                                                 C.c_int32(max_per_ray), _p(counts, i32p), _p(seg_t), _p(seg_s),
+                                                 _p(seg_v, i32p)))
+        return counts, seg_t, seg_s, seg_v
+
+    def sample_t_maj(self, mode, rays7, rng, u, lam):  # SampleT_maj
+        rays7 = _f32(rays7); rng = np.ascontiguousarray(rng, dtype=np.uint64); u = _f32(u); lam = _f32(lam)
+        n = rays7.size // 7
+        out = np.zeros(n, dtype=TMAJ_DTYPE)
+        self.ctx.check(self.lib.avr_sample_tmaj(self.h, C.c_int(mode), _p(rays7), C.c_int64(n), _p(rng, u64p), _p(u),
+                                                _p(lam), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def sample_t_maj_device(self, mode, exact, rays_ptr, n, rng_ptr, u_ptr, lam, out_ptr):
+        lam = _f32(lam)
+        self.ctx.check(self.lib.avr_sample_tmaj_device(self.h, C.c_int(mode), C.c_int(1 if exact else 0),
+                                                       C.c_void_p(rays_ptr), C.c_int64(n), C.c_void_p(rng_ptr),
+                                                       C.c_void_p(u_ptr), _p(lam), C.c_void_p(out_ptr)))
+
+    def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):
+        rays6 = _f32(rays6); pixel = np.ascontiguousarray(pixel, dtype=np.int32); ts = _f32(ts); lam = _f32(lam)
+        n = rays6.size // 6
+        out = np.empty(n, dtype=np.float32)
+        self.ctx.check(self.lib.avr_graph_light_rays(self.h, _p(rays6), _p(pixel, i32p), _p(ts), C.c_int64(n),
+                                                     C.c_int32(iterations), C.c_int32(seed), _p(lam), _p(out)))
+        return out
+
+
+class Graph:
+    def __init__(self, ctx, h, n, nnz):
+        self.ctx, self.h, self.n, self.nnz = ctx, h, n, nnz
+        self.lib = ctx.lib
+
+    def close(self):
+        if self.h:
+            self.lib.avr_graph_destroy(self.h)
+            self.h = None
+
+    def compute_final_light(self, L0, bounces):  # LightingCalculator::ComputeFinalLight
+        L0 = _f32(L0)
+        total = np.empty(self.n, dtype=np.float32)
+        it = C.c_int32(0)
+        self.ctx.check(self.lib.avr_graph_propagate(self.h, _p(L0), C.c_int32(bounces), _p(total), C.byref(it)))
+        return total, int(it.value)
+
+    def propagate_device(self, L0_ptr, bounces, total_ptr, stream=None, want_iters=False):
+        it = C.c_int32(-1)
+        self.ctx.check(self.lib.avr_graph_propagate_device(self.h, C.c_void_p(L0_ptr), C.c_int32(bounces),
+                                                           C.c_void_p(total_ptr), C.byref(it) if want_iters else None,
+                                                           C.c_void_p(stream or 0)))
+        return int(it.value)
+
+    def spmv_rows_device(self, cur_in_ptr, cur_out_ptr, r0, r1, flag_ptr, stream=None):
+        self.ctx.check(self.lib.avr_graph_spmv_rows_device(self.h, C.c_void_p(cur_in_ptr), C.c_void_p(cur_out_ptr),
+                                                           C.c_int32(r0), C.c_int32(r1), C.c_void_p(flag_ptr),
+                                                           C.c_void_p(stream or 0)))
+
+    def axpy_rows_device(self, cur_ptr, total_ptr, r0, r1, flag_ptr, stream=None):
+        self.ctx.check(self.lib.avr_graph_axpy_rows_device(self.h, C.c_void_p(cur_ptr), C.c_void_p(total_ptr),
+                                                           C.c_int32(r0), C.c_int32(r1), C.c_void_p(flag_ptr),
+                                                           C.c_void_p(stream or 0)))
+
+    def set_vertices(self, pos, light, search_range, vertex_radius):
+        pos = _f32(pos); light = _f32(light)
+        rng = None if search_range is None else _f32(search_range)
+        self.ctx.check(self.lib.avr_graph_set_vertices(self.h, _p(pos), _p(light), _p(rng) if rng is not None else None,
+                                                       C.c_float(vertex_radius)))
+
+    def connect(self, points):  # GraphIntegrator::ConnectToGraph
+        points = _f32(points); n = points.size // 3
+        out = np.empty(n, dtype=np.float32)
+        self.ctx.check(self.lib.avr_graph_connect(self.h, _p(points), C.c_int64(n), _p(out)))
+        return out

@@ -1,0 +1,276 @@
+// avr_graph.cu — kernel 3 and the graph-side kernels: radiance propagation (SpMV), graph lookup
+// (ConnectToGraph), graph rendering and the light-vector estimator.
+// Reference: src/graph/lighting_calculator.cpp:23-155, src/graph/graph_integrator.cpp:24-280,
+// src/graph/util.h:344-366,814-839.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "avr_render_host.h"
+
+using namespace avr;
+
+namespace avr {
+
+// ---- kernel 3: one propagation iteration -------------------------------------------------------------
+// cur_out = T * cur_in over rows [row_begin,row_end); optionally total += cur_in (the previous
+// iteration's result, valid because its NaN/Inf flag is final when this launch starts).
+// Layout: CSR (int64 rowptr, int32 col, fp32 val).  A CTA owns kRowsPerCta consecutive rows; their nnz
+// range is streamed through shared memory in coalesced 128-bit-friendly chunks as PRODUCTS
+// val[k]*x[col[k]], then each thread sums its own row's products in column order starting from 0 —
+// the exact summation order of Eigen's column-major SparseMatrix * SparseVector, so results are
+// bit-identical to the reference while every global access is coalesced.
+constexpr int kRowsPerCta = 256;
+constexpr int kChunk = 2048;
+
+// flags[0]: set to 1 when any NaN/Inf was produced; flags[1]: first bad iteration (atomicMin).
+__global__ void __launch_bounds__(kRowsPerCta)
+k_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ col, const float *__restrict__ val,
+       const float *__restrict__ x, float *__restrict__ y, float *__restrict__ total, int row_begin, int row_end,
+       int *flags, int iteration, int add_prev) {
+    __shared__ float s_prod[kChunk];
+    if (flags[0]) return;  // an earlier iteration was invalid: the reference has stopped
+    int r0 = row_begin + blockIdx.x * kRowsPerCta;
+    int r1 = min(r0 + kRowsPerCta, row_end);
+    int r = r0 + threadIdx.x;
+    bool have = r < r1;
+    int64_t rs = 0, re = 0;
+    if (have) { rs = rowptr[r]; re = rowptr[r + 1]; }
+    int64_t k0 = rowptr[r0], k1 = rowptr[r1];
+    float acc = 0;
+    for (int64_t c0 = k0; c0 < k1; c0 += kChunk) {
+        int64_t c1 = min(c0 + (int64_t)kChunk, k1);
+        for (int64_t k = c0 + threadIdx.x; k < c1; k += kRowsPerCta) s_prod[k - c0] = val[k] * __ldg(x + col[k]);
+        __syncthreads();
+        if (have) {
+            int64_t a = max(rs, c0), b = min(re, c1);
+            for (int64_t k = a; k < b; ++k) acc += s_prod[k - c0];
+        }
+        __syncthreads();
+    }
+    if (have) {
+        y[r] = acc;
+        if (isnan(acc) || isinf(acc)) {
+            atomicExch(&flags[0], 1);
+            atomicMin(&flags[1], iteration);
+        }
+        if (add_prev) total[r] += x[r];
+    }
+}
+
+// total[r] += cur[r] unless the iteration that produced cur was invalid.
+__global__ void k_axpy(const float *__restrict__ cur, float *__restrict__ total, int row_begin, int row_end,
+                       const int *flags) {
+    if (flags[0]) return;
+    int r = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < row_end) total[r] += cur[r];
+}
+
+// ---- ConnectToGraph over a uniform hash grid ------------------------------------------------------------
+struct GraphView {
+    const float4 *vert;   // x,y,z,lightScalar sorted by cell
+    const float *range2;  // renderSearchRange^2, same order (or null)
+    const int *cell_start;
+    int gres[3];
+    float gmin[3], inv_cell;
+    float sq_radius, perc99, max_range;
+    int use_range, n;
+};
+
+AVR_DEV bool graph_search(const GraphView &g, V3 p, float r2, bool filter, float *avg, float *wsum) {
+    float r = sqrtf(r2);
+    int lo[3], hi[3];
+    float pp[3] = {p.x, p.y, p.z};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        lo[i] = max(0, (int)floorf((pp[i] - r - g.gmin[i]) * g.inv_cell));
+        hi[i] = min(g.gres[i] - 1, (int)floorf((pp[i] + r - g.gmin[i]) * g.inv_cell));
+    }
+    float a = 0, w = 0;
+    bool any = false;
+    for (int z = lo[2]; z <= hi[2]; ++z)
+        for (int y = lo[1]; y <= hi[1]; ++y) {
+            int c0 = (z * g.gres[1] + y) * g.gres[0];
+            int s = g.cell_start[c0 + lo[0]], e = g.cell_start[c0 + hi[0] + 1];
+            for (int k = s; k < e; ++k) {
+                float4 v = __ldg(g.vert + k);
+                float dx = p.x - v.x, dy = p.y - v.y, dz = p.z - v.z;
+                float d2 = dx * dx + dy * dy + dz * dz;
+                if (d2 < r2) {
+                    if (filter && d2 > __ldg(g.range2 + k)) continue;
+                    float wt = 1.f / d2;
+                    a += v.w * wt;
+                    w += wt;
+                    any = true;
+                }
+            }
+        }
+    *avg = a;
+    *wsum = w;
+    return any;
+}
+// graph_integrator.cpp:249-280 (summation order differs from nanoflann's distance-sorted list:
+// parity is to 1e-5 relative, stated in the tests)
+AVR_DEV float connect_to_graph(const GraphView &g, V3 p) {
+    float a, w;
+    bool any = graph_search(g, p, g.sq_radius, false, &a, &w);
+    if (g.use_range && !any) {
+        any = graph_search(g, p, g.perc99, true, &a, &w);
+        if (!any) any = graph_search(g, p, g.max_range, true, &a, &w);
+    }
+    if (!any) return 0.f;
+    if (w == 0) return 0.f;
+    return a / w;
+}
+
+__global__ void k_graph_connect(GraphView g, const float *pts, int64_t n, float *out) {
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    out[i] = connect_to_graph(g, v3(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]));
+}
+
+// ---- light-vector estimator: ComputeRaysToSphere + SampleTransmittance ------------------------------
+template <typename TR>
+__global__ void __launch_bounds__(128)
+k_light_rays(MediumView mv, const float *rays, const int32_t *pixel, const float *ts, int64_t n, int iterations,
+             int seed, float l0, float l1, float l2, float l3, float *out) {
+    constexpr int N = TR::NCH;
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    float lambda[4] = {l0, l1, l2, l3};
+    LambdaCtx<N> lc = make_lambda_ctx<N>(mv, lambda);
+    const float *r = rays + 6 * i;
+    V3 o = v3(r[0], r[1], r[2]), d = v3(r[3], r[4], r[5]);
+    float average = 0, totalWeight = 0;
+    for (int it = 0; it < iterations; ++it) {
+        RNG srng;
+        srng.set_sequence(hash_3u32((uint32_t)pixel[2 * i], (uint32_t)pixel[2 * i + 1], (uint32_t)seed));
+        srng.advance((long long)it * 65536ll);
+        float curDist = ts[2 * i + 1] * srng.uniform();
+        float tMax = ts[2 * i] + curDist;
+        // unsequenced draws in the reference (util.h:346); GCC order: first draw -> offset
+        uint64_t h1 = hash_float(srng.uniform());
+        uint64_t h0 = hash_float(srng.uniform());
+        RNG rng;
+        rng.set_sequence(h0, h1);
+        float u = srng.uniform();
+        float Tr = 1;
+        TmajCount cnt = {0, 0};
+        sample_tmaj<TR>(mv, mv.maj, lc, o, d, tMax, u, rng,
+                        [&](float, const PropsN<N> &mp, Spec<N> sigma_maj, Spec<N>) {
+                            Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                            Tr *= sigma_n[0] / sigma_maj[0];
+                            return Tr != 0;
+                        }, &cnt);
+        average += Tr * 1.f;
+        totalWeight += 1.f;
+    }
+    out[i] = (iterations == 0 || totalWeight == 0) ? 0.f : average / totalWeight;
+}
+
+// ---- GraphIntegrator::Li, free-graph branch (graph_integrator.cpp:180-244) ---------------------------
+struct XfRows {
+    float a[12];
+};
+template <typename TR>
+__global__ void __launch_bounds__(128)
+k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *film) {
+    constexpr int N = TR::NCH;
+    long long npix = (long long)(rp.x1 - rp.x0) * (rp.y1 - rp.y0);
+    long long total = npix * (rp.s1 - rp.s0);
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    if ((i >> 5) % rp.world != rp.rank) return;
+    int s = rp.s0 + int(i / npix);
+    int pi = int(i % npix);
+    int px = rp.x0 + pi % (rp.x1 - rp.x0), py = rp.y0 + pi / (rp.x1 - rp.x0);
+    PathLane<TR> ln;  // reuse start-of-path arithmetic
+    ln.px = px; ln.py = py; ln.samp = s;
+    ln.srng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)rp.seed));
+    ln.srng.advance((long long)s * 65536ll);
+    float lu = ln.srng.uniform();
+    float pdf[4];
+    sample_visible_wavelengths(lu, ln.lambda, pdf);
+    LambdaCtx<N> lc = make_lambda_ctx<N>(mv, ln.lambda);
+    float f0 = ln.srng.uniform(), f1 = ln.srng.uniform();
+    float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
+    float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
+    ln.srng.uniform(); ln.srng.uniform(); ln.srng.uniform();
+    const float *c = rp.cfr;
+    float xp = c[0] * pfx + c[1] * pfy + c[2] * 0.f + c[3];
+    float yp = c[4] * pfx + c[5] * pfy + c[6] * 0.f + c[7];
+    float zp = c[8] * pfx + c[9] * pfy + c[10] * 0.f + c[11];
+    float wp = c[12] * pfx + c[13] * pfy + c[14] * 0.f + c[15];
+    V3 pc = v3(xp, yp, zp);
+    if (wp != 1) pc = pc / wp;
+    V3 dir = pc / sqrtf(sqr(pc.x) + sqr(pc.y) + sqr(pc.z));
+    V3 ro, rd;
+    xform_ray_exact(rp.rfc, true, v3(0, 0, 0), dir, nullptr, &ro, &rd);
+    float Lg = 0;
+    float t0, t1;
+    if (boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0) {
+        if (t0 > 0) ro = v3(ro.x + rd.x * t0, ro.y + rd.y * t0, ro.z + rd.z * t0);
+        if (boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0) {
+            uint64_t hash0 = hash_float(ln.srng.uniform());
+            uint64_t hash1 = hash_float(ln.srng.uniform());
+            RNG rng;
+            rng.set_sequence(hash0, hash1);
+            float u = ln.srng.uniform();
+            TmajCount cnt = {0, 0};
+            float len = sqrtf(sqr(rd.x) + sqr(rd.y) + sqr(rd.z));
+            V3 dn = rd / len;
+            sample_tmaj<TR>(mv, mv.maj, lc, ro, rd, t1, u, rng,
+                            [&](float t, const PropsN<N> &mp, Spec<N> sigma_maj, Spec<N>) {
+                                float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                                float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                                float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
+                                float um = rng.uniform();
+                                int md = sample_discrete3(pAbsorb, pScatter, pNull, um);
+                                if (md == 0) return false;
+                                if (md == 1) {
+                                    V3 p = v3(ro.x + dn.x * t, ro.y + dn.y * t, ro.z + dn.z * t);
+                                    // worldFromRender(p): Transform::operator()(Point3f)
+                                    const float *a = wfr.a;
+                                    V3 pw = v3(a[0] * p.x + a[1] * p.y + a[2] * p.z + a[3],
+                                               a[4] * p.x + a[5] * p.y + a[6] * p.z + a[7],
+                                               a[8] * p.x + a[9] * p.y + a[10] * p.z + a[11]);
+                                    Lg += connect_to_graph(g, pw);
+                                    return false;
+                                }
+                                return true;
+                            }, &cnt);
+        }
+    }
+    // spectrum * L (graph_integrator.cpp:243), then the film path of avr_render_volpath
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ln.L[k] = sample_dense1(rp.light_spec, ln.lambda[k]) * Lg;
+    RenderParams rpl = rp;
+    rpl.dump_samples = 0;
+    // inline copy of finish_path's film branch
+    float rgb[3];
+    float Ld[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        bool bad = isnan(ln.L[k]) || isinf(ln.L[k]);
+        Ld[k] = (pdf[k] != 0 && !bad) ? ln.L[k] / pdf[k] : 0.f;
+    }
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        float sacc = sample_dense1(rp.sensor + ch * kNSpec, ln.lambda[0]) * Ld[0];
+#pragma unroll
+        for (int k = 1; k < 4; ++k) sacc += sample_dense1(rp.sensor + ch * kNSpec, ln.lambda[k]) * Ld[k];
+        rgb[ch] = rp.imaging_ratio * (sacc / 4);
+    }
+    float m = fmaxf(rgb[0], fmaxf(rgb[1], rgb[2]));
+    if (m > rp.max_component) { float k = rp.max_component / m; rgb[0] *= k; rgb[1] *= k; rgb[2] *= k; }
+    double *pxl = film + 4 * ((size_t)py * rp.width + px);
+    atomicAdd(pxl + 0, (double)rgb[0]);
+    atomicAdd(pxl + 1, (double)rgb[1]);
+    atomicAdd(pxl + 2, (double)rgb[2]);
+    atomicAdd(pxl + 3, 1.0);
+}
+
+}  // namespace avr
+
+#include "avr_graph_host.inc"

@@ -1,0 +1,62 @@
+// avr_internal.h — host-side objects behind the opaque handles of include/avr.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/avr.h"
+#include "avr_medium.cuh"
+
+struct avr_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    std::string err;
+    // render scratch (grown on demand)
+    unsigned long long *d_counters = nullptr;  // work counter + stats
+    double *d_film = nullptr;
+    size_t film_bytes = 0;
+    float *d_tables = nullptr;  // light spectrum + sensor tables for the current render
+};
+
+struct avr_medium {
+    avr_ctx *ctx = nullptr;
+    avr::MediumView view{};
+    std::vector<void *> allocs;
+    int64_t bytes = 0;
+    float *d_maj = nullptr;
+    int mres[3] = {16, 16, 16};
+};
+
+struct avr_graph {
+    avr_ctx *ctx = nullptr;
+    int32_t n = 0;
+    int64_t nnz = 0;
+    int64_t *d_rowptr = nullptr;
+    int32_t *d_col = nullptr;
+    float *d_val = nullptr;
+    float *d_cur = nullptr, *d_nxt = nullptr, *d_total = nullptr;
+    int32_t *d_flag = nullptr;
+    // vertices + uniform hash grid for ConnectToGraph
+    float4 *d_vert = nullptr;     // x,y,z,lightScalar  (sorted by cell)
+    float *d_range2 = nullptr;    // renderSearchRange^2 (sorted by cell) or null
+    int32_t *d_vid = nullptr;     // original vertex id (sorted by cell)
+    int32_t *d_cell_start = nullptr;
+    int gres[3] = {0, 0, 0};
+    float gmin[3] = {0, 0, 0}, cell = 0;
+    float sq_radius = 0, perc99 = 0, max_range = -1;
+    bool use_range = false;
+};
+
+namespace avr {
+avr_status set_err(avr_ctx *ctx, avr_status code, const std::string &msg);
+avr_status set_cuda_err(avr_ctx *ctx, cudaError_t e, const char *what);
+}  // namespace avr
+
+#define AVR_CUDA(ctx, call)                                                   \
+    do {                                                                      \
+        cudaError_t e__ = (call);                                             \
+        if (e__ != cudaSuccess) return avr::set_cuda_err((ctx), e__, #call);  \
+    } while (0)

@@ -1,0 +1,357 @@
+// avr_lib.cu — context, media (upload, majorant-grid build, octet packing) and the small query
+// kernels behind include/avr.h.  sm_100a only; no CPU fallback: without a CUDA device every entry
+// point fails with AVR_ERR_CUDA.
+#include <cuda_fp16.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "avr_internal.h"
+#include "avr_tmaj.cuh"
+
+using namespace avr;
+
+#define AVR_STR2(x) #x
+#define AVR_STR(x) AVR_STR2(x)
+
+static thread_local std::string g_create_err;
+
+namespace avr {
+avr_status set_err(avr_ctx *ctx, avr_status code, const std::string &msg) {
+    if (ctx) ctx->err = msg; else g_create_err = msg;
+    return code;
+}
+avr_status set_cuda_err(avr_ctx *ctx, cudaError_t e, const char *what) {
+    std::string m = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+    cudaGetLastError();
+    return set_err(ctx, e == cudaErrorMemoryAllocation ? AVR_ERR_OOM : AVR_ERR_CUDA, m);
+}
+}  // namespace avr
+
+extern "C" const char *avr_version(void) { return "avr_b200 0.1 sm_100a (CUDA " AVR_STR(CUDART_VERSION) ")"; }
+
+extern "C" const char *avr_last_error(const avr_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
+    if (!out) return set_err(nullptr, AVR_ERR_BAD_ARG, "avr_ctx_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return set_err(nullptr, AVR_ERR_CUDA,
+                       std::string("avr_ctx_create: no CUDA device (") + cudaGetErrorString(e) +
+                           "); libavr_b200 has no CPU fallback");
+    if (device < 0 || device >= count) return set_err(nullptr, AVR_ERR_BAD_ARG, "avr_ctx_create: bad device index");
+    avr_ctx *ctx = new avr_ctx();
+    ctx->device = device;
+    AVR_CUDA(nullptr, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    AVR_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    AVR_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    AVR_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
+    AVR_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    AVR_CUDA(nullptr, cudaMalloc(&ctx->d_counters, 64 * sizeof(unsigned long long)));
+    AVR_CUDA(nullptr, cudaMalloc(&ctx->d_tables, 4 * kNSpec * sizeof(float)));
+    *out = ctx;
+    return AVR_OK;
+}
+
+extern "C" void avr_ctx_destroy(avr_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_counters);
+    cudaFree(ctx->d_film);
+    cudaFree(ctx->d_tables);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+// ---- build kernels -----------------------------------------------------------------------------------
+// MajorantGrid construction, media.cpp:240-246 (GridMedium) / :364-377 (RGBGridMedium):
+// one CTA per majorant voxel, max over the density voxels SampledGrid::MaxValue(bounds) visits
+// (util/containers.h:838-858).  Bit-exact: only IEEE divisions/multiplications feed the index box.
+template <bool RGB>
+__global__ void k_build_majorants(MediumView mv, float *out) {
+    __shared__ float sm[32];
+    int mx = blockIdx.x, my = blockIdx.y, mz = blockIdx.z;
+    int r[3] = {mv.mres[0], mv.mres[1], mv.mres[2]};
+    int n[3] = {mv.nx, mv.ny, mv.nz};
+    int idx[3] = {mx, my, mz};
+    int lo[3], hi[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float b0 = float(idx[i]) / r[i], b1 = float(idx[i] + 1) / r[i];  // MajorantGrid::VoxelBounds
+        float p0 = b0 * n[i] - .5f, p1 = b1 * n[i] - .5f;
+        lo[i] = max((int)floorf(p0), 0);
+        hi[i] = min((int)floorf(p1) + 1, n[i] - 1);
+    }
+    auto value = [&](const float4 *gr, int x, int y, int z) -> float {
+        if ((unsigned)x >= (unsigned)mv.nx || (unsigned)y >= (unsigned)mv.ny || (unsigned)z >= (unsigned)mv.nz) return 0.f;
+        float4 v = gr[(size_t(z) * mv.ny + y) * mv.nx + x];
+        // RGBUnboundedSpectrum::MaxValue = scale * RGBSigmoidPolynomial::MaxValue (util/color.h:346-352)
+        float result = fmaxf(rsp_eval(v.y, v.z, v.w, 360.f), rsp_eval(v.y, v.z, v.w, 830.f));
+        float lambda = -v.z / (2 * v.y);
+        if (lambda >= 360 && lambda <= 830) result = fmaxf(result, rsp_eval(v.y, v.z, v.w, lambda));
+        return v.x * result;
+    };
+    auto box_max = [&](const float *dense, const float4 *gr) -> float {
+        float m = RGB ? value(gr, lo[0], lo[1], lo[2]) : dense_at(dense, mv.nx, mv.ny, mv.nz, lo[0], lo[1], lo[2]);
+        int ex = hi[0] - lo[0] + 1, ey = hi[1] - lo[1] + 1, ez = hi[2] - lo[2] + 1;
+        if (ex > 0 && ey > 0 && ez > 0) {
+            int tot = ex * ey * ez;
+            for (int i = threadIdx.x; i < tot; i += blockDim.x) {
+                int x = lo[0] + i % ex, y = lo[1] + (i / ex) % ey, z = lo[2] + i / (ex * ey);
+                float v = RGB ? value(gr, x, y, z) : dense[(size_t(z) * mv.ny + y) * mv.nx + x];
+                m = fmaxf(m, v);
+            }
+        }
+        // block max
+        __syncthreads();
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+        __syncthreads();
+        int nw = (blockDim.x + 31) >> 5;
+        float r2 = sm[0];
+        for (int w = 1; w < nw; ++w) r2 = fmaxf(r2, sm[w]);
+        __syncthreads();
+        return r2;
+    };
+    float res;
+    if (RGB) {
+        float ma = mv.rgb_a ? box_max(nullptr, mv.rgb_a) : 1.f;
+        float ms = mv.rgb_s ? box_max(nullptr, mv.rgb_s) : 1.f;
+        res = mv.sigma_scale * (ma + ms);
+    } else
+        res = box_max(mv.dense, nullptr);
+    if (threadIdx.x == 0) out[mx + r[0] * (my + r[1] * mz)] = res;
+}
+
+// Octet packing: one thread per interpolation cell (cx,cy,cz) in [0,nx]x[0,ny]x[0,nz]
+// (cell c covers taps c-1 and c); bricks beyond the lattice edge are zero-filled by the memset.
+template <bool HALF>
+__global__ void k_pack_octets(MediumView mv, float4 *out32, uint4 *out16) {
+    size_t ncx = mv.nx + 1, ncy = mv.ny + 1, ncz = mv.nz + 1;
+    size_t total = ncx * ncy * ncz;
+    for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+        int cx = int(i % ncx), cy = int((i / ncx) % ncy), cz = int(i / (ncx * ncy));
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            v[k] = dense_at(mv.dense, mv.nx, mv.ny, mv.nz, cx - 1 + (k & 1), cy - 1 + ((k >> 1) & 1), cz - 1 + (k >> 2));
+        size_t o = octet_index(cx, cy, cz, mv.nbx, mv.nby);
+        if (HALF) {
+            __half2 h0 = __floats2half2_rn(v[0], v[1]), h1 = __floats2half2_rn(v[2], v[3]);
+            __half2 h2 = __floats2half2_rn(v[4], v[5]), h3 = __floats2half2_rn(v[6], v[7]);
+            uint4 q;
+            q.x = *reinterpret_cast<uint32_t *>(&h0);
+            q.y = *reinterpret_cast<uint32_t *>(&h1);
+            q.z = *reinterpret_cast<uint32_t *>(&h2);
+            q.w = *reinterpret_cast<uint32_t *>(&h3);
+            out16[o] = q;
+        } else {
+            out32[2 * o] = make_float4(v[0], v[1], v[2], v[3]);
+            out32[2 * o + 1] = make_float4(v[4], v[5], v[6], v[7]);
+        }
+    }
+}
+
+// ---- medium creation ---------------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+avr_status upload(avr_medium *m, const T *host, size_t count, const T **dev) {
+    void *d = nullptr;
+    AVR_CUDA(m->ctx, cudaMalloc(&d, count * sizeof(T)));
+    m->allocs.push_back(d);
+    m->bytes += int64_t(count * sizeof(T));
+    AVR_CUDA(m->ctx, cudaMemcpyAsync(d, host, count * sizeof(T), cudaMemcpyHostToDevice, m->ctx->stream));
+    *dev = (const T *)d;
+    return AVR_OK;
+}
+
+bool affine_rows(const float m16[16], float out12[12]) {
+    if (m16[12] != 0.f || m16[13] != 0.f || m16[14] != 0.f || m16[15] != 1.f) return false;
+    std::memcpy(out12, m16, 12 * sizeof(float));
+    return true;
+}
+
+// FAST-path folding: s_i = ((minv_i . p) - bmin_i) / (bmax_i - bmin_i) * n_i - .5
+void fold_grid_from_render(MediumView &v) {
+    int n[3] = {v.nx, v.ny, v.nz};
+    for (int i = 0; i < 3; ++i) {
+        double ext = double(v.bmax[i]) - double(v.bmin[i]);
+        double s = (ext > 0 ? 1.0 / ext : 1.0) * n[i];
+        for (int j = 0; j < 3; ++j) v.gfr[4 * i + j] = float(double(v.minv[4 * i + j]) * s);
+        v.gfr[4 * i + 3] = float((double(v.minv[4 * i + 3]) - double(v.bmin[i])) * s - 0.5);
+    }
+}
+
+avr_status finish_common(avr_medium *m, const float p0[3], const float p1[3], const float rfm[16],
+                         const float mfr[16], const int32_t mres_in[3]) {
+    MediumView &v = m->view;
+    for (int i = 0; i < 3; ++i) {
+        v.bmin[i] = p0[i];
+        v.bmax[i] = p1[i];
+        m->mres[i] = v.mres[i] = mres_in[i] > 0 ? mres_in[i] : 16;
+    }
+    if (!affine_rows(rfm, v.m) || !affine_rows(mfr, v.minv))
+        return set_err(m->ctx, AVR_ERR_UNSUPPORTED, "medium transform must be affine (last row 0 0 0 1)");
+    fold_grid_from_render(v);
+    size_t nm = size_t(v.mres[0]) * v.mres[1] * v.mres[2];
+    AVR_CUDA(m->ctx, cudaMalloc(&m->d_maj, nm * sizeof(float)));
+    m->allocs.push_back(m->d_maj);
+    v.maj = m->d_maj;
+    return AVR_OK;
+}
+
+void free_medium(avr_medium *m) {
+    if (!m) return;
+    cudaSetDevice(m->ctx->device);
+    for (void *p : m->allocs) cudaFree(p);
+    delete m;
+}
+
+}  // namespace
+
+extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid_desc *d, int layout,
+                                                    avr_medium **out) {
+    if (!ctx || !d || !out) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_medium_create_uniformgrid: NULL argument");
+    *out = nullptr;
+    // reference error behaviour: GridMedium::Create ErrorExit()s on these (media.cpp:252-270)
+    if (!d->density) return set_err(ctx, AVR_ERR_BAD_ARG, "No \"density\" value provided for grid medium.");
+    if (d->nx < 1 || d->ny < 1 || d->nz < 1) return set_err(ctx, AVR_ERR_BAD_ARG, "grid medium: nx, ny, nz must be >= 1");
+    if (!d->sigma_a || !d->sigma_s) return set_err(ctx, AVR_ERR_BAD_ARG, "grid medium: sigma_a / sigma_s tables missing");
+    if (d->le && d->temperature)
+        return set_err(ctx, AVR_ERR_BAD_ARG, "Both \"Le\" and \"temperature\" values were provided.");
+    if (layout < 0 || layout > 2) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    avr_medium *m = new avr_medium();
+    m->ctx = ctx;
+    MediumView &v = m->view;
+    v.kind = KIND_GRID;
+    v.layout = layout;
+    v.nx = d->nx; v.ny = d->ny; v.nz = d->nz;
+    size_t n = size_t(d->nx) * d->ny * d->nz;
+    avr_status st;
+#define TRY(x) do { st = (x); if (st != AVR_OK) { free_medium(m); return st; } } while (0)
+    TRY(upload(m, d->density, n, &v.dense));
+    if (d->temperature) TRY(upload(m, d->temperature, n, &v.temperature));
+    v.has_temperature = d->temperature != nullptr;
+    if (d->lescale) {  // media.cpp:295-306: LeScale[i] *= LeNorm
+        std::vector<float> ls(d->lescale, d->lescale + n);
+        for (float &x : ls) x *= d->le_norm;
+        TRY(upload(m, ls.data(), n, &v.lescale));
+        AVR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        v.lnx = d->nx; v.lny = d->ny; v.lnz = d->nz;
+    } else {
+        float one = d->le_norm;
+        TRY(upload(m, &one, 1, &v.lescale));
+        AVR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        v.lnx = v.lny = v.lnz = 1;
+    }
+    std::vector<float> sa(d->sigma_a, d->sigma_a + kNSpec), ss(d->sigma_s, d->sigma_s + kNSpec), le(kNSpec, 0.f);
+    for (float &x : sa) x *= d->sigma_scale;  // DenselySampledSpectrum::Scale, media.cpp:229-230
+    for (float &x : ss) x *= d->sigma_scale;
+    if (d->le) le.assign(d->le, d->le + kNSpec);
+    float leMax = le[0];
+    bool achro = true;
+    for (int i = 0; i < kNSpec; ++i) {
+        leMax = std::fmax(leMax, le[i]);
+        if (sa[i] != sa[0] || ss[i] != ss[0]) achro = false;
+    }
+    v.emissive = v.has_temperature ? 1 : (leMax > 0 ? 1 : 0);  // media.cpp:238
+    v.achromatic = achro ? 1 : 0;
+    TRY(upload(m, sa.data(), (size_t)kNSpec, &v.sigma_a_spec));
+    TRY(upload(m, ss.data(), (size_t)kNSpec, &v.sigma_s_spec));
+    TRY(upload(m, le.data(), (size_t)kNSpec, &v.le_spec));
+    AVR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    v.g = d->g;
+    v.temp_offset = d->temperature_offset;
+    v.temp_scale = d->temperature_scale;
+    v.sigma_scale = 1.f;
+    TRY(finish_common(m, d->p0, d->p1, d->render_from_medium, d->medium_from_render, d->majorant_res));
+    k_build_majorants<false><<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, m->d_maj);
+    AVR_CUDA(ctx, cudaGetLastError());
+    if (layout != LAYOUT_DENSE_F32) {
+        v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
+        size_t cells = size_t(v.nbx) * v.nby * v.nbz * 64;
+        size_t bytes = cells * (layout == LAYOUT_OCTET_F32 ? 32 : 16);
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "cudaMalloc(octets)"); }
+        m->allocs.push_back(p);
+        m->bytes += int64_t(bytes);
+        AVR_CUDA(ctx, cudaMemsetAsync(p, 0, bytes, ctx->stream));
+        int blocks = ctx->sm_count * 8;
+        if (layout == LAYOUT_OCTET_F32) {
+            v.oct32 = (const float4 *)p;
+            k_pack_octets<false><<<blocks, 256, 0, ctx->stream>>>(v, (float4 *)p, nullptr);
+        } else {
+            v.oct16 = (const uint4 *)p;
+            k_pack_octets<true><<<blocks, 256, 0, ctx->stream>>>(v, nullptr, (uint4 *)p);
+        }
+        AVR_CUDA(ctx, cudaGetLastError());
+    }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "medium build"); }
+    *out = m;
+    return AVR_OK;
+}
+
+extern "C" avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_desc *d, avr_medium **out) {
+    if (!ctx || !d || !out) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_medium_create_rgbgrid: NULL argument");
+    *out = nullptr;
+    // RGBGridMedium::Create, media.cpp:386-407
+    if (!d->sigma_a && !d->sigma_s)
+        return set_err(ctx, AVR_ERR_BAD_ARG, "RGB grid requires \"sigma_a\" and/or \"sigma_s\" parameter values.");
+    if (d->le && !d->sigma_a) return set_err(ctx, AVR_ERR_BAD_ARG, "RGB grid requires \"sigma_a\" if \"Le\" value provided.");
+    if (d->le && !d->le_illuminant) return set_err(ctx, AVR_ERR_BAD_ARG, "rgbgrid: le_illuminant table missing");
+    if (d->nx < 1 || d->ny < 1 || d->nz < 1) return set_err(ctx, AVR_ERR_BAD_ARG, "rgbgrid: nx, ny, nz must be >= 1");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    avr_medium *m = new avr_medium();
+    m->ctx = ctx;
+    MediumView &v = m->view;
+    v.kind = KIND_RGB;
+    v.layout = LAYOUT_DENSE_F32;
+    v.nx = d->nx; v.ny = d->ny; v.nz = d->nz;
+    size_t n = size_t(d->nx) * d->ny * d->nz;
+    avr_status st;
+    if (d->sigma_a) TRY(upload(m, (const float4 *)d->sigma_a, n, &v.rgb_a));
+    if (d->sigma_s) TRY(upload(m, (const float4 *)d->sigma_s, n, &v.rgb_s));
+    if (d->le) {
+        TRY(upload(m, (const float4 *)d->le, n, &v.rgb_le));
+        TRY(upload(m, d->le_illuminant, (size_t)kNSpec, &v.le_illum));
+    }
+    v.le_scale = d->le_scale;
+    v.sigma_scale = d->sigma_scale;
+    v.g = d->g;
+    v.emissive = (d->le && d->le_scale > 0) ? 1 : 0;  // media.h:374
+    v.achromatic = 0;
+    TRY(finish_common(m, d->p0, d->p1, d->render_from_medium, d->medium_from_render, d->majorant_res));
+    k_build_majorants<true><<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, m->d_maj);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "rgb medium build"); }
+    *out = m;
+    return AVR_OK;
+#undef TRY
+}
+
+extern "C" void avr_medium_destroy(avr_medium *m) { free_medium(m); }
+extern "C" int avr_medium_is_emissive(const avr_medium *m) { return m ? m->view.emissive : 0; }
+extern "C" int64_t avr_medium_bytes(const avr_medium *m) { return m ? m->bytes : 0; }
+
+extern "C" avr_status avr_medium_majorants(avr_medium *m, float *out, int32_t res[3]) {
+    if (!m || !out || !res) return set_err(m ? m->ctx : nullptr, AVR_ERR_BAD_ARG, "avr_medium_majorants: NULL argument");
+    AVR_CUDA(m->ctx, cudaSetDevice(m->ctx->device));
+    for (int i = 0; i < 3; ++i) res[i] = m->mres[i];
+    size_t nm = size_t(m->mres[0]) * m->mres[1] * m->mres[2];
+    AVR_CUDA(m->ctx, cudaMemcpy(out, m->d_maj, nm * sizeof(float), cudaMemcpyDeviceToHost));
+    return AVR_OK;
+}
+
+#include "avr_queries.inc"

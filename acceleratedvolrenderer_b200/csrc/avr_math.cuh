@@ -1,0 +1,303 @@
+// avr_math.cuh — device-side arithmetic of the volumetric hot path (sm_100a).
+//
+// The library is compiled with -fmad=false: a plain C expression is never contracted, so the
+// EXACT code paths reproduce the reference's CPU rounding (built -ffp-contract=off) operation by
+// operation; every FMA below is deliberate (__fmaf_rn), either because the reference itself calls
+// std::fma (FastExp / EvaluatePolynomial, util/math.h:329-337,450-475) or because the path is the
+// FAST variant (which mirrors the reference's own GPU branch, util/math.h:451-452, and is allowed to
+// re-associate).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace avr {
+
+#define AVR_DEV __device__ __forceinline__
+#define AVR_HD __host__ __device__ __forceinline__
+
+constexpr int kNSpec = 471;
+constexpr float kOneMinusEps = 0x1.fffffep-1f;
+constexpr float kMachEps = 0x1p-24f;
+constexpr float kGamma3 = (3 * kMachEps) / (1 - 3 * kMachEps);  // util/float.h:195-197
+constexpr float kPi = 3.14159265358979323846f;
+constexpr float kInv4Pi = 0.07957747154594766788f;
+constexpr float kShadowEps = 0.0001f;
+constexpr float kFltMax = 3.402823466e+38f;
+
+struct V3 {
+    float x, y, z;
+};
+AVR_HD V3 v3(float x, float y, float z) { return V3{x, y, z}; }
+AVR_HD V3 operator+(V3 a, V3 b) { return V3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+AVR_HD V3 operator-(V3 a, V3 b) { return V3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+AVR_HD V3 operator*(V3 a, float s) { return V3{a.x * s, a.y * s, a.z * s}; }
+AVR_HD V3 operator/(V3 a, float s) { return V3{a.x / s, a.y / s, a.z / s}; }
+AVR_HD V3 operator-(V3 a) { return V3{-a.x, -a.y, -a.z}; }
+AVR_HD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }  // vecmath.h:964-967
+AVR_HD float sqr(float x) { return x * x; }
+AVR_HD float comp(V3 v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
+
+// ---- N-channel spectrum (N = 4: SampledSpectrum; N = 1: achromatic media, all channels equal) ---
+template <int N>
+struct Spec {
+    float v[N];
+    AVR_HD float operator[](int i) const { return v[i]; }
+    AVR_HD float &operator[](int i) { return v[i]; }
+};
+template <int N>
+AVR_HD Spec<N> sconst(float c) {
+    Spec<N> r;
+#pragma unroll
+    for (int i = 0; i < N; ++i) r.v[i] = c;
+    return r;
+}
+#define AVR_SPEC_OP(op)                                              \
+    template <int N>                                                 \
+    AVR_HD Spec<N> operator op(Spec<N> a, Spec<N> b) {               \
+        Spec<N> r;                                                   \
+        _Pragma("unroll") for (int i = 0; i < N; ++i) r.v[i] = a.v[i] op b.v[i]; \
+        return r;                                                    \
+    }                                                                \
+    template <int N>                                                 \
+    AVR_HD Spec<N> operator op(Spec<N> a, float s) {                 \
+        Spec<N> r;                                                   \
+        _Pragma("unroll") for (int i = 0; i < N; ++i) r.v[i] = a.v[i] op s; \
+        return r;                                                    \
+    }
+AVR_SPEC_OP(+)
+AVR_SPEC_OP(-)
+AVR_SPEC_OP(*)
+AVR_SPEC_OP(/)
+#undef AVR_SPEC_OP
+template <int N>
+AVR_HD bool nonzero(Spec<N> a) {
+    bool r = false;
+#pragma unroll
+    for (int i = 0; i < N; ++i) r = r || (a.v[i] != 0);
+    return r;
+}
+template <int N>
+AVR_HD float average(Spec<N> a) {  // SampledSpectrum::Average: sum left to right, / NSpectrumSamples
+    if (N == 1) return (((a.v[0] + a.v[0]) + a.v[0]) + a.v[0]) / 4;
+    float s = a.v[0];
+#pragma unroll
+    for (int i = 1; i < N; ++i) s += a.v[i];
+    return s / N;
+}
+template <int N>
+AVR_HD float max_component(Spec<N> a) {
+    float m = a.v[0];
+#pragma unroll
+    for (int i = 1; i < N; ++i) m = fmaxf(m, a.v[i]);
+    return m;
+}
+template <int N>
+AVR_HD Spec<N> clamp_zero(Spec<N> a) {
+    Spec<N> r;
+#pragma unroll
+    for (int i = 0; i < N; ++i) r.v[i] = fmaxf(0.f, a.v[i]);
+    return r;
+}
+
+// ---- util/float.h NextFloatUp/Down (CPU branch of the rounded interval ops) ------------------
+AVR_DEV float next_up(float v) {
+    if (isinf(v) && v > 0.f) return v;
+    if (v == -0.f) v = 0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v >= 0) ++ui; else --ui;
+    return __uint_as_float(ui);
+}
+AVR_DEV float next_down(float v) {
+    if (isinf(v) && v < 0.f) return v;
+    if (v == 0.f) v = -0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v > 0) --ui; else ++ui;
+    return __uint_as_float(ui);
+}
+
+// ---- util/hash.h MurmurHash64A over 4 / 12 bytes, MixBits ---------------------------------------
+AVR_HD uint64_t mix_bits(uint64_t v) {
+    v ^= (v >> 31); v *= 0x7fb5d329728ea185ull;
+    v ^= (v >> 27); v *= 0x81dadef4bc2dd44dull;
+    v ^= (v >> 33);
+    return v;
+}
+AVR_HD uint64_t murmur_finish(uint64_t h) {
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    h ^= h >> 47; h *= m; h ^= h >> 47;
+    return h;
+}
+// Hash(float): len = 4, tail bytes only
+AVR_HD uint64_t hash_u32(uint32_t bits) {
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    uint64_t h = 0 ^ (4ull * m);
+    h ^= uint64_t(bits);
+    h *= m;
+    return murmur_finish(h);
+}
+// Hash of 12 bytes (Point3f / Vector3f / (Point2i, int)): one 8-byte block + 4 tail bytes
+AVR_HD uint64_t hash_3u32(uint32_t a, uint32_t b, uint32_t c) {
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    uint64_t h = 0 ^ (12ull * m);
+    uint64_t k = uint64_t(a) | (uint64_t(b) << 32);
+    k *= m; k ^= k >> 47; k *= m;
+    h ^= k; h *= m;
+    h ^= uint64_t(c);
+    h *= m;
+    return murmur_finish(h);
+}
+AVR_DEV uint64_t hash_float(float f) { return hash_u32(__float_as_uint(f)); }
+AVR_DEV uint64_t hash_v3(V3 p) {
+    return hash_3u32(__float_as_uint(p.x), __float_as_uint(p.y), __float_as_uint(p.z));
+}
+
+// ---- util/rng.h PCG32 -------------------------------------------------------------------------------
+struct RNG {
+    uint64_t state, inc;
+    static constexpr uint64_t MULT = 0x5851f42d4c957f2dULL;
+    AVR_HD uint32_t u32() {
+        uint64_t old = state;
+        state = old * MULT + inc;
+        uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+        uint32_t rot = (uint32_t)(old >> 59u);
+        return (xs >> rot) | (xs << ((~rot + 1u) & 31));
+    }
+    AVR_HD void set_sequence(uint64_t seq, uint64_t seed) {
+        state = 0u; inc = (seq << 1u) | 1u;
+        u32(); state += seed; u32();
+    }
+    AVR_HD void set_sequence(uint64_t seq) { set_sequence(seq, mix_bits(seq)); }
+    AVR_HD float uniform() {
+        float f = u32() * 0x1p-32f;
+        return f < kOneMinusEps ? f : kOneMinusEps;
+    }
+    AVR_HD void advance(int64_t idelta) {
+        uint64_t curMult = MULT, curPlus = inc, accMult = 1u, accPlus = 0u, delta = (uint64_t)idelta;
+        while (delta > 0) {
+            if (delta & 1) { accMult *= curMult; accPlus = accPlus * curMult + curPlus; }
+            curPlus = (curMult + 1) * curPlus;
+            curMult *= curMult;
+            delta /= 2;
+        }
+        state = accMult * state + accPlus;
+    }
+};
+
+// ---- FastExp: EXACT = CPU branch util/math.h:453-474 ; FAST = GPU branch (__expf) :451-452 -----
+AVR_DEV float fast_exp_exact(float x) {
+    float xp = x * 1.442695041f;
+    float fxp = floorf(xp), f = xp - fxp;
+    int i = (int)fxp;
+    float twoToF = __fmaf_rn(f, __fmaf_rn(f, __fmaf_rn(f, 0.0781455737f, 0.226173572f), 0.695556856f), 1.f);
+    int exponent = int(__float_as_uint(twoToF) >> 23) - 127 + i;
+    if (exponent < -126) return 0;
+    if (exponent > 127) return __int_as_float(0x7f800000);
+    uint32_t bits = __float_as_uint(twoToF);
+    bits &= 0x807fffffu;
+    bits |= (uint32_t)(exponent + 127) << 23;
+    return __uint_as_float(bits);
+}
+template <bool EXACT>
+AVR_DEV float fast_exp(float x) {
+    if (EXACT) return fast_exp_exact(x);
+    return __expf(x);
+}
+template <bool EXACT>
+AVR_DEV float sample_exponential(float u, float a) {  // util/sampling.h:222-225
+    if (EXACT) return -logf(1 - u) / a;
+    return __fdividef(-__logf(1 - u), a);
+}
+template <bool EXACT>
+AVR_DEV float fdiv(float a, float b) {
+    if (EXACT) return a / b;
+    return __fdividef(a, b);
+}
+AVR_DEV float lerp_exact(float x, float a, float b) { return (1 - x) * a + x * b; }  // util/math.h:210
+AVR_DEV float lerp_fast(float x, float a, float b) { return __fmaf_rn(x, b - a, a); }
+template <bool EXACT>
+AVR_DEV float lerpf(float x, float a, float b) {
+    return EXACT ? lerp_exact(x, a, b) : lerp_fast(x, a, b);
+}
+AVR_DEV float safe_sqrt(float x) { return sqrtf(fmaxf(0.f, x)); }
+AVR_DEV float clampf(float v, float lo, float hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// util/sampling.h:79-110 SampleDiscrete over {a, s, n}
+AVR_DEV int sample_discrete3(float w0, float w1, float w2, float u) {
+    float sum = 0;
+    sum += w0; sum += w1; sum += w2;
+    float up = u * sum;
+    if (up == sum) up = next_down(up);
+    float acc = 0;
+    if (!(acc + w0 <= up)) return 0;
+    acc += w0;
+    if (!(acc + w1 <= up)) return 1;
+    return 2;
+}
+
+// util/scattering.h:49-58 HenyeyGreenstein ; util/sampling.cpp:348-374 SampleHenyeyGreenstein
+AVR_DEV float henyey_greenstein(float cosTheta, float g) {
+    g = clampf(g, -.99f, .99f);
+    float denom = 1 + sqr(g) + 2 * g * cosTheta;
+    return kInv4Pi * (1 - sqr(g)) / (denom * safe_sqrt(denom));
+}
+AVR_DEV V3 sample_hg(V3 wo, float g, float u0, float u1, float *pdf) {
+    g = clampf(g, -.99f, .99f);
+    float cosTheta;
+    if (fabsf(g) < 1e-3f)
+        cosTheta = 1 - 2 * u0;
+    else
+        cosTheta = -1 / (2 * g) * (1 + sqr(g) - sqr((1 - sqr(g)) / (1 + g - 2 * g * u0)));
+    float sinTheta = safe_sqrt(1 - sqr(cosTheta));
+    float phi = 2 * kPi * u1;
+    // CoordinateSystem (vecmath.h:1007-1013), Frame::FromZ(wo).FromLocal(SphericalDirection(...))
+    float sign = copysignf(1.f, wo.z);
+    float a = -1 / (sign + wo.z);
+    float b = wo.x * wo.y * a;
+    V3 fx = v3(1 + sign * sqr(wo.x) * a, sign * b, -sign * wo.x);
+    V3 fy = v3(b, sign + sqr(wo.y) * a, -wo.y);
+    float st = clampf(sinTheta, -1.f, 1.f), ct = clampf(cosTheta, -1.f, 1.f);
+    float sp, cp;
+    sincosf(phi, &sp, &cp);
+    V3 l = v3(st * cp, st * sp, ct);
+    V3 wi = fx * l.x + fy * l.y + wo * l.z;
+    *pdf = henyey_greenstein(cosTheta, g);
+    return wi;
+}
+
+// util/sampling.h:163-171 + util/spectrum.h:334-346: SampledWavelengths::SampleVisible
+AVR_DEV void sample_visible_wavelengths(float u, float lambda[4], float pdf[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float up = u + float(i) / 4;
+        if (up > 1) up -= 1;
+        float l = 538 - 138.888889f * atanhf(0.85691062f - 1.82750197f * up);
+        lambda[i] = l;
+        pdf[i] = (l < 360 || l > 830) ? 0.f : 0.0039398042f / sqr(coshf(0.0072f * (l - 538)));
+    }
+}
+// DenselySampledSpectrum::Sample, util/spectrum.h:390-399 (std::lround: half away from zero)
+AVR_DEV float sample_dense1(const float *tab, float lambda) {
+    int offset = (int)lroundf(lambda) - 360;
+    return (offset < 0 || offset >= kNSpec) ? 0.f : __ldg(tab + offset);
+}
+
+// util/spectrum.h:69-80 Blackbody (FastExp inside), :500-523 BlackbodySpectrum normalisation
+AVR_DEV float blackbody(float lambda, float T) {
+    if (T <= 0) return 0;
+    const float c = 299792458.f, h = 6.62606957e-34f, kb = 1.3806488e-23f;
+    float l = lambda * 1e-9f;
+    float l2 = l * l;
+    float l5 = l2 * l2 * l;
+    return (2 * h * c * c) / (l5 * (fast_exp_exact((h * c) / (l * kb * T)) - 1));
+}
+// util/color.h:340-360 RGBSigmoidPolynomial over a {scale,c0,c1,c2} voxel
+AVR_DEV float sigmoid_s(float x) {
+    if (isinf(x)) return x > 0 ? 1.f : 0.f;
+    return .5f + x / (2 * sqrtf(1 + sqr(x)));
+}
+AVR_DEV float rsp_eval(float c0, float c1, float c2, float lambda) {
+    return sigmoid_s(__fmaf_rn(lambda, __fmaf_rn(lambda, c0, c1), c2));
+}
+
+}  // namespace avr

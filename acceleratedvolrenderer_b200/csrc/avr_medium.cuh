@@ -1,0 +1,357 @@
+// avr_medium.cuh — device view of a grid medium, its HBM layouts, the DDA majorant iterator and the
+// SampleT_maj driver (reference: src/pbrt/media.h:105-214,265-427,741-806; util/containers.h:765-869;
+// util/transform.h:391-433 + transform.cpp:263-303).
+#pragma once
+#include "avr_math.cuh"
+
+namespace avr {
+
+enum { LAYOUT_DENSE_F32 = 0, LAYOUT_OCTET_F32 = 1, LAYOUT_OCTET_F16 = 2 };
+enum { KIND_GRID = 0, KIND_RGB = 1 };
+
+// Plain-old-data view handed to kernels by value (lives in the kernel parameter bank).
+struct MediumView {
+    int kind, layout;
+    int nx, ny, nz;
+    // scalar density grid (KIND_GRID)
+    const float *dense;       // [nz][ny][nx] fp32 — reference layout, always resident
+    const float4 *oct32;      // 2 x float4 per interpolation cell, 4x4x4-cell bricks (or null)
+    const uint4 *oct16;       // 8 x fp16 per interpolation cell (or null)
+    int nbx, nby, nbz;        // bricks per axis over the (nx+1)(ny+1)(nz+1) cell lattice
+    const float *temperature; // null or [nz][ny][nx]
+    const float *lescale;     // [lnz][lny][lnx] (1x1x1 when the scene gave no "Lescale")
+    int lnx, lny, lnz;
+    const float *sigma_a_spec, *sigma_s_spec, *le_spec;  // kNSpec each; sigma_* already * "scale"
+    int emissive, has_temperature, achromatic;
+    float temp_offset, temp_scale;
+    // RGB grids (KIND_RGB): {scale,c0,c1,c2} per voxel
+    const float4 *rgb_a, *rgb_s, *rgb_le;
+    const float *le_illum;
+    float sigma_scale, le_scale;
+    // common
+    float g;
+    float bmin[3], bmax[3];
+    float m[12], minv[12];    // renderFromMedium / mediumFromRender, rows 0..2 (affine; row 3 = 0 0 0 1)
+    const float *maj;         // majorant grid, x fastest
+    int mres[3];
+    // FAST path: sample coordinates straight from render space, s = gfr * p + gfr[.][3]  (s = p_grid*n - .5)
+    float gfr[12];
+};
+
+// ---- Transform::ApplyInverse(Point3f) + Bounds3::Offset: render point -> grid [0,1]^3 ------------
+AVR_DEV V3 grid_point_exact(const MediumView &mv, V3 p) {
+    const float *a = mv.minv;
+    float xp = (a[0] * p.x + a[1] * p.y) + (a[2] * p.z + a[3]);
+    float yp = (a[4] * p.x + a[5] * p.y) + (a[6] * p.z + a[7]);
+    float zp = (a[8] * p.x + a[9] * p.y) + (a[10] * p.z + a[11]);
+    // wp == 1 exactly for an affine transform: (0*x + 0*y) + (0*z + 1)
+    V3 o = v3(xp - mv.bmin[0], yp - mv.bmin[1], zp - mv.bmin[2]);
+    if (mv.bmax[0] > mv.bmin[0]) o.x /= mv.bmax[0] - mv.bmin[0];
+    if (mv.bmax[1] > mv.bmin[1]) o.y /= mv.bmax[1] - mv.bmin[1];
+    if (mv.bmax[2] > mv.bmin[2]) o.z /= mv.bmax[2] - mv.bmin[2];
+    return o;
+}
+
+// ---- SampledGrid<Float>::Lookup, util/containers.h:804-835 ----------------------------------------
+AVR_DEV float dense_at(const float *v, int nx, int ny, int nz, int x, int y, int z) {
+    if ((unsigned)x >= (unsigned)nx || (unsigned)y >= (unsigned)ny || (unsigned)z >= (unsigned)nz) return 0.f;
+    return __ldg(v + (size_t(z) * ny + y) * nx + x);
+}
+template <bool EXACT>
+AVR_DEV float trilerp8(float dx, float dy, float dz, float v000, float v100, float v010, float v110, float v001,
+                       float v101, float v011, float v111) {
+    float d00 = lerpf<EXACT>(dx, v000, v100);
+    float d10 = lerpf<EXACT>(dx, v010, v110);
+    float d01 = lerpf<EXACT>(dx, v001, v101);
+    float d11 = lerpf<EXACT>(dx, v011, v111);
+    return lerpf<EXACT>(dz, lerpf<EXACT>(dy, d00, d10), lerpf<EXACT>(dy, d01, d11));
+}
+// s = p*n - .5 already formed
+template <bool EXACT>
+AVR_DEV float lookup_dense_s(const float *v, int nx, int ny, int nz, float sx, float sy, float sz) {
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    float dx = sx - fx, dy = sy - fy, dz = sz - fz;
+    return trilerp8<EXACT>(dx, dy, dz, dense_at(v, nx, ny, nz, ix, iy, iz), dense_at(v, nx, ny, nz, ix + 1, iy, iz),
+                           dense_at(v, nx, ny, nz, ix, iy + 1, iz), dense_at(v, nx, ny, nz, ix + 1, iy + 1, iz),
+                           dense_at(v, nx, ny, nz, ix, iy, iz + 1), dense_at(v, nx, ny, nz, ix + 1, iy, iz + 1),
+                           dense_at(v, nx, ny, nz, ix, iy + 1, iz + 1), dense_at(v, nx, ny, nz, ix + 1, iy + 1, iz + 1));
+}
+template <bool EXACT>
+AVR_DEV float lookup_dense(const float *v, int nx, int ny, int nz, V3 p) {
+    return lookup_dense_s<EXACT>(v, nx, ny, nz, p.x * nx - .5f, p.y * ny - .5f, p.z * nz - .5f);
+}
+
+// Octet layouts: cell (ix,iy,iz), ix in [-1, nx-1], stores its 8 corner taps contiguously
+// {v000,v100,v010,v110 | v001,v101,v011,v111} (out-of-range taps baked as 0); cells are grouped
+// in 4x4x4 bricks, x fastest inside the brick, so one fetch = one 32-byte sector (fp32) or one
+// 16-byte vector (fp16) and the 4 x-neighbours of a cell share a 128-byte line.
+AVR_HD size_t octet_index(int cx, int cy, int cz, int nbx, int nby) {
+    size_t brick = (size_t(cz >> 2) * nby + (cy >> 2)) * nbx + (cx >> 2);
+    return brick * 64 + ((cz & 3) * 16 + (cy & 3) * 4 + (cx & 3));
+}
+AVR_DEV void ldg256(const float4 *p, float4 &a, float4 &b) {
+#if AVR_USE_LDG256
+    asm volatile("ld.global.nc.L2::256B.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+#else
+    a = __ldg(p);
+    b = __ldg(p + 1);
+#endif
+}
+template <bool EXACT>
+AVR_DEV float lookup_oct32_s(const MediumView &mv, float sx, float sy, float sz) {
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int cx = (int)fx + 1, cy = (int)fy + 1, cz = (int)fz + 1;
+    if ((unsigned)cx > (unsigned)mv.nx || (unsigned)cy > (unsigned)mv.ny || (unsigned)cz > (unsigned)mv.nz) return 0.f;
+    float4 a, b;
+    ldg256(mv.oct32 + 2 * octet_index(cx, cy, cz, mv.nbx, mv.nby), a, b);
+    return trilerp8<EXACT>(sx - fx, sy - fy, sz - fz, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
+}
+AVR_DEV float2 h2f(uint32_t u) {
+    __half2 h = *reinterpret_cast<__half2 *>(&u);
+    return __half22float2(h);
+}
+template <bool EXACT>
+AVR_DEV float lookup_oct16_s(const MediumView &mv, float sx, float sy, float sz) {
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int cx = (int)fx + 1, cy = (int)fy + 1, cz = (int)fz + 1;
+    if ((unsigned)cx > (unsigned)mv.nx || (unsigned)cy > (unsigned)mv.ny || (unsigned)cz > (unsigned)mv.nz) return 0.f;
+    uint4 q = __ldg(mv.oct16 + octet_index(cx, cy, cz, mv.nbx, mv.nby));
+    float2 a = h2f(q.x), b = h2f(q.y), c = h2f(q.z), d = h2f(q.w);
+    return trilerp8<EXACT>(sx - fx, sy - fy, sz - fz, a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y);
+}
+// density at grid-normalised p, any layout (runtime switch; the hot kernels are templated on LAYOUT)
+template <bool EXACT, int LAYOUT>
+AVR_DEV float lookup_density_s(const MediumView &mv, float sx, float sy, float sz) {
+    if (LAYOUT == LAYOUT_OCTET_F32) return lookup_oct32_s<EXACT>(mv, sx, sy, sz);
+    if (LAYOUT == LAYOUT_OCTET_F16) return lookup_oct16_s<EXACT>(mv, sx, sy, sz);
+    return lookup_dense_s<EXACT>(mv.dense, mv.nx, mv.ny, mv.nz, sx, sy, sz);
+}
+template <bool EXACT>
+AVR_DEV float lookup_density_rt(const MediumView &mv, V3 p) {
+    float sx = p.x * mv.nx - .5f, sy = p.y * mv.ny - .5f, sz = p.z * mv.nz - .5f;
+    if (mv.layout == LAYOUT_OCTET_F32) return lookup_oct32_s<EXACT>(mv, sx, sy, sz);
+    if (mv.layout == LAYOUT_OCTET_F16) return lookup_oct16_s<EXACT>(mv, sx, sy, sz);
+    return lookup_dense_s<EXACT>(mv.dense, mv.nx, mv.ny, mv.nz, sx, sy, sz);
+}
+
+// ---- general SamplePoint: GridMedium media.h:287-319, RGBGridMedium media.h:377-401 -------------
+struct Props4 {
+    Spec<4> sigma_a, sigma_s, Le;
+};
+AVR_DEV Spec<4> sample_dense4(const float *tab, const float lambda[4]) {
+    Spec<4> s;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s.v[i] = sample_dense1(tab, lambda[i]);
+    return s;
+}
+AVR_DEV Spec<4> rgb_tap(const float4 *gr, const MediumView &mv, int x, int y, int z, const float lambda[4],
+                        const float *illum) {
+    Spec<4> s = sconst<4>(0.f);
+    bool oob = (unsigned)x >= (unsigned)mv.nx || (unsigned)y >= (unsigned)mv.ny || (unsigned)z >= (unsigned)mv.nz;
+    if (oob) {
+        // default-constructed RGBUnboundedSpectrum: scale 0, rsp(0,0,0) -> 0 * s(0) = 0 ; illuminant: 0
+        return s;
+    }
+    float4 v = __ldg(gr + (size_t(z) * mv.ny + y) * mv.nx + x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s.v[i] = v.x * rsp_eval(v.y, v.z, v.w, lambda[i]);
+    if (illum) s = s * sample_dense4(illum, lambda);
+    return s;
+}
+AVR_DEV Spec<4> lerp4(float t, Spec<4> a, Spec<4> b) { return a * (1 - t) + b * t; }
+AVR_DEV Spec<4> rgb_lookup(const float4 *gr, const MediumView &mv, V3 p, const float lambda[4], const float *illum) {
+    float sx = p.x * mv.nx - .5f, sy = p.y * mv.ny - .5f, sz = p.z * mv.nz - .5f;
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    float dx = sx - fx, dy = sy - fy, dz = sz - fz;
+    Spec<4> d00 = lerp4(dx, rgb_tap(gr, mv, ix, iy, iz, lambda, illum), rgb_tap(gr, mv, ix + 1, iy, iz, lambda, illum));
+    Spec<4> d10 = lerp4(dx, rgb_tap(gr, mv, ix, iy + 1, iz, lambda, illum), rgb_tap(gr, mv, ix + 1, iy + 1, iz, lambda, illum));
+    Spec<4> d01 = lerp4(dx, rgb_tap(gr, mv, ix, iy, iz + 1, lambda, illum), rgb_tap(gr, mv, ix + 1, iy, iz + 1, lambda, illum));
+    Spec<4> d11 = lerp4(dx, rgb_tap(gr, mv, ix, iy + 1, iz + 1, lambda, illum), rgb_tap(gr, mv, ix + 1, iy + 1, iz + 1, lambda, illum));
+    return lerp4(dz, lerp4(dy, d00, d10), lerp4(dy, d01, d11));
+}
+// Emission part of GridMedium::SamplePoint (media.h:299-316); p grid-normalised
+AVR_DEV Spec<4> grid_emission(const MediumView &mv, V3 p, const float lambda[4]) {
+    Spec<4> Le = sconst<4>(0.f);
+    float scale = lookup_dense<true>(mv.lescale, mv.lnx, mv.lny, mv.lnz, p);
+    if (scale > 0) {
+        if (mv.has_temperature) {
+            float temp = lookup_dense<true>(mv.temperature, mv.nx, mv.ny, mv.nz, p);
+            temp = (temp - mv.temp_offset) * mv.temp_scale;
+            if (temp > 100.f) {
+                float lambdaMax = 2.8977721e-3f / temp;
+                float norm = 1 / blackbody(lambdaMax * 1e9f, temp);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) Le.v[i] = blackbody(lambda[i], temp) * norm;
+                Le = Le * scale;
+            }
+        } else
+            Le = sample_dense4(mv.le_spec, lambda) * scale;
+    }
+    return Le;
+}
+// Full SamplePoint, exact arithmetic, any medium kind/layout (used by the general kernels and the
+// avr_medium_sample_point entry point).  sig_a/sig_s: the medium's spectra sampled at lambda.
+AVR_DEV Props4 sample_point_general(const MediumView &mv, V3 p_render, const float lambda[4], Spec<4> sig_a,
+                                    Spec<4> sig_s) {
+    Props4 mp;
+    V3 p = grid_point_exact(mv, p_render);
+    mp.Le = sconst<4>(0.f);
+    if (mv.kind == KIND_RGB) {
+        mp.sigma_a = (mv.rgb_a ? rgb_lookup(mv.rgb_a, mv, p, lambda, nullptr) : sconst<4>(1.f)) * mv.sigma_scale;
+        mp.sigma_s = (mv.rgb_s ? rgb_lookup(mv.rgb_s, mv, p, lambda, nullptr) : sconst<4>(1.f)) * mv.sigma_scale;
+        if (mv.rgb_le && mv.le_scale > 0) mp.Le = rgb_lookup(mv.rgb_le, mv, p, lambda, mv.le_illum) * mv.le_scale;
+        return mp;
+    }
+    float d = lookup_density_rt<true>(mv, p);
+    mp.sigma_a = sig_a * d;
+    mp.sigma_s = sig_s * d;
+    if (mv.emissive) mp.Le = grid_emission(mv, p, lambda);
+    return mp;
+}
+
+// ---- medium-space ray: Transform::ApplyInverse(Ray,&tMax) + Bounds3::IntersectP ------------------
+struct MRay {
+    V3 o, d;
+    float tMin, tMax;
+    bool hit;
+};
+AVR_DEV void ivl_from(float v, float err, float &lo, float &hi) {  // Interval::FromValueAndError
+    if (err == 0) { lo = hi = v; return; }
+    lo = next_down(v - err);
+    hi = next_up(v + err);
+}
+AVR_DEV void ivl_add_scalar(float &lo, float &hi, float f) {  // Interval += Float (math.h:873,921)
+    float l = next_down(lo + f), h = next_up(hi + f);
+    lo = fminf(l, h);
+    hi = fmaxf(l, h);
+}
+// a: 3x4 affine rows of the matrix being applied; trans_err: forward (operator()) includes |a[i][3]|
+AVR_DEV void xform_ray_exact(const float *a, bool trans_err, V3 o, V3 d, float *tMax, V3 *oo, V3 *od) {
+    float xp = (a[0] * o.x + a[1] * o.y) + (a[2] * o.z + a[3]);
+    float yp = (a[4] * o.x + a[5] * o.y) + (a[6] * o.z + a[7]);
+    float zp = (a[8] * o.x + a[9] * o.y) + (a[10] * o.z + a[11]);
+    float e[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float s = fabsf(a[4 * i] * o.x) + fabsf(a[4 * i + 1] * o.y) + fabsf(a[4 * i + 2] * o.z);
+        if (trans_err) s = s + fabsf(a[4 * i + 3]);
+        e[i] = kGamma3 * s;
+    }
+    float xl, xh, yl, yh, zl, zh;
+    ivl_from(xp, e[0], xl, xh);
+    ivl_from(yp, e[1], yl, yh);
+    ivl_from(zp, e[2], zl, zh);
+    V3 dd = v3(a[0] * d.x + a[1] * d.y + a[2] * d.z, a[4] * d.x + a[5] * d.y + a[6] * d.z,
+               a[8] * d.x + a[9] * d.y + a[10] * d.z);
+    float lengthSquared = sqr(dd.x) + sqr(dd.y) + sqr(dd.z);
+    if (lengthSquared > 0) {
+        V3 oErr = v3((xh - xl) / 2, (yh - yl) / 2, (zh - zl) / 2);
+        float dt = dot(v3(fabsf(dd.x), fabsf(dd.y), fabsf(dd.z)), oErr) / lengthSquared;
+        V3 off = dd * dt;
+        ivl_add_scalar(xl, xh, off.x);
+        ivl_add_scalar(yl, yh, off.y);
+        ivl_add_scalar(zl, zh, off.z);
+        if (tMax) *tMax -= dt;
+    }
+    *oo = v3((xl + xh) / 2, (yl + yh) / 2, (zl + zh) / 2);
+    *od = dd;
+}
+AVR_DEV bool slab_test(const float bmin[3], const float bmax[3], V3 o, V3 d, float tMax, float *h0, float *h1) {
+    float t0 = 0, t1 = tMax;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float inv = 1 / comp(d, i);
+        float tNear = (bmin[i] - comp(o, i)) * inv;
+        float tFar = (bmax[i] - comp(o, i)) * inv;
+        if (tNear > tFar) { float t = tNear; tNear = tFar; tFar = t; }
+        tFar *= 1 + 2 * kGamma3;
+        t0 = tNear > t0 ? tNear : t0;
+        t1 = tFar < t1 ? tFar : t1;
+        if (t0 > t1) return false;
+    }
+    *h0 = t0;
+    *h1 = t1;
+    return true;
+}
+AVR_DEV MRay ray_to_medium(const MediumView &mv, V3 o, V3 d, float raytMax) {
+    MRay r;
+    xform_ray_exact(mv.minv, false, o, d, &raytMax, &r.o, &r.d);
+    r.tMin = r.tMax = 0;
+    r.hit = slab_test(mv.bmin, mv.bmax, r.o, r.d, raytMax, &r.tMin, &r.tMax);
+    return r;
+}
+
+// ---- DDAMajorantIterator, media.h:136-214 (bit-exact contract) --------------------------------------
+struct DDA {
+    float tMin, tMax;
+    float nextCrossingT[3], deltaT[3];
+    int voxel[3];
+    int stepBits;  // bit i set: step[i] = +1 (voxelLimit = res), else -1 (voxelLimit = -1)
+
+    AVR_DEV void invalidate() { tMin = __int_as_float(0x7f800000); tMax = __int_as_float(0xff800000); }
+    AVR_DEV void init(const MediumView &mv, V3 o, V3 d, float tMin_, float tMax_) {
+        tMin = tMin_;
+        tMax = tMax_;
+        stepBits = 0;
+        V3 diag = v3(mv.bmax[0] - mv.bmin[0], mv.bmax[1] - mv.bmin[1], mv.bmax[2] - mv.bmin[2]);
+        // bounds.Offset(ray.o)
+        V3 ro = v3(o.x - mv.bmin[0], o.y - mv.bmin[1], o.z - mv.bmin[2]);
+        if (mv.bmax[0] > mv.bmin[0]) ro.x /= diag.x;
+        if (mv.bmax[1] > mv.bmin[1]) ro.y /= diag.y;
+        if (mv.bmax[2] > mv.bmin[2]) ro.z /= diag.z;
+        V3 rd = v3(d.x / diag.x, d.y / diag.y, d.z / diag.z);
+        V3 gi = v3(ro.x + rd.x * tMin, ro.y + rd.y * tMin, ro.z + rd.z * tMin);
+#pragma unroll
+        for (int axis = 0; axis < 3; ++axis) {
+            int r = mv.mres[axis];
+            float g = comp(gi, axis), dd = comp(rd, axis);
+            float gv = g * r;
+            int vx;
+            if (gv < 0) vx = 0;
+            else if (gv > float(r - 1)) vx = r - 1;
+            else vx = (int)gv;
+            voxel[axis] = vx;
+            deltaT[axis] = 1 / (fabsf(dd) * r);
+            if (dd == -0.f) dd = 0.f;
+            if (dd >= 0) {
+                float nextVoxelPos = float(vx + 1) / r;
+                nextCrossingT[axis] = tMin + (nextVoxelPos - g) / dd;
+                stepBits |= 1 << axis;
+            } else {
+                float nextVoxelPos = float(vx) / r;
+                nextCrossingT[axis] = tMin + (nextVoxelPos - g) / dd;
+            }
+        }
+    }
+    // Returns false when the iterator is exhausted.  *vox = linear voxel index of the segment.
+    AVR_DEV bool next(const MediumView &mv, float *segMin, float *segMax, int *vox) {
+        if (tMin >= tMax) return false;
+        int bits = ((nextCrossingT[0] < nextCrossingT[1]) << 2) + ((nextCrossingT[0] < nextCrossingT[2]) << 1) +
+                   ((nextCrossingT[1] < nextCrossingT[2]));
+        // cmpToAxis = {2,1,2,1,2,2,0,0} packed 2 bits per entry
+        int stepAxis = (0x0A66 >> (2 * bits)) & 3;
+        float nct = stepAxis == 0 ? nextCrossingT[0] : (stepAxis == 1 ? nextCrossingT[1] : nextCrossingT[2]);
+        float tVoxelExit = fminf(tMax, nct);
+        *vox = voxel[0] + mv.mres[0] * (voxel[1] + mv.mres[1] * voxel[2]);
+        *segMin = tMin;
+        *segMax = tVoxelExit;
+        tMin = tVoxelExit;
+        if (nct > tMax) tMin = tMax;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            if (a == stepAxis) {
+                bool pos = (stepBits >> a) & 1;
+                voxel[a] += pos ? 1 : -1;
+                if (voxel[a] == (pos ? mv.mres[a] : -1)) tMin = tMax;
+                nextCrossingT[a] += deltaT[a];
+            }
+        }
+        return true;
+    }
+};
+
+}  // namespace avr

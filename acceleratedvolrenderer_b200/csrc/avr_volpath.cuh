@@ -1,0 +1,104 @@
+// avr_volpath.cuh — kernel 1b: persistent-thread wavefront volumetric path tracer.
+//
+// Replaces (for the scene class of include/avr.h) ImageTileIntegrator::Render + EvaluatePixelSample
+// (cpu/integrators.cpp:72-298), VolPathIntegrator::Li volume branch (:962-1106) and SampleLd
+// (:1282-1399), with SampleT_maj (media.h:741-806) unrolled into a per-lane state machine:
+//
+//   * one CTA-resident thread = one path in flight; finished lanes pull the next (pixel, sample)
+//     from a global counter with one warp-aggregated atomic (ballot + popc), so divergent path
+//     lengths never idle a lane for longer than one step;
+//   * camera-segment delta tracking and NEE shadow-ray ratio tracking are the SAME state (TRACK)
+//     with a mode bit, so both kinds of ray execute the exponential step + density fetch
+//     convergently and only the short event epilogue diverges;
+//   * every loop trip performs, per lane, "advance the DDA to the next non-empty majorant segment"
+//     and then exactly one tentative collision (one log, one exp, one 32-byte density fetch).
+#pragma once
+#include "avr_tmaj.cuh"
+
+namespace avr {
+
+struct RenderParams {
+    int width, height;
+    int x0, y0, x1, y1;
+    int s0, s1;
+    int max_depth, seed;
+    float filter_rx, filter_ry;
+    float cfr[16];   // cameraFromRaster (projective)
+    float rfc[12];   // renderFromCamera (affine rows)
+    float light_dir[3];
+    float scene_radius;
+    int boundary_type;
+    float boundary[6];
+    const float *light_spec;  // device, kNSpec
+    const float *sensor;      // device, 3*kNSpec
+    float imaging_ratio, max_component;
+    int rank, world;
+    int tiles_x;
+    long long local_items;    // work items owned by this rank (multiple of 32)
+    long long total_items;    // padded global item count
+    int dump_samples;         // 1: write L/lambda/pdf per sample instead of the film
+};
+
+// stats slots in the counters array
+enum { CNT_WORK = 0, CNT_RAYS = 1, CNT_CAM_FETCH = 2, CNT_SH_FETCH = 3, CNT_SEG = 4, CNT_SCATTER = 5 };
+
+AVR_DEV bool boundary_hit(const RenderParams &rp, V3 o, V3 d, float *t0, float *t1) {
+    if (rp.boundary_type == 0) {
+        double ox = double(o.x) - rp.boundary[0], oy = double(o.y) - rp.boundary[1], oz = double(o.z) - rp.boundary[2];
+        double r = rp.boundary[3];
+        double a = double(d.x) * d.x + double(d.y) * d.y + double(d.z) * d.z;
+        double b = 2 * (ox * d.x + oy * d.y + oz * d.z);
+        double c = ox * ox + oy * oy + oz * oz - r * r;
+        double disc = b * b - 4 * a * c;
+        if (!(disc >= 0) || a == 0) return false;
+        double s = sqrt(disc);
+        double q = (b < 0) ? -0.5 * (b - s) : -0.5 * (b + s);
+        double ta = q / a, tb = (q != 0) ? c / q : ta;
+        if (ta > tb) { double t = ta; ta = tb; tb = t; }
+        *t0 = (float)ta;
+        *t1 = (float)tb;
+        return true;
+    }
+    float a0 = __int_as_float(0xff800000), a1 = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float inv = 1 / comp(d, i);
+        float tn = (rp.boundary[i] - comp(o, i)) * inv, tf = (rp.boundary[3 + i] - comp(o, i)) * inv;
+        if (tn > tf) { float t = tn; tn = tf; tf = t; }
+        a0 = tn > a0 ? tn : a0;
+        a1 = tf < a1 ? tf : a1;
+        if (a0 > a1) return false;
+    }
+    *t0 = a0;
+    *t1 = a1;
+    return true;
+}
+
+template <typename TR>
+struct PathLane {
+    static constexpr int N = TR::NCH;
+    // work / sampler
+    int px, py, samp;
+    RNG srng;          // IndependentSampler stream
+    float lambda[4];
+    // radiance state
+    float L[4];
+    Spec<N> beta, r_u, r_l;
+    int depth;
+    // tracking state (camera segment or shadow ray)
+    int state;         // 0 need work, 1 tracking, 2 retired
+    bool shadow, in_seg;
+    Fetcher<TR> fe;
+    DDA dda;
+    float cur_tMin, seg_tMax, u;
+    Spec<N> sigma_maj, T_maj;
+    RNG trng;
+    // shadow-ray state
+    Spec<N> T_ray, s_rl, s_ru;
+    float f_hat;
+    V3 wo;
+    // stats
+    unsigned n_cam, n_sh, n_seg, n_sc;
+};
+
+}  // namespace avr

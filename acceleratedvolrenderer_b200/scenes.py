@@ -42,7 +42,7 @@ SRGB_FROM_XYZ = np.array([[3.2404542, -1.5371385, -0.4985314],
 CIE_Y_INTEGRAL = 106.856895
 
 
-def fbm_density(nx, ny=None, nz=None, seed=7, octaves=5, frequency=3.0, threshold=0.45, sharp=4.0):
+def fbm_density(nx, ny=None, nz=None, seed=7, octaves=5, frequency=3.0, threshold=0.3, sharp=3.0):
     """Cloud-like procedural density in [0,1]: trilinear value-noise fBm, thresholded so that a good
     part of the volume is empty (what makes the majorant grid pay off).  Returns [nz, ny, nx] fp32."""
     ny = ny or nx
@@ -132,7 +132,7 @@ def scale_translate(scale, translate):
     return m.astype(np.float32)
 
 
-def cloud_scene(density, *, width, height, spp, sigma_t=8.0, albedo=0.99, g=0.0, max_depth=5, fov=30.0,
+def cloud_scene(density, *, width, height, spp, sigma_t=8.0, albedo=0.99, g=0.0, max_depth=5, fov=20.0,
                 eye=(0.0, 0.35, -3.2), light_dir=(0.4, 0.8, -0.45), light_scale=3.0, boundary="sphere",
                 majorant_res=(16, 16, 16), exact_math=1, sampler_seed=0, chromatic=False):
     """A volume-only scene of the class the fork's graph pipeline accepts (SURVEY.md App. A gotchas):

@@ -169,6 +169,13 @@ avr_status avr_sample_tmaj(avr_medium *m, int mode, const float *rays, int64_t n
                            const uint64_t *rng, const float *u, const float lambda[4],
                            avr_tmaj_result *out);
 
+/* Same on DEVICE pointers (no copies; asynchronous on the context's stream).  exact_math: 1 = the
+ * restated CPU arithmetic of the parity contract, 0 = fast intrinsics + folded transforms (the
+ * reference's own GPU branch uses __expf, util/math.h:451-452). */
+avr_status avr_sample_tmaj_device(avr_medium *m, int mode, int exact_math, const float *rays_dev, int64_t n,
+                                  const uint64_t *rng_dev, const float *u_dev, const float lambda[4],
+                                  avr_tmaj_result *out_dev);
+
 /* ---- kernel 1b: volumetric path tracing -------------------------------------------------------- */
 /* Replaces Integrator::Create("volpath"/"volpathcustom") + ImageTileIntegrator::Render
  * (cpu/integrators.cpp:72-232), RayIntegrator::EvaluatePixelSample (:235-298),
@@ -243,6 +250,10 @@ void avr_graph_destroy(avr_graph *g);
  * total += cur.  iters_done = the function's return value. */
 avr_status avr_graph_propagate(avr_graph *g, const float *L0, int32_t bounces, float *total,
                                int32_t *iters_done);
+/* Same with L0/total resident on the device; iters_done may be NULL (then the call is asynchronous
+ * on `stream`, NULL = the context's stream). */
+avr_status avr_graph_propagate_device(avr_graph *g, const float *L0_dev, int32_t bounces, float *total_dev,
+                                      int32_t *iters_done, void *stream);
 /* Row-range shard of one iteration on device pointers, for the multi-GPU path (caller all-gathers
  * `cur_out` rows with NCCL): cur_out[r] = sum_j T[r,j]*cur_in[j], total[r] += cur_out[r] unless
  * *bad_flag is raised; rows [row_begin,row_end).  Asynchronous on `stream`. */

@@ -20,6 +20,7 @@
 #include <pbrt/util/transform.h>
 
 #include <Eigen/Sparse>
+#include <graph/util.h>
 
 #include "../include/avr.h"
 
@@ -378,6 +379,32 @@ int ref_graph_propagate(int32_t n, int64_t nnz, const int64_t *rowptr, const int
     }
     for (int i = 0; i < n; ++i) total[i] = totalLight.coeff(i);
     return curIteration;
+}
+
+
+// LightingCalculator::GetLightVector's per-ray estimator: the fork's own graph::ComputeRaysToSphere
+// (src/graph/util.h:814-839) -> util::SampleTransmittance (:344-366) -> SampleT_maj, unmodified.
+// samplingIndex = y * 65536 + x with Options->graph.samplingResolution = (65536, 65536).
+void ref_graph_light_rays(void *mp, const float *rays, const int32_t *pixel, const float *ts, int64_t n,
+                          int32_t iterations, int32_t seed, const float lambda[4], float *out) {
+    RefMedium *rm = (RefMedium *)mp;
+    static PBRTOptions opts;
+    opts.graph.samplingResolution = Point2i(65536, 65536);
+    Options = &opts;
+    util::MediumData md;
+    md.defaultLambda = make_lambda(lambda);
+    md.medium = rm->medium;
+    IndependentSampler is(iterations, seed);
+    Sampler sampler(&is);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays + 6 * i;
+        RayDifferential ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5]), 0.f, rm->medium);
+        util::StartEndT se{};
+        se.startScatterT = ts[2 * i];
+        se.endScatterT = ts[2 * i] + ts[2 * i + 1];
+        uint64_t idx = uint64_t(pixel[2 * i + 1]) * 65536ull + uint64_t(pixel[2 * i]);
+        out[i] = graph::ComputeRaysToSphere(ray, std::nullopt, se, md, sampler, iterations, idx);
+    }
 }
 
 }  // extern "C"

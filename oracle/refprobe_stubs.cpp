@@ -2,6 +2,9 @@
 // Link-time stand-ins for the handful of reference symbols the hot-path templates reference but never
 // reach from the probe's entry points (logging, stats registry, a spectrum type the probe does not
 // construct).  Everything on the measured/parity path is the reference's own object code.
+#include <pbrt/options.h>
+#include <pbrt/samplers.h>
+#include <pbrt/util/bluenoise.h>
 #include <pbrt/util/log.h>
 #include <pbrt/util/print.h>
 #include <pbrt/util/spectrum.h>
@@ -17,6 +20,12 @@ void LogFatal(LogLevel, const char *file, int line, const char *s) {
 }
 StatRegisterer::StatRegisterer(AccumFunc, PixelAccumFunc) {}
 void StatsAccumulator::ReportMemoryCounter(const char *, int64_t) {}
+void StatsAccumulator::ReportPercentage(const char *, int64_t, int64_t) {}
+PBRTOptions *Options = nullptr;  // options.cpp:14 (the probe points it at a local PBRTOptions)
+// bluenoise.cpp is one of the blobs missing from the reference mount (.MISSING_LARGE_BLOBS); only the
+// PMJ02BN sampler reads it, which the probe never instantiates.
+const uint16_t BlueNoiseTextures[NumBlueNoiseTextures][BlueNoiseResolution][BlueNoiseResolution] = {};
+Float MLTSampler::Get1D() { std::abort(); }
 Float PiecewiseLinearSpectrum::operator()(Float) const {
     std::fprintf(stderr, "refprobe: PiecewiseLinearSpectrum is not part of the probe\n");
     std::abort();
@@ -24,6 +33,7 @@ Float PiecewiseLinearSpectrum::operator()(Float) const {
 namespace detail {
 // only reached from ToString()/StringPrintf on error paths
 std::string FloatToString(float v) { return std::to_string(v); }
+std::string DoubleToString(double v) { return std::to_string(v); }
 void stringPrintfRecursive(std::string *s, const char *fmt) { *s += fmt; }
 std::string copyToFormatString(const char **fmt_ptr, std::string *s) {
     *s += *fmt_ptr;

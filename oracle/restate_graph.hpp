@@ -107,8 +107,12 @@ inline float light_ray_transmittance(const Medium &m, V3 o, V3 d, int px, int py
         s.start_pixel_sample(px, py, i);
         float curDistInSphere = distInSphere * s.get1d();
         float tMax = startScatterT + curDistInSphere;
-        uint64_t h0 = hash_float(s.get1d());
+        // util.h:346 `RNG rng(Hash(sampler.Get1D()), Hash(sampler.Get1D()))`: the two draws are
+        // unsequenced in the reference; GCC (the reference's Linux compiler, and the refprobe's)
+        // evaluates constructor arguments right to left, so the FIRST draw seeds `offset` and the
+        // second the sequence index.  Pinned against refprobe.
         uint64_t h1 = hash_float(s.get1d());
+        uint64_t h0 = hash_float(s.get1d());
         float u = s.get1d();
         TmajResult r = run_tmaj(m, 0, o, d, tMax, h0, h1, u, lambda);
         average += r.Tr[0] * 1.f;

@@ -1,0 +1,170 @@
+"""GPU parity: kernel 1b (wavefront volpath) and the graph kernels against the CPU oracle.
+
+Bars:
+  * per-pixel-sample radiance under identical IndependentSampler/PCG32 streams (exact_math=1):
+    >= 99% of samples within 1e-3 relative (device logf/sincosf/atanhf differ from glibc by an ulp,
+    which can flip a discrete decision on a long path), wavelengths within 2e-6 relative;
+  * converged image (exact and fast math, all layouts): relMSE of GPU-vs-oracle no larger than
+    3x the oracle's own seed-to-seed relMSE at the same spp (tolerance = Monte Carlo noise floor);
+  * analytic: homogeneous non-scattering slab, Tr = exp(-sigma_t * L) to 2e-3 relative;
+  * SpMV total bit-exact, iterations identical; ConnectToGraph 1e-5 relative.
+"""
+import numpy as np
+import pytest
+
+from acceleratedvolrenderer_b200 import scenes
+from acceleratedvolrenderer_b200._abi import GridDesc
+
+pytestmark = pytest.mark.gpu
+
+
+def small_scene(**kw):
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    args = dict(width=48, height=36, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8)
+    args.update(kw)
+    return dens, scenes.cloud_scene(dens, **args)
+
+
+@pytest.mark.parametrize("variant", ["achromatic-sphere", "chromatic-box", "emissive"])
+def test_per_sample_radiance_matches_oracle(ctx, orc, variant):
+    if variant == "achromatic-sphere":
+        dens, (gd, rd) = small_scene()
+    elif variant == "chromatic-box":
+        dens, (gd, rd) = small_scene(chromatic=True, boundary="box", g=-0.3)
+    else:
+        dens, (gd, rd) = small_scene()
+        gd = GridDesc(dens, gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=0.4, temperature=dens * 2500 + 200,
+                      lescale=dens * 0.5, le_norm=1.0)
+    mo = orc.medium_uniformgrid(gd)
+    want, wstats = mo.render_samples(rd)
+    for layout in (["dense", "octet32"] if variant != "emissive" else ["dense"]):
+        md = ctx.create_medium("uniformgrid", gd, layout=layout)
+        got, gstats = ctx.render_volpath_samples(md, rd)
+        md.close()
+        assert np.allclose(got[:, 4:8], want[:, 4:8], rtol=2e-6), "wavelengths"
+        L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+        scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+        ok = (np.abs(L - Lw).max(axis=1) <= 1e-3 * scale)
+        assert ok.mean() >= 0.99, f"{variant}/{layout}: {ok.mean():.4f} of samples match"
+        assert Lw.sum() > 0
+        # counters agree to the same degree
+        assert gstats["camera_rays"] == wstats[0]
+        for k, i in (("camera_fetches", 1), ("shadow_fetches", 2), ("segments", 3), ("scatter_events", 4)):
+            assert abs(gstats[k] - wstats[i]) <= 0.02 * max(1, wstats[i]), k
+    mo.close()
+
+
+def rel_mse(a, b):
+    a = a.astype(np.float64); b = b.astype(np.float64)
+    return float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+
+
+@pytest.mark.parametrize("exact,layout", [(1, "octet32"), (0, "dense"), (0, "octet32"), (0, "octet16")])
+def test_converged_image_matches_oracle(ctx, orc, exact, layout):
+    dens, (gd, rd) = small_scene(width=32, height=24, spp=64, max_depth=6)
+    mo = orc.medium_uniformgrid(gd)
+    ref_a, _ = mo.render(rd, threads=8)
+    ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
+    mo.close()
+    img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
+    noise = rel_mse(img_a, img_b)
+    md = ctx.create_medium("uniformgrid", gd, layout=layout)
+    film, stats = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2 if not exact else 0))
+    md.close()
+    assert np.all(film[..., 3] == 64)
+    img = ctx.film_resolve(rd, film)
+    err = rel_mse(img, img_a)
+    assert err <= 3 * noise + 1e-6, (err, noise)
+    assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
+
+
+def test_sample_sharding_is_additive(ctx):
+    """Multi-GPU contract: rendering sample shards / rank partitions into one film equals one render."""
+    dens, (gd, rd) = small_scene(width=24, height=20, spp=8)
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    full, _ = ctx.render_volpath(md, rd)
+    acc = np.zeros_like(full)
+    ctx.render_volpath(md, rd.with_(sample_begin=0, sample_end=3), film=acc)
+    ctx.render_volpath(md, rd.with_(sample_begin=3, sample_end=8), film=acc)
+    assert np.allclose(acc, full, rtol=1e-12, atol=1e-14)
+    acc2 = np.zeros_like(full)
+    for r in range(3):
+        ctx.render_volpath(md, rd.with_(rank=r, world=3), film=acc2)
+    assert np.allclose(acc2, full, rtol=1e-12, atol=1e-14)
+    md.close()
+
+
+def test_analytic_transmittance(ctx):
+    """Constant density, absorption only: ratio-tracked Tr along a chord of length L averages to
+    exp(-sigma_a L) (the KAT of the reference's stale cmd/transmittance_test.cpp:51-92, adapted)."""
+    dens = np.ones((8, 8, 8), dtype=np.float32)
+    gd = GridDesc(dens, scenes.const_spectrum(2.5), scenes.const_spectrum(0.0))
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    n = 200000
+    rays = np.zeros((n, 7), dtype=np.float32)
+    rays[:, :3] = (0.5, 0.5, -1.0); rays[:, 3:6] = (0, 0, 1); rays[:, 6] = 10
+    rng = np.random.default_rng(0)
+    seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64); u = rng.random(n, dtype=np.float32)
+    out = md.sample_t_maj(0, rays, seeds, u, np.array([500, 550, 600, 650], dtype=np.float32))
+    # sigma_maj == sigma_t everywhere -> no null collisions: Tr is 0 or the analytic T_maj
+    est = (out["Tr"][:, 0] * out["T_maj"][:, 0]).mean()
+    assert abs(est - np.exp(-2.5)) < 2e-3 * 5
+    md.close()
+
+
+def test_graph_propagation_bit_exact(ctx, orc):
+    for n in (1, 50, 5000, 200000):
+        rowptr, col, val = scenes.random_graph(n, avg_deg=4, seed=n)
+        L0 = np.random.default_rng(n).random(n, dtype=np.float32)
+        g = ctx.create_graph(rowptr, col, val)
+        for b in (0, 1, 3, 7):
+            got, it = g.compute_final_light(L0, b)
+            want, wit = orc.graph_propagate(rowptr, col, val, L0, b)
+            assert it == wit
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (n, b)
+        # NaN/Inf early-out: lighting_calculator.cpp:38-46
+        got, it = g.compute_final_light(L0, 30) if n < 50 else (None, None)
+        big = ctx.create_graph(rowptr, col, val * 1e7)
+        got, it = big.compute_final_light(L0, 20)
+        want, wit = orc.graph_propagate(rowptr, col, val * 1e7, L0, 20)
+        assert it == wit
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        big.close(); g.close()
+
+
+def test_graph_connect(ctx, orc):
+    rng = np.random.default_rng(3)
+    n = 4000
+    pos = rng.uniform(-0.5, 0.5, (n, 3)).astype(np.float32)
+    light = rng.random(n, dtype=np.float32)
+    rng_r = rng.uniform(0.02, 0.2, n).astype(np.float32)
+    rowptr, col, val = scenes.random_graph(n, seed=1)
+    g = ctx.create_graph(rowptr, col, val)
+    pts = rng.uniform(-0.6, 0.6, (3000, 3)).astype(np.float32)
+    for rr in (None, rng_r):
+        g.set_vertices(pos, light, rr, 0.03)
+        got = g.connect(pts)
+        want = orc.graph_connect(pos, light, rr, 0.03, pts)
+        assert np.allclose(got, want, rtol=1e-5, atol=1e-7)
+        assert (want > 0).mean() > 0.05
+    g.close()
+
+
+def test_graph_light_rays(ctx, orc):
+    dens = scenes.fbm_density(24, 20, 28, seed=3)
+    gd = GridDesc(dens, scenes.const_spectrum(0.2), scenes.const_spectrum(9.0), g=0.3)
+    rng = np.random.default_rng(9)
+    n = 4000
+    org = np.c_[rng.uniform(0, 1, (n, 2)), np.full(n, -1.0)]
+    d = np.tile([0.05, 0.02, 1.0], (n, 1)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.c_[org, d].astype(np.float32)
+    pix = np.c_[rng.integers(0, 500, n), rng.integers(0, 500, n)].astype(np.int32)
+    ts = np.c_[rng.uniform(1.0, 1.5, n), rng.uniform(0.05, 0.4, n)].astype(np.float32)
+    lam = np.array([412.3, 533.9, 601.2, 688.8], dtype=np.float32)
+    mo = orc.medium_uniformgrid(gd); md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    got = md.graph_light_rays(rays, pix, ts, 8, 0, lam)
+    want = mo.graph_light_rays(rays, pix, ts, 8, 0, lam)
+    ok = np.abs(got - want) <= 1e-4 * np.maximum(want, 1e-6)
+    assert ok.mean() >= 0.995
+    assert abs(got.mean() - want.mean()) < 1e-3
+    md.close(); mo.close()

@@ -38,7 +38,7 @@ ABI_SYMBOLS = [
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
     "avr_graph_create", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
-    "avr_render_graph", "avr_graph_light_rays",
+    "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
 ]
 
 
@@ -161,6 +161,11 @@ class Context:
         if st != 0:
             raise AvrError(st, "avr_film_resolve: bad argument")
         return rgb
+
+    def debug_math(self, kind, x):
+        x = _f32(x); out = np.empty_like(x)
+        self.check(self.lib.avr_debug_math(self.h, C.c_int(kind), _p(x), C.c_int64(x.size), _p(out)))
+        return out
 
     def create_graph(self, rowptr, col, val):
         rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)

@@ -84,11 +84,16 @@ AVR_DEV bool graph_search(const GraphView &g, V3 p, float r2, bool filter, float
     float pp[3] = {p.x, p.y, p.z};
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        lo[i] = max(0, (int)floorf((pp[i] - r - g.gmin[i]) * g.inv_cell));
-        hi[i] = min(g.gres[i] - 1, (int)floorf((pp[i] + r - g.gmin[i]) * g.inv_cell));
+        float flo = floorf((pp[i] - r - g.gmin[i]) * g.inv_cell), fhi = floorf((pp[i] + r - g.gmin[i]) * g.inv_cell);
+        lo[i] = (int)fmaxf(flo, 0.f);
+        hi[i] = (int)fminf(fhi, float(g.gres[i] - 1));
+        if (!(flo <= float(g.gres[i] - 1)) || !(fhi >= 0.f)) lo[i] = hi[i] + 1;  // outside the grid (or NaN)
     }
     float a = 0, w = 0;
     bool any = false;
+    *avg = 0;
+    *wsum = 0;
+    if (lo[0] > hi[0] || lo[1] > hi[1] || lo[2] > hi[2]) return false;
     for (int z = lo[2]; z <= hi[2]; ++z)
         for (int y = lo[1]; y <= hi[1]; ++y) {
             int c0 = (z * g.gres[1] + y) * g.gres[0];

@@ -184,6 +184,85 @@ struct RNG {
     }
 };
 
+
+// ---- libm restatements for the EXACT path ---------------------------------------------------------
+// The reference calls std::log / std::sin / std::cos on floats, i.e. glibc's logf / sinf / cosf (the
+// ARM optimized-routines algorithms: table + double-precision polynomial).  Scatter positions feed
+// Hash(p) / Hash(d) RNG seeds (cpu/integrators.cpp:1338), so a 1-ulp libm difference changes a whole
+// shadow-ray random stream; CUDA's logf/sinf/cosf (<= 1-2 ulp) are therefore not good enough for
+// per-sample parity.  These restatements were checked bit-for-bit against the host libm over ALL
+// positive floats (logf) and all floats in [0, 2*pi] (sinf, cosf) — tests/test_libm_restatement.py.
+__device__ const double kLogfInvC[16] = {
+    0x1.661ec79f8f3bep+0, 0x1.571ed4aaf883dp+0, 0x1.49539f0f010bp+0, 0x1.3c995b0b80385p+0,
+    0x1.30d190c8864a5p+0, 0x1.25e227b0b8eap+0, 0x1.1bb4a4a1a343fp+0, 0x1.12358f08ae5bap+0,
+    0x1.0953f419900a7p+0, 0x1p+0, 0x1.e608cfd9a47acp-1, 0x1.ca4b31f026aap-1,
+    0x1.b2036576afce6p-1, 0x1.9c2d163a1aa2dp-1, 0x1.886e6037841edp-1, 0x1.767dcf5534862p-1};
+__device__ const double kLogfLogC[16] = {
+    -0x1.57bf7808caadep-2, -0x1.2bef0a7c06ddbp-2, -0x1.01eae7f513a67p-2, -0x1.b31d8a68224e9p-3,
+    -0x1.6574f0ac07758p-3, -0x1.1aa2bc79c81p-3, -0x1.a4e76ce8c0e5ep-4, -0x1.1973c5a611cccp-4,
+    -0x1.252f438e10c1ep-5, 0x0p+0, 0x1.aa5aa5df25984p-5, 0x1.c5e53aa362eb4p-4,
+    0x1.526e57720db08p-3, 0x1.bc2860d22477p-3, 0x1.1058bc8a07ee1p-2, 0x1.4043057b6ee09p-2};
+AVR_DEV float glibc_logf(float x) {
+    uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.f;
+    if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
+        if (ix * 2 == 0) return __int_as_float(0xff800000);
+        if (ix == 0x7f800000u) return x;
+        if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return __int_as_float(0x7fc00000);
+        x *= 0x1p23f;
+        ix = __float_as_uint(x);
+        ix -= 23u << 23;
+    }
+    uint32_t tmp = ix - 0x3f330000u;
+    int i = (tmp >> 19) % 16;
+    int k = (int32_t)tmp >> 23;
+    uint32_t iz = ix - (tmp & 0xff800000u);
+    double z = (double)__uint_as_float(iz);
+    double r = z * kLogfInvC[i] - 1;
+    double y0 = kLogfLogC[i] + (double)k * 0x1.62e42fefa39efp-1;
+    double r2 = r * r;
+    double y = 0x1.5575b0be00b6ap-2 * r + -0x1.ffffef20a4123p-2;
+    y = -0x1.00ea348b88334p-2 * r2 + y;
+    y = y * r2 + (y0 + r);
+    return (float)y;
+}
+// sinf/cosf for |y| < 120 (the path only evaluates phi = 2*pi*u in [0, 2*pi))
+AVR_DEV float glibc_sincos_poly(double x, double x2, bool neg_table, int n) {
+    const double sg = neg_table ? -1.0 : 1.0;
+    if ((n & 1) == 0) {
+        double x3 = x * x2;
+        double s1 = 0x1.1107605230bc4p-7 + x2 * -0x1.994eb3774cf24p-13;
+        double x7 = x3 * x2;
+        double s = x + x3 * -0x1.555545995a603p-3;
+        return (float)(s + x7 * s1);
+    }
+    double x4 = x2 * x2;
+    double c2 = (sg * -0x1.6c087e89a359dp-10) + x2 * (sg * 0x1.99343027bf8c3p-16);
+    double c1 = (sg * 0x1p0) + x2 * (sg * -0x1.ffffffd0c621cp-2);
+    double x6 = x4 * x2;
+    double c = c1 + x4 * (sg * 0x1.55553e1068f19p-5);
+    return (float)(c + x6 * c2);
+}
+AVR_DEV uint32_t abstop12(float x) { return (__float_as_uint(x) >> 20) & 0x7ff; }
+AVR_DEV float glibc_sincosf_one(float y, bool want_cos) {
+    double x = y;
+    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
+        double s = x * x;
+        if (abstop12(y) < abstop12(0x1p-12f)) return want_cos ? 1.0f : y;
+        return glibc_sincos_poly(x, s, false, want_cos ? 1 : 0);
+    }
+    double r = x * 0x1.45F306DC9C883p+23;
+    int n = ((int32_t)r + 0x800000) >> 24;
+    x = x - n * 0x1.921FB54442D18p0;
+    // sign[] of table 0 = {1,-1,-1,1}; the sign applies to x before the (odd/even) polynomial
+    const int q = n & 3;
+    double sgn = (q == 1 || q == 2) ? -1.0 : 1.0;
+    bool neg_table = (n & 2) != 0;  // glibc reads sign[] from table 0, then switches polynomial tables
+    return glibc_sincos_poly(x * sgn, x * x, neg_table, want_cos ? (n ^ 1) : n);
+}
+AVR_DEV float glibc_sinf(float y) { return glibc_sincosf_one(y, false); }
+AVR_DEV float glibc_cosf(float y) { return glibc_sincosf_one(y, true); }
+
 // ---- FastExp: EXACT = CPU branch util/math.h:453-474 ; FAST = GPU branch (__expf) :451-452 -----
 AVR_DEV float fast_exp_exact(float x) {
     float xp = x * 1.442695041f;
@@ -205,7 +284,7 @@ AVR_DEV float fast_exp(float x) {
 }
 template <bool EXACT>
 AVR_DEV float sample_exponential(float u, float a) {  // util/sampling.h:222-225
-    if (EXACT) return -logf(1 - u) / a;
+    if (EXACT) return -glibc_logf(1 - u) / a;
     return __fdividef(-__logf(1 - u), a);
 }
 template <bool EXACT>
@@ -257,8 +336,7 @@ AVR_DEV V3 sample_hg(V3 wo, float g, float u0, float u1, float *pdf) {
     V3 fx = v3(1 + sign * sqr(wo.x) * a, sign * b, -sign * wo.x);
     V3 fy = v3(b, sign + sqr(wo.y) * a, -wo.y);
     float st = clampf(sinTheta, -1.f, 1.f), ct = clampf(cosTheta, -1.f, 1.f);
-    float sp, cp;
-    sincosf(phi, &sp, &cp);
+    float sp = glibc_sinf(phi), cp = glibc_cosf(phi);
     V3 l = v3(st * cp, st * sp, ct);
     V3 wi = fx * l.x + fy * l.y + wo * l.z;
     *pdf = henyey_greenstein(cosTheta, g);

@@ -286,6 +286,10 @@ avr_status avr_graph_light_rays(avr_medium *m, const float *rays, const int32_t 
                                 const float *ts, int64_t n, int32_t iterations, int32_t sampler_seed,
                                 const float lambda[4], float *out);
 
+/* Parity probe for the EXACT path's restated scalar functions: kind 0 = logf (glibc algorithm),
+ * 1 = sinf, 2 = cosf (glibc), 3 = FastExp CPU branch (util/math.h:453-474).  Host buffers. */
+avr_status avr_debug_math(avr_ctx *ctx, int kind, const float *x, int64_t n, float *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,10 @@ const char *orc_kind() { return "port"; }
 void orc_fast_exp(const float *x, int64_t n, float *out) {
     for (int64_t i = 0; i < n; ++i) out[i] = fast_exp(x[i]);
 }
+// host libm exactly as the reference calls it (std::log / std::sin / std::cos on floats)
+void orc_libm(int kind, const float *x, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) out[i] = kind == 0 ? std::log(x[i]) : kind == 1 ? std::sin(x[i]) : std::cos(x[i]);
+}
 void orc_mix_bits(const uint64_t *x, int64_t n, uint64_t *out) {
     for (int64_t i = 0; i < n; ++i) out[i] = mix_bits(x[i]);
 }

@@ -60,6 +60,11 @@ class Checker:
         self.fn("fast_exp")(_p(x, f32p), C.c_int64(x.size), _p(out, f32p))
         return out
 
+    def libm(self, kind, x):
+        x = f32(x); out = np.empty_like(x)
+        self.fn("libm")(C.c_int(kind), _p(x, f32p), C.c_int64(x.size), _p(out, f32p))
+        return out
+
     def mix_bits(self, x):
         x = np.ascontiguousarray(x, dtype=np.uint64); out = np.empty_like(x)
         self.fn("mix_bits")(_p(x, u64p), C.c_int64(x.size), _p(out, u64p))

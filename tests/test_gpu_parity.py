@@ -184,3 +184,16 @@ def test_error_behaviour(ctx):
     md = ctx.create_medium("uniformgrid", GridDesc(dens, scenes.const_spectrum(1), scenes.const_spectrum(1)))
     assert md.dda_segments(np.zeros((0, 8), dtype=np.float32))[0].size == 0  # empty batch is fine
     md.close()
+
+
+def test_exact_path_scalar_functions_bit_exact(ctx, orc):
+    """glibc logf / sinf / cosf restatements and FastExp on the device vs the host libm / oracle."""
+    rng = np.random.default_rng(0)
+    u = rng.random(1 << 21, dtype=np.float32)
+    x = np.concatenate([1 - u, np.float32(2.0) ** -np.arange(0, 25, dtype=np.float32), rng.uniform(0, 50, 100000).astype(np.float32)])
+    assert bits_equal(ctx.debug_math(0, x), orc.libm(0, x))
+    phi = np.concatenate([(2 * np.pi * u).astype(np.float32), np.array([0, 1e-5, 0.785398, 0.7853982, 1.5707964, 3.1415927, 6.2831855], dtype=np.float32)])
+    assert bits_equal(ctx.debug_math(1, phi), orc.libm(1, phi))
+    assert bits_equal(ctx.debug_math(2, phi), orc.libm(2, phi))
+    e = np.concatenate([rng.uniform(-100, 5, 1 << 20).astype(np.float32), np.array([0, -0.0, -1e30, 88, 100, -87.5], dtype=np.float32)])
+    assert bits_equal(ctx.debug_math(3, e), orc.fast_exp(e))

@@ -106,9 +106,12 @@ def test_analytic_transmittance(ctx):
     rng = np.random.default_rng(0)
     seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64); u = rng.random(n, dtype=np.float32)
     out = md.sample_t_maj(0, rays, seeds, u, np.array([500, 550, 600, 650], dtype=np.float32))
-    # sigma_maj == sigma_t everywhere -> no null collisions: Tr is 0 or the analytic T_maj
-    est = (out["Tr"][:, 0] * out["T_maj"][:, 0]).mean()
-    assert abs(est - np.exp(-2.5)) < 2e-3 * 5
+    # sigma_maj == sigma_t everywhere -> sigma_n = 0: Tr is 1 for rays with no collision (probability
+    # exp(-sigma_a L)) and 0 otherwise; binomial std at n = 2e5 is 6e-4
+    est = out["Tr"][:, 0].mean()
+    assert abs(est - np.exp(-2.5)) < 3e-3
+    esc = out["n_fetch"] == 0
+    assert np.allclose(out["T_maj"][esc, 0], np.exp(-2.5), rtol=2e-3)  # residual majorant transmittance
     md.close()
 
 

@@ -31,11 +31,14 @@ WORKLOADS = {
     # Disney-cloud stand-in (the real wdas_cloud .nvdb is not in the reference repo and cannot be
     # fetched): fBm cloud at the quarter-res voxel count, 64^3 majorant grid as NanoVDBMedium uses
     # (media.cpp:521), high albedo, forward-peaked phase function, long paths.
-    "disney-cloud-standin-720p": dict(grid=(512, 352, 624), width=1280, height=720, sigma_t=60.0, albedo=0.99,
-                                      g=0.877, max_depth=100, majorant_res=(64, 64, 64)),
+    # sigma_t gives an optical depth of ~100 through the centre; camera framed so the
+    # cloud fills about half of the frame as in the pbrt-v4-scenes disney-cloud view.
+    "disney-cloud-standin-720p": dict(grid=(512, 352, 624), width=1280, height=720, sigma_t=200.0, albedo=0.999,
+                                      g=0.877, max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4),
+                                      fov=16.0),
     # small variant for smoke runs / CPU-box sanity
-    "cloud-small": dict(grid=(96, 80, 104), width=320, height=180, sigma_t=30.0, albedo=0.99, g=0.877,
-                        max_depth=100, majorant_res=(16, 16, 16)),
+    "cloud-small": dict(grid=(96, 80, 104), width=320, height=180, sigma_t=200.0, albedo=0.999, g=0.877,
+                        max_depth=100, majorant_res=(16, 16, 16), eye=(0.0, 0.3, -2.4), fov=16.0),
 }
 
 
@@ -85,7 +88,7 @@ def make_density(w, device):
 def make_scene(w, density, spp, exact):
     return scenes.cloud_scene(density, width=w["width"], height=w["height"], spp=spp, sigma_t=w["sigma_t"],
                               albedo=w["albedo"], g=w["g"], max_depth=w["max_depth"], majorant_res=w["majorant_res"],
-                              exact_math=exact)
+                              exact_math=exact, eye=w.get("eye", (0.0, 0.35, -3.2)), fov=w.get("fov", 20.0))
 
 
 class ClockSampler:

@@ -1,5 +1,17 @@
 // avr_volpath.cu — kernel 1b (see avr_volpath.cuh) and its C entry points.
+//
+// v2 layout of the per-lane state machine: every heavy operation has ONE call site and runs as a
+// warp-convergent phase, so SIMT lanes execute it together and the SASS stays small:
+//   R  regenerate : dead lanes flush their finished sample to the film and pull new (pixel, sample)
+//                   work with one warp-aggregated atomic; runs when >= regen_lanes lanes are dead
+//   S  setup      : boundary hit, RNG seeding, ray -> medium space, slab test, DDA init
+//                   (camera segment or NEE shadow ray: same code, a mode bit apart)
+//   T  track      : trips of {skip empty majorant segments; one tentative collision = one log, one
+//                   exp, one 32-byte density fetch} until >= event_lanes lanes wait for an event
+//   E  events     : scatter -> NEE preparation; shadow end -> NEE accumulate + phase sampling;
+//                   absorb / escape / maxdepth -> lane dead with a pending film sample
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "avr_render_host.h"
@@ -10,46 +22,16 @@ namespace avr {
 
 constexpr int kBlock = 128;
 
-// ---- per-lane building blocks ---------------------------------------------------------------------------
-template <typename TR>
-AVR_DEV void begin_track(const MediumView &mv, PathLane<TR> &ln, V3 o, V3 d, float tMax) {
-    // SampleT_maj prologue (media.h:744-749)
-    float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
-    tMax *= len;
-    d = d / len;
-    MRay mr = ray_to_medium(mv, o, d, tMax);
-    if (mr.hit) ln.dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
-    ln.fe.bind(mv, o, d);
-    ln.T_maj = sconst<TR::NCH>(1.f);
-    ln.in_seg = false;
-    ln.state = 1;
-}
+enum { ST_DEAD = 0, ST_SETUP = 1, ST_TRACK = 2, ST_EV_SCATTER = 3, ST_EV_SHADOW_END = 4, ST_EV_PATH_END = 5 };
 
-// One iteration of VolPathIntegrator::Li's while(true) for a ray inside the boundary:
-// Intersect -> tMax, seed the tracking RNG from the sampler (cpu/integrators.cpp:976-988).
-// Returns false when the ray leaves without touching the boundary (path ends).
+// film / sample write of a finished path: cpu/integrators.cpp:272-297, film.h:95-100,239-255
 template <typename TR>
-AVR_DEV bool begin_camera_segment(const MediumView &mv, const RenderParams &rp, PathLane<TR> &ln, V3 o, V3 d) {
-    float t0, t1;
-    if (!(boundary_hit(rp, o, d, &t0, &t1) && t1 > 0)) return false;
-    ln.wo = -d;
-    uint64_t hash0 = hash_float(ln.srng.uniform());
-    uint64_t hash1 = hash_float(ln.srng.uniform());
-    ln.trng.set_sequence(hash0, hash1);
-    ln.u = ln.srng.uniform();
-    ln.shadow = false;
-    begin_track(mv, ln, o, d, t1);
-    return true;
-}
-
-template <typename TR>
-AVR_DEV void finish_path(const RenderParams &rp, PathLane<TR> &ln, double *film, float *samples_out) {
+AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double *film, float *samples_out) {
     float L[4] = {ln.L[0], ln.L[1], ln.L[2], ln.L[3]};
-    // cpu/integrators.cpp:272-282: NaN / infinite radiance -> black
     bool bad = false;
 #pragma unroll
     for (int i = 0; i < 4; ++i) bad = bad || isnan(L[i]) || isinf(L[i]);
-    if (bad) L[0] = L[1] = L[2] = L[3] = 0.f;
+    if (bad) L[0] = L[1] = L[2] = L[3] = 0.f;  // NaN / infinite radiance -> black
     float lam[4], pdf[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -63,45 +45,45 @@ AVR_DEV void finish_path(const RenderParams &rp, PathLane<TR> &ln, double *film,
         float *o = samples_out + idx * 12;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { o[i] = L[i]; o[4 + i] = lam[i]; o[8 + i] = pdf[i]; }
-    } else {
-        // PixelSensor::ToSensorRGB film.h:95-100 ; RGBFilm::AddSample film.h:239-255 (weight = 1: box filter)
-        float Ld[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) Ld[i] = pdf[i] != 0 ? L[i] / pdf[i] : 0.f;
-        float rgb[3];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            float s = sample_dense1(rp.sensor + c * kNSpec, lam[0]) * Ld[0];
-#pragma unroll
-            for (int i = 1; i < 4; ++i) s += sample_dense1(rp.sensor + c * kNSpec, lam[i]) * Ld[i];
-            rgb[c] = rp.imaging_ratio * (s / 4);
-        }
-        float m = fmaxf(rgb[0], fmaxf(rgb[1], rgb[2]));
-        if (m > rp.max_component) {
-            float k = rp.max_component / m;
-            rgb[0] *= k; rgb[1] *= k; rgb[2] *= k;
-        }
-        double *px = film + 4 * ((size_t)ln.py * rp.width + ln.px);
-        atomicAdd(px + 0, (double)(1.f * rgb[0]));
-        atomicAdd(px + 1, (double)(1.f * rgb[1]));
-        atomicAdd(px + 2, (double)(1.f * rgb[2]));
-        atomicAdd(px + 3, 1.0);
+        return;
     }
-    ln.state = 0;
+    // PixelSensor::ToSensorRGB film.h:95-100 ; RGBFilm::AddSample film.h:239-255 (weight 1: box filter)
+    float Ld[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) Ld[i] = pdf[i] != 0 ? L[i] / pdf[i] : 0.f;
+    float rgb[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float s = sample_dense1(rp.sensor + c * kNSpec, lam[0]) * Ld[0];
+#pragma unroll
+        for (int i = 1; i < 4; ++i) s += sample_dense1(rp.sensor + c * kNSpec, lam[i]) * Ld[i];
+        rgb[c] = rp.imaging_ratio * (s / 4);
+    }
+    float m = fmaxf(rgb[0], fmaxf(rgb[1], rgb[2]));
+    if (m > rp.max_component) {
+        float k = rp.max_component / m;
+        rgb[0] *= k; rgb[1] *= k; rgb[2] *= k;
+    }
+    double *px = film + 4 * ((size_t)ln.py * rp.width + ln.px);
+    if (rgb[0] != 0) atomicAdd(px + 0, (double)(1.f * rgb[0]));  // adding +-0 leaves the sum unchanged
+    if (rgb[1] != 0) atomicAdd(px + 1, (double)(1.f * rgb[1]));
+    if (rgb[2] != 0) atomicAdd(px + 2, (double)(1.f * rgb[2]));
+    atomicAdd(px + 3, 1.0);
 }
 
 // RayIntegrator::EvaluatePixelSample prologue (cpu/integrators.cpp:235-262): sampler start,
-// wavelengths, box-filter camera sample, PerspectiveCamera::GenerateRayDifferential.
+// wavelengths, box-filter camera sample, PerspectiveCamera::GenerateRayDifferential, entry into the
+// boundary.  Leaves the pending camera ray in ln.fe.o / ln.fe.d.  Returns false for a padding item.
 template <typename TR>
 AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<TR> &ln, long long item,
-                        LambdaCtx<TR::NCH> &lc, double *film, float *samples_out) {
+                        LambdaCtx<TR::NCH> &lc) {
     long long npix_pad = rp.total_items / (rp.s1 - rp.s0);
     int s = rp.s0 + int(item / npix_pad);
     long long pi = item % npix_pad;
     int tile = int(pi >> 5), within = int(pi & 31);
     int px = rp.x0 + (tile % rp.tiles_x) * 8 + (within & 7);
     int py = rp.y0 + (tile / rp.tiles_x) * 4 + (within >> 3);
-    if (px >= rp.x1 || py >= rp.y1) { ln.state = 0; return false; }  // padding lane of an edge tile
+    if (px >= rp.x1 || py >= rp.y1) return false;  // padding lane of an edge tile
     ln.px = px; ln.py = py; ln.samp = s;
     // IndependentSampler::StartPixelSample, samplers.h:457-460
     ln.srng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)rp.seed));
@@ -134,45 +116,18 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     ln.r_u = sconst<TR::NCH>(1.f);
     ln.r_l = sconst<TR::NCH>(1.f);
     ln.depth = 0;
-    ln.state = 1;
+    ln.shadow = false;
     // entry into the boundary (Intersect + SkipIntersection of the "interface" surface)
     float t0, t1;
-    if (!(boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0)) { finish_path(rp, ln, film, samples_out); return true; }
-    if (t0 > 0) ro = v3(ro.x + rd.x * t0, ro.y + rd.y * t0, ro.z + rd.z * t0);
-    if (!begin_camera_segment(mv, rp, ln, ro, rd)) finish_path(rp, ln, film, samples_out);
-    return true;
-}
-
-// After the NEE shadow ray (or when NEE contributes nothing): sample the phase function and start
-// the next camera segment (cpu/integrators.cpp:1041-1060).
-template <typename TR>
-AVR_DEV void scatter_continue(const MediumView &mv, const RenderParams &rp, PathLane<TR> &ln, V3 p, double *film,
-                              float *samples_out) {
-    float ua = ln.srng.uniform(), ub = ln.srng.uniform();
-    float pdf;
-    V3 wi = sample_hg(ln.wo, mv.g, ua, ub, &pdf);
-    if (pdf == 0) { finish_path(rp, ln, film, samples_out); return; }
-    ln.beta = ln.beta * (pdf / pdf);
-    ln.r_l = ln.r_u / pdf;
-    if (!begin_camera_segment(mv, rp, ln, p, wi)) finish_path(rp, ln, film, samples_out);
-}
-
-// End of the shadow ray: VolPathIntegrator::SampleLd epilogue (cpu/integrators.cpp:1382-1398).
-template <typename TR>
-AVR_DEV void finish_nee(const RenderParams &rp, PathLane<TR> &ln, Spec<TR::NCH> T_maj) {
-    constexpr int N = TR::NCH;
-    Spec<N> T_ray = ln.T_ray * (T_maj / T_maj[0]);
-    Spec<N> r_l = ln.s_rl * (T_maj / T_maj[0]);
-    if (!nonzero(T_ray)) return;
-    r_l = r_l * (ln.r_u * 1.f);  // r_l *= r_p * p_l ; p_l = 1 (single delta light)
-    float avg = average(r_l);
-    Spec<N> bf = ln.beta * ln.f_hat;
-    bf = bf * T_ray;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float Ll = sample_dense1(rp.light_spec, ln.lambda[i]);
-        ln.L[i] += (bf[i % N] * Ll) / avg;
+    if (!(boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0)) {
+        ln.state = ST_EV_PATH_END;  // L = 0; retired by the event phase of this trip
+        return true;
     }
+    if (t0 > 0) ro = v3(ro.x + rd.x * t0, ro.y + rd.y * t0, ro.z + rd.z * t0);
+    ln.fe.o = ro;
+    ln.fe.d = rd;
+    ln.state = ST_SETUP;
+    return true;
 }
 
 template <typename TR>
@@ -192,180 +147,270 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     }
     const unsigned lane = threadIdx.x & 31;
     PathLane<TR> ln;
-    ln.state = 0;
+    ln.state = ST_DEAD;
     ln.n_cam = ln.n_sh = ln.n_seg = ln.n_sc = 0;
     ln.shadow = false;
     ln.in_seg = false;
     unsigned n_rays = 0;
     LambdaCtx<N> lc;
-    bool retired = false;
+    bool retired = false, pending = false;  // pending: a finished sample waits for its film write
 
     while (true) {
-        // ---- 1. path regeneration: one warp-aggregated atomic for all lanes that need work ----
-        bool need = (ln.state == 0) && !retired;
-        unsigned m = __ballot_sync(0xffffffffu, need);
-        if (m) {
-            unsigned long long base = 0;
-            int leader = __ffs(m) - 1;
-            if ((int)lane == leader) base = atomicAdd(&counters[CNT_WORK], (unsigned long long)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (need) {
-                long long idx = (long long)base + __popc(m & ((1u << lane) - 1));
-                if (idx < rp.local_items) {
-                    long long chunk = idx >> 5;
-                    long long item = ((chunk * rp.world + rp.rank) << 5) + (idx & 31);
-                    if (start_path(mv, rp, ln, item, lc, film, samples_out)) n_rays++;
-                } else
-                    retired = true;
+        // ---- R. regenerate ------------------------------------------------------------------------
+        {
+            bool dead = (ln.state == ST_DEAD) && !retired;
+            unsigned md = __ballot_sync(0xffffffffu, dead);
+            bool none_live = __all_sync(0xffffffffu, ln.state == ST_DEAD);
+            if (md && (__popc(md) >= rp.regen_lanes || none_live)) {
+                if (dead && pending) {
+                    write_sample(rp, ln, film, samples_out);
+                    pending = false;
+                }
+                unsigned long long base = 0;
+                int leader = __ffs(md) - 1;
+                if ((int)lane == leader) base = atomicAdd(&counters[CNT_WORK], (unsigned long long)__popc(md));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (dead) {
+                    long long idx = (long long)base + __popc(md & ((1u << lane) - 1));
+                    if (idx < rp.local_items) {
+                        long long chunk = idx >> 5;
+                        long long item = ((chunk * rp.world + rp.rank) << 5) + (idx & 31);
+                        if (start_path(mv, rp, ln, item, lc)) n_rays++;
+                    } else
+                        retired = true;
+                }
+            }
+            if (__all_sync(0xffffffffu, retired)) break;
+        }
+
+        // ---- S. setup of the next tracking ray (camera segment or shadow ray) -------------------
+        if (ln.state == ST_SETUP) {
+            V3 o = ln.fe.o, d = ln.fe.d;
+            float t0, t1;
+            bool hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
+            float tMax;
+            if (ln.shadow) {
+                // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
+                ln.trng.set_sequence(hash_v3(o), hash_v3(d));
+                tMax = 1 - kShadowEps;
+                if (hit && t1 < tMax) tMax = t1;
+                ln.u = ln.trng.uniform();
+                hit = true;
+            } else {
+                // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
+                ln.wo = -d;
+                tMax = t1;
+                if (hit) {
+                    uint64_t hash0 = hash_float(ln.srng.uniform());
+                    uint64_t hash1 = hash_float(ln.srng.uniform());
+                    ln.trng.set_sequence(hash0, hash1);
+                    ln.u = ln.srng.uniform();
+                }
+            }
+            if (!hit) {
+                ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
+            } else {
+                // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
+                float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
+                tMax *= len;
+                d = d / len;
+                MRay mr = ray_to_medium(mv, o, d, tMax);
+                if (mr.hit) ln.dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
+                ln.fe.bind(mv, o, d);
+                ln.T_maj = sconst<N>(1.f);
+                ln.in_seg = false;
+                ln.state = ST_TRACK;
             }
         }
-        if (__all_sync(0xffffffffu, retired)) break;
 
-        // ---- 2. advance the DDA to the next majorant segment with sigma_maj[0] != 0 -----------
-        if (ln.state == 1 && !ln.in_seg) {
-            while (true) {
-                float a, b;
-                int vox;
-                if (!ln.dda.next(mv, &a, &b, &vox)) {
-                    // majorant iterator exhausted: SampleT_maj returns T_maj
-                    if (ln.shadow) {
-                        finish_nee(rp, ln, ln.T_maj);
-                        scatter_continue(mv, rp, ln, ln.fe.o, film, samples_out);
-                    } else {
-                        // unscattered camera ray leaves the medium and the boundary: no infinite
-                        // lights in the scene class (cpu/integrators.cpp:1081-1106) -> path done
-                        finish_path(rp, ln, film, samples_out);
+        // ---- T. tracking: the SampleT_maj walk ------------------------------------------------------
+        while (true) {
+            unsigned mt = __ballot_sync(0xffffffffu, ln.state == ST_TRACK);
+            unsigned me = __ballot_sync(0xffffffffu, ln.state > ST_TRACK);
+            if (mt == 0 || __popc(me) >= rp.event_lanes) break;
+            // T1. advance the DDA to the next majorant segment with sigma_maj[0] != 0
+            if (ln.state == ST_TRACK && !ln.in_seg) {
+                while (true) {
+                    float a, b;
+                    int vox;
+                    if (!ln.dda.next(mv, &a, &b, &vox)) {
+                        // iterator exhausted: SampleT_maj returns T_maj.  An unscattered camera ray
+                        // leaves medium and boundary; no infinite lights in the scene class
+                        // (cpu/integrators.cpp:1081-1106) -> path done
+                        ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
+                        break;
                     }
+                    ln.n_seg++;
+                    Spec<N> sm = lc.sigma_t * maj[vox];
+                    if (sm[0] == 0) {
+                        float dt = b - a;
+                        if (isinf(dt)) dt = kFltMax;
+                        ln.T_maj = ln.T_maj * exp_neg<EX>(dt, sm);
+                        continue;
+                    }
+                    ln.sigma_maj = sm;
+                    ln.cur_tMin = a;
+                    ln.seg_tMax = b;
+                    ln.in_seg = true;
                     break;
                 }
-                ln.n_seg++;
-                Spec<N> sm = lc.sigma_t * maj[vox];
-                if (sm[0] == 0) {
-                    float dt = b - a;
+            }
+            // T2. one tentative collision along the current segment
+            if (ln.state == ST_TRACK && ln.in_seg) {
+                float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
+                ln.u = ln.trng.uniform();
+                if (t < ln.seg_tMax) {
+                    Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
+                    PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
+                    Spec<N> sigma_maj = ln.sigma_maj;
+                    bool cont;
+                    if (ln.shadow) {
+                        // ratio tracking + Russian roulette, cpu/integrators.cpp:1356-1378
+                        ln.n_sh++;
+                        Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                        float pdf = T_maj[0] * sigma_maj[0];
+                        ln.T_ray = ln.T_ray * (T_maj * sigma_n / pdf);
+                        ln.s_rl = ln.s_rl * (T_maj * sigma_maj / pdf);
+                        ln.s_ru = ln.s_ru * (T_maj * sigma_n / pdf);
+                        Spec<N> Tr = ln.T_ray / average(ln.s_rl + ln.s_ru);
+                        if (max_component(Tr) < 0.05f) {
+                            float q = 0.75f;
+                            if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
+                            else ln.T_ray = ln.T_ray / (1 - q);
+                        }
+                        cont = nonzero(ln.T_ray);
+                        if (!cont) {
+                            ln.T_maj = sconst<N>(1.f);  // SampleT_maj returns 1 when the callback stops
+                            ln.state = ST_EV_SHADOW_END;
+                        }
+                    } else {
+                        // VolPathIntegrator::Li callback, cpu/integrators.cpp:990-1078
+                        cont = false;
+                        if (!nonzero(ln.beta)) {
+                            ln.state = ST_EV_PATH_END;
+                        } else {
+                            ln.n_cam++;
+                            if (TR::GENERAL && ln.depth < rp.max_depth && nonzero(mp.Le)) {
+                                float pdf = sigma_maj[0] * T_maj[0];
+                                Spec<N> betap = ln.beta * T_maj / pdf;
+                                Spec<N> r_e = ln.r_u * sigma_maj * T_maj / pdf;
+                                if (nonzero(r_e)) {
+                                    float avg = average(r_e);
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i)
+                                        ln.L[i] += ((betap[i % N] * mp.sigma_a[i % N]) * mp.Le[i]) / avg;
+                                }
+                            }
+                            float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                            float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                            float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
+                            float um = ln.trng.uniform();
+                            int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
+                            if (mode == 0) {
+                                ln.state = ST_EV_PATH_END;
+                            } else if (mode == 1) {
+                                if (ln.depth++ >= rp.max_depth) {
+                                    ln.state = ST_EV_PATH_END;
+                                } else {
+                                    float pdf = T_maj[0] * mp.sigma_s[0];
+                                    ln.beta = ln.beta * (T_maj * mp.sigma_s / pdf);
+                                    ln.r_u = ln.r_u * (T_maj * mp.sigma_s / pdf);
+                                    if (nonzero(ln.beta) && nonzero(ln.r_u)) {
+                                        ln.cur_tMin = t;  // scatter position parameter for the event phase
+                                        ln.state = ST_EV_SCATTER;
+                                    } else
+                                        ln.state = ST_EV_PATH_END;
+                                }
+                            } else {
+                                Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                                float pdf = T_maj[0] * sigma_n[0];
+                                ln.beta = ln.beta * (T_maj * sigma_n / pdf);
+                                if (pdf == 0) ln.beta = sconst<N>(0.f);
+                                ln.r_u = ln.r_u * (T_maj * sigma_n / pdf);
+                                ln.r_l = ln.r_l * (T_maj * sigma_maj / pdf);
+                                cont = nonzero(ln.beta) && nonzero(ln.r_u);
+                                if (!cont) ln.state = ST_EV_PATH_END;
+                            }
+                        }
+                    }
+                    if (cont) {
+                        ln.T_maj = sconst<N>(1.f);
+                        ln.cur_tMin = t;
+                    }
+                } else {
+                    float dt = ln.seg_tMax - ln.cur_tMin;
                     if (isinf(dt)) dt = kFltMax;
-                    ln.T_maj = ln.T_maj * exp_neg<EX>(dt, sm);
-                    continue;
+                    ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
+                    ln.in_seg = false;
                 }
-                ln.sigma_maj = sm;
-                ln.cur_tMin = a;
-                ln.seg_tMax = b;
-                ln.in_seg = true;
-                break;
             }
         }
 
-        // ---- 3. one tentative collision along the current segment ---------------------------------
-        if (ln.state == 1 && ln.in_seg) {
-            float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
-            ln.u = ln.trng.uniform();
-            if (t < ln.seg_tMax) {
-                Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
-                PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
-                Spec<N> sigma_maj = ln.sigma_maj;
-                bool cont;
-                if (ln.shadow) {
-                    // ratio tracking + Russian roulette, cpu/integrators.cpp:1356-1378
-                    ln.n_sh++;
-                    Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                    float pdf = T_maj[0] * sigma_maj[0];
-                    ln.T_ray = ln.T_ray * (T_maj * sigma_n / pdf);
-                    ln.s_rl = ln.s_rl * (T_maj * sigma_maj / pdf);
-                    ln.s_ru = ln.s_ru * (T_maj * sigma_n / pdf);
-                    Spec<N> Tr = ln.T_ray / average(ln.s_rl + ln.s_ru);
-                    if (max_component(Tr) < 0.05f) {
-                        float q = 0.75f;
-                        if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
-                        else ln.T_ray = ln.T_ray / (1 - q);
-                    }
-                    cont = nonzero(ln.T_ray);
-                    if (!cont) scatter_continue(mv, rp, ln, ln.fe.o, film, samples_out);  // Ld = 0
-                } else {
-                    // VolPathIntegrator::Li callback, cpu/integrators.cpp:990-1078
-                    cont = false;
-                    if (!nonzero(ln.beta)) {
-                        finish_path(rp, ln, film, samples_out);
-                    } else {
-                        ln.n_cam++;
-                        if (TR::GENERAL && ln.depth < rp.max_depth && nonzero(mp.Le)) {
-                            float pdf = sigma_maj[0] * T_maj[0];
-                            Spec<N> betap = ln.beta * T_maj / pdf;
-                            Spec<N> r_e = ln.r_u * sigma_maj * T_maj / pdf;
-                            if (nonzero(r_e)) {
-                                float avg = average(r_e);
+        // ---- E. events ----------------------------------------------------------------------------------
+        // E1. real scattering: SampleLd prologue (cpu/integrators.cpp:1300-1338) -> pending shadow ray
+        if (ln.state == ST_EV_SCATTER) {
+            ln.n_sc++;
+            V3 p = ln.fe.point(ln.cur_tMin);
+            ln.srng.uniform();  // light choice (single light, p = 1)
+            ln.srng.uniform();  // uLight
+            ln.srng.uniform();
+            V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
+            float two_r = 2 * rp.scene_radius;
+            V3 pLight = v3(p.x + wi.x * two_r, p.y + wi.y * two_r, p.z + wi.z * two_r);
+            bool lit = false;
 #pragma unroll
-                                for (int i = 0; i < 4; ++i)
-                                    ln.L[i] += ((betap[i % N] * mp.sigma_a[i % N]) * mp.Le[i]) / avg;
-                            }
-                        }
-                        float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
-                        float pScatter = mp.sigma_s[0] / sigma_maj[0];
-                        float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
-                        float um = ln.trng.uniform();
-                        int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
-                        if (mode == 0) {
-                            finish_path(rp, ln, film, samples_out);
-                        } else if (mode == 1) {
-                            if (ln.depth++ >= rp.max_depth) {
-                                finish_path(rp, ln, film, samples_out);
-                            } else {
-                                float pdf = T_maj[0] * mp.sigma_s[0];
-                                ln.beta = ln.beta * (T_maj * mp.sigma_s / pdf);
-                                ln.r_u = ln.r_u * (T_maj * mp.sigma_s / pdf);
-                                if (nonzero(ln.beta) && nonzero(ln.r_u)) {
-                                    ln.n_sc++;
-                                    // SampleLd prologue, cpu/integrators.cpp:1300-1338
-                                    V3 p = ln.fe.point(t);
-                                    ln.srng.uniform();  // light choice (single light, p = 1)
-                                    ln.srng.uniform();  // uLight
-                                    ln.srng.uniform();
-                                    V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
-                                    float two_r = 2 * rp.scene_radius;
-                                    V3 pLight = v3(p.x + wi.x * two_r, p.y + wi.y * two_r, p.z + wi.z * two_r);
-                                    bool lit = false;
-#pragma unroll
-                                    for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
-                                    float ph = henyey_greenstein(dot(ln.wo, wi), mv.g);
-                                    V3 rd = pLight - p;
-                                    if (lit && ph != 0 && !(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
-                                        ln.f_hat = ph;
-                                        ln.T_ray = sconst<N>(1.f);
-                                        ln.s_rl = sconst<N>(1.f);
-                                        ln.s_ru = sconst<N>(1.f);
-                                        ln.trng.set_sequence(hash_v3(p), hash_v3(rd));
-                                        float t0, t1, tMax = 1 - kShadowEps;
-                                        if (boundary_hit(rp, p, rd, &t0, &t1) && t1 > 0 && t1 < tMax) tMax = t1;
-                                        ln.u = ln.trng.uniform();
-                                        ln.shadow = true;
-                                        begin_track(mv, ln, p, rd, tMax);
-                                    } else {
-                                        scatter_continue(mv, rp, ln, p, film, samples_out);
-                                    }
-                                } else {
-                                    finish_path(rp, ln, film, samples_out);
-                                }
-                            }
-                        } else {
-                            Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                            float pdf = T_maj[0] * sigma_n[0];
-                            ln.beta = ln.beta * (T_maj * sigma_n / pdf);
-                            if (pdf == 0) ln.beta = sconst<N>(0.f);
-                            ln.r_u = ln.r_u * (T_maj * sigma_n / pdf);
-                            ln.r_l = ln.r_l * (T_maj * sigma_maj / pdf);
-                            cont = nonzero(ln.beta) && nonzero(ln.r_u);
-                            if (!cont) finish_path(rp, ln, film, samples_out);
-                        }
-                    }
-                }
-                if (cont) {
-                    ln.T_maj = sconst<N>(1.f);
-                    ln.cur_tMin = t;
-                }
+            for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
+            float ph = henyey_greenstein(dot(ln.wo, wi), mv.g);
+            V3 rd = pLight - p;
+            ln.fe.o = p;  // scatter point: origin of the shadow ray and of the next camera segment
+            if (lit && ph != 0 && !(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
+                ln.f_hat = ph;
+                ln.T_ray = sconst<N>(1.f);
+                ln.s_rl = sconst<N>(1.f);
+                ln.s_ru = sconst<N>(1.f);
+                ln.fe.d = rd;
+                ln.shadow = true;
+                ln.state = ST_SETUP;
             } else {
-                float dt = ln.seg_tMax - ln.cur_tMin;
-                if (isinf(dt)) dt = kFltMax;
-                ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
-                ln.in_seg = false;
+                ln.T_ray = sconst<N>(0.f);  // Ld = 0: straight to phase sampling
+                ln.T_maj = sconst<N>(1.f);
+                ln.state = ST_EV_SHADOW_END;
             }
+        }
+        // E2. end of the shadow ray: SampleLd epilogue (cpu/integrators.cpp:1382-1398), then phase
+        //     sampling and the next camera segment (cpu/integrators.cpp:1041-1060)
+        if (ln.state == ST_EV_SHADOW_END) {
+            Spec<N> T_ray = ln.T_ray * (ln.T_maj / ln.T_maj[0]);
+            if (nonzero(T_ray)) {
+                Spec<N> r_l = ln.s_rl * (ln.T_maj / ln.T_maj[0]);
+                r_l = r_l * (ln.r_u * 1.f);  // r_l *= r_p * p_l ; p_l = 1 (single delta light)
+                float avg = average(r_l);
+                Spec<N> bf = ln.beta * ln.f_hat;
+                bf = bf * T_ray;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float Ll = sample_dense1(rp.light_spec, ln.lambda[i]);
+                    ln.L[i] += (bf[i % N] * Ll) / avg;
+                }
+            }
+            float ua = ln.srng.uniform(), ub = ln.srng.uniform();
+            float pdf;
+            V3 wi = sample_hg(ln.wo, mv.g, ua, ub, &pdf);
+            if (pdf == 0) {
+                ln.state = ST_EV_PATH_END;
+            } else {
+                ln.beta = ln.beta * (pdf / pdf);
+                ln.r_l = ln.r_u / pdf;
+                ln.fe.d = wi;  // fe.o still holds the scatter point
+                ln.shadow = false;
+                ln.state = ST_SETUP;
+            }
+        }
+        // E3. path finished (absorbed, escaped, max depth, zero throughput): the film write waits for
+        //     the regeneration phase so that it runs convergently
+        if (ln.state == ST_EV_PATH_END) {
+            ln.state = ST_DEAD;
+            pending = true;
         }
     }
 

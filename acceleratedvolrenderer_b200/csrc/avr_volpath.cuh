@@ -37,6 +37,8 @@ struct RenderParams {
     long long local_items;    // work items owned by this rank (multiple of 32)
     long long total_items;    // padded global item count
     int dump_samples;         // 1: write L/lambda/pdf per sample instead of the film
+    int regen_lanes;          // dead lanes per warp that trigger the regeneration phase
+    int event_lanes;          // lanes waiting for an event that end the tracking phase
 };
 
 // stats slots in the counters array
@@ -86,7 +88,7 @@ struct PathLane {
     Spec<N> beta, r_u, r_l;
     int depth;
     // tracking state (camera segment or shadow ray)
-    int state;         // 0 need work, 1 tracking, 2 retired
+    int state;         // ST_* of avr_volpath.cu
     bool shadow, in_seg;
     Fetcher<TR> fe;
     DDA dda;

@@ -37,8 +37,9 @@ struct RenderParams {
     long long local_items;    // work items owned by this rank (multiple of 32)
     long long total_items;    // padded global item count
     int dump_samples;         // 1: write L/lambda/pdf per sample instead of the film
-    int regen_lanes;          // dead lanes per warp that trigger the regeneration phase
-    int event_lanes;          // lanes waiting for an event that end the tracking phase
+    int op_weight[6];         // scheduler weights of the ops R, S, A, B, E1, E2 (avr_volpath.cu)
+    int walk_steps;           // DDA steps per A trip
+    int collide_repeat;       // B repeats while at least this many lanes stay in a segment
 };
 
 // stats slots in the counters array
@@ -89,7 +90,7 @@ struct PathLane {
     int depth;
     // tracking state (camera segment or shadow ray)
     int state;         // ST_* of avr_volpath.cu
-    bool shadow, in_seg;
+    bool shadow;
     Fetcher<TR> fe;
     DDA dda;
     float cur_tMin, seg_tMax, u;

@@ -3,7 +3,7 @@
 
 Prints one line per configuration: kernel ms for 1 spp at the bench workload, fetches, GB/s.
 Knobs are environment variables read by the library at every render call:
-AVR_REGEN_LANES, AVR_EVENT_LANES, AVR_BLOCKS_PER_SM.
+AVR_OP_WEIGHTS (R,S,A,B,E1,E2), AVR_WALK_STEPS, AVR_COLLIDE_REPEAT, AVR_BLOCKS_PER_SM.
 """
 import argparse
 import itertools
@@ -25,9 +25,8 @@ def main():
     ap.add_argument("--spp", type=int, default=1)
     ap.add_argument("--layouts", default="octet32")
     ap.add_argument("--exact", default="0")
-    ap.add_argument("--regen", default="8")
-    ap.add_argument("--event", default="8")
-    ap.add_argument("--bpsm", default="0")
+    ap.add_argument("--env", action="append", default=[],
+                    help="NAME=v1;v2;... (repeatable); the product of all lists is swept")
     ap.add_argument("--reps", type=int, default=2)
     args = ap.parse_args()
     w = bench.WORKLOADS[args.workload]
@@ -39,11 +38,11 @@ def main():
     for layout in args.layouts.split(","):
         gd, rd = bench.make_scene(w, density, args.spp, 0)
         med = ctx.create_medium("uniformgrid", gd, layout=layout)
-        for exact, rg, ev, bp in itertools.product(args.exact.split(","), args.regen.split(","),
-                                                   args.event.split(","), args.bpsm.split(",")):
-            os.environ["AVR_REGEN_LANES"] = rg
-            os.environ["AVR_EVENT_LANES"] = ev
-            os.environ["AVR_BLOCKS_PER_SM"] = bp
+        names = [e.split("=", 1)[0] for e in args.env]
+        lists = [e.split("=", 1)[1].split(";") for e in args.env]
+        for exact, *vals in itertools.product(args.exact.split(","), *lists):
+            for n, v in zip(names, vals):
+                os.environ[n] = v
             r = rd.with_(exact_math=int(exact))
             best = None
             for i in range(args.reps + 1):
@@ -53,7 +52,7 @@ def main():
                     best = st
             f = best["camera_fetches"] + best["shadow_fetches"]
             bpf = 16 if layout == "octet16" else 32
-            print(json.dumps({"layout": layout, "exact": int(exact), "regen": int(rg), "event": int(ev), "bpsm": int(bp),
+            print(json.dumps({"layout": layout, "exact": int(exact), "env": dict(zip(names, vals)),
                               "kernel_ms": round(best["kernel_ms"], 2),
                               "Msamples_s": round(W * H * args.spp / best["kernel_ms"] / 1e3, 2),
                               "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1)}),

@@ -13,6 +13,7 @@ struct avr_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
+    size_t smem_per_sm = 0, smem_per_block_optin = 0;
     std::string err;
     // render scratch (grown on demand)
     unsigned long long *d_counters = nullptr;  // work counter + stats

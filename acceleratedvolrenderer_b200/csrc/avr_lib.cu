@@ -49,6 +49,8 @@ extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
     cudaDeviceProp prop;
     AVR_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
+    ctx->smem_per_block_optin = prop.sharedMemPerBlockOptin;
     AVR_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     AVR_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     AVR_CUDA(nullptr, cudaEventCreate(&ctx->ev1));

@@ -145,308 +145,622 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     return true;
 }
 
+// ---- CTA path pool ------------------------------------------------------------------------------------
+// A CTA owns `pool` paths whose state lives in shared-memory slots; a lane copies a slot into
+// registers, runs one op on it and copies it back.  Between ops a path waits in one of four queues
+// (slot ids), so ANY lane of the CTA can pick it up: event ops run on full 32-path batches and the
+// tracking loop refills a lane the moment its path hits an event.
+
+enum { Q_DEAD = 0, Q_SCATTER = 1, Q_SHADOW_END = 2, Q_TRACK = 3, kNumQueues = 4 };
+
+// bounded MPMC ring (Vyukov cell sequence numbers) + a committed-entries counter for batched pops
+struct PoolQueue {
+    unsigned head, tail;   // monotonic positions
+    int count;             // entries committed and not yet claimed
+    unsigned pad;
+};
+
+struct PoolView {
+    uint4 *slots;              // pool * kSlotQuads
+    volatile unsigned *seq;    // kNumQueues * cap
+    volatile unsigned short *data;
+    PoolQueue *q;              // kNumQueues
+    volatile int *live;        // slots not yet retired
+    unsigned cap_mask;         // cap - 1 (cap = power of two >= pool)
+    unsigned cap;
+};
+
+// Push the slot ids of the lanes in `mask` (a subset of the converged lanes calling this) to queue qi.
+// The callers' slot stores must precede the call; the fence below publishes them.
+AVR_DEV void pool_push(const PoolView &pv, int qi, unsigned mask, unsigned lane, int slot) {
+    if (mask == 0) return;
+    int n = __popc(mask);
+    int leader = __ffs(mask) - 1;
+    unsigned pos0 = 0;
+    __threadfence_block();
+    if ((int)lane == leader) pos0 = atomicAdd(&pv.q[qi].tail, (unsigned)n);
+    pos0 = __shfl_sync(0xffffffffu, pos0, leader);
+    if (mask >> lane & 1u) {
+        unsigned pos = pos0 + __popc(mask & ((1u << lane) - 1));
+        unsigned cell = qi * pv.cap + (pos & pv.cap_mask);
+        while (pv.seq[cell] != pos) {}
+        pv.data[cell] = (unsigned short)slot;
+        __threadfence_block();
+        pv.seq[cell] = pos + 1;
+    }
+    __syncwarp();
+    if ((int)lane == leader) atomicAdd(&pv.q[qi].count, n);
+}
+
+// Pop up to `want` slot ids from queue qi.  Returns n; lane k (k-th set bit of `takers`) receives the
+// k-th id in *slot when k < n.  `takers` are the lanes that want a path; all 32 lanes must call.
+AVR_DEV int pool_pop(const PoolView &pv, int qi, unsigned takers, unsigned lane, int *slot) {
+    int want = __popc(takers);
+    int n = 0;
+    unsigned pos0 = 0;
+    if (lane == 0 && want > 0) {
+        int c = *(volatile int *)&pv.q[qi].count;
+        while (true) {
+            n = c < want ? c : want;
+            if (n <= 0) { n = 0; break; }
+            int old = atomicCAS(&pv.q[qi].count, c, c - n);
+            if (old == c) break;
+            c = old;
+        }
+        if (n > 0) pos0 = atomicAdd(&pv.q[qi].head, (unsigned)n);
+    }
+    n = __shfl_sync(0xffffffffu, n, 0);
+    pos0 = __shfl_sync(0xffffffffu, pos0, 0);
+    if (takers >> lane & 1u) {
+        int k = __popc(takers & ((1u << lane) - 1));
+        if (k < n) {
+            unsigned pos = pos0 + k;
+            unsigned cell = qi * pv.cap + (pos & pv.cap_mask);
+            while (pv.seq[cell] != pos + 1) {}
+            *slot = pv.data[cell];
+            __threadfence_block();
+            pv.seq[cell] = pos + pv.cap;
+        }
+    }
+    __syncwarp();
+    __threadfence_block();
+    return n;
+}
+
+// Slot <-> register copy of a path.  Word order is fixed by the two functions below; kSlotQuads is
+// odd so that consecutive slots start in different 16-byte bank groups.
 template <typename TR>
-__global__ void __launch_bounds__(kBlock)
-k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *film, float *samples_out) {
+struct SlotIO {
+    static constexpr int N = TR::NCH;
+    static constexpr int kWords = 2 + 4 + 4 + 4 + 3 * N + 1 + 12 + 12 + 3 + 2 * N + 4 + 3 * N + 1 + 3 + 2 * N;
+    static constexpr int kQuadsRaw = (kWords + 3) / 4;
+    static constexpr int kSlotQuads = kQuadsRaw | 1;
+
+    template <typename F>
+    AVR_DEV static void visit(PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending, F &&f) {
+        // f(uint32_t&) or f(float&) for every persistent word, always in this order
+        unsigned pxy = (unsigned)ln.px | ((unsigned)ln.py << 16);
+        f(pxy);
+        ln.px = int(pxy & 0xffffu); ln.py = int(pxy >> 16);
+        unsigned sm = (unsigned)ln.samp;
+        f(sm);
+        ln.samp = (int)sm;
+        unsigned lo, hi;
+        lo = (unsigned)ln.srng.state; hi = (unsigned)(ln.srng.state >> 32); f(lo); f(hi);
+        ln.srng.state = ((uint64_t)hi << 32) | lo;
+        lo = (unsigned)ln.srng.inc; hi = (unsigned)(ln.srng.inc >> 32); f(lo); f(hi);
+        ln.srng.inc = ((uint64_t)hi << 32) | lo;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f(ln.lambda[i]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f(ln.L[i]);
+#pragma unroll
+        for (int i = 0; i < N; ++i) { f(ln.beta.v[i]); f(ln.r_u.v[i]); f(ln.r_l.v[i]); }
+        unsigned fl = (unsigned)ln.state | ((unsigned)ln.shadow << 8) | ((unsigned)pending << 9) | ((unsigned)ln.depth << 16);
+        f(fl);
+        ln.state = int(fl & 0xffu); ln.shadow = (fl >> 8) & 1u; pending = (fl >> 9) & 1u; ln.depth = int(fl >> 16);
+        f(ln.fe.o.x); f(ln.fe.o.y); f(ln.fe.o.z); f(ln.fe.d.x); f(ln.fe.d.y); f(ln.fe.d.z);
+        f(ln.fe.so.x); f(ln.fe.so.y); f(ln.fe.so.z); f(ln.fe.sd.x); f(ln.fe.sd.y); f(ln.fe.sd.z);
+        f(ln.dda.tMin); f(ln.dda.tMax);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { f(ln.dda.nextCrossingT[i]); f(ln.dda.deltaT[i]); }
+        unsigned vx = (unsigned)(ln.dda.voxel[0] + 1), vy = (unsigned)(ln.dda.voxel[1] + 1), vz = (unsigned)(ln.dda.voxel[2] + 1);
+        f(vx); f(vy); f(vz);
+        ln.dda.voxel[0] = int(vx) - 1; ln.dda.voxel[1] = int(vy) - 1; ln.dda.voxel[2] = int(vz) - 1;
+        unsigned sb = (unsigned)ln.dda.stepBits;
+        f(sb);
+        ln.dda.stepBits = (int)sb;
+        f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
+#pragma unroll
+        for (int i = 0; i < N; ++i) { f(ln.sigma_maj.v[i]); f(ln.T_maj.v[i]); }
+        lo = (unsigned)ln.trng.state; hi = (unsigned)(ln.trng.state >> 32); f(lo); f(hi);
+        ln.trng.state = ((uint64_t)hi << 32) | lo;
+        lo = (unsigned)ln.trng.inc; hi = (unsigned)(ln.trng.inc >> 32); f(lo); f(hi);
+        ln.trng.inc = ((uint64_t)hi << 32) | lo;
+#pragma unroll
+        for (int i = 0; i < N; ++i) { f(ln.T_ray.v[i]); f(ln.s_rl.v[i]); f(ln.s_ru.v[i]); }
+        f(ln.f_hat);
+        f(ln.wo.x); f(ln.wo.y); f(ln.wo.z);
+#pragma unroll
+        for (int i = 0; i < N; ++i) { f(lc.sig_a.v[i]); f(lc.sig_s.v[i]); }
+    }
+
+    struct Packer {
+        unsigned w[kSlotQuads * 4];
+        int k = 0;
+        AVR_DEV void operator()(unsigned &x) { w[k++] = x; }
+        AVR_DEV void operator()(float &x) { w[k++] = __float_as_uint(x); }
+    };
+    struct Unpacker {
+        unsigned w[kSlotQuads * 4];
+        int k = 0;
+        AVR_DEV void operator()(unsigned &x) { x = w[k++]; }
+        AVR_DEV void operator()(float &x) { x = __uint_as_float(w[k++]); }
+    };
+
+    AVR_DEV static void store(uint4 *sp, PathLane<TR> &ln, LambdaCtx<N> &lc, bool pending) {
+        Packer p;
+        visit(ln, lc, pending, p);
+#pragma unroll
+        for (int i = p.k; i < kSlotQuads * 4; ++i) p.w[i] = 0;
+#pragma unroll
+        for (int q = 0; q < kQuadsRaw; ++q) sp[q] = make_uint4(p.w[4 * q], p.w[4 * q + 1], p.w[4 * q + 2], p.w[4 * q + 3]);
+    }
+    AVR_DEV static void load(const uint4 *sp, const MediumView &mv, PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending) {
+        Unpacker u;
+#pragma unroll
+        for (int q = 0; q < kQuadsRaw; ++q) {
+            uint4 v = sp[q];
+            u.w[4 * q] = v.x; u.w[4 * q + 1] = v.y; u.w[4 * q + 2] = v.z; u.w[4 * q + 3] = v.w;
+        }
+        visit(ln, lc, pending, u);
+        // derived: sigma_t and the wavelengths of the batch (make_lambda_ctx, avr_tmaj.cuh)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) lc.lambda[i] = ln.lambda[i];
+        if (mv.kind == KIND_RGB) lc.sigma_t = sconst<N>(1.f);
+        else lc.sigma_t = lc.sig_a + lc.sig_s;
+    }
+};
+
+// shared-memory layout, computed identically on host and device
+struct PoolLayout {
+    unsigned off_slots, off_seq, off_data, off_q, off_live, total, cap;
+};
+__host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned pool, unsigned slot_quads) {
+    PoolLayout l;
+    l.cap = 32;
+    while (l.cap < pool) l.cap <<= 1;
+    l.off_slots = (maj_bytes + 15u) & ~15u;
+    l.off_seq = l.off_slots + pool * slot_quads * 16u;
+    l.off_data = l.off_seq + kNumQueues * l.cap * 4u;
+    l.off_q = (l.off_data + kNumQueues * l.cap * 2u + 15u) & ~15u;
+    l.off_live = l.off_q + kNumQueues * (unsigned)sizeof(PoolQueue);
+    l.total = l.off_live + 16u;
+    return l;
+}
+
+template <typename TR>
+struct KernelCfg {
+    static constexpr int kThreads = 256;
+    static constexpr int kMinBlocks = (TR::NCH == 1 && !TR::GENERAL) ? 2 : 1;
+};
+
+struct LaneCounters {
+    unsigned rays, cam, sh, seg, sc;
+};
+
+// After an op: hand every path of the batch to the queue of the op it waits for next.
+template <typename TR>
+AVR_DEV void requeue(const PoolView &pv, unsigned lane, bool have, int slot, PathLane<TR> &ln,
+                     LambdaCtx<TR::NCH> &lc, bool pending) {
+    if (have && ln.state == ST_EV_PATH_END) {
+        // absorbed / escaped / max depth / zero throughput: the film write happens in the next R op
+        ln.state = ST_DEAD;
+        pending = true;
+    }
+    if (have && ln.state != ST_RETIRED) SlotIO<TR>::store(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln, lc, pending);
+    __syncwarp();
+    unsigned m_tr = __ballot_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_COLLIDE));
+    unsigned m_sc = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SCATTER);
+    unsigned m_se = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SHADOW_END);
+    unsigned m_dd = __ballot_sync(0xffffffffu, have && ln.state == ST_DEAD);
+    unsigned m_rt = __ballot_sync(0xffffffffu, have && ln.state == ST_RETIRED);
+    pool_push(pv, Q_TRACK, m_tr, lane, slot);
+    pool_push(pv, Q_SCATTER, m_sc, lane, slot);
+    pool_push(pv, Q_SHADOW_END, m_se, lane, slot);
+    pool_push(pv, Q_DEAD, m_dd, lane, slot);
+    if (m_rt && lane == 0) atomicSub((int *)pv.live, __popc(m_rt));
+}
+
+// One batch of an event op (R, E1 or E2, chosen warp-uniformly by the queue served), followed by the
+// ray setup S for every path of the batch that now has a pending ray.
+template <typename TR>
+AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const PoolView &pv, int qi, unsigned lane,
+                         PathLane<TR> &ln, LambdaCtx<TR::NCH> &lc, LaneCounters &cn, unsigned long long *counters,
+                         double *film, float *samples_out) {
+    constexpr int N = TR::NCH;
+    int slot = 0;
+    int n = pool_pop(pv, qi, 0xffffffffu, lane, &slot);
+    if (n == 0) return;
+    bool have = (int)lane < n;
+    bool pending = false;
+    if (have) SlotIO<TR>::load(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
+
+    if (qi == Q_DEAD) {
+        // ---- R. regenerate: flush the finished sample, fetch work with one aggregated atomic ---------
+        if (have && pending) {
+            write_sample(rp, ln, film, samples_out);
+            pending = false;
+        }
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&counters[CNT_WORK], (unsigned long long)n);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (have) {
+            long long idx = (long long)base + lane;
+            if (idx < rp.local_items) {
+                long long chunk = idx >> 5;
+                long long item = ((chunk * rp.world + rp.rank) << 5) + (idx & 31);
+                if (start_path(mv, rp, ln, item, lc)) cn.rays++;
+                else ln.state = ST_DEAD;  // padding item of an edge tile: nothing pending, fetch again
+            } else
+                ln.state = ST_RETIRED;
+        }
+    } else if (qi == Q_SCATTER) {
+        // ---- E1. real scattering: SampleLd prologue (cpu/integrators.cpp:1300-1338) -> shadow ray ----
+        if (have) {
+            cn.sc++;
+            V3 p = ln.fe.point(ln.cur_tMin);
+            ln.srng.uniform();  // light choice (single light, p = 1)
+            ln.srng.uniform();  // uLight
+            ln.srng.uniform();
+            V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
+            float two_r = 2 * rp.scene_radius;
+            V3 pLight = v3(p.x + wi.x * two_r, p.y + wi.y * two_r, p.z + wi.z * two_r);
+            bool lit = false;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
+            float ph = henyey_greenstein(dot(ln.wo, wi), mv.g);
+            V3 rd = pLight - p;
+            ln.fe.o = p;  // scatter point: origin of the shadow ray and of the next camera segment
+            if (lit && ph != 0 && !(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
+                ln.f_hat = ph;
+                ln.T_ray = sconst<N>(1.f);
+                ln.s_rl = sconst<N>(1.f);
+                ln.s_ru = sconst<N>(1.f);
+                ln.fe.d = rd;
+                ln.shadow = true;
+                ln.state = ST_SETUP;
+            } else {
+                ln.T_ray = sconst<N>(0.f);  // Ld = 0: straight to phase sampling
+                ln.T_maj = sconst<N>(1.f);
+                ln.state = ST_EV_SHADOW_END;
+            }
+        }
+    } else {
+        // ---- E2. end of the shadow ray: SampleLd epilogue (cpu/integrators.cpp:1382-1398), then phase
+        //      sampling and the next camera segment (cpu/integrators.cpp:1041-1060) -------------------
+        if (have) {
+            Spec<N> T_ray = ln.T_ray * (ln.T_maj / ln.T_maj[0]);
+            if (nonzero(T_ray)) {
+                Spec<N> r_l = ln.s_rl * (ln.T_maj / ln.T_maj[0]);
+                r_l = r_l * (ln.r_u * 1.f);  // r_l *= r_p * p_l ; p_l = 1 (single delta light)
+                float avg = average(r_l);
+                Spec<N> bf = ln.beta * ln.f_hat;
+                bf = bf * T_ray;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float Ll = sample_dense1(rp.light_spec, ln.lambda[i]);
+                    ln.L[i] += (bf[i % N] * Ll) / avg;
+                }
+            }
+            float ua = ln.srng.uniform(), ub = ln.srng.uniform();
+            float pdf;
+            V3 wi = sample_hg(ln.wo, mv.g, ua, ub, &pdf);
+            if (pdf == 0) {
+                ln.state = ST_EV_PATH_END;
+            } else {
+                ln.beta = ln.beta * (pdf / pdf);
+                ln.r_l = ln.r_u / pdf;
+                ln.fe.d = wi;  // fe.o still holds the scatter point
+                ln.shadow = false;
+                ln.state = ST_SETUP;
+            }
+        }
+    }
+
+    // ---- S. setup of the pending ray (camera segment or shadow ray) ------------------------------------
+    if (have && ln.state == ST_SETUP) {
+        V3 o = ln.fe.o, d = ln.fe.d;
+        float t0, t1;
+        bool hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
+        float tMax;
+        if (ln.shadow) {
+            // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
+            ln.trng.set_sequence(hash_v3(o), hash_v3(d));
+            tMax = 1 - kShadowEps;
+            if (hit && t1 < tMax) tMax = t1;
+            ln.u = ln.trng.uniform();
+            hit = true;
+        } else {
+            // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
+            ln.wo = -d;
+            tMax = t1;
+            if (hit) {
+                uint64_t hash0 = hash_float(ln.srng.uniform());
+                uint64_t hash1 = hash_float(ln.srng.uniform());
+                ln.trng.set_sequence(hash0, hash1);
+                ln.u = ln.srng.uniform();
+            }
+        }
+        if (!hit) {
+            ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
+        } else {
+            // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
+            float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
+            tMax *= len;
+            d = d / len;
+            MRay mr = ray_to_medium(mv, o, d, tMax);
+            if (mr.hit) ln.dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
+            ln.fe.bind(mv, o, d);
+            ln.T_maj = sconst<N>(1.f);
+            ln.state = ST_WALK;
+        }
+    }
+    requeue<TR>(pv, lane, have, slot, ln, lc, pending);
+}
+
+// Tracking loop of one warp: every lane holds a path in registers and walks SampleT_maj (ops A and B);
+// a lane whose path reaches an event parks it in its slot, queues it for the event op and is refilled
+// from Q_TRACK.  The warp leaves when it runs dry, or yields its few remaining paths back to Q_TRACK
+// when event batches are waiting.
+template <typename TR>
+AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const PoolView &pv, const float *maj,
+                        unsigned lane, PathLane<TR> &ln, LambdaCtx<TR::NCH> &lc, LaneCounters &cn) {
     constexpr int N = TR::NCH;
     constexpr bool EX = TR::EXACT;
-    extern __shared__ float s_maj[];
+    bool have = false, pending = false;
+    int slot = 0;
+    ln.state = ST_DEAD;
+    while (true) {
+        // ---- refill idle lanes from Q_TRACK --------------------------------------------------------
+        unsigned idle = __ballot_sync(0xffffffffu, !have);
+        if (__popc(idle) >= rp.refill_lanes || idle == 0xffffffffu) {
+            int got = -1;
+            int n = pool_pop(pv, Q_TRACK, idle, lane, &got);
+            if (!have && __popc(idle & ((1u << lane) - 1)) < n) {
+                slot = got;
+                SlotIO<TR>::load(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
+                have = true;
+            }
+            int active = 32 - __popc(idle) + n;
+            if (active == 0) return;
+            if (n == 0) {
+                // nothing to refill with: give the remaining paths back if event work is waiting
+                int ev = 0;
+                if (lane == 0) {
+                    int a = *(volatile int *)&pv.q[Q_SCATTER].count, b = *(volatile int *)&pv.q[Q_SHADOW_END].count;
+                    int c = *(volatile int *)&pv.q[Q_DEAD].count;
+                    ev = a > b ? a : b;
+                    ev = c > ev ? c : ev;
+                }
+                ev = __shfl_sync(0xffffffffu, ev, 0);
+                if ((ev >= 32 && active <= rp.yield_lanes_full) || (ev > 0 && active <= rp.yield_lanes)) {
+                    requeue<TR>(pv, lane, have, slot, ln, lc, pending);
+                    return;
+                }
+            }
+        }
+
+        // ---- A. DDA steps to the next majorant segment with sigma_maj[0] != 0 ----------------------
+        for (int k = 0; k < rp.walk_steps; ++k) {
+            if (!__any_sync(0xffffffffu, have && ln.state == ST_WALK)) break;
+            if (have && ln.state == ST_WALK) {
+                float a, b;
+                int vox;
+                if (!ln.dda.next(mv, &a, &b, &vox)) {
+                    // iterator exhausted: SampleT_maj returns T_maj.  An unscattered camera ray
+                    // leaves medium and boundary; no infinite lights in the scene class
+                    // (cpu/integrators.cpp:1081-1106) -> path done
+                    ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
+                } else {
+                    cn.seg++;
+                    Spec<N> sm = lc.sigma_t * maj[vox];
+                    if (sm[0] == 0) {
+                        float dt = b - a;
+                        if (isinf(dt)) dt = kFltMax;
+                        ln.T_maj = ln.T_maj * exp_neg<EX>(dt, sm);
+                    } else {
+                        ln.sigma_maj = sm;
+                        ln.cur_tMin = a;
+                        ln.seg_tMax = b;
+                        ln.state = ST_COLLIDE;
+                    }
+                }
+            }
+        }
+
+        // ---- B. one tentative collision along the current segment ------------------------------------
+        if (have && ln.state == ST_COLLIDE) {
+            float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
+            ln.u = ln.trng.uniform();
+            if (t < ln.seg_tMax) {
+                Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
+                PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
+                Spec<N> sigma_maj = ln.sigma_maj;
+                bool cont;
+                if (ln.shadow) {
+                    // ratio tracking + Russian roulette, cpu/integrators.cpp:1356-1378
+                    cn.sh++;
+                    Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                    float pdf = T_maj[0] * sigma_maj[0];
+                    ln.T_ray = ln.T_ray * (T_maj * sigma_n / pdf);
+                    ln.s_rl = ln.s_rl * (T_maj * sigma_maj / pdf);
+                    ln.s_ru = ln.s_ru * (T_maj * sigma_n / pdf);
+                    Spec<N> Tr = ln.T_ray / average(ln.s_rl + ln.s_ru);
+                    if (max_component(Tr) < 0.05f) {
+                        float q = 0.75f;
+                        if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
+                        else ln.T_ray = ln.T_ray / (1 - q);
+                    }
+                    cont = nonzero(ln.T_ray);
+                    if (!cont) {
+                        ln.T_maj = sconst<N>(1.f);  // SampleT_maj returns 1 when the callback stops
+                        ln.state = ST_EV_SHADOW_END;
+                    }
+                } else {
+                    // VolPathIntegrator::Li callback, cpu/integrators.cpp:990-1078
+                    cont = false;
+                    if (!nonzero(ln.beta)) {
+                        ln.state = ST_EV_PATH_END;
+                    } else {
+                        cn.cam++;
+                        if (TR::GENERAL && ln.depth < rp.max_depth && nonzero(mp.Le)) {
+                            float pdf = sigma_maj[0] * T_maj[0];
+                            Spec<N> betap = ln.beta * T_maj / pdf;
+                            Spec<N> r_e = ln.r_u * sigma_maj * T_maj / pdf;
+                            if (nonzero(r_e)) {
+                                float avg = average(r_e);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    ln.L[i] += ((betap[i % N] * mp.sigma_a[i % N]) * mp.Le[i]) / avg;
+                            }
+                        }
+                        float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                        float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                        float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
+                        float um = ln.trng.uniform();
+                        int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
+                        if (mode == 0) {
+                            ln.state = ST_EV_PATH_END;
+                        } else if (mode == 1) {
+                            if (ln.depth++ >= rp.max_depth) {
+                                ln.state = ST_EV_PATH_END;
+                            } else {
+                                float pdf = T_maj[0] * mp.sigma_s[0];
+                                ln.beta = ln.beta * (T_maj * mp.sigma_s / pdf);
+                                ln.r_u = ln.r_u * (T_maj * mp.sigma_s / pdf);
+                                if (nonzero(ln.beta) && nonzero(ln.r_u)) {
+                                    ln.cur_tMin = t;  // scatter position parameter for E1
+                                    ln.state = ST_EV_SCATTER;
+                                } else
+                                    ln.state = ST_EV_PATH_END;
+                            }
+                        } else {
+                            Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                            float pdf = T_maj[0] * sigma_n[0];
+                            ln.beta = ln.beta * (T_maj * sigma_n / pdf);
+                            if (pdf == 0) ln.beta = sconst<N>(0.f);
+                            ln.r_u = ln.r_u * (T_maj * sigma_n / pdf);
+                            ln.r_l = ln.r_l * (T_maj * sigma_maj / pdf);
+                            cont = nonzero(ln.beta) && nonzero(ln.r_u);
+                            if (!cont) ln.state = ST_EV_PATH_END;
+                        }
+                    }
+                }
+                if (cont) {
+                    ln.T_maj = sconst<N>(1.f);
+                    ln.cur_tMin = t;
+                }
+            } else {
+                float dt = ln.seg_tMax - ln.cur_tMin;
+                if (isinf(dt)) dt = kFltMax;
+                ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
+                ln.state = ST_WALK;
+            }
+        }
+
+        // ---- park the paths that reached an event ----------------------------------------------------
+        bool fin = have && ln.state >= ST_EV_SCATTER;
+        if (__any_sync(0xffffffffu, fin)) {
+            requeue<TR>(pv, lane, fin, slot, ln, lc, pending);
+            if (fin) {
+                have = false;
+                ln.state = ST_DEAD;
+            }
+        }
+    }
+}
+
+template <typename TR>
+__global__ void __launch_bounds__(KernelCfg<TR>::kThreads, KernelCfg<TR>::kMinBlocks)
+k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *film, float *samples_out) {
+    constexpr int N = TR::NCH;
+    using IO = SlotIO<TR>;
+    extern __shared__ uint4 smem_q[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(smem_q);
     const float *maj = mv.maj;
+    const unsigned maj_bytes = rp.maj_in_smem ? unsigned(mv.mres[0] * mv.mres[1] * mv.mres[2]) * 4u : 0u;
+    const PoolLayout lay = pool_layout(maj_bytes, (unsigned)rp.pool, IO::kSlotQuads);
+    PoolView pv;
+    pv.slots = reinterpret_cast<uint4 *>(smem + lay.off_slots);
+    pv.seq = reinterpret_cast<volatile unsigned *>(smem + lay.off_seq);
+    pv.data = reinterpret_cast<volatile unsigned short *>(smem + lay.off_data);
+    pv.q = reinterpret_cast<PoolQueue *>(smem + lay.off_q);
+    pv.live = reinterpret_cast<volatile int *>(smem + lay.off_live);
+    pv.cap = lay.cap;
+    pv.cap_mask = lay.cap - 1;
     {
-        int nm = mv.mres[0] * mv.mres[1] * mv.mres[2];
-        if (nm * 4 <= 48 * 1024) {
-            for (int i = threadIdx.x; i < nm; i += blockDim.x) s_maj[i] = mv.maj[i];
-            __syncthreads();
+        if (rp.maj_in_smem) {
+            float *s_maj = reinterpret_cast<float *>(smem);
+            for (unsigned i = threadIdx.x; i < maj_bytes / 4; i += blockDim.x) s_maj[i] = mv.maj[i];
             maj = s_maj;
         }
+        // all slots start dead (state word 0 = ST_DEAD, nothing pending) and queued in Q_DEAD
+        for (unsigned i = threadIdx.x; i < (unsigned)rp.pool * IO::kSlotQuads; i += blockDim.x)
+            pv.slots[i] = make_uint4(0, 0, 0, 0);
+        for (unsigned i = threadIdx.x; i < kNumQueues * lay.cap; i += blockDim.x) {
+            unsigned qi = i / lay.cap, c = i % lay.cap;
+            bool filled = qi == Q_DEAD && c < (unsigned)rp.pool;
+            pv.seq[i] = filled ? c + 1 : c;
+            pv.data[i] = (unsigned short)c;
+        }
+        if (threadIdx.x < kNumQueues) {
+            pv.q[threadIdx.x].head = 0;
+            pv.q[threadIdx.x].tail = threadIdx.x == Q_DEAD ? (unsigned)rp.pool : 0u;
+            pv.q[threadIdx.x].count = threadIdx.x == Q_DEAD ? rp.pool : 0;
+        }
+        if (threadIdx.x == 0) *pv.live = rp.pool;
+        __syncthreads();
     }
     const unsigned lane = threadIdx.x & 31;
     PathLane<TR> ln;
-    ln.state = ST_DEAD;
-    ln.n_cam = ln.n_sh = ln.n_seg = ln.n_sc = 0;
-    ln.shadow = false;
-    unsigned n_rays = 0;
     LambdaCtx<N> lc;
-    bool pending = false;  // pending: a finished sample waits for its film write
+    LaneCounters cn = {0, 0, 0, 0, 0};
 
     while (true) {
-        // ---- scheduler: count the lanes waiting for each op with one warp reduction, run the op
-        //      with the best score = lanes * weight (weights ~ 1 / op cost: a cheap op may run for few
-        //      lanes, an expensive one waits until enough lanes want it) ------------------------
-        int best;
-        {
-            // 5-bit fields hold counts up to 31; a full warp in one op overflows into the next field,
-            // which the all-equal test below catches first
-            int s0 = __shfl_sync(0xffffffffu, ln.state, 0);
-            if (__all_sync(0xffffffffu, ln.state == s0)) {
-                if (ln.state == ST_RETIRED) break;
-                best = ln.state;
-            } else {
-                unsigned packed = ln.state < kNumOps ? (1u << (5 * ln.state)) : 0u;
-                packed = __reduce_add_sync(0xffffffffu, packed);
-                int bs = -1;
-                best = 0;
-#pragma unroll
-                for (int op = 0; op < kNumOps; ++op) {
-                    int sc = int((packed >> (5 * op)) & 31u) * rp.op_weight[op];
-                    if (sc > bs) { bs = sc; best = op; }
-                }
-            }
+        // ---- warp-level dispatch on the queue fill levels ---------------------------------------------
+        int c_dead = 0, c_sc = 0, c_se = 0, c_tr = 0, live = 0;
+        if (lane == 0) {
+            c_dead = *(volatile int *)&pv.q[Q_DEAD].count;
+            c_sc = *(volatile int *)&pv.q[Q_SCATTER].count;
+            c_se = *(volatile int *)&pv.q[Q_SHADOW_END].count;
+            c_tr = *(volatile int *)&pv.q[Q_TRACK].count;
+            live = *pv.live;
         }
-
-        if (best == ST_DEAD) {
-            // ---- R. regenerate: flush finished samples, fetch work with one aggregated atomic ------
-            bool dead = ln.state == ST_DEAD;
-            unsigned md = __ballot_sync(0xffffffffu, dead);
-            if (dead && pending) {
-                write_sample(rp, ln, film, samples_out);
-                pending = false;
-            }
-            unsigned long long base = 0;
-            int leader = __ffs(md) - 1;
-            if ((int)lane == leader) base = atomicAdd(&counters[CNT_WORK], (unsigned long long)__popc(md));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (dead) {
-                long long idx = (long long)base + __popc(md & ((1u << lane) - 1));
-                if (idx < rp.local_items) {
-                    long long chunk = idx >> 5;
-                    long long item = ((chunk * rp.world + rp.rank) << 5) + (idx & 31);
-                    if (start_path(mv, rp, ln, item, lc)) n_rays++;
-                } else
-                    ln.state = ST_RETIRED;
-            }
-        } else if (best == ST_SETUP) {
-            // ---- S. setup of the next tracking ray (camera segment or shadow ray) ---------------
-            if (ln.state == ST_SETUP) {
-                V3 o = ln.fe.o, d = ln.fe.d;
-                float t0, t1;
-                bool hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
-                float tMax;
-                if (ln.shadow) {
-                    // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
-                    ln.trng.set_sequence(hash_v3(o), hash_v3(d));
-                    tMax = 1 - kShadowEps;
-                    if (hit && t1 < tMax) tMax = t1;
-                    ln.u = ln.trng.uniform();
-                    hit = true;
-                } else {
-                    // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
-                    ln.wo = -d;
-                    tMax = t1;
-                    if (hit) {
-                        uint64_t hash0 = hash_float(ln.srng.uniform());
-                        uint64_t hash1 = hash_float(ln.srng.uniform());
-                        ln.trng.set_sequence(hash0, hash1);
-                        ln.u = ln.srng.uniform();
-                    }
-                }
-                if (!hit) {
-                    ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
-                } else {
-                    // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
-                    float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
-                    tMax *= len;
-                    d = d / len;
-                    MRay mr = ray_to_medium(mv, o, d, tMax);
-                    if (mr.hit) ln.dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
-                    ln.fe.bind(mv, o, d);
-                    ln.T_maj = sconst<N>(1.f);
-                    ln.state = ST_WALK;
-                }
-            }
-        } else if (best == ST_WALK) {
-            // ---- A. DDA steps towards the next majorant segment with sigma_maj[0] != 0 (at most
-            //      walk_steps per trip, so colliding lanes are not held up by long empty stretches) ---
-            for (int k = 0; k < rp.walk_steps; ++k) {
-                if (ln.state == ST_WALK) {
-                    float a, b;
-                    int vox;
-                    if (!ln.dda.next(mv, &a, &b, &vox)) {
-                        // iterator exhausted: SampleT_maj returns T_maj.  An unscattered camera ray
-                        // leaves medium and boundary; no infinite lights in the scene class
-                        // (cpu/integrators.cpp:1081-1106) -> path done
-                        ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
-                    } else {
-                        ln.n_seg++;
-                        Spec<N> sm = lc.sigma_t * maj[vox];
-                        if (sm[0] == 0) {
-                            float dt = b - a;
-                            if (isinf(dt)) dt = kFltMax;
-                            ln.T_maj = ln.T_maj * exp_neg<EX>(dt, sm);
-                        } else {
-                            ln.sigma_maj = sm;
-                            ln.cur_tMin = a;
-                            ln.seg_tMax = b;
-                            ln.state = ST_COLLIDE;
-                        }
-                    }
-                }
-                if (!__any_sync(0xffffffffu, ln.state == ST_WALK)) break;
-            }
-        } else if (best == ST_COLLIDE) {
-            // ---- B. tentative collisions along the current segment; repeats while enough lanes
-            //      stay in the segment loop ---------------------------------------------------------
-            do {
-                if (ln.state == ST_COLLIDE) {
-                    float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
-                    ln.u = ln.trng.uniform();
-                    if (t < ln.seg_tMax) {
-                        Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
-                        PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
-                        Spec<N> sigma_maj = ln.sigma_maj;
-                        bool cont;
-                        if (ln.shadow) {
-                            // ratio tracking + Russian roulette, cpu/integrators.cpp:1356-1378
-                            ln.n_sh++;
-                            Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                            float pdf = T_maj[0] * sigma_maj[0];
-                            ln.T_ray = ln.T_ray * (T_maj * sigma_n / pdf);
-                            ln.s_rl = ln.s_rl * (T_maj * sigma_maj / pdf);
-                            ln.s_ru = ln.s_ru * (T_maj * sigma_n / pdf);
-                            Spec<N> Tr = ln.T_ray / average(ln.s_rl + ln.s_ru);
-                            if (max_component(Tr) < 0.05f) {
-                                float q = 0.75f;
-                                if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
-                                else ln.T_ray = ln.T_ray / (1 - q);
-                            }
-                            cont = nonzero(ln.T_ray);
-                            if (!cont) {
-                                ln.T_maj = sconst<N>(1.f);  // SampleT_maj returns 1 when the callback stops
-                                ln.state = ST_EV_SHADOW_END;
-                            }
-                        } else {
-                            // VolPathIntegrator::Li callback, cpu/integrators.cpp:990-1078
-                            cont = false;
-                            if (!nonzero(ln.beta)) {
-                                ln.state = ST_EV_PATH_END;
-                            } else {
-                                ln.n_cam++;
-                                if (TR::GENERAL && ln.depth < rp.max_depth && nonzero(mp.Le)) {
-                                    float pdf = sigma_maj[0] * T_maj[0];
-                                    Spec<N> betap = ln.beta * T_maj / pdf;
-                                    Spec<N> r_e = ln.r_u * sigma_maj * T_maj / pdf;
-                                    if (nonzero(r_e)) {
-                                        float avg = average(r_e);
-#pragma unroll
-                                        for (int i = 0; i < 4; ++i)
-                                            ln.L[i] += ((betap[i % N] * mp.sigma_a[i % N]) * mp.Le[i]) / avg;
-                                    }
-                                }
-                                float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
-                                float pScatter = mp.sigma_s[0] / sigma_maj[0];
-                                float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
-                                float um = ln.trng.uniform();
-                                int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
-                                if (mode == 0) {
-                                    ln.state = ST_EV_PATH_END;
-                                } else if (mode == 1) {
-                                    if (ln.depth++ >= rp.max_depth) {
-                                        ln.state = ST_EV_PATH_END;
-                                    } else {
-                                        float pdf = T_maj[0] * mp.sigma_s[0];
-                                        ln.beta = ln.beta * (T_maj * mp.sigma_s / pdf);
-                                        ln.r_u = ln.r_u * (T_maj * mp.sigma_s / pdf);
-                                        if (nonzero(ln.beta) && nonzero(ln.r_u)) {
-                                            ln.cur_tMin = t;  // scatter position parameter for E1
-                                            ln.state = ST_EV_SCATTER;
-                                        } else
-                                            ln.state = ST_EV_PATH_END;
-                                    }
-                                } else {
-                                    Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                                    float pdf = T_maj[0] * sigma_n[0];
-                                    ln.beta = ln.beta * (T_maj * sigma_n / pdf);
-                                    if (pdf == 0) ln.beta = sconst<N>(0.f);
-                                    ln.r_u = ln.r_u * (T_maj * sigma_n / pdf);
-                                    ln.r_l = ln.r_l * (T_maj * sigma_maj / pdf);
-                                    cont = nonzero(ln.beta) && nonzero(ln.r_u);
-                                    if (!cont) ln.state = ST_EV_PATH_END;
-                                }
-                            }
-                        }
-                        if (cont) {
-                            ln.T_maj = sconst<N>(1.f);
-                            ln.cur_tMin = t;
-                        }
-                    } else {
-                        float dt = ln.seg_tMax - ln.cur_tMin;
-                        if (isinf(dt)) dt = kFltMax;
-                        ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
-                        ln.state = ST_WALK;
-                    }
-                }
-            } while (__popc(__ballot_sync(0xffffffffu, ln.state == ST_COLLIDE)) >= rp.collide_repeat);
-        } else if (best == ST_EV_SCATTER) {
-            // ---- E1. real scattering: SampleLd prologue (cpu/integrators.cpp:1300-1338) -> shadow ray
-            if (ln.state == ST_EV_SCATTER) {
-                ln.n_sc++;
-                V3 p = ln.fe.point(ln.cur_tMin);
-                ln.srng.uniform();  // light choice (single light, p = 1)
-                ln.srng.uniform();  // uLight
-                ln.srng.uniform();
-                V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
-                float two_r = 2 * rp.scene_radius;
-                V3 pLight = v3(p.x + wi.x * two_r, p.y + wi.y * two_r, p.z + wi.z * two_r);
-                bool lit = false;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
-                float ph = henyey_greenstein(dot(ln.wo, wi), mv.g);
-                V3 rd = pLight - p;
-                ln.fe.o = p;  // scatter point: origin of the shadow ray and of the next camera segment
-                if (lit && ph != 0 && !(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
-                    ln.f_hat = ph;
-                    ln.T_ray = sconst<N>(1.f);
-                    ln.s_rl = sconst<N>(1.f);
-                    ln.s_ru = sconst<N>(1.f);
-                    ln.fe.d = rd;
-                    ln.shadow = true;
-                    ln.state = ST_SETUP;
-                } else {
-                    ln.T_ray = sconst<N>(0.f);  // Ld = 0: straight to phase sampling
-                    ln.T_maj = sconst<N>(1.f);
-                    ln.state = ST_EV_SHADOW_END;
-                }
-            }
-        } else {
-            // ---- E2. end of the shadow ray: SampleLd epilogue (cpu/integrators.cpp:1382-1398), then
-            //      phase sampling and the next camera segment (cpu/integrators.cpp:1041-1060) --------
-            if (ln.state == ST_EV_SHADOW_END) {
-                Spec<N> T_ray = ln.T_ray * (ln.T_maj / ln.T_maj[0]);
-                if (nonzero(T_ray)) {
-                    Spec<N> r_l = ln.s_rl * (ln.T_maj / ln.T_maj[0]);
-                    r_l = r_l * (ln.r_u * 1.f);  // r_l *= r_p * p_l ; p_l = 1 (single delta light)
-                    float avg = average(r_l);
-                    Spec<N> bf = ln.beta * ln.f_hat;
-                    bf = bf * T_ray;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float Ll = sample_dense1(rp.light_spec, ln.lambda[i]);
-                        ln.L[i] += (bf[i % N] * Ll) / avg;
-                    }
-                }
-                float ua = ln.srng.uniform(), ub = ln.srng.uniform();
-                float pdf;
-                V3 wi = sample_hg(ln.wo, mv.g, ua, ub, &pdf);
-                if (pdf == 0) {
-                    ln.state = ST_EV_PATH_END;
-                } else {
-                    ln.beta = ln.beta * (pdf / pdf);
-                    ln.r_l = ln.r_u / pdf;
-                    ln.fe.d = wi;  // fe.o still holds the scatter point
-                    ln.shadow = false;
-                    ln.state = ST_SETUP;
-                }
-            }
+        int choice;  // queue to serve, -1: sleep, -2: done
+        if (lane == 0) {
+            if (live <= 0) choice = -2;
+            else if (c_sc >= 32) choice = Q_SCATTER;
+            else if (c_se >= 32) choice = Q_SHADOW_END;
+            else if (c_dead >= 32) choice = Q_DEAD;
+            else if (c_tr >= rp.track_min) choice = Q_TRACK;
+            else if (c_sc > 0 || c_se > 0 || c_dead > 0)
+                choice = (c_sc >= c_se && c_sc >= c_dead) ? Q_SCATTER : (c_se >= c_dead ? Q_SHADOW_END : Q_DEAD);
+            else if (c_tr > 0) choice = Q_TRACK;
+            else choice = -1;
         }
-        if (ln.state == ST_EV_PATH_END) {
-            // absorbed / escaped / max depth / zero throughput: the film write waits for R
-            ln.state = ST_DEAD;
-            pending = true;
+        choice = __shfl_sync(0xffffffffu, choice, 0);
+        if (choice == -2) break;
+        if (choice == -1) {
+            __nanosleep(200);
+            continue;
         }
+        if (choice == Q_TRACK) track_mode<TR>(mv, rp, pv, maj, lane, ln, lc, cn);
+        else event_batch<TR>(mv, rp, pv, choice, lane, ln, lc, cn, counters, film, samples_out);
     }
 
     // ---- stats: warp reduce, one atomic per counter per warp ------------------------------------------
-    unsigned vals[5] = {n_rays, ln.n_cam, ln.n_sh, ln.n_seg, ln.n_sc};
+    unsigned vals[5] = {cn.rays, cn.cam, cn.sh, cn.seg, cn.sc};
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
         unsigned long long v = vals[k];

@@ -1,17 +1,8 @@
-// avr_volpath.cuh — kernel 1b: persistent-thread wavefront volumetric path tracer.
+// avr_volpath.cuh — kernel 1b: persistent volumetric path tracer over a CTA-resident path pool.
 //
 // Replaces (for the scene class of include/avr.h) ImageTileIntegrator::Render + EvaluatePixelSample
 // (cpu/integrators.cpp:72-298), VolPathIntegrator::Li volume branch (:962-1106) and SampleLd
-// (:1282-1399), with SampleT_maj (media.h:741-806) unrolled into a per-lane state machine:
-//
-//   * one CTA-resident thread = one path in flight; finished lanes pull the next (pixel, sample)
-//     from a global counter with one warp-aggregated atomic (ballot + popc), so divergent path
-//     lengths never idle a lane for longer than one step;
-//   * camera-segment delta tracking and NEE shadow-ray ratio tracking are the SAME state (TRACK)
-//     with a mode bit, so both kinds of ray execute the exponential step + density fetch
-//     convergently and only the short event epilogue diverges;
-//   * every loop trip performs, per lane, "advance the DDA to the next non-empty majorant segment"
-//     and then exactly one tentative collision (one log, one exp, one 32-byte density fetch).
+// (:1282-1399), with SampleT_maj (media.h:741-806) unrolled into per-path ops; see avr_volpath.cu.
 #pragma once
 #include "avr_tmaj.cuh"
 
@@ -37,9 +28,14 @@ struct RenderParams {
     long long local_items;    // work items owned by this rank (multiple of 32)
     long long total_items;    // padded global item count
     int dump_samples;         // 1: write L/lambda/pdf per sample instead of the film
-    int op_weight[6];         // scheduler weights of the ops R, S, A, B, E1, E2 (avr_volpath.cu)
-    int walk_steps;           // DDA steps per A trip
-    int collide_repeat;       // B repeats while at least this many lanes stay in a segment
+    // CTA path pool and its scheduling knobs (avr_volpath.cu); they order the work, never change a result
+    int pool;                 // paths resident per CTA (shared-memory slots)
+    int maj_in_smem;          // 1: the majorant grid is staged in shared memory
+    int walk_steps;           // DDA steps per tracking trip
+    int refill_lanes;         // idle lanes of a tracking warp that trigger a refill from Q_TRACK
+    int track_min;            // Q_TRACK fill level at which a warp prefers tracking over partial event batches
+    int yield_lanes;          // a dry tracking warp with <= this many paths gives them back if any event waits
+    int yield_lanes_full;     // ... or with <= this many paths if a full event batch waits
 };
 
 // stats slots in the counters array
@@ -100,8 +96,6 @@ struct PathLane {
     Spec<N> T_ray, s_rl, s_ru;
     float f_hat;
     V3 wo;
-    // stats
-    unsigned n_cam, n_sh, n_seg, n_sc;
 };
 
 }  // namespace avr

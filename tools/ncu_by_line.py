@@ -51,3 +51,23 @@ for key_i, title in ((1, 'outermost (kernel file) line'), (0, 'innermost line'))
     print(f'## by {title}: total warp-inst {T}, samples {S}')
     for k, v in ex.most_common(top_n):
         print(f'{k:34s} inst {v:11d} {100*v/T:5.1f}%  lanes {th[k]/max(v,1):5.1f}  samples {100*sm[k]/S:5.1f}%')
+
+# optional: phase ranges "name:lo-hi,name:lo-hi" on the kernel file's lines (argv[5])
+if len(sys.argv) > 5:
+    ex = collections.Counter(); th = collections.Counter(); sm = collections.Counter()
+    ranges = []
+    for part in sys.argv[5].split(','):
+        name, r = part.split(':')
+        lo, hi = r.split('-')
+        ranges.append((name, int(lo), int(hi)))
+    for (s, e, t, p), loc in zip(inst[:n], locs[:n]):
+        f, ln_ = loc[1].rsplit(':', 1)
+        name = 'other'
+        for nm, lo, hi in ranges:
+            if lo <= int(ln_) <= hi:
+                name = nm
+        ex[name] += e; th[name] += t; sm[name] += p
+    T = sum(ex.values()); TT = sum(th.values()); S = sum(sm.values())
+    print('## by phase')
+    for k, v in ex.most_common():
+        print(f'{k:10s} warp-inst {v:11d} {100*v/T:5.1f}%  thread-inst {th[k]:12d} {100*th[k]/TT:5.1f}%  lanes {th[k]/max(v,1):5.1f}  samples {100*sm[k]/S:5.1f}%')

@@ -200,6 +200,14 @@ avr_status finish_common(avr_medium *m, const float p0[3], const float p1[3], co
         v.bmax[i] = p1[i];
         m->mres[i] = v.mres[i] = mres_in[i] > 0 ? mres_in[i] : 16;
     }
+    if (v.mres[0] > 1023 || v.mres[1] > 1023 || v.mres[2] > 1023)
+        return set_err(m->ctx, AVR_ERR_UNSUPPORTED, "majorant grid resolution > 1023 per axis");
+    for (int i = 0; i < 3; ++i) {
+        v.cell[i] = (v.bmax[i] - v.bmin[i]) / float(v.mres[i]);
+        v.inv_cell[i] = v.cell[i] > 0 ? 1.f / v.cell[i] : 0.f;
+        v.nz_lo[i] = 0;
+        v.nz_hi[i] = v.mres[i] - 1;
+    }
     if (!affine_rows(rfm, v.m) || !affine_rows(mfr, v.minv))
         return set_err(m->ctx, AVR_ERR_UNSUPPORTED, "medium transform must be affine (last row 0 0 0 1)");
     fold_grid_from_render(v);
@@ -207,6 +215,33 @@ avr_status finish_common(avr_medium *m, const float p0[3], const float p1[3], co
     AVR_CUDA(m->ctx, cudaMalloc(&m->d_maj, nm * sizeof(float)));
     m->allocs.push_back(m->d_maj);
     v.maj = m->d_maj;
+    return AVR_OK;
+}
+
+// Bounding box of the non-zero majorant cells (the renderer's DDA stops at its faces, avr_medium.cuh).
+avr_status finish_majorants(avr_medium *m) {
+    MediumView &v = m->view;
+    size_t nm = size_t(v.mres[0]) * v.mres[1] * v.mres[2];
+    std::vector<float> h(nm);
+    AVR_CUDA(m->ctx, cudaMemcpyAsync(h.data(), m->d_maj, nm * sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
+    AVR_CUDA(m->ctx, cudaStreamSynchronize(m->ctx->stream));
+    int lo[3] = {v.mres[0], v.mres[1], v.mres[2]}, hi[3] = {-1, -1, -1};
+    for (int z = 0; z < v.mres[2]; ++z)
+        for (int y = 0; y < v.mres[1]; ++y)
+            for (int x = 0; x < v.mres[0]; ++x) {
+                float f = h[(size_t(z) * v.mres[1] + y) * v.mres[0] + x];
+                if (f == 0.f) continue;  // NaN / negative majorants stay inside the box
+                int c[3] = {x, y, z};
+                for (int i = 0; i < 3; ++i) {
+                    lo[i] = c[i] < lo[i] ? c[i] : lo[i];
+                    hi[i] = c[i] > hi[i] ? c[i] : hi[i];
+                }
+            }
+    for (int i = 0; i < 3; ++i) {
+        if (hi[i] < lo[i]) { lo[i] = 0; hi[i] = -1; }  // all-zero grid: every walk ends at once
+        v.nz_lo[i] = lo[i];
+        v.nz_hi[i] = hi[i];
+    }
     return AVR_OK;
 }
 
@@ -300,6 +335,7 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     }
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "medium build"); }
+    TRY(finish_majorants(m));
     *out = m;
     return AVR_OK;
 }
@@ -338,6 +374,7 @@ extern "C" avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "rgb medium build"); }
+    TRY(finish_majorants(m));
     *out = m;
     return AVR_OK;
 #undef TRY

@@ -292,6 +292,12 @@ AVR_DEV float fdiv(float a, float b) {
     if (EXACT) return a / b;
     return __fdividef(a, b);
 }
+// EXACT: a / s per channel (IEEE).  FAST: one approximate reciprocal, then multiplies.
+template <bool EXACT, int N>
+AVR_DEV Spec<N> sdiv(Spec<N> a, float s) {
+    if (EXACT) return a / s;
+    return a * __fdividef(1.f, s);
+}
 AVR_DEV float lerp_exact(float x, float a, float b) { return (1 - x) * a + x * b; }  // util/math.h:210
 AVR_DEV float lerp_fast(float x, float a, float b) { return __fmaf_rn(x, b - a, a); }
 template <bool EXACT>
@@ -320,26 +326,41 @@ AVR_DEV float henyey_greenstein(float cosTheta, float g) {
     float denom = 1 + sqr(g) + 2 * g * cosTheta;
     return kInv4Pi * (1 - sqr(g)) / (denom * safe_sqrt(denom));
 }
+AVR_DEV float henyey_greenstein_fast(float cosTheta, float g) {
+    g = clampf(g, -.99f, .99f);
+    float denom = fmaxf(__fmaf_rn(2 * g, cosTheta, 1 + g * g), 1e-12f);
+    float r = rsqrtf(denom);
+    return kInv4Pi * (1 - g * g) * (r * r * r);
+}
+template <bool EXACT>
+AVR_DEV float hg_phase(float cosTheta, float g) {
+    return EXACT ? henyey_greenstein(cosTheta, g) : henyey_greenstein_fast(cosTheta, g);
+}
+template <bool EXACT = true>
 AVR_DEV V3 sample_hg(V3 wo, float g, float u0, float u1, float *pdf) {
     g = clampf(g, -.99f, .99f);
     float cosTheta;
     if (fabsf(g) < 1e-3f)
         cosTheta = 1 - 2 * u0;
-    else
+    else if (EXACT)
         cosTheta = -1 / (2 * g) * (1 + sqr(g) - sqr((1 - sqr(g)) / (1 + g - 2 * g * u0)));
+    else
+        cosTheta = __fdividef(-1.f, 2 * g) * (1 + g * g - sqr(__fdividef(1 - g * g, 1 + g - 2 * g * u0)));
     float sinTheta = safe_sqrt(1 - sqr(cosTheta));
     float phi = 2 * kPi * u1;
     // CoordinateSystem (vecmath.h:1007-1013), Frame::FromZ(wo).FromLocal(SphericalDirection(...))
     float sign = copysignf(1.f, wo.z);
-    float a = -1 / (sign + wo.z);
+    float a = EXACT ? -1 / (sign + wo.z) : __fdividef(-1.f, sign + wo.z);
     float b = wo.x * wo.y * a;
     V3 fx = v3(1 + sign * sqr(wo.x) * a, sign * b, -sign * wo.x);
     V3 fy = v3(b, sign + sqr(wo.y) * a, -wo.y);
     float st = clampf(sinTheta, -1.f, 1.f), ct = clampf(cosTheta, -1.f, 1.f);
-    float sp = glibc_sinf(phi), cp = glibc_cosf(phi);
+    float sp, cp;
+    if (EXACT) { sp = glibc_sinf(phi); cp = glibc_cosf(phi); }
+    else __sincosf(phi, &sp, &cp);
     V3 l = v3(st * cp, st * sp, ct);
     V3 wi = fx * l.x + fy * l.y + wo * l.z;
-    *pdf = henyey_greenstein(cosTheta, g);
+    *pdf = hg_phase<EXACT>(cosTheta, g);
     return wi;
 }
 

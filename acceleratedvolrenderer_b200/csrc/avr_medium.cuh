@@ -36,6 +36,8 @@ struct MediumView {
     int mres[3];
     // FAST path: sample coordinates straight from render space, s = gfr * p + gfr[.][3]  (s = p_grid*n - .5)
     float gfr[12];
+    float cell[3], inv_cell[3];  // majorant cell size in medium space and its reciprocal
+    int nz_lo[3], nz_hi[3];      // bounding box (inclusive voxel range) of the majorant cells != 0
 };
 
 // ---- Transform::ApplyInverse(Point3f) + Bounds3::Offset: render point -> grid [0,1]^3 ------------
@@ -286,17 +288,39 @@ AVR_DEV MRay ray_to_medium(const MediumView &mv, V3 o, V3 d, float raytMax) {
 }
 
 // ---- DDAMajorantIterator, media.h:136-214 (bit-exact contract) --------------------------------------
+// State kept per ray: the reference's tMin/tMax/nextCrossingT/deltaT, plus the voxel as a linear index
+// and, per axis, the number of steps left before the walk leaves the grid (10-bit fields of `rem`).
+// The step direction of an axis is the sign of dTs (|dTs| = deltaT).  With TRIM the walk also ends
+// when it leaves the bounding box of the non-zero majorant cells (mv.nz_lo/nz_hi): every voxel beyond
+// has sigma_maj = 0, whose segments multiply T_maj by FastExp(-0) = 1 exactly, so results are
+// unchanged and only the trailing empty segments are not enumerated.
 struct DDA {
     float tMin, tMax;
-    float nextCrossingT[3], deltaT[3];
-    int voxel[3];
-    int stepBits;  // bit i set: step[i] = +1 (voxelLimit = res), else -1 (voxelLimit = -1)
+    float nct[3], dTs[3];
+    int lin;
+    unsigned rem;
 
     AVR_DEV void invalidate() { tMin = __int_as_float(0x7f800000); tMax = __int_as_float(0xff800000); }
+    // finish init from per-axis voxel / direction sign; returns false if no voxel can be visited
+    template <bool TRIM>
+    AVR_DEV bool set_voxels(const MediumView &mv, const int vx[3], const bool pos[3]) {
+        lin = vx[0] + mv.mres[0] * (vx[1] + mv.mres[1] * vx[2]);
+        rem = 0;
+        bool ok = true;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            int hi = TRIM ? mv.nz_hi[a] + 1 : mv.mres[a];  // leaving towards + when voxel == hi
+            int lo = TRIM ? mv.nz_lo[a] - 1 : -1;          // leaving towards - when voxel == lo
+            int r = pos[a] ? hi - vx[a] : vx[a] - lo;
+            ok = ok && r > 0;
+            rem |= (unsigned)(r & 1023) << (10 * a);
+        }
+        return ok;
+    }
+    template <bool TRIM>
     AVR_DEV void init(const MediumView &mv, V3 o, V3 d, float tMin_, float tMax_) {
         tMin = tMin_;
         tMax = tMax_;
-        stepBits = 0;
         V3 diag = v3(mv.bmax[0] - mv.bmin[0], mv.bmax[1] - mv.bmin[1], mv.bmax[2] - mv.bmin[2]);
         // bounds.Offset(ray.o)
         V3 ro = v3(o.x - mv.bmin[0], o.y - mv.bmin[1], o.z - mv.bmin[2]);
@@ -305,51 +329,73 @@ struct DDA {
         if (mv.bmax[2] > mv.bmin[2]) ro.z /= diag.z;
         V3 rd = v3(d.x / diag.x, d.y / diag.y, d.z / diag.z);
         V3 gi = v3(ro.x + rd.x * tMin, ro.y + rd.y * tMin, ro.z + rd.z * tMin);
+        int vx[3];
+        bool pos[3];
 #pragma unroll
         for (int axis = 0; axis < 3; ++axis) {
             int r = mv.mres[axis];
             float g = comp(gi, axis), dd = comp(rd, axis);
             float gv = g * r;
-            int vx;
-            if (gv < 0) vx = 0;
-            else if (gv > float(r - 1)) vx = r - 1;
-            else vx = (int)gv;
-            voxel[axis] = vx;
-            deltaT[axis] = 1 / (fabsf(dd) * r);
+            int v;
+            if (gv < 0) v = 0;
+            else if (gv > float(r - 1)) v = r - 1;
+            else v = (int)gv;
+            vx[axis] = v;
+            float dT = 1 / (fabsf(dd) * r);
             if (dd == -0.f) dd = 0.f;
-            if (dd >= 0) {
-                float nextVoxelPos = float(vx + 1) / r;
-                nextCrossingT[axis] = tMin + (nextVoxelPos - g) / dd;
-                stepBits |= 1 << axis;
-            } else {
-                float nextVoxelPos = float(vx) / r;
-                nextCrossingT[axis] = tMin + (nextVoxelPos - g) / dd;
-            }
+            pos[axis] = dd >= 0;
+            float nextVoxelPos = float(pos[axis] ? v + 1 : v) / r;
+            nct[axis] = tMin + (nextVoxelPos - g) / dd;
+            dTs[axis] = pos[axis] ? dT : -dT;
         }
+        if (!set_voxels<TRIM>(mv, vx, pos)) invalidate();
+    }
+    // FAST variant: medium-space arithmetic with reciprocals (not bit-compatible with the reference)
+    template <bool TRIM>
+    AVR_DEV void init_fast(const MediumView &mv, V3 o, V3 inv_d, V3 d, float tMin_, float tMax_) {
+        tMin = tMin_;
+        tMax = tMax_;
+        int vx[3];
+        bool pos[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            int r = mv.mres[a];
+            float p = __fmaf_rn(comp(d, a), tMin, comp(o, a)) - mv.bmin[a];
+            int v = (int)(p * mv.inv_cell[a]);
+            v = v < 0 ? 0 : (v > r - 1 ? r - 1 : v);
+            vx[a] = v;
+            float id = comp(inv_d, a);
+            pos[a] = !(comp(d, a) < 0);
+            float edge = mv.bmin[a] + float(pos[a] ? v + 1 : v) * mv.cell[a];
+            nct[a] = (edge - comp(o, a)) * id;
+            if (comp(d, a) == 0) nct[a] = __int_as_float(0x7f800000);
+            float dT = fabsf(id) * mv.cell[a];
+            dTs[a] = pos[a] ? dT : -dT;
+        }
+        if (!set_voxels<TRIM>(mv, vx, pos)) invalidate();
     }
     // Returns false when the iterator is exhausted.  *vox = linear voxel index of the segment.
     AVR_DEV bool next(const MediumView &mv, float *segMin, float *segMax, int *vox) {
         if (tMin >= tMax) return false;
-        int bits = ((nextCrossingT[0] < nextCrossingT[1]) << 2) + ((nextCrossingT[0] < nextCrossingT[2]) << 1) +
-                   ((nextCrossingT[1] < nextCrossingT[2]));
-        // cmpToAxis = {2,1,2,1,2,2,0,0} packed 2 bits per entry
-        int stepAxis = (0x0A66 >> (2 * bits)) & 3;
-        float nct = stepAxis == 0 ? nextCrossingT[0] : (stepAxis == 1 ? nextCrossingT[1] : nextCrossingT[2]);
-        float tVoxelExit = fminf(tMax, nct);
-        *vox = voxel[0] + mv.mres[0] * (voxel[1] + mv.mres[1] * voxel[2]);
+        // stepAxis = cmpToAxis[bits], cmpToAxis = {2,1,2,1,2,2,0,0}: 0 iff c01 & c02, 1 iff !c01 & c12
+        bool c01 = nct[0] < nct[1], c02 = nct[0] < nct[2], c12 = nct[1] < nct[2];
+        bool p0 = c01 && c02, p1 = !c01 && c12;
+        float n = p0 ? nct[0] : (p1 ? nct[1] : nct[2]);
+        float ds = p0 ? dTs[0] : (p1 ? dTs[1] : dTs[2]);
+        float tVoxelExit = n < tMax ? n : tMax;  // std::min(tMax, nextCrossingT[stepAxis])
+        *vox = lin;
         *segMin = tMin;
         *segMax = tVoxelExit;
         tMin = tVoxelExit;
-        if (nct > tMax) tMin = tMax;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            if (a == stepAxis) {
-                bool pos = (stepBits >> a) & 1;
-                voxel[a] += pos ? 1 : -1;
-                if (voxel[a] == (pos ? mv.mres[a] : -1)) tMin = tMax;
-                nextCrossingT[a] += deltaT[a];
-            }
-        }
+        int stride = p0 ? 1 : (p1 ? mv.mres[0] : mv.mres[0] * mv.mres[1]);
+        lin += ds >= 0 ? stride : -stride;
+        unsigned sh = p0 ? 0u : (p1 ? 10u : 20u);
+        rem -= 1u << sh;
+        if (((rem >> sh) & 1023u) == 0) tMin = tMax;  // voxel[stepAxis] == voxelLimit[stepAxis]
+        float nn = n + fabsf(ds);
+        if (p0) nct[0] = nn;
+        else if (p1) nct[1] = nn;
+        else nct[2] = nn;
         return true;
     }
 };

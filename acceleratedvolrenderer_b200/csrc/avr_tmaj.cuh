@@ -125,7 +125,7 @@ AVR_DEV Spec<TR::NCH> sample_tmaj(const MediumView &mv, const float *maj, const 
     d = d / len;
     MRay mr = ray_to_medium(mv, o, d, tMax);
     DDA dda;
-    if (mr.hit) dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else dda.invalidate();
+    if (mr.hit) dda.init<false>(mv, mr.o, mr.d, mr.tMin, mr.tMax); else dda.invalidate();
     Fetcher<TR> fe;
     fe.bind(mv, o, d);
     Spec<N> T_maj = sconst<N>(1.f);

@@ -232,7 +232,7 @@ AVR_DEV int pool_pop(const PoolView &pv, int qi, unsigned takers, unsigned lane,
 template <typename TR>
 struct SlotIO {
     static constexpr int N = TR::NCH;
-    static constexpr int kWords = 2 + 4 + 4 + 4 + 3 * N + 1 + 12 + 12 + 3 + 2 * N + 4 + 3 * N + 1 + 3 + 2 * N;
+    static constexpr int kWords = 2 + 4 + 4 + 4 + 3 * N + 1 + 12 + 10 + 3 + 2 * N + 4 + 3 * N + 1 + 3 + 2 * N;
     static constexpr int kQuadsRaw = (kWords + 3) / 4;
     static constexpr int kSlotQuads = kQuadsRaw | 1;
 
@@ -263,13 +263,10 @@ struct SlotIO {
         f(ln.fe.so.x); f(ln.fe.so.y); f(ln.fe.so.z); f(ln.fe.sd.x); f(ln.fe.sd.y); f(ln.fe.sd.z);
         f(ln.dda.tMin); f(ln.dda.tMax);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) { f(ln.dda.nextCrossingT[i]); f(ln.dda.deltaT[i]); }
-        unsigned vx = (unsigned)(ln.dda.voxel[0] + 1), vy = (unsigned)(ln.dda.voxel[1] + 1), vz = (unsigned)(ln.dda.voxel[2] + 1);
-        f(vx); f(vy); f(vz);
-        ln.dda.voxel[0] = int(vx) - 1; ln.dda.voxel[1] = int(vy) - 1; ln.dda.voxel[2] = int(vz) - 1;
-        unsigned sb = (unsigned)ln.dda.stepBits;
-        f(sb);
-        ln.dda.stepBits = (int)sb;
+        for (int i = 0; i < 3; ++i) { f(ln.dda.nct[i]); f(ln.dda.dTs[i]); }
+        unsigned dl = (unsigned)ln.dda.lin;
+        f(dl); f(ln.dda.rem);
+        ln.dda.lin = (int)dl;
         f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
 #pragma unroll
         for (int i = 0; i < N; ++i) { f(ln.sigma_maj.v[i]); f(ln.T_maj.v[i]); }
@@ -419,7 +416,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             bool lit = false;
 #pragma unroll
             for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
-            float ph = henyey_greenstein(dot(ln.wo, wi), mv.g);
+            float ph = hg_phase<TR::EXACT>(dot(ln.wo, wi), mv.g);
             V3 rd = pLight - p;
             ln.fe.o = p;  // scatter point: origin of the shadow ray and of the next camera segment
             if (lit && ph != 0 && !(rd.x == 0 && rd.y == 0 && rd.z == 0)) {
@@ -455,7 +452,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             }
             float ua = ln.srng.uniform(), ub = ln.srng.uniform();
             float pdf;
-            V3 wi = sample_hg(ln.wo, mv.g, ua, ub, &pdf);
+            V3 wi = sample_hg<TR::EXACT>(ln.wo, mv.g, ua, ub, &pdf);
             if (pdf == 0) {
                 ln.state = ST_EV_PATH_END;
             } else {
@@ -471,36 +468,76 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
     // ---- S. setup of the pending ray (camera segment or shadow ray) ------------------------------------
     if (have && ln.state == ST_SETUP) {
         V3 o = ln.fe.o, d = ln.fe.d;
-        float t0, t1;
-        bool hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
-        float tMax;
-        if (ln.shadow) {
-            // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
-            ln.trng.set_sequence(hash_v3(o), hash_v3(d));
-            tMax = 1 - kShadowEps;
-            if (hit && t1 < tMax) tMax = t1;
-            ln.u = ln.trng.uniform();
-            hit = true;
+        float t0, t1, tMax;
+        bool hit;
+        if (TR::EXACT) {
+            hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
+            if (ln.shadow) {
+                // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
+                ln.trng.set_sequence(hash_v3(o), hash_v3(d));
+                tMax = 1 - kShadowEps;
+                if (hit && t1 < tMax) tMax = t1;
+                ln.u = ln.trng.uniform();
+                hit = true;
+            } else {
+                // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
+                ln.wo = -d;
+                tMax = t1;
+                if (hit) {
+                    uint64_t hash0 = hash_float(ln.srng.uniform());
+                    uint64_t hash1 = hash_float(ln.srng.uniform());
+                    ln.trng.set_sequence(hash0, hash1);
+                    ln.u = ln.srng.uniform();
+                }
+            }
         } else {
-            // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
-            ln.wo = -d;
-            tMax = t1;
-            if (hit) {
-                uint64_t hash0 = hash_float(ln.srng.uniform());
-                uint64_t hash1 = hash_float(ln.srng.uniform());
-                ln.trng.set_sequence(hash0, hash1);
-                ln.u = ln.srng.uniform();
+            // FAST: same estimator; the tracking stream of either ray kind is seeded from two sampler draws
+            hit = boundary_hit_fast(rp, o, d, &t0, &t1) && t1 > 0;
+            uint32_t ra = ln.srng.u32(), rb = ln.srng.u32();
+            ln.trng.set_sequence(((uint64_t)ra << 32) | rb, ((uint64_t)rb << 32) | ra);
+            ln.u = ln.trng.uniform();
+            if (ln.shadow) {
+                tMax = 1 - kShadowEps;
+                if (hit && t1 < tMax) tMax = t1;
+                hit = true;
+            } else {
+                ln.wo = -d;
+                tMax = t1;
             }
         }
         if (!hit) {
             ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
-        } else {
+        } else if (TR::EXACT) {
             // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
             float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
             tMax *= len;
             d = d / len;
             MRay mr = ray_to_medium(mv, o, d, tMax);
-            if (mr.hit) ln.dda.init(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
+            if (mr.hit) ln.dda.template init<true>(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
+            ln.fe.bind(mv, o, d);
+            ln.T_maj = sconst<N>(1.f);
+            ln.state = ST_WALK;
+        } else {
+            float l2 = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, d.z * d.z));
+            float rl = rsqrtf(l2);
+            tMax *= l2 * rl;
+            d = d * rl;
+            const float *a = mv.minv;
+            V3 mo = v3(__fmaf_rn(a[0], o.x, __fmaf_rn(a[1], o.y, __fmaf_rn(a[2], o.z, a[3]))),
+                       __fmaf_rn(a[4], o.x, __fmaf_rn(a[5], o.y, __fmaf_rn(a[6], o.z, a[7]))),
+                       __fmaf_rn(a[8], o.x, __fmaf_rn(a[9], o.y, __fmaf_rn(a[10], o.z, a[11]))));
+            V3 md = v3(__fmaf_rn(a[0], d.x, __fmaf_rn(a[1], d.y, a[2] * d.z)),
+                       __fmaf_rn(a[4], d.x, __fmaf_rn(a[5], d.y, a[6] * d.z)),
+                       __fmaf_rn(a[8], d.x, __fmaf_rn(a[9], d.y, a[10] * d.z)));
+            V3 inv = v3(__fdividef(1.f, md.x), __fdividef(1.f, md.y), __fdividef(1.f, md.z));
+            float h0 = 0.f, h1 = tMax;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                float tn = (mv.bmin[i] - comp(mo, i)) * comp(inv, i), tf = (mv.bmax[i] - comp(mo, i)) * comp(inv, i);
+                h0 = fmaxf(h0, fminf(tn, tf));
+                h1 = fminf(h1, fmaxf(tn, tf));
+            }
+            if (h0 <= h1) ln.dda.template init_fast<true>(mv, mo, inv, md, h0, h1); else ln.dda.invalidate();
             ln.fe.bind(mv, o, d);
             ln.T_maj = sconst<N>(1.f);
             ln.state = ST_WALK;
@@ -564,8 +601,11 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
                 } else {
                     cn.seg++;
-                    Spec<N> sm = lc.sigma_t * maj[vox];
-                    if (sm[0] == 0) {
+                    float mj = maj[vox];
+                    Spec<N> sm = lc.sigma_t * mj;
+                    if (mj == 0) {
+                        // sigma_maj = 0 in every channel: T_maj *= FastExp(-0) = 1 exactly, nothing to do
+                    } else if (sm[0] == 0) {
                         float dt = b - a;
                         if (isinf(dt)) dt = kFltMax;
                         ln.T_maj = ln.T_maj * exp_neg<EX>(dt, sm);
@@ -593,10 +633,10 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     cn.sh++;
                     Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
                     float pdf = T_maj[0] * sigma_maj[0];
-                    ln.T_ray = ln.T_ray * (T_maj * sigma_n / pdf);
-                    ln.s_rl = ln.s_rl * (T_maj * sigma_maj / pdf);
-                    ln.s_ru = ln.s_ru * (T_maj * sigma_n / pdf);
-                    Spec<N> Tr = ln.T_ray / average(ln.s_rl + ln.s_ru);
+                    ln.T_ray = ln.T_ray * sdiv<EX>(T_maj * sigma_n, pdf);
+                    ln.s_rl = ln.s_rl * sdiv<EX>(T_maj * sigma_maj, pdf);
+                    ln.s_ru = ln.s_ru * sdiv<EX>(T_maj * sigma_n, pdf);
+                    Spec<N> Tr = sdiv<EX>(ln.T_ray, average(ln.s_rl + ln.s_ru));
                     if (max_component(Tr) < 0.05f) {
                         float q = 0.75f;
                         if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
@@ -625,8 +665,8 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                                     ln.L[i] += ((betap[i % N] * mp.sigma_a[i % N]) * mp.Le[i]) / avg;
                             }
                         }
-                        float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
-                        float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                        float pAbsorb = fdiv<EX>(mp.sigma_a[0], sigma_maj[0]);
+                        float pScatter = fdiv<EX>(mp.sigma_s[0], sigma_maj[0]);
                         float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
                         float um = ln.trng.uniform();
                         int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
@@ -637,8 +677,8 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                                 ln.state = ST_EV_PATH_END;
                             } else {
                                 float pdf = T_maj[0] * mp.sigma_s[0];
-                                ln.beta = ln.beta * (T_maj * mp.sigma_s / pdf);
-                                ln.r_u = ln.r_u * (T_maj * mp.sigma_s / pdf);
+                                ln.beta = ln.beta * sdiv<EX>(T_maj * mp.sigma_s, pdf);
+                                ln.r_u = ln.r_u * sdiv<EX>(T_maj * mp.sigma_s, pdf);
                                 if (nonzero(ln.beta) && nonzero(ln.r_u)) {
                                     ln.cur_tMin = t;  // scatter position parameter for E1
                                     ln.state = ST_EV_SCATTER;
@@ -648,10 +688,10 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                         } else {
                             Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
                             float pdf = T_maj[0] * sigma_n[0];
-                            ln.beta = ln.beta * (T_maj * sigma_n / pdf);
+                            ln.beta = ln.beta * sdiv<EX>(T_maj * sigma_n, pdf);
                             if (pdf == 0) ln.beta = sconst<N>(0.f);
-                            ln.r_u = ln.r_u * (T_maj * sigma_n / pdf);
-                            ln.r_l = ln.r_l * (T_maj * sigma_maj / pdf);
+                            ln.r_u = ln.r_u * sdiv<EX>(T_maj * sigma_n, pdf);
+                            ln.r_l = ln.r_l * sdiv<EX>(T_maj * sigma_maj, pdf);
                             cont = nonzero(ln.beta) && nonzero(ln.r_u);
                             if (!cont) ln.state = ST_EV_PATH_END;
                         }

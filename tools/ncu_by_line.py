@@ -8,6 +8,7 @@ import sys
 
 src_csv, dis_txt, func_pat = sys.argv[1:4]
 top_n = int(sys.argv[4]) if len(sys.argv) > 4 else 40
+KERNEL_FILE = 'avr_volpath.cu'  # phase ranges refer to the innermost frame inside this file
 rows = list(csv.reader(open(src_csv)))
 hdr = rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
@@ -34,7 +35,9 @@ for l in lines[start + 1:]:
         chain.append(f'{m.group(1).split("/")[-1]}:{m.group(2)}')
         if m.group(3):
             chain.append(f'{m.group(3).split("/")[-1]}:{m.group(4)}')
-        cur_inner, cur_outer = chain[0], chain[-1]
+        cur_inner = chain[0]
+        kf = [c for c in chain if c.startswith(KERNEL_FILE + ':')]
+        cur_outer = kf[0] if kf else chain[-1]
         prev_was_loc = True
         continue
     prev_was_loc = False
@@ -43,7 +46,7 @@ for l in lines[start + 1:]:
         locs.append((cur_inner, cur_outer, m.group(2)))
 print(f'# {len(inst)} ncu rows, {len(locs)} disassembled instructions', file=sys.stderr)
 n = min(len(inst), len(locs))
-for key_i, title in ((1, 'outermost (kernel file) line'), (0, 'innermost line')):
+for key_i, title in ((1, 'kernel-file line (innermost frame inside the kernel file)'), (0, 'innermost line')):
     ex = collections.Counter(); th = collections.Counter(); sm = collections.Counter()
     for (s, e, t, p), loc in zip(inst[:n], locs[:n]):
         ex[loc[key_i]] += e; th[loc[key_i]] += t; sm[loc[key_i]] += p
@@ -71,3 +74,13 @@ if len(sys.argv) > 5:
     print('## by phase')
     for k, v in ex.most_common():
         print(f'{k:10s} warp-inst {v:11d} {100*v/T:5.1f}%  thread-inst {th[k]:12d} {100*th[k]/TT:5.1f}%  lanes {th[k]/max(v,1):5.1f}  samples {100*sm[k]/S:5.1f}%')
+    # static code size per phase (SASS instructions)
+    st = collections.Counter()
+    for loc in locs[:n]:
+        f, ln_ = loc[1].rsplit(':', 1)
+        name = 'other'
+        for nm, lo, hi in ranges:
+            if lo <= int(ln_) <= hi:
+                name = nm
+        st[name] += 1
+    print('## static SASS instructions per phase:', dict(st.most_common()))

@@ -491,10 +491,12 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                 }
             }
         } else {
-            // FAST: same estimator; the tracking stream of either ray kind is seeded from two sampler draws
+            // FAST: same estimator; the tracking stream of either ray kind is seeded from two hashed sampler draws
             hit = boundary_hit_fast(rp, o, d, &t0, &t1) && t1 > 0;
-            uint32_t ra = ln.srng.u32(), rb = ln.srng.u32();
-            ln.trng.set_sequence(((uint64_t)ra << 32) | rb, ((uint64_t)rb << 32) | ra);
+            // (raw draws as PCG32 sequence / seed give correlated streams: they must go through the hash)
+            uint64_t hash0 = hash_u32(ln.srng.u32());
+            uint64_t hash1 = hash_u32(ln.srng.u32());
+            ln.trng.set_sequence(hash0, hash1);
             ln.u = ln.trng.uniform();
             if (ln.shadow) {
                 tMax = 1 - kShadowEps;

@@ -153,61 +153,62 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
 
 enum { Q_DEAD = 0, Q_SCATTER = 1, Q_SHADOW_END = 2, Q_TRACK = 3, kNumQueues = 4 };
 
-// bounded MPMC ring (Vyukov cell sequence numbers) + a committed-entries counter for batched pops
+// Bounded MPMC ring of slot ids.  A cell word is (round << 16) | slot while it holds an entry and
+// (round << 16) | 0xffff while it is free for the producer of that round (Vyukov's per-cell sequence,
+// folded into one word so that publishing an entry is a single store).  tail - head counts entries
+// that are at least reserved; a consumer that claims a reserved cell spins until its producer's store.
 struct PoolQueue {
-    unsigned head, tail;   // monotonic positions
-    int count;             // entries committed and not yet claimed
-    unsigned pad;
+    unsigned head, tail;  // monotonic positions
 };
 
 struct PoolView {
     uint4 *slots;              // pool * kSlotQuads
-    volatile unsigned *seq;    // kNumQueues * cap
-    volatile unsigned short *data;
+    volatile unsigned *cells;  // kNumQueues * cap
     PoolQueue *q;              // kNumQueues
     volatile int *live;        // slots not yet retired
     unsigned cap_mask;         // cap - 1 (cap = power of two >= pool)
-    unsigned cap;
+    unsigned cap_log2;
 };
 
+AVR_DEV int pool_fill(const PoolView &pv, int qi) {
+    unsigned h = *(volatile unsigned *)&pv.q[qi].head, t = *(volatile unsigned *)&pv.q[qi].tail;
+    return (int)(t - h);
+}
+
 // Push the slot ids of the lanes in `mask` (a subset of the converged lanes calling this) to queue qi.
-// The callers' slot stores must precede the call; the fence below publishes them.
+// The callers' slot stores and a __threadfence_block() must precede the call.
 AVR_DEV void pool_push(const PoolView &pv, int qi, unsigned mask, unsigned lane, int slot) {
     if (mask == 0) return;
-    int n = __popc(mask);
     int leader = __ffs(mask) - 1;
     unsigned pos0 = 0;
-    __threadfence_block();
-    if ((int)lane == leader) pos0 = atomicAdd(&pv.q[qi].tail, (unsigned)n);
+    if ((int)lane == leader) pos0 = atomicAdd(&pv.q[qi].tail, (unsigned)__popc(mask));
     pos0 = __shfl_sync(0xffffffffu, pos0, leader);
     if (mask >> lane & 1u) {
         unsigned pos = pos0 + __popc(mask & ((1u << lane) - 1));
-        unsigned cell = qi * pv.cap + (pos & pv.cap_mask);
-        while (pv.seq[cell] != pos) {}
-        pv.data[cell] = (unsigned short)slot;
-        __threadfence_block();
-        pv.seq[cell] = pos + 1;
+        unsigned cell = ((unsigned)qi << pv.cap_log2) + (pos & pv.cap_mask);
+        unsigned round = (pos >> pv.cap_log2) << 16;
+        while (pv.cells[cell] != (round | 0xffffu)) {}
+        pv.cells[cell] = round | (unsigned)slot;
     }
-    __syncwarp();
-    if ((int)lane == leader) atomicAdd(&pv.q[qi].count, n);
 }
 
-// Pop up to `want` slot ids from queue qi.  Returns n; lane k (k-th set bit of `takers`) receives the
-// k-th id in *slot when k < n.  `takers` are the lanes that want a path; all 32 lanes must call.
+// Pop up to popc(takers) slot ids from queue qi.  Returns n; the k-th taker lane (k < n) receives an
+// id in *slot.  All 32 lanes must call.  A __threadfence_block() must follow before the slots are read.
 AVR_DEV int pool_pop(const PoolView &pv, int qi, unsigned takers, unsigned lane, int *slot) {
     int want = __popc(takers);
     int n = 0;
     unsigned pos0 = 0;
     if (lane == 0 && want > 0) {
-        int c = *(volatile int *)&pv.q[qi].count;
+        unsigned h = *(volatile unsigned *)&pv.q[qi].head;
         while (true) {
-            n = c < want ? c : want;
+            int avail = (int)(*(volatile unsigned *)&pv.q[qi].tail - h);
+            n = avail < want ? avail : want;
             if (n <= 0) { n = 0; break; }
-            int old = atomicCAS(&pv.q[qi].count, c, c - n);
-            if (old == c) break;
-            c = old;
+            unsigned old = atomicCAS(&pv.q[qi].head, h, h + (unsigned)n);
+            if (old == h) break;
+            h = old;
         }
-        if (n > 0) pos0 = atomicAdd(&pv.q[qi].head, (unsigned)n);
+        pos0 = h;
     }
     n = __shfl_sync(0xffffffffu, n, 0);
     pos0 = __shfl_sync(0xffffffffu, pos0, 0);
@@ -215,122 +216,146 @@ AVR_DEV int pool_pop(const PoolView &pv, int qi, unsigned takers, unsigned lane,
         int k = __popc(takers & ((1u << lane) - 1));
         if (k < n) {
             unsigned pos = pos0 + k;
-            unsigned cell = qi * pv.cap + (pos & pv.cap_mask);
-            while (pv.seq[cell] != pos + 1) {}
-            *slot = pv.data[cell];
-            __threadfence_block();
-            pv.seq[cell] = pos + pv.cap;
+            unsigned cell = ((unsigned)qi << pv.cap_log2) + (pos & pv.cap_mask);
+            unsigned round = (pos >> pv.cap_log2) << 16;
+            unsigned w;
+            while (((w = pv.cells[cell]) ^ round) >= 0xffffu) {}  // other round, or still free
+            *slot = int(w & 0xffffu);
+            pv.cells[cell] = ((round + 0x10000u) | 0xffffu);
         }
     }
-    __syncwarp();
-    __threadfence_block();
     return n;
 }
 
-// Slot <-> register copy of a path.  Word order is fixed by the two functions below; kSlotQuads is
-// odd so that consecutive slots start in different 16-byte bank groups.
+// Slot <-> register copy of a path, in three groups of 16-byte quads so that an op moves only what
+// it touches:
+//   A  event-only state   : pixel, sample index, sampler stream, wo, f_hat, ray o/d, wavelengths, L
+//   B  shared small state : flags, throughputs, shadow-ray weights, T_maj, current segment, sampled spectra
+//   C  tracking input     : sample-space ray, DDA, tracking RNG
+// Events load A+B and store A+B+C; the tracking loop loads B+C (plus A where the variant needs the
+// render-space ray or accumulates emission) and parks a finished path by storing B alone.
+enum { GRP_A = 1, GRP_B = 2, GRP_C = 4, GRP_ALL = 7 };
+
 template <typename TR>
 struct SlotIO {
     static constexpr int N = TR::NCH;
-    static constexpr int kWords = 2 + 4 + 4 + 4 + 3 * N + 1 + 12 + 10 + 3 + 2 * N + 4 + 3 * N + 1 + 3 + 2 * N;
-    static constexpr int kQuadsRaw = (kWords + 3) / 4;
-    static constexpr int kSlotQuads = kQuadsRaw | 1;
+    static constexpr int kQuadsA = 6;
+    static constexpr int kQuadsB = (4 + 10 * N + 3) / 4;
+    static constexpr int kQuadsC = 5;
+    static constexpr int kSlotQuads = (kQuadsA + kQuadsB + kQuadsC) | 1;  // odd: consecutive slots start in different bank groups
+    // groups the tracking loop needs besides B and C, and what it must write back when parking
+    static constexpr int kTrackLoad = GRP_B | GRP_C | ((TR::EXACT || TR::GENERAL) ? GRP_A : 0);
+    static constexpr int kTrackPark = GRP_B | (TR::GENERAL ? GRP_A : 0);
+
+    template <int Q>
+    struct Packer {
+        unsigned w[Q * 4];
+        int k = 0;
+        AVR_DEV void operator()(unsigned &x) { w[k++] = x; }
+        AVR_DEV void operator()(float &x) { w[k++] = __float_as_uint(x); }
+        AVR_DEV void flush(uint4 *sp) {
+#pragma unroll
+            for (int i = k; i < Q * 4; ++i) w[i] = 0;
+#pragma unroll
+            for (int q = 0; q < Q; ++q) sp[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        }
+    };
+    template <int Q>
+    struct Unpacker {
+        unsigned w[Q * 4];
+        int k = 0;
+        AVR_DEV void fill(const uint4 *sp) {
+#pragma unroll
+            for (int q = 0; q < Q; ++q) {
+                uint4 v = sp[q];
+                w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+            }
+        }
+        AVR_DEV void operator()(unsigned &x) { x = w[k++]; }
+        AVR_DEV void operator()(float &x) { x = __uint_as_float(w[k++]); }
+    };
+    AVR_DEV static void split64(uint64_t v, unsigned &lo, unsigned &hi) { lo = (unsigned)v; hi = (unsigned)(v >> 32); }
+    AVR_DEV static uint64_t join64(unsigned lo, unsigned hi) { return ((uint64_t)hi << 32) | lo; }
 
     template <typename F>
-    AVR_DEV static void visit(PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending, F &&f) {
-        // f(uint32_t&) or f(float&) for every persistent word, always in this order
-        unsigned pxy = (unsigned)ln.px | ((unsigned)ln.py << 16);
-        f(pxy);
-        ln.px = int(pxy & 0xffffu); ln.py = int(pxy >> 16);
-        unsigned sm = (unsigned)ln.samp;
-        f(sm);
-        ln.samp = (int)sm;
-        unsigned lo, hi;
-        lo = (unsigned)ln.srng.state; hi = (unsigned)(ln.srng.state >> 32); f(lo); f(hi);
-        ln.srng.state = ((uint64_t)hi << 32) | lo;
-        lo = (unsigned)ln.srng.inc; hi = (unsigned)(ln.srng.inc >> 32); f(lo); f(hi);
-        ln.srng.inc = ((uint64_t)hi << 32) | lo;
+    AVR_DEV static void visit_a(PathLane<TR> &ln, F &f) {
+        unsigned pxy = (unsigned)ln.px | ((unsigned)ln.py << 16), sm = (unsigned)ln.samp, lo, hi, lo2, hi2;
+        split64(ln.srng.state, lo, hi);
+        split64(ln.srng.inc, lo2, hi2);
+        f(pxy); f(sm); f(lo); f(hi); f(lo2); f(hi2);
+        ln.px = int(pxy & 0xffffu); ln.py = int(pxy >> 16); ln.samp = (int)sm;
+        ln.srng.state = join64(lo, hi); ln.srng.inc = join64(lo2, hi2);
+        f(ln.wo.x); f(ln.wo.y); f(ln.wo.z); f(ln.f_hat);
+        f(ln.fe.o.x); f(ln.fe.o.y); f(ln.fe.o.z); f(ln.fe.d.x); f(ln.fe.d.y); f(ln.fe.d.z);
 #pragma unroll
         for (int i = 0; i < 4; ++i) f(ln.lambda[i]);
 #pragma unroll
         for (int i = 0; i < 4; ++i) f(ln.L[i]);
-#pragma unroll
-        for (int i = 0; i < N; ++i) { f(ln.beta.v[i]); f(ln.r_u.v[i]); f(ln.r_l.v[i]); }
+    }
+    template <typename F>
+    AVR_DEV static void visit_b(PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending, F &f) {
         unsigned fl = (unsigned)ln.state | ((unsigned)ln.shadow << 8) | ((unsigned)pending << 9) | ((unsigned)ln.depth << 16);
         f(fl);
         ln.state = int(fl & 0xffu); ln.shadow = (fl >> 8) & 1u; pending = (fl >> 9) & 1u; ln.depth = int(fl >> 16);
-        f(ln.fe.o.x); f(ln.fe.o.y); f(ln.fe.o.z); f(ln.fe.d.x); f(ln.fe.d.y); f(ln.fe.d.z);
+        f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            f(ln.beta.v[i]); f(ln.r_u.v[i]); f(ln.r_l.v[i]);
+            f(ln.T_ray.v[i]); f(ln.s_rl.v[i]); f(ln.s_ru.v[i]);
+            f(ln.T_maj.v[i]); f(ln.sigma_maj.v[i]);
+            f(lc.sig_a.v[i]); f(lc.sig_s.v[i]);
+        }
+    }
+    template <typename F>
+    AVR_DEV static void visit_c(PathLane<TR> &ln, F &f) {
         f(ln.fe.so.x); f(ln.fe.so.y); f(ln.fe.so.z); f(ln.fe.sd.x); f(ln.fe.sd.y); f(ln.fe.sd.z);
         f(ln.dda.tMin); f(ln.dda.tMax);
 #pragma unroll
         for (int i = 0; i < 3; ++i) { f(ln.dda.nct[i]); f(ln.dda.dTs[i]); }
-        unsigned dl = (unsigned)ln.dda.lin;
+        unsigned dl = (unsigned)ln.dda.lin, lo, hi, lo2, hi2;
         f(dl); f(ln.dda.rem);
         ln.dda.lin = (int)dl;
-        f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
-#pragma unroll
-        for (int i = 0; i < N; ++i) { f(ln.sigma_maj.v[i]); f(ln.T_maj.v[i]); }
-        lo = (unsigned)ln.trng.state; hi = (unsigned)(ln.trng.state >> 32); f(lo); f(hi);
-        ln.trng.state = ((uint64_t)hi << 32) | lo;
-        lo = (unsigned)ln.trng.inc; hi = (unsigned)(ln.trng.inc >> 32); f(lo); f(hi);
-        ln.trng.inc = ((uint64_t)hi << 32) | lo;
-#pragma unroll
-        for (int i = 0; i < N; ++i) { f(ln.T_ray.v[i]); f(ln.s_rl.v[i]); f(ln.s_ru.v[i]); }
-        f(ln.f_hat);
-        f(ln.wo.x); f(ln.wo.y); f(ln.wo.z);
-#pragma unroll
-        for (int i = 0; i < N; ++i) { f(lc.sig_a.v[i]); f(lc.sig_s.v[i]); }
+        split64(ln.trng.state, lo, hi);
+        split64(ln.trng.inc, lo2, hi2);
+        f(lo); f(hi); f(lo2); f(hi2);
+        ln.trng.state = join64(lo, hi); ln.trng.inc = join64(lo2, hi2);
     }
 
-    struct Packer {
-        unsigned w[kSlotQuads * 4];
-        int k = 0;
-        AVR_DEV void operator()(unsigned &x) { w[k++] = x; }
-        AVR_DEV void operator()(float &x) { w[k++] = __float_as_uint(x); }
-    };
-    struct Unpacker {
-        unsigned w[kSlotQuads * 4];
-        int k = 0;
-        AVR_DEV void operator()(unsigned &x) { x = w[k++]; }
-        AVR_DEV void operator()(float &x) { x = __uint_as_float(w[k++]); }
-    };
-
+    template <int GROUPS>
     AVR_DEV static void store(uint4 *sp, PathLane<TR> &ln, LambdaCtx<N> &lc, bool pending) {
-        Packer p;
-        visit(ln, lc, pending, p);
-#pragma unroll
-        for (int i = p.k; i < kSlotQuads * 4; ++i) p.w[i] = 0;
-#pragma unroll
-        for (int q = 0; q < kQuadsRaw; ++q) sp[q] = make_uint4(p.w[4 * q], p.w[4 * q + 1], p.w[4 * q + 2], p.w[4 * q + 3]);
+        if (GROUPS & GRP_A) { Packer<kQuadsA> p; visit_a(ln, p); p.flush(sp); }
+        if (GROUPS & GRP_B) { Packer<kQuadsB> p; visit_b(ln, lc, pending, p); p.flush(sp + kQuadsA); }
+        if (GROUPS & GRP_C) { Packer<kQuadsC> p; visit_c(ln, p); p.flush(sp + kQuadsA + kQuadsB); }
     }
+    template <int GROUPS>
     AVR_DEV static void load(const uint4 *sp, const MediumView &mv, PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending) {
-        Unpacker u;
+        if (GROUPS & GRP_A) { Unpacker<kQuadsA> u; u.fill(sp); visit_a(ln, u); }
+        if (GROUPS & GRP_B) {
+            Unpacker<kQuadsB> u;
+            u.fill(sp + kQuadsA);
+            visit_b(ln, lc, pending, u);
+            // derived: sigma_t and the wavelengths of the batch (make_lambda_ctx, avr_tmaj.cuh)
 #pragma unroll
-        for (int q = 0; q < kQuadsRaw; ++q) {
-            uint4 v = sp[q];
-            u.w[4 * q] = v.x; u.w[4 * q + 1] = v.y; u.w[4 * q + 2] = v.z; u.w[4 * q + 3] = v.w;
+            for (int i = 0; i < 4; ++i) lc.lambda[i] = ln.lambda[i];
+            if (mv.kind == KIND_RGB) lc.sigma_t = sconst<N>(1.f);
+            else lc.sigma_t = lc.sig_a + lc.sig_s;
         }
-        visit(ln, lc, pending, u);
-        // derived: sigma_t and the wavelengths of the batch (make_lambda_ctx, avr_tmaj.cuh)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) lc.lambda[i] = ln.lambda[i];
-        if (mv.kind == KIND_RGB) lc.sigma_t = sconst<N>(1.f);
-        else lc.sigma_t = lc.sig_a + lc.sig_s;
+        if (GROUPS & GRP_C) { Unpacker<kQuadsC> u; u.fill(sp + kQuadsA + kQuadsB); visit_c(ln, u); }
     }
 };
 
 // shared-memory layout, computed identically on host and device
 struct PoolLayout {
-    unsigned off_slots, off_seq, off_data, off_q, off_live, total, cap;
+    unsigned off_slots, off_cells, off_q, off_live, total, cap, cap_log2;
 };
 __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned pool, unsigned slot_quads) {
     PoolLayout l;
     l.cap = 32;
-    while (l.cap < pool) l.cap <<= 1;
+    l.cap_log2 = 5;
+    while (l.cap < pool) { l.cap <<= 1; l.cap_log2++; }
     l.off_slots = (maj_bytes + 15u) & ~15u;
-    l.off_seq = l.off_slots + pool * slot_quads * 16u;
-    l.off_data = l.off_seq + kNumQueues * l.cap * 4u;
-    l.off_q = (l.off_data + kNumQueues * l.cap * 2u + 15u) & ~15u;
+    l.off_cells = l.off_slots + pool * slot_quads * 16u;
+    l.off_q = l.off_cells + kNumQueues * l.cap * 4u;
     l.off_live = l.off_q + kNumQueues * (unsigned)sizeof(PoolQueue);
     l.total = l.off_live + 16u;
     return l;
@@ -347,7 +372,7 @@ struct LaneCounters {
 };
 
 // After an op: hand every path of the batch to the queue of the op it waits for next.
-template <typename TR>
+template <typename TR, int GROUPS>
 AVR_DEV void requeue(const PoolView &pv, unsigned lane, bool have, int slot, PathLane<TR> &ln,
                      LambdaCtx<TR::NCH> &lc, bool pending) {
     if (have && ln.state == ST_EV_PATH_END) {
@@ -355,8 +380,9 @@ AVR_DEV void requeue(const PoolView &pv, unsigned lane, bool have, int slot, Pat
         ln.state = ST_DEAD;
         pending = true;
     }
-    if (have && ln.state != ST_RETIRED) SlotIO<TR>::store(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln, lc, pending);
-    __syncwarp();
+    if (have && ln.state != ST_RETIRED)
+        SlotIO<TR>::template store<GROUPS>(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln, lc, pending);
+    __threadfence_block();  // slot contents before the queue cells that publish them
     unsigned m_tr = __ballot_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_COLLIDE));
     unsigned m_sc = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SCATTER);
     unsigned m_se = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SHADOW_END);
@@ -379,9 +405,10 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
     int slot = 0;
     int n = pool_pop(pv, qi, 0xffffffffu, lane, &slot);
     if (n == 0) return;
+    __threadfence_block();
     bool have = (int)lane < n;
     bool pending = false;
-    if (have) SlotIO<TR>::load(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
+    if (have) SlotIO<TR>::template load<GRP_A | GRP_B>(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
 
     if (qi == Q_DEAD) {
         // ---- R. regenerate: flush the finished sample, fetch work with one aggregated atomic ---------
@@ -545,7 +572,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             ln.state = ST_WALK;
         }
     }
-    requeue<TR>(pv, lane, have, slot, ln, lc, pending);
+    requeue<TR, GRP_ALL>(pv, lane, have, slot, ln, lc, pending);
 }
 
 // Tracking loop of one warp: every lane holds a path in registers and walks SampleT_maj (ops A and B);
@@ -557,18 +584,27 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                         unsigned lane, PathLane<TR> &ln, LambdaCtx<TR::NCH> &lc, LaneCounters &cn) {
     constexpr int N = TR::NCH;
     constexpr bool EX = TR::EXACT;
-    bool have = false, pending = false;
+    bool have = false, pending = false;  // have: the lane holds a path (tracking, or finished and not yet parked)
     int slot = 0;
     ln.state = ST_DEAD;
     while (true) {
-        // ---- refill idle lanes from Q_TRACK --------------------------------------------------------
-        unsigned idle = __ballot_sync(0xffffffffu, !have);
+        // ---- park finished paths and refill from Q_TRACK, both in batches of >= refill_lanes -------
+        bool fin = have && ln.state >= ST_EV_SCATTER;
+        unsigned idle = __ballot_sync(0xffffffffu, !have || fin);
         if (__popc(idle) >= rp.refill_lanes || idle == 0xffffffffu) {
+            if (__any_sync(0xffffffffu, fin)) {
+                requeue<TR, SlotIO<TR>::kTrackPark>(pv, lane, fin, slot, ln, lc, pending);
+                if (fin) {
+                    have = false;
+                    ln.state = ST_DEAD;
+                }
+            }
             int got = -1;
             int n = pool_pop(pv, Q_TRACK, idle, lane, &got);
+            __threadfence_block();
             if (!have && __popc(idle & ((1u << lane) - 1)) < n) {
                 slot = got;
-                SlotIO<TR>::load(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
+                SlotIO<TR>::template load<SlotIO<TR>::kTrackLoad>(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
                 have = true;
             }
             int active = 32 - __popc(idle) + n;
@@ -577,14 +613,13 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 // nothing to refill with: give the remaining paths back if event work is waiting
                 int ev = 0;
                 if (lane == 0) {
-                    int a = *(volatile int *)&pv.q[Q_SCATTER].count, b = *(volatile int *)&pv.q[Q_SHADOW_END].count;
-                    int c = *(volatile int *)&pv.q[Q_DEAD].count;
+                    int a = pool_fill(pv, Q_SCATTER), b = pool_fill(pv, Q_SHADOW_END), c = pool_fill(pv, Q_DEAD);
                     ev = a > b ? a : b;
                     ev = c > ev ? c : ev;
                 }
                 ev = __shfl_sync(0xffffffffu, ev, 0);
                 if ((ev >= 32 && active <= rp.yield_lanes_full) || (ev > 0 && active <= rp.yield_lanes)) {
-                    requeue<TR>(pv, lane, have, slot, ln, lc, pending);
+                    requeue<TR, SlotIO<TR>::kTrackLoad>(pv, lane, have, slot, ln, lc, pending);
                     return;
                 }
             }
@@ -711,15 +746,6 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             }
         }
 
-        // ---- park the paths that reached an event ----------------------------------------------------
-        bool fin = have && ln.state >= ST_EV_SCATTER;
-        if (__any_sync(0xffffffffu, fin)) {
-            requeue<TR>(pv, lane, fin, slot, ln, lc, pending);
-            if (fin) {
-                have = false;
-                ln.state = ST_DEAD;
-            }
-        }
     }
 }
 
@@ -735,11 +761,10 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     const PoolLayout lay = pool_layout(maj_bytes, (unsigned)rp.pool, IO::kSlotQuads);
     PoolView pv;
     pv.slots = reinterpret_cast<uint4 *>(smem + lay.off_slots);
-    pv.seq = reinterpret_cast<volatile unsigned *>(smem + lay.off_seq);
-    pv.data = reinterpret_cast<volatile unsigned short *>(smem + lay.off_data);
+    pv.cells = reinterpret_cast<volatile unsigned *>(smem + lay.off_cells);
     pv.q = reinterpret_cast<PoolQueue *>(smem + lay.off_q);
     pv.live = reinterpret_cast<volatile int *>(smem + lay.off_live);
-    pv.cap = lay.cap;
+    pv.cap_log2 = lay.cap_log2;
     pv.cap_mask = lay.cap - 1;
     {
         if (rp.maj_in_smem) {
@@ -751,15 +776,13 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
         for (unsigned i = threadIdx.x; i < (unsigned)rp.pool * IO::kSlotQuads; i += blockDim.x)
             pv.slots[i] = make_uint4(0, 0, 0, 0);
         for (unsigned i = threadIdx.x; i < kNumQueues * lay.cap; i += blockDim.x) {
-            unsigned qi = i / lay.cap, c = i % lay.cap;
+            unsigned qi = i >> lay.cap_log2, c = i & (lay.cap - 1);
             bool filled = qi == Q_DEAD && c < (unsigned)rp.pool;
-            pv.seq[i] = filled ? c + 1 : c;
-            pv.data[i] = (unsigned short)c;
+            pv.cells[i] = filled ? c : 0xffffu;  // round 0: entry c, or free
         }
         if (threadIdx.x < kNumQueues) {
             pv.q[threadIdx.x].head = 0;
             pv.q[threadIdx.x].tail = threadIdx.x == Q_DEAD ? (unsigned)rp.pool : 0u;
-            pv.q[threadIdx.x].count = threadIdx.x == Q_DEAD ? rp.pool : 0;
         }
         if (threadIdx.x == 0) *pv.live = rp.pool;
         __syncthreads();
@@ -773,10 +796,10 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
         // ---- warp-level dispatch on the queue fill levels ---------------------------------------------
         int c_dead = 0, c_sc = 0, c_se = 0, c_tr = 0, live = 0;
         if (lane == 0) {
-            c_dead = *(volatile int *)&pv.q[Q_DEAD].count;
-            c_sc = *(volatile int *)&pv.q[Q_SCATTER].count;
-            c_se = *(volatile int *)&pv.q[Q_SHADOW_END].count;
-            c_tr = *(volatile int *)&pv.q[Q_TRACK].count;
+            c_dead = pool_fill(pv, Q_DEAD);
+            c_sc = pool_fill(pv, Q_SCATTER);
+            c_se = pool_fill(pv, Q_SHADOW_END);
+            c_tr = pool_fill(pv, Q_TRACK);
             live = *pv.live;
         }
         int choice;  // queue to serve, -1: sleep, -2: done

@@ -364,7 +364,7 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 template <typename TR>
 struct KernelCfg {
     static constexpr int kThreads = 256;
-    static constexpr int kMinBlocks = (TR::NCH == 1 && !TR::GENERAL) ? 2 : 1;
+    static constexpr int kMinBlocks = (TR::NCH == 1 && !TR::GENERAL) ? AVR_MIN_BLOCKS : 1;
 };
 
 struct LaneCounters {
@@ -656,7 +656,13 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             }
         }
 
-        // ---- B. one tentative collision along the current segment ------------------------------------
+        // ---- B. one tentative collision along the current segment: runs when enough lanes wait for it
+        //      (it costs ~5 DDA steps), or when no lane is left walking ---------------------------------
+        {
+            unsigned mc = __ballot_sync(0xffffffffu, have && ln.state == ST_COLLIDE);
+            if (mc == 0) continue;
+            if (__popc(mc) < rp.collide_min && __any_sync(0xffffffffu, have && ln.state == ST_WALK)) continue;
+        }
         if (have && ln.state == ST_COLLIDE) {
             float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
             ln.u = ln.trng.uniform();

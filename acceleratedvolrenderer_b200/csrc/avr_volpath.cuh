@@ -32,6 +32,7 @@ struct RenderParams {
     int pool;                 // paths resident per CTA (shared-memory slots)
     int maj_in_smem;          // 1: the majorant grid is staged in shared memory
     int walk_steps;           // DDA steps per tracking trip
+    int collide_min;          // lanes inside a segment that make the collision op worth running
     int refill_lanes;         // idle lanes of a tracking warp that trigger a refill from Q_TRACK
     int track_min;            // Q_TRACK fill level at which a warp prefers tracking over partial event batches
     int yield_lanes;          // a dry tracking warp with <= this many paths gives them back if any event waits

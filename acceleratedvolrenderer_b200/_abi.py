@@ -199,6 +199,13 @@ class RenderDesc:
         c.rank, c.world = rank, world
         self.c = c
 
+    def __getattr__(self, name):
+        # scalar fields of the C struct read through (width, height, spp, sample_begin, ...)
+        c = self.__dict__.get("c")
+        if c is not None and name in {f[0] for f in avr_render_desc._fields_}:
+            return getattr(c, name)
+        raise AttributeError(name)
+
     def ranges(self):
         c = self.c
         x0, y0, x1, y1 = list(c.pixel_bounds)

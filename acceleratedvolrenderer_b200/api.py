@@ -286,6 +286,22 @@ class Graph:
                                                            C.c_int32(r0), C.c_int32(r1), C.c_void_p(flag_ptr),
                                                            C.c_void_p(stream or 0)))
 
+    def compute_final_light_sharded(self, L0_dev, bounces, rank, world, group=None):
+        """Row-sharded ComputeFinalLight over `world` ranks (one GPU each): every rank holds the whole CSR and
+        multiplies its vertex range; slices travel by ncclAllGather (sharding.propagate_sharded).
+        L0_dev: float32 CUDA tensor of n elements.  Returns (total tensor, iterations)."""
+        import torch
+        from . import sharding
+        full = torch.empty(self.n, dtype=torch.float32, device=L0_dev.device)
+        flag = torch.zeros(2, dtype=torch.int32, device=L0_dev.device)
+        stream = torch.cuda.current_stream(L0_dev.device).cuda_stream
+
+        def spmv_rows(cur, r0, r1):
+            self.spmv_rows_device(cur.data_ptr(), full.data_ptr(), r0, r1, flag.data_ptr(), stream=stream)
+            return full[r0:r1]
+
+        return sharding.propagate_sharded(spmv_rows, L0_dev, bounces, rank, world, group)
+
     def set_vertices(self, pos, light, search_range, vertex_radius):
         pos = _f32(pos); light = _f32(light)
         rng = None if search_range is None else _f32(search_range)

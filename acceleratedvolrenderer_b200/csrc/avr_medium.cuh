@@ -93,8 +93,14 @@ AVR_HD size_t octet_index(int cx, int cy, int cz, int nbx, int nby) {
     return brick * 64 + ((cz & 3) * 16 + (cy & 3) * 4 + (cx & 3));
 }
 AVR_DEV void ldg256(const float4 *p, float4 &a, float4 &b) {
-#if AVR_USE_LDG256
+#if AVR_USE_LDG256 == 1
+    // one 256-bit load; the L2::256B hint also pulls the neighbouring cells' sectors into L2
     asm volatile("ld.global.nc.L2::256B.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+#elif AVR_USE_LDG256 == 2
+    // one 256-bit load, no prefetch hint: DRAM traffic = the 32-byte sector of the cell
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
                  : "l"(p));
 #else

@@ -25,7 +25,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from acceleratedvolrenderer_b200 import scenes  # noqa: E402
+from acceleratedvolrenderer_b200 import scenes, sharding  # noqa: E402
 
 WORKLOADS = {
     # Disney-cloud stand-in (the real wdas_cloud .nvdb is not in the reference repo and cannot be
@@ -229,7 +229,7 @@ def main():
     W, H = w["width"], w["height"]
     film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
     # weak scaling by sample index: every rank renders its own `spp` samples of every pixel
-    rdr = rd.with_(spp=spp * world, sample_begin=rank * spp, sample_end=(rank + 1) * spp)
+    rdr = sharding.shard_samples(rd, rank, world, spp)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -241,8 +241,7 @@ def main():
         film.zero_()
         r = rdr.with_(sampler_seed=step)
         st = ctx.render_volpath_device(med, r, film.data_ptr(), want_stats=True)  # syncs the library stream
-        if world > 1:
-            dist.reduce(film, dst=0)
+        sharding.reduce_film(film, dst=0)
         return st
 
     for i in range(args.warmup):

@@ -1,0 +1,229 @@
+"""Seeded input cases shared by tests/golden/make_golden.py (which runs them through the reference's own
+compiled templates, oracle/_ref) and tests/test_oracle_golden.py (which runs them through the CPU
+restatement, oracle/liboracle.so).  Every case returns {name: ndarray}; the bar is bit-exactness.
+
+Case inputs are small on purpose: the fixtures travel with the repository.
+"""
+import numpy as np
+
+from acceleratedvolrenderer_b200 import scenes
+from acceleratedvolrenderer_b200._abi import GridDesc, RGBGridDesc
+
+LAMBDA = np.array([412.3, 533.9, 601.2, 688.8], dtype=np.float32)
+
+
+def case_scalar(ck):
+    """util/math.h FastExp, util/hash.h, util/rng.h, samplers.h IndependentSampler, util/sampling.h,
+    util/scattering.h HG, util/spectrum.h wavelengths/blackbody, util/containers.h SampledGrid::Lookup."""
+    rng = np.random.default_rng(1)
+    out = {}
+    x = np.concatenate([rng.uniform(-100, 5, 2000), [-1e30, 0, -0.0, 88, 100, -87.5, -126 * 0.6931]]).astype(np.float32)
+    out["fast_exp"] = ck.fast_exp(x)
+    out["mix_bits"] = ck.mix_bits(rng.integers(0, 2 ** 63, 256, dtype=np.uint64))
+    out["hash_float"] = ck.hash_float(rng.random(256, dtype=np.float32))
+    out["hash_point3"] = ck.hash_point3(rng.normal(size=(255, 3)).astype(np.float32))
+    for i, args in enumerate([(5, 7, 1, 0), (123456789, 0, 0, 1000), (2 ** 40 + 3, 99, 1, 65536 * 3 + 5)]):
+        u32, f = ck.rng_stream(*args, 64)
+        out[f"rng_u32_{i}"] = u32
+        out[f"rng_f_{i}"] = f
+    out["sampler_a"] = ck.independent_sampler(3, 9, 0, 5, 0, 32)
+    out["sampler_b"] = ck.independent_sampler(300, 200, 7, 127, 3, 32)
+    w = rng.random((1000, 3), dtype=np.float32)
+    w[:50, 2] = 0
+    u = rng.random(1000, dtype=np.float32)
+    u[:5] = [0, 0.99999994, 0.5, 1e-9, 0.999]
+    out["sample_discrete3"] = ck.sample_discrete3(w, u)
+    out["sample_exponential"] = ck.sample_exponential(u, rng.uniform(0.01, 100, 1000).astype(np.float32))
+    wo = rng.normal(size=(1000, 3))
+    wo /= np.linalg.norm(wo, axis=1, keepdims=True)
+    u2 = rng.random((1000, 2), dtype=np.float32)
+    for g in [0.0, 0.877, -0.5, 0.995, 5e-4]:
+        wi, pdf = ck.hg_sample(wo, g, u2)
+        out[f"hg_wi_{g}"] = wi
+        out[f"hg_pdf_{g}"] = pdf
+        out[f"hg_p_{g}"] = ck.hg_p(rng.uniform(-1, 1, 200), g)
+    out["wavelengths"] = ck.sample_wavelengths(u)
+    out["blackbody"] = ck.blackbody(rng.uniform(50, 6000, 200), [400., 500., 600., 700.])
+    grid = rng.random((7, 9, 11), dtype=np.float32)
+    p = rng.uniform(-0.1, 1.1, (3000, 3)).astype(np.float32)
+    p[:10] = [[0, 0, 0], [1, 1, 1], [0.5, 0.5, 0.5], [1, 0, 0], [0, 1, 0], [0, 0, 1], [.9999999, .5, .5],
+              [1e-8, .5, .5], [.5 / 11, .5 / 9, .5 / 7], [1 - .5 / 11, .5, .5]]
+    out["grid_lookup"] = ck.grid_lookup(grid, p)
+    return out
+
+
+def _dda_rays(rng, bounds, n):
+    b = np.asarray(bounds, dtype=np.float32)
+    c = (b[:3] + b[3:]) / 2
+    e = (b[3:] - b[:3])
+    o_ = c + rng.normal(size=(n, 3)) * e * 1.5
+    tgt = b[:3] + rng.random((n, 3)) * e
+    d = tgt - o_
+    d[:n // 10, 0] = 0
+    d[n // 10:n // 5, 1] = -0.0
+    d[n // 5:n // 4, 2] = 0
+    rays = np.zeros((n, 8), dtype=np.float32)
+    rays[:, :3] = o_
+    rays[:, 3:6] = d
+    rays[:, 6] = rng.uniform(0, 0.8, n)
+    rays[:, 7] = rays[:, 6] + rng.uniform(0, 1.5, n)
+    return rays
+
+
+def case_dda(ck):
+    """DDAMajorantIterator, media.h:136-214: per-ray segment lists (t range, sigma_maj, voxel)."""
+    rng = np.random.default_rng(2)
+    out = {}
+    for k, (bounds, res, n, cap) in enumerate([((0, 0, 0, 1, 1, 1), (16, 16, 16), 600, 64),
+                                               ((-1, -2, 0.5, 3, 1, 2.5), (64, 64, 64), 200, 200),
+                                               ((0, 0, 0, 1, 1, 1), (5, 7, 3), 600, 32)]):
+        vox = rng.random(res[0] * res[1] * res[2], dtype=np.float32)
+        vox[rng.random(vox.size) < 0.3] = 0
+        rays = _dda_rays(rng, bounds, n)
+        cnt, t, sig, vx = ck.dda(bounds, res, vox, rays, sigma_t=1.7, max_per_ray=cap)
+        out[f"dda{k}_count"] = cnt
+        # keep the fixture small: only the valid prefix of every ray
+        m = np.arange(cap)[None, :] < np.minimum(cnt, cap)[:, None]
+        out[f"dda{k}_t"] = t.reshape(n, cap, 2)[m]
+        out[f"dda{k}_sigma"] = sig.reshape(n, cap)[m]
+        out[f"dda{k}_voxel"] = vx.reshape(n, cap)[m]
+    return out
+
+
+def _rot_scale():
+    M = scenes.scale_translate((2, 0.5, 1.5), (0.3, -1, 2)).astype(np.float64)
+    th = 0.7
+    R = np.eye(4)
+    R[0, 0] = np.cos(th); R[0, 2] = np.sin(th); R[2, 0] = -np.sin(th); R[2, 2] = np.cos(th)
+    M2 = (M @ R).astype(np.float32)
+    M2i = np.linalg.inv(M2.astype(np.float64)).astype(np.float32)
+    return M2, M2i
+
+
+def case_transform(ck):
+    """Transform::operator()(Ray) / ApplyInverse(Ray), util/transform.h:391-433 (interval arithmetic)."""
+    rng = np.random.default_rng(3)
+    M2, M2i = _rot_scale()
+    rays7 = np.zeros((1500, 7), dtype=np.float32)
+    rays7[:, :3] = rng.normal(size=(1500, 3)) * 3
+    rays7[:, 3:6] = rng.normal(size=(1500, 3))
+    rays7[:, 6] = rng.uniform(0, 10, 1500)
+    rays7[:10, 3:6] = 0
+    eye = np.eye(4, dtype=np.float32)
+    return {"apply_inverse_ray": ck.apply_inverse_ray(M2, M2i, rays7), "apply_ray": ck.apply_ray(M2, M2i, rays7),
+            "apply_inverse_ray_identity": ck.apply_inverse_ray(eye, eye, rays7)}
+
+
+def _tmaj_fields(prefix, res, out, approx_t_event=False):
+    for f in res.dtype.names:
+        if f == "n_seg":
+            continue  # the probe counts segments differently (it cannot see inside the iterator)
+        if f == "t_event" and approx_t_event:
+            continue
+        out[f"{prefix}_{f}"] = np.ascontiguousarray(res[f])
+
+
+def case_uniformgrid(ck):
+    """GridMedium ctor / SamplePoint / SampleRay (media.h:265-337, media.cpp:221-331) and SampleT_maj
+    (media.h:741-806) under the three callbacks of the hot path."""
+    rng = np.random.default_rng(4)
+    out = {}
+    dens = scenes.fbm_density(24, 20, 28, seed=3)
+    M2, M2i = _rot_scale()
+    variants = [dict(), dict(render_from_medium=M2, medium_from_render=M2i, p0=(-1, 0, 0.5), p1=(1, 2, 1.5), scale=3.0),
+                dict(temperature=dens * 3000 + 50, lescale=dens * 2, le_norm=0.5, temperature_offset=10, temperature_scale=1.1),
+                dict(le=scenes.ramp_spectrum(0.2, 1.0), le_norm=0.01)]
+    for k, kw in enumerate(variants):
+        gd = GridDesc(dens, scenes.ramp_spectrum(0.5, 1.5), scenes.ramp_spectrum(6, 9), g=0.3, **kw)
+        m = ck.medium_uniformgrid(gd)
+        out[f"ug{k}_majorants"] = m.majorants()
+        out[f"ug{k}_emissive"] = np.array([m.is_emissive()], dtype=np.int32)
+        b0, b1 = gd.p0, gd.p1
+        npts = 1200
+        pm = (b0 + rng.uniform(-0.05, 1.05, (npts, 3)) * (b1 - b0)).astype(np.float32)
+        pr = (np.c_[pm, np.ones(npts)] @ gd.m.reshape(4, 4).T.astype(np.float64))[:, :3].astype(np.float32)
+        out[f"ug{k}_sample_point"] = m.sample_point(pr, LAMBDA)
+        n = 1500
+        org = rng.normal(size=(n, 3))
+        org /= np.linalg.norm(org, axis=1, keepdims=True)
+        org *= 3
+        ctr = (np.r_[(b0 + b1) / 2, 1] @ gd.m.reshape(4, 4).T)[:3]
+        tgt = pr[rng.integers(0, npts, n)]
+        rays7 = np.zeros((n, 7), dtype=np.float32)
+        rays7[:, :3] = org + ctr
+        rays7[:, 3:6] = (tgt - rays7[:, :3]) * rng.uniform(0.5, 2, (n, 1))
+        rays7[:, 6] = rng.uniform(0.2, 3, n)
+        out[f"ug{k}_ray_to_medium"] = m.ray_to_medium(rays7)
+        seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64)
+        u = rng.random(n, dtype=np.float32)
+        for mode in (0, 1, 2):
+            _tmaj_fields(f"ug{k}_tmaj{mode}", m.sample_tmaj(mode, rays7, seeds, u, LAMBDA), out, approx_t_event=(mode == 1))
+        m.close()
+    return out
+
+
+def case_rgbgrid(ck):
+    """RGBGridMedium (media.h:341-427, media.cpp:333-443)."""
+    rng = np.random.default_rng(5)
+    out = {}
+    dens = scenes.fbm_density(20, 18, 22, seed=3)
+    sa = scenes.rgb_voxels(dens * 0.5, rng)
+    ss = scenes.rgb_voxels(dens * 6, rng)
+    le = scenes.rgb_voxels(dens * 2, rng)
+    for k, kw in enumerate([dict(sigma_a=sa, sigma_s=ss), dict(sigma_s=ss, scale=2.0),
+                            dict(sigma_a=sa, sigma_s=ss, le=le, le_illuminant=scenes.ramp_spectrum(0.5, 1.5), le_scale=0.7, g=0.5)]):
+        gd = RGBGridDesc(**kw)
+        m = ck.medium_rgbgrid(gd)
+        out[f"rgb{k}_majorants"] = m.majorants()
+        out[f"rgb{k}_emissive"] = np.array([m.is_emissive()], dtype=np.int32)
+        pr = rng.uniform(-0.05, 1.05, (1000, 3)).astype(np.float32)
+        out[f"rgb{k}_sample_point"] = m.sample_point(pr, LAMBDA)
+        n = 800
+        org = rng.normal(size=(n, 3))
+        org /= np.linalg.norm(org, axis=1, keepdims=True)
+        org = org * 3 + 0.5
+        tgt = pr[rng.integers(0, 1000, n)]
+        rays7 = np.zeros((n, 7), dtype=np.float32)
+        rays7[:, :3] = org
+        rays7[:, 3:6] = (tgt - org) * rng.uniform(0.5, 2, (n, 1))
+        rays7[:, 6] = rng.uniform(0.2, 3, n)
+        seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64)
+        u = rng.random(n, dtype=np.float32)
+        for mode in (0, 1, 2):
+            _tmaj_fields(f"rgb{k}_tmaj{mode}", m.sample_tmaj(mode, rays7, seeds, u, LAMBDA), out, approx_t_event=True)
+        m.close()
+    return out
+
+
+def case_graph(ck):
+    """src/graph: Eigen SpMV propagation (free_graph.cpp:345-375) and the light-ray transmittance
+    estimator (graph/util.h SampleTransmittance)."""
+    rng = np.random.default_rng(6)
+    out = {}
+    for n in (50, 2000):
+        rowptr, col, val = scenes.random_graph(n, avg_deg=4, seed=n)
+        L0 = rng.random(n, dtype=np.float32)
+        for b in (0, 1, 3, 7):
+            total, iters = ck.graph_propagate(rowptr, col, val, L0, b)
+            out[f"graph{n}_b{b}_total"] = total
+            out[f"graph{n}_b{b}_iters"] = np.array([iters], dtype=np.int32)
+        total, iters = ck.graph_propagate(rowptr, col, val * 4e7, L0, 20)  # overflows: early-out path
+        out[f"graph{n}_overflow_total"] = total
+        out[f"graph{n}_overflow_iters"] = np.array([iters], dtype=np.int32)
+    dens = scenes.fbm_density(24, 20, 28, seed=3)
+    gd = GridDesc(dens, scenes.const_spectrum(0.2), scenes.const_spectrum(9.0), g=0.3)
+    m = ck.medium_uniformgrid(gd)
+    n = 600
+    org = np.c_[rng.uniform(0, 1, (n, 2)), np.full(n, -1.0)]
+    d = np.tile([0.05, 0.02, 1.0], (n, 1))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.c_[org, d].astype(np.float32)
+    pix = np.c_[rng.integers(0, 500, n), rng.integers(0, 500, n)].astype(np.int32)
+    ts = np.c_[rng.uniform(1.0, 1.5, n), rng.uniform(0.05, 0.4, n)].astype(np.float32)
+    out["graph_light_rays"] = m.graph_light_rays(rays, pix, ts, 8, 0, LAMBDA)
+    m.close()
+    return out
+
+
+CASES = {"scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
+         "rgbgrid": case_rgbgrid, "graph": case_graph}

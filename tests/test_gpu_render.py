@@ -176,3 +176,20 @@ def test_graph_light_rays(ctx, orc):
     assert ok.mean() >= 0.995
     assert abs(got.mean() - want.mean()) < 1e-3
     md.close(); mo.close()
+
+
+def test_graph_row_sharded_propagation_single_rank(ctx, orc):
+    """The multi-GPU propagation path (sharding.propagate_sharded over avr_graph_spmv_rows_device) at
+    world = 1: bit-identical to the oracle, same early-out iteration."""
+    import torch
+    for n, bounces, scale in ((5000, 6, 1.0), (777, 20, 4e7), (64, 0, 1.0)):
+        rowptr, col, val = scenes.random_graph(n, avg_deg=5, seed=n)
+        val = (val * scale).astype(np.float32)
+        L0 = np.random.default_rng(1).random(n, dtype=np.float32)
+        g = ctx.create_graph(rowptr, col, val)
+        total, it = g.compute_final_light_sharded(torch.from_numpy(L0).cuda(), bounces, 0, 1)
+        torch.cuda.synchronize()
+        g.close()
+        want, want_it = orc.graph_propagate(rowptr, col, val, L0, bounces)
+        assert it == want_it
+        assert (total.cpu().numpy().view(np.uint32) == want.view(np.uint32)).all()

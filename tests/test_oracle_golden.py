@@ -1,0 +1,80 @@
+"""CPU: the oracle (oracle/liboracle.so, the restatement every GPU parity test is judged by) against
+the golden vectors produced by the reference's own compiled code (tests/golden/make_golden.py), and
+- where /root/reference is present and oracle/_ref was built - against that code live.
+
+Bar: bit-exact on every array (NaNs must sit in the same places).  The light-ray estimator of
+src/graph is compared after its float sum, also bit-exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from cpu_checker import Checker, have_ref
+from golden_cases import CASES
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.npz")
+
+
+def bits_equal(a, b):
+    a = np.ascontiguousarray(a)
+    b = np.ascontiguousarray(b)
+    if a.shape != b.shape or a.dtype != b.dtype:
+        return False
+    return bool((a.view(np.uint8) == b.view(np.uint8)).all())
+
+
+def same_values(a, b):
+    """bit-equal, or equal as numbers with NaN == NaN (different NaN payloads are not a parity matter)"""
+    if bits_equal(a, b):
+        return True
+    a = np.asarray(a)
+    b = np.asarray(b)
+    if a.shape != b.shape or a.dtype != b.dtype or a.dtype.kind != "f":
+        return False
+    return bool(((a == b) | (np.isnan(a) & np.isnan(b))).all()) and bool((np.signbit(a) == np.signbit(b)).all())
+
+
+@pytest.fixture(scope="module")
+def golden():
+    assert os.path.exists(GOLDEN), "tests/golden/reference_vectors.npz missing (tests/golden/make_golden.py)"
+    return np.load(GOLDEN)
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_oracle_matches_reference_vectors(orc, golden, case):
+    got = CASES[case](orc)
+    keys = [k for k in golden.files if k.startswith(case + "/")]
+    assert len(keys) == len(got) and len(keys) > 0
+    bad = [k for k in keys if not same_values(got[k.split("/", 1)[1]], golden[k])]
+    assert not bad, f"{len(bad)} of {len(keys)} arrays differ from the reference: {bad[:5]}"
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (no /root/reference on this machine)")
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_oracle_matches_reference_live(orc, case):
+    ref = Checker("ref")
+    got, want = CASES[case](orc), CASES[case](ref)
+    bad = [k for k in want if not same_values(got[k], want[k])]
+    assert not bad, bad[:5]
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (no /root/reference on this machine)")
+def test_golden_file_is_current(golden):
+    """The committed fixture is what the reference produces today (guards against a stale .npz)."""
+    ref = Checker("ref")
+    for case in ("scalar", "transform"):
+        want = CASES[case](ref)
+        for k, v in want.items():
+            assert same_values(v, golden[f"{case}/{k}"]), k
+
+
+def test_host_libm_is_the_reference_libm(orc):
+    """The EXACT device path restates glibc's logf/sinf/cosf (avr_math.cuh); the oracle calls the host
+    libm the way the reference does.  Pin a few known-answer values so a different libm is noticed."""
+    x = np.array([0.5, 1.0, 2.0, 0.1, 7.25, 1e-20], dtype=np.float32)
+    got = orc.libm(0, x)
+    want = np.array([-0.6931472, 0.0, 0.6931472, -2.3025851, 1.9810015, -46.0517], dtype=np.float32)
+    assert np.allclose(got, want, rtol=3e-7, atol=0)
+    assert orc.libm(1, np.array([0.0], dtype=np.float32))[0] == 0.0
+    assert orc.libm(2, np.array([0.0], dtype=np.float32))[0] == 1.0

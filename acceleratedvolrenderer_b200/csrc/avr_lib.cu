@@ -316,6 +316,7 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     if (layout != LAYOUT_DENSE_F32) {
         v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
         size_t cells = size_t(v.nbx) * v.nby * v.nbz * 64;
+        if (cells >= (size_t(1) << 32)) { free_medium(m); return set_err(ctx, AVR_ERR_UNSUPPORTED, "octet layout: 2^32 or more cells"); }
         size_t bytes = cells * (layout == LAYOUT_OCTET_F32 ? 32 : 16);
         void *p = nullptr;
         cudaError_t e = cudaMalloc(&p, bytes);

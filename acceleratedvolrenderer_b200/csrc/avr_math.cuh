@@ -16,6 +16,12 @@ namespace avr {
 #define AVR_DEV __device__ __forceinline__
 #define AVR_HD __host__ __device__ __forceinline__
 
+// FAST-mode approximations with flush-to-zero (no denormal fix-up code around the MUFU)
+__device__ __forceinline__ float ftz_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ftz_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ftz_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ftz_div(float a, float b) { return a * ftz_rcp(b); }
+
 constexpr int kNSpec = 471;
 constexpr float kOneMinusEps = 0x1.fffffep-1f;
 constexpr float kMachEps = 0x1p-24f;
@@ -280,23 +286,23 @@ AVR_DEV float fast_exp_exact(float x) {
 template <bool EXACT>
 AVR_DEV float fast_exp(float x) {
     if (EXACT) return fast_exp_exact(x);
-    return __expf(x);
+    return ftz_ex2(x * 1.4426950408889634f);
 }
 template <bool EXACT>
 AVR_DEV float sample_exponential(float u, float a) {  // util/sampling.h:222-225
     if (EXACT) return -glibc_logf(1 - u) / a;
-    return __fdividef(-__logf(1 - u), a);
+    return ftz_lg2(1 - u) * -0.6931471805599453f * ftz_rcp(a);
 }
 template <bool EXACT>
 AVR_DEV float fdiv(float a, float b) {
     if (EXACT) return a / b;
-    return __fdividef(a, b);
+    return ftz_div(a, b);
 }
 // EXACT: a / s per channel (IEEE).  FAST: one approximate reciprocal, then multiplies.
 template <bool EXACT, int N>
 AVR_DEV Spec<N> sdiv(Spec<N> a, float s) {
     if (EXACT) return a / s;
-    return a * __fdividef(1.f, s);
+    return a * ftz_rcp(s);
 }
 AVR_DEV float lerp_exact(float x, float a, float b) { return (1 - x) * a + x * b; }  // util/math.h:210
 AVR_DEV float lerp_fast(float x, float a, float b) { return __fmaf_rn(x, b - a, a); }

@@ -88,9 +88,10 @@ AVR_DEV float lookup_dense(const float *v, int nx, int ny, int nz, V3 p) {
 // {v000,v100,v010,v110 | v001,v101,v011,v111} (out-of-range taps baked as 0); cells are grouped
 // in 4x4x4 bricks, x fastest inside the brick, so one fetch = one 32-byte sector (fp32) or one
 // 16-byte vector (fp16) and the 4 x-neighbours of a cell share a 128-byte line.
-AVR_HD size_t octet_index(int cx, int cy, int cz, int nbx, int nby) {
-    size_t brick = (size_t(cz >> 2) * nby + (cy >> 2)) * nbx + (cx >> 2);
-    return brick * 64 + ((cz & 3) * 16 + (cy & 3) * 4 + (cx & 3));
+// 32-bit cell index (medium creation rejects octet layouts with 2^32 or more cells)
+AVR_HD uint32_t octet_index(int cx, int cy, int cz, int nbx, int nby) {
+    uint32_t brick = (uint32_t(cz >> 2) * uint32_t(nby) + uint32_t(cy >> 2)) * uint32_t(nbx) + uint32_t(cx >> 2);
+    return brick * 64u + uint32_t((cz & 3) * 16 + (cy & 3) * 4 + (cx & 3));
 }
 AVR_DEV void ldg256(const float4 *p, float4 &a, float4 &b) {
 #if AVR_USE_LDG256 == 1
@@ -114,7 +115,7 @@ AVR_DEV float lookup_oct32_s(const MediumView &mv, float sx, float sy, float sz)
     int cx = (int)fx + 1, cy = (int)fy + 1, cz = (int)fz + 1;
     if ((unsigned)cx > (unsigned)mv.nx || (unsigned)cy > (unsigned)mv.ny || (unsigned)cz > (unsigned)mv.nz) return 0.f;
     float4 a, b;
-    ldg256(mv.oct32 + 2 * octet_index(cx, cy, cz, mv.nbx, mv.nby), a, b);
+    ldg256(mv.oct32 + 2 * size_t(octet_index(cx, cy, cz, mv.nbx, mv.nby)), a, b);
     return trilerp8<EXACT>(sx - fx, sy - fy, sz - fz, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
 }
 AVR_DEV float2 h2f(uint32_t u) {

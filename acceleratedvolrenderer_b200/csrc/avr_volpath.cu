@@ -558,7 +558,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             V3 md = v3(__fmaf_rn(a[0], d.x, __fmaf_rn(a[1], d.y, a[2] * d.z)),
                        __fmaf_rn(a[4], d.x, __fmaf_rn(a[5], d.y, a[6] * d.z)),
                        __fmaf_rn(a[8], d.x, __fmaf_rn(a[9], d.y, a[10] * d.z)));
-            V3 inv = v3(__fdividef(1.f, md.x), __fdividef(1.f, md.y), __fdividef(1.f, md.z));
+            V3 inv = v3(ftz_rcp(md.x), ftz_rcp(md.y), ftz_rcp(md.z));
             float h0 = 0.f, h1 = tMax;
 #pragma unroll
             for (int i = 0; i < 3; ++i) {

@@ -82,7 +82,7 @@ AVR_DEV bool boundary_hit_fast(const RenderParams &rp, V3 o, V3 d, float *t0, fl
         float a = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, d.z * d.z));
         float hb = __fmaf_rn(ox, d.x, __fmaf_rn(oy, d.y, oz * d.z));  // b / 2
         // |o - (o.d/a) d|^2 form of the discriminant: stable for origins far from / on the sphere
-        float ia = __fdividef(1.f, a);
+        float ia = ftz_rcp(a);
         float k = hb * ia;
         float px = __fmaf_rn(-k, d.x, ox), py = __fmaf_rn(-k, d.y, oy), pz = __fmaf_rn(-k, d.z, oz);
         float disc = r * r - __fmaf_rn(px, px, __fmaf_rn(py, py, pz * pz));  // = (b^2/4 - a c) / a
@@ -95,7 +95,7 @@ AVR_DEV bool boundary_hit_fast(const RenderParams &rp, V3 o, V3 d, float *t0, fl
     float a0 = __int_as_float(0xff800000), a1 = __int_as_float(0x7f800000);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-        float inv = __fdividef(1.f, comp(d, i));
+        float inv = ftz_rcp(comp(d, i));
         float tn = (rp.boundary[i] - comp(o, i)) * inv, tf = (rp.boundary[3 + i] - comp(o, i)) * inv;
         a0 = fmaxf(a0, fminf(tn, tf));
         a1 = fminf(a1, fmaxf(tn, tf));

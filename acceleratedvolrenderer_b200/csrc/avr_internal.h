@@ -19,6 +19,9 @@ struct avr_ctx {
     unsigned long long *d_counters = nullptr;  // work counter + stats
     double *d_film = nullptr;
     size_t film_bytes = 0;
+    double *h_film = nullptr;  // pinned staging for the film read-back
+    size_t h_film_bytes = 0;
+    cudaEvent_t ev_chunk[8] = {};
     float *d_tables = nullptr;  // light spectrum + sensor tables for the current render
 };
 

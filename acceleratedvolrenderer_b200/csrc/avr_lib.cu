@@ -65,6 +65,8 @@ extern "C" void avr_ctx_destroy(avr_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_film);
+    if (ctx->h_film) cudaFreeHost(ctx->h_film);
+    for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
     cudaFree(ctx->d_tables);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);

@@ -6,4 +6,9 @@
 namespace avr {
 // Validates an avr_render_desc, uploads its light/sensor tables and fills the kernel parameter block.
 avr_status fill_render_params(avr_ctx *ctx, const avr_render_desc *d, RenderParams *rp, cudaStream_t stream);
+// Device film scratch of the context, zeroed on `stream` (grown on demand).
+avr_status film_scratch(avr_ctx *ctx, size_t bytes, cudaStream_t stream);
+// film[i] += device film: pinned staging, the copy runs in chunks on ctx->stream while host threads add
+// the chunks that have arrived.
+avr_status film_add_to_host(avr_ctx *ctx, size_t bytes, double *film);
 }  // namespace avr

@@ -279,9 +279,9 @@ def main():
     ctx.render_volpath(med, rdr, film=host_film)  # warm
     sync_all()
     t = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 2))
+    e2e_steps = max(1, args.steps)
     for i in range(e2e_steps):
-        host_film[:] = 0
+        # progressive accumulation: every step adds its samples to the same host film (the C entry ADDS)
         ctx.render_volpath(med, rdr.with_(sampler_seed=100 + i), film=host_film)
     if world > 1:
         dist.barrier()

@@ -577,6 +577,18 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
     requeue<TR, GRP_ALL>(pv, lane, have, slot, ln, lc, pending);
 }
 
+// Inside the tracking loop a shadow-ray lane carries (T_ray, r_u, r_l of the shadow ray) in the fields
+// (beta, r_u, r_l), so that camera and shadow lanes share the weight-update instructions of op B.
+// Applied after a slot load and undone before a slot store.
+template <typename TR>
+AVR_DEV void swap_shadow_weights(PathLane<TR> &ln) {
+    if (!ln.shadow) return;
+    Spec<TR::NCH> t;
+    t = ln.beta; ln.beta = ln.T_ray; ln.T_ray = t;
+    t = ln.r_u; ln.r_u = ln.s_ru; ln.s_ru = t;
+    t = ln.r_l; ln.r_l = ln.s_rl; ln.s_rl = t;
+}
+
 // Tracking loop of one warp: every lane holds a path in registers and walks SampleT_maj (ops A and B);
 // a lane whose path reaches an event parks it in its slot, queues it for the event op and is refilled
 // from Q_TRACK.  The warp leaves when it runs dry, or yields its few remaining paths back to Q_TRACK
@@ -595,6 +607,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
         unsigned idle = __ballot_sync(0xffffffffu, !have || fin);
         if (__popc(idle) >= rp.refill_lanes || idle == 0xffffffffu) {
             if (__any_sync(0xffffffffu, fin)) {
+                if (fin) swap_shadow_weights(ln);
                 requeue<TR, SlotIO<TR>::kTrackPark>(pv, lane, fin, slot, ln, lc, pending);
                 if (fin) {
                     have = false;
@@ -607,6 +620,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             if (!have && __popc(idle & ((1u << lane) - 1)) < n) {
                 slot = got;
                 SlotIO<TR>::template load<SlotIO<TR>::kTrackLoad>(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
+                swap_shadow_weights(ln);
                 have = true;
             }
             int active = 32 - __popc(idle) + n;
@@ -621,6 +635,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 }
                 ev = __shfl_sync(0xffffffffu, ev, 0);
                 if ((ev >= 32 && active <= rp.yield_lanes_full) || (ev > 0 && active <= rp.yield_lanes)) {
+                    if (have) swap_shadow_weights(ln);
                     requeue<TR, SlotIO<TR>::kTrackLoad>(pv, lane, have, slot, ln, lc, pending);
                     return;
                 }
@@ -672,31 +687,16 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
                 PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
                 Spec<N> sigma_maj = ln.sigma_maj;
-                bool cont;
-                if (ln.shadow) {
-                    // ratio tracking + Russian roulette, cpu/integrators.cpp:1356-1378
-                    cn.sh++;
-                    Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                    float pdf = T_maj[0] * sigma_maj[0];
-                    ln.T_ray = ln.T_ray * sdiv<EX>(T_maj * sigma_n, pdf);
-                    ln.s_rl = ln.s_rl * sdiv<EX>(T_maj * sigma_maj, pdf);
-                    ln.s_ru = ln.s_ru * sdiv<EX>(T_maj * sigma_n, pdf);
-                    Spec<N> Tr = sdiv<EX>(ln.T_ray, average(ln.s_rl + ln.s_ru));
-                    if (max_component(Tr) < 0.05f) {
-                        float q = 0.75f;
-                        if (ln.trng.uniform() < q) ln.T_ray = sconst<N>(0.f);
-                        else ln.T_ray = ln.T_ray / (1 - q);
-                    }
-                    cont = nonzero(ln.T_ray);
-                    if (!cont) {
-                        ln.T_maj = sconst<N>(1.f);  // SampleT_maj returns 1 when the callback stops
-                        ln.state = ST_EV_SHADOW_END;
-                    }
-                } else {
-                    // VolPathIntegrator::Li callback, cpu/integrators.cpp:990-1078
-                    cont = false;
+                Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
+                // One instruction stream for both ray kinds.  Inside this loop a shadow lane keeps its
+                // ratio-tracking weights in the camera fields (swap_shadow_weights): beta = T_ray,
+                // r_u = its r_u, r_l = its r_l, so the weight update below is the same code.
+                bool cont = false, alive = true;
+                int mode = 2;  // 0 absorb, 1 scatter, 2 null collision (the only event of a shadow ray)
+                if (!ln.shadow) {
+                    // VolPathIntegrator::Li callback: event selection, cpu/integrators.cpp:990-1022
                     if (!nonzero(ln.beta)) {
-                        ln.state = ST_EV_PATH_END;
+                        alive = false;
                     } else {
                         cn.cam++;
                         if (TR::GENERAL && ln.depth < rp.max_depth && nonzero(mp.Le)) {
@@ -714,32 +714,47 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                         float pScatter = fdiv<EX>(mp.sigma_s[0], sigma_maj[0]);
                         float pNull = fmaxf(0.f, 1 - pAbsorb - pScatter);
                         float um = ln.trng.uniform();
-                        int mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
-                        if (mode == 0) {
-                            ln.state = ST_EV_PATH_END;
-                        } else if (mode == 1) {
-                            if (ln.depth++ >= rp.max_depth) {
-                                ln.state = ST_EV_PATH_END;
-                            } else {
-                                float pdf = T_maj[0] * mp.sigma_s[0];
-                                ln.beta = ln.beta * sdiv<EX>(T_maj * mp.sigma_s, pdf);
-                                ln.r_u = ln.r_u * sdiv<EX>(T_maj * mp.sigma_s, pdf);
-                                if (nonzero(ln.beta) && nonzero(ln.r_u)) {
-                                    ln.cur_tMin = t;  // scatter position parameter for E1
-                                    ln.state = ST_EV_SCATTER;
-                                } else
-                                    ln.state = ST_EV_PATH_END;
-                            }
-                        } else {
-                            Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
-                            float pdf = T_maj[0] * sigma_n[0];
-                            ln.beta = ln.beta * sdiv<EX>(T_maj * sigma_n, pdf);
-                            if (pdf == 0) ln.beta = sconst<N>(0.f);
-                            ln.r_u = ln.r_u * sdiv<EX>(T_maj * sigma_n, pdf);
-                            ln.r_l = ln.r_l * sdiv<EX>(T_maj * sigma_maj, pdf);
-                            cont = nonzero(ln.beta) && nonzero(ln.r_u);
-                            if (!cont) ln.state = ST_EV_PATH_END;
+                        mode = sample_discrete3(pAbsorb, pScatter, pNull, um);
+                        if (mode == 0) alive = false;
+                        else if (mode == 1 && ln.depth++ >= rp.max_depth) alive = false;
+                    }
+                } else {
+                    cn.sh++;
+                }
+                if (!alive) {
+                    ln.state = ST_EV_PATH_END;
+                } else {
+                    // weight update: camera scatter (:1031-1035) and null (:1066-1074), shadow ratio
+                    // tracking (:1356-1367); pdf is the probability of the event that was taken
+                    Spec<N> sx = mode == 1 ? mp.sigma_s : sigma_n;
+                    float pdf = T_maj[0] * (ln.shadow ? sigma_maj[0] : sx[0]);
+                    Spec<N> fx = sdiv<EX>(T_maj * sx, pdf);
+                    ln.beta = ln.beta * fx;
+                    if (!ln.shadow && mode == 2 && pdf == 0) ln.beta = sconst<N>(0.f);
+                    ln.r_u = ln.r_u * fx;
+                    if (mode == 2) ln.r_l = ln.r_l * sdiv<EX>(T_maj * sigma_maj, pdf);
+                    if (ln.shadow) {
+                        // Russian roulette on the ratio-tracking estimate, cpu/integrators.cpp:1369-1378
+                        Spec<N> Tr = sdiv<EX>(ln.beta, average(ln.r_l + ln.r_u));
+                        if (max_component(Tr) < 0.05f) {
+                            float q = 0.75f;
+                            if (ln.trng.uniform() < q) ln.beta = sconst<N>(0.f);
+                            else ln.beta = ln.beta / (1 - q);
                         }
+                        cont = nonzero(ln.beta);
+                        if (!cont) {
+                            ln.T_maj = sconst<N>(1.f);  // SampleT_maj returns 1 when the callback stops
+                            ln.state = ST_EV_SHADOW_END;
+                        }
+                    } else if (mode == 1) {
+                        if (nonzero(ln.beta) && nonzero(ln.r_u)) {
+                            ln.cur_tMin = t;  // scatter position parameter for E1
+                            ln.state = ST_EV_SCATTER;
+                        } else
+                            ln.state = ST_EV_PATH_END;
+                    } else {
+                        cont = nonzero(ln.beta) && nonzero(ln.r_u);
+                        if (!cont) ln.state = ST_EV_PATH_END;
                     }
                 }
                 if (cont) {

@@ -363,10 +363,14 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
     return l;
 }
 
+#ifndef AVR_CTA_THREADS
+#define AVR_CTA_THREADS 256
+#endif
 template <typename TR>
 struct KernelCfg {
-    static constexpr int kThreads = 256;
-    static constexpr int kMinBlocks = (TR::NCH == 1 && !TR::GENERAL) ? AVR_MIN_BLOCKS : 1;
+    static constexpr int kThreads = AVR_CTA_THREADS;
+    static constexpr int kMinBlocks =
+        (TR::NCH == 1 && !TR::GENERAL && AVR_MIN_BLOCKS * 256 >= AVR_CTA_THREADS) ? AVR_MIN_BLOCKS * 256 / AVR_CTA_THREADS : 1;
 };
 
 struct LaneCounters {

@@ -135,6 +135,17 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback"
 
 
+def measured_traffic(workload, layout, exact, spp):
+    """DRAM bytes per k_volpath launch from the committed ncu capture of this configuration (or None)."""
+    p = os.path.join(ROOT, "profiles", "r1_volpath_dram_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    for e in json.load(open(p))["entries"]:
+        if (e["workload"], e["layout"], e["exact_math"], e["spp_per_launch"]) == (workload, layout, int(exact), spp):
+            return e["dram_read_bytes"] + e["dram_write_bytes"], e["capture"]
+    return None, None
+
+
 def run_reference_arm(args, w, density):
     """--impl reference: time the CPU path with all host threads; each step = a bounded crop."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -296,6 +307,7 @@ def main():
         fetch_bytes = 32 if args.layout != "octet16" else 16
         alg_bytes = (cam_f + sh_f) * fetch_bytes + segs * 4
         achieved = alg_bytes / max(kern_max, 1e-9) / 1e9 / max(world, 1)  # per-GPU GB/s of the dominant kernel
+        traffic, traffic_src = measured_traffic(args.workload, args.layout, args.exact, spp)
         out = dict(base)
         out.update({"impl": "avr_b200", "value": value, "ms_per_step": wall_max / args.steps * 1e3,
                     "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 4 * 471 * 4,
@@ -303,7 +315,9 @@ def main():
                     "gpu_launches": args.steps,
                     "roofline": {"bound": "hbm", "kernel": "k_volpath", "achieved": achieved, "peak": peaks["hbm_gbs"],
                                  "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                                 "traffic": None, "fetches_per_step": (cam_f + sh_f) / args.steps,
+                                 "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write)",
+                                 "traffic_capture": traffic_src, "algorithmic_bytes": alg_bytes / args.steps / max(world, 1),
+                                 "fetches_per_step": (cam_f + sh_f) / args.steps,
                                  "segments_per_step": segs / args.steps, "bytes_per_fetch": fetch_bytes,
                                  "kernel_ms_per_step": kern_max / args.steps * 1e3},
                     "clocks": clk, "medium_build_s": build_s, "medium_bytes": med.bytes()})

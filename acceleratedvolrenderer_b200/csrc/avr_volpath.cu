@@ -368,9 +368,12 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 #endif
 template <typename TR>
 struct KernelCfg {
-    static constexpr int kThreads = AVR_CTA_THREADS;
+    // achromatic scalar grids: AVR_MIN_BLOCKS CTAs of 256 threads (<= 128 registers); the chromatic and general
+    // kernels need 144..181 registers: one CTA per SM with as many warps as the register file holds
+    static constexpr bool kLean = TR::NCH == 1 && !TR::GENERAL;
+    static constexpr int kThreads = kLean ? AVR_CTA_THREADS : 384;  // 3 warps per scheduler: 168-register cap
     static constexpr int kMinBlocks =
-        (TR::NCH == 1 && !TR::GENERAL && AVR_MIN_BLOCKS * 256 >= AVR_CTA_THREADS) ? AVR_MIN_BLOCKS * 256 / AVR_CTA_THREADS : 1;
+        (kLean && AVR_MIN_BLOCKS * 256 >= AVR_CTA_THREADS) ? AVR_MIN_BLOCKS * 256 / AVR_CTA_THREADS : 1;
 };
 
 struct LaneCounters {

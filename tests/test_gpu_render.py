@@ -80,6 +80,49 @@ def test_converged_image_matches_oracle(ctx, orc, exact, layout):
     assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
 
 
+def general_media(kind):
+    """Small RGB-grid / emissive scenes of the class SURVEY.md 8(d) C5 sweeps (general kernel: 4 channels)."""
+    from acceleratedvolrenderer_b200._abi import RGBGridDesc
+    dens, (gd, rd) = small_scene(width=32, height=24, spp=32, max_depth=6, g=0.2)
+    if kind == "rgbgrid":
+        rng = np.random.default_rng(11)
+        desc = RGBGridDesc(sigma_a=scenes.rgb_voxels(dens * 0.6, rng), sigma_s=scenes.rgb_voxels(dens * 12, rng),
+                           render_from_medium=gd.m, g=0.2)
+        return "rgbgrid", desc, rd
+    desc = GridDesc(dens, gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=0.2, temperature=dens * 2500 + 200,
+                    lescale=dens * 0.5, le_norm=1.0)
+    return "uniformgrid", desc, rd
+
+
+@pytest.mark.parametrize("kind", ["rgbgrid", "emissive"])
+def test_general_media_render_matches_oracle(ctx, orc, kind):
+    """RGB grids and emissive grids through k_volpath's general kernel: per-sample radiance under the
+    exact arithmetic, and the converged image under fast math within the Monte Carlo noise floor."""
+    name, desc, rd = general_media(kind)
+    mo = orc.medium_rgbgrid(desc) if name == "rgbgrid" else orc.medium_uniformgrid(desc)
+    md = ctx.create_medium(name, desc) if name == "rgbgrid" else ctx.create_medium(name, desc, layout="dense")
+    rs = rd.with_(spp=4)
+    want, wstats = mo.render_samples(rs)
+    got, gstats = ctx.render_volpath_samples(md, rs)
+    L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+    scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+    ok = np.abs(L - Lw).max(axis=1) <= 1e-3 * scale
+    assert ok.mean() >= 0.99, f"{kind}: {ok.mean():.4f} of samples match"
+    assert Lw.sum() > 0 and gstats["camera_rays"] == wstats[0]
+    ref_a, _ = mo.render(rd, threads=8)
+    ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
+    img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
+    noise = rel_mse(img_a, img_b)
+    for exact in (1, 0):
+        film, _ = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2))
+        assert np.all(film[..., 3] == rd.spp)
+        img = ctx.film_resolve(rd, film)
+        err = rel_mse(img, img_a)
+        assert err <= 3 * noise + 1e-6, (kind, exact, err, noise)
+        assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
+    md.close(); mo.close()
+
+
 def test_sample_sharding_is_additive(ctx):
     """Multi-GPU contract: rendering sample shards / rank partitions into one film equals one render."""
     dens, (gd, rd) = small_scene(width=24, height=20, spp=8)

@@ -28,17 +28,18 @@ namespace avr {
 
 constexpr int kBlock = 128;
 
-// Lane states.  The first six double as the op a lane waits for (see the scheduler in k_volpath).
+// Lane states.  Values >= ST_WALK are the tracking states (the path sits in Q_TRACK or in a lane of the
+// tracking loop); the others name the event op the path waits for.
 enum {
     ST_DEAD = 0,           // R: needs a new path (a finished sample may be pending)
     ST_SETUP = 1,          // S: pending ray in fe.o / fe.d
-    ST_WALK = 2,           // A: between majorant segments, DDA step next
-    ST_COLLIDE = 3,        // B: inside a non-empty majorant segment, tentative collision next
-    ST_EV_SCATTER = 4,     // E1: real scattering event
-    ST_EV_SHADOW_END = 5,  // E2: shadow ray finished
-    kNumOps = 6,
-    ST_EV_PATH_END = 6,    // transient: becomes ST_DEAD + pending at the end of the trip
-    ST_RETIRED = 7         // no work left
+    ST_EV_SCATTER = 2,     // E1: real scattering event
+    ST_EV_SHADOW_END = 3,  // E2: shadow ray finished
+    ST_EV_PATH_END = 4,    // transient: becomes ST_DEAD + pending at the end of the trip
+    ST_RETIRED = 5,        // no work left
+    ST_WALK = 8,           // A: between majorant segments, DDA step next
+    ST_SAMPLE = 9,         // A': inside a non-empty majorant segment, next tentative-collision distance to draw
+    ST_COLLIDE = 10        // B: tentative collision at cur_tMin, medium lookup + event next
 };
 
 // film / sample write of a finished path: cpu/integrators.cpp:272-297, film.h:95-100,239-255
@@ -392,7 +393,7 @@ AVR_DEV void requeue(const PoolView &pv, unsigned lane, bool have, int slot, Pat
     if (have && ln.state != ST_RETIRED)
         SlotIO<TR>::template store<GROUPS>(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln, lc, pending);
     __threadfence_block();  // slot contents before the queue cells that publish them
-    unsigned m_tr = __ballot_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_COLLIDE));
+    unsigned m_tr = __ballot_sync(0xffffffffu, have && ln.state >= ST_WALK);
     unsigned m_sc = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SCATTER);
     unsigned m_se = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SHADOW_END);
     unsigned m_dd = __ballot_sync(0xffffffffu, have && ln.state == ST_DEAD);
@@ -610,7 +611,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
     ln.state = ST_DEAD;
     while (true) {
         // ---- park finished paths and refill from Q_TRACK, both in batches of >= refill_lanes -------
-        bool fin = have && ln.state >= ST_EV_SCATTER;
+        bool fin = have && ln.state < ST_WALK;
         unsigned idle = __ballot_sync(0xffffffffu, !have || fin);
         if (__popc(idle) >= rp.refill_lanes || idle == 0xffffffffu) {
             if (__any_sync(0xffffffffu, fin)) {
@@ -649,9 +650,11 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             }
         }
 
-        // ---- A. DDA steps to the next majorant segment with sigma_maj[0] != 0 ----------------------
+        // ---- A. DDA steps to the next majorant segment with sigma_maj[0] != 0, each followed by A': the
+        //      draw of the next tentative-collision distance inside the current segment.  Leaving a
+        //      segment without a collision costs no B op -----------------------------------------------
         for (int k = 0; k < rp.walk_steps; ++k) {
-            if (!__any_sync(0xffffffffu, have && ln.state == ST_WALK)) break;
+            if (!__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
             if (have && ln.state == ST_WALK) {
                 float a, b;
                 int vox;
@@ -674,24 +677,35 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                         ln.sigma_maj = sm;
                         ln.cur_tMin = a;
                         ln.seg_tMax = b;
-                        ln.state = ST_COLLIDE;
+                        ln.state = ST_SAMPLE;
                     }
                 }
             }
+            if (have && ln.state == ST_SAMPLE) {
+                // media.h:779-803: t = tMin + SampleExponential(u, sigma_maj[0]); u = rng.Uniform();
+                // T_maj *= FastExp(-(t - tMin) sigma_maj) at a collision, FastExp(-(tMax - tMin) sigma_maj) at the exit
+                float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
+                ln.u = ln.trng.uniform();
+                bool hit = t < ln.seg_tMax;
+                float dt = (hit ? t : ln.seg_tMax) - ln.cur_tMin;
+                if (!hit && isinf(dt)) dt = kFltMax;
+                ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
+                if (hit) ln.cur_tMin = t;
+                ln.state = hit ? ST_COLLIDE : ST_WALK;
+            }
         }
 
-        // ---- B. one tentative collision along the current segment: runs when enough lanes wait for it
-        //      (it costs ~5 DDA steps), or when no lane is left walking ---------------------------------
+        // ---- B. the tentative collision at t = cur_tMin (medium lookup, event, weight update): runs when
+        //      enough lanes wait for it, or when no lane is left walking -------------------------------
         {
             unsigned mc = __ballot_sync(0xffffffffu, have && ln.state == ST_COLLIDE);
             if (mc == 0) continue;
             if (__popc(mc) < rp.collide_min && __any_sync(0xffffffffu, have && ln.state == ST_WALK)) continue;
         }
         if (have && ln.state == ST_COLLIDE) {
-            float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
-            ln.u = ln.trng.uniform();
-            if (t < ln.seg_tMax) {
-                Spec<N> T_maj = ln.T_maj * exp_neg<EX>(t - ln.cur_tMin, ln.sigma_maj);
+            {
+                const float t = ln.cur_tMin;
+                Spec<N> T_maj = ln.T_maj;
                 PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
                 Spec<N> sigma_maj = ln.sigma_maj;
                 Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
@@ -766,13 +780,8 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 }
                 if (cont) {
                     ln.T_maj = sconst<N>(1.f);
-                    ln.cur_tMin = t;
+                    ln.state = ST_SAMPLE;  // tMin = t already
                 }
-            } else {
-                float dt = ln.seg_tMax - ln.cur_tMin;
-                if (isinf(dt)) dt = kFltMax;
-                ln.T_maj = ln.T_maj * exp_neg<EX>(dt, ln.sigma_maj);
-                ln.state = ST_WALK;
             }
         }
 

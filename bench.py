@@ -187,7 +187,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="avr_b200")
     ap.add_argument("--workload", default=os.environ.get("AVR_BENCH_WORKLOAD", "disney-cloud-standin-720p"))
-    ap.add_argument("--spp-per-step", type=int, default=4)
+    ap.add_argument("--spp-per-step", type=int, default=16)
     ap.add_argument("--layout", default="octet32")
     ap.add_argument("--exact", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -183,7 +183,7 @@ def run_reference_arm(args, w, density):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="avr_b200")
     ap.add_argument("--workload", default=os.environ.get("AVR_BENCH_WORKLOAD", "disney-cloud-standin-720p"))

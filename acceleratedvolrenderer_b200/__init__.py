@@ -4,9 +4,9 @@ The product is libavr_b200.so (hand-written sm_100a CUDA behind the C ABI of inc
 package is the thin Python host mirror used by tests and bench: it loads the library with ctypes
 and fails loudly if it is missing — there is no CPU fallback anywhere in the package.
 """
-from ._abi import NSPEC, GridDesc, RGBGridDesc, RenderDesc  # noqa: F401
+from ._abi import NSPEC, GridDesc, NanoVDBDesc, NanoVDBGrid, RGBGridDesc, RenderDesc  # noqa: F401
 
-__all__ = ["NSPEC", "GridDesc", "RGBGridDesc", "RenderDesc", "load_library", "Context"]
+__all__ = ["NSPEC", "GridDesc", "NanoVDBDesc", "NanoVDBGrid", "RGBGridDesc", "RenderDesc", "load_library", "Context"]
 
 
 def load_library():

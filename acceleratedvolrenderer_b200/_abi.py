@@ -42,6 +42,26 @@ class avr_rgbgrid_desc(C.Structure):
     ]
 
 
+class avr_nanovdb_grid(C.Structure):
+    _fields_ = [
+        ("values", f32p),
+        ("index_min", C.c_int32 * 3), ("dims", C.c_int32 * 3),
+        ("inv_mat", C.c_float * 9), ("vec", C.c_float * 3),
+        ("world_bbox", C.c_double * 6),
+    ]
+
+
+class avr_nanovdb_desc(C.Structure):
+    _fields_ = [
+        ("density", avr_nanovdb_grid), ("temperature", avr_nanovdb_grid),
+        ("render_from_medium", C.c_float * 16), ("medium_from_render", C.c_float * 16),
+        ("sigma_a", f32p), ("sigma_s", f32p),
+        ("sigma_scale", C.c_float), ("g", C.c_float), ("le_scale", C.c_float),
+        ("temperature_offset", C.c_float), ("temperature_scale", C.c_float),
+        ("majorant_res", C.c_int32 * 3),
+    ]
+
+
 class avr_render_desc(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32),
@@ -162,6 +182,87 @@ class RGBGridDesc:
             c.majorant_res[i] = self.majorant_res[i]
         self.c = c
         self.p0 = np.asarray(p0, dtype=np.float32); self.p1 = np.asarray(p1, dtype=np.float32)
+
+
+class NanoVDBGrid:
+    """One flattened nanovdb::FloatGrid (see avr_nanovdb_grid): values [dz, dy, dx] over the inclusive
+    index bounding box, the float inverse map (mInvMatF, mVecF) and the double world bounding box."""
+
+    def __init__(self, values, index_min, inv_mat, vec, world_bbox, source=None):
+        self.values = _f32(values)
+        assert self.values.ndim == 3
+        self.index_min = np.asarray(index_min, dtype=np.int32)
+        self.dims = np.asarray(self.values.shape[::-1], dtype=np.int32)
+        self.inv_mat = _f32(inv_mat).ravel()
+        self.vec = _f32(vec).ravel()
+        self.world_bbox = np.asarray(world_bbox, dtype=np.float64).ravel()
+        self.source = source  # (dense, origin_ijk, voxel_size, origin_world): lets the reference probe rebuild it
+
+    def fill(self, c):
+        c.values = _ptr(self.values)
+        for i in range(3):
+            c.index_min[i] = int(self.index_min[i]); c.dims[i] = int(self.dims[i]); c.vec[i] = float(self.vec[i])
+        for i in range(9):
+            c.inv_mat[i] = float(self.inv_mat[i])
+        for i in range(6):
+            c.world_bbox[i] = float(self.world_bbox[i])
+
+    @staticmethod
+    def from_dense(dense, origin_ijk=(0, 0, 0), voxel_size=1.0, origin_world=(0.0, 0.0, 0.0)):
+        """Host-side equivalent of nanovdb::GridBuilder<float>(0)(dense over a box).getHandle(voxel_size,
+        origin): the index box is that of the non-background voxels (GridBuilder.h:259-271), the map a
+        uniform scale + translation (GridBuilder.h:535-560, Map::set NanoVDB.h:2045-2063), the world box
+        map(min) .. map(max+1) (GridStats.h:551-563).  voxel_size must be a power of two so that the
+        fma-based applyMap is reproduced exactly by a multiply and an add."""
+        dense = _f32(dense)
+        m, e = np.frexp(voxel_size)
+        assert m == 0.5, "voxel_size must be a power of two"
+        nzv = np.argwhere(dense != 0)
+        assert len(nzv), "empty grid"
+        lo = nzv.min(axis=0); hi = nzv.max(axis=0)           # (z, y, x)
+        vals = dense[lo[0]:hi[0] + 1, lo[1]:hi[1] + 1, lo[2]:hi[2] + 1]
+        imin = np.asarray(origin_ijk, dtype=np.int64) + lo[::-1]
+        imax1 = np.asarray(origin_ijk, dtype=np.int64) + hi[::-1] + 1
+        ow = np.asarray(origin_world, dtype=np.float64)
+        wb = np.r_[imin.astype(np.float64) * voxel_size + ow, imax1.astype(np.float64) * voxel_size + ow]
+        inv = np.zeros(9, dtype=np.float32)
+        inv[[0, 4, 8]] = np.float32(1.0 / voxel_size)
+        return NanoVDBGrid(vals, imin, inv, ow.astype(np.float32), wb,
+                           source=(dense, tuple(int(v) for v in origin_ijk), float(voxel_size), tuple(float(v) for v in ow)))
+
+
+class NanoVDBDesc:
+    """Parameters of MakeNamedMedium "nanovdb" (reference media.cpp:628-665) with the grids flattened."""
+
+    def __init__(self, density: NanoVDBGrid, sigma_a=1.0, sigma_s=1.0, *, temperature: NanoVDBGrid = None,
+                 render_from_medium=None, medium_from_render=None, scale=1.0, g=0.0, le_scale=1.0,
+                 temperature_offset=0.0, temperature_scale=1.0, majorant_res=(64, 64, 64)):
+        self.density, self.temperature = density, temperature
+        self.sigma_a = _f32(np.broadcast_to(sigma_a, (NSPEC,)))
+        self.sigma_s = _f32(np.broadcast_to(sigma_s, (NSPEC,)))
+        self.majorant_res = tuple(int(r) for r in majorant_res)
+        m = IDENTITY16 if render_from_medium is None else _f32(render_from_medium).ravel()
+        if medium_from_render is None:
+            mi = np.linalg.inv(np.asarray(m, dtype=np.float64).reshape(4, 4)).astype(np.float32).ravel()
+        else:
+            mi = _f32(medium_from_render).ravel()
+        self.m, self.minv = m, mi
+        c = avr_nanovdb_desc()
+        density.fill(c.density)
+        if temperature is not None:
+            temperature.fill(c.temperature)
+        _set_arr(c.render_from_medium, m); _set_arr(c.medium_from_render, mi)
+        c.sigma_a = _ptr(self.sigma_a); c.sigma_s = _ptr(self.sigma_s)
+        c.sigma_scale = scale; c.g = g; c.le_scale = le_scale
+        c.temperature_offset = temperature_offset; c.temperature_scale = temperature_scale
+        for i in range(3):
+            c.majorant_res[i] = self.majorant_res[i]
+        self.c = c
+        wb = density.world_bbox.astype(np.float32)
+        if temperature is not None:
+            wt = temperature.world_bbox.astype(np.float32)
+            wb = np.r_[np.minimum(wb[:3], wt[:3]), np.maximum(wb[3:], wt[3:])]
+        self.p0, self.p1 = wb[:3].copy(), wb[3:].copy()   # NanoVDBMedium::bounds, media.cpp:536-551
 
 
 class RenderDesc:

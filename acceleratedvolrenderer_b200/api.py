@@ -1,6 +1,6 @@
 """Host-side mirror of the reference's medium / integrator interface over the C ABI (include/avr.h).
 
-Names follow the reference: `Context.create_medium("uniformgrid" | "rgbgrid", ...)` is
+Names follow the reference: `Context.create_medium("uniformgrid" | "rgbgrid" | "nanovdb", ...)` is
 Medium::Create (media.cpp:667-689); `Medium.sample_point / sample_ray_segments / sample_t_maj`
 are Medium::SamplePoint / SampleRay+DDAMajorantIterator::Next / SampleT_maj (media.h);
 `Context.render("volpath" | "graph", ...)` is Integrator::Create(name)->Render()
@@ -13,8 +13,8 @@ import os
 
 import numpy as np
 
-from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, RenderDesc, RGBGridDesc, avr_grid_desc, avr_render_desc,
-                   avr_render_stats, avr_rgbgrid_desc)
+from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_grid_desc,
+                   avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
 
@@ -32,8 +32,8 @@ _lib = None
 # every symbol include/avr.h declares (tests check that the .so exports all of them)
 ABI_SYMBOLS = [
     "avr_ctx_create", "avr_ctx_destroy", "avr_last_error", "avr_version",
-    "avr_medium_create_uniformgrid", "avr_medium_create_rgbgrid", "avr_medium_destroy", "avr_medium_is_emissive",
-    "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
+    "avr_medium_create_uniformgrid", "avr_medium_create_rgbgrid", "avr_medium_create_nanovdb", "avr_medium_destroy",
+    "avr_medium_is_emissive", "avr_medium_bounds", "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
     "avr_graph_create", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
@@ -118,6 +118,10 @@ class Context:
         elif name == "rgbgrid":
             assert isinstance(desc, RGBGridDesc)
             self.check(self.lib.avr_medium_create_rgbgrid(self.h, C.byref(desc.c), C.byref(h)))
+        elif name == "nanovdb":
+            assert isinstance(desc, NanoVDBDesc)
+            self.check(self.lib.avr_medium_create_nanovdb(self.h, C.byref(desc.c), C.c_int(LAYOUTS[layout]),
+                                                          C.byref(h)))
         else:
             # the reference: ErrorExit(loc, "%s: medium unknown.", name)
             raise AvrError(1, f"{name}: medium unknown.")
@@ -192,6 +196,11 @@ class Medium:
 
     def bytes(self):
         return int(self.lib.avr_medium_bytes(self.h))
+
+    def bounds(self):  # Medium bounds in medium space (NanoVDBMedium::GetBounds)
+        out = np.zeros(6, dtype=np.float32)
+        self.ctx.check(self.lib.avr_medium_bounds(self.h, _p(out)))
+        return out
 
     def majorants(self):
         mr = self.desc.majorant_res

@@ -32,6 +32,7 @@ struct avr_medium {
     int64_t bytes = 0;
     float *d_maj = nullptr;
     int mres[3] = {16, 16, 16};
+    int reports_emissive = -1;  // IsEmissive() when it differs from view.emissive (kernel selection)
 };
 
 struct avr_graph {

@@ -134,6 +134,52 @@ __global__ void k_build_majorants(MediumView mv, float *out) {
     if (threadIdx.x == 0) out[mx + r[0] * (my + r[1] * mz)] = res;
 }
 
+// NanoVDBMedium majorants, media.cpp:560-616: per majorant cell, Bounds3::Lerp of the cell corners ->
+// worldToIndexF(Vec3R) (subtraction and innermost product in double, fmaf arguments narrowed to float:
+// NanoVDB.h:1409-1414 instantiated for Vec3<double>) -> int(i0 - 1) .. int(i1 + 1) clipped to the index
+// box -> max of the voxel values, starting from 0.
+__global__ void k_build_majorants_nvdb(MediumView mv, float *out) {
+    __shared__ float sm[32];
+    int idx[3] = {(int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z};
+    int n[3] = {mv.nx, mv.ny, mv.nz};
+    double w0[3], w1[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float t0 = float(idx[i]) / mv.mres[i], t1 = float(idx[i] + 1) / mv.mres[i];
+        w0[i] = double((1 - t0) * mv.bmin[i] + t0 * mv.bmax[i]);  // pbrt::Lerp(t, pMin, pMax), float
+        w1[i] = double((1 - t1) * mv.bmin[i] + t1 * mv.bmax[i]);
+    }
+    auto to_index = [&](const double w[3], int r) -> double {
+        double x = w[0] - double(mv.nv_vec[0]), y = w[1] - double(mv.nv_vec[1]), z = w[2] - double(mv.nv_vec[2]);
+        float inner = float(z * double(mv.nv_inv[3 * r + 2]));
+        return double(__fmaf_rn(float(x), mv.nv_inv[3 * r], __fmaf_rn(float(y), mv.nv_inv[3 * r + 1], inner)));
+    };
+    int lo[3], hi[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        lo[i] = max(__double2int_rz(to_index(w0, i) - 1.0), mv.nv_imin[i]) - mv.nv_imin[i];
+        hi[i] = min(__double2int_rz(to_index(w1, i) + 1.0), mv.nv_imin[i] + n[i] - 1) - mv.nv_imin[i];
+    }
+    float m = 0.f;
+    int ex = hi[0] - lo[0] + 1, ey = hi[1] - lo[1] + 1, ez = hi[2] - lo[2] + 1;
+    if (ex > 0 && ey > 0 && ez > 0) {
+        int tot = ex * ey * ez;
+        for (int i = threadIdx.x; i < tot; i += blockDim.x) {
+            int x = lo[0] + i % ex, y = lo[1] + (i / ex) % ey, z = lo[2] + i / (ex * ey);
+            m = fmaxf(m, mv.dense[(size_t(z) * mv.ny + y) * mv.nx + x]);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        float r2 = sm[0];
+        for (int w = 1; w < nw; ++w) r2 = fmaxf(r2, sm[w]);
+        out[idx[0] + mv.mres[0] * (idx[1] + mv.mres[1] * idx[2])] = r2;
+    }
+}
+
 // Octet packing: one thread per interpolation cell (cx,cy,cz) in [0,nx]x[0,ny]x[0,nz]
 // (cell c covers taps c-1 and c); bricks beyond the lattice edge are zero-filled by the memset.
 template <bool HALF>
@@ -194,13 +240,27 @@ void fold_grid_from_render(MediumView &v) {
     }
 }
 
+// KIND_NVDB: s = invMat * (minv . p - vec) - index_min  (sample space = index space relative to the box)
+void fold_index_from_render(MediumView &v) {
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) {
+            double a = 0;
+            for (int k = 0; k < 3; ++k) a += double(v.nv_inv[3 * i + k]) * double(v.minv[4 * k + j]);
+            v.gfr[4 * i + j] = float(a);
+        }
+        double t = 0;
+        for (int k = 0; k < 3; ++k) t += double(v.nv_inv[3 * i + k]) * (double(v.minv[4 * k + 3]) - double(v.nv_vec[k]));
+        v.gfr[4 * i + 3] = float(t - double(v.nv_imin[i]));
+    }
+}
+
 avr_status finish_common(avr_medium *m, const float p0[3], const float p1[3], const float rfm[16],
-                         const float mfr[16], const int32_t mres_in[3]) {
+                         const float mfr[16], const int32_t mres_in[3], int mres_default = 16) {
     MediumView &v = m->view;
     for (int i = 0; i < 3; ++i) {
         v.bmin[i] = p0[i];
         v.bmax[i] = p1[i];
-        m->mres[i] = v.mres[i] = mres_in[i] > 0 ? mres_in[i] : 16;
+        m->mres[i] = v.mres[i] = mres_in[i] > 0 ? mres_in[i] : mres_default;
     }
     if (v.mres[0] > 1023 || v.mres[1] > 1023 || v.mres[2] > 1023)
         return set_err(m->ctx, AVR_ERR_UNSUPPORTED, "majorant grid resolution > 1023 per axis");
@@ -212,7 +272,7 @@ avr_status finish_common(avr_medium *m, const float p0[3], const float p1[3], co
     }
     if (!affine_rows(rfm, v.m) || !affine_rows(mfr, v.minv))
         return set_err(m->ctx, AVR_ERR_UNSUPPORTED, "medium transform must be affine (last row 0 0 0 1)");
-    fold_grid_from_render(v);
+    if (v.kind == KIND_NVDB) fold_index_from_render(v); else fold_grid_from_render(v);
     size_t nm = size_t(v.mres[0]) * v.mres[1] * v.mres[2];
     AVR_CUDA(m->ctx, cudaMalloc(&m->d_maj, nm * sizeof(float)));
     m->allocs.push_back(m->d_maj);
@@ -244,6 +304,33 @@ avr_status finish_majorants(avr_medium *m) {
         v.nz_lo[i] = lo[i];
         v.nz_hi[i] = hi[i];
     }
+    return AVR_OK;
+}
+
+// Octet store of the scalar density grid (layouts 1, 2): cell c holds taps c-1, c on every axis.
+avr_status build_octets(avr_medium *m, int layout) {
+    if (layout == LAYOUT_DENSE_F32) return AVR_OK;
+    avr_ctx *ctx = m->ctx;
+    MediumView &v = m->view;
+    v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
+    size_t cells = size_t(v.nbx) * v.nby * v.nbz * 64;
+    if (cells >= (size_t(1) << 32)) return set_err(ctx, AVR_ERR_UNSUPPORTED, "octet layout: 2^32 or more cells");
+    size_t bytes = cells * (layout == LAYOUT_OCTET_F32 ? 32 : 16);
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return set_cuda_err(ctx, e, "cudaMalloc(octets)");
+    m->allocs.push_back(p);
+    m->bytes += int64_t(bytes);
+    AVR_CUDA(ctx, cudaMemsetAsync(p, 0, bytes, ctx->stream));
+    int blocks = ctx->sm_count * 8;
+    if (layout == LAYOUT_OCTET_F32) {
+        v.oct32 = (const float4 *)p;
+        k_pack_octets<false><<<blocks, 256, 0, ctx->stream>>>(v, (float4 *)p, nullptr);
+    } else {
+        v.oct16 = (const uint4 *)p;
+        k_pack_octets<true><<<blocks, 256, 0, ctx->stream>>>(v, nullptr, (uint4 *)p);
+    }
+    AVR_CUDA(ctx, cudaGetLastError());
     return AVR_OK;
 }
 
@@ -315,29 +402,81 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     TRY(finish_common(m, d->p0, d->p1, d->render_from_medium, d->medium_from_render, d->majorant_res));
     k_build_majorants<false><<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, m->d_maj);
     AVR_CUDA(ctx, cudaGetLastError());
-    if (layout != LAYOUT_DENSE_F32) {
-        v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
-        size_t cells = size_t(v.nbx) * v.nby * v.nbz * 64;
-        if (cells >= (size_t(1) << 32)) { free_medium(m); return set_err(ctx, AVR_ERR_UNSUPPORTED, "octet layout: 2^32 or more cells"); }
-        size_t bytes = cells * (layout == LAYOUT_OCTET_F32 ? 32 : 16);
-        void *p = nullptr;
-        cudaError_t e = cudaMalloc(&p, bytes);
-        if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "cudaMalloc(octets)"); }
-        m->allocs.push_back(p);
-        m->bytes += int64_t(bytes);
-        AVR_CUDA(ctx, cudaMemsetAsync(p, 0, bytes, ctx->stream));
-        int blocks = ctx->sm_count * 8;
-        if (layout == LAYOUT_OCTET_F32) {
-            v.oct32 = (const float4 *)p;
-            k_pack_octets<false><<<blocks, 256, 0, ctx->stream>>>(v, (float4 *)p, nullptr);
-        } else {
-            v.oct16 = (const uint4 *)p;
-            k_pack_octets<true><<<blocks, 256, 0, ctx->stream>>>(v, nullptr, (uint4 *)p);
-        }
-        AVR_CUDA(ctx, cudaGetLastError());
-    }
+    TRY(build_octets(m, layout));
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "medium build"); }
+    TRY(finish_majorants(m));
+    *out = m;
+    return AVR_OK;
+}
+
+extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_desc *d, int layout, avr_medium **out) {
+    if (!ctx || !d || !out) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_medium_create_nanovdb: NULL argument");
+    *out = nullptr;
+    // NanoVDBMedium::Create ErrorExit()s when the density grid is missing (media.cpp:636-637)
+    if (!d->density.values) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: didn't find \"density\" grid.");
+    for (int i = 0; i < 3; ++i)
+        if (d->density.dims[i] < 1 || (d->temperature.values && d->temperature.dims[i] < 1))
+            return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: empty index bounding box");
+    if (!d->sigma_a || !d->sigma_s) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb medium: sigma_a / sigma_s tables missing");
+    if (layout < 0 || layout > 2) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    avr_medium *m = new avr_medium();
+    m->ctx = ctx;
+    MediumView &v = m->view;
+    v.kind = KIND_NVDB;
+    v.layout = layout;
+    const avr_nanovdb_grid &dg = d->density, &tg = d->temperature;
+    v.nx = dg.dims[0]; v.ny = dg.dims[1]; v.nz = dg.dims[2];
+    avr_status st;
+    TRY(upload(m, dg.values, size_t(v.nx) * v.ny * v.nz, &v.dense));
+    float p0[3], p1[3];
+    for (int i = 0; i < 3; ++i) {
+        v.nv_imin[i] = dg.index_min[i];
+        v.nv_vec[i] = dg.vec[i];
+        p0[i] = float(dg.world_bbox[i]);  // Bounds3f(Point3f(bbox.min()...)), media.cpp:536-538
+        p1[i] = float(dg.world_bbox[3 + i]);
+    }
+    for (int i = 0; i < 9; ++i) v.nv_inv[i] = dg.inv_mat[i];
+    v.has_temperature = tg.values != nullptr;
+    if (v.has_temperature) {
+        TRY(upload(m, tg.values, size_t(tg.dims[0]) * tg.dims[1] * tg.dims[2], &v.temperature));
+        for (int i = 0; i < 3; ++i) {
+            v.nv_tdim[i] = tg.dims[i];
+            v.nv_timin[i] = tg.index_min[i];
+            v.nv_tvec[i] = tg.vec[i];
+            p0[i] = std::fmin(p0[i], float(tg.world_bbox[i]));  // Union, media.cpp:546-550
+            p1[i] = std::fmax(p1[i], float(tg.world_bbox[3 + i]));
+        }
+        for (int i = 0; i < 9; ++i) v.nv_tinv[i] = tg.inv_mat[i];
+    }
+    std::vector<float> sa(d->sigma_a, d->sigma_a + kNSpec), ss(d->sigma_s, d->sigma_s + kNSpec), le(kNSpec, 0.f);
+    bool achro = true;
+    for (int i = 0; i < kNSpec; ++i) {
+        sa[i] *= d->sigma_scale;
+        ss[i] *= d->sigma_scale;
+        if (sa[i] != sa[0] || ss[i] != ss[0]) achro = false;
+    }
+    v.achromatic = achro ? 1 : 0;
+    // IsEmissive, media.h:621.  A temperature grid with Lescale <= 0 still goes through Le() in the
+    // reference; the general kernels are used whenever the grid is present.
+    v.emissive = v.has_temperature ? 1 : 0;
+    m->reports_emissive = (v.has_temperature && d->le_scale > 0) ? 1 : 0;
+    TRY(upload(m, sa.data(), (size_t)kNSpec, &v.sigma_a_spec));
+    TRY(upload(m, ss.data(), (size_t)kNSpec, &v.sigma_s_spec));
+    TRY(upload(m, le.data(), (size_t)kNSpec, &v.le_spec));
+    AVR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    v.g = d->g;
+    v.le_scale = d->le_scale;
+    v.temp_offset = d->temperature_offset;
+    v.temp_scale = d->temperature_scale;
+    v.sigma_scale = 1.f;
+    TRY(finish_common(m, p0, p1, d->render_from_medium, d->medium_from_render, d->majorant_res, 64));
+    k_build_majorants_nvdb<<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, m->d_maj);
+    AVR_CUDA(ctx, cudaGetLastError());
+    TRY(build_octets(m, layout));
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "nanovdb medium build"); }
     TRY(finish_majorants(m));
     *out = m;
     return AVR_OK;
@@ -384,7 +523,14 @@ extern "C" avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_
 }
 
 extern "C" void avr_medium_destroy(avr_medium *m) { free_medium(m); }
-extern "C" int avr_medium_is_emissive(const avr_medium *m) { return m ? m->view.emissive : 0; }
+extern "C" int avr_medium_is_emissive(const avr_medium *m) {
+    return m ? (m->reports_emissive >= 0 ? m->reports_emissive : m->view.emissive) : 0;
+}
+extern "C" avr_status avr_medium_bounds(const avr_medium *m, float out[6]) {
+    if (!m || !out) return set_err(m ? m->ctx : nullptr, AVR_ERR_BAD_ARG, "avr_medium_bounds: NULL argument");
+    for (int i = 0; i < 3; ++i) { out[i] = m->view.bmin[i]; out[3 + i] = m->view.bmax[i]; }
+    return AVR_OK;
+}
 extern "C" int64_t avr_medium_bytes(const avr_medium *m) { return m ? m->bytes : 0; }
 
 extern "C" avr_status avr_medium_majorants(avr_medium *m, float *out, int32_t res[3]) {

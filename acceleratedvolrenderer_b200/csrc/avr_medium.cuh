@@ -7,7 +7,7 @@
 namespace avr {
 
 enum { LAYOUT_DENSE_F32 = 0, LAYOUT_OCTET_F32 = 1, LAYOUT_OCTET_F16 = 2 };
-enum { KIND_GRID = 0, KIND_RGB = 1 };
+enum { KIND_GRID = 0, KIND_RGB = 1, KIND_NVDB = 2 };
 
 // Plain-old-data view handed to kernels by value (lives in the kernel parameter bank).
 struct MediumView {
@@ -38,6 +38,12 @@ struct MediumView {
     float gfr[12];
     float cell[3], inv_cell[3];  // majorant cell size in medium space and its reciprocal
     int nz_lo[3], nz_hi[3];      // bounding box (inclusive voxel range) of the majorant cells != 0
+    // KIND_NVDB (NanoVDBMedium): `dense`/octets hold the density grid flattened over its index box
+    // (nx,ny,nz = box dims); index-space sampling, see nv_sample.  Temperature grid: own box and map.
+    int nv_imin[3];
+    float nv_inv[9], nv_vec[3];  // Map::mInvMatF / mVecF of the density grid
+    int nv_tdim[3], nv_timin[3];
+    float nv_tinv[9], nv_tvec[3];
 };
 
 // ---- Transform::ApplyInverse(Point3f) + Bounds3::Offset: render point -> grid [0,1]^3 ------------
@@ -146,6 +152,63 @@ AVR_DEV float lookup_density_rt(const MediumView &mv, V3 p) {
     return lookup_dense_s<EXACT>(mv.dense, mv.nx, mv.ny, mv.nz, sx, sy, sz);
 }
 
+// ---- NanoVDBMedium sampling (media.h:624-638): worldToIndexF + SampleFromVoxels<Tree,1,false> ------
+// NanoVDB.h:2028-2031 applyInverseMapF, :1409-1414 matMult (fmaf chain, innermost term a plain product)
+AVR_DEV V3 nv_world_to_index(const float *inv, const float *vec, V3 p) {
+    float x = p.x - vec[0], y = p.y - vec[1], z = p.z - vec[2];
+    return v3(__fmaf_rn(x, inv[0], __fmaf_rn(y, inv[1], __fmul_rn(z, inv[2]))),
+              __fmaf_rn(x, inv[3], __fmaf_rn(y, inv[4], __fmul_rn(z, inv[5]))),
+              __fmaf_rn(x, inv[6], __fmaf_rn(y, inv[7], __fmul_rn(z, inv[8]))));
+}
+// util/SampleFromVoxels.h:419-461: lerp(a,b,w) = a + w*(b-a), along z, then y, then x.
+// Tap naming as trilerp8: v<dx><dy><dz>.
+AVR_DEV float nv_lerp(float a, float b, float w) { return __fadd_rn(a, __fmul_rn(w, __fsub_rn(b, a))); }
+AVR_DEV float nv_trilerp8(float wx, float wy, float wz, float v000, float v100, float v010, float v110, float v001,
+                          float v101, float v011, float v111) {
+    float vx = nv_lerp(nv_lerp(v000, v001, wz), nv_lerp(v010, v011, wz), wy);
+    float vx1 = nv_lerp(nv_lerp(v100, v101, wz), nv_lerp(v110, v111, wz), wy);
+    return nv_lerp(vx, vx1, wx);
+}
+// xyz in index space; grid flattened over [imin, imin+n-1], background 0 (dense layout)
+AVR_DEV float nv_sample_dense(const float *v, int nx, int ny, int nz, const int imin[3], V3 xyz) {
+    float fx = floorf(xyz.x), fy = floorf(xyz.y), fz = floorf(xyz.z);
+    int ix = (int)fx - imin[0], iy = (int)fy - imin[1], iz = (int)fz - imin[2];
+    return nv_trilerp8(xyz.x - fx, xyz.y - fy, xyz.z - fz, dense_at(v, nx, ny, nz, ix, iy, iz),
+                       dense_at(v, nx, ny, nz, ix + 1, iy, iz), dense_at(v, nx, ny, nz, ix, iy + 1, iz),
+                       dense_at(v, nx, ny, nz, ix + 1, iy + 1, iz), dense_at(v, nx, ny, nz, ix, iy, iz + 1),
+                       dense_at(v, nx, ny, nz, ix + 1, iy, iz + 1), dense_at(v, nx, ny, nz, ix, iy + 1, iz + 1),
+                       dense_at(v, nx, ny, nz, ix + 1, iy + 1, iz + 1));
+}
+// density grid of a KIND_NVDB medium, any layout (the octet cell (c) holds taps c-1, c: same store as
+// the SampledGrid convention, addressed by floor(index) - imin + 1)
+template <int LAYOUT>
+AVR_DEV float nv_density(const MediumView &mv, V3 xyz) {
+    if (LAYOUT == LAYOUT_DENSE_F32) return nv_sample_dense(mv.dense, mv.nx, mv.ny, mv.nz, mv.nv_imin, xyz);
+    float fx = floorf(xyz.x), fy = floorf(xyz.y), fz = floorf(xyz.z);
+    int cx = (int)fx - mv.nv_imin[0] + 1, cy = (int)fy - mv.nv_imin[1] + 1, cz = (int)fz - mv.nv_imin[2] + 1;
+    if ((unsigned)cx > (unsigned)mv.nx || (unsigned)cy > (unsigned)mv.ny || (unsigned)cz > (unsigned)mv.nz) return 0.f;
+    float wx = xyz.x - fx, wy = xyz.y - fy, wz = xyz.z - fz;
+    if (LAYOUT == LAYOUT_OCTET_F32) {
+        float4 a, b;
+        ldg256(mv.oct32 + 2 * size_t(octet_index(cx, cy, cz, mv.nbx, mv.nby)), a, b);
+        return nv_trilerp8(wx, wy, wz, a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w);
+    }
+    uint4 q = __ldg(mv.oct16 + octet_index(cx, cy, cz, mv.nbx, mv.nby));
+    float2 a = h2f(q.x), b = h2f(q.y), c = h2f(q.z), d = h2f(q.w);
+    return nv_trilerp8(wx, wy, wz, a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y);
+}
+AVR_DEV float nv_density_rt(const MediumView &mv, V3 xyz) {
+    if (mv.layout == LAYOUT_OCTET_F32) return nv_density<LAYOUT_OCTET_F32>(mv, xyz);
+    if (mv.layout == LAYOUT_OCTET_F16) return nv_density<LAYOUT_OCTET_F16>(mv, xyz);
+    return nv_density<LAYOUT_DENSE_F32>(mv, xyz);
+}
+// Transform::ApplyInverse(Point3f) alone (render -> medium space), util/transform.h:391-402
+AVR_DEV V3 medium_point_exact(const MediumView &mv, V3 p) {
+    const float *a = mv.minv;
+    return v3((a[0] * p.x + a[1] * p.y) + (a[2] * p.z + a[3]), (a[4] * p.x + a[5] * p.y) + (a[6] * p.z + a[7]),
+              (a[8] * p.x + a[9] * p.y) + (a[10] * p.z + a[11]));
+}
+
 // ---- general SamplePoint: GridMedium media.h:287-319, RGBGridMedium media.h:377-401 -------------
 struct Props4 {
     Spec<4> sigma_a, sigma_s, Le;
@@ -207,8 +270,27 @@ AVR_DEV Spec<4> grid_emission(const MediumView &mv, V3 p, const float lambda[4])
 AVR_DEV Props4 sample_point_general(const MediumView &mv, V3 p_render, const float lambda[4], Spec<4> sig_a,
                                     Spec<4> sig_s) {
     Props4 mp;
-    V3 p = grid_point_exact(mv, p_render);
     mp.Le = sconst<4>(0.f);
+    if (mv.kind == KIND_NVDB) {  // NanoVDBMedium::SamplePoint + Le, media.h:624-638, :661-672
+        V3 pm = medium_point_exact(mv, p_render);
+        float d = nv_density_rt(mv, nv_world_to_index(mv.nv_inv, mv.nv_vec, pm));
+        mp.sigma_a = sig_a * d;
+        mp.sigma_s = sig_s * d;
+        if (mv.has_temperature) {
+            float temp = nv_sample_dense(mv.temperature, mv.nv_tdim[0], mv.nv_tdim[1], mv.nv_tdim[2], mv.nv_timin,
+                                         nv_world_to_index(mv.nv_tinv, mv.nv_tvec, pm));
+            temp = (temp - mv.temp_offset) * mv.temp_scale;
+            if (!(temp <= 100.f)) {
+                float lambdaMax = 2.8977721e-3f / temp;
+                float norm = 1 / blackbody(lambdaMax * 1e9f, temp);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) mp.Le.v[i] = blackbody(lambda[i], temp) * norm;
+                mp.Le = mp.Le * mv.le_scale;
+            }
+        }
+        return mp;
+    }
+    V3 p = grid_point_exact(mv, p_render);
     if (mv.kind == KIND_RGB) {
         mp.sigma_a = (mv.rgb_a ? rgb_lookup(mv.rgb_a, mv, p, lambda, nullptr) : sconst<4>(1.f)) * mv.sigma_scale;
         mp.sigma_s = (mv.rgb_s ? rgb_lookup(mv.rgb_s, mv, p, lambda, nullptr) : sconst<4>(1.f)) * mv.sigma_scale;

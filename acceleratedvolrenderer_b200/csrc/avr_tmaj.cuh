@@ -75,6 +75,8 @@ struct Fetcher {
     // scalar density at ray(t) for a non-GENERAL medium
     AVR_DEV float density(const MediumView &mv, float t) const {
         if (TR::EXACT) {
+            if (mv.kind == KIND_NVDB)
+                return nv_density<TR::LAYOUT>(mv, nv_world_to_index(mv.nv_inv, mv.nv_vec, medium_point_exact(mv, point(t))));
             V3 p = grid_point_exact(mv, point(t));
             return lookup_density_s<true, TR::LAYOUT>(mv, p.x * mv.nx - .5f, p.y * mv.ny - .5f, p.z * mv.nz - .5f);
         }

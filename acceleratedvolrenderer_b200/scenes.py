@@ -164,6 +164,35 @@ def cloud_scene(density, *, width, height, spp, sigma_t=8.0, albedo=0.99, g=0.0,
     return gd, rd
 
 
+def cloud_scene_nanovdb(density, *, temperature=None, voxel_size=1.0 / 64, le_scale=1.0, sigma_t=8.0, albedo=0.99,
+                        g=0.0, **kw):
+    """The same scene class with the volume as a "nanovdb" medium (what pbrt-v4-scenes' Disney cloud is):
+    a FloatGrid with uniform voxel size whose world box is centred on the render-space origin."""
+    from ._abi import NanoVDBDesc, NanoVDBGrid
+    dg = NanoVDBGrid.from_dense(density, (0, 0, 0), voxel_size, (0.0, 0.0, 0.0))
+    tg = None if temperature is None else NanoVDBGrid.from_dense(temperature, (0, 0, 0), voxel_size, (0.0, 0.0, 0.0))
+    wb = dg.world_bbox
+    ctr = (wb[:3] + wb[3:]) / 2
+    ext = wb[3:] - wb[:3]
+    rfm = scale_translate((1, 1, 1), tuple(-ctr))
+    nd = NanoVDBDesc(dg, const_spectrum(sigma_t * (1 - albedo)), const_spectrum(sigma_t * albedo), temperature=tg,
+                     render_from_medium=rfm, g=g, le_scale=le_scale)
+    # camera / light / film exactly as cloud_scene builds them for a grid of the same extent
+    m = float(ext.max())
+    fake = np.zeros((max(1, int(round(ext[2] / m * 8))), max(1, int(round(ext[1] / m * 8))), max(1, int(round(ext[0] / m * 8)))),
+                    dtype=np.float32)
+    _, rd = cloud_scene(fake, sigma_t=sigma_t, albedo=albedo, g=g, **kw)
+    half_diag = 0.5 * float(np.linalg.norm(ext))
+    rd.c.scene_radius = half_diag * 1.001
+    if rd.c.boundary_type == 0:
+        for i, v in enumerate((0.0, 0.0, 0.0, half_diag * 1.001)):
+            rd.c.boundary[i] = v
+    else:
+        for i, v in enumerate(tuple(-ext / 2) + tuple(ext / 2)):
+            rd.c.boundary[i] = float(v)
+    return nd, rd
+
+
 def rgb_voxels(rgb_like, rng):
     """Synthetic {scale,c0,c1,c2} sigmoid-polynomial voxels (what RGBUnboundedSpectrum(cs, rgb) yields,
     util/spectrum.cpp:236-247) for an [nz,ny,nx] scale field: smooth, bounded coefficient ranges."""

@@ -96,8 +96,44 @@ typedef struct avr_rgbgrid_desc {
     int32_t majorant_res[3];
 } avr_rgbgrid_desc;
 
+/* One NanoVDB FloatGrid flattened by the host the way the reference's own cmd/nanovdb2pbrt.cpp:100-110
+ * does it (tree().getValue over the index bounding box), plus the pieces of nanovdb::GridData the
+ * reference reads: the float inverse map of worldToIndexF (NanoVDB.h Map::applyInverseMapF:
+ * mInvMatF, mVecF), indexBBox() (inclusive on both ends) and worldBBox() (doubles).  Voxels outside
+ * the index box read as the background value, which must be 0 (fog volumes). */
+typedef struct avr_nanovdb_grid {
+    const float *values;       /* dims[0]*dims[1]*dims[2] floats, x fastest; NULL = grid absent   */
+    int32_t index_min[3];      /* indexBBox().min()                                               */
+    int32_t dims[3];           /* indexBBox().max() - min() + 1                                   */
+    float inv_mat[9];          /* Map::mInvMatF, row-major                                        */
+    float vec[3];              /* Map::mVecF                                                      */
+    double world_bbox[6];      /* worldBBox(): min xyz, max xyz                                   */
+} avr_nanovdb_grid;
+
+/* Replaces NanoVDBMedium::Create + ctor, media.cpp:511-665 ("nanovdb"; what pbrt-v4-scenes' Disney
+ * cloud uses).  Sampling follows nanovdb::SampleFromVoxels<Tree,1,false> (node-centred, lerp
+ * a + w*(b-a), order z,y,x; SampleFromVoxels.h:226-238), NOT SampledGrid::Lookup; the majorant grid
+ * is 64^3 built as in media.cpp:560-616. */
+typedef struct avr_nanovdb_desc {
+    avr_nanovdb_grid density;      /* "gridname" (default "density")                              */
+    avr_nanovdb_grid temperature;  /* "temperaturename"; values == NULL when the file has none     */
+    float render_from_medium[16];
+    float medium_from_render[16];
+    const float *sigma_a;      /* AVR_NSPEC, unscaled (ConstantSpectrum(1) when the scene gives none) */
+    const float *sigma_s;      /* AVR_NSPEC                                                   */
+    float sigma_scale;         /* "scale"                                                     */
+    float g;
+    float le_scale;            /* "Lescale"                                                   */
+    float temperature_offset;  /* "temperatureoffset" / "temperaturecutoff"                   */
+    float temperature_scale;   /* "temperaturescale"                                          */
+    int32_t majorant_res[3];   /* 0 -> {64,64,64} (media.cpp:521)                             */
+} avr_nanovdb_desc;
+
 avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid_desc *desc, int layout,
                                          avr_medium **out);
+/* layout: as for uniformgrid (the octet layouts hold the 8 stencil taps of one index-space cell). */
+avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_desc *desc, int layout,
+                                     avr_medium **out);
 avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_desc *desc, avr_medium **out);
 void avr_medium_destroy(avr_medium *m);
 
@@ -110,8 +146,13 @@ int64_t avr_medium_bytes(const avr_medium *m);
  * :364-377) to host: out has res[0]*res[1]*res[2] floats, x fastest.  Bit-exact contract. */
 avr_status avr_medium_majorants(avr_medium *m, float *out, int32_t res[3]);
 
+/* Medium-space bounds: GridMedium/RGBGridMedium "p0","p1"; NanoVDBMedium::GetBounds() = the union of
+ * the grids' worldBBox() narrowed to float (media.h:616, media.cpp:536-551).  out: min xyz, max xyz. */
+avr_status avr_medium_bounds(const avr_medium *m, float out[6]);
+
 /* SampledGrid<Float>::Lookup(Point3f), util/containers.h:804-819, on the medium's density grid.
- * p in grid-normalised [0,1]^3 coordinates (after bounds.Offset), 3 floats per point. */
+ * p in grid-normalised [0,1]^3 coordinates (after bounds.Offset), 3 floats per point.  For a nanovdb
+ * medium: nanovdb::SampleFromVoxels<Tree,1,false>::operator()(xyz), p in INDEX space. */
 avr_status avr_medium_lookup_density(avr_medium *m, const float *p, int64_t n, float *out);
 
 /* MediumProperties Medium::SamplePoint(p, lambda), media.h:287-319 / :377-401.  p in render space,

@@ -146,6 +146,27 @@ void *orc_medium_create_rgbgrid(const avr_rgbgrid_desc *d) {
                 d->render_from_medium, d->medium_from_render, d->sigma_scale, d->g, d->majorant_res);
     return m;
 }
+static NvGrid nv_from(const avr_nanovdb_grid &g) {
+    NvGrid n;
+    n.present = g.values != nullptr;
+    if (!n.present) return n;
+    for (int i = 0; i < 3; ++i) { n.imin[i] = g.index_min[i]; n.dims[i] = g.dims[i]; n.vec[i] = g.vec[i]; }
+    for (int i = 0; i < 9; ++i) n.inv[i] = g.inv_mat[i];
+    for (int i = 0; i < 6; ++i) n.wbox[i] = g.world_bbox[i];
+    n.v.assign(g.values, g.values + size_t(g.dims[0]) * g.dims[1] * g.dims[2]);
+    return n;
+}
+void *orc_medium_create_nanovdb(const avr_nanovdb_desc *d) {
+    Medium *m = new Medium();
+    m->init_nanovdb(nv_from(d->density), nv_from(d->temperature), d->render_from_medium, d->medium_from_render,
+                    d->sigma_a, d->sigma_s, d->sigma_scale, d->g, d->le_scale, d->temperature_offset,
+                    d->temperature_scale, d->majorant_res);
+    return m;
+}
+void orc_medium_bounds(void *m, float out[6]) {
+    const Bounds &b = ((Medium *)m)->bounds;
+    for (int i = 0; i < 3; ++i) { out[i] = b.pMin[i]; out[3 + i] = b.pMax[i]; }
+}
 void orc_medium_destroy(void *m) { delete (Medium *)m; }
 int orc_medium_is_emissive(void *m) { return ((Medium *)m)->emissive ? 1 : 0; }
 void orc_medium_majorants(void *mp, float *out, int32_t res[3]) {

@@ -19,6 +19,8 @@
 #include <pbrt/util/spectrum.h>
 #include <pbrt/util/transform.h>
 
+#include <nanovdb/util/GridBuilder.h>
+
 #include <Eigen/Sparse>
 #include <graph/util.h>
 
@@ -48,6 +50,7 @@ struct RefMedium {
     Medium medium;
     GridMedium *grid = nullptr;
     RGBGridMedium *rgb = nullptr;
+    NanoVDBMedium *nvdb = nullptr;
     std::vector<DenselySampledSpectrum *> keep;
 };
 DenselySampledSpectrum *dense_from(const float *tab) {
@@ -240,11 +243,74 @@ void *ref_medium_create_rgbgrid(const avr_rgbgrid_desc *d) {
     rm->medium = rm->rgb;
     return rm;
 }
+// ---- NanoVDB: a real nanovdb::FloatGrid built with the vendored GridBuilder, handed to the
+// reference's own NanoVDBMedium constructor (media.cpp:511-616) -------------------------------------
+using NvHandle = nanovdb::GridHandle<NanoVDBBuffer>;
+void *ref_nanovdb_grid_build(const float *dense, const int32_t dims[3], const int32_t origin_ijk[3],
+                             double voxel_size, const double origin_world[3]) {
+    nanovdb::GridBuilder<float> builder(0.f, nanovdb::GridClass::FogVolume);
+    nanovdb::CoordBBox box(nanovdb::Coord(origin_ijk[0], origin_ijk[1], origin_ijk[2]),
+                           nanovdb::Coord(origin_ijk[0] + dims[0] - 1, origin_ijk[1] + dims[1] - 1,
+                                          origin_ijk[2] + dims[2] - 1));
+    builder([&](const nanovdb::Coord &c) -> float {
+        int i = c[0] - origin_ijk[0], j = c[1] - origin_ijk[1], k = c[2] - origin_ijk[2];
+        return dense[(size_t(k) * dims[1] + j) * dims[0] + i];
+    }, box);
+    NvHandle h = builder.getHandle<nanovdb::AbsDiff, NanoVDBBuffer>(
+        voxel_size, nanovdb::Vec3d(origin_world[0], origin_world[1], origin_world[2]), "density", nanovdb::AbsDiff(),
+        NanoVDBBuffer(Allocator()));
+    return new NvHandle(std::move(h));
+}
+void ref_nanovdb_grid_free(void *h) { delete (NvHandle *)h; }
+// what the host adapter reads off the grid to fill avr_nanovdb_grid
+void ref_nanovdb_grid_info(void *hp, int32_t index_min[3], int32_t dims[3], float inv_mat[9], float vec[3],
+                           double world_bbox[6]) {
+    const nanovdb::FloatGrid *g = ((NvHandle *)hp)->grid<float>();
+    auto ib = g->indexBBox();
+    auto wb = g->worldBBox();
+    for (int i = 0; i < 3; ++i) {
+        index_min[i] = ib.min()[i];
+        dims[i] = ib.max()[i] - ib.min()[i] + 1;
+        vec[i] = g->map().mVecF[i];
+        world_bbox[i] = wb.min()[i];
+        world_bbox[3 + i] = wb.max()[i];
+    }
+    for (int i = 0; i < 9; ++i) inv_mat[i] = g->map().mInvMatF[i];
+}
+// cmd/nanovdb2pbrt.cpp:100-110 style flattening over the inclusive index box
+void ref_nanovdb_grid_flatten(void *hp, float *out) {
+    const nanovdb::FloatGrid *g = ((NvHandle *)hp)->grid<float>();
+    auto ib = g->indexBBox();
+    size_t n = 0;
+    for (int z = ib.min()[2]; z <= ib.max()[2]; ++z)
+        for (int y = ib.min()[1]; y <= ib.max()[1]; ++y)
+            for (int x = ib.min()[0]; x <= ib.max()[0]; ++x) out[n++] = g->tree().getValue({x, y, z});
+}
+// consumes (moves from) the two grid handles; temperature may be NULL
+void *ref_medium_create_nanovdb(const avr_nanovdb_desc *d, void *density_h, void *temperature_h) {
+    Allocator alloc;
+    RefMedium *rm = new RefMedium();
+    DenselySampledSpectrum *sa = dense_from(d->sigma_a), *ss = dense_from(d->sigma_s);
+    rm->keep = {sa, ss};
+    Transform xf = make_xf(d->render_from_medium, d->medium_from_render);
+    NvHandle dg = std::move(*(NvHandle *)density_h);
+    NvHandle tg;
+    if (temperature_h) tg = std::move(*(NvHandle *)temperature_h);
+    rm->nvdb = new NanoVDBMedium(xf, sa, ss, d->sigma_scale, d->g, std::move(dg), std::move(tg), d->le_scale,
+                                 d->temperature_offset, d->temperature_scale, alloc);
+    rm->medium = rm->nvdb;
+    return rm;
+}
+void ref_medium_bounds(void *m, float out[6]) {
+    RefMedium *rm = (RefMedium *)m;
+    const Bounds3f &b = rm->grid ? rm->grid->bounds : rm->rgb ? rm->rgb->bounds : rm->nvdb->bounds;
+    for (int i = 0; i < 3; ++i) { out[i] = b.pMin[i]; out[3 + i] = b.pMax[i]; }
+}
 void ref_medium_destroy(void *m) { delete (RefMedium *)m; }
 int ref_medium_is_emissive(void *m) { return ((RefMedium *)m)->medium.IsEmissive() ? 1 : 0; }
 void ref_medium_majorants(void *mp, float *out, int32_t res[3]) {
     RefMedium *rm = (RefMedium *)mp;
-    const MajorantGrid &g = rm->grid ? rm->grid->majorantGrid : rm->rgb->majorantGrid;
+    const MajorantGrid &g = rm->grid ? rm->grid->majorantGrid : rm->rgb ? rm->rgb->majorantGrid : rm->nvdb->majorantGrid;
     for (int i = 0; i < 3; ++i) res[i] = g.res[i];
     for (size_t i = 0; i < g.voxels.size(); ++i) out[i] = g.voxels[i];
 }
@@ -263,8 +329,8 @@ void ref_medium_sample_point(void *mp, const float *p, int64_t n, const float la
 // SampleRay prologue exactly as media.h:322-337 writes it (ApplyInverse + IntersectP)
 void ref_medium_ray_to_medium(void *mp, const float *rays, int64_t n, float *out) {
     RefMedium *rm = (RefMedium *)mp;
-    const Transform &xf = rm->grid ? rm->grid->renderFromMedium : rm->rgb->renderFromMedium;
-    const Bounds3f &b = rm->grid ? rm->grid->bounds : rm->rgb->bounds;
+    const Transform &xf = rm->grid ? rm->grid->renderFromMedium : rm->rgb ? rm->rgb->renderFromMedium : rm->nvdb->renderFromMedium;
+    const Bounds3f &b = rm->grid ? rm->grid->bounds : rm->rgb ? rm->rgb->bounds : rm->nvdb->bounds;
     for (int64_t i = 0; i < n; ++i) {
         const float *r = rays + 7 * i;
         Float raytMax = r[6];

@@ -6,6 +6,7 @@
 #include <pbrt/samplers.h>
 #include <pbrt/util/bluenoise.h>
 #include <pbrt/util/log.h>
+#include <pbrt/util/parallel.h>
 #include <pbrt/util/print.h>
 #include <pbrt/util/spectrum.h>
 #include <pbrt/util/stats.h>
@@ -18,6 +19,11 @@ void LogFatal(LogLevel, const char *file, int line, const char *s) {
     std::fprintf(stderr, "refprobe: reference CHECK failed at %s:%d: %s\n", file, line, s);
     std::abort();
 }
+// NanoVDBMedium's constructor (media.cpp:511-616) logs at Verbose level and fills the majorant grid
+// with ParallelFor; the probe runs that loop body serially (scheduling only, same per-cell code).
+namespace logging { LogLevel logLevel = LogLevel::Error; }
+void Log(LogLevel, const char *file, int line, const char *s) { std::fprintf(stderr, "refprobe: %s:%d: %s\n", file, line, s); }
+void ParallelFor(int64_t start, int64_t end, std::function<void(int64_t, int64_t)> func) { func(start, end); }
 StatRegisterer::StatRegisterer(AccumFunc, PixelAccumFunc) {}
 void StatsAccumulator::ReportMemoryCounter(const char *, int64_t) {}
 void StatsAccumulator::ReportPercentage(const char *, int64_t, int64_t) {}

@@ -166,6 +166,52 @@ struct Grid {
     }
 };
 
+// ---- NanoVDB FloatGrid as NanoVDBMedium reads it (media.h:624-672, media.cpp:511-616) --------------
+// Arithmetic restated from the vendored headers the reference compiles against
+// (src/ext/openvdb/nanovdb/nanovdb, submodule 414bed84): Map::applyInverseMapF (NanoVDB.h:2028-2031),
+// matMult (NanoVDB.h:1409-1414), Floor (util/SampleFromVoxels.h:58-65), SampleFromVoxels<Tree,1,false>
+// (util/SampleFromVoxels.h:419-461).  The tree is a dense flattening of the index bounding box
+// (cmd/nanovdb2pbrt.cpp:100-110); voxels outside it hold the background value 0.
+struct NvGrid {
+    bool present = false;
+    std::vector<float> v;
+    int imin[3] = {0, 0, 0}, dims[3] = {0, 0, 0};
+    float inv[9], vec[3];
+    double wbox[6];
+    float get(int i, int j, int k) const {  // ReadAccessor::getValue
+        i -= imin[0]; j -= imin[1]; k -= imin[2];
+        if (i < 0 || j < 0 || k < 0 || i >= dims[0] || j >= dims[1] || k >= dims[2]) return 0.f;
+        return v[(size_t(k) * dims[1] + j) * dims[0] + i];
+    }
+    // worldToIndexF(Vec3<float>)
+    V3 world_to_index_f(V3 p) const {
+        float x = p.x - vec[0], y = p.y - vec[1], z = p.z - vec[2];
+        return {std::fmaf(x, inv[0], std::fmaf(y, inv[1], z * inv[2])),
+                std::fmaf(x, inv[3], std::fmaf(y, inv[4], z * inv[5])),
+                std::fmaf(x, inv[6], std::fmaf(y, inv[7], z * inv[8]))};
+    }
+    // worldToIndexF(Vec3R): the subtraction and the innermost product run in double, every fmaf
+    // argument is narrowed to float (matMult(const float*, Vec3<double>) calls fmaf)
+    void world_to_index_f_from_double(const double p[3], double out[3]) const {
+        double x = p[0] - vec[0], y = p[1] - vec[1], z = p[2] - vec[2];
+        for (int r = 0; r < 3; ++r)
+            out[r] = std::fmaf(float(x), inv[3 * r], std::fmaf(float(y), inv[3 * r + 1], float(z * inv[3 * r + 2])));
+    }
+    float sample(V3 xyz) const {  // SampleFromVoxels<TreeT,1,false>::operator()(Vec3<float>)
+        float fi = std::floor(xyz.x), fj = std::floor(xyz.y), fk = std::floor(xyz.z);
+        float wx = xyz.x - fi, wy = xyz.y - fj, wz = xyz.z - fk;
+        int i = int32_t(fi), j = int32_t(fj), k = int32_t(fk);
+        auto lerpn = [](float a, float b, float w) { return a + w * (b - a); };
+        float vy = lerpn(get(i, j, k), get(i, j, k + 1), wz);
+        float vy1 = lerpn(get(i, j + 1, k), get(i, j + 1, k + 1), wz);
+        float vx = lerpn(vy, vy1, wy);
+        vy1 = lerpn(get(i + 1, j + 1, k), get(i + 1, j + 1, k + 1), wz);
+        vy = lerpn(get(i + 1, j, k), get(i + 1, j, k + 1), wz);
+        float vx1 = lerpn(vy, vy1, wy);
+        return lerpn(vx, vx1, wx);
+    }
+};
+
 // ---- MajorantGrid, media.h:105-133 ------------------------------------------------------------------
 struct MajGrid {
     Bounds bounds;

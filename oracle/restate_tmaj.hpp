@@ -22,6 +22,9 @@ struct Medium {
     std::vector<float> rgb_a, rgb_s, rgb_le, le_illum;
     int nx = 0, ny = 0, nz = 0;
     float sigma_scale = 1, le_scale = 0;
+    // NanoVDBMedium
+    bool is_nvdb = false;
+    NvGrid nv_density, nv_temperature;
 
     // GridMedium ctor, media.cpp:212-247
     void init_grid(int nx_, int ny_, int nz_, const float *dens, const float *temp, const float *lesc,
@@ -104,6 +107,66 @@ struct Medium {
                 }
     }
 
+    // NanoVDBMedium ctor, media.cpp:511-616.  dg/tg carry what the reference reads from the two
+    // GridHandles (flattened values, float inverse map, index and world bounding boxes).
+    void init_nanovdb(const NvGrid &dg, const NvGrid &tg, const float m[16], const float minv[16], const float *sa,
+                      const float *ss, float sigScale, float g_, float leScale, float tOff, float tScale,
+                      const int mres[3]) {
+        is_nvdb = true;
+        nv_density = dg;
+        nv_temperature = tg;
+        std::memcpy(xf.m, m, 64);
+        std::memcpy(xf.mInv, minv, 64);
+        sigma_a_spec.assign(sa, sa + NSPEC);
+        sigma_s_spec.assign(ss, ss + NSPEC);
+        for (float &v : sigma_a_spec) v *= sigScale;
+        for (float &v : sigma_s_spec) v *= sigScale;
+        g = g_; le_scale = leScale; temp_offset = tOff; temp_scale = tScale;
+        has_temperature = tg.present;
+        emissive = tg.present && leScale > 0;  // media.h:621
+        // bounds = Bounds3f(worldBBox) [double -> float], Union with the temperature grid's (:536-551)
+        auto fbox = [](const double w[6]) {
+            return Bounds{{float(w[0]), float(w[1]), float(w[2])}, {float(w[3]), float(w[4]), float(w[5])}};
+        };
+        bounds = fbox(dg.wbox);
+        if (tg.present) {
+            Bounds b2 = fbox(tg.wbox);
+            for (int i = 0; i < 3; ++i) {
+                bounds.pMin[i] = std::min(bounds.pMin[i], b2.pMin[i]);
+                bounds.pMax[i] = std::max(bounds.pMax[i], b2.pMax[i]);
+            }
+        }
+        maj.bounds = bounds;
+        for (int i = 0; i < 3; ++i) maj.res[i] = mres[i] > 0 ? mres[i] : 64;
+        maj.vox.resize(size_t(maj.res[0]) * maj.res[1] * maj.res[2]);
+        auto blerp = [&](float tx, float ty, float tz, double out[3]) {  // Bounds3::Lerp -> Vec3R
+            out[0] = lerp(tx, bounds.pMin.x, bounds.pMax.x);
+            out[1] = lerp(ty, bounds.pMin.y, bounds.pMax.y);
+            out[2] = lerp(tz, bounds.pMin.z, bounds.pMax.z);
+        };
+        for (int z = 0; z < maj.res[2]; ++z)
+            for (int y = 0; y < maj.res[1]; ++y)
+                for (int x = 0; x < maj.res[0]; ++x) {
+                    double w0[3], w1[3], i0[3], i1[3];
+                    blerp(float(x) / maj.res[0], float(y) / maj.res[1], float(z) / maj.res[2], w0);
+                    blerp(float(x + 1) / maj.res[0], float(y + 1) / maj.res[1], float(z + 1) / maj.res[2], w1);
+                    dg.world_to_index_f_from_double(w0, i0);
+                    dg.world_to_index_f_from_double(w1, i1);
+                    float delta = 1.f;
+                    int lo[3], hi[3];
+                    for (int a = 0; a < 3; ++a) {
+                        lo[a] = std::max(int(i0[a] - delta), dg.imin[a]);
+                        hi[a] = std::min(int(i1[a] + delta), dg.imin[a] + dg.dims[a] - 1);
+                    }
+                    float maxValue = 0;
+                    for (int nz_ = lo[2]; nz_ <= hi[2]; ++nz_)
+                        for (int ny_ = lo[1]; ny_ <= hi[1]; ++ny_)
+                            for (int nx_ = lo[0]; nx_ <= hi[0]; ++nx_)
+                                maxValue = std::max(maxValue, dg.get(nx_, ny_, nz_));
+                    maj.vox[x + maj.res[0] * (y + maj.res[1] * z)] = maxValue;
+                }
+    }
+
     // SampledGrid<RGB*Spectrum>::Lookup(p, convert): convert-then-lerp, containers.h:785-801
     Spec4 rgb_lookup(const std::vector<float> &gr, V3 p, const float lambda[4], const float *illum) const {
         float sx = p.x * nx - .5f, sy = p.y * ny - .5f, sz = p.z * nz - .5f;
@@ -135,8 +198,21 @@ struct Medium {
     MediumProps sample_point(V3 p, const float lambda[4]) const {
         MediumProps mp;
         p = apply_inverse_point(xf, p);
-        p = bounds.offset(p);
         mp.Le = spec(0.f);
+        if (is_nvdb) {  // NanoVDBMedium::SamplePoint + Le, media.h:624-638, :661-672
+            mp.sigma_a = sample_dense(sigma_a_spec.data(), lambda);
+            mp.sigma_s = sample_dense(sigma_s_spec.data(), lambda);
+            float d = nv_density.sample(nv_density.world_to_index_f(p));
+            mp.sigma_a = mp.sigma_a * d;
+            mp.sigma_s = mp.sigma_s * d;
+            if (nv_temperature.present) {
+                float temp = nv_temperature.sample(nv_temperature.world_to_index_f(p));
+                temp = (temp - temp_offset) * temp_scale;
+                if (!(temp <= 100.f)) mp.Le = le_scale * blackbody_sample(temp, lambda);
+            }
+            return mp;
+        }
+        p = bounds.offset(p);
         if (is_rgb) {
             mp.sigma_a = sigma_scale * (rgb_a.empty() ? spec(1.f) : rgb_lookup(rgb_a, p, lambda, nullptr));
             mp.sigma_s = sigma_scale * (rgb_s.empty() ? spec(1.f) : rgb_lookup(rgb_s, p, lambda, nullptr));

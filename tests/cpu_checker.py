@@ -10,7 +10,7 @@ import os
 
 import numpy as np
 
-from acceleratedvolrenderer_b200._abi import GridDesc, RGBGridDesc, RenderDesc, TMAJ_DTYPE
+from acceleratedvolrenderer_b200._abi import GridDesc, NanoVDBDesc, NanoVDBGrid, RGBGridDesc, RenderDesc, TMAJ_DTYPE
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORC_PATH = os.path.join(ROOT, "oracle", "liboracle.so")
@@ -44,8 +44,10 @@ class Checker:
             raise FileNotFoundError(f"{path} missing: run `make -C oracle`")
         self.lib = C.CDLL(path)
         self.pfx = kind + "_"
-        for name in ("medium_create_uniformgrid", "medium_create_rgbgrid"):
+        for name in ("medium_create_uniformgrid", "medium_create_rgbgrid", "medium_create_nanovdb"):
             getattr(self.lib, self.pfx + name).restype = C.c_void_p
+        if kind == "ref":
+            self.lib.ref_nanovdb_grid_build.restype = C.c_void_p
         self.fn("kind").restype = C.c_char_p
 
     def fn(self, name):
@@ -163,6 +165,43 @@ class Checker:
         h = self.fn("medium_create_rgbgrid")(C.byref(desc.c))
         return CheckerMedium(self, h, desc)
 
+    # NanoVDB: under "ref" the grid is a real nanovdb::FloatGrid built with the vendored GridBuilder and
+    # read back (index box, float inverse map, world box, flattened values); under "orc" the same
+    # numbers come from the host-side helper NanoVDBGrid.from_dense.  The golden comparison of the
+    # returned arrays pins the helper to NanoVDB itself.
+    def _ref_grid_handle(self, source):
+        dense, oijk, vs, ow = source
+        dense = f32(dense)
+        dims = np.asarray(dense.shape[::-1], dtype=np.int32); oijk = np.asarray(oijk, dtype=np.int32)
+        ow = np.asarray(ow, dtype=np.float64)
+        return C.c_void_p(self.lib.ref_nanovdb_grid_build(_p(dense, f32p), _p(dims, i32p), _p(oijk, i32p), C.c_double(vs),
+                                                          _p(ow, f64p)))
+
+    def nanovdb_grid(self, dense, origin_ijk, voxel_size, origin_world) -> NanoVDBGrid:
+        py = NanoVDBGrid.from_dense(dense, origin_ijk, voxel_size, origin_world)
+        if self.kind != "ref":
+            return py
+        h = self._ref_grid_handle(py.source)
+        imin = np.zeros(3, dtype=np.int32); dims = np.zeros(3, dtype=np.int32)
+        inv = np.zeros(9, dtype=np.float32); vec = np.zeros(3, dtype=np.float32); wb = np.zeros(6, dtype=np.float64)
+        self.lib.ref_nanovdb_grid_info(h, _p(imin, i32p), _p(dims, i32p), _p(inv, f32p), _p(vec, f32p), _p(wb, f64p))
+        vals = np.empty((dims[2], dims[1], dims[0]), dtype=np.float32)
+        self.lib.ref_nanovdb_grid_flatten(h, _p(vals, f32p))
+        self.lib.ref_nanovdb_grid_free(h)
+        return NanoVDBGrid(vals, imin, inv, vec, wb, source=py.source)
+
+    def medium_nanovdb(self, desc: NanoVDBDesc):
+        if self.kind == "ref":
+            dh = self._ref_grid_handle(desc.density.source)
+            th = self._ref_grid_handle(desc.temperature.source) if desc.temperature is not None else None
+            h = self.lib.ref_medium_create_nanovdb(C.byref(desc.c), dh, th)
+            self.lib.ref_nanovdb_grid_free(dh)
+            if th is not None:
+                self.lib.ref_nanovdb_grid_free(th)
+        else:
+            h = self.fn("medium_create_nanovdb")(C.byref(desc.c))
+        return CheckerMedium(self, h, desc)
+
     # ---- graph -----------------------------------------------------------------------------------
     def graph_propagate(self, rowptr, col, val, L0, bounces):
         rowptr = np.ascontiguousarray(rowptr, dtype=np.int64); col = np.ascontiguousarray(col, dtype=np.int32)
@@ -198,9 +237,14 @@ class CheckerMedium:
     def majorants(self):
         res = np.zeros(3, dtype=np.int32)
         mr = self.desc.majorant_res
-        out = np.empty(max(int(np.prod(mr)), 4096), dtype=np.float32)
+        out = np.empty(max(int(np.prod(mr)), 64 ** 3), dtype=np.float32)
         self.ck.fn("medium_majorants")(self.h, _p(out, f32p), _p(res, i32p))
         return out[: int(np.prod(res))].reshape(res[2], res[1], res[0])
+
+    def bounds(self):
+        out = np.zeros(6, dtype=np.float32)
+        self.ck.fn("medium_bounds")(self.h, _p(out, f32p))
+        return out
 
     def sample_point(self, p, lam):
         p = f32(p); lam = f32(lam); n = p.size // 3

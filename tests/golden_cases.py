@@ -7,7 +7,7 @@ Case inputs are small on purpose: the fixtures travel with the repository.
 import numpy as np
 
 from acceleratedvolrenderer_b200 import scenes
-from acceleratedvolrenderer_b200._abi import GridDesc, RGBGridDesc
+from acceleratedvolrenderer_b200._abi import GridDesc, NanoVDBDesc, RGBGridDesc
 
 LAMBDA = np.array([412.3, 533.9, 601.2, 688.8], dtype=np.float32)
 
@@ -195,6 +195,66 @@ def case_rgbgrid(ck):
     return out
 
 
+def nanovdb_variants(ck):
+    """(name, NanoVDBDesc) pairs shared with the GPU parity tests."""
+    dens = scenes.fbm_density(40, 33, 37, seed=5)
+    dens[dens < 0.05] = 0          # sparse: inactive voxels = background
+    dens[:2] = 0; dens[:, :, -3:] = 0   # empty border slabs: index box != build box
+    temp = (scenes.fbm_density(40, 33, 37, seed=9) * 2500 + 80).astype(np.float32)
+    temp[:, :5] = 0
+    M2, M2i = _rot_scale()
+    g0 = ck.nanovdb_grid(dens, (-7, 3, 11), 0.0625, (0.37, -1.21, 0.05))
+    g1 = ck.nanovdb_grid(dens, (100, -200, -30), 0.03125, (-4.0, 6.5, 1.25))
+    t1 = ck.nanovdb_grid(temp, (101, -198, -33), 0.03125, (-4.0, 6.5, 1.25))
+    return [("nv0", NanoVDBDesc(g0, scenes.ramp_spectrum(0.5, 1.5), scenes.ramp_spectrum(6, 9), g=0.3)),
+            ("nv1", NanoVDBDesc(g1, scenes.ramp_spectrum(0.2, 0.4), scenes.ramp_spectrum(3, 5), temperature=t1,
+                                render_from_medium=M2, medium_from_render=M2i, scale=2.5, g=0.877, le_scale=0.6,
+                                temperature_offset=20, temperature_scale=1.05))]
+
+
+def case_nanovdb(ck):
+    """NanoVDBMedium (media.h:602-685, media.cpp:511-616) over real nanovdb::FloatGrids: the grid
+    read-back the host adapter does, the 64^3 majorant grid, bounds, SamplePoint (SampleFromVoxels
+    trilinear + blackbody emission), SampleRay prologue and SampleT_maj under the three callbacks."""
+    rng = np.random.default_rng(8)
+    out = {}
+    for name, nd in nanovdb_variants(ck):
+        for gname, gr in (("density", nd.density), ("temperature", nd.temperature)):
+            if gr is None:
+                continue
+            out[f"{name}_{gname}_values"] = gr.values
+            out[f"{name}_{gname}_index_min"] = gr.index_min
+            out[f"{name}_{gname}_inv_mat"] = gr.inv_mat
+            out[f"{name}_{gname}_vec"] = gr.vec
+            out[f"{name}_{gname}_world_bbox"] = gr.world_bbox
+        m = ck.medium_nanovdb(nd)
+        out[f"{name}_bounds"] = m.bounds()
+        out[f"{name}_majorants"] = m.majorants()
+        out[f"{name}_emissive"] = np.array([m.is_emissive()], dtype=np.int32)
+        b0, b1 = nd.p0, nd.p1
+        npts = 1500
+        pm = (b0 + rng.uniform(-0.05, 1.05, (npts, 3)) * (b1 - b0)).astype(np.float32)
+        pr = (np.c_[pm, np.ones(npts)] @ nd.m.reshape(4, 4).T.astype(np.float64))[:, :3].astype(np.float32)
+        out[f"{name}_sample_point"] = m.sample_point(pr, LAMBDA)
+        n = 1200
+        org = rng.normal(size=(n, 3))
+        org /= np.linalg.norm(org, axis=1, keepdims=True)
+        org *= 2.5 * float(np.linalg.norm(b1 - b0))
+        ctr = (np.r_[(b0 + b1) / 2, 1] @ nd.m.reshape(4, 4).T)[:3]
+        tgt = pr[rng.integers(0, npts, n)]
+        rays7 = np.zeros((n, 7), dtype=np.float32)
+        rays7[:, :3] = org + ctr
+        rays7[:, 3:6] = (tgt - rays7[:, :3]) * rng.uniform(0.5, 2, (n, 1))
+        rays7[:, 6] = rng.uniform(0.2, 3, n)
+        out[f"{name}_ray_to_medium"] = m.ray_to_medium(rays7)
+        seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64)
+        u = rng.random(n, dtype=np.float32)
+        for mode in (0, 1, 2):
+            _tmaj_fields(f"{name}_tmaj{mode}", m.sample_tmaj(mode, rays7, seeds, u, LAMBDA), out, approx_t_event=True)
+        m.close()
+    return out
+
+
 def case_graph(ck):
     """src/graph: Eigen SpMV propagation (free_graph.cpp:345-375) and the light-ray transmittance
     estimator (graph/util.h SampleTransmittance)."""
@@ -226,4 +286,4 @@ def case_graph(ck):
 
 
 CASES = {"scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
-         "rgbgrid": case_rgbgrid, "graph": case_graph}
+         "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph}

@@ -123,6 +123,47 @@ def test_general_media_render_matches_oracle(ctx, orc, kind):
     md.close(); mo.close()
 
 
+@pytest.mark.parametrize("emissive", [False, True])
+def test_nanovdb_render_matches_oracle(ctx, orc, emissive):
+    """"nanovdb" media through k_volpath: per-sample radiance under the exact arithmetic (all layouts
+    that keep fp32 taps), converged image under fast math (incl. fp16 octets) within the noise floor."""
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    dens[dens < 0.02] = 0
+    temp = (dens * 2500 + 200).astype(np.float32) if emissive else None
+    nd, rd = scenes.cloud_scene_nanovdb(dens, temperature=temp, le_scale=0.4, width=32, height=24, spp=32,
+                                        sigma_t=18.0, albedo=0.95, g=0.4, max_depth=6)
+    mo = orc.medium_nanovdb(nd)
+    rs = rd.with_(spp=4)
+    want, wstats = mo.render_samples(rs)
+    Lw = want[:, :4].astype(np.float64)
+    assert Lw.sum() > 0
+    for layout in (["dense"] if emissive else ["dense", "octet32"]):
+        md = ctx.create_medium("nanovdb", nd, layout=layout)
+        got, gstats = ctx.render_volpath_samples(md, rs)
+        md.close()
+        L = got[:, :4].astype(np.float64)
+        scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+        ok = np.abs(L - Lw).max(axis=1) <= 1e-3 * scale
+        assert ok.mean() >= 0.99, f"nanovdb/{layout}: {ok.mean():.4f} of samples match"
+        assert gstats["camera_rays"] == wstats[0]
+        for k, i in (("camera_fetches", 1), ("shadow_fetches", 2), ("scatter_events", 4)):
+            assert abs(gstats[k] - wstats[i]) <= 0.02 * max(1, wstats[i]), k
+    ref_a, _ = mo.render(rd, threads=8)
+    ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
+    mo.close()
+    img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
+    noise = rel_mse(img_a, img_b)
+    for layout in (["dense"] if emissive else ["dense", "octet32", "octet16"]):
+        md = ctx.create_medium("nanovdb", nd, layout=layout)
+        film, _ = ctx.render_volpath(md, rd.with_(exact_math=0, sampler_seed=2))
+        md.close()
+        assert np.all(film[..., 3] == rd.spp)
+        img = ctx.film_resolve(rd, film)
+        err = rel_mse(img, img_a)
+        assert err <= 3 * noise + 1e-6, (layout, err, noise)
+        assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
+
+
 def test_sample_sharding_is_additive(ctx):
     """Multi-GPU contract: rendering sample shards / rank partitions into one film equals one render."""
     dens, (gd, rd) = small_scene(width=24, height=20, spp=8)

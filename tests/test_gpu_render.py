@@ -161,7 +161,8 @@ def test_nanovdb_render_matches_oracle(ctx, orc, emissive):
         img = ctx.film_resolve(rd, film)
         err = rel_mse(img, img_a)
         assert err <= 3 * noise + 1e-6, (layout, err, noise)
-        assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
+        # image mean: 5 %, or 3x the oracle's own seed-to-seed difference where blackbody spikes make that larger
+        assert abs(img.mean() - img_a.mean()) <= max(0.05 * img_a.mean(), 3 * abs(img_a.mean() - img_b.mean()))
 
 
 def test_sample_sharding_is_additive(ctx):

@@ -62,6 +62,24 @@ class avr_nanovdb_desc(C.Structure):
     ]
 
 
+i32p_ = C.POINTER(C.c_int32)
+
+
+class avr_graph_file(C.Structure):
+    _fields_ = [
+        ("description", C.c_char * 64),
+        ("vertex_radius", C.c_float),
+        ("use_coors", C.c_int32), ("use_samples", C.c_int32), ("use_ray_vertex_types", C.c_int32),
+        ("use_lighting", C.c_int32), ("use_render_search_range", C.c_int32),
+        ("cur_vertex_id", C.c_int32), ("cur_edge_id", C.c_int32), ("cur_path_id", C.c_int32),
+        ("n_vertices", C.c_int32), ("n_edges", C.c_int32), ("n_paths", C.c_int32),
+        ("vertex_id", i32p_), ("vertex_pos", f32p), ("vertex_type", i32p_), ("vertex_light", f32p),
+        ("vertex_samples", i32p_), ("vertex_range", f32p), ("vertex_coors", i32p_),
+        ("edge_id", i32p_), ("edge_from", i32p_), ("edge_to", i32p_), ("edge_samples", i32p_),
+        ("path_id", i32p_), ("path_offset", C.POINTER(C.c_int64)), ("path_vertices", i32p_),
+    ]
+
+
 class avr_render_desc(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32),

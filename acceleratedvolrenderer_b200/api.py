@@ -13,8 +13,8 @@ import os
 
 import numpy as np
 
-from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_grid_desc,
-                   avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
+from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
+                   avr_grid_desc, avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
 
@@ -36,7 +36,8 @@ ABI_SYMBOLS = [
     "avr_medium_is_emissive", "avr_medium_bounds", "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
-    "avr_graph_create", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
+    "avr_graph_create", "avr_graph_create_from_edges", "avr_graph_get_csr", "avr_graph_file_read",
+    "avr_graph_file_write", "avr_graph_file_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
 ]
@@ -64,11 +65,13 @@ def load_library():
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
-                        "avr_graph_destroy"):
+                        "avr_graph_destroy", "avr_graph_file_free"):
             fn.restype = C.c_int
     lib.avr_ctx_destroy.restype = None
     lib.avr_medium_destroy.restype = None
     lib.avr_graph_destroy.restype = None
+    lib.avr_graph_file_free.restype = None
+    lib.avr_graph_file_free.argtypes = [C.c_void_p]
     _lib = lib
     return lib
 
@@ -180,6 +183,93 @@ class Context:
                                              _p(col, i32p), _p(val), C.byref(h)))
         return Graph(self, h, rowptr.size - 1, col.size)
 
+    # LightingCalculator::GetTransportMatrix on the device, from vertex sample counts and an edge list
+    def create_graph_from_edges(self, vertex_samples, edge_from, edge_to, edge_samples):
+        vs = np.ascontiguousarray(vertex_samples, dtype=np.int32)
+        ef = np.ascontiguousarray(edge_from, dtype=np.int32); et = np.ascontiguousarray(edge_to, dtype=np.int32)
+        es = np.ascontiguousarray(edge_samples, dtype=np.int32)
+        h = C.c_void_p()
+        self.check(self.lib.avr_graph_create_from_edges(self.h, C.c_int32(vs.size), _p(vs, i32p), C.c_int64(ef.size),
+                                                        _p(ef, i32p), _p(et, i32p), _p(es, i32p), C.byref(h)))
+        g = Graph(self, h, vs.size, 0)
+        g.nnz = g.csr_sizes()[1]
+        return g
+
+
+class GraphFile:
+    """The fork's graph text file (src/graph/graph.cpp:284-416, :644-663) as numpy arrays.  Host-only:
+    needs the library but no GPU.  Fields that a flag switches off are None."""
+
+    FIELDS = ("vertex_id", "vertex_pos", "vertex_type", "vertex_light", "vertex_samples", "vertex_range",
+              "vertex_coors", "edge_id", "edge_from", "edge_to", "edge_samples", "path_id", "path_offset",
+              "path_vertices")
+
+    def __init__(self, vertex_radius, vertex_id, vertex_pos, *, description="basic", vertex_type=None, vertex_light=None,
+                 vertex_samples=None, vertex_range=None, vertex_coors=None, edge_id=None, edge_from=None, edge_to=None,
+                 edge_samples=None, path_id=None, path_offset=None, path_vertices=None, cur_ids=(0, 0, 0)):
+        i32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.int32)  # noqa: E731
+        f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float32)  # noqa: E731
+        self.description, self.vertex_radius, self.cur_ids = description, float(vertex_radius), tuple(cur_ids)
+        self.vertex_id, self.vertex_pos = i32(vertex_id), f32(vertex_pos)
+        self.vertex_type, self.vertex_light, self.vertex_samples = i32(vertex_type), f32(vertex_light), i32(vertex_samples)
+        self.vertex_range, self.vertex_coors = f32(vertex_range), i32(vertex_coors)
+        self.edge_id, self.edge_from, self.edge_to, self.edge_samples = i32(edge_id), i32(edge_from), i32(edge_to), i32(edge_samples)
+        self.path_id, self.path_vertices = i32(path_id), i32(path_vertices)
+        self.path_offset = None if path_offset is None else np.ascontiguousarray(path_offset, dtype=np.int64)
+
+    # FreeGraph::ReadFromDisk
+    @staticmethod
+    def read(path):
+        lib = load_library()
+        h = C.POINTER(avr_graph_file)()
+        st = lib.avr_graph_file_read(str(path).encode(), C.byref(h))
+        if st != 0:
+            raise AvrError(st, lib.avr_last_error(None).decode())
+        c = h.contents
+        nv, ne, npth = c.n_vertices, c.n_edges, c.n_paths
+
+        def arr(ptr, n, dt):
+            return None if not ptr else np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True)
+
+        npv = int(c.path_offset[npth]) if c.path_offset else 0
+        g = GraphFile(c.vertex_radius, arr(c.vertex_id, nv, np.int32), arr(c.vertex_pos, 3 * nv, np.float32),
+                      description=c.description.decode(), vertex_type=arr(c.vertex_type, nv, np.int32),
+                      vertex_light=arr(c.vertex_light, nv, np.float32), vertex_samples=arr(c.vertex_samples, nv, np.int32),
+                      vertex_range=arr(c.vertex_range, nv, np.float32), vertex_coors=arr(c.vertex_coors, 3 * nv, np.int32),
+                      edge_id=arr(c.edge_id, ne, np.int32), edge_from=arr(c.edge_from, ne, np.int32),
+                      edge_to=arr(c.edge_to, ne, np.int32), edge_samples=arr(c.edge_samples, ne, np.int32),
+                      path_id=arr(c.path_id, npth, np.int32), path_offset=arr(c.path_offset, npth + 1, np.int64),
+                      path_vertices=arr(c.path_vertices, npv, np.int32),
+                      cur_ids=(c.cur_vertex_id, c.cur_edge_id, c.cur_path_id))
+        g.flags = (c.use_coors, c.use_samples, c.use_ray_vertex_types, c.use_lighting, c.use_render_search_range)
+        g.counts = (nv, ne, npth)
+        if g.vertex_pos is not None:
+            g.vertex_pos = g.vertex_pos.reshape(-1, 3)
+        if g.vertex_coors is not None:
+            g.vertex_coors = g.vertex_coors.reshape(-1, 3)
+        lib.avr_graph_file_free(h)
+        return g
+
+    # Graph::WriteToDisk; flags = (useCoors, useSamples, useRayVertexTypes, useLighting, useRenderSearchRange),
+    # options = (writeVertices, writeEdges, writePaths) as graph::StreamFlags / StreamOptions
+    def write(self, path, flags, options=(1, 1, 1)):
+        lib = load_library()
+        c = avr_graph_file()
+        c.description = self.description.encode()
+        c.vertex_radius = self.vertex_radius
+        (c.use_coors, c.use_samples, c.use_ray_vertex_types, c.use_lighting, c.use_render_search_range) = [int(bool(f)) for f in flags]
+        c.cur_vertex_id, c.cur_edge_id, c.cur_path_id = self.cur_ids
+        c.n_vertices = self.vertex_id.size if options[0] and self.vertex_id is not None else 0
+        c.n_edges = self.edge_id.size if options[1] and self.edge_id is not None else 0
+        c.n_paths = self.path_id.size if options[2] and self.path_id is not None else 0
+        for name in self.FIELDS:
+            a = getattr(self, name)
+            if a is not None and a.size:
+                setattr(c, name, a.ctypes.data_as(dict(avr_graph_file._fields_)[name]))
+        st = lib.avr_graph_file_write(str(path).encode(), C.byref(c))
+        if st != 0:
+            raise AvrError(st, lib.avr_last_error(None).decode())
+
 
 class Medium:
     def __init__(self, ctx, h, desc):
@@ -270,6 +360,18 @@ class Graph:
         if self.h:
             self.lib.avr_graph_destroy(self.h)
             self.h = None
+
+    def csr_sizes(self):
+        n = C.c_int32(); nnz = C.c_int64()
+        self.ctx.check(self.lib.avr_graph_get_csr(self.h, C.byref(n), C.byref(nnz), None, None, None))
+        return int(n.value), int(nnz.value)
+
+    def csr(self):
+        n, nnz = self.csr_sizes()
+        rowptr = np.zeros(n + 1, np.int64); col = np.zeros(nnz, np.int32); val = np.zeros(nnz, np.float32)
+        self.ctx.check(self.lib.avr_graph_get_csr(self.h, None, None, _p(rowptr, i64p), _p(col, i32p) if nnz else None,
+                                                  _p(val) if nnz else None))
+        return rowptr, col, val
 
     def compute_final_light(self, L0, bounces):  # LightingCalculator::ComputeFinalLight
         L0 = _f32(L0)

@@ -227,3 +227,23 @@ def random_graph(n, avg_deg=4, seed=3, albedo=0.95):
     rowsum = np.bincount(rows, weights=w, minlength=n).astype(np.float32)
     val = (w / np.maximum(rowsum[rows], 1e-20) * albedo).astype(np.float32)
     return rowptr, col, val
+
+
+def random_edge_graph(n, n_edges, seed=3):
+    """A FreeGraph-like record set (what FreeGraphBuilder leaves behind, src/graph/free/free_graph_builder.cpp):
+    vertices with positions / sample counts, an edge list with repeated (from, to) pairs, self loops and a few
+    edges to vertices that do not exist (Graph::AddEdge merges the first and drops the last), paths."""
+    rng = np.random.default_rng(seed)
+    pos = rng.normal(size=(n, 3)).astype(np.float32)
+    efrom = rng.integers(0, n, n_edges).astype(np.int32)
+    eto = np.clip(efrom + np.rint(rng.normal(0, 3, n_edges)).astype(np.int64), -2, n + 1).astype(np.int32)
+    dup = rng.integers(0, n_edges, n_edges // 5)          # repeat a fifth of the pairs
+    efrom = np.r_[efrom, efrom[dup]].astype(np.int32); eto = np.r_[eto, eto[dup]].astype(np.int32)
+    esamples = rng.integers(1, 6, efrom.size).astype(np.int32)
+    vsamples = (np.bincount(efrom, weights=esamples, minlength=n)[:n] + rng.integers(1, 4, n)).astype(np.int32)
+    plen = rng.integers(1, 6, max(1, n // 10))
+    poff = np.r_[0, np.cumsum(plen)].astype(np.int64)
+    pverts = rng.integers(0, n, int(poff[-1])).astype(np.int32)
+    return dict(pos=pos, vsamples=vsamples, efrom=efrom, eto=eto, esamples=esamples, poff=poff, pverts=pverts,
+                vlight=rng.random(n).astype(np.float32) * 3, vrange=(rng.random(n).astype(np.float32) + 0.01) * 0.2,
+                vtype=rng.integers(0, 5, n).astype(np.int32), vcoors=rng.integers(-50, 50, (n, 3)).astype(np.int32))

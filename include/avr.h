@@ -286,6 +286,19 @@ avr_status avr_graph_create(avr_ctx *ctx, int32_t n_vertices, int64_t nnz, const
                             const int32_t *col, const float *val, avr_graph **out);
 void avr_graph_destroy(avr_graph *g);
 
+/* LightingCalculator::GetTransportMatrix itself (src/graph/lighting_calculator.cpp:61-82) on the
+ * device, from what a graph file / FreeGraph holds: per-vertex `samples` and the edge list
+ * {from, to, samples}.  Follows Graph::AddEdge (src/graph/graph.cpp:202-235): edges whose endpoints are
+ * not vertices (ids outside [0, n_vertices)) are dropped, edges with the same (from, to) are merged by
+ * adding their samples; val = float(edge samples) / float(vertex samples of `from`).  Rows come out
+ * with ascending column indices (std::map outEdges / Eigen column order). */
+avr_status avr_graph_create_from_edges(avr_ctx *ctx, int32_t n_vertices, const int32_t *vertex_samples,
+                                       int64_t n_edges, const int32_t *edge_from, const int32_t *edge_to,
+                                       const int32_t *edge_samples, avr_graph **out);
+/* Size and contents of the device CSR (parity surface for the call above; buffers may be NULL). */
+avr_status avr_graph_get_csr(avr_graph *g, int32_t *n_vertices, int64_t *nnz, int64_t *rowptr, int32_t *col,
+                             float *val);
+
 /* LightingCalculator::ComputeFinalLight (src/graph/lighting_calculator.cpp:23-59):
  * total = L0; cur = L0; repeat `bounces`: cur = T*cur; stop BEFORE adding if any NaN/Inf;
  * total += cur.  iters_done = the function's return value. */
@@ -326,6 +339,40 @@ avr_status avr_render_graph(avr_ctx *ctx, avr_medium *m, avr_graph *g, const avr
 avr_status avr_graph_light_rays(avr_medium *m, const float *rays, const int32_t *pixel,
                                 const float *ts, int64_t n, int32_t iterations, int32_t sampler_seed,
                                 const float lambda[4], float *out);
+
+/* ---- graph text files (src/graph/graph.cpp:284-416 WriteToStream/ReadFromStream, :644-663 FreeGraph;
+ * layout in files/format.txt) ----------------------------------------------------------------------
+ *   line 1: description (one token, e.g. "basic")      line 2: "free" vertexRadius
+ *   line 3: five True/False flags: useCoors useSamples useRayVertexTypes useLighting useRenderSearchRange
+ *   line 4: curVertexId curEdgeId curPathId numVertices numEdges numPaths
+ *   vertices: id x y z [type] [lightScalar] [samples] [renderSearchRange] [cx cy cz]
+ *   edges:    id from to [samples]            paths: id length v0 v1 ...
+ * Floats are written as the reference's `ostream << float` does (6 significant digits, %g).  Arrays
+ * that a flag switches off are NULL.  Pure host code (no CUDA device needed). */
+typedef struct avr_graph_file {
+    char description[64];
+    float vertex_radius;
+    int32_t use_coors, use_samples, use_ray_vertex_types, use_lighting, use_render_search_range;
+    int32_t cur_vertex_id, cur_edge_id, cur_path_id;
+    int32_t n_vertices, n_edges, n_paths;
+    int32_t *vertex_id;        /* n_vertices                                                   */
+    float *vertex_pos;         /* 3 * n_vertices                                               */
+    int32_t *vertex_type;      /* RayVertexType, src/graph/graph.h:38-44                       */
+    float *vertex_light;       /* lightScalar                                                  */
+    int32_t *vertex_samples;
+    float *vertex_range;       /* renderSearchRange                                            */
+    int32_t *vertex_coors;     /* 3 * n_vertices                                               */
+    int32_t *edge_id, *edge_from, *edge_to, *edge_samples;
+    int32_t *path_id;
+    int64_t *path_offset;      /* n_paths + 1                                                  */
+    int32_t *path_vertices;    /* path_offset[n_paths]                                         */
+} avr_graph_file;
+
+/* FreeGraph::ReadFromDisk (graph.cpp:657-663).  *out is allocated by the library. */
+avr_status avr_graph_file_read(const char *path, avr_graph_file **out);
+/* Graph::WriteToDisk + FreeGraph::WriteToStream (graph.cpp:419-433, :644-648). */
+avr_status avr_graph_file_write(const char *path, const avr_graph_file *g);
+void avr_graph_file_free(avr_graph_file *g);
 
 /* Parity probe for the EXACT path's restated scalar functions: kind 0 = logf (glibc algorithm),
  * 1 = sinf, 2 = cosf (glibc), 3 = FastExp CPU branch (util/math.h:453-474).  Host buffers. */

@@ -3,7 +3,7 @@
 // into oracle/liboracle.so.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs may load it.  Signatures match oracle/refprobe.cpp (ref_* symbols), which
 // runs the same calls through the reference's own templates.
-#include "restate_graph.hpp"
+#include "restate_graphfile.hpp"
 #include "restate_tmaj.hpp"
 #include "restate_volpath.hpp"
 

@@ -23,6 +23,10 @@
 
 #include <Eigen/Sparse>
 #include <graph/util.h>
+#include <graph/graph.h>
+#include <graph/lighting_calculator.h>
+
+#include <fstream>
 
 #include "../include/avr.h"
 
@@ -471,6 +475,119 @@ void ref_graph_light_rays(void *mp, const float *rays, const int32_t *pixel, con
         uint64_t idx = uint64_t(pixel[2 * i + 1]) * 65536ull + uint64_t(pixel[2 * i]);
         out[i] = graph::ComputeRaysToSphere(ray, std::nullopt, se, md, sampler, iterations, idx);
     }
+}
+
+
+// ---- src/graph: the fork's own FreeGraph (graph.cpp) and LightingCalculator (lighting_calculator.cpp) ----
+struct RefGraph {
+    graph::FreeGraph g;
+    explicit RefGraph(float r) : g(r) {}
+    RefGraph() = default;
+};
+// Build a FreeGraph the way FreeGraphBuilder / ReadFromStream do: AddVertex(id, p, data), AddEdge(id, from, to,
+// data) (graph.cpp:202-235: drops edges with unknown endpoints, merges duplicates), AddPath + AddVertexToPath.
+void *ref_graph_build(float vertex_radius, int32_t nv, const int32_t *vid, const float *pos, const int32_t *vtype,
+                      const float *vlight, const int32_t *vsamples, const float *vrange, const int32_t *vcoors,
+                      int32_t ne, const int32_t *eid, const int32_t *efrom, const int32_t *eto, const int32_t *esamples,
+                      int32_t np, const int32_t *pid, const int64_t *poff, const int32_t *pverts) {
+    RefGraph *rg = new RefGraph(vertex_radius);
+    for (int i = 0; i < nv; ++i) {
+        graph::VertexData d{vtype ? graph::RayVertexType(vtype[i]) : graph::none, vlight ? vlight[i] : -1.f,
+                            vsamples ? vsamples[i] : 0, vrange ? vrange[i] : -1.f};
+        graph::Vertex &v = rg->g.AddVertex(vid[i], Point3f(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]), d);
+        if (vcoors) v.coors = Point3i(vcoors[3 * i], vcoors[3 * i + 1], vcoors[3 * i + 2]);
+    }
+    for (int i = 0; i < ne; ++i) rg->g.AddEdge(eid[i], efrom[i], eto[i], graph::EdgeData{esamples ? esamples[i] : 0});
+    for (int i = 0; i < np; ++i) {
+        graph::Path &p = rg->g.AddPath(pid[i], graph::PathData{});
+        for (int64_t j = poff[i]; j < poff[i + 1]; ++j) rg->g.AddVertexToPath(pverts[j], p.id);
+    }
+    return rg;
+}
+void ref_graph_free(void *h) { delete (RefGraph *)h; }
+// Graph::WriteToDisk (graph.cpp:419-433) minus its "files/graphs/" path prefix
+void ref_graph_write(void *h, const char *path, const char *desc, const int32_t flags[5], const int32_t opts[3]) {
+    RefGraph *rg = (RefGraph *)h;
+    rg->g.streamFlags = graph::StreamFlags{flags[0] != 0, flags[1] != 0, flags[2] != 0, flags[3] != 0, flags[4] != 0};
+    rg->g.streamOptions = graph::StreamOptions{opts[0] != 0, opts[1] != 0, opts[2] != 0};
+    std::ofstream file(path);
+    file << desc << '\n';  // NEW, graph.cpp:11
+    rg->g.WriteToStream(file);
+    file.close();
+}
+// FreeGraph::ReadFromDisk (graph.cpp:657-663) minus the path prefix
+void *ref_graph_read(const char *path) {
+    RefGraph *rg = new RefGraph();
+    std::ifstream file(path);
+    rg->g.ReadFromStream(file);
+    file.close();
+    return rg;
+}
+void ref_graph_counts(void *h, int32_t out[11], float *vertex_radius) {
+    RefGraph *rg = (RefGraph *)h;
+    const auto &f = rg->g.streamFlags;
+    out[0] = f && f->useCoors; out[1] = f && f->useSamples; out[2] = f && f->useRayVertexTypes;
+    out[3] = f && f->useLighting; out[4] = f && f->useRenderSearchRange;
+    out[5] = rg->g.GetCurVertexId(); out[6] = rg->g.GetCurEdgeId(); out[7] = rg->g.GetCurPathId();
+    out[8] = int(rg->g.GetVerticesConst().size()); out[9] = int(rg->g.GetEdgesConst().size());
+    out[10] = int(rg->g.GetPathsConst().size());
+    *vertex_radius = rg->g.GetVertexRadius();
+}
+// vertices / edges in ascending id order
+void ref_graph_get(void *h, int32_t *vid, float *pos, int32_t *vtype, float *vlight, int32_t *vsamples, float *vrange,
+                   int32_t *vcoors, int32_t *eid, int32_t *efrom, int32_t *eto, int32_t *esamples) {
+    RefGraph *rg = (RefGraph *)h;
+    std::vector<int> ids;
+    for (auto &kv : rg->g.GetVerticesConst()) ids.push_back(kv.first);
+    std::sort(ids.begin(), ids.end());
+    for (size_t i = 0; i < ids.size(); ++i) {
+        const graph::Vertex &v = rg->g.GetVerticesConst().at(ids[i]);
+        vid[i] = v.id;
+        pos[3 * i] = v.point.x; pos[3 * i + 1] = v.point.y; pos[3 * i + 2] = v.point.z;
+        vtype[i] = int(v.data.type); vlight[i] = v.data.lightScalar; vsamples[i] = v.data.samples;
+        vrange[i] = v.data.renderSearchRange;
+        for (int k = 0; k < 3; ++k) vcoors[3 * i + k] = v.coors ? (*v.coors)[k] : 0;
+    }
+    ids.clear();
+    for (auto &kv : rg->g.GetEdgesConst()) ids.push_back(kv.first);
+    std::sort(ids.begin(), ids.end());
+    for (size_t i = 0; i < ids.size(); ++i) {
+        const graph::Edge &e = rg->g.GetEdgesConst().at(ids[i]);
+        eid[i] = e.id; efrom[i] = e.from; eto[i] = e.to; esamples[i] = e.data.samples;
+    }
+}
+// LightingCalculator::GetTransportMatrix (lighting_calculator.cpp:61-82) and ComputeFinalLight(lightVec,
+// transportMat, 0) (:23-59), the fork's own member functions.  CSR out: rows ascending, columns ascending.
+// Returns nnz; total (n floats) = vertex.data.lightScalar after ComputeFinalLight when L0 != NULL.
+int64_t ref_graph_transport(void *h, int64_t cap, int64_t *rowptr, int32_t *col, float *val, const float *L0,
+                            int32_t bounces, float *total, int32_t *iters) {
+    RefGraph *rg = (RefGraph *)h;
+    util::MediumData md;
+    IndependentSampler is(1, 0);
+    graph::LightingCalculatorConfig cfg{1, 1, {bounces}, false};
+    graph::LightingCalculator lc(rg->g, md, Vector3f(0, 0, 1), Sampler(&is), cfg, true);
+    graph::SparseMat T = lc.GetTransportMatrix();
+    int n = int(rg->g.GetVerticesConst().size());
+    std::vector<std::vector<std::pair<int, float>>> rows(n);
+    for (int c = 0; c < T.outerSize(); ++c)
+        for (graph::SparseMat::InnerIterator it(T, c); it; ++it) rows[it.row()].emplace_back(int(it.col()), it.value());
+    int64_t k = 0;
+    for (int r = 0; r < n; ++r) {
+        rowptr[r] = k;
+        std::sort(rows[r].begin(), rows[r].end());
+        for (auto &e : rows[r]) {
+            if (k < cap) { col[k] = e.first; val[k] = e.second; }
+            ++k;
+        }
+    }
+    rowptr[n] = k;
+    if (L0) {
+        graph::SparseVec lightVec(n);
+        for (int i = 0; i < n; ++i) lightVec.coeffRef(i) = L0[i];
+        *iters = lc.ComputeFinalLight(lightVec, T, 0);
+        for (int i = 0; i < n; ++i) total[i] = rg->g.GetVerticesConst().at(i).data.lightScalar;
+    }
+    return k;
 }
 
 }  // extern "C"

@@ -7,6 +7,8 @@
 #include <pbrt/util/bluenoise.h>
 #include <pbrt/util/log.h>
 #include <pbrt/util/parallel.h>
+#include <pbrt/util/progressreporter.h>
+#include <pbrt/util/error.h>
 #include <pbrt/util/print.h>
 #include <pbrt/util/spectrum.h>
 #include <pbrt/util/stats.h>
@@ -24,6 +26,16 @@ void LogFatal(LogLevel, const char *file, int line, const char *s) {
 namespace logging { LogLevel logLevel = LogLevel::Error; }
 void Log(LogLevel, const char *file, int line, const char *s) { std::fprintf(stderr, "refprobe: %s:%d: %s\n", file, line, s); }
 void ParallelFor(int64_t start, int64_t end, std::function<void(int64_t, int64_t)> func) { func(start, end); }
+// src/graph prints progress bars and exits on errors; neither is arithmetic of the path.
+ProgressReporter::ProgressReporter(int64_t totalWork, std::string title, bool, bool)
+    : totalWork(totalWork), title(std::move(title)), quiet(true), workDone(0), exitThread(true), printPlusStatus(0) {}
+ProgressReporter::~ProgressReporter() {}
+void ProgressReporter::Done() {}
+void ErrorExit(const FileLoc *, const char *message) {
+    std::fprintf(stderr, "refprobe: reference ErrorExit: %s\n", message);
+    std::abort();
+}
+int RunningThreads() { return 1; }
 StatRegisterer::StatRegisterer(AccumFunc, PixelAccumFunc) {}
 void StatsAccumulator::ReportMemoryCounter(const char *, int64_t) {}
 void StatsAccumulator::ReportPercentage(const char *, int64_t, int64_t) {}

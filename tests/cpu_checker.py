@@ -212,6 +212,25 @@ class Checker:
                                         _p(val, f32p), _p(L0, f32p), C.c_int32(bounces), _p(total, f32p))
         return total, it
 
+    def graph_build(self, vertex_radius, vid, pos, *, vtype=None, vlight=None, vsamples=None, vrange=None, vcoors=None,
+                    eid=(), efrom=(), eto=(), esamples=None, pid=(), poff=(0,), pverts=()):
+        i32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.int32)  # noqa: E731
+        opt = lambda a, t: None if a is None else _p(a, t)  # noqa: E731
+        vid = i32(vid); pos = f32(pos); vtype = i32(vtype); vsamples = i32(vsamples); vcoors = i32(vcoors)
+        vlight = None if vlight is None else f32(vlight); vrange = None if vrange is None else f32(vrange)
+        eid = i32(eid); efrom = i32(efrom); eto = i32(eto); esamples = i32(esamples)
+        pid = i32(pid); poff = np.ascontiguousarray(poff, dtype=np.int64); pverts = i32(pverts)
+        fn = self.fn("graph_build"); fn.restype = C.c_void_p
+        h = fn(C.c_float(vertex_radius), C.c_int32(vid.size), _p(vid, i32p), _p(pos, f32p), opt(vtype, i32p),
+               opt(vlight, f32p), opt(vsamples, i32p), opt(vrange, f32p), opt(vcoors, i32p), C.c_int32(eid.size),
+               _p(eid, i32p), _p(efrom, i32p), _p(eto, i32p), opt(esamples, i32p), C.c_int32(pid.size), _p(pid, i32p),
+               _p(poff, i64p), _p(pverts, i32p))
+        return CheckerGraph(self, h)
+
+    def graph_read(self, path):
+        fn = self.fn("graph_read"); fn.restype = C.c_void_p
+        return CheckerGraph(self, fn(path.encode()))
+
     def graph_connect(self, pos, light, search_range, vertex_radius, points):
         pos = f32(pos); light = f32(light); points = f32(points); n = light.size; npts = points.size // 3
         rng = None if search_range is None else f32(search_range)
@@ -220,6 +239,51 @@ class Checker:
                                  _p(rng, f32p) if rng is not None else None, C.c_float(vertex_radius),
                                  _p(points, f32p), C.c_int64(npts), _p(out, f32p))
         return out
+
+
+class CheckerGraph:
+    """A FreeGraph held by the checker (reference: the fork's own graph::FreeGraph; oracle: FreeGraphR)."""
+
+    def __init__(self, ck, handle):
+        self.ck, self.h = ck, C.c_void_p(handle)
+
+    def close(self):
+        if self.h:
+            self.ck.fn("graph_free")(self.h)
+            self.h = None
+
+    def write(self, path, desc, flags, opts=(1, 1, 1)):
+        fl = np.asarray(flags, dtype=np.int32); op = np.asarray(opts, dtype=np.int32)
+        self.ck.fn("graph_write")(self.h, path.encode(), desc.encode(), _p(fl, i32p), _p(op, i32p))
+
+    def counts(self):
+        out = np.zeros(11, dtype=np.int32); r = C.c_float()
+        self.ck.fn("graph_counts")(self.h, _p(out, i32p), C.byref(r))
+        return out, np.float32(r.value)
+
+    def get(self):
+        c, _ = self.counts()
+        nv, ne = int(c[8]), int(c[9])
+        d = dict(vid=np.zeros(nv, np.int32), pos=np.zeros((nv, 3), np.float32), vtype=np.zeros(nv, np.int32),
+                 vlight=np.zeros(nv, np.float32), vsamples=np.zeros(nv, np.int32), vrange=np.zeros(nv, np.float32),
+                 vcoors=np.zeros((nv, 3), np.int32), eid=np.zeros(ne, np.int32), efrom=np.zeros(ne, np.int32),
+                 eto=np.zeros(ne, np.int32), esamples=np.zeros(ne, np.int32))
+        self.ck.fn("graph_get")(self.h, _p(d["vid"], i32p), _p(d["pos"], f32p), _p(d["vtype"], i32p), _p(d["vlight"], f32p),
+                                _p(d["vsamples"], i32p), _p(d["vrange"], f32p), _p(d["vcoors"], i32p), _p(d["eid"], i32p),
+                                _p(d["efrom"], i32p), _p(d["eto"], i32p), _p(d["esamples"], i32p))
+        return d
+
+    def transport(self, L0=None, bounces=0):
+        """LightingCalculator::GetTransportMatrix as CSR (+ ComputeFinalLight(L0, T) when L0 is given)."""
+        c, _ = self.counts()
+        n, cap = int(c[8]), int(c[9])
+        rowptr = np.zeros(n + 1, np.int64); col = np.zeros(max(cap, 1), np.int32); val = np.zeros(max(cap, 1), np.float32)
+        total = np.zeros(n, np.float32); iters = C.c_int32(-1)
+        fn = self.ck.fn("graph_transport"); fn.restype = C.c_int64
+        l0 = None if L0 is None else f32(L0)
+        nnz = fn(self.h, C.c_int64(cap), _p(rowptr, i64p), _p(col, i32p), _p(val, f32p),
+                 _p(l0, f32p) if l0 is not None else None, C.c_int32(bounces), _p(total, f32p), C.byref(iters))
+        return rowptr, col[:nnz].copy(), val[:nnz].copy(), total, iters.value
 
 
 class CheckerMedium:

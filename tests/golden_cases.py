@@ -285,5 +285,51 @@ def case_graph(ck):
     return out
 
 
+def case_graphfile(ck):
+    """src/graph: FreeGraph containers (AddEdge merge / drop, graph.cpp:202-235), the text format
+    (graph.cpp:284-416, :644-655; bytes of the written file), LightingCalculator::GetTransportMatrix
+    (lighting_calculator.cpp:61-82) and ComputeFinalLight over that matrix (:23-59)."""
+    import tempfile
+    out = {}
+    rng = np.random.default_rng(12)
+    for n, ne in ((40, 150), (1500, 7000)):
+        r = scenes.random_edge_graph(n, ne, seed=n)
+        vid = np.arange(n, dtype=np.int32)
+        eid = np.arange(r["efrom"].size, dtype=np.int32)
+        pid = np.arange(r["poff"].size - 1, dtype=np.int32)
+        g = ck.graph_build(0.0125, vid, r["pos"], vtype=r["vtype"], vlight=r["vlight"], vsamples=r["vsamples"],
+                           vrange=r["vrange"], vcoors=r["vcoors"], eid=eid, efrom=r["efrom"], eto=r["eto"],
+                           esamples=r["esamples"], pid=pid, poff=r["poff"], pverts=r["pverts"])
+        for k, v in g.get().items():
+            out[f"g{n}_{k}"] = v
+        L0 = rng.random(n, dtype=np.float32)
+        for b in (0, 3):
+            rowptr, col, val, total, iters = g.transport(L0, b)
+            out[f"g{n}_b{b}_total"] = total
+            out[f"g{n}_b{b}_iters"] = np.array([iters], dtype=np.int32)
+        out[f"g{n}_rowptr"], out[f"g{n}_col"], out[f"g{n}_val"] = rowptr, col, val
+        with tempfile.TemporaryDirectory() as td:
+            # what graph_maker writes (cmd/graph_maker.cpp:171-173): vertices only, lighting + search range
+            for tag, flags, opts in (("maker", (0, 0, 0, 1, 1), (1, 0, 0)), ("full", (1, 1, 1, 1, 1), (1, 1, 1)),
+                                     ("bare", (0, 0, 0, 0, 0), (1, 1, 0))):
+                path = f"{td}/{tag}.txt"
+                g.write(path, "basic", flags, opts)
+                data = open(path, "rb").read()
+                # records appear in the writer's container order (an unordered_map in the reference):
+                # compare the file as a header + a sorted set of record lines
+                lines = data.split(b"\n")
+                out[f"g{n}_{tag}_header"] = np.frombuffer(b"\n".join(lines[:4]), dtype=np.uint8).copy()
+                out[f"g{n}_{tag}_records"] = np.frombuffer(b"\n".join(sorted(lines[4:])), dtype=np.uint8).copy()
+                g2 = ck.graph_read(path)
+                c, radius = g2.counts()
+                out[f"g{n}_{tag}_counts"] = c
+                out[f"g{n}_{tag}_radius"] = np.array([radius], dtype=np.float32)
+                for k, v in g2.get().items():
+                    out[f"g{n}_{tag}_read_{k}"] = v
+                g2.close()
+        g.close()
+    return out
+
+
 CASES = {"scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
-         "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph}
+         "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph, "graphfile": case_graphfile}

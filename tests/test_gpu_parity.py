@@ -227,6 +227,45 @@ def test_nanovdb_index_space_lookup(ctx, orc):
         m.close()
 
 
+@pytest.mark.parametrize("n,ne", [(40, 150), (1500, 7000), (200000, 1200000)])
+def test_transport_matrix_from_edges_bit_exact(ctx, orc, n, ne):
+    """LightingCalculator::GetTransportMatrix on the device (sort + reduce-by-key over the edge list) against
+    the oracle's std::map walk (pinned to the fork's own FreeGraph/LightingCalculator by the "graphfile"
+    golden case): CSR structure and values bit-exact, then ComputeFinalLight over it bit-exact."""
+    r = scenes.random_edge_graph(n, ne, seed=n)
+    go = orc.graph_build(0.0125, np.arange(n), r["pos"], vsamples=r["vsamples"], eid=np.arange(r["efrom"].size),
+                         efrom=r["efrom"], eto=r["eto"], esamples=r["esamples"])
+    L0 = np.random.default_rng(1).random(n, dtype=np.float32)
+    rowptr, col, val, total, iters = go.transport(L0, 5)
+    go.close()
+    g = ctx.create_graph_from_edges(r["vsamples"], r["efrom"], r["eto"], r["esamples"])
+    grow, gcol, gval = g.csr()
+    assert np.array_equal(grow, rowptr) and np.array_equal(gcol, col)
+    assert bits_equal(gval, val)
+    assert (r["eto"] < 0).any() or (r["eto"] >= n).any()      # dropped edges were exercised
+    assert col.size < r["efrom"].size                          # merged duplicates were exercised
+    gtotal, giters = g.compute_final_light(L0, 5)
+    assert giters == iters and bits_equal(gtotal, total)
+    g.close()
+
+
+def test_transport_matrix_edge_cases(ctx):
+    g = ctx.create_graph_from_edges([3, 2, 1], [], [], [])     # no edges at all
+    rowptr, col, val = g.csr()
+    assert np.array_equal(rowptr, [0, 0, 0, 0]) and col.size == 0
+    total, it = g.compute_final_light([1, 2, 3], 4)
+    assert np.array_equal(total, [1, 2, 3]) and it == 4
+    g.close()
+    g = ctx.create_graph_from_edges([3, 2, 1], [5, -1, 0], [0, 1, 7], [1, 1, 1])   # every edge dangling
+    assert g.csr()[1].size == 0
+    g.close()
+    g = ctx.create_graph_from_edges([4, 0], [0, 0, 0, 1], [1, 1, 0, 0], [1, 2, 4, 3])  # zero-sample vertex -> inf
+    rowptr, col, val = g.csr()
+    assert np.array_equal(rowptr, [0, 2, 3]) and np.array_equal(col, [0, 1, 0])
+    assert val[0] == 1.0 and val[1] == 0.75 and np.isinf(val[2])
+    g.close()
+
+
 def test_error_behaviour(ctx):
     """Argument misuse returns a status + message (the host adapter turns it into ErrorExit)."""
     from acceleratedvolrenderer_b200.api import AvrError

@@ -132,6 +132,22 @@ def scale_translate(scale, translate):
     return m.astype(np.float32)
 
 
+def distant_light_scene_radius(boundary_type, boundary):
+    """DistantLight::Preprocess (lights.h:269-271): sceneBounds.BoundingSphere(&c, &sceneRadius) over the
+    aggregate's bounds, in fp32 as the reference computes it.  The bounds of a Shape "sphere" are the box
+    c +- r (Sphere::Bounds through Transform::operator()(Bounds3f)), so sceneRadius = |(r, r, r)|, not r."""
+    f = np.float32
+    b = [f(v) for v in boundary]
+    if boundary_type == 0:
+        lo = [f(b[i] - b[3]) for i in range(3)]
+        hi = [f(b[i] + b[3]) for i in range(3)]
+    else:
+        lo, hi = b[:3], b[3:6]
+    ctr = [f(f(lo[i] + hi[i]) / f(2)) for i in range(3)]
+    d = [f(hi[i] - ctr[i]) for i in range(3)]
+    return float(np.sqrt(f(f(f(d[0] * d[0]) + f(d[1] * d[1])) + f(d[2] * d[2]))))
+
+
 def cloud_scene(density, *, width, height, spp, sigma_t=8.0, albedo=0.99, g=0.0, max_depth=5, fov=20.0,
                 eye=(0.0, 0.35, -3.2), light_dir=(0.4, 0.8, -0.45), light_scale=3.0, boundary="sphere",
                 majorant_res=(16, 16, 16), exact_math=1, sampler_seed=0, chromatic=False):
@@ -155,9 +171,10 @@ def cloud_scene(density, *, width, height, spp, sigma_t=8.0, albedo=0.99, g=0.0,
         btype, bvals = 0, (0.0, 0.0, 0.0, half_diag * 1.001)
     else:
         btype, bvals = 1, (-ext[0] / 2, -ext[1] / 2, -ext[2] / 2, ext[0] / 2, ext[1] / 2, ext[2] / 2)
+    scene_radius = distant_light_scene_radius(btype, bvals)
     xyz = cie_xyz_tables()
     rd = RenderDesc(width, height, spp, camera_from_raster=cfr, render_from_camera=rfc, light_dir=light_dir,
-                    light_spectrum=const_spectrum(light_scale), scene_radius=half_diag * 1.001,
+                    light_spectrum=const_spectrum(light_scale), scene_radius=scene_radius,
                     boundary_type=btype, boundary=bvals, sensor_rgb=xyz, max_depth=max_depth,
                     sampler_seed=sampler_seed, exact_math=exact_math, imaging_ratio=1.0 / CIE_Y_INTEGRAL * 100,
                     output_rgb_from_sensor=SRGB_FROM_XYZ.ravel())
@@ -183,13 +200,13 @@ def cloud_scene_nanovdb(density, *, temperature=None, voxel_size=1.0 / 64, le_sc
                     dtype=np.float32)
     _, rd = cloud_scene(fake, sigma_t=sigma_t, albedo=albedo, g=g, **kw)
     half_diag = 0.5 * float(np.linalg.norm(ext))
-    rd.c.scene_radius = half_diag * 1.001
     if rd.c.boundary_type == 0:
         for i, v in enumerate((0.0, 0.0, 0.0, half_diag * 1.001)):
             rd.c.boundary[i] = v
     else:
         for i, v in enumerate(tuple(-ext / 2) + tuple(ext / 2)):
             rd.c.boundary[i] = float(v)
+    rd.c.scene_radius = distant_light_scene_radius(rd.c.boundary_type, list(rd.c.boundary))
     return nd, rd
 
 

@@ -592,3 +592,8 @@ int64_t ref_graph_transport(void *h, int64_t cap, int64_t *rowptr, int32_t *col,
 
 }  // extern "C"
 #pragma GCC visibility pop
+
+// handle -> the reference Medium object (for refprobe_volpath.cpp)
+extern "C" __attribute__((visibility("default"))) const pbrt::Medium *ref_medium_ptr(void *m) {
+    return &((RefMedium *)m)->medium;
+}

@@ -1,0 +1,90 @@
+// oracle/refprobe_volpath.cpp — TEST INFRASTRUCTURE ONLY.
+//
+// Probe over the reference's OWN VolPathIntegrator (src/pbrt/cpu/integrators.cpp:962-1106 Li, :1282-1399
+// SampleLd), compiled from the sources where they lie under /root/reference together with its Sphere,
+// GeometricPrimitive, DistantLight, BVHLightSampler and IndependentSampler.  Builds the scene class of
+// include/avr.h in the reference's own objects (one grid medium inside a sphere with Material
+// "interface", one distant light) and evaluates pixel samples the way
+// RayIntegrator::EvaluatePixelSample does (:235-298): StartPixelSample, wavelengths from Get1D,
+// GetCameraSample (samplers.h:797-814), then Li on the camera ray.  Camera rays are passed in (the film /
+// camera classes need the reference's generated rgb2spec tables and OpenEXR and are not built here).
+// Everything the integrator references but never reaches for this scene class (surface materials,
+// textures, image IO, other shapes) is closed at link time by generated abort() stubs, see Makefile.
+#include <pbrt/cpu/aggregates.h>
+#include <pbrt/cpu/integrators.h>
+#include <pbrt/cpu/primitive.h>
+#include <pbrt/filters.h>
+#include <pbrt/lights.h>
+#include <pbrt/media.h>
+#include <pbrt/samplers.h>
+#include <pbrt/shapes.h>
+#include <pbrt/util/spectrum.h>
+
+using namespace pbrt;
+
+extern "C" const pbrt::Medium *ref_medium_ptr(void *m);  // refprobe.cpp
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+// samples: per sample {px, py, sampleIndex}; rays: per sample {o.xyz, d.xyz} (render space, as the oracle's
+// camera generates them).  out: 12 floats per sample {L[4], lambda[4], pdf[4]} (lambda/pdf after Li, which
+// may terminate secondary wavelengths).  info: {wi.xyz of the light as DistantLight::SampleLi computes it,
+// sceneRadius after Preprocess}.
+void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir[3], const float *light_spec,
+                    int32_t max_depth, int32_t sampler_seed, int32_t spp, const int32_t *samples, const float *rays,
+                    int64_t n, float *out, float *info) {
+    // --disable-texture-filtering: SurfaceInteraction::ComputeDifferentials (interaction.cpp:41-47) then
+    // skips the camera-based footprint estimate, the only use Li makes of the camera (none is built
+    // here); it feeds texture lookups only, which the "interface" boundary does not have.
+    static PBRTOptions opts;
+    opts.disableTextureFiltering = true;
+    Options = &opts;
+    Allocator alloc;
+    Medium medium = *ref_medium_ptr(medium_h);
+    // Shape "sphere" at Translate(c): shapes.cpp Sphere::Create defaults zmin = -radius, zmax = radius, phimax = 360
+    Transform *rfo = new Transform(Translate(Vector3f(sphere[0], sphere[1], sphere[2])));
+    Transform *ofr = new Transform(Inverse(*rfo));
+    Sphere *sph = new Sphere(rfo, ofr, false, sphere[3], -sphere[3], sphere[3], 360.f);
+    // Material "interface" = null material; MediumInterface(inside = medium, outside = none)
+    GeometricPrimitive *prim = new GeometricPrimitive(Shape(sph), Material(), Light(), MediumInterface(medium, nullptr));
+    Primitive aggregate(prim);
+    // LightSource "distant": renderFromLight maps +z to the direction towards the light
+    Vector3f w = Normalize(Vector3f(light_dir[0], light_dir[1], light_dir[2]));
+    Frame f = Frame::FromZ(w);
+    SquareMatrix<4> m(f.x.x, f.y.x, f.z.x, 0, f.x.y, f.y.y, f.z.y, 0, f.x.z, f.y.z, f.z.z, 0, 0, 0, 0, 1);
+    Transform renderFromLight(m);
+    DenselySampledSpectrum *Lemit = new DenselySampledSpectrum(
+        DenselySampledSpectrum::SampleFunction([&](Float l) { return light_spec[int(l) - 360]; }));
+    DistantLight *dl = new DistantLight(renderFromLight, Lemit, 1.f);
+    std::vector<Light> lights = {Light(dl)};
+    IndependentSampler proto(spp, sampler_seed);
+    VolPathIntegrator integrator(max_depth, Camera(), Sampler(&proto), aggregate, lights, "bvh", false);
+    Vector3f wi = Normalize(renderFromLight(Vector3f(0, 0, 1)));
+    info[0] = wi.x; info[1] = wi.y; info[2] = wi.z;
+    info[3] = dl->sceneRadius;
+    Filter filter = new BoxFilter(Vector2f(0.5f, 0.5f));
+    ScratchBuffer scratch(65536);
+    for (int64_t i = 0; i < n; ++i) {
+        IndependentSampler is(spp, sampler_seed);
+        Sampler sampler(&is);
+        Point2i pPixel(samples[3 * i], samples[3 * i + 1]);
+        sampler.StartPixelSample(pPixel, samples[3 * i + 2]);
+        Float lu = sampler.Get1D();
+        SampledWavelengths lambda = SampledWavelengths::SampleVisible(lu);  // RGBFilm::SampleWavelengths, film.h
+        CameraSample cs = GetCameraSample(sampler, pPixel, filter);
+        (void)cs;
+        const float *r = rays + 6 * i;
+        RayDifferential ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5]), 0.f, Medium());
+        SampledSpectrum L = integrator.Li(ray, lambda, sampler, scratch, nullptr);
+        scratch.Reset();
+        for (int k = 0; k < 4; ++k) {
+            out[12 * i + k] = L[k];
+            out[12 * i + 4 + k] = lambda[k];
+            out[12 * i + 8 + k] = lambda.PDF()[k];
+        }
+    }
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

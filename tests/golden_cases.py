@@ -333,3 +333,64 @@ def case_graphfile(ck):
 
 CASES = {"scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
          "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph, "graphfile": case_graphfile}
+
+
+# ---- VolPathIntegrator::Li as a whole (cpu/integrators.cpp:962-1106, :1282-1399) -----------------------
+# Not part of CASES: the comparison is by tolerance, not bit-exact.  The reference spawns rays at the
+# boundary sphere with its error-bound offsets (interaction.cpp), the restatement does not; positions then
+# differ in the last bits, and because the reference seeds every shadow ray's RNG from Hash(ray.o),
+# Hash(ray.d) (cpu/integrators.cpp:1338), next-event estimates de-correlate completely.  Hence two kinds:
+#   "lockstep": emissive medium + black light: every random number comes from the sampler streams, the
+#               two implementations walk the same path and per-sample radiance agrees to rounding;
+#   "image":    the full estimator (NEE on), compared as converged images against the reference's own
+#               seed-to-seed noise.
+def li_scenes():
+    from acceleratedvolrenderer_b200._abi import GridDesc
+    out = []
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    gd, rd = scenes.cloud_scene(dens, width=48, height=36, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8)
+    em = GridDesc(dens, gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=0.4, temperature=dens * 2500 + 200,
+                  lescale=dens * 0.5, le_norm=1.0)
+    black = scenes.cloud_scene(dens, width=48, height=36, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8,
+                               light_scale=0.0)[1]
+    out.append(("lockstep_grid", "uniformgrid", em, black))
+    d2 = dens.copy(); d2[d2 < 0.02] = 0
+    nd, rdn = scenes.cloud_scene_nanovdb(d2, temperature=(d2 * 2500 + 200).astype(np.float32), le_scale=0.4, width=40,
+                                         height=30, spp=4, sigma_t=18.0, albedo=0.95, g=0.4, max_depth=6, light_scale=0.0)
+    out.append(("lockstep_nanovdb", "nanovdb", nd, rdn))
+    gdc, rdc = scenes.cloud_scene(dens, width=32, height=24, spp=128, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=6,
+                                  chromatic=True)
+    out.append(("image_chromatic", "uniformgrid", gdc, rdc))
+    ndi, rdi = scenes.cloud_scene_nanovdb(d2, width=32, height=24, spp=128, sigma_t=18.0, albedo=0.95, g=0.4, max_depth=6)
+    out.append(("image_nanovdb", "nanovdb", ndi, rdi))
+    return out
+
+
+def li_medium(ck, kind, desc):
+    return ck.medium_uniformgrid(desc) if kind == "uniformgrid" else ck.medium_nanovdb(desc)
+
+
+def li_mono_image(samples12, rdesc):
+    """Per-pixel mean over samples of Average(L / pdf): the film estimate before the sensor response."""
+    x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+    L = samples12[:, :4].astype(np.float64); pdf = samples12[:, 8:12].astype(np.float64)
+    v = np.where(pdf > 0, L / np.where(pdf > 0, pdf, 1), 0).mean(axis=1)
+    return v.reshape(y1 - y0, x1 - x0, s1 - s0).mean(axis=2)
+
+
+def case_volpath_li(ck):
+    """Reference outputs kept in the fixture (ck = Checker("ref")), or the restatement's (Checker("orc"))."""
+    out = {}
+    for name, kind, desc, rd in li_scenes():
+        m = li_medium(ck, kind, desc)
+        if name.startswith("lockstep"):
+            smp, info = m.volpath_li(rd)
+            out[f"{name}_samples"] = smp
+            out[f"{name}_info"] = info
+        else:
+            for seed in (0, 1):
+                smp, info = m.volpath_li(rd.with_(sampler_seed=seed))
+                out[f"{name}_mono{seed}"] = li_mono_image(smp, rd).astype(np.float32)
+            out[f"{name}_info"] = info
+        m.close()
+    return out

@@ -230,11 +230,9 @@ class NanoVDBGrid:
         """Host-side equivalent of nanovdb::GridBuilder<float>(0)(dense over a box).getHandle(voxel_size,
         origin): the index box is that of the non-background voxels (GridBuilder.h:259-271), the map a
         uniform scale + translation (GridBuilder.h:535-560, Map::set NanoVDB.h:2045-2063), the world box
-        map(min) .. map(max+1) (GridStats.h:551-563).  voxel_size must be a power of two so that the
-        fma-based applyMap is reproduced exactly by a multiply and an add."""
+        map(min) .. map(max+1) (GridStats.h:551-563)."""
+        from fractions import Fraction
         dense = _f32(dense)
-        m, e = np.frexp(voxel_size)
-        assert m == 0.5, "voxel_size must be a power of two"
         nzv = np.argwhere(dense != 0)
         assert len(nzv), "empty grid"
         lo = nzv.min(axis=0); hi = nzv.max(axis=0)           # (z, y, x)
@@ -242,7 +240,9 @@ class NanoVDBGrid:
         imin = np.asarray(origin_ijk, dtype=np.int64) + lo[::-1]
         imax1 = np.asarray(origin_ijk, dtype=np.int64) + hi[::-1] + 1
         ow = np.asarray(origin_world, dtype=np.float64)
-        wb = np.r_[imin.astype(np.float64) * voxel_size + ow, imax1.astype(np.float64) * voxel_size + ow]
+        # Map::applyMap = fma(x, dx, T): one rounding of the exact product-sum (exact rationals here)
+        fma = lambda i, t: float(Fraction(int(i)) * Fraction(float(voxel_size)) + Fraction(float(t)))  # noqa: E731
+        wb = np.array([fma(imin[k], ow[k]) for k in range(3)] + [fma(imax1[k], ow[k]) for k in range(3)])
         inv = np.zeros(9, dtype=np.float32)
         inv[[0, 4, 8]] = np.float32(1.0 / voxel_size)
         return NanoVDBGrid(vals, imin, inv, ow.astype(np.float32), wb,

@@ -38,7 +38,7 @@ WORKLOADS = {
                                       fov=16.0),
     # small variant for smoke runs / CPU-box sanity
     "cloud-small": dict(grid=(96, 80, 104), width=320, height=180, sigma_t=200.0, albedo=0.999, g=0.877,
-                        max_depth=100, majorant_res=(16, 16, 16), eye=(0.0, 0.3, -2.4), fov=16.0),
+                        max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4), fov=16.0),
 }
 
 
@@ -86,9 +86,13 @@ def make_density(w, device):
 
 
 def make_scene(w, density, spp, exact):
-    return scenes.cloud_scene(density, width=w["width"], height=w["height"], spp=spp, sigma_t=w["sigma_t"],
-                              albedo=w["albedo"], g=w["g"], max_depth=w["max_depth"], majorant_res=w["majorant_res"],
-                              exact_math=exact, eye=w.get("eye", (0.0, 0.35, -3.2)), fov=w.get("fov", 20.0))
+    """The cloud as a "nanovdb" medium — the medium type of pbrt-v4-scenes' Disney cloud (media.cpp:628-665):
+    index-space trilinear sampling, 64^3 majorant grid — inside a sphere "interface" boundary."""
+    nx, ny, nz = w["grid"]
+    return scenes.cloud_scene_nanovdb(density, voxel_size=1.0 / max(nx, ny, nz), width=w["width"], height=w["height"],
+                                      spp=spp, sigma_t=w["sigma_t"], albedo=w["albedo"], g=w["g"],
+                                      max_depth=w["max_depth"], exact_math=exact, eye=w.get("eye", (0.0, 0.35, -3.2)),
+                                      fov=w.get("fov", 20.0))
 
 
 class ClockSampler:
@@ -147,37 +151,72 @@ def measured_traffic(workload, layout, exact, spp):
 
 
 def run_reference_arm(args, w, density):
-    """--impl reference: time the CPU path with all host threads; each step = a bounded crop."""
+    """--impl reference / cpu_baseline: the CPU path on all host threads, each step a bounded sample of the
+    frame (a pixel lattice, 1 spp).  kind "reference": the reference's OWN NanoVDBMedium (over a real
+    nanovdb grid built with its vendored GridBuilder) and VolPathIntegrator::Li, compiled from
+    /root/reference into oracle/_ref/libavr_refprobe.so (shipped to the GPU box as a built artefact).
+    kind "port": the oracle restatement, when that library is not there."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
-    from cpu_checker import Checker
-    orc = Checker("orc")
+    from cpu_checker import Checker, have_ref
     threads = os.cpu_count() or 1
-    gd, rd = make_scene(w, density, 1, 1)
-    mo = orc.medium_uniformgrid(gd)
-    # bounded sample: a pixel lattice (every `stride`-th pixel in x and y) over the whole frame, stride
-    # calibrated so that one step is a few seconds of CPU work
+    nd, rd = make_scene(w, density, 1, 1)
     W, H = w["width"], w["height"]
+    kind = "reference" if have_ref() else "port"
+    if kind == "port":
+        orc = Checker("orc")
+        mo = orc.medium_nanovdb(nd)
+
+        def render(stride, seed):
+            orc.lib.orc_set_pixel_stride(C.c_int(stride))
+            mo.render(rd.with_(sampler_seed=seed), threads=threads)
+            orc.lib.orc_set_pixel_stride(C.c_int(1))
+    else:
+        ref = Checker("ref")
+        mo = ref.medium_nanovdb(nd)
+
+        def render(stride, seed):
+            xs, ys = np.arange(0, W, stride), np.arange(0, H, stride)
+            smp = np.stack([np.tile(xs, ys.size), np.repeat(ys, xs.size), np.zeros(xs.size * ys.size)], axis=1).astype(np.int32)
+            r = rd.with_(sampler_seed=seed)
+            smp, rays = mo.camera_rays(r, smp)
+            # interleaved shares: neighbouring pixels cost alike, so every thread gets the same mix
+            parts = [(smp[k::threads * 4], rays[k::threads * 4]) for k in range(threads * 4)]
+            it = iter(parts)
+            lock = threading.Lock()
+
+            def work():
+                while True:
+                    with lock:
+                        job = next(it, None)
+                    if job is None:
+                        return
+                    mo.volpath_li(r, job[0], job[1])  # ctypes releases the GIL inside the reference code
+            pool = [threading.Thread(target=work) for _ in range(threads)]
+            for t in pool:
+                t.start()
+            for t in pool:
+                t.join()
+
+    # bounded sample: every `stride`-th pixel in x and y of the whole frame, stride calibrated so that one
+    # step is a few seconds of CPU work
     stride = 16
-    orc.lib.orc_set_pixel_stride(C.c_int(stride))
-    t = time.perf_counter(); mo.render(rd, threads=threads); cal = time.perf_counter() - t
+    t = time.perf_counter(); render(stride, 0); cal = time.perf_counter() - t
     while stride > 1 and cal * 4 < 4.0:
         stride //= 2; cal *= 4
-    orc.lib.orc_set_pixel_stride(C.c_int(stride))
-    crop = rd
     cw, ch = (W + stride - 1) // stride, (H + stride - 1) // stride
-    for _ in range(args.warmup):
-        mo.render(crop, threads=threads)
+    for i in range(args.warmup):
+        render(stride, 1 + i)
     t = time.perf_counter()
-    for _ in range(args.steps):
-        mo.render(crop, threads=threads)
+    for i in range(args.steps):
+        render(stride, 100 + i)
     dt = time.perf_counter() - t
     mo.close()
-    orc.lib.orc_set_pixel_stride(C.c_int(1))
-    samples = cw * ch * args.steps
-    value = samples / dt / 1e6
-    sample_desc = f"every {stride}th pixel in x and y of {W}x{H} ({cw}x{ch} paths), 1 spp per step"
-    return value, dt / args.steps * 1e3, threads, sample_desc
+    value = cw * ch * args.steps / dt / 1e6
+    what = ("the reference's NanoVDBMedium + VolPathIntegrator::Li (oracle/_ref)" if kind == "reference"
+            else "oracle port of the reference renderer")
+    sample_desc = f"every {stride}th pixel in x and y of {W}x{H} ({cw}x{ch} paths), 1 spp per step; {what}"
+    return value, dt / args.steps * 1e3, threads, sample_desc, kind
 
 
 def main():
@@ -199,7 +238,8 @@ def main():
     base = {"metric": "Msamples/s on Disney cloud 720p volpath", "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "film": [w["width"], w["height"]], "grid": list(w["grid"]),
+            "config": {"workload": args.workload, "medium": "nanovdb (dense fBm stand-in flattened over its index box)",
+                       "film": [w["width"], w["height"]], "grid": list(w["grid"]),
                        "majorant_res": list(w["majorant_res"]), "sigma_t": w["sigma_t"], "albedo": w["albedo"],
                        "g": w["g"], "max_depth": w["max_depth"], "sampler": "independent",
                        "l2": "density store (octets, 3.6 GB at 720p workload) is far larger than the 126 MB L2"}}
@@ -210,10 +250,10 @@ def main():
         import torch  # only for the density generator when a GPU is around
         dev = "cuda:0" if torch.cuda.is_available() else None
         density = make_density(w, dev) if dev else scenes.fbm_density(*w["grid"])
-        value, ms, threads, sample_desc = run_reference_arm(args, w, density)
+        value, ms, threads, sample_desc, kind = run_reference_arm(args, w, density)
         out = dict(base)
         out.update({"impl": "reference", "value": value, "ms_per_step": ms, "n_gpus": args.gpus,
-                    "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": threads, "kind": "port",
+                    "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": threads, "kind": kind,
                                      "sample": sample_desc},
                     "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     "gpu_launches": 0})
@@ -232,10 +272,10 @@ def main():
     dev = torch.device("cuda", local_rank)
     density = make_density(w, dev)
     spp = args.spp_per_step
-    gd, rd = make_scene(w, density, spp, args.exact)
+    nd, rd = make_scene(w, density, spp, args.exact)
     ctx = Context(local_rank)
     t0 = time.perf_counter()
-    med = ctx.create_medium("uniformgrid", gd, layout=args.layout)
+    med = ctx.create_medium("nanovdb", nd, layout=args.layout)
     build_s = time.perf_counter() - t0
     W, H = w["width"], w["height"]
     film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
@@ -325,8 +365,8 @@ def main():
                               "parallelism": f"sample-index sharded x{world} ({spp} spp per rank per step), film ncclReduce" if world > 1 else "1 gpu"})
         if not args.no_cpu_baseline:
             try:
-                v, ms, threads, sample_desc = run_reference_arm(argparse.Namespace(steps=1, warmup=0), w, density)
-                out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port",
+                v, ms, threads, sample_desc, kind = run_reference_arm(argparse.Namespace(steps=1, warmup=0), w, density)
+                out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind,
                                        "sample": sample_desc}
             except Exception as e:  # the GPU numbers stand on their own
                 out["cpu_baseline"] = {"value": None, "error": str(e)}

@@ -346,26 +346,32 @@ class CheckerMedium:
         self.ck.fn("render_volpath")(self.h, C.byref(rdesc.c), _p(film, f64p), C.c_int(threads), _p(stats, i64p))
         return film, stats
 
-    def camera_rays(self, rdesc: RenderDesc):
-        """(pixel, sample) enumeration and camera rays of a render, as the oracle's camera forms them."""
-        x0, y0, x1, y1, s0, s1 = rdesc.ranges()
-        samples = np.array([(x, y, s) for y in range(y0, y1) for x in range(x0, x1) for s in range(s0, s1)], dtype=np.int32)
+    def camera_rays(self, rdesc: RenderDesc, samples=None):
+        """(pixel, sample) list {px, py, sampleIndex} (default: the render's own enumeration) and its camera
+        rays, as the oracle's camera forms them."""
+        if samples is None:
+            x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+            samples = np.array([(x, y, s) for y in range(y0, y1) for x in range(x0, x1) for s in range(s0, s1)], dtype=np.int32)
+        samples = np.ascontiguousarray(samples, dtype=np.int32)
         rays = np.zeros((samples.shape[0], 6), dtype=np.float32)
         orc = Checker("orc") if self.ck.kind != "orc" else self.ck
-        orc.lib.orc_camera_rays(C.byref(rdesc.c), _p(rays, f32p))
+        orc.lib.orc_camera_rays_list(C.byref(rdesc.c), _p(samples, i32p), C.c_int64(samples.shape[0]), _p(rays, f32p))
         return samples, rays
 
-    def volpath_li(self, rdesc: RenderDesc):
+    def volpath_li(self, rdesc: RenderDesc, samples=None, rays=None):
         """Per-sample {L[4], lambda[4], pdf[4]} of the render.  "ref": the reference's own
         VolPathIntegrator::Li (oracle/refprobe_volpath.cpp) over the oracle's camera rays, sphere boundary
         only; also returns {light wi, sceneRadius} as the reference's DistantLight computes them.
-        "orc": the restatement (render_samples)."""
+        "orc": the restatement (render_samples).  The call releases the GIL: host threads may run
+        disjoint sample lists concurrently (bench.py --impl reference)."""
         if self.ck.kind != "ref":
             out, _ = self.render_samples(rdesc)
             c = rdesc.c
             return out, np.array([c.light_dir[0], c.light_dir[1], c.light_dir[2], c.scene_radius], dtype=np.float32)
         assert rdesc.c.boundary_type == 0, "the reference probe builds a Shape \"sphere\" boundary"
-        samples, rays = self.camera_rays(rdesc)
+        if rays is None:
+            samples, rays = self.camera_rays(rdesc, samples)
+        samples = np.ascontiguousarray(samples, dtype=np.int32); rays = f32(rays)
         n = samples.shape[0]
         sphere = np.array(list(rdesc.c.boundary)[:4], dtype=np.float32)
         ld = np.array(list(rdesc.c.light_dir), dtype=np.float32)

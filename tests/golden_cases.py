@@ -203,7 +203,7 @@ def nanovdb_variants(ck):
     temp = (scenes.fbm_density(40, 33, 37, seed=9) * 2500 + 80).astype(np.float32)
     temp[:, :5] = 0
     M2, M2i = _rot_scale()
-    g0 = ck.nanovdb_grid(dens, (-7, 3, 11), 0.0625, (0.37, -1.21, 0.05))
+    g0 = ck.nanovdb_grid(dens, (-7, 3, 11), 0.07, (0.37, -1.21, 0.05))  # voxel size not a power of two
     g1 = ck.nanovdb_grid(dens, (100, -200, -30), 0.03125, (-4.0, 6.5, 1.25))
     t1 = ck.nanovdb_grid(temp, (101, -198, -33), 0.03125, (-4.0, 6.5, 1.25))
     return [("nv0", NanoVDBDesc(g0, scenes.ramp_spectrum(0.5, 1.5), scenes.ramp_spectrum(6, 9), g=0.3)),

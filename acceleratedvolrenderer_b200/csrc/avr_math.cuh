@@ -293,6 +293,8 @@ AVR_DEV float sample_exponential(float u, float a) {  // util/sampling.h:222-225
     if (EXACT) return -glibc_logf(1 - u) / a;
     return ftz_lg2(1 - u) * -0.6931471805599453f * ftz_rcp(a);
 }
+// FAST: -ln(1 - u), the optical depth to the next tentative collision (SampleExponential with a = 1)
+AVR_DEV float neg_log1m(float u) { return ftz_lg2(1 - u) * -0.6931471805599453f; }
 template <bool EXACT>
 AVR_DEV float fdiv(float a, float b) {
     if (EXACT) return a / b;

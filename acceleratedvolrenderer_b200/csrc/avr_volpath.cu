@@ -534,7 +534,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             uint64_t hash0 = hash_u32(ln.srng.u32());
             uint64_t hash1 = hash_u32(ln.srng.u32());
             ln.trng.set_sequence(hash0, hash1);
-            ln.u = ln.trng.uniform();
+            ln.u = neg_log1m(ln.trng.uniform());  // remaining optical depth to the first tentative collision
             if (ln.shadow) {
                 tMax = 1 - kShadowEps;
                 if (hit && t1 < tMax) tMax = t1;
@@ -663,6 +663,30 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     // leaves medium and boundary; no infinite lights in the scene class
                     // (cpu/integrators.cpp:1081-1106) -> path done
                     ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
+                } else if (!EX) {
+                    // FAST: the distance to the next tentative collision is carried across segments as a
+                    // remaining optical depth tau = -ln(1 - u) (ln.u holds it): by the memorylessness of
+                    // the exponential this samples the same free-flight distribution as redrawing u in
+                    // every segment (media.h:779-803) with one logarithm and one PCG32 draw per
+                    // collision instead of one per segment.  With one channel T_maj / T_maj[0] == 1
+                    // everywhere it is used, so T_maj is not tracked at all.
+                    cn.seg++;
+                    float mj = maj[vox];
+                    if (mj != 0) {
+                        Spec<N> sm = lc.sigma_t * mj;
+                        float dtau = sm[0] * (b - a);
+                        bool hit = ln.u <= dtau && sm[0] != 0;
+                        float tt = b;
+                        if (hit) tt = __fmaf_rn(ln.u, ftz_rcp(sm[0]), a);
+                        if (N > 1) ln.T_maj = ln.T_maj * exp_neg<false>(tt - a, sm);
+                        if (hit) {
+                            ln.sigma_maj = sm;
+                            ln.cur_tMin = tt;
+                            ln.seg_tMax = b;
+                            ln.state = ST_COLLIDE;
+                        } else
+                            ln.u -= dtau;
+                    }
                 } else {
                     cn.seg++;
                     float mj = maj[vox];
@@ -681,7 +705,18 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     }
                 }
             }
-            if (have && ln.state == ST_SAMPLE) {
+            if (!EX && have && ln.state == ST_SAMPLE) {
+                // FAST, after a null collision: fresh tau, tested against the rest of the current segment
+                float tau = neg_log1m(ln.trng.uniform());
+                float dtau = ln.sigma_maj[0] * (ln.seg_tMax - ln.cur_tMin);
+                bool hit = tau <= dtau;
+                float tt = ln.seg_tMax;
+                if (hit) tt = __fmaf_rn(tau, ftz_rcp(ln.sigma_maj[0]), ln.cur_tMin);
+                if (N > 1) ln.T_maj = ln.T_maj * exp_neg<false>(tt - ln.cur_tMin, ln.sigma_maj);
+                if (hit) ln.cur_tMin = tt; else ln.u = tau - dtau;
+                ln.state = hit ? ST_COLLIDE : ST_WALK;
+            }
+            if (EX && have && ln.state == ST_SAMPLE) {
                 // media.h:779-803: t = tMin + SampleExponential(u, sigma_maj[0]); u = rng.Uniform();
                 // T_maj *= FastExp(-(t - tMin) sigma_maj) at a collision, FastExp(-(tMax - tMin) sigma_maj) at the exit
                 float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);

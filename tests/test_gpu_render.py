@@ -5,7 +5,7 @@ Bars:
     >= 99% of samples within 1e-3 relative (device logf/sincosf/atanhf differ from glibc by an ulp,
     which can flip a discrete decision on a long path), wavelengths within 2e-6 relative;
   * converged image (exact and fast math, all layouts): relMSE of GPU-vs-oracle no larger than
-    3x the oracle's own seed-to-seed relMSE at the same spp (tolerance = Monte Carlo noise floor);
+    1.5x the oracle's own seed-to-seed relMSE (tolerance = Monte Carlo noise floor; see noise_floor);
   * analytic: homogeneous non-scattering slab, Tr = exp(-sigma_t * L) to 2e-3 relative;
   * SpMV total bit-exact, iterations identical; ConnectToGraph 1e-5 relative.
 """
@@ -16,6 +16,20 @@ from acceleratedvolrenderer_b200 import scenes
 from acceleratedvolrenderer_b200._abi import GridDesc
 
 pytestmark = pytest.mark.gpu
+
+GPU_SPP_FACTOR = 8
+
+
+def noise_floor(img_a, img_b):
+    """The oracle's own seed-to-seed relMSE, symmetrised (relMSE weighs a firefly differently depending on
+    which image carries it, and blackbody emitters make fireflies)."""
+    return 0.5 * (rel_mse(img_a, img_b) + rel_mse(img_b, img_a))
+
+
+def image_error(img, img_a, img_b):
+    """relMSE of a device image against both oracle images.  The device renders GPU_SPP_FACTOR x the oracle's
+    samples, so an unbiased device image scores about half the noise floor; the bar is 1.5x."""
+    return 0.5 * (rel_mse(img, img_a) + rel_mse(img, img_b))
 
 
 def small_scene(**kw):
@@ -57,8 +71,10 @@ def test_per_sample_radiance_matches_oracle(ctx, orc, variant):
 
 
 def rel_mse(a, b):
+    """Relative MSE; the floor of the denominator is 5 % of the image mean, so that the handful of nearly
+    black silhouette pixels (where one stray sample is a large relative error) does not decide the test."""
     a = a.astype(np.float64); b = b.astype(np.float64)
-    return float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+    return float(np.mean((a - b) ** 2 / (b ** 2 + (0.05 * b.mean()) ** 2)))
 
 
 @pytest.mark.parametrize("exact,layout", [(1, "octet32"), (0, "dense"), (0, "octet32"), (0, "octet16")])
@@ -69,14 +85,16 @@ def test_converged_image_matches_oracle(ctx, orc, exact, layout):
     ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
     mo.close()
     img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
-    noise = rel_mse(img_a, img_b)
+    noise = noise_floor(img_a, img_b)
     md = ctx.create_medium("uniformgrid", gd, layout=layout)
-    film, stats = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2 if not exact else 0))
+    # the device renders GPU_SPP_FACTOR x the oracle's samples: its own noise then hardly contributes and the
+    # comparison measures the oracle's noise plus any bias
+    film, stats = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2 if not exact else 0, spp=64 * GPU_SPP_FACTOR))
     md.close()
-    assert np.all(film[..., 3] == 64)
+    assert np.all(film[..., 3] == 64 * GPU_SPP_FACTOR)
     img = ctx.film_resolve(rd, film)
-    err = rel_mse(img, img_a)
-    assert err <= 3 * noise + 1e-6, (err, noise)
+    err = image_error(img, img_a, img_b)
+    assert err <= 1.5 * noise + 1e-6, (err, noise)
     assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
 
 
@@ -112,13 +130,13 @@ def test_general_media_render_matches_oracle(ctx, orc, kind):
     ref_a, _ = mo.render(rd, threads=8)
     ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
     img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
-    noise = rel_mse(img_a, img_b)
+    noise = noise_floor(img_a, img_b)
     for exact in (1, 0):
-        film, _ = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2))
-        assert np.all(film[..., 3] == rd.spp)
+        film, _ = ctx.render_volpath(md, rd.with_(exact_math=exact, sampler_seed=2, spp=rd.spp * GPU_SPP_FACTOR))
+        assert np.all(film[..., 3] == rd.spp * GPU_SPP_FACTOR)
         img = ctx.film_resolve(rd, film)
-        err = rel_mse(img, img_a)
-        assert err <= 3 * noise + 1e-6, (kind, exact, err, noise)
+        err = image_error(img, img_a, img_b)
+        assert err <= 1.5 * noise + 1e-6, (kind, exact, err, noise)
         assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
     md.close(); mo.close()
 
@@ -152,17 +170,47 @@ def test_nanovdb_render_matches_oracle(ctx, orc, emissive):
     ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
     mo.close()
     img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
-    noise = rel_mse(img_a, img_b)
+    noise = noise_floor(img_a, img_b)
     for layout in (["dense"] if emissive else ["dense", "octet32", "octet16"]):
         md = ctx.create_medium("nanovdb", nd, layout=layout)
-        film, _ = ctx.render_volpath(md, rd.with_(exact_math=0, sampler_seed=2))
+        film, _ = ctx.render_volpath(md, rd.with_(exact_math=0, sampler_seed=2, spp=rd.spp * GPU_SPP_FACTOR))
         md.close()
-        assert np.all(film[..., 3] == rd.spp)
+        assert np.all(film[..., 3] == rd.spp * GPU_SPP_FACTOR)
         img = ctx.film_resolve(rd, film)
-        err = rel_mse(img, img_a)
-        assert err <= 3 * noise + 1e-6, (layout, err, noise)
+        err = image_error(img, img_a, img_b)
+        assert err <= 1.5 * noise + 1e-6, (layout, err, noise)
         # image mean: 5 %, or 3x the oracle's own seed-to-seed difference where blackbody spikes make that larger
         assert abs(img.mean() - img_a.mean()) <= max(0.05 * img_a.mean(), 3 * abs(img_a.mean() - img_b.mean()))
+
+
+def test_volpath_matches_reference_integrator(ctx):
+    """k_volpath against the REFERENCE's own VolPathIntegrator::Li (the committed vectors that
+    oracle/refprobe_volpath.cpp produced from cpu/integrators.cpp, tests/golden case volpath_li), without
+    the oracle in between.  Lockstep scenes (emissive medium, black light: every random number comes from
+    the sampler streams): wavelengths bit-equal, >= 99 % of pixel samples within 1e-3 relative radiance
+    under the exact arithmetic.  Full-estimator scenes: converged fast-math image within 3x the reference's
+    own seed-to-seed relMSE."""
+    import os
+    from golden_cases import li_mono_image, li_scenes
+    golden = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.npz"))
+    for name, kind, desc, rd in li_scenes():
+        md = ctx.create_medium(kind, desc, layout="dense")
+        if name.startswith("lockstep"):
+            want = golden[f"volpath_li/{name}_samples"]
+            got, _ = ctx.render_volpath_samples(md, rd)
+            assert np.allclose(got[:, 4:8], want[:, 4:8], rtol=2e-6), "wavelengths"
+            L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+            scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+            ok = np.abs(L - Lw).max(axis=1) <= 1e-3 * scale
+            assert ok.mean() >= 0.99, f"{name}: {ok.mean():.4f} of samples match the reference"
+        else:
+            w0, w1 = golden[f"volpath_li/{name}_mono0"], golden[f"volpath_li/{name}_mono1"]
+            for exact, seed in ((1, 0), (0, 5)):
+                got, _ = ctx.render_volpath_samples(md, rd.with_(exact_math=exact, sampler_seed=seed))
+                img = li_mono_image(got, rd)
+                assert rel_mse(img, w1) <= 3 * rel_mse(w0, w1), (name, exact)
+                assert abs(img.mean() - w0.mean()) <= max(0.05 * w0.mean(), 3 * abs(w0.mean() - w1.mean())), (name, exact)
+        md.close()
 
 
 def test_sample_sharding_is_additive(ctx):
@@ -197,7 +245,7 @@ def test_analytic_transmittance(ctx, orc):
     # density along the chord); the integral is taken numerically with the oracle's grid lookup
     z = np.linspace(0, 1, 40001)
     pts = np.c_[np.full_like(z, 0.5), np.full_like(z, 0.5), z].astype(np.float32)
-    tau = 2.5 * np.trapz(orc.grid_lookup(dens, pts).astype(np.float64), z)
+    tau = 2.5 * np.trapezoid(orc.grid_lookup(dens, pts).astype(np.float64), z)
     est = out["Tr"][:, 0].astype(np.float64).mean()
     assert abs(est - np.exp(-tau)) < 4e-3, (est, np.exp(-tau))
     esc = out["n_fetch"] == 0

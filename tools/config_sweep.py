@@ -81,7 +81,7 @@ def run_volpath(ctx, peak, args):
         for layout, bpf in (("octet32", 32), ("octet16", 16), ("dense", 32)):
             for exact in ((0, 1) if layout == "octet32" else (0,)):
                 gd, rd = bench.make_scene(w2, density, spp, exact)
-                med = ctx.create_medium("uniformgrid", gd, layout=layout)
+                med = ctx.create_medium("nanovdb", gd, layout=layout)
                 volpath_case(ctx, peak, f"{name} {spp}spp", med, rd, bpf, args.reps, layout=layout, exact_math=exact)
                 med.close()
     del density

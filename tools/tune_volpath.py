@@ -37,7 +37,7 @@ def main():
     film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
     for layout in args.layouts.split(","):
         gd, rd = bench.make_scene(w, density, args.spp, 0)
-        med = ctx.create_medium("uniformgrid", gd, layout=layout)
+        med = ctx.create_medium("nanovdb", gd, layout=layout)
         names = [e.split("=", 1)[0] for e in args.env]
         lists = [e.split("=", 1)[1].split(";") for e in args.env]
         for exact, *vals in itertools.product(args.exact.split(","), *lists):

@@ -630,6 +630,9 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 SlotIO<TR>::template load<SlotIO<TR>::kTrackLoad>(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
                 swap_shadow_weights(ln);
                 have = true;
+                ln.mj = ln.dda.tMin < ln.dda.tMax ? maj[ln.dda.lin] : 0.f;
+                // a path that was given back with its tentative collision pending: request the taps again
+                if (Fetcher<TR>::kSplitFetch && ln.state == ST_COLLIDE) ln.fe.request(mv, ln.cur_tMin, ln.tapA, ln.tapB);
             }
             int active = 32 - __popc(idle) + n;
             if (active == 0) return;
@@ -664,6 +667,10 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     // (cpu/integrators.cpp:1081-1106) -> path done
                     ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
                 } else if (!EX) {
+                    // the majorant of this segment was requested when the DDA entered the voxel; request the
+                    // next one now, a whole loop trip before it is needed
+                    const float mj = ln.mj;
+                    if (ln.dda.tMin < ln.dda.tMax) ln.mj = maj[ln.dda.lin];
                     // FAST: the distance to the next tentative collision is carried across segments as a
                     // remaining optical depth tau = -ln(1 - u) (ln.u holds it): by the memorylessness of
                     // the exponential this samples the same free-flight distribution as redrawing u in
@@ -671,7 +678,6 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     // collision instead of one per segment.  With one channel T_maj / T_maj[0] == 1
                     // everywhere it is used, so T_maj is not tracked at all.
                     cn.seg++;
-                    float mj = maj[vox];
                     if (mj != 0) {
                         Spec<N> sm = lc.sigma_t * mj;
                         float dtau = sm[0] * (b - a);
@@ -684,12 +690,14 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                             ln.cur_tMin = tt;
                             ln.seg_tMax = b;
                             ln.state = ST_COLLIDE;
+                            if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
                         } else
                             ln.u -= dtau;
                     }
                 } else {
                     cn.seg++;
-                    float mj = maj[vox];
+                    const float mj = ln.mj;
+                    if (ln.dda.tMin < ln.dda.tMax) ln.mj = maj[ln.dda.lin];
                     Spec<N> sm = lc.sigma_t * mj;
                     if (mj == 0) {
                         // sigma_maj = 0 in every channel: T_maj *= FastExp(-0) = 1 exactly, nothing to do
@@ -713,7 +721,11 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 float tt = ln.seg_tMax;
                 if (hit) tt = __fmaf_rn(tau, ftz_rcp(ln.sigma_maj[0]), ln.cur_tMin);
                 if (N > 1) ln.T_maj = ln.T_maj * exp_neg<false>(tt - ln.cur_tMin, ln.sigma_maj);
-                if (hit) ln.cur_tMin = tt; else ln.u = tau - dtau;
+                if (hit) {
+                    ln.cur_tMin = tt;
+                    if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
+                } else
+                    ln.u = tau - dtau;
                 ln.state = hit ? ST_COLLIDE : ST_WALK;
             }
             if (EX && have && ln.state == ST_SAMPLE) {
@@ -741,7 +753,14 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             {
                 const float t = ln.cur_tMin;
                 Spec<N> T_maj = ln.T_maj;
-                PropsN<N> mp = ln.fe.template props<N>(mv, lc, t);
+                PropsN<N> mp;
+                if (Fetcher<TR>::kSplitFetch) {
+                    float dens = ln.fe.resolve(t, ln.tapA, ln.tapB);
+                    mp.sigma_a = lc.sig_a * dens;
+                    mp.sigma_s = lc.sig_s * dens;
+                    mp.Le = sconst<4>(0.f);
+                } else
+                    mp = ln.fe.template props<N>(mv, lc, t);
                 Spec<N> sigma_maj = ln.sigma_maj;
                 Spec<N> sigma_n = clamp_zero(sigma_maj - mp.sigma_a - mp.sigma_s);
                 // One instruction stream for both ray kinds.  Inside this loop a shadow lane keeps its

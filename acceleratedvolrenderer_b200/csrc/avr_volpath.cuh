@@ -122,6 +122,8 @@ struct PathLane {
     Fetcher<TR> fe;
     DDA dda;
     float cur_tMin, seg_tMax, u;
+    float mj;          // majorant of the voxel the DDA stands in, requested one step ahead (registers only)
+    float4 tapA, tapB; // density taps of the pending tentative collision, requested when its distance was drawn
     Spec<N> sigma_maj, T_maj;
     RNG trng;
     // shadow-ray state

@@ -373,8 +373,12 @@ struct KernelCfg {
     // kernels need 144..181 registers: one CTA per SM with as many warps as the register file holds
     static constexpr bool kLean = TR::NCH == 1 && !TR::GENERAL;
     static constexpr int kThreads = kLean ? AVR_CTA_THREADS : 384;  // 3 warps per scheduler: 168-register cap
+#ifdef AVR_LEAN_MIN_BLOCKS
+    static constexpr int kMinBlocks = kLean ? AVR_LEAN_MIN_BLOCKS : 1;
+#else
     static constexpr int kMinBlocks =
         (kLean && AVR_MIN_BLOCKS * 256 >= AVR_CTA_THREADS) ? AVR_MIN_BLOCKS * 256 / AVR_CTA_THREADS : 1;
+#endif
 };
 
 struct LaneCounters {
@@ -885,6 +889,9 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     LambdaCtx<N> lc;
     LaneCounters cn = {0, 0, 0, 0, 0};
 
+    // warps of one sub-partition share its L0 instruction cache: with a mask other than 15 the event code
+    // stays on the chosen sub-partitions as long as both kinds of work are queued
+    const bool ev_first = (rp.event_smsp_mask >> ((threadIdx.x >> 5) & 3)) & 1;
     while (true) {
         // ---- warp-level dispatch on the queue fill levels ---------------------------------------------
         int c_dead = 0, c_sc = 0, c_se = 0, c_tr = 0, live = 0;
@@ -898,6 +905,7 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
         int choice;  // queue to serve, -1: sleep, -2: done
         if (lane == 0) {
             if (live <= 0) choice = -2;
+            else if (!ev_first && c_tr >= rp.track_min) choice = Q_TRACK;
             else if (c_sc >= 32) choice = Q_SCATTER;
             else if (c_se >= 32) choice = Q_SHADOW_END;
             else if (c_dead >= 32) choice = Q_DEAD;

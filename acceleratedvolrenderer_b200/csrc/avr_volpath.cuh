@@ -37,6 +37,7 @@ struct RenderParams {
     int track_min;            // Q_TRACK fill level at which a warp prefers tracking over partial event batches
     int yield_lanes;          // a dry tracking warp with <= this many paths gives them back if any event waits
     int yield_lanes_full;     // ... or with <= this many paths if a full event batch waits
+    int event_smsp_mask;      // bit s set: warps on sub-partition s (warp id & 3) serve events first; the others track first
 };
 
 // stats slots in the counters array

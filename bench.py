@@ -145,6 +145,8 @@ def measured_traffic(workload, layout, exact, spp):
     if not os.path.exists(p):
         return None, None
     for e in json.load(open(p))["entries"]:
+        if e.get("superseded_by"):
+            continue
         if (e["workload"], e["layout"], e["exact_math"], e["spp_per_launch"]) == (workload, layout, int(exact), spp):
             return e["dram_read_bytes"] + e["dram_write_bytes"], e["capture"]
     return None, None
@@ -215,7 +217,8 @@ def run_reference_arm(args, w, density):
     value = cw * ch * args.steps / dt / 1e6
     what = ("the reference's NanoVDBMedium + VolPathIntegrator::Li (oracle/_ref)" if kind == "reference"
             else "oracle port of the reference renderer")
-    sample_desc = f"every {stride}th pixel in x and y of {W}x{H} ({cw}x{ch} paths), 1 spp per step; {what}"
+    lattice = "every pixel" if stride == 1 else f"every {stride}th pixel in x and y"
+    sample_desc = f"{lattice} of {W}x{H} ({cw}x{ch} paths), 1 spp per step; {what}"
     return value, dt / args.steps * 1e3, threads, sample_desc, kind
 
 

@@ -98,6 +98,7 @@ class avr_render_desc(C.Structure):
         ("output_rgb_from_sensor", C.c_float * 9),
         ("max_component_value", C.c_float),
         ("rank", C.c_int32), ("world", C.c_int32),
+        ("sampler", C.c_int32), ("randomize", C.c_int32),
     ]
 
 
@@ -283,13 +284,18 @@ class NanoVDBDesc:
         self.p0, self.p1 = wb[:3].copy(), wb[3:].copy()   # NanoVDBMedium::bounds, media.cpp:536-551
 
 
+SAMPLERS = {"independent": 0, "zsobol": 1}
+RANDOMIZE = {"none": 0, "permutedigits": 1, "fastowen": 2, "owen": 3}
+
+
 class RenderDesc:
     """Camera / light / film / sampler parameters of one volpath render (see avr_render_desc)."""
 
     def __init__(self, width, height, spp, *, camera_from_raster, render_from_camera, light_dir, light_spectrum,
                  scene_radius, boundary_type, boundary, sensor_rgb, max_depth=5, sampler_seed=0, exact_math=1,
                  filter_radius=(0.5, 0.5), imaging_ratio=1.0, output_rgb_from_sensor=None,
-                 max_component_value=float("inf"), pixel_bounds=None, sample_begin=0, sample_end=0, rank=0, world=1):
+                 max_component_value=float("inf"), pixel_bounds=None, sample_begin=0, sample_end=0, rank=0, world=1,
+                 sampler="independent", randomize="fastowen"):
         self.light_spectrum = _f32(np.broadcast_to(light_spectrum, (NSPEC,)))
         self.sensor_rgb = _f32(sensor_rgb).reshape(3, NSPEC)
         c = avr_render_desc()
@@ -316,6 +322,9 @@ class RenderDesc:
                  else output_rgb_from_sensor)
         c.max_component_value = max_component_value
         c.rank, c.world = rank, world
+        # "Sampler" names and "randomization" values as the scene file spells them (samplers.cpp:157-165, 417-431)
+        c.sampler = SAMPLERS[sampler] if isinstance(sampler, str) else int(sampler)
+        c.randomize = RANDOMIZE[randomize] if isinstance(randomize, str) else int(randomize)
         self.c = c
 
     def __getattr__(self, name):

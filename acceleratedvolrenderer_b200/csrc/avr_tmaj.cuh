@@ -16,8 +16,9 @@ namespace avr {
 //            all four channels carry bit-identical values and one is enough)
 //  LAYOUT  : density layout (ignored when GENERAL)
 //  GENERAL : any medium kind (rgbgrid, emissive uniformgrid) through sample_point_general; NCH = 4
-template <bool EXACT_, int NCH_, int LAYOUT_, bool GENERAL_>
+template <bool EXACT_, int NCH_, int LAYOUT_, bool GENERAL_, bool ZSOBOL_ = false>
 struct Traits {
+    static constexpr bool ZSOBOL = ZSOBOL_;  // render kernels: the integrator's sampler is ZSobolSampler
     static constexpr bool EXACT = EXACT_;
     static constexpr int NCH = NCH_;
     static constexpr int LAYOUT = LAYOUT_;

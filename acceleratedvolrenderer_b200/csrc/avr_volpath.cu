@@ -103,19 +103,18 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     int py = rp.y0 + (tile / rp.tiles_x) * 4 + (within >> 3);
     if (px >= rp.x1 || py >= rp.y1) return false;  // padding lane of an edge tile
     ln.px = px; ln.py = py; ln.samp = s;
-    // IndependentSampler::StartPixelSample, samplers.h:457-460
-    ln.srng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)rp.seed));
-    ln.srng.advance((long long)s * 65536ll);
-    float lu = ln.srng.uniform();
+    PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, px, py, s};
+    smp.start_pixel_sample();
+    float lu = smp.get1d();
     float pdf[4];
     sample_visible_wavelengths(lu, ln.lambda, pdf);
     lc = make_lambda_ctx<TR::NCH>(mv, ln.lambda);
-    float f0 = ln.srng.uniform(), f1 = ln.srng.uniform();
+    float f0, f1, l0, l1;
+    smp.get2d(&f0, &f1);  // GetCameraSample: GetPixel2D, samplers.h:797-814
     float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
-    ln.srng.uniform();  // time
-    ln.srng.uniform();  // lens
-    ln.srng.uniform();
+    smp.get1d();          // time
+    smp.get2d(&l0, &l1);  // lens
     // cameraFromRaster(pFilm): Transform::operator()(Point3f), util/transform.h:314-323
     const float *c = rp.cfr;
     float xp = c[0] * pfx + c[1] * pfy + c[2] * 0.f + c[3];
@@ -448,9 +447,12 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
         if (have) {
             cn.sc++;
             V3 p = ln.fe.point(ln.cur_tMin);
-            ln.srng.uniform();  // light choice (single light, p = 1)
-            ln.srng.uniform();  // uLight
-            ln.srng.uniform();
+            {
+                PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+                float ul0, ul1;
+                smp.get1d();            // light choice (single light, p = 1)
+                smp.get2d(&ul0, &ul1);  // uLight
+            }
             V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
             float two_r = 2 * rp.scene_radius;
             V3 pLight = v3(p.x + wi.x * two_r, p.y + wi.y * two_r, p.z + wi.z * two_r);
@@ -491,7 +493,8 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                     ln.L[i] += (bf[i % N] * Ll) / avg;
                 }
             }
-            float ua = ln.srng.uniform(), ub = ln.srng.uniform();
+            float ua, ub;
+            PathSamplerRef<TR::ZSOBOL>{rp.smp, ln.srng, ln.px, ln.py, ln.samp}.get2d(&ua, &ub);
             float pdf;
             V3 wi = sample_hg<TR::EXACT>(ln.wo, mv.g, ua, ub, &pdf);
             if (pdf == 0) {
@@ -525,18 +528,34 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                 ln.wo = -d;
                 tMax = t1;
                 if (hit) {
-                    uint64_t hash0 = hash_float(ln.srng.uniform());
-                    uint64_t hash1 = hash_float(ln.srng.uniform());
+                    PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+                    uint64_t hash0 = hash_float(smp.get1d());
+                    uint64_t hash1 = hash_float(smp.get1d());
                     ln.trng.set_sequence(hash0, hash1);
-                    ln.u = ln.srng.uniform();
+                    ln.u = smp.get1d();
                 }
             }
         } else {
             // FAST: same estimator; the tracking stream of either ray kind is seeded from two hashed sampler draws
             hit = boundary_hit_fast(rp, o, d, &t0, &t1) && t1 > 0;
             // (raw draws as PCG32 sequence / seed give correlated streams: they must go through the hash)
-            uint64_t hash0 = hash_u32(ln.srng.u32());
-            uint64_t hash1 = hash_u32(ln.srng.u32());
+            uint64_t hash0, hash1;
+            if (TR::ZSOBOL) {
+                // zsobol keeps the reference's dimension layout: camera rays take the three draws of
+                // cpu/integrators.cpp:985-988, shadow rays hash their origin and direction (:1338)
+                if (ln.shadow) {
+                    hash0 = hash_v3(o);
+                    hash1 = hash_v3(d);
+                } else {
+                    PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+                    hash0 = hash_float(smp.get1d());
+                    hash1 = hash_float(smp.get1d());
+                    smp.get1d();
+                }
+            } else {
+                hash0 = hash_u32(ln.srng.u32());
+                hash1 = hash_u32(ln.srng.u32());
+            }
             ln.trng.set_sequence(hash0, hash1);
             ln.u = neg_log1m(ln.trng.uniform());  // remaining optical depth to the first tentative collision
             if (ln.shadow) {

@@ -4,6 +4,7 @@
 // (cpu/integrators.cpp:72-298), VolPathIntegrator::Li volume branch (:962-1106) and SampleLd
 // (:1282-1399), with SampleT_maj (media.h:741-806) unrolled into per-path ops; see avr_volpath.cu.
 #pragma once
+#include "avr_sampler.cuh"
 #include "avr_tmaj.cuh"
 
 namespace avr {
@@ -13,6 +14,7 @@ struct RenderParams {
     int x0, y0, x1, y1;
     int s0, s1;
     int max_depth, seed;
+    SamplerCfg smp;           // the integrator's sampler (independent | zsobol)
     float filter_rx, filter_ry;
     float cfr[16];   // cameraFromRaster (projective)
     float rfc[12];   // renderFromCamera (affine rows)

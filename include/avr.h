@@ -225,6 +225,9 @@ avr_status avr_sample_tmaj_device(avr_medium *m, int mode, int exact_math, const
  * boundary shape with Material "interface", ONE distant light, perspective camera, box pixel filter,
  * Sampler "independent". */
 enum { AVR_BOUNDARY_SPHERE = 0, AVR_BOUNDARY_BOX = 1 };
+enum { AVR_SAMPLER_INDEPENDENT = 0, AVR_SAMPLER_ZSOBOL = 1 };
+/* RandomizeStrategy, util/lowdiscrepancy.h:261 (same order) */
+enum { AVR_RANDOMIZE_NONE = 0, AVR_RANDOMIZE_PERMUTE_DIGITS = 1, AVR_RANDOMIZE_FAST_OWEN = 2, AVR_RANDOMIZE_OWEN = 3 };
 
 typedef struct avr_render_desc {
     int32_t width, height;           /* full film resolution                                   */
@@ -233,7 +236,7 @@ typedef struct avr_render_desc {
     int32_t sample_begin, sample_end;/* sample-index range rendered by this call (multi-GPU
                                         sharding by sample index); both 0 -> [0, spp)          */
     int32_t max_depth;               /* "maxdepth" (default 5, cpu/integrators.cpp:1410)       */
-    int32_t sampler_seed;            /* IndependentSampler seed, samplers.h:442-476            */
+    int32_t sampler_seed;            /* the sampler's "seed" (IndependentSampler / ZSobolSampler) */
     int32_t exact_math;              /* 1: restated CPU FastExp/logf/IEEE div (parity mode);
                                         0: ex2.approx / lg2.approx (reference's own GPU branch,
                                         util/math.h:451-452)                                   */
@@ -251,6 +254,12 @@ typedef struct avr_render_desc {
     float max_component_value;       /* RGBFilm clamp, film.h:246                              */
     int32_t rank, world;             /* tile/sample partition: this call renders work items
                                         with (item % world) == rank; world 0 -> 1              */
+    int32_t sampler;                 /* AVR_SAMPLER_INDEPENDENT ("independent", samplers.h:442-476)
+                                        or AVR_SAMPLER_ZSOBOL ("zsobol", pbrt's default sampler,
+                                        samplers.h:225-364: constructed from spp, the full film
+                                        resolution, `randomize` and sampler_seed)               */
+    int32_t randomize;               /* zsobol "randomization": AVR_RANDOMIZE_* (pbrt's default
+                                        is fastowen, samplers.cpp:157); ignored for independent */
 } avr_render_desc;
 
 typedef struct avr_render_stats {

@@ -35,6 +35,8 @@ void ErrorExit(const FileLoc *, const char *message) {
     std::fprintf(stderr, "refprobe: reference ErrorExit: %s\n", message);
     std::abort();
 }
+// ZSobolSampler's constructor warns about sample counts that are not powers of two (samplers.h:231-234)
+void Warning(const FileLoc *, const char *) {}
 int RunningThreads() { return 1; }
 StatRegisterer::StatRegisterer(AccumFunc, PixelAccumFunc) {}
 void StatsAccumulator::ReportMemoryCounter(const char *, int64_t) {}

@@ -33,7 +33,8 @@ extern "C" {
 // sceneRadius after Preprocess}.
 void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir[3], const float *light_spec,
                     int32_t max_depth, int32_t sampler_seed, int32_t spp, const int32_t *samples, const float *rays,
-                    int64_t n, float *out, float *info) {
+                    int64_t n, float *out, float *info, const int32_t sampler_cfg[4]) {
+    // sampler_cfg = {0 independent | 1 zsobol, RandomizeStrategy, film width, film height}
     // --disable-texture-filtering: SurfaceInteraction::ComputeDifferentials (interaction.cpp:41-47) then
     // skips the camera-based footprint estimate, the only use Li makes of the camera (none is built
     // here); it feeds texture lookups only, which the "interface" boundary does not have.
@@ -67,7 +68,8 @@ void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir
     ScratchBuffer scratch(65536);
     for (int64_t i = 0; i < n; ++i) {
         IndependentSampler is(spp, sampler_seed);
-        Sampler sampler(&is);
+        ZSobolSampler zs(spp, Point2i(sampler_cfg[2], sampler_cfg[3]), RandomizeStrategy(sampler_cfg[1]), sampler_seed);
+        Sampler sampler = sampler_cfg[0] == 1 ? Sampler(&zs) : Sampler(&is);
         Point2i pPixel(samples[3 * i], samples[3 * i + 1]);
         sampler.StartPixelSample(pPixel, samples[3 * i + 2]);
         Float lu = sampler.Get1D();
@@ -84,6 +86,28 @@ void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir
             out[12 * i + 8 + k] = lambda.PDF()[k];
         }
     }
+}
+
+// ZSobolSampler streams (samplers.h:225-364): per sample {px, py, sampleIndex}, `rounds` times
+// {Get1D, Get2D} after StartPixelSample -> 3 floats per round.
+void ref_zsobol_samples(int32_t spp, int32_t resx, int32_t resy, int32_t randomize, int32_t seed, const int32_t *samples,
+                        int64_t n, int32_t rounds, float *out) {
+    ZSobolSampler zs(spp, Point2i(resx, resy), RandomizeStrategy(randomize), seed);
+    for (int64_t i = 0; i < n; ++i) {
+        zs.StartPixelSample(Point2i(samples[3 * i], samples[3 * i + 1]), samples[3 * i + 2], 0);
+        for (int r = 0; r < rounds; ++r) {
+            float *q = out + (i * rounds + r) * 3;
+            q[0] = zs.Get1D();
+            Point2f u = zs.Get2D();
+            q[1] = u.x;
+            q[2] = u.y;
+        }
+    }
+}
+
+// first two dimensions of util/sobolmatrices.cpp: 2 * SobolMatrixSize words
+void ref_sobol_matrices(uint32_t *out) {
+    for (int i = 0; i < 2 * SobolMatrixSize; ++i) out[i] = SobolMatrices32[i];
 }
 
 }  // extern "C"

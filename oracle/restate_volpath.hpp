@@ -16,12 +16,14 @@
 //    re-spawned at o + d*tHit without pbrt's error-bound offset (interaction.cpp:91-97);
 //  * "IsInf(L.y(lambda))" (cpu/integrators.cpp:277) is evaluated as "any component of L is inf".
 #pragma once
+#include "restate_sampler.hpp"
 #include "restate_tmaj.hpp"
 
 namespace avro {
 
 struct Scene {
     int width = 0, height = 0, spp = 1, max_depth = 5, sampler_seed = 0;
+    int sampler_kind = SAMPLER_INDEPENDENT, sampler_randomize = RANDOMIZE_FAST_OWEN;  // "independent" | "zsobol"
     float filter_radius[2] = {0.5f, 0.5f};
     Xform camera_from_raster, render_from_camera;  // only .m is used
     V3 light_dir;                                  // wi towards the light, normalised
@@ -72,11 +74,11 @@ inline bool boundary_hit(const Scene &sc, V3 o, V3 d, float *t0, float *t1) {
 
 // VolPathIntegrator::SampleLd, medium-interaction branch, cpu/integrators.cpp:1282-1399
 inline Spec4 sample_ld(const Scene &sc, const Medium &med, V3 p, V3 wo, const float lambda[4],
-                       IndependentSampler &sampler, Spec4 beta, Spec4 r_p, RenderCounters *rc) {
+                       PathSampler &sampler, Spec4 beta, Spec4 r_p, RenderCounters *rc) {
     float u = sampler.get1d();  // light choice: single light, p = 1
     (void)u;
-    sampler.get1d();  // uLight
-    sampler.get1d();
+    float ul0, ul1;
+    sampler.get2d(&ul0, &ul1);  // uLight
     // DistantLight::SampleLi, lights.h:284-291
     V3 wi = sc.light_dir;
     V3 pLight = p + wi * (2 * sc.scene_radius);
@@ -126,7 +128,7 @@ inline Spec4 sample_ld(const Scene &sc, const Medium &med, V3 p, V3 wo, const fl
 
 // VolPathIntegrator::Li, cpu/integrators.cpp:962-1106, for a ray that starts outside the boundary.
 inline Spec4 volpath_li(const Scene &sc, const Medium &med, V3 ro, V3 rd, const float lambda[4],
-                        IndependentSampler &sampler, RenderCounters *rc) {
+                        PathSampler &sampler, RenderCounters *rc) {
     Spec4 L = spec(0.f), beta = spec(1.f), r_u = spec(1.f), r_l = spec(1.f);
     int depth = 0;
     float t0, t1;
@@ -169,7 +171,8 @@ inline Spec4 volpath_li(const Scene &sc, const Medium &med, V3 ro, V3 rd, const 
                         if (rc) rc->scatter_events++;
                         V3 wo = -rd;  // ray.d is the normalised direction inside SampleT_maj's caller
                         L = L + sample_ld(sc, med, p, wo, lambda, sampler, beta, r_u, rc);
-                        float ua = sampler.get1d(), ub = sampler.get1d();
+                        float ua, ub;
+                        sampler.get2d(&ua, &ub);
                         float pdfp;
                         V3 wi = sample_hg(wo, med.g, ua, ub, &pdfp);
                         if (pdfp == 0) terminated = true;
@@ -210,14 +213,23 @@ struct PixelSampleOut {
     float weight;
 };
 
+// the scene's sampler: IndependentSampler(seed) or ZSobolSampler(spp, film resolution, randomize, seed)
+inline PathSampler make_sampler(const Scene &sc) {
+    PathSampler s;
+    s.kind = sc.sampler_kind;
+    s.ind.seed = sc.sampler_seed;
+    if (s.kind == SAMPLER_ZSOBOL) s.zs.configure(sc.spp, sc.width, sc.height, sc.sampler_randomize, sc.sampler_seed);
+    return s;
+}
+
 // Camera ray of one pixel sample (GetCameraSample + PerspectiveCamera::GenerateRay), as
 // evaluate_pixel_sample below forms it; exported so that the reference probe traces the same rays.
 inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro, V3 *rd) {
-    IndependentSampler sampler;
-    sampler.seed = sc.sampler_seed;
+    PathSampler sampler = make_sampler(sc);
     sampler.start_pixel_sample(px, py, sampleIndex);
     sampler.get1d();
-    float f0 = sampler.get1d(), f1 = sampler.get1d();
+    float f0, f1;
+    sampler.get2d(&f0, &f1);
     float fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
     float fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
@@ -228,20 +240,19 @@ inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro,
 // RayIntegrator::EvaluatePixelSample, cpu/integrators.cpp:235-298
 inline PixelSampleOut evaluate_pixel_sample(const Scene &sc, const Medium &med, int px, int py, int sampleIndex,
                                             RenderCounters *rc) {
-    IndependentSampler sampler;
-    sampler.seed = sc.sampler_seed;
+    PathSampler sampler = make_sampler(sc);
     sampler.start_pixel_sample(px, py, sampleIndex);
     float lu = sampler.get1d();
     PixelSampleOut out;
     out.lambda = sample_visible_wavelengths(lu);
     // GetCameraSample with BoxFilter::Sample (filters.h:67-70)
-    float f0 = sampler.get1d(), f1 = sampler.get1d();
+    float f0, f1, l0, l1;
+    sampler.get2d(&f0, &f1);  // GetPixel2D
     float fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
     float fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
-    sampler.get1d();  // time
-    sampler.get1d();  // lens
-    sampler.get1d();
+    sampler.get1d();          // time
+    sampler.get2d(&l0, &l1);  // lens
     out.weight = 1;
     V3 pCamera = apply_point(sc.camera_from_raster, {pfx, pfy, 0});
     V3 dir = normalize(pCamera);

@@ -72,6 +72,20 @@ class Checker:
         self.fn("mix_bits")(_p(x, u64p), C.c_int64(x.size), _p(out, u64p))
         return out
 
+    def zsobol_samples(self, spp, res, randomize, seed, samples, rounds):
+        """ZSobolSampler streams: per {px, py, sampleIndex}, `rounds` x {Get1D, Get2D} -> (n, rounds, 3) floats."""
+        samples = np.ascontiguousarray(samples, dtype=np.int32)
+        n = samples.shape[0]
+        out = np.zeros((n, rounds, 3), dtype=np.float32)
+        self.fn("zsobol_samples")(C.c_int32(spp), C.c_int32(res[0]), C.c_int32(res[1]), C.c_int32(randomize),
+                                  C.c_int32(seed), _p(samples, i32p), C.c_int64(n), C.c_int32(rounds), _p(out, f32p))
+        return out
+
+    def sobol_matrices(self):
+        out = np.zeros(104, dtype=np.uint32)
+        self.fn("sobol_matrices")(out.ctypes.data_as(C.c_void_p))
+        return out
+
     def hash_float(self, x):
         x = f32(x); out = np.empty(x.size, dtype=np.uint64)
         self.fn("hash_float")(_p(x, f32p), C.c_int64(x.size), _p(out, u64p))
@@ -378,7 +392,9 @@ class CheckerMedium:
         out = np.zeros((n, 12), dtype=np.float32); info = np.zeros(4, dtype=np.float32)
         self.ck.lib.ref_volpath_li(self.h, _p(sphere, f32p), _p(ld, f32p), _p(rdesc.light_spectrum, f32p),
                                    C.c_int32(rdesc.c.max_depth), C.c_int32(rdesc.c.sampler_seed), C.c_int32(rdesc.c.spp),
-                                   _p(samples, i32p), _p(rays, f32p), C.c_int64(n), _p(out, f32p), _p(info, f32p))
+                                   _p(samples, i32p), _p(rays, f32p), C.c_int64(n), _p(out, f32p), _p(info, f32p),
+                                   _p(np.array([rdesc.c.sampler, rdesc.c.randomize, rdesc.c.width, rdesc.c.height],
+                                               dtype=np.int32), i32p))
         return out, info
 
     def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):

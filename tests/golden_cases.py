@@ -331,7 +331,33 @@ def case_graphfile(ck):
     return out
 
 
-CASES = {"scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
+# ---- ZSobolSampler (samplers.h:225-364) + SobolSample randomizers (util/lowdiscrepancy.h:168-258) -------
+def zsobol_configs():
+    """(spp, film resolution, RandomizeStrategy, seed): powers of 4, of 2 only, non-powers of two, odd films."""
+    return [(1, (1280, 720), 2, 0), (16, (1280, 720), 2, 0), (256, (1280, 720), 2, 7), (8, (64, 48), 2, 3),
+            (2, (33, 17), 3, 5), (64, (40, 30), 3, -2), (4, (48, 36), 1, 1), (32, (4096, 4096), 0, 0),
+            (3, (20, 20), 2, 9), (100, (1, 1), 3, 4)]
+
+
+def zsobol_samples_list(cfg, n=96):
+    spp, res, _, seed = cfg
+    rng = np.random.default_rng(1000 + spp + res[0])
+    s = np.stack([rng.integers(0, res[0], n), rng.integers(0, res[1], n), rng.integers(0, spp, n)], axis=1)
+    s[0] = (res[0] - 1, res[1] - 1, spp - 1)
+    s[1] = (0, 0, 0)
+    return s.astype(np.int32)
+
+
+def case_zsobol(ck):
+    out = {"sobol_matrices_dim01": ck.sobol_matrices()}
+    for i, cfg in enumerate(zsobol_configs()):
+        spp, res, rz, seed = cfg
+        # 24 rounds of {Get1D, Get2D} = 72 dimensions: past the camera sample and several path vertices
+        out[f"stream{i}"] = ck.zsobol_samples(spp, res, rz, seed, zsobol_samples_list(cfg), 24)
+    return out
+
+
+CASES = {"zsobol": case_zsobol, "scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
          "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph, "graphfile": case_graphfile}
 
 
@@ -358,6 +384,9 @@ def li_scenes():
     nd, rdn = scenes.cloud_scene_nanovdb(d2, temperature=(d2 * 2500 + 200).astype(np.float32), le_scale=0.4, width=40,
                                          height=30, spp=4, sigma_t=18.0, albedo=0.95, g=0.4, max_depth=6, light_scale=0.0)
     out.append(("lockstep_nanovdb", "nanovdb", nd, rdn))
+    # the same scene through pbrt's default sampler ("zsobol", fastowen) and its full Owen variant
+    out.append(("lockstep_nanovdb_zsobol", "nanovdb", nd, rdn.with_(sampler=1, randomize=2)))
+    out.append(("lockstep_grid_zsobol_owen", "uniformgrid", em, black.with_(sampler=1, randomize=3, sampler_seed=5)))
     gdc, rdc = scenes.cloud_scene(dens, width=32, height=24, spp=128, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=6,
                                   chromatic=True)
     out.append(("image_chromatic", "uniformgrid", gdc, rdc))

@@ -98,6 +98,59 @@ def test_converged_image_matches_oracle(ctx, orc, exact, layout):
     assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
 
 
+@pytest.mark.parametrize("randomize", ["none", "permutedigits", "fastowen", "owen"])
+def test_zsobol_per_sample_radiance_matches_oracle(ctx, orc, randomize):
+    """pbrt's default sampler (ZSobolSampler, samplers.h:225-364) on the device: integer arithmetic, so the
+    streams are the reference's bit for bit (the restatement is pinned to the reference's class in
+    tests/test_oracle_golden.py, case "zsobol"); full estimator with NEE, exact arithmetic, same bar as the
+    independent sampler: >= 99 % of pixel samples within 1e-3, wavelengths (dimension 0) to 2e-6."""
+    from acceleratedvolrenderer_b200._abi import RANDOMIZE
+    spp = {"none": 4, "permutedigits": 2, "fastowen": 8, "owen": 3}[randomize]  # powers of 4 / of 2 only / none
+    dens, (gd, rd) = small_scene(spp=spp, width=40, height=28)
+    rd = rd.with_(sampler=1, randomize=RANDOMIZE[randomize], sampler_seed=3)
+    mo = orc.medium_uniformgrid(gd)
+    want, wstats = mo.render_samples(rd)
+    mo.close()
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    got, gstats = ctx.render_volpath_samples(md, rd)
+    md.close()
+    assert np.allclose(got[:, 4:8], want[:, 4:8], rtol=2e-6), "wavelengths"
+    L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+    scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+    ok = (np.abs(L - Lw).max(axis=1) <= 1e-3 * scale)
+    assert ok.mean() >= 0.99, f"zsobol/{randomize}: {ok.mean():.4f} of samples match"
+    assert Lw.sum() > 0 and gstats["camera_rays"] == wstats[0]
+    for k, i in (("camera_fetches", 1), ("shadow_fetches", 2), ("scatter_events", 4)):
+        assert abs(gstats[k] - wstats[i]) <= 0.02 * max(1, wstats[i]), k
+
+
+def test_zsobol_converged_image_fast_math(ctx, orc):
+    """FAST math with the zsobol sampler: same estimator, image within the oracle's noise (the oracle images
+    use the independent sampler: two different samplers must agree on the expectation)."""
+    dens, (gd, rd) = small_scene(width=32, height=24, spp=64, max_depth=6)
+    mo = orc.medium_uniformgrid(gd)
+    ref_a, _ = mo.render(rd, threads=8)
+    ref_b, _ = mo.render(rd.with_(sampler_seed=1), threads=8)
+    mo.close()
+    img_a = ctx.film_resolve(rd, ref_a); img_b = ctx.film_resolve(rd, ref_b)
+    noise = noise_floor(img_a, img_b)
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    film, _ = ctx.render_volpath(md, rd.with_(exact_math=0, sampler=1, randomize=2, spp=64 * GPU_SPP_FACTOR))
+    md.close()
+    img = ctx.film_resolve(rd, film)
+    err = image_error(img, img_a, img_b)
+    assert err <= 1.5 * noise + 1e-6, (err, noise)
+    assert abs(img.mean() - img_a.mean()) <= 0.05 * img_a.mean()
+
+
+def test_unknown_sampler_is_rejected(ctx):
+    dens, (gd, rd) = small_scene(width=8, height=8, spp=1)
+    md = ctx.create_medium("uniformgrid", gd, layout="dense")
+    with pytest.raises(Exception):
+        ctx.render_volpath(md, rd.with_(sampler=7))
+    md.close()
+
+
 def general_media(kind):
     """Small RGB-grid / emissive scenes of the class SURVEY.md 8(d) C5 sweeps (general kernel: 4 channels)."""
     from acceleratedvolrenderer_b200._abi import RGBGridDesc

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--env", action="append", default=[],
                     help="NAME=v1;v2;... (repeatable); the product of all lists is swept")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--sampler", default="independent", help="independent | zsobol (fastowen)")
     args = ap.parse_args()
     w = bench.WORKLOADS[args.workload]
     dev = torch.device("cuda", 0)
@@ -43,7 +44,7 @@ def main():
         for exact, *vals in itertools.product(args.exact.split(","), *lists):
             for n, v in zip(names, vals):
                 os.environ[n] = v
-            r = rd.with_(exact_math=int(exact))
+            r = rd.with_(exact_math=int(exact), sampler=1 if args.sampler == "zsobol" else 0, randomize=2)
             best = None
             for i in range(args.reps + 1):
                 film.zero_()
@@ -52,7 +53,7 @@ def main():
                     best = st
             f = best["camera_fetches"] + best["shadow_fetches"]
             bpf = 16 if layout == "octet16" else 32
-            print(json.dumps({"layout": layout, "exact": int(exact), "env": dict(zip(names, vals)),
+            print(json.dumps({"layout": layout, "exact": int(exact), "sampler": args.sampler, "env": dict(zip(names, vals)),
                               "kernel_ms": round(best["kernel_ms"], 2),
                               "Msamples_s": round(W * H * args.spp / best["kernel_ms"] / 1e3, 2),
                               "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1)}),

@@ -80,6 +80,14 @@ class avr_graph_file(C.Structure):
     ]
 
 
+class avr_graph_sidecar(C.Structure):
+    _fields_ = [
+        ("n_vertices", C.c_int32), ("nnz", C.c_int64),
+        ("rowptr", C.POINTER(C.c_int64)), ("col", i32p_), ("val", f32p),
+        ("vertex_pos", f32p), ("light", f32p), ("search_range", f32p),
+    ]
+
+
 class avr_render_desc(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32),

@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-from ._abi import (NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
+from ._abi import (avr_graph_sidecar, NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
                    avr_grid_desc, avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
     "avr_graph_create", "avr_graph_create_from_edges", "avr_graph_get_csr", "avr_graph_file_read",
-    "avr_graph_file_write", "avr_graph_file_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
+    "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
 ]
@@ -65,13 +65,15 @@ def load_library():
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
-                        "avr_graph_destroy", "avr_graph_file_free"):
+                        "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free"):
             fn.restype = C.c_int
     lib.avr_ctx_destroy.restype = None
     lib.avr_medium_destroy.restype = None
     lib.avr_graph_destroy.restype = None
     lib.avr_graph_file_free.restype = None
     lib.avr_graph_file_free.argtypes = [C.c_void_p]
+    lib.avr_graph_sidecar_free.restype = None
+    lib.avr_graph_sidecar_free.argtypes = [C.c_void_p]
     _lib = lib
     return lib
 
@@ -193,6 +195,65 @@ class Context:
                                                         _p(ef, i32p), _p(et, i32p), _p(es, i32p), C.byref(h)))
         g = Graph(self, h, vs.size, 0)
         g.nnz = g.csr_sizes()[1]
+        return g
+
+
+class GraphSidecar:
+    """Binary ".avrg" sidecar of a graph (include/avr.h: avr_graph_sidecar): the CSR transport matrix plus the
+    per-vertex position, light vector L0 and render search range that `graph_maker` never writes to disk
+    (cmd/graph_maker.cpp:167-169).  Host-only."""
+
+    def __init__(self, rowptr, col, val, vertex_pos=None, light=None, search_range=None):
+        f32 = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float32)  # noqa: E731
+        self.rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        self.col = np.ascontiguousarray(col, dtype=np.int32)
+        self.val = _f32(val)
+        self.vertex_pos, self.light, self.search_range = f32(vertex_pos), f32(light), f32(search_range)
+
+    @property
+    def n_vertices(self):
+        return self.rowptr.size - 1
+
+    def write(self, path):
+        lib = load_library()
+        c = avr_graph_sidecar()
+        c.n_vertices, c.nnz = self.n_vertices, self.col.size
+        c.rowptr = _p(self.rowptr, i64p)
+        if self.col.size:
+            c.col, c.val = _p(self.col, i32p), _p(self.val)
+        keep = []
+        for name in ("vertex_pos", "light", "search_range"):
+            a = getattr(self, name)
+            if a is not None:
+                want = self.n_vertices * (3 if name == "vertex_pos" else 1)
+                if a.size != want:
+                    raise ValueError(f"{name}: {a.size} values for {self.n_vertices} vertices")
+                flat = np.ascontiguousarray(a.reshape(-1)); keep.append(flat)
+                setattr(c, name, _p(flat))
+        st = lib.avr_graph_sidecar_write(str(path).encode(), C.byref(c))
+        if st != 0:
+            raise AvrError(st, lib.avr_last_error(None).decode())
+
+    @staticmethod
+    def read(path):
+        lib = load_library()
+        h = C.POINTER(avr_graph_sidecar)()
+        st = lib.avr_graph_sidecar_read(str(path).encode(), C.byref(h))
+        if st != 0:
+            raise AvrError(st, lib.avr_last_error(None).decode())
+        c = h.contents
+        n, nnz = c.n_vertices, c.nnz
+
+        def arr(ptr, cnt, dt):
+            if not ptr:
+                return None
+            return np.ctypeslib.as_array(ptr, shape=(cnt,)).astype(dt, copy=True) if cnt else np.zeros(0, dt)
+
+        g = GraphSidecar(arr(c.rowptr, n + 1, np.int64), arr(c.col, nnz, np.int32), arr(c.val, nnz, np.float32),
+                         arr(c.vertex_pos, 3 * n, np.float32), arr(c.light, n, np.float32), arr(c.search_range, n, np.float32))
+        if g.vertex_pos is not None:
+            g.vertex_pos = g.vertex_pos.reshape(-1, 3)
+        lib.avr_graph_sidecar_free(h)
         return g
 
 

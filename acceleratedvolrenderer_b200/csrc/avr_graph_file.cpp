@@ -205,3 +205,138 @@ extern "C" avr_status avr_graph_file_write(const char *path, const avr_graph_fil
     if (bad) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_file_write: write error on ") + path);
     return AVR_OK;
 }
+
+// ---- binary CSR sidecar (include/avr.h: avr_graph_sidecar) -------------------------------------------
+namespace {
+
+struct Fnv {
+    uint64_t h = 0xcbf29ce484222325ull;
+    void add(const void *p, size_t n) {
+        const unsigned char *b = (const unsigned char *)p;
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 0x100000001b3ull; }
+    }
+};
+struct Writer {
+    FILE *f;
+    Fnv fnv;
+    bool ok = true;
+    void put(const void *p, size_t n) {
+        if (!n) return;
+        fnv.add(p, n);
+        ok = ok && std::fwrite(p, 1, n, f) == n;
+    }
+};
+struct Reader {
+    FILE *f;
+    Fnv fnv;
+    bool get(void *p, size_t n) {
+        if (!n) return true;
+        if (std::fread(p, 1, n, f) != n) return false;
+        fnv.add(p, n);
+        return true;
+    }
+};
+enum { SC_POS = 1, SC_LIGHT = 2, SC_RANGE = 4 };
+
+// NULL if rowptr / col describe a CSR matrix over n_vertices rows and columns
+const char *csr_defect(const avr_graph_sidecar *s) {
+    size_t n = size_t(s->n_vertices), nnz = size_t(s->nnz);
+    if (s->rowptr[0] != 0 || s->rowptr[n] != s->nnz) return "rowptr does not span [0, nnz]";
+    for (size_t i = 0; i < n; ++i)
+        if (s->rowptr[i + 1] < s->rowptr[i]) return "rowptr not monotone";
+    for (size_t i = 0; i < nnz; ++i)
+        if (s->col[i] < 0 || s->col[i] >= s->n_vertices) return "column index outside [0, n)";
+    return nullptr;
+}
+
+}  // namespace
+
+extern "C" void avr_graph_sidecar_free(avr_graph_sidecar *s) {
+    if (!s) return;
+    void *ptrs[] = {s->rowptr, s->col, s->val, s->vertex_pos, s->light, s->search_range};
+    for (void *p : ptrs) std::free(p);
+    std::free(s);
+}
+
+extern "C" avr_status avr_graph_sidecar_write(const char *path, const avr_graph_sidecar *s) {
+    if (!path || !s) return fail(AVR_ERR_BAD_ARG, "avr_graph_sidecar_write: NULL argument");
+    if (s->n_vertices < 1 || s->nnz < 0 || !s->rowptr || (s->nnz && (!s->col || !s->val)))
+        return fail(AVR_ERR_BAD_ARG, "avr_graph_sidecar_write: need n_vertices >= 1, rowptr, and col / val for nnz > 0");
+    if (const char *why = csr_defect(s))
+        return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_sidecar_write: ") + why);
+    FILE *f = std::fopen(path, "wb");
+    if (!f) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_sidecar_write: cannot open ") + path);
+    Writer w{f};
+    size_t n = size_t(s->n_vertices), nnz = size_t(s->nnz);
+    uint32_t version = 1, flags = (s->vertex_pos ? SC_POS : 0) | (s->light ? SC_LIGHT : 0) | (s->search_range ? SC_RANGE : 0);
+    w.put("AVRG", 4);
+    w.put(&version, 4);
+    w.put(&s->n_vertices, 4);
+    w.put(&flags, 4);
+    w.put(&s->nnz, 8);
+    w.put(s->rowptr, (n + 1) * 8);
+    w.put(s->col, nnz * 4);
+    w.put(s->val, nnz * 4);
+    if (s->vertex_pos) w.put(s->vertex_pos, 3 * n * 4);
+    if (s->light) w.put(s->light, n * 4);
+    if (s->search_range) w.put(s->search_range, n * 4);
+    uint64_t sum = w.fnv.h;
+    bool ok = w.ok && std::fwrite(&sum, 1, 8, f) == 8;
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_sidecar_write: write error on ") + path);
+    return AVR_OK;
+}
+
+extern "C" avr_status avr_graph_sidecar_read(const char *path, avr_graph_sidecar **out) {
+    if (!path || !out) return fail(AVR_ERR_BAD_ARG, "avr_graph_sidecar_read: NULL argument");
+    *out = nullptr;
+    FILE *f = std::fopen(path, "rb");
+    if (!f) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_sidecar_read: cannot open ") + path);
+    std::fseek(f, 0, SEEK_END);
+    long file_bytes = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    Reader r{f};
+    char magic[4];
+    uint32_t version = 0, flags = 0;
+    int32_t n = 0;
+    int64_t nnz = 0;
+    avr_graph_sidecar *s = nullptr;
+    auto bail = [&](const char *msg) {
+        std::fclose(f);
+        avr_graph_sidecar_free(s);
+        return fail(AVR_ERR_BAD_ARG, std::string("graph sidecar: ") + msg);
+    };
+    if (!r.get(magic, 4) || std::memcmp(magic, "AVRG", 4) != 0) return bail("not an AVRG file");
+    if (!r.get(&version, 4) || version != 1) return bail("unsupported version");
+    if (!r.get(&n, 4) || !r.get(&flags, 4) || !r.get(&nnz, 8) || n < 1 || nnz < 0 || (flags & ~7u))
+        return bail("bad header");
+    // the header fixes the file size: check it before allocating from untrusted counts
+    unsigned long long per_vertex = 8ull + ((flags & SC_POS) ? 12ull : 0ull) + ((flags & SC_LIGHT) ? 4ull : 0ull) +
+                                    ((flags & SC_RANGE) ? 4ull : 0ull);
+    unsigned long long want = 24ull + 8ull + per_vertex * (unsigned long long)n + 8ull * (unsigned long long)nnz + 8ull;
+    if ((unsigned long long)file_bytes != want) return bail("file size does not match its header (truncated?)");
+    s = (avr_graph_sidecar *)std::calloc(1, sizeof(avr_graph_sidecar));
+    s->n_vertices = n;
+    s->nnz = nnz;
+    size_t N = size_t(n), NNZ = size_t(nnz);
+    s->rowptr = (int64_t *)std::malloc((N + 1) * 8);
+    s->col = (int32_t *)std::malloc(NNZ ? NNZ * 4 : 4);
+    s->val = (float *)std::malloc(NNZ ? NNZ * 4 : 4);
+    if (flags & SC_POS) s->vertex_pos = (float *)std::malloc(3 * N * 4);
+    if (flags & SC_LIGHT) s->light = (float *)std::malloc(N * 4);
+    if (flags & SC_RANGE) s->search_range = (float *)std::malloc(N * 4);
+    if (!s->rowptr || !s->col || !s->val || ((flags & SC_POS) && !s->vertex_pos) || ((flags & SC_LIGHT) && !s->light) ||
+        ((flags & SC_RANGE) && !s->search_range))
+        return bail("out of memory");
+    bool ok = r.get(s->rowptr, (N + 1) * 8) && r.get(s->col, NNZ * 4) && r.get(s->val, NNZ * 4);
+    if (ok && s->vertex_pos) ok = r.get(s->vertex_pos, 3 * N * 4);
+    if (ok && s->light) ok = r.get(s->light, N * 4);
+    if (ok && s->search_range) ok = r.get(s->search_range, N * 4);
+    uint64_t sum = 0;
+    if (!ok || std::fread(&sum, 1, 8, f) != 8) return bail("truncated");
+    if (sum != r.fnv.h) return bail("checksum mismatch");
+    if (const char *why = csr_defect(s)) return bail(why);
+    std::fclose(f);
+    *out = s;
+    return AVR_OK;
+}

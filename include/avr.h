@@ -383,6 +383,34 @@ avr_status avr_graph_file_read(const char *path, avr_graph_file **out);
 avr_status avr_graph_file_write(const char *path, const avr_graph_file *g);
 void avr_graph_file_free(avr_graph_file *g);
 
+/* ---- binary sidecar of a graph -------------------------------------------------
+ * `graph_maker` keeps the edge weights only in memory (cmd/graph_maker.cpp:167-169: lightVec and
+ * transportMat are built, used and dropped; the files it writes hold vertices only), so the
+ * propagation can only be fed from inside that tool.  The sidecar persists exactly what kernel 3 and
+ * the graph render consume: the transport matrix in CSR (as avr_graph_get_csr returns it), and per
+ * vertex the position, the light vector entry L0 (LightingCalculator::GetLightVector) and the
+ * render search range.  Little-endian file "<name>.avrg":
+ *   char magic[4] = "AVRG"; u32 version = 1; i32 n_vertices; u32 flags (1 pos, 2 light, 4 range);
+ *   i64 nnz; i64 rowptr[n+1]; i32 col[nnz]; f32 val[nnz]; f32 pos[3n]; f32 light[n]; f32 range[n]
+ *   (absent arrays skipped); u64 FNV-1a of every preceding byte.
+ * Pure host code.  Arrays not present are NULL. */
+typedef struct avr_graph_sidecar {
+    int32_t n_vertices;
+    int64_t nnz;
+    int64_t *rowptr;      /* n_vertices + 1 */
+    int32_t *col;         /* nnz            */
+    float *val;           /* nnz: edge.samples / vertex.samples (lighting_calculator.cpp:74-77) */
+    float *vertex_pos;    /* 3 * n_vertices, or NULL */
+    float *light;         /* n_vertices: L0, or NULL  */
+    float *search_range;  /* n_vertices: renderSearchRange, or NULL */
+} avr_graph_sidecar;
+
+avr_status avr_graph_sidecar_write(const char *path, const avr_graph_sidecar *s);
+/* *out is allocated by the library; a truncated file, a bad checksum or an inconsistent CSR
+ * (rowptr not monotone, col outside [0, n)) is AVR_ERR_BAD_ARG. */
+avr_status avr_graph_sidecar_read(const char *path, avr_graph_sidecar **out);
+void avr_graph_sidecar_free(avr_graph_sidecar *s);
+
 /* Parity probe for the EXACT path's restated scalar functions: kind 0 = logf (glibc algorithm),
  * 1 = sinf, 2 = cosf (glibc), 3 = FastExp CPU branch (util/math.h:453-474).  Host buffers. */
 avr_status avr_debug_math(avr_ctx *ctx, int kind, const float *x, int64_t n, float *out);

@@ -127,3 +127,71 @@ def test_round_trip_and_errors(tmp_path):
         GraphFile.read(tmp_path / "uni.txt")
     with pytest.raises(AvrError, match="flag is set"):
         gf.write(tmp_path / "x.txt", (0, 1, 0, 1, 1), (1, 0, 0))  # useSamples without vertex samples
+
+
+# ---- binary ".avrg" sidecar (include/avr.h: avr_graph_sidecar) -------------------------
+def sidecar_case(orc, n=1500, ne=7000):
+    from acceleratedvolrenderer_b200.api import GraphSidecar
+    g, r = build(orc, n, ne)
+    T = g.transport()  # the reference-pinned GetTransportMatrix of the same graph (rowptr, col, val)
+    g.close()
+    rng = np.random.default_rng(5)
+    return GraphSidecar(T[0], T[1], T[2], vertex_pos=r["pos"], light=rng.random(n, dtype=np.float32),
+                        search_range=r["vrange"]), T
+
+
+def test_sidecar_round_trip_is_bit_exact(orc, tmp_path):
+    from acceleratedvolrenderer_b200.api import GraphSidecar
+    sc, T = sidecar_case(orc)
+    p = tmp_path / "graph.avrg"
+    sc.write(p)
+    n, nnz = sc.n_vertices, sc.col.size
+    assert os.path.getsize(p) == 24 + 8 * (n + 1) + 8 * nnz + 20 * n + 8
+    back = GraphSidecar.read(p)
+    for name in ("rowptr", "col", "val", "vertex_pos", "light", "search_range"):
+        a, b = getattr(sc, name), getattr(back, name)
+        assert a.reshape(-1).tobytes() == b.reshape(-1).tobytes(), name
+    # optional arrays may be absent; an edgeless graph is legal
+    bare = GraphSidecar(np.zeros(4, np.int64), np.zeros(0, np.int32), np.zeros(0, np.float32))
+    bare.write(p)
+    b2 = GraphSidecar.read(p)
+    assert b2.n_vertices == 3 and b2.col.size == 0 and b2.vertex_pos is None and b2.light is None and b2.search_range is None
+
+
+def test_sidecar_rejects_damaged_files(orc, tmp_path):
+    from acceleratedvolrenderer_b200.api import GraphSidecar
+    sc, _ = sidecar_case(orc, 40, 150)
+    p = tmp_path / "graph.avrg"
+    sc.write(p)
+    data = bytearray(open(p, "rb").read())
+    cases = {"truncated": bytes(data[:-9]), "magic": b"AVRX" + bytes(data[4:]), "version": bytes(data[:4]) + b"\x02\0\0\0" + bytes(data[8:])}
+    flipped = bytearray(data); flipped[len(data) // 2] ^= 0x10
+    cases["bit flip"] = bytes(flipped)
+    for name, blob in cases.items():
+        q = tmp_path / "bad.avrg"
+        open(q, "wb").write(blob)
+        with pytest.raises(AvrError):
+            GraphSidecar.read(q)
+    with pytest.raises(AvrError):
+        GraphSidecar.read(tmp_path / "missing.avrg")
+    # a CSR that does not describe n vertices is refused at write time
+    bad = GraphSidecar(np.array([0, 2, 1], np.int64), np.zeros(1, np.int32), np.ones(1, np.float32))
+    with pytest.raises(AvrError):
+        bad.write(tmp_path / "bad2.avrg")
+
+
+@pytest.mark.gpu
+def test_sidecar_feeds_the_propagation(ctx, orc, tmp_path):
+    """graph_maker -> .avrg -> kernel 3: the light the device propagates from a sidecar read back from disk
+    is bit-identical to the oracle's ComputeFinalLight on the in-memory graph."""
+    from acceleratedvolrenderer_b200.api import GraphSidecar
+    from cpu_checker import Checker  # noqa: F401
+    sc, T = sidecar_case(orc)
+    p = tmp_path / "graph.avrg"
+    sc.write(p)
+    back = GraphSidecar.read(p)
+    g = ctx.create_graph(back.rowptr, back.col, back.val)
+    total, it = g.compute_final_light(back.light, 6)
+    g.close()
+    want, wit = orc.graph_propagate(T[0], T[1], T[2], sc.light, 6)
+    assert it == wit and total.tobytes() == want.tobytes()

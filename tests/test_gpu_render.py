@@ -151,6 +151,57 @@ def test_unknown_sampler_is_rejected(ctx):
     md.close()
 
 
+def test_render_edge_cases(ctx, orc):
+    """Shapes at the edges of the scene class, each against the oracle on identical sampler streams:
+    an all-zero density grid (no collision can happen), a 1x1 film, maxdepth 0 and 1, a cropped
+    pixel window with a sample sub-range, and a camera that misses the boundary altogether."""
+    dens, (gd, rd) = small_scene(width=20, height=16, spp=2)
+
+    def compare(gd_, rd_, frac=0.99):
+        mo = orc.medium_uniformgrid(gd_)
+        want, wstats = mo.render_samples(rd_)
+        mo.close()
+        md = ctx.create_medium("uniformgrid", gd_, layout="octet32")
+        got, gstats = ctx.render_volpath_samples(md, rd_)
+        md.close()
+        assert got.shape == want.shape and gstats["camera_rays"] == wstats[0]
+        assert np.allclose(got[:, 4:8], want[:, 4:8], rtol=2e-6)
+        scale = np.maximum(np.abs(want[:, :4]).max(axis=1), 1e-6)
+        ok = np.abs(got[:, :4].astype(np.float64) - want[:, :4]).max(axis=1) <= 1e-3 * scale
+        assert ok.mean() >= frac, ok.mean()
+        return got, want, gstats, wstats
+
+    # empty medium: radiance exactly zero, no density fetch, no scattering
+    empty = GridDesc(np.zeros_like(dens), gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=0.4)
+    got, want, gs, ws = compare(empty, rd, frac=1.0)
+    assert not got[:, :4].any() and not want[:, :4].any()
+    assert gs["camera_fetches"] == ws[1] == 0 and gs["scatter_events"] == 0 and gs["shadow_fetches"] == 0
+    # 1x1 film, odd sample count
+    _, (gd1, rd1) = small_scene(width=1, height=1, spp=5)
+    compare(gd1, rd1, frac=1.0)
+    # maxdepth 0: emission only (none here) -> zero; maxdepth 1: single scattering
+    got0, want0, _, _ = compare(gd, rd.with_(max_depth=0), frac=1.0)
+    assert not got0[:, :4].any()
+    got1, _, gs1, ws1 = compare(gd, rd.with_(max_depth=1))
+    assert got1[:, :4].sum() > 0 and abs(gs1["scatter_events"] - ws1[4]) <= 0.02 * ws1[4]
+    # crop window + sample sub-range: the same numbers as the corresponding block of the full render
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    full, _ = ctx.render_volpath_samples(md, rd)
+    crop, _ = ctx.render_volpath_samples(md, rd.with_(pixel_bounds=(3, 5, 11, 12), sample_begin=1, sample_end=2))
+    md.close()
+    full = full.reshape(16, 20, 2, 12)
+    assert crop.tobytes() == np.ascontiguousarray(full[5:12, 3:11, 1:2]).reshape(-1, 12).tobytes()
+    compare(gd, rd.with_(pixel_bounds=(3, 5, 11, 12), sample_begin=1, sample_end=2))
+    # camera looking away from the boundary: every ray misses, L = 0, no work
+    rfc = np.array(list(rd.c.render_from_camera), dtype=np.float32).reshape(4, 4).copy()
+    rfc[:3, :3] = -rfc[:3, :3]  # turn the camera around (keeps it a rigid transform up to handedness)
+    away = rd.with_()
+    for i, v in enumerate(rfc.ravel()):
+        away.c.render_from_camera[i] = float(v)
+    got, want, gs, ws = compare(gd, away, frac=1.0)
+    assert not got[:, :4].any() and gs["segments"] == 0 and gs["camera_fetches"] == 0
+
+
 def general_media(kind):
     """Small RGB-grid / emissive scenes of the class SURVEY.md 8(d) C5 sweeps (general kernel: 4 channels)."""
     from acceleratedvolrenderer_b200._abi import RGBGridDesc

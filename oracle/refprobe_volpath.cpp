@@ -18,6 +18,8 @@
 #include <pbrt/media.h>
 #include <pbrt/samplers.h>
 #include <pbrt/shapes.h>
+#include <pbrt/util/buffercache.h>
+#include <pbrt/util/mesh.h>
 #include <pbrt/util/spectrum.h>
 
 using namespace pbrt;
@@ -33,8 +35,11 @@ extern "C" {
 // sceneRadius after Preprocess}.
 void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir[3], const float *light_spec,
                     int32_t max_depth, int32_t sampler_seed, int32_t spp, const int32_t *samples, const float *rays,
-                    int64_t n, float *out, float *info, const int32_t sampler_cfg[4]) {
-    // sampler_cfg = {0 independent | 1 zsobol, RandomizeStrategy, film width, film height}
+                    int64_t n, float *out, float *info, const int32_t sampler_cfg[5]) {
+    // sampler_cfg = {0 independent | 1 zsobol, RandomizeStrategy, film width, film height,
+    //                boundary: 0 = Shape "sphere" (sphere[0..3] = centre, radius),
+    //                          1 = Shape "trianglemesh" box (sphere[0..5] = min xyz, max xyz), 12 outward-wound
+    //                              triangles under the default BVH aggregate}
     // --disable-texture-filtering: SurfaceInteraction::ComputeDifferentials (interaction.cpp:41-47) then
     // skips the camera-based footprint estimate, the only use Li makes of the camera (none is built
     // here); it feeds texture lookups only, which the "interface" boundary does not have.
@@ -43,13 +48,40 @@ void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir
     Options = &opts;
     Allocator alloc;
     Medium medium = *ref_medium_ptr(medium_h);
-    // Shape "sphere" at Translate(c): shapes.cpp Sphere::Create defaults zmin = -radius, zmax = radius, phimax = 360
-    Transform *rfo = new Transform(Translate(Vector3f(sphere[0], sphere[1], sphere[2])));
-    Transform *ofr = new Transform(Inverse(*rfo));
-    Sphere *sph = new Sphere(rfo, ofr, false, sphere[3], -sphere[3], sphere[3], 360.f);
-    // Material "interface" = null material; MediumInterface(inside = medium, outside = none)
-    GeometricPrimitive *prim = new GeometricPrimitive(Shape(sph), Material(), Light(), MediumInterface(medium, nullptr));
-    Primitive aggregate(prim);
+    Primitive aggregate;
+    if (sampler_cfg[4] == 0) {
+        // Shape "sphere" at Translate(c): shapes.cpp Sphere::Create defaults zmin = -radius, zmax = radius, phimax = 360
+        Transform *rfo = new Transform(Translate(Vector3f(sphere[0], sphere[1], sphere[2])));
+        Transform *ofr = new Transform(Inverse(*rfo));
+        Sphere *sph = new Sphere(rfo, ofr, false, sphere[3], -sphere[3], sphere[3], 360.f);
+        // Material "interface" = null material; MediumInterface(inside = medium, outside = none)
+        aggregate = new GeometricPrimitive(Shape(sph), Material(), Light(), MediumInterface(medium, nullptr));
+    } else {
+        // Shape "trianglemesh": the 8 corners, 12 triangles with outward geometric normals (SURVEY appendix A:
+        // an inward-wound cube assigns the medium to the wrong side); BVHAggregate defaults of the scene
+        // loader (maxnodeprims 4, SAH: cpu/aggregates.cpp BVHAggregate::Create)
+        static bool init = false;
+        if (!init) {
+            InitBufferCaches();
+            Triangle::Init(alloc);
+            init = true;
+        }
+        const float *b = sphere;
+        std::vector<Point3f> P;
+        for (int i = 0; i < 8; ++i) P.push_back(Point3f(b[(i & 1) ? 3 : 0], b[(i & 2) ? 4 : 1], b[(i & 4) ? 5 : 2]));
+        std::vector<int> idx = {0, 2, 1, 1, 2, 3,   // z = min (normal -z)
+                                4, 5, 6, 5, 7, 6,   // z = max (+z)
+                                0, 1, 4, 1, 5, 4,   // y = min (-y)
+                                2, 6, 3, 3, 6, 7,   // y = max (+y)
+                                0, 4, 2, 2, 4, 6,   // x = min (-x)
+                                1, 3, 5, 3, 7, 5};  // x = max (+x)
+        TriangleMesh *mesh = new TriangleMesh(Transform(), false, idx, P, {}, {}, {}, {}, alloc);
+        pstd::vector<Shape> tris = Triangle::CreateTriangles(mesh, alloc);
+        std::vector<Primitive> prims;
+        for (Shape sh : tris)
+            prims.push_back(new GeometricPrimitive(sh, Material(), Light(), MediumInterface(medium, nullptr)));
+        aggregate = new BVHAggregate(prims, 4, BVHAggregate::SplitMethod::SAH);
+    }
     // LightSource "distant": renderFromLight maps +z to the direction towards the light
     Vector3f w = Normalize(Vector3f(light_dir[0], light_dir[1], light_dir[2]));
     Frame f = Frame::FromZ(w);

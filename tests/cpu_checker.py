@@ -382,18 +382,18 @@ class CheckerMedium:
             out, _ = self.render_samples(rdesc)
             c = rdesc.c
             return out, np.array([c.light_dir[0], c.light_dir[1], c.light_dir[2], c.scene_radius], dtype=np.float32)
-        assert rdesc.c.boundary_type == 0, "the reference probe builds a Shape \"sphere\" boundary"
+        btype = int(rdesc.c.boundary_type)  # 0: Shape "sphere"; 1: 12-triangle box under a BVH
         if rays is None:
             samples, rays = self.camera_rays(rdesc, samples)
         samples = np.ascontiguousarray(samples, dtype=np.int32); rays = f32(rays)
         n = samples.shape[0]
-        sphere = np.array(list(rdesc.c.boundary)[:4], dtype=np.float32)
+        sphere = np.array(list(rdesc.c.boundary)[:6], dtype=np.float32)
         ld = np.array(list(rdesc.c.light_dir), dtype=np.float32)
         out = np.zeros((n, 12), dtype=np.float32); info = np.zeros(4, dtype=np.float32)
         self.ck.lib.ref_volpath_li(self.h, _p(sphere, f32p), _p(ld, f32p), _p(rdesc.light_spectrum, f32p),
                                    C.c_int32(rdesc.c.max_depth), C.c_int32(rdesc.c.sampler_seed), C.c_int32(rdesc.c.spp),
                                    _p(samples, i32p), _p(rays, f32p), C.c_int64(n), _p(out, f32p), _p(info, f32p),
-                                   _p(np.array([rdesc.c.sampler, rdesc.c.randomize, rdesc.c.width, rdesc.c.height],
+                                   _p(np.array([rdesc.c.sampler, rdesc.c.randomize, rdesc.c.width, rdesc.c.height, btype],
                                                dtype=np.int32), i32p))
         return out, info
 

@@ -380,6 +380,10 @@ def li_scenes():
     black = scenes.cloud_scene(dens, width=48, height=36, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8,
                                light_scale=0.0)[1]
     out.append(("lockstep_grid", "uniformgrid", em, black))
+    # box boundary: the reference side is a 12-triangle "trianglemesh" cube under the default BVH aggregate
+    black_box = scenes.cloud_scene(dens, width=48, height=36, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8,
+                                   light_scale=0.0, boundary="box")[1]
+    out.append(("lockstep_grid_box", "uniformgrid", em, black_box))
     d2 = dens.copy(); d2[d2 < 0.02] = 0
     nd, rdn = scenes.cloud_scene_nanovdb(d2, temperature=(d2 * 2500 + 200).astype(np.float32), le_scale=0.4, width=40,
                                          height=30, spp=4, sigma_t=18.0, albedo=0.95, g=0.4, max_depth=6, light_scale=0.0)

@@ -53,11 +53,38 @@ AVR_DEV uint32_t zsobol_perm(int p) {
     return uint32_t(w >> (8 * (p & 7))) & 0xffu;
 }
 
+// (MixBits(v) >> 24) % 24 for v < 2^32: the 64-bit mix with a 32-bit input, and the modulo without a 64-bit
+// division: x % 24 = 8 ((x >> 3) % 3) + (x & 7), and 2^32 = 1 (mod 3)
+AVR_DEV int zsobol_perm_index32(uint32_t v32) {
+    uint64_t v = mix_bits(uint64_t(v32));
+    uint32_t lo = uint32_t(v >> 24), hi = uint32_t(v >> 56);  // x = hi * 2^32 + lo, hi < 256
+    uint32_t ylo = (lo >> 3) | (hi << 29), yhi = hi >> 3;
+    uint32_t r3 = (ylo % 3u + yhi) % 3u;
+    return int(8u * r3 + (lo & 7u));
+}
+
 AVR_DEV uint64_t zsobol_sample_index(const SamplerCfg &c, uint64_t morton, int dimension) {
-    uint64_t idx = 0;
     const bool pow2 = c.log2spp & 1;
     const int last = pow2 ? 1 : 0;
-    const uint64_t dmix = uint64_t(0x55555555u * (uint32_t)dimension);
+    const uint32_t dmix32 = 0x55555555u * (uint32_t)dimension;
+    if (2 * c.nbase4 <= 32) {
+        // every film up to 4096^2 x 256 spp: the Morton index fits 32 bits, all shifts are 32-bit
+        const uint32_t m = uint32_t(morton);
+        uint32_t idx = 0;
+#pragma unroll 1
+        for (int i = c.nbase4 - 1; i >= last; --i) {
+            int shift = 2 * i - (pow2 ? 1 : 0);
+            uint32_t digit = (m >> shift) & 3u;
+            uint32_t higher = shift + 2 < 32 ? m >> (shift + 2) : 0u;
+            int p = zsobol_perm_index32(higher ^ dmix32);
+            idx |= ((zsobol_perm(p) >> (2 * digit)) & 3u) << shift;
+        }
+        if (pow2) idx |= (m & 1u) ^ uint32_t(mix_bits(uint64_t((m >> 1) ^ dmix32)) & 1ull);
+        return idx;
+    }
+    uint64_t idx = 0;
+    const uint64_t dmix = uint64_t(dmix32);
+#pragma unroll 1
     for (int i = c.nbase4 - 1; i >= last; --i) {
         int shift = 2 * i - (pow2 ? 1 : 0);
         int digit = int((morton >> shift) & 3);
@@ -85,6 +112,7 @@ AVR_DEV uint32_t randomize_bits(int strategy, uint32_t seed, uint32_t v) {
         return __brev(v);
     }
     if (seed & 1u) v ^= 1u << 31;
+#pragma unroll 1
     for (int b = 1; b < 32; ++b) {
         uint32_t mask = (~0u) << (32 - b);
         if (uint32_t(mix_bits(uint64_t((v & mask) ^ seed))) & (1u << b)) v ^= 1u << (31 - b);

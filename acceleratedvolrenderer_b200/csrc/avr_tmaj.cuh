@@ -4,6 +4,9 @@
 #pragma once
 #include "avr_medium.cuh"
 
+#ifndef AVR_PREFETCH
+#define AVR_PREFETCH 0  // build knob: 1 / 2 = prefetch.global.L1 / .L2 of the density octet when the collision distance is drawn
+#endif
 #ifndef AVR_SPLIT_FETCH
 #define AVR_SPLIT_FETCH 0  // build knob: 1 = request the density taps when the collision distance is drawn (measured slower: 59.8 -> 70.2 ms)
 #endif
@@ -102,6 +105,20 @@ struct Fetcher {
             uint4 q = __ldg(mv.oct16 + octet_index(cx, cy, cz, mv.nbx, mv.nby));
             a = make_float4(__uint_as_float(q.x), __uint_as_float(q.y), __uint_as_float(q.z), __uint_as_float(q.w));
         }
+    }
+    // FAST octet layouts: fire-and-forget prefetch of the octet a tentative collision at t will read; the
+    // render kernel issues it when the collision distance becomes known, up to walk_steps DDA steps
+    // before op B consumes the octet.  No register is held across the gap.
+    static constexpr int kPrefetch = (!TR::EXACT && !TR::GENERAL && TR::LAYOUT != LAYOUT_DENSE_F32) ? AVR_PREFETCH : 0;
+    AVR_DEV void prefetch(const MediumView &mv, float t) const {
+        float sx = __fmaf_rn(sd.x, t, so.x), sy = __fmaf_rn(sd.y, t, so.y), sz = __fmaf_rn(sd.z, t, so.z);
+        int cx = (int)floorf(sx) + 1, cy = (int)floorf(sy) + 1, cz = (int)floorf(sz) + 1;
+        if ((unsigned)cx > (unsigned)mv.nx || (unsigned)cy > (unsigned)mv.ny || (unsigned)cz > (unsigned)mv.nz) return;
+        const void *p = TR::LAYOUT == LAYOUT_OCTET_F32
+                            ? (const void *)(mv.oct32 + 2 * size_t(octet_index(cx, cy, cz, mv.nbx, mv.nby)))
+                            : (const void *)(mv.oct16 + octet_index(cx, cy, cz, mv.nbx, mv.nby));
+        if (kPrefetch == 1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+        else asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     }
     AVR_DEV float resolve(float t, const float4 &a, const float4 &b) const {
         float sx = __fmaf_rn(sd.x, t, so.x), sy = __fmaf_rn(sd.y, t, so.y), sz = __fmaf_rn(sd.z, t, so.z);

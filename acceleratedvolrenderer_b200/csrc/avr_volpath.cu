@@ -714,6 +714,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                             ln.seg_tMax = b;
                             ln.state = ST_COLLIDE;
                             if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
+                            if (Fetcher<TR>::kPrefetch) ln.fe.prefetch(mv, tt);
                         } else
                             ln.u -= dtau;
                     }
@@ -747,6 +748,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 if (hit) {
                     ln.cur_tMin = tt;
                     if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
+                    if (Fetcher<TR>::kPrefetch) ln.fe.prefetch(mv, tt);
                 } else
                     ln.u = tau - dtau;
                 ln.state = hit ? ST_COLLIDE : ST_WALK;

@@ -255,6 +255,41 @@ class Checker:
         return out
 
 
+    def graph_connect_info(self, search_range, n, vertex_radius):
+        rng = None if search_range is None else f32(search_range)
+        out = np.zeros(3, dtype=np.float32)
+        self.fn("graph_connect_info")(C.c_int32(n), _p(rng, f32p) if rng is not None else None, C.c_float(vertex_radius),
+                                      _p(out, f32p))
+        return out
+
+
+class RefGraphIntegrator:
+    """The reference's own GraphIntegrator::Initialize + ConnectToGraph (oracle/refprobe_graphint.cpp) over a graph
+    file `<directory>/files/graphs/<name>.txt` written by the reference's writer."""
+
+    def __init__(self, ck, directory, name):
+        assert ck.kind == "ref"
+        self.ck = ck
+        fn = ck.lib.ref_graph_integrator_open; fn.restype = C.c_void_p
+        h = fn(str(directory).encode(), str(name).encode())
+        assert h, "ref_graph_integrator_open failed"
+        self.h = C.c_void_p(h)
+
+    def info(self):
+        out = np.zeros(4, dtype=np.float32)
+        self.ck.lib.ref_graph_integrator_info(self.h, _p(out, f32p))
+        return out
+
+    def connect(self, points):
+        points = f32(points); n = points.size // 3
+        out = np.empty(n, dtype=np.float32)
+        self.ck.lib.ref_graph_connect(self.h, _p(points, f32p), C.c_int64(n), _p(out, f32p))
+        return out
+
+    def close(self):
+        self.ck.lib.ref_graph_integrator_close(self.h)
+
+
 class CheckerGraph:
     """A FreeGraph held by the checker (reference: the fork's own graph::FreeGraph; oracle: FreeGraphR)."""
 

@@ -4,6 +4,8 @@ restatement, oracle/liboracle.so).  Every case returns {name: ndarray}; the bar 
 
 Case inputs are small on purpose: the fixtures travel with the repository.
 """
+import os
+
 import numpy as np
 
 from acceleratedvolrenderer_b200 import scenes
@@ -331,6 +333,40 @@ def case_graphfile(ck):
     return out
 
 
+# ---- GraphIntegrator::Initialize + ConnectToGraph (graph/graph_integrator.cpp:24-80, :249-280) ----------
+def case_graphconnect(ck):
+    """ck "ref": the reference's own compiled GraphIntegrator methods over a graph file written and read by the
+    reference (oracle/refprobe_graphint.cpp); ck "orc": the restatement over the same file contents (its
+    writer is byte-identical, case "graphfile")."""
+    import tempfile
+    from cpu_checker import RefGraphIntegrator
+    n, ne, radius = 1500, 7000, 0.05
+    r = scenes.random_edge_graph(n, ne, seed=n)
+    g = ck.graph_build(radius, np.arange(n), r["pos"], vtype=r["vtype"], vlight=r["vlight"], vsamples=r["vsamples"],
+                       vrange=r["vrange"] * 3, vcoors=r["vcoors"])
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        os.makedirs(os.path.join(tmp, "files", "graphs"))
+        for use_range in (1, 0):
+            path = os.path.join(tmp, "files", "graphs", f"probe{use_range}.txt")
+            g.write(path, "basic", (0, 0, 0, 1, use_range), (1, 0, 0))  # what graph_maker writes
+            back = ck.graph_read(path); d = back.get(); back.close()
+            rng = np.random.default_rng(3)
+            near = d["pos"].reshape(-1, 3)[rng.integers(0, n, 600)] + rng.normal(0, radius * 0.6, (600, 3)).astype(np.float32)
+            far = rng.uniform(-1, 3, (600, 3)).astype(np.float32)
+            pts = np.concatenate([near, far]).astype(np.float32)
+            if ck.kind == "ref":
+                gi = RefGraphIntegrator(ck, tmp, f"probe{use_range}")
+                out[f"info{use_range}"] = gi.info()[:3]
+                out[f"connect{use_range}"] = gi.connect(pts)
+                gi.close()
+            else:
+                out[f"info{use_range}"] = ck.graph_connect_info(d["vrange"] if use_range else None, n, radius)
+                out[f"connect{use_range}"] = ck.graph_connect(d["pos"], d["vlight"], d["vrange"] if use_range else None, radius, pts)
+    g.close()
+    return out
+
+
 # ---- ZSobolSampler (samplers.h:225-364) + SobolSample randomizers (util/lowdiscrepancy.h:168-258) -------
 def zsobol_configs():
     """(spp, film resolution, RandomizeStrategy, seed): powers of 4, of 2 only, non-powers of two, odd films."""
@@ -357,7 +393,7 @@ def case_zsobol(ck):
     return out
 
 
-CASES = {"zsobol": case_zsobol, "scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
+CASES = {"zsobol": case_zsobol, "graphconnect": case_graphconnect, "scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
          "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph, "graphfile": case_graphfile}
 
 

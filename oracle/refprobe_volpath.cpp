@@ -10,9 +10,13 @@
 // camera classes need the reference's generated rgb2spec tables and OpenEXR and are not built here).
 // Everything the integrator references but never reaches for this scene class (surface materials,
 // textures, image IO, other shapes) is closed at link time by generated abort() stubs, see Makefile.
+#include <cstring>
+
 #include <pbrt/cpu/aggregates.h>
 #include <pbrt/cpu/integrators.h>
 #include <pbrt/cpu/primitive.h>
+#include <pbrt/cameras.h>
+#include <pbrt/film.h>
 #include <pbrt/filters.h>
 #include <pbrt/lights.h>
 #include <pbrt/media.h>
@@ -117,6 +121,106 @@ void ref_volpath_li(void *medium_h, const float sphere[4], const float light_dir
             out[12 * i + 4 + k] = lambda[k];
             out[12 * i + 8 + k] = lambda.PDF()[k];
         }
+    }
+}
+
+// The reference's inline film code: PixelSensor::ToSensorRGB (film.h:95-100), RGBFilm::AddSample (:239-255) and
+// RGBFilm::GetPixelRGB (:257-275).  Their constructors need RGBColorSpace objects (generated rgb2spec tables,
+// not buildable here) that none of the three methods reads: sensor and film are laid out in zeroed storage
+// and only the members those methods use are constructed (the three response curves, imagingRatio,
+// maxComponentValue, filterIntegral = 1 for the splat term, outputRGBFromSensorRGB, the pixel array).
+// samples: pixels {px, py}, values {L[4], lambda[4], pdf[4]}, weight 1, in the order given.
+// film: width*height*4 doubles {rgbSum[3], weightSum}; rgb: width*height*3 floats from GetPixelRGB.
+void ref_film_add_samples(int32_t width, int32_t height, const float *sensor_rgb, float imaging_ratio,
+                          float max_component, const float out_from_sensor[9], const int32_t *pixels, const float *vals,
+                          int64_t n, double *film, float *rgb_out) {
+    Allocator alloc;
+    PixelSensor *sensor = (PixelSensor *)::operator new(sizeof(PixelSensor));
+    std::memset((void *)sensor, 0, sizeof(PixelSensor));
+    auto curve = [&](int c) {
+        return DenselySampledSpectrum::SampleFunction([&](Float l) { return sensor_rgb[c * 471 + (int(l) - 360)]; });
+    };
+    new (&sensor->r_bar) DenselySampledSpectrum(curve(0));
+    new (&sensor->g_bar) DenselySampledSpectrum(curve(1));
+    new (&sensor->b_bar) DenselySampledSpectrum(curve(2));
+    sensor->imagingRatio = imaging_ratio;
+    RGBFilm *f = (RGBFilm *)::operator new(sizeof(RGBFilm));
+    std::memset((void *)f, 0, sizeof(RGBFilm));
+    f->sensor = sensor;
+    f->fullResolution = Point2i(width, height);
+    f->pixelBounds = Bounds2i(Point2i(0, 0), Point2i(width, height));
+    f->maxComponentValue = max_component;
+    f->filterIntegral = 1;
+    const float *M = out_from_sensor;
+    f->outputRGBFromSensorRGB = SquareMatrix<3>(M[0], M[1], M[2], M[3], M[4], M[5], M[6], M[7], M[8]);
+    new (&f->pixels) Array2D<RGBFilm::Pixel>(f->pixelBounds, alloc);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *v = vals + 12 * i;
+        SampledSpectrum L(0.f);
+        SampledWavelengths lambda;
+        for (int k = 0; k < 4; ++k) { L[k] = v[k]; lambda.lambda[k] = v[4 + k]; lambda.pdf[k] = v[8 + k]; }
+        f->AddSample(Point2i(pixels[2 * i], pixels[2 * i + 1]), L, lambda, nullptr, 1.f);
+    }
+    for (int y = 0; y < height; ++y)
+        for (int x = 0; x < width; ++x) {
+            const RGBFilm::Pixel &p = f->pixels[Point2i(x, y)];
+            double *o = film + 4 * (size_t(y) * width + x);
+            o[0] = p.rgbSum[0]; o[1] = p.rgbSum[1]; o[2] = p.rgbSum[2]; o[3] = p.weightSum;
+            RGB c = f->GetPixelRGB(Point2i(x, y));
+            float *q = rgb_out + 3 * (size_t(y) * width + x);
+            q[0] = c.r; q[1] = c.g; q[2] = c.b;
+        }
+}
+
+// The reference's camera: the REAL PerspectiveCamera constructor (cameras.h:343-370 over ProjectiveCamera and
+// CameraBase; world-space rendering so that render space == world space as include/avr.h assumes) over a film
+// that only has to answer FullResolution() and GetFilter() (an RGBFilm laid out in zeroed storage, see
+// ref_film_add_samples), then, per pixel sample, the prologue of RayIntegrator::EvaluatePixelSample
+// (cpu/integrators.cpp:235-262): StartPixelSample, the wavelength draw, GetCameraSample (samplers.h:797-814),
+// camera.GenerateRayDifferential (cameras.cpp:428-490).
+// world_from_camera: row-major 4x4; screen_window = {xmin, ymin, xmax, ymax}.  rays: {o, d} per sample;
+// matrices: cameraFromRaster then renderFromCamera, row-major 4x4 each.
+void ref_camera_rays(const float world_from_camera[16], float fov, const float screen_window[4], int32_t width,
+                     int32_t height, int32_t sampler_seed, int32_t spp, const int32_t *samples, int64_t n, float *rays,
+                     float *matrices) {
+    static PBRTOptions opts;
+    opts.disableTextureFiltering = true;
+    opts.renderingSpace = RenderingCoordinateSystem::World;
+    Options = &opts;
+    Allocator alloc;
+    Filter filter = new BoxFilter(Vector2f(0.5f, 0.5f));
+    RGBFilm *f = (RGBFilm *)::operator new(sizeof(RGBFilm));
+    std::memset((void *)f, 0, sizeof(RGBFilm));
+    f->fullResolution = Point2i(width, height);
+    f->pixelBounds = Bounds2i(Point2i(0, 0), Point2i(width, height));
+    f->filter = filter;
+    const float *w = world_from_camera;
+    Transform worldFromCamera(SquareMatrix<4>(w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7], w[8], w[9], w[10], w[11], w[12],
+                                              w[13], w[14], w[15]));
+    CameraTransform cameraTransform{AnimatedTransform(worldFromCamera, 0, worldFromCamera, 1)};
+    CameraBaseParameters base;
+    base.cameraTransform = cameraTransform;
+    base.film = Film(f);
+    PerspectiveCamera *cam = new PerspectiveCamera(
+        base, fov, Bounds2f(Point2f(screen_window[0], screen_window[1]), Point2f(screen_window[2], screen_window[3])), 0.f,
+        1e6f);
+    Camera camera(cam);
+    const SquareMatrix<4> &a = cam->cameraFromRaster.GetMatrix();
+    const SquareMatrix<4> &b = cam->cameraTransform.RenderFromCamera().startTransform.GetMatrix();
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) { matrices[4 * i + j] = a[i][j]; matrices[16 + 4 * i + j] = b[i][j]; }
+    for (int64_t i = 0; i < n; ++i) {
+        IndependentSampler is(spp, sampler_seed);
+        Sampler sampler(&is);
+        Point2i pPixel(samples[3 * i], samples[3 * i + 1]);
+        sampler.StartPixelSample(pPixel, samples[3 * i + 2]);
+        Float lu = sampler.Get1D();
+        SampledWavelengths lambda = SampledWavelengths::SampleVisible(lu);
+        CameraSample cs = GetCameraSample(sampler, pPixel, filter);
+        pstd::optional<CameraRayDifferential> cr = camera.GenerateRayDifferential(cs, lambda);
+        float *q = rays + 6 * i;
+        q[0] = cr->ray.o.x; q[1] = cr->ray.o.y; q[2] = cr->ray.o.z;
+        q[3] = cr->ray.d.x; q[4] = cr->ray.d.y; q[5] = cr->ray.d.z;
     }
 }
 

@@ -9,10 +9,11 @@
 // compiled from /root/reference (oracle/refprobe.cpp -> oracle/_ref/libavr_refprobe.so: real
 // GridMedium/RGBGridMedium ctors, SampleT_maj<>, DDAMajorantIterator, SampledGrid, RNG, Hash, FastExp,
 // SampleDiscrete, HG, Transform, Interval) and against the golden fixtures generated from it
-// (tests/golden/, tests/golden/make_golden.py).  The VolPath Li/SampleLd loop cannot be pinned
-// that way (cpu/integrators.cpp needs the whole renderer, which only builds through the
-// reference's cmake): that one function pair is "parity unpinned" beyond its primitives and
-// analytic checks.  Each function cites the reference file:line it follows.
+// (tests/golden/, tests/golden/make_golden.py).  The VolPath Li/SampleLd loop as a whole is
+// pinned by tolerance against the reference's own VolPathIntegrator (see restate_volpath.hpp);
+// camera, film, samplers, graph containers / files / ConnectToGraph bit for bit against the
+// reference's classes (refprobe_volpath.cpp, refprobe_graphint.cpp).  Each function cites the
+// reference file:line it follows.
 #pragma once
 #include <algorithm>
 #include <cmath>

@@ -10,7 +10,8 @@
 // sampler streams): tests/test_oracle_golden.py::test_oracle_volpath_li_* (>= 99.5 % of pixel samples
 // within 1e-3 where every random number comes from the sampler; converged images within the reference's
 // own noise where next-event estimation is on).  Bit-exactness is not available: see the two choices
-// below.  The primitives Li is made of are pinned bit-exact individually.
+// below.  The primitives Li is made of are pinned bit-exact individually, and so are the camera rays
+// (against the real PerspectiveCamera) and the film arithmetic (against the reference's inline film code).
 // Deliberate restatement choices where the reference goes through its BVH / shape code:
 //  * boundary hits are analytic (sphere: quadratic in double; box: slab test) and the ray is
 //    re-spawned at o + d*tHit without pbrt's error-bound offset (interaction.cpp:91-97);
@@ -237,6 +238,16 @@ inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro,
     apply_ray(sc.render_from_camera, {0, 0, 0}, normalize(pCamera), nullptr, ro, rd);
 }
 
+// PixelSensor::ToSensorRGB (film.h:95-100) followed by the clamp of RGBFilm::AddSample (film.h:244-247).
+// Pinned bit for bit against the reference's inline film code (refprobe: ref_film_add_samples).
+inline void sensor_rgb_clamped(const Scene &sc, Spec4 L, const float lambda[4], Spec4 pdf, float rgb[3]) {
+    Spec4 Ld = safe_div(L, pdf);
+    for (int c = 0; c < 3; ++c)
+        rgb[c] = sc.imaging_ratio * average(sample_dense(sc.sensor_rgb.data() + c * NSPEC, lambda) * Ld);
+    float m = std::max({rgb[0], rgb[1], rgb[2]});
+    if (m > sc.max_component) for (int c = 0; c < 3; ++c) rgb[c] *= sc.max_component / m;
+}
+
 // RayIntegrator::EvaluatePixelSample, cpu/integrators.cpp:235-298
 inline PixelSampleOut evaluate_pixel_sample(const Scene &sc, const Medium &med, int px, int py, int sampleIndex,
                                             RenderCounters *rc) {
@@ -263,14 +274,8 @@ inline PixelSampleOut evaluate_pixel_sample(const Scene &sc, const Medium &med, 
     if (has_nans(L)) L = spec(0.f);
     else if (std::isinf(L[0]) || std::isinf(L[1]) || std::isinf(L[2]) || std::isinf(L[3])) L = spec(0.f);
     out.L = L;
-    // PixelSensor::ToSensorRGB film.h:95-100
     Spec4 pdf = {{out.lambda.pdf[0], out.lambda.pdf[1], out.lambda.pdf[2], out.lambda.pdf[3]}};
-    Spec4 Ld = safe_div(L, pdf);
-    for (int c = 0; c < 3; ++c)
-        out.rgb[c] = sc.imaging_ratio * average(sample_dense(sc.sensor_rgb.data() + c * NSPEC, out.lambda.lambda) * Ld);
-    // RGBFilm::AddSample clamp film.h:244-247
-    float m = std::max({out.rgb[0], out.rgb[1], out.rgb[2]});
-    if (m > sc.max_component) for (int c = 0; c < 3; ++c) out.rgb[c] *= sc.max_component / m;
+    sensor_rgb_clamped(sc, L, out.lambda.lambda, pdf, out.rgb);
     return out;
 }
 

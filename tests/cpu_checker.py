@@ -255,6 +255,36 @@ class Checker:
         return out
 
 
+    def film_add_samples(self, rdesc, pixels, vals):
+        """RGBFilm::AddSample over explicit samples (pixels {px, py}; vals {L[4], lambda[4], pdf[4]}), in order.
+        Returns the film sums (H, W, 4) doubles and RGBFilm::GetPixelRGB (H, W, 3)."""
+        pixels = np.ascontiguousarray(pixels, dtype=np.int32); vals = f32(vals); n = pixels.shape[0]
+        W, H = rdesc.c.width, rdesc.c.height
+        film = np.zeros((H, W, 4), dtype=np.float64)
+        if self.kind == "ref":
+            rgb = np.zeros((H, W, 3), dtype=np.float32)
+            M = np.array(list(rdesc.c.output_rgb_from_sensor), dtype=np.float32)
+            self.lib.ref_film_add_samples(C.c_int32(W), C.c_int32(H), _p(rdesc.sensor_rgb, f32p), C.c_float(rdesc.c.imaging_ratio),
+                                          C.c_float(rdesc.c.max_component_value), _p(M, f32p), _p(pixels, i32p),
+                                          _p(vals, f32p), C.c_int64(n), _p(film, f64p), _p(rgb, f32p))
+            return film, rgb
+        self.lib.orc_film_add_samples(C.byref(rdesc.c), _p(pixels, i32p), _p(vals, f32p), C.c_int64(n), _p(film, f64p))
+        rgb = np.zeros((H, W, 3), dtype=np.float32)
+        self.lib.orc_film_resolve(C.byref(rdesc.c), _p(film, f64p), _p(rgb, f32p))
+        return film, rgb
+
+    def camera_rays_reference(self, world_from_camera, fov, screen_window, width, height, seed, spp, samples):
+        """"ref" only: the reference's real PerspectiveCamera (constructor + GenerateRayDifferential) driven like
+        EvaluatePixelSample.  Returns rays (n, 6) and {cameraFromRaster, renderFromCamera} (2, 4, 4)."""
+        assert self.kind == "ref"
+        wfc = f32(np.asarray(world_from_camera).ravel()); sw = f32(screen_window)
+        samples = np.ascontiguousarray(samples, dtype=np.int32); n = samples.shape[0]
+        rays = np.zeros((n, 6), dtype=np.float32); mats = np.zeros((2, 4, 4), dtype=np.float32)
+        self.lib.ref_camera_rays(_p(wfc, f32p), C.c_float(fov), _p(sw, f32p), C.c_int32(width), C.c_int32(height),
+                                 C.c_int32(seed), C.c_int32(spp), _p(samples, i32p), C.c_int64(n), _p(rays, f32p),
+                                 _p(mats, f32p))
+        return rays, mats
+
     def graph_connect_info(self, search_range, n, vertex_radius):
         rng = None if search_range is None else f32(search_range)
         out = np.zeros(3, dtype=np.float32)

@@ -18,7 +18,7 @@ sys.path.insert(0, os.path.dirname(HERE))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 
 from cpu_checker import Checker, have_ref  # noqa: E402
-from golden_cases import CASES, case_volpath_li  # noqa: E402
+from golden_cases import CASES, case_camera_reference, case_volpath_li  # noqa: E402
 
 
 def main():
@@ -32,6 +32,9 @@ def main():
     # the reference's own VolPathIntegrator::Li (compared by tolerance, tests/test_oracle_golden.py)
     for k, v in case_volpath_li(ck).items():
         out[f"volpath_li/{k}"] = np.asarray(v)
+    # the reference's real PerspectiveCamera (matrices + rays); the restatement is run on these matrices
+    for k, v in case_camera_reference(ck).items():
+        out[f"camera/{k}"] = np.asarray(v)
     path = os.path.join(HERE, "reference_vectors.npz")
     np.savez_compressed(path, **out)
     print(f"wrote {path}: {len(out)} arrays, {os.path.getsize(path) / 1e6:.2f} MB")

@@ -333,6 +333,79 @@ def case_graphfile(ck):
     return out
 
 
+# ---- PerspectiveCamera (cameras.h:343-370, cameras.cpp:428-490) + GetCameraSample (samplers.h:797-814) ----
+def camera_configs():
+    """(width, height, fov, eye, sampler seed): landscape and portrait films (fov spans the shorter axis)."""
+    return [(48, 36, 20.0, (0.0, 0.35, -3.2), 0), (31, 57, 37.5, (1.5, -0.7, 2.2), 3)]
+
+
+def camera_samples(cfg, n=400):
+    W, H = cfg[0], cfg[1]
+    rng = np.random.default_rng(2 + W)
+    s = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), rng.integers(0, 4, n)], axis=1).astype(np.int32)
+    s[0] = (0, 0, 0); s[1] = (W - 1, H - 1, 3)
+    return s
+
+
+def case_camera_reference(ref):
+    """Reference side only (fixture keys camera/*): matrices the real PerspectiveCamera constructor builds and
+    the rays its GenerateRayDifferential returns for pixel samples drawn as EvaluatePixelSample draws them."""
+    out = {}
+    for i, (W, H, fov, eye, seed) in enumerate(camera_configs()):
+        aspect = W / H
+        sw = (-aspect, -1, aspect, 1) if aspect > 1 else (-1, -1 / aspect, 1, 1 / aspect)
+        rays, mats = ref.camera_rays_reference(scenes.look_at(eye, (0, 0, 0), (0, 1, 0)), fov, sw, W, H, seed, 4,
+                                               camera_samples((W, H)))
+        out[f"rays{i}"] = rays
+        out[f"matrices{i}"] = mats
+    return out
+
+
+def camera_rays_restated(orc, matrices, i):
+    """The restatement's camera rays for configuration i, fed with the reference's two matrices."""
+    W, H, fov, eye, seed = camera_configs()[i]
+    dens = scenes.fbm_density(8, 8, 8, seed=1)
+    gd, rd = scenes.cloud_scene(dens, width=W, height=H, spp=4, fov=fov, eye=eye, sampler_seed=seed)
+    for k in range(16):
+        rd.c.camera_from_raster[k] = float(matrices[0].ravel()[k])
+        rd.c.render_from_camera[k] = float(matrices[1].ravel()[k])
+    m = orc.medium_uniformgrid(gd)
+    _, rays = m.camera_rays(rd, camera_samples((W, H)))
+    m.close()
+    own = np.stack([np.array(list(scenes.cloud_scene(dens, width=W, height=H, spp=4, fov=fov, eye=eye)[1].c.camera_from_raster),
+                             dtype=np.float32).reshape(4, 4),
+                    np.array(list(scenes.cloud_scene(dens, width=W, height=H, spp=4, fov=fov, eye=eye)[1].c.render_from_camera),
+                             dtype=np.float32).reshape(4, 4)])
+    return rays, own
+
+
+# ---- PixelSensor::ToSensorRGB, RGBFilm::AddSample / GetPixelRGB (film.h:95-100, :239-275) ---------------
+def film_case_inputs():
+    """A 12x9 film, 4000 samples: radiance over 8 decades, zero pdfs (terminated secondary wavelengths), black
+    samples, and a clamp (maxcomponentvalue) that bites on part of them; a non-trivial output matrix."""
+    dens = scenes.fbm_density(8, 8, 8, seed=1)
+    _, rd = scenes.cloud_scene(dens, width=12, height=9, spp=1)
+    rd = rd.with_(max_component_value=2.5)
+    M = np.array([1.2, -0.15, -0.05, -0.1, 1.3, -0.2, 0.02, -0.3, 1.28], dtype=np.float32)
+    for i, v in enumerate(M):
+        rd.c.output_rgb_from_sensor[i] = float(v)
+    rng = np.random.default_rng(21)
+    n = 4000
+    pixels = np.stack([rng.integers(0, 12, n), rng.integers(0, 9, n)], axis=1).astype(np.int32)
+    lam = rng.uniform(360, 830, (n, 4)).astype(np.float32)
+    pdf = (0.0039398042 / np.cosh(0.0072 * (lam.astype(np.float64) - 538)) ** 2).astype(np.float32)
+    L = (10.0 ** rng.uniform(-6, 2, (n, 4))).astype(np.float32) * pdf
+    pdf[rng.random((n, 4)) < 0.1] = 0          # SampledWavelengths::TerminateSecondary
+    L[rng.random(n) < 0.05] = 0
+    return rd, pixels, np.concatenate([L, lam, pdf], axis=1).astype(np.float32)
+
+
+def case_film(ck):
+    rd, pixels, vals = film_case_inputs()
+    film, rgb = ck.film_add_samples(rd, pixels, vals)
+    return {"film": film, "rgb": rgb}  # the product's avr_film_resolve is checked against "rgb" too (tests/test_abi.py)
+
+
 # ---- GraphIntegrator::Initialize + ConnectToGraph (graph/graph_integrator.cpp:24-80, :249-280) ----------
 def case_graphconnect(ck):
     """ck "ref": the reference's own compiled GraphIntegrator methods over a graph file written and read by the
@@ -393,7 +466,7 @@ def case_zsobol(ck):
     return out
 
 
-CASES = {"zsobol": case_zsobol, "graphconnect": case_graphconnect, "scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
+CASES = {"film": case_film, "zsobol": case_zsobol, "graphconnect": case_graphconnect, "scalar": case_scalar, "dda": case_dda, "transform": case_transform, "uniformgrid": case_uniformgrid,
          "rgbgrid": case_rgbgrid, "nanovdb": case_nanovdb, "graph": case_graph, "graphfile": case_graphfile}
 
 

@@ -50,3 +50,22 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(api, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(ImportError):
         api.load_library()
+
+
+def test_film_resolve_matches_the_reference_film():
+    """avr_film_resolve (host code of the product, no GPU) against RGBFilm::GetPixelRGB of the reference
+    (film.h:257-275; fixture case "film", produced by the reference's own inline film code): bit-exact."""
+    import sys
+    import numpy as np
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from golden_cases import film_case_inputs
+    golden = np.load(os.path.join(ROOT, "tests", "golden", "reference_vectors.npz"))
+    rd, _, _ = film_case_inputs()
+    film = np.ascontiguousarray(golden["film/film"], dtype=np.float64)
+    rgb = np.zeros(film.shape[:2] + (3,), dtype=np.float32)
+    lib = api.load_library()
+    st = lib.avr_film_resolve(ctypes.byref(rd.c), film.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                              rgb.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
+    assert st == 0
+    assert rgb.tobytes() == np.ascontiguousarray(golden["film/rgb"]).tobytes()
+    assert np.abs(rgb).max() > 0

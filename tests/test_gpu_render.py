@@ -202,6 +202,28 @@ def test_render_edge_cases(ctx, orc):
     assert not got[:, :4].any() and gs["segments"] == 0 and gs["camera_fetches"] == 0
 
 
+def test_device_film_is_the_reference_film_of_its_samples(ctx, orc):
+    """Film path of k_volpath (PixelSensor::ToSensorRGB + RGBFilm::AddSample, film.h:95-100, :239-255): the film
+    the device accumulates equals the film that the oracle's film arithmetic — pinned bit for bit to the
+    reference's inline film code (fixture case "film") — builds from the device's own per-sample radiance.
+    Only the order of the fp64 additions differs (atomics): 1e-12.  Run without and with a clamp that bites."""
+    dens, (gd, rd) = small_scene(width=24, height=20, spp=6)
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    x0, y0, x1, y1, s0, s1 = rd.ranges()
+    pixels = np.array([(x, y) for y in range(y0, y1) for x in range(x0, x1) for _ in range(s0, s1)], dtype=np.int32)
+    clamp = float("inf")
+    for _ in range(2):
+        r = rd.with_(max_component_value=clamp)
+        film, _ = ctx.render_volpath(md, r)
+        samples, _ = ctx.render_volpath_samples(md, r)
+        want, _ = orc.film_add_samples(r, pixels, samples)
+        assert np.all(film[..., 3] == want[..., 3]) and want[..., :3].max() > 0
+        assert np.allclose(film, want, rtol=1e-12, atol=0)
+        unclamped = want[..., :3].max(axis=2) / want[..., 3]
+        clamp = float(0.25 * unclamped.max())  # second pass: the brightest samples are clamped
+    md.close()
+
+
 def general_media(kind):
     """Small RGB-grid / emissive scenes of the class SURVEY.md 8(d) C5 sweeps (general kernel: 4 channels)."""
     from acceleratedvolrenderer_b200._abi import RGBGridDesc

@@ -121,6 +121,28 @@ def _check_li(got, want):
     assert n_lock >= 2 and n_img >= 2
 
 
+def _check_camera(orc, want):
+    from golden_cases import camera_configs, camera_rays_restated
+    for i in range(len(camera_configs())):
+        rays, own = camera_rays_restated(orc, want[f"matrices{i}"], i)
+        # GetCameraSample + GenerateRayDifferential + RenderFromCamera on the reference's matrices: bit-exact
+        assert same_values(rays, want[f"rays{i}"]), f"camera rays {i}"
+        # scenes.py composes the two matrices in float64, pbrt's constructor in fp32: equal to a few ulp
+        assert np.allclose(own, want[f"matrices{i}"], rtol=2e-6, atol=1e-6), f"camera matrices {i}"
+
+
+def test_oracle_camera_matches_reference_vectors(orc, golden):
+    want = {k.split("/", 1)[1]: golden[k] for k in golden.files if k.startswith("camera/")}
+    assert want, "camera/* missing from the fixture (tests/golden/make_golden.py)"
+    _check_camera(orc, want)
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (no /root/reference on this machine)")
+def test_oracle_camera_matches_reference_live(orc):
+    from golden_cases import case_camera_reference
+    _check_camera(orc, case_camera_reference(Checker("ref")))
+
+
 def test_oracle_volpath_li_matches_reference_vectors(orc, golden):
     from golden_cases import case_volpath_li
     want = {k.split("/", 1)[1]: golden[k] for k in golden.files if k.startswith("volpath_li/")}

@@ -136,7 +136,9 @@ struct Grid {
     int nx = 0, ny = 0, nz = 0;
     float at(int x, int y, int z) const {  // Lookup(Point3i), :830-835
         if (x < 0 || y < 0 || z < 0 || x >= nx || y >= ny || z >= nz) return 0.f;
-        return v[(z * ny + y) * nx + x];
+        // the reference indexes with int (util/containers.h SampledGrid): identical below 2^31 voxels, and UB
+        // above; 64-bit here so that the checker stays defined for the device's larger grids
+        return v[(size_t(z) * ny + y) * nx + x];
     }
     float lookup(V3 p) const {  // :804-819
         float sx = p.x * nx - .5f, sy = p.y * ny - .5f, sz = p.z * nz - .5f;

@@ -266,6 +266,55 @@ def test_transport_matrix_edge_cases(ctx):
     g.close()
 
 
+def test_dense_grid_beyond_2_31_voxels(ctx, orc):
+    """Maximum sizes: a dense grid of 2.16e9 voxels (8.7 GB; linear voxel indices exceed 2^31, SURVEY 8(d) sizes
+    the real Disney cloud at 6.6e9).  Lookups in the last z-slabs, where the linear index is largest, are
+    bit-identical to the oracle's; the octet layouts refuse grids of 2^32 or more cells instead of wrapping."""
+    import psutil
+    if psutil.virtual_memory().available < 30e9:
+        pytest.skip("needs ~9 GB of host memory for the voxel array")
+    nx, ny, nz = 1290, 1290, 1300
+    assert nx * ny * nz > 2 ** 31
+    dens = np.zeros((nz, ny, nx), dtype=np.float32)
+    rng = np.random.default_rng(8)
+    dens[-3:] = rng.random((3, ny, nx), dtype=np.float32)
+    dens[:2] = rng.random((2, ny, nx), dtype=np.float32)
+    gd, _ = scenes.cloud_scene(dens, width=8, height=8, spp=1)
+    assert gd.density.ctypes.data == dens.ctypes.data  # no host copy of the 8.7 GB array
+    md = ctx.create_medium("uniformgrid", gd, layout="dense")
+    n = 20000
+    pg = rng.uniform(0, 1, (n, 3)).astype(np.float32)
+    pg[: n // 2, 2] = rng.uniform((nz - 3.5) / nz, 1.001, n // 2).astype(np.float32)   # last slabs
+    pg[n // 2:, 2] = rng.uniform(-0.001, 2.5 / nz, n - n // 2).astype(np.float32)      # first slabs
+    got = md.lookup_density(pg)
+    want = orc.grid_lookup(dens, pg)
+    assert (want != 0).mean() > 0.5
+    assert bits_equal(got, want)
+    # majorants of the top and bottom cell layers see the data, the middle is empty
+    maj = md.majorants()
+    assert maj[-1].max() > 0.99 and maj[0].max() > 0.99 and maj[maj.shape[0] // 2].max() == 0
+    md.close()
+
+
+def test_octet_layout_refuses_2_32_cells(ctx):
+    """An octet store of 2^32 or more cells would wrap its 32-bit cell index: creation fails loudly
+    (AVR_ERR_UNSUPPORTED) and the same grid is accepted in the dense layout."""
+    import psutil
+    from acceleratedvolrenderer_b200.api import AvrError
+    if psutil.virtual_memory().available < 40e9:
+        pytest.skip("needs a 17 GB (untouched, zero) host array")
+    n = 1626
+    assert n ** 3 > 2 ** 32
+    dens = np.zeros((n, n, n), dtype=np.float32)  # never written: stays the shared zero page on the host
+    gd, _ = scenes.cloud_scene(dens, width=8, height=8, spp=1)
+    with pytest.raises(AvrError) as e:
+        ctx.create_medium("uniformgrid", gd, layout="octet32")
+    assert "2^32" in str(e.value)
+    md = ctx.create_medium("uniformgrid", gd, layout="dense")
+    assert md.lookup_density(np.array([[0.999, 0.999, 0.999]], dtype=np.float32))[0] == 0
+    md.close()
+
+
 def test_error_behaviour(ctx):
     """Argument misuse returns a status + message (the host adapter turns it into ErrorExit)."""
     from acceleratedvolrenderer_b200.api import AvrError

@@ -363,6 +363,9 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
     return l;
 }
 
+#ifndef AVR_WALK_CHECK
+#define AVR_WALK_CHECK 1  // 1: leave the walk phase as soon as no lane walks (every step); 2: test every other step; 0: first step only
+#endif
 #ifndef AVR_CTA_THREADS
 #define AVR_CTA_THREADS 256
 #endif
@@ -680,7 +683,13 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
         //      draw of the next tentative-collision distance inside the current segment.  Leaving a
         //      segment without a collision costs no B op -----------------------------------------------
         for (int k = 0; k < rp.walk_steps; ++k) {
+#if AVR_WALK_CHECK == 1
             if (!__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
+#elif AVR_WALK_CHECK == 2
+            if ((k & 1) == 0 && !__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
+#else
+            if (k == 0 && !__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
+#endif
             if (have && ln.state == ST_WALK) {
                 float a, b;
                 int vox;

@@ -224,6 +224,48 @@ def test_device_film_is_the_reference_film_of_its_samples(ctx, orc):
     md.close()
 
 
+def test_full_size_properties(ctx):
+    """BASELINE.json's headline configuration at its full size (the bench workload: 512x352x624 nanovdb cloud,
+    1280x720, depth 100), where the CPU oracle would take hours: size-independent properties instead.
+    (1) every pixel sample is accounted for (weightSum == spp everywhere, camera_rays == W*H*spp);
+    (2) sample shards add up to the whole render to 1e-12 (the multi-GPU contract); (3) so do rank partitions;
+    (4) FAST and EXACT arithmetic are the same estimator: image means within 1.5 %, density fetches per sample
+    within 1 %; (5) energy: with a black light and no emission the film is exactly zero."""
+    import os
+    import sys
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    w = bench.WORKLOADS["disney-cloud-standin-720p"]
+    W, H, spp = w["width"], w["height"], 4
+    density = bench.make_density(w, torch.device("cuda", 0))
+    nd, rd = bench.make_scene(w, density, spp, 0)
+    md = ctx.create_medium("nanovdb", nd, layout="octet32")
+    full, st = ctx.render_volpath(md, rd)
+    assert np.all(full[..., 3] == spp) and st["camera_rays"] == W * H * spp
+    assert full[..., :3].min() >= 0 and full[..., :3].sum() > 0
+    acc = np.zeros_like(full)
+    ctx.render_volpath(md, rd.with_(sample_begin=0, sample_end=1), film=acc)
+    ctx.render_volpath(md, rd.with_(sample_begin=1, sample_end=4), film=acc)
+    assert np.allclose(acc, full, rtol=1e-12, atol=1e-300)
+    acc = np.zeros_like(full)
+    for r in range(2):
+        ctx.render_volpath(md, rd.with_(rank=r, world=2), film=acc)
+    assert np.allclose(acc, full, rtol=1e-12, atol=1e-300)
+    exact, ste = ctx.render_volpath(md, rd.with_(exact_math=1))
+    m_fast = full[..., :3].sum() / full[..., 3].sum(); m_exact = exact[..., :3].sum() / exact[..., 3].sum()
+    assert abs(m_fast - m_exact) <= 0.015 * m_exact, (m_fast, m_exact)
+    f_fast = st["camera_fetches"] + st["shadow_fetches"]; f_exact = ste["camera_fetches"] + ste["shadow_fetches"]
+    assert abs(f_fast - f_exact) <= 0.01 * f_exact, (f_fast, f_exact)
+    black = rd.with_()
+    dark = np.zeros(len(rd.light_spectrum), dtype=np.float32)
+    black.light_spectrum = dark
+    black.c.light_spectrum = dark.ctypes.data_as(type(black.c.light_spectrum))
+    zero, _ = ctx.render_volpath(md, black)
+    assert not zero[..., :3].any() and np.all(zero[..., 3] == spp)
+    md.close()
+
+
 def general_media(kind):
     """Small RGB-grid / emissive scenes of the class SURVEY.md 8(d) C5 sweeps (general kernel: 4 channels)."""
     from acceleratedvolrenderer_b200._abi import RGBGridDesc

@@ -441,6 +441,23 @@ def test_graph_propagation_bit_exact(ctx, orc):
         big.close(); g.close()
 
 
+def test_graph_propagation_full_size(ctx, orc):
+    """BASELINE config 4 at its full size (10^7 vertices, 6 x 10^7 edges, 8 bounces): the CPU oracle still
+    finishes in seconds here, so the bar stays bit-exact; plus linearity (scaling L0 by a power of two scales
+    the result exactly) as the size-independent property."""
+    n = 10_000_000
+    rowptr, col, val = scenes.random_graph(n, avg_deg=6, seed=5)
+    L0 = np.random.default_rng(5).random(n, dtype=np.float32)
+    g = ctx.create_graph(rowptr, col, val)
+    got, it = g.compute_final_light(L0, 8)
+    want, wit = orc.graph_propagate(rowptr, col, val, L0, 8)
+    assert it == wit == 8
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    got4, _ = g.compute_final_light(L0 * np.float32(4), 8)
+    assert np.array_equal(got4.view(np.uint32), (got * np.float32(4)).view(np.uint32))
+    g.close()
+
+
 def test_graph_connect(ctx, orc):
     rng = np.random.default_rng(3)
     n = 4000

@@ -124,6 +124,36 @@ def test_zsobol_per_sample_radiance_matches_oracle(ctx, orc, randomize):
         assert abs(gstats[k] - wstats[i]) <= 0.02 * max(1, wstats[i]), k
 
 
+@pytest.mark.parametrize("variant", ["chromatic-box", "emissive", "rgbgrid"])
+def test_zsobol_on_the_other_kernel_families(ctx, orc, variant):
+    """The zsobol variants of the 4-channel scalar kernel (chromatic medium, box boundary) and of the general
+    kernel (emissive grid, RGB grid) against the oracle, per pixel sample, exact arithmetic."""
+    if variant == "chromatic-box":
+        dens, (gd, rd) = small_scene(chromatic=True, boundary="box", g=-0.3, width=32, height=24)
+        kind, desc = "uniformgrid", gd
+    elif variant == "emissive":
+        dens, (gd, rd) = small_scene(width=32, height=24)
+        kind = "uniformgrid"
+        desc = GridDesc(dens, gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=0.4, temperature=dens * 2500 + 200,
+                        lescale=dens * 0.5, le_norm=1.0)
+    else:
+        kind, desc, rd = general_media("rgbgrid")
+        rd = rd.with_(spp=4)
+    rd = rd.with_(sampler=1, randomize=2, sampler_seed=11)
+    mo = orc.medium_uniformgrid(desc) if kind == "uniformgrid" else orc.medium_rgbgrid(desc)
+    want, wstats = mo.render_samples(rd)
+    mo.close()
+    md = ctx.create_medium(kind, desc) if kind == "rgbgrid" else ctx.create_medium(kind, desc, layout="dense")
+    got, gstats = ctx.render_volpath_samples(md, rd)
+    md.close()
+    assert np.allclose(got[:, 4:8], want[:, 4:8], rtol=2e-6), "wavelengths"
+    L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+    scale = np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+    ok = np.abs(L - Lw).max(axis=1) <= 1e-3 * scale
+    assert ok.mean() >= 0.99, f"zsobol/{variant}: {ok.mean():.4f} of samples match"
+    assert Lw.sum() > 0 and gstats["camera_rays"] == wstats[0]
+
+
 def test_zsobol_converged_image_fast_math(ctx, orc):
     """FAST math with the zsobol sampler: same estimator, image within the oracle's noise (the oracle images
     use the independent sampler: two different samplers must agree on the expectation)."""

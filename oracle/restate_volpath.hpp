@@ -17,6 +17,7 @@
 //    re-spawned at o + d*tHit without pbrt's error-bound offset (interaction.cpp:91-97);
 //  * "IsInf(L.y(lambda))" (cpu/integrators.cpp:277) is evaluated as "any component of L is inf".
 #pragma once
+#include "restate_graph.hpp"
 #include "restate_sampler.hpp"
 #include "restate_tmaj.hpp"
 
@@ -213,6 +214,46 @@ struct PixelSampleOut {
     float rgb[3];
     float weight;
 };
+
+// GraphIntegrator::Li, free-graph branch (graph/graph_integrator.cpp:180-246) for a camera ray that starts
+// outside the boundary: skip the entry hit, one SampleT_maj through the medium whose first real collision
+// either absorbs the path or connects it to the graph (ConnectToGraph of the WORLD-space point), then
+// spectrum * L.  world_from_render: affine rows (12 floats).
+inline Spec4 graph_li(const Scene &sc, const Medium &med, const GraphVerts &g, const float *wfr, V3 ro, V3 rd,
+                      const float lambda[4], PathSampler &sampler) {
+    float Lg = 0;
+    float t0, t1;
+    if (boundary_hit(sc, ro, rd, &t0, &t1) && t1 > 0) {
+        if (t0 > 0) ro = ro + rd * t0;
+        if (boundary_hit(sc, ro, rd, &t0, &t1) && t1 > 0) {
+            uint64_t hash0 = hash_float(sampler.get1d());
+            uint64_t hash1 = hash_float(sampler.get1d());
+            RNG rng(hash0, hash1);
+            float u0 = sampler.get1d();
+            TmajCounters cnt;
+            sample_tmaj(med, ro, rd, t1, u0, rng, lambda,
+                        [&](V3 p, float, const MediumProps &mp, Spec4 sigma_maj, Spec4) {
+                            float pAbsorb = mp.sigma_a[0] / sigma_maj[0];
+                            float pScatter = mp.sigma_s[0] / sigma_maj[0];
+                            float pNull = std::max<float>(0, 1 - pAbsorb - pScatter);
+                            float um = rng.uniform();
+                            float w[3] = {pAbsorb, pScatter, pNull};
+                            int mode = sample_discrete(w, 3, um);
+                            if (mode == 0) return false;
+                            if (mode == 1) {
+                                V3 pw = {wfr[0] * p.x + wfr[1] * p.y + wfr[2] * p.z + wfr[3],
+                                         wfr[4] * p.x + wfr[5] * p.y + wfr[6] * p.z + wfr[7],
+                                         wfr[8] * p.x + wfr[9] * p.y + wfr[10] * p.z + wfr[11]};
+                                Lg += connect_to_graph(g, pw);
+                                return false;
+                            }
+                            return true;
+                        }, &cnt);
+        }
+    }
+    Spec4 spectrum = sample_dense(sc.light_spec.data(), lambda);
+    return spectrum * Lg;
+}
 
 // the scene's sampler: IndependentSampler(seed) or ZSobolSampler(spp, film resolution, randomize, seed)
 inline PathSampler make_sampler(const Scene &sc) {

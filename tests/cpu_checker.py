@@ -437,6 +437,18 @@ class CheckerMedium:
         orc.lib.orc_camera_rays_list(C.byref(rdesc.c), _p(samples, i32p), C.c_int64(samples.shape[0]), _p(rays, f32p))
         return samples, rays
 
+    def render_graph_samples(self, rdesc: RenderDesc, pos, light, search_range, vertex_radius, world_from_render=None):
+        """GraphIntegrator::Li (free-graph branch) per pixel sample ("orc" only): {L[4], lambda[4], pdf[4]}."""
+        pos = f32(pos); light = f32(light); n = light.size
+        rng = None if search_range is None else f32(search_range)
+        wfr = f32(np.eye(4) if world_from_render is None else world_from_render).ravel()
+        x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+        out = np.zeros(((x1 - x0) * (y1 - y0) * (s1 - s0), 12), dtype=np.float32)
+        self.ck.lib.orc_render_graph_samples(self.h, C.byref(rdesc.c), C.c_int32(n), _p(pos, f32p), _p(light, f32p),
+                                             _p(rng, f32p) if rng is not None else None, C.c_float(vertex_radius),
+                                             _p(wfr, f32p), _p(out, f32p))
+        return out
+
     def volpath_li(self, rdesc: RenderDesc, samples=None, rays=None):
         """Per-sample {L[4], lambda[4], pdf[4]} of the render.  "ref": the reference's own
         VolPathIntegrator::Li (oracle/refprobe_volpath.cpp) over the oracle's camera rays, sphere boundary

@@ -506,6 +506,40 @@ def test_graph_connect(ctx, orc):
     g.close()
 
 
+def test_graph_render_matches_oracle(ctx, orc):
+    """avr_render_graph = GraphIntegrator::Li, free-graph branch (graph/graph_integrator.cpp:180-246): camera ray,
+    one SampleT_maj to the first real collision, ConnectToGraph there, spectrum * L into the film.  Against the
+    restated Li pushed through the film arithmetic that is pinned to the reference (case "film"): the only
+    difference is the summation order of ConnectToGraph's weighted average (hash grid vs sorted kd-tree
+    result), so the bar is 1e-4 relative per pixel; both search-range modes; a non-trivial worldFromRender."""
+    dens, (gd, rd) = small_scene(width=40, height=30, spp=3, sigma_t=10.0)
+    rng = np.random.default_rng(6)
+    n = 6000
+    pos = rng.uniform(-0.55, 0.55, (n, 3)).astype(np.float32)
+    light = rng.random(n, dtype=np.float32)
+    ranges = rng.uniform(0.03, 0.25, n).astype(np.float32)
+    wfr = np.eye(4, dtype=np.float32)
+    wfr[:3, 3] = (0.02, -0.01, 0.03)
+    rowptr, col, val = scenes.random_graph(n, seed=2)
+    g = ctx.create_graph(rowptr, col, val)
+    md = ctx.create_medium("uniformgrid", gd, layout="dense")
+    mo = orc.medium_uniformgrid(gd)
+    x0, y0, x1, y1, s0, s1 = rd.ranges()
+    pixels = np.array([(x, y) for y in range(y0, y1) for x in range(x0, x1) for _ in range(s0, s1)], dtype=np.int32)
+    for rr in (ranges, None):
+        g.set_vertices(pos, light, rr, 0.06)
+        film, _ = ctx.render_graph(md, g, rd, world_from_render=wfr)
+        samples = mo.render_graph_samples(rd, pos, light, rr, 0.06, world_from_render=wfr)
+        want, _ = orc.film_add_samples(rd, pixels, samples)
+        assert np.all(film[..., 3] == want[..., 3])
+        lit = want[..., :3].max(axis=2) > 0
+        assert lit.mean() > 0.2
+        err = np.abs(film[..., :3] - want[..., :3]).max(axis=2)
+        ok = err <= 1e-4 * np.maximum(want[..., :3].max(axis=2), 1e-6)
+        assert ok.mean() >= 0.995, ok.mean()
+    md.close(); mo.close(); g.close()
+
+
 def test_graph_light_rays(ctx, orc):
     dens = scenes.fbm_density(24, 20, 28, seed=3)
     gd = GridDesc(dens, scenes.const_spectrum(0.2), scenes.const_spectrum(9.0), g=0.3)

@@ -223,7 +223,7 @@ avr_status avr_sample_tmaj_device(avr_medium *m, int mode, int exact_math, const
  * VolPathIntegrator::Li volume branch (:962-1106) and SampleLd (:1282-1399) for the scene class the
  * fork's graph pipeline accepts (src/graph/util.h:61-132): ONE grid medium inside ONE convex
  * boundary shape with Material "interface", ONE distant light, perspective camera, box pixel filter,
- * Sampler "independent". */
+ * Sampler "independent" or "zsobol". */
 enum { AVR_BOUNDARY_SPHERE = 0, AVR_BOUNDARY_BOX = 1 };
 enum { AVR_SAMPLER_INDEPENDENT = 0, AVR_SAMPLER_ZSOBOL = 1 };
 /* RandomizeStrategy, util/lowdiscrepancy.h:261 (same order) */
@@ -336,7 +336,8 @@ avr_status avr_graph_set_vertices(avr_graph *g, const float *pos, const float *l
  * perc99 / max fallbacks and 1/dist^2 weighted mean.  points in WORLD space, 3 floats each. */
 avr_status avr_graph_connect(avr_graph *g, const float *points, int64_t n, float *out);
 /* GraphIntegrator::Li free-graph branch (src/graph/graph_integrator.cpp:180-244) rendered over the
- * same scene class as avr_render_volpath; world_from_render: 16 floats row-major. */
+ * same scene class as avr_render_volpath; world_from_render: 16 floats row-major.  Draws from the
+ * independent sampler; desc->sampler = zsobol is AVR_ERR_UNSUPPORTED here. */
 avr_status avr_render_graph(avr_ctx *ctx, avr_medium *m, avr_graph *g, const avr_render_desc *desc,
                             const float *world_from_render, double *film, avr_render_stats *stats);
 

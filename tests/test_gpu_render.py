@@ -537,6 +537,10 @@ def test_graph_render_matches_oracle(ctx, orc):
         err = np.abs(film[..., :3] - want[..., :3]).max(axis=2)
         ok = err <= 1e-4 * np.maximum(want[..., :3].max(axis=2), 1e-6)
         assert ok.mean() >= 0.995, ok.mean()
+    # the graph render draws from the independent sampler only: anything else is refused, not ignored
+    from acceleratedvolrenderer_b200.api import AvrError
+    with pytest.raises(AvrError):
+        ctx.render_graph(md, g, rd.with_(sampler=1), world_from_render=wfr)
     md.close(); mo.close(); g.close()
 
 

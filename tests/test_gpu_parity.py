@@ -315,6 +315,45 @@ def test_octet_layout_refuses_2_32_cells(ctx):
     md.close()
 
 
+def test_device_pointer_entries_equal_host_entries(ctx):
+    """avr_sample_tmaj_device and avr_graph_propagate_device (device pointers, asynchronous: what bench.py and
+    the sharded host logic call) return exactly what their host-buffer twins return."""
+    import torch
+    from acceleratedvolrenderer_b200._abi import TMAJ_DTYPE
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(33)
+    name, gd = next(iter(medium_variants()))
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    n = 20000
+    rays, _ = rays_into(gd, n, rng)
+    seeds = rng.integers(0, 2 ** 63, (n, 2), dtype=np.uint64)
+    u = rng.random(n, dtype=np.float32)
+    t_rays = torch.from_numpy(np.ascontiguousarray(rays, dtype=np.float32)).to(dev)
+    t_seeds = torch.from_numpy(seeds.view(np.int64)).to(dev)
+    t_u = torch.from_numpy(u).to(dev)
+    for mode in (0, 1, 2):
+        want = md.sample_t_maj(mode, rays, seeds, u, LAM)
+        t_out = torch.zeros(n * TMAJ_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+        torch.cuda.synchronize()  # the library launches on its own stream, not torch's
+        md.sample_t_maj_device(mode, True, t_rays.data_ptr(), n, t_seeds.data_ptr(), t_u.data_ptr(), LAM, t_out.data_ptr())
+        torch.cuda.synchronize()
+        got = t_out.cpu().numpy().view(TMAJ_DTYPE)
+        assert got.tobytes() == want.tobytes(), mode
+    md.close()
+    nv = 50000
+    rowptr, col, val = scenes.random_graph(nv, avg_deg=5, seed=9)
+    L0 = rng.random(nv, dtype=np.float32)
+    g = ctx.create_graph(rowptr, col, val)
+    want, wit = g.compute_final_light(L0, 6)
+    t_L0 = torch.from_numpy(L0).to(dev)
+    t_total = torch.zeros(nv, dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+    it = g.propagate_device(t_L0.data_ptr(), 6, t_total.data_ptr(), want_iters=True)
+    torch.cuda.synchronize()
+    assert it == wit and t_total.cpu().numpy().tobytes() == want.tobytes()
+    g.close()
+
+
 def test_error_behaviour(ctx):
     """Argument misuse returns a status + message (the host adapter turns it into ErrorExit)."""
     from acceleratedvolrenderer_b200.api import AvrError

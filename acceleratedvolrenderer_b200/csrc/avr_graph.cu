@@ -24,13 +24,16 @@ namespace avr {
 constexpr int kRowsPerCta = 256;
 constexpr int kChunk = 2048;
 
-// flags[0]: set to 1 when any NaN/Inf was produced; flags[1]: first bad iteration (atomicMin).
+// flags[0]: set to 1 when any NaN/Inf was produced; flags[1]: first bad iteration (atomicMin; starts at INT_MAX).
 __global__ void __launch_bounds__(kRowsPerCta)
 k_spmv(const int64_t *__restrict__ rowptr, const int32_t *__restrict__ col, const float *__restrict__ val,
        const float *__restrict__ x, float *__restrict__ y, float *__restrict__ total, int row_begin, int row_end,
        int *flags, int iteration, int add_prev) {
     __shared__ float s_prod[kChunk];
-    if (flags[0]) return;  // an earlier iteration was invalid: the reference has stopped
+    // An EARLIER iteration was invalid: the reference has stopped.  Gated on the first bad iteration, not on
+    // the raised flag: a CTA of this same launch may raise the flag while others have yet to start, and those
+    // must still do their fused `total += x` for the valid previous iteration.
+    if (flags[1] < iteration) return;
     int r0 = row_begin + blockIdx.x * kRowsPerCta;
     int r1 = min(r0 + kRowsPerCta, row_end);
     int r = r0 + threadIdx.x;

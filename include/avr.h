@@ -318,8 +318,11 @@ avr_status avr_graph_propagate(avr_graph *g, const float *L0, int32_t bounces, f
 avr_status avr_graph_propagate_device(avr_graph *g, const float *L0_dev, int32_t bounces, float *total_dev,
                                       int32_t *iters_done, void *stream);
 /* Row-range shard of one iteration on device pointers, for the multi-GPU path (caller all-gathers
- * `cur_out` rows with NCCL): cur_out[r] = sum_j T[r,j]*cur_in[j], total[r] += cur_out[r] unless
- * *bad_flag is raised; rows [row_begin,row_end).  Asynchronous on `stream`. */
+ * `cur_out` rows with NCCL): cur_out[r] = sum_j T[r,j]*cur_in[j] over rows [row_begin,row_end); nothing is
+ * added to any total here (that is avr_graph_axpy_rows_device).  bad_flag_dev points to TWO device ints
+ * {raised, first bad iteration}, which the caller initialises to {0, INT_MAX}: a NaN/Inf result sets
+ * raised = 1 and lowers the second word to 0 (this entry always runs as iteration 0).  axpy:
+ * total[r] += cur[r] unless bad_flag_dev[0] is raised.  Asynchronous on `stream`. */
 avr_status avr_graph_spmv_rows_device(avr_graph *g, const float *cur_in_dev, float *cur_out_dev,
                                       int32_t row_begin, int32_t row_end, int32_t *bad_flag_dev,
                                       void *stream);

@@ -471,6 +471,29 @@ def test_graph_propagation_bit_exact(ctx, orc):
         big.close(); g.close()
 
 
+def test_graph_propagation_overflow_many_ctas(ctx, orc):
+    """NaN/Inf early-out on a graph of several waves of CTAs (2 * 10^6 rows = 7813 CTAs): the iteration that
+    overflows raises the flag while other CTAs of the same launch have not started; those must still add the
+    last VALID iteration (lighting_calculator.cpp:36-48 adds every valid iteration for all rows).  Only a few
+    rows overflow (a heavy sub-graph at the END of the row range, so its CTAs start last... and FIRST in a
+    second variant), bit-exact total and identical iteration count, repeated to catch a scheduling race."""
+    n = 2_000_000
+    rowptr, col, val = scenes.random_graph(n, avg_deg=4, seed=21)
+    L0 = np.random.default_rng(21).random(n, dtype=np.float32)
+    for where in ("tail", "head"):
+        v = val.copy()
+        rows = slice(n - 300, n) if where == "tail" else slice(0, 300)
+        v[rowptr[rows.start]:rowptr[rows.stop]] *= np.float32(3e9)
+        g = ctx.create_graph(rowptr, col, v)
+        want, wit = orc.graph_propagate(rowptr, col, v, L0, 30)
+        assert 0 < wit < 30
+        for _ in range(5):
+            got, it = g.compute_final_light(L0, 30)
+            assert it == wit
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), where
+        g.close()
+
+
 def test_graph_propagation_full_size(ctx, orc):
     """BASELINE config 4 at its full size (10^7 vertices, 6 x 10^7 edges, 8 bounces): the CPU oracle still
     finishes in seconds here, so the bar stays bit-exact; plus linearity (scaling L0 by a power of two scales

@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
     "avr_graph_create", "avr_graph_create_from_edges", "avr_graph_get_csr", "avr_graph_file_read",
-    "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device",
+    "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
 ]
@@ -446,6 +446,17 @@ class Graph:
         self.ctx.check(self.lib.avr_graph_propagate_device(self.h, C.c_void_p(L0_ptr), C.c_int32(bounces),
                                                            C.c_void_p(total_ptr), C.byref(it) if want_iters else None,
                                                            C.c_void_p(stream or 0)))
+        return int(it.value)
+
+    NOALLOC_MAX_VERTICES = 1 << 20  # AVR_NOALLOC_MAX_VERTICES
+
+    def propagate_noalloc(self, L0_ptr, bounces, total_ptr, stream=None, want_iters=False):
+        """avr_graph_propagate_noalloc: as propagate_device, scratch in the library's static device array
+        (no allocation inside the call; at most NOALLOC_MAX_VERTICES vertices; calls must not overlap)."""
+        it = C.c_int32(-1)
+        self.ctx.check(self.lib.avr_graph_propagate_noalloc(self.h, C.c_void_p(L0_ptr), C.c_int32(bounces),
+                                                            C.c_void_p(total_ptr), C.byref(it) if want_iters else None,
+                                                            C.c_void_p(stream or 0)))
         return int(it.value)
 
     def spmv_rows_device(self, cur_in_ptr, cur_out_ptr, r0, r1, flag_ptr, stream=None):

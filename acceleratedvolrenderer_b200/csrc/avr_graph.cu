@@ -5,7 +5,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <numeric>
+#include <string>
 
 #include "avr_render_host.h"
 
@@ -282,3 +284,85 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
 }  // namespace avr
 
 #include "avr_graph_host.inc"
+
+// ---- avr_graph_propagate_noalloc: ComputeFinalLight with its scratch in a static device array ---------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops).  The ping-pong vectors and the
+// NaN/Inf flags of the propagation live in ONE file-scope array that every GPU loading this library
+// holds until exit: 2 * AVR_NOALLOC_MAX_VERTICES floats + one 256-byte flag line = 8 MiB + 256 B.
+// Every call shares it, so calls that overlap on one GPU race; contents survive from call to call and
+// the init kernel below rewrites what must start clean (flags, cur[0,n)); nxt is written before read.
+namespace {
+
+constexpr size_t kNoallocFloats = 2 * size_t(AVR_NOALLOC_MAX_VERTICES) + 64;
+static __device__ __align__(256) float g_noalloc_scratch[kNoallocFloats];
+
+// cur = total = L0 and flags = {0, INT_MAX}, in one launch instead of two copies and a host upload
+__global__ void k_noalloc_init(const float *__restrict__ L0, float *__restrict__ cur, float *__restrict__ total,
+                               int *flags, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { flags[0] = 0; flags[1] = 0x7fffffff; }
+    if (i < n) { float v = L0[i]; cur[i] = v; total[i] = v; }
+}
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kMaxDevices = 64;
+float *s_noalloc_ptr[kMaxDevices] = {};
+std::mutex s_noalloc_mutex;
+
+avr_status noalloc_scratch(avr_ctx *ctx, float **out) {
+    if (ctx->device < 0 || ctx->device >= kMaxDevices)
+        return set_err(ctx, AVR_ERR_UNSUPPORTED, "avr_graph_propagate_noalloc: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(s_noalloc_mutex);
+    if (!s_noalloc_ptr[ctx->device]) {
+        int cur_dev = -1;
+        AVR_CUDA(ctx, cudaGetDevice(&cur_dev));
+        if (cur_dev != ctx->device)
+            return set_err(ctx, AVR_ERR_CUDA, "avr_graph_propagate_noalloc: the context's device is not current");
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return set_cuda_err(ctx, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+        if (!p) return set_err(ctx, AVR_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch) returned NULL");
+        s_noalloc_ptr[ctx->device] = static_cast<float *>(p);
+    }
+    *out = s_noalloc_ptr[ctx->device];
+    return AVR_OK;
+}
+
+}  // namespace
+
+extern "C" avr_status avr_graph_propagate_noalloc(avr_graph *g, const float *L0_dev, int32_t bounces, float *total_dev,
+                                                  int32_t *iters_done, void *stream_) {
+    if (!g || !L0_dev || !total_dev)
+        return set_err(g ? g->ctx : nullptr, AVR_ERR_BAD_ARG, "avr_graph_propagate_noalloc: NULL argument");
+    avr_ctx *ctx = g->ctx;
+    if (bounces < 0) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_graph_propagate_noalloc: bounces must be >= 0");
+    if (g->n > AVR_NOALLOC_MAX_VERTICES)
+        return set_err(ctx, AVR_ERR_UNSUPPORTED,
+                       "avr_graph_propagate_noalloc: " + std::to_string(g->n) + " vertices exceed the static scratch of " +
+                           std::to_string(AVR_NOALLOC_MAX_VERTICES) + " (AVR_NOALLOC_MAX_VERTICES); use avr_graph_propagate_device");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    float *scratch = nullptr;
+    avr_status st = noalloc_scratch(ctx, &scratch);
+    if (st != AVR_OK) return st;
+    float *cur = scratch, *nxt = scratch + AVR_NOALLOC_MAX_VERTICES;
+    int *flags = reinterpret_cast<int *>(scratch + 2 * size_t(AVR_NOALLOC_MAX_VERTICES));
+    cudaStream_t s = stream_ ? (cudaStream_t)stream_ : ctx->stream;
+    k_noalloc_init<<<blocks_for(g->n, 256), 256, 0, s>>>(L0_dev, cur, total_dev, flags, g->n);
+    int nblk = blocks_for(g->n, kRowsPerCta);
+    for (int it = 0; it < bounces; ++it) {
+        k_spmv<<<nblk, kRowsPerCta, 0, s>>>(g->d_rowptr, g->d_col, g->d_val, cur, nxt, total_dev, 0, g->n, flags, it,
+                                             it > 0 ? 1 : 0);
+        std::swap(cur, nxt);
+    }
+    if (bounces > 0) k_axpy<<<blocks_for(g->n, 256), 256, 0, s>>>(cur, total_dev, 0, g->n, flags);
+    AVR_CUDA(ctx, cudaGetLastError());
+    if (iters_done) {
+        int32_t fl[2];
+        AVR_CUDA(ctx, cudaMemcpyAsync(fl, flags, sizeof(fl), cudaMemcpyDeviceToHost, s));
+        AVR_CUDA(ctx, cudaStreamSynchronize(s));
+        *iters_done = fl[0] ? fl[1] : bounces;
+    }
+    return AVR_OK;
+}

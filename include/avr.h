@@ -317,6 +317,19 @@ avr_status avr_graph_propagate(avr_graph *g, const float *L0, int32_t bounces, f
  * on `stream`, NULL = the context's stream). */
 avr_status avr_graph_propagate_device(avr_graph *g, const float *L0_dev, int32_t bounces, float *total_dev,
                                       int32_t *iters_done, void *stream);
+/* ComputeFinalLight as avr_graph_propagate_device, for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  NO counterpart in the reference.
+ * The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine): the ping-pong vectors and the NaN/Inf flags live in one file-scope
+ * `static __device__` array of 2 * AVR_NOALLOC_MAX_VERTICES floats + 256 bytes (8 MiB + 256 B), which
+ * every GPU that loads the library holds until exit.  Graphs with more vertices are refused with
+ * AVR_ERR_UNSUPPORTED and a message naming the limit.  All calls on one GPU share that array and it keeps
+ * the last call's contents (the call rewrites what must start clean): calls that overlap on the GPU —
+ * two streams, two contexts, two host threads — RACE; serialise them.  L0_dev / total_dev: n floats on
+ * the device, caller-owned; iters_done: host int or NULL (NULL = fully asynchronous on `stream`). */
+#define AVR_NOALLOC_MAX_VERTICES 1048576
+avr_status avr_graph_propagate_noalloc(avr_graph *g, const float *L0_dev, int32_t bounces, float *total_dev,
+                                       int32_t *iters_done, void *stream);
 /* Row-range shard of one iteration on device pointers, for the multi-GPU path (caller all-gathers
  * `cur_out` rows with NCCL): cur_out[r] = sum_j T[r,j]*cur_in[j] over rows [row_begin,row_end); nothing is
  * added to any total here (that is avr_graph_axpy_rows_device).  bad_flag_dev points to TWO device ints

@@ -209,6 +209,45 @@ __global__ void k_pack_octets(MediumView mv, float4 *out32, uint4 *out16) {
     }
 }
 
+// ---- empty-space distance field of the majorant grid (FAST render kernels, MediumView::maj_fast) --------
+// Chebyshev distance in cells from every EMPTY majorant cell to the nearest non-empty one, by three 1-D
+// passes: d1 = distance along x; d2 = min over y' of max(|y - y'|, d1(y')); d3 the same along z.
+// Distances are capped at kLeapCap; a thread scans outwards and stops once the offset reaches its best.
+constexpr int kLeapCap = 255;
+__global__ void k_empty_dist_x(const float *maj, int rx, int ry, int rz, unsigned char *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rx * ry * rz) return;
+    int x = i % rx;
+    const float *row = maj + (i - x);
+    int best = kLeapCap;
+    for (int o = 0; o < best; ++o) {
+        bool hit = (x - o >= 0 && row[x - o] != 0.f) || (x + o < rx && row[x + o] != 0.f);
+        if (hit) { best = o; break; }
+    }
+    out[i] = (unsigned char)best;
+}
+// axis 1: stride rx, extent ry; axis 2: stride rx*ry, extent rz
+__global__ void k_empty_dist_next(const unsigned char *in, int n_total, int stride, int extent, unsigned char *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_total) return;
+    int c = (i / stride) % extent;
+    int best = in[i];
+    for (int o = 1; o < best; ++o) {
+        int a = c - o >= 0 ? in[i - o * stride] : kLeapCap, b = c + o < extent ? in[i + o * stride] : kLeapCap;
+        int m = min(a, b);
+        best = min(best, max(o, m));
+    }
+    out[i] = (unsigned char)best;
+}
+__global__ void k_maj_fast(const float *maj, const unsigned char *dist, int n, float *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float m = maj[i];
+    // a non-empty cell keeps its majorant; an empty one holds -distance (>= 1); a negative majorant (invalid
+    // input) must not read as a distance: it becomes 0 = "empty, no leap"
+    out[i] = m != 0.f ? (m > 0.f || m != m ? m : 0.f) : -float(max((int)dist[i], 1));
+}
+
 // ---- medium creation ---------------------------------------------------------------------------------
 namespace {
 
@@ -304,6 +343,27 @@ avr_status finish_majorants(avr_medium *m) {
         v.nz_lo[i] = lo[i];
         v.nz_hi[i] = hi[i];
     }
+    // FAST kernels: majorants with the empty-space distance field folded in
+    float *mf = nullptr;
+    unsigned char *d0 = nullptr, *d1 = nullptr;
+    AVR_CUDA(m->ctx, cudaMalloc(&mf, nm * sizeof(float)));
+    m->allocs.push_back(mf);
+    m->bytes += int64_t(nm * sizeof(float));
+    AVR_CUDA(m->ctx, cudaMalloc(&d0, nm));
+    cudaError_t e = cudaMalloc(&d1, nm);
+    if (e != cudaSuccess) { cudaFree(d0); return set_cuda_err(m->ctx, e, "cudaMalloc(distance field)"); }
+    int nb = int((nm + 255) / 256), rx = v.mres[0], ry = v.mres[1], rz = v.mres[2];
+    cudaStream_t s = m->ctx->stream;
+    k_empty_dist_x<<<nb, 256, 0, s>>>(m->d_maj, rx, ry, rz, d0);
+    k_empty_dist_next<<<nb, 256, 0, s>>>(d0, int(nm), rx, ry, d1);
+    k_empty_dist_next<<<nb, 256, 0, s>>>(d1, int(nm), rx * ry, rz, d0);
+    k_maj_fast<<<nb, 256, 0, s>>>(m->d_maj, d0, int(nm), mf);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d0);
+    cudaFree(d1);
+    if (e != cudaSuccess) return set_cuda_err(m->ctx, e, "empty-space distance field");
+    v.maj_fast = mf;
     return AVR_OK;
 }
 
@@ -391,6 +451,8 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     }
     v.emissive = v.has_temperature ? 1 : (leMax > 0 ? 1 : 0);  // media.cpp:238
     v.achromatic = achro ? 1 : 0;
+    v.ach_sig_a = sa[0];
+    v.ach_sig_s = ss[0];
     TRY(upload(m, sa.data(), (size_t)kNSpec, &v.sigma_a_spec));
     TRY(upload(m, ss.data(), (size_t)kNSpec, &v.sigma_s_spec));
     TRY(upload(m, le.data(), (size_t)kNSpec, &v.le_spec));
@@ -458,6 +520,8 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
         if (sa[i] != sa[0] || ss[i] != ss[0]) achro = false;
     }
     v.achromatic = achro ? 1 : 0;
+    v.ach_sig_a = sa[0];
+    v.ach_sig_s = ss[0];
     // IsEmissive, media.h:621.  A temperature grid with Lescale <= 0 still goes through Le() in the
     // reference; the general kernels are used whenever the grid is present.
     v.emissive = v.has_temperature ? 1 : 0;

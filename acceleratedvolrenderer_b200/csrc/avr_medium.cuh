@@ -34,6 +34,11 @@ struct MediumView {
     float m[12], minv[12];    // renderFromMedium / mediumFromRender, rows 0..2 (affine; row 3 = 0 0 0 1)
     const float *maj;         // majorant grid, x fastest
     int mres[3];
+    // FAST render kernels: the same grid with every EMPTY cell (majorant 0) holding -d, d >= 1 the Chebyshev
+    // distance in cells to the nearest non-empty cell (cells closer than d are all empty: the walk leaps to
+    // the face of that cube, DDA::leap); non-empty cells hold their majorant
+    const float *maj_fast;
+    float ach_sig_a, ach_sig_s;  // achromatic media: the constant sigma_a / sigma_s (already * "scale")
     // FAST path: sample coordinates straight from render space, s = gfr * p + gfr[.][3]  (s = p_grid*n - .5)
     float gfr[12];
     float cell[3], inv_cell[3];  // majorant cell size in medium space and its reciprocal
@@ -458,10 +463,45 @@ struct DDA {
             float edge = mv.bmin[a] + float(pos[a] ? v + 1 : v) * mv.cell[a];
             nct[a] = (edge - comp(o, a)) * id;
             if (comp(d, a) == 0) nct[a] = __int_as_float(0x7f800000);
-            float dT = fabsf(id) * mv.cell[a];
+            float dT = fminf(fabsf(id) * mv.cell[a], 1e30f);  // finite: leap() multiplies it by a cell count
             dTs[a] = pos[a] ? dT : -dT;
         }
         if (!set_voxels<TRIM>(mv, vx, pos)) invalidate();
+    }
+    // FAST variant only.  The current voxel and every voxel at Chebyshev distance < d (d >= 2) are empty
+    // (sigma_maj = 0: nothing can happen there): advance straight to the first crossing that leaves that
+    // cube, or to the end of the walk.  Per axis, k = the cells that may still be entered inside the cube
+    // (and inside the trimmed box); the exit axis takes k + 1 crossings, the others the crossings before
+    // the exit time.  No segment is emitted.
+    AVR_DEV void leap(const MediumView &mv, int d) {
+        int r[3] = {int(rem & 1023u), int((rem >> 10) & 1023u), int(rem >> 20)};
+        float a[3], tb[3];
+        int k[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            k[i] = min(d, r[i]) - 1;
+            a[i] = fabsf(dTs[i]);
+            tb[i] = __fmaf_rn(float(k[i]), a[i], nct[i]);
+        }
+        float T = fminf(fminf(tb[0], tb[1]), tb[2]);
+        if (!(T < tMax)) { tMin = tMax; return; }  // the ray ends inside the cube
+        bool e0 = tb[0] <= tb[1] && tb[0] <= tb[2], e1 = !e0 && tb[1] <= tb[2];
+        bool ex[3] = {e0, e1, !e0 && !e1};
+        int stride[3] = {1, mv.mres[0], mv.mres[0] * mv.mres[1]};
+        bool out = false;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            int n = k[i] + 1;
+            if (!ex[i]) {
+                int c = nct[i] < T ? (int)((T - nct[i]) * ftz_rcp(a[i])) + 1 : 0;
+                n = min(c, k[i]);
+            }
+            nct[i] = __fmaf_rn(float(n), a[i], nct[i]);
+            lin += (dTs[i] >= 0 ? n : -n) * stride[i];
+            rem -= unsigned(n) << (10 * i);
+            out = out || (ex[i] && n == r[i]);
+        }
+        tMin = out ? tMax : T;  // left the (trimmed) grid: every voxel beyond is empty
     }
     // Returns false when the iterator is exhausted.  *vox = linear voxel index of the segment.
     AVR_DEV bool next(const MediumView &mv, float *segMin, float *segMax, int *vox) {

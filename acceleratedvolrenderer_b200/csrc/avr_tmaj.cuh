@@ -26,6 +26,10 @@ struct Traits {
     static constexpr int NCH = NCH_;
     static constexpr int LAYOUT = LAYOUT_;
     static constexpr bool GENERAL = GENERAL_;
+    // FAST kernels of achromatic scalar media: with one channel every spectral-MIS weight of the path is an
+    // exact ratio x / x = 1 (beta, r_u, r_l of the camera path, r_l of a shadow ray), so they are not carried
+    // at all: analog delta tracking for the camera segments, plain ratio tracking for the shadow rays
+    static constexpr bool LEAN = !EXACT_ && NCH_ == 1 && !GENERAL_;
 };
 
 template <int NCH>

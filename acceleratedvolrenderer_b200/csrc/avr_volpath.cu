@@ -22,6 +22,10 @@
 
 #include "avr_render_host.h"
 
+#ifndef AVR_VOLPATH_PART
+#define AVR_VOLPATH_PART 0
+#endif
+
 using namespace avr;
 
 namespace avr {
@@ -134,6 +138,12 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     ln.r_l = sconst<TR::NCH>(1.f);
     ln.depth = 0;
     ln.shadow = false;
+    if (!TR::EXACT && !TR::ZSOBOL) {
+        // FAST: one tracking stream per path (raw draws as PCG32 sequence / seed give correlated streams:
+        // they go through the hash)
+        uint64_t h0 = hash_u32(ln.srng.u32()), h1 = hash_u32(ln.srng.u32());
+        ln.trng.set_sequence(h0, h1);
+    }
     // entry into the boundary (Intersect + SkipIntersection of the "interface" surface)
     float t0, t1;
     if (!(boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0)) {
@@ -242,8 +252,12 @@ template <typename TR>
 struct SlotIO {
     static constexpr int N = TR::NCH;
     static constexpr int kQuadsA = 6;
-    static constexpr int kQuadsB = (4 + 10 * N + 3) / 4;
-    static constexpr int kQuadsC = 5;
+    // FAST kernels with the independent sampler seed the tracking RNG once per path (start_path) instead of
+    // once per ray: it then belongs to the state every op touches (group B), not to the per-ray group C
+    static constexpr bool kTrngInB = !TR::EXACT && !TR::ZSOBOL;
+    static constexpr int kWordsB = (TR::LEAN ? 7 : 4 + 10 * N) + (kTrngInB ? 4 : 0);
+    static constexpr int kQuadsB = (kWordsB + 3) / 4;
+    static constexpr int kQuadsC = kTrngInB ? 4 : 5;
     static constexpr int kSlotQuads = (kQuadsA + kQuadsB + kQuadsC) | 1;  // odd: consecutive slots start in different bank groups
     // groups the tracking loop needs besides B and C, and what it must write back when parking
     static constexpr int kTrackLoad = GRP_B | GRP_C | ((TR::EXACT || TR::GENERAL) ? GRP_A : 0);
@@ -300,6 +314,12 @@ struct SlotIO {
         f(fl);
         ln.state = int(fl & 0xffu); ln.shadow = (fl >> 8) & 1u; pending = (fl >> 9) & 1u; ln.depth = int(fl >> 16);
         f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
+        if (kTrngInB) visit_rng(ln.trng, f);
+        if (TR::LEAN) {
+            // the medium's sigma_a / sigma_s are constants of the MediumView, the path weights are not carried
+            f(ln.T_ray.v[0]); f(ln.s_ru.v[0]); f(ln.sigma_maj.v[0]);
+            return;
+        }
 #pragma unroll
         for (int i = 0; i < N; ++i) {
             f(ln.beta.v[i]); f(ln.r_u.v[i]); f(ln.r_l.v[i]);
@@ -314,13 +334,18 @@ struct SlotIO {
         f(ln.dda.tMin); f(ln.dda.tMax);
 #pragma unroll
         for (int i = 0; i < 3; ++i) { f(ln.dda.nct[i]); f(ln.dda.dTs[i]); }
-        unsigned dl = (unsigned)ln.dda.lin, lo, hi, lo2, hi2;
+        unsigned dl = (unsigned)ln.dda.lin;
         f(dl); f(ln.dda.rem);
         ln.dda.lin = (int)dl;
-        split64(ln.trng.state, lo, hi);
-        split64(ln.trng.inc, lo2, hi2);
+        if (!kTrngInB) visit_rng(ln.trng, f);
+    }
+    template <typename F>
+    AVR_DEV static void visit_rng(RNG &r, F &f) {
+        unsigned lo, hi, lo2, hi2;
+        split64(r.state, lo, hi);
+        split64(r.inc, lo2, hi2);
         f(lo); f(hi); f(lo2); f(hi2);
-        ln.trng.state = join64(lo, hi); ln.trng.inc = join64(lo2, hi2);
+        r.state = join64(lo, hi); r.inc = join64(lo2, hi2);
     }
 
     template <int GROUPS>
@@ -339,6 +364,10 @@ struct SlotIO {
             // derived: sigma_t and the wavelengths of the batch (make_lambda_ctx, avr_tmaj.cuh)
 #pragma unroll
             for (int i = 0; i < 4; ++i) lc.lambda[i] = ln.lambda[i];
+            if (TR::LEAN) {
+                lc.sig_a = sconst<N>(mv.ach_sig_a);
+                lc.sig_s = sconst<N>(mv.ach_sig_s);
+            }
             if (mv.kind == KIND_RGB) lc.sigma_t = sconst<N>(1.f);
             else lc.sigma_t = lc.sig_a + lc.sig_s;
         }
@@ -367,7 +396,7 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 #define AVR_WALK_CHECK 1  // 1: leave the walk phase as soon as no lane walks (every step); 2: test every other step; 0: first step only
 #endif
 #ifndef AVR_CTA_THREADS
-#define AVR_CTA_THREADS 256
+#define AVR_CTA_THREADS 512  // one 512-thread CTA per SM with one pool: 1.6 % faster than two of 256 (fuller batches)
 #endif
 template <typename TR>
 struct KernelCfg {
@@ -482,7 +511,14 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
     } else {
         // ---- E2. end of the shadow ray: SampleLd epilogue (cpu/integrators.cpp:1382-1398), then phase
         //      sampling and the next camera segment (cpu/integrators.cpp:1041-1060) -------------------
-        if (have) {
+        if (have && TR::LEAN) {
+            // one channel: T_maj / T_maj[0] = 1, r_l = r_u = beta = 1 (see Traits::LEAN)
+            if (ln.T_ray[0] != 0) {
+                float w = ln.f_hat * ln.T_ray[0];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) ln.L[i] += w * sample_dense1(rp.light_spec, ln.lambda[i]);
+            }
+        } else if (have) {
             Spec<N> T_ray = ln.T_ray * (ln.T_maj / ln.T_maj[0]);
             if (nonzero(T_ray)) {
                 Spec<N> r_l = ln.s_rl * (ln.T_maj / ln.T_maj[0]);
@@ -496,6 +532,8 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                     ln.L[i] += (bf[i % N] * Ll) / avg;
                 }
             }
+        }
+        if (have) {
             float ua, ub;
             PathSamplerRef<TR::ZSOBOL>{rp.smp, ln.srng, ln.px, ln.py, ln.samp}.get2d(&ua, &ub);
             float pdf;
@@ -503,8 +541,10 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             if (pdf == 0) {
                 ln.state = ST_EV_PATH_END;
             } else {
-                ln.beta = ln.beta * (pdf / pdf);
-                ln.r_l = ln.r_u / pdf;
+                if (!TR::LEAN) {
+                    ln.beta = ln.beta * (pdf / pdf);
+                    ln.r_l = ln.r_u / pdf;
+                }
                 ln.fe.d = wi;  // fe.o still holds the scatter point
                 ln.shadow = false;
                 ln.state = ST_SETUP;
@@ -555,11 +595,9 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                     hash1 = hash_float(smp.get1d());
                     smp.get1d();
                 }
-            } else {
-                hash0 = hash_u32(ln.srng.u32());
-                hash1 = hash_u32(ln.srng.u32());
+                ln.trng.set_sequence(hash0, hash1);
             }
-            ln.trng.set_sequence(hash0, hash1);
+            // (independent sampler: the path's tracking stream, seeded in start_path, simply continues)
             ln.u = neg_log1m(ln.trng.uniform());  // remaining optical depth to the first tentative collision
             if (ln.shadow) {
                 tMax = 1 - kShadowEps;
@@ -616,7 +654,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
 // Applied after a slot load and undone before a slot store.
 template <typename TR>
 AVR_DEV void swap_shadow_weights(PathLane<TR> &ln) {
-    if (!ln.shadow) return;
+    if (TR::LEAN || !ln.shadow) return;
     Spec<TR::NCH> t;
     t = ln.beta; ln.beta = ln.T_ray; ln.T_ray = t;
     t = ln.r_u; ln.r_u = ln.s_ru; ln.s_ru = t;
@@ -690,7 +728,17 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
 #else
             if (k == 0 && !__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
 #endif
-            if (have && ln.state == ST_WALK) {
+            if (!EX && have && ln.state == ST_WALK && ln.mj < -1.5f) {
+                // FAST: the walk stands inside an empty cube of the majorant grid (MediumView::maj_fast):
+                // one leap to the face of the cube instead of a step per cell
+                ln.dda.leap(mv, (int)(-ln.mj));
+                cn.seg++;
+#ifdef AVR_SEGSTAT
+                cn.sc++;  // leaps
+#endif
+                if (ln.dda.tMin < ln.dda.tMax) ln.mj = maj[ln.dda.lin];
+                else ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
+            } else if (have && ln.state == ST_WALK) {
                 float a, b;
                 int vox;
                 if (!ln.dda.next(mv, &a, &b, &vox)) {
@@ -710,7 +758,11 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     // collision instead of one per segment.  With one channel T_maj / T_maj[0] == 1
                     // everywhere it is used, so T_maj is not tracked at all.
                     cn.seg++;
-                    if (mj != 0) {
+#ifdef AVR_SEGSTAT
+                    if (!(mj > 0)) cn.rays++;  // empty cell next to a non-empty one (d = 1)
+                    else if (lc.sigma_t[0] * mj * (b - a) < 0.25f) cn.cam++;  // thin segment
+#endif
+                    if (mj > 0) {
                         Spec<N> sm = lc.sigma_t * mj;
                         float dtau = sm[0] * (b - a);
                         bool hit = ln.u <= dtau && sm[0] != 0;
@@ -783,7 +835,38 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
             if (mc == 0) continue;
             if (__popc(mc) < rp.collide_min && __any_sync(0xffffffffu, have && ln.state == ST_WALK)) continue;
         }
-        if (have && ln.state == ST_COLLIDE) {
+        if (TR::LEAN && have && ln.state == ST_COLLIDE) {
+            // one channel, fast arithmetic: the event probabilities are all that is left of
+            // cpu/integrators.cpp:990-1074 (camera) and :1352-1380 (shadow) — see Traits::LEAN
+            const float t = ln.cur_tMin;
+            const float dens = ln.fe.density(mv, t);
+            const float smj = ln.sigma_maj[0], inv = ftz_rcp(smj);
+            const float sa = mv.ach_sig_a * dens, ss = mv.ach_sig_s * dens;
+            if (!ln.shadow) {
+                cn.cam++;
+                const float pA = sa * inv, pS = ss * inv;
+                const float sum = pA + pS + fmaxf(0.f, 1 - pA - pS);
+                const float up = ln.trng.uniform() * sum;
+                if (up < pA) {
+                    ln.state = ST_EV_PATH_END;  // absorbed
+                } else if (up < pA + pS) {
+                    ln.state = ln.depth++ >= rp.max_depth ? ST_EV_PATH_END : ST_EV_SCATTER;  // cur_tMin = t already
+                } else
+                    ln.state = ST_SAMPLE;  // null collision: tMin = t already
+            } else {
+                cn.sh++;
+                // ratio tracking: T_ray and r_u take sigma_n / sigma_maj, r_l stays 1; Russian roulette on
+                // Tr = T_ray / Average(r_l + r_u)
+                const float ratio = fmaxf(0.f, smj - sa - ss) * inv;
+                float T = ln.T_ray[0] * ratio;
+                const float ru = ln.s_ru[0] * ratio;
+                if (T * ftz_rcp(1 + ru) < 0.05f) T = ln.trng.uniform() < 0.75f ? 0.f : T * 4.f;
+                ln.T_ray.v[0] = T;
+                ln.s_ru.v[0] = ru;
+                ln.state = T != 0 ? ST_SAMPLE : ST_EV_SHADOW_END;
+            }
+        }
+        if (!TR::LEAN && have && ln.state == ST_COLLIDE) {
             {
                 const float t = ln.cur_tMin;
                 Spec<N> T_maj = ln.T_maj;
@@ -883,7 +966,7 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     using IO = SlotIO<TR>;
     extern __shared__ uint4 smem_q[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(smem_q);
-    const float *maj = mv.maj;
+    const float *maj = TR::EXACT ? mv.maj : mv.maj_fast;
     const unsigned maj_bytes = rp.maj_in_smem ? unsigned(mv.mres[0] * mv.mres[1] * mv.mres[2]) * 4u : 0u;
     const PoolLayout lay = pool_layout(maj_bytes, (unsigned)rp.pool, IO::kSlotQuads);
     PoolView pv;
@@ -896,7 +979,7 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     {
         if (rp.maj_in_smem) {
             float *s_maj = reinterpret_cast<float *>(smem);
-            for (unsigned i = threadIdx.x; i < maj_bytes / 4; i += blockDim.x) s_maj[i] = mv.maj[i];
+            for (unsigned i = threadIdx.x; i < maj_bytes / 4; i += blockDim.x) s_maj[i] = maj[i];
             maj = s_maj;
         }
         // all slots start dead (state word 0 = ST_DEAD, nothing pending) and queued in Q_DEAD

@@ -7,10 +7,10 @@ cd "$(dirname "$0")/.."
 args=$1; shift
 lib=acceleratedvolrenderer_b200/libavr_b200.so
 cp $lib /tmp/libavr_base.so
-echo "== base"; python tools/tune_volpath.py $args | cut -c1-160
+echo "== base"; python tools/tune_volpath.py $args 
 for v in "$@"; do
   cp acceleratedvolrenderer_b200/variants/libavr_$v.so $lib
-  echo "== $v"; python tools/tune_volpath.py $args | cut -c1-160
+  echo "== $v"; python tools/tune_volpath.py $args 
 done
 cp /tmp/libavr_base.so $lib
-echo "== base again"; python tools/tune_volpath.py $args | cut -c1-160
+echo "== base again"; python tools/tune_volpath.py $args 

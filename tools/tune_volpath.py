@@ -56,7 +56,8 @@ def main():
             print(json.dumps({"layout": layout, "exact": int(exact), "sampler": args.sampler, "env": dict(zip(names, vals)),
                               "kernel_ms": round(best["kernel_ms"], 2),
                               "Msamples_s": round(W * H * args.spp / best["kernel_ms"] / 1e3, 2),
-                              "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1)}),
+                              "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1),
+                              "stats": {k: v for k, v in best.items() if k != "kernel_ms"}}),
                   flush=True)
         med.close()
     ctx.close()

@@ -40,6 +40,8 @@ ABI_SYMBOLS = [
     "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
+    "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world",
+    "avr_render_volpath_multi", "avr_graph_propagate_multi",
 ]
 
 
@@ -65,7 +67,7 @@ def load_library():
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
-                        "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free"):
+                        "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free", "avr_comm_destroy"):
             fn.restype = C.c_int
     lib.avr_ctx_destroy.restype = None
     lib.avr_medium_destroy.restype = None
@@ -74,6 +76,8 @@ def load_library():
     lib.avr_graph_file_free.argtypes = [C.c_void_p]
     lib.avr_graph_sidecar_free.restype = None
     lib.avr_graph_sidecar_free.argtypes = [C.c_void_p]
+    lib.avr_comm_destroy.restype = None
+    lib.avr_comm_destroy.argtypes = [C.c_void_p]
     _lib = lib
     return lib
 
@@ -196,6 +200,56 @@ class Context:
         g = Graph(self, h, vs.size, 0)
         g.nnz = g.csr_sizes()[1]
         return g
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id():
+    """avr_comm_unique_id: 128 bytes that rank 0 creates and hands to every other rank."""
+    lib = load_library()
+    buf = (C.c_uint8 * COMM_ID_BYTES)()
+    st = lib.avr_comm_unique_id(buf)
+    if st != 0:
+        raise AvrError(st, lib.avr_last_error(None).decode())
+    return bytes(buf)
+
+
+class Comm:
+    """avr_comm: this rank's end of the NCCL communicator behind the C ABI (one rank per GPU)."""
+
+    def __init__(self, ctx, unique_id: bytes, rank: int, world: int):
+        self.ctx, self.lib, self.rank, self.world = ctx, ctx.lib, rank, world
+        buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(unique_id)
+        h = C.c_void_p()
+        ctx.check(self.lib.avr_comm_init_rank(ctx.h, buf, C.c_int32(rank), C.c_int32(world), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.avr_comm_destroy(self.h)
+            self.h = None
+
+    # Integrator::Render over all ranks: the complete film lands (is ADDED) in rank 0's host array
+    def render_volpath(self, medium, rdesc: RenderDesc, film=None):
+        if film is None and self.rank == 0:
+            film = np.zeros((rdesc.c.height, rdesc.c.width, 4), dtype=np.float64)
+        stats = avr_render_stats()
+        self.ctx.check(self.lib.avr_render_volpath_multi(self.h, medium.h, C.byref(rdesc.c),
+                                                         _p(film, f64p) if film is not None else None, C.byref(stats)))
+        return film, stats.as_dict()
+
+    # LightingCalculator::ComputeFinalLight, rows split over the ranks; total_ptr: n floats, this rank's rows written
+    def propagate(self, graph, L0_ptr, bounces, total_ptr, stream=None, want_iters=True):
+        it = C.c_int32(-1)
+        self.ctx.check(self.lib.avr_graph_propagate_multi(self.h, graph.h, C.c_void_p(L0_ptr), C.c_int32(bounces),
+                                                          C.c_void_p(total_ptr), C.byref(it) if want_iters else None,
+                                                          C.c_void_p(stream or 0)))
+        return int(it.value)
+
+    def row_range(self, n):
+        chunk = (n + self.world - 1) // self.world
+        return min(self.rank * chunk, n), min((self.rank + 1) * chunk, n)
 
 
 class GraphSidecar:

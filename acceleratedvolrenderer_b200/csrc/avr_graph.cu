@@ -9,6 +9,7 @@
 #include <numeric>
 #include <string>
 
+#include "avr_comm.h"
 #include "avr_render_host.h"
 
 using namespace avr;
@@ -361,6 +362,109 @@ extern "C" avr_status avr_graph_propagate_noalloc(avr_graph *g, const float *L0_
     if (iters_done) {
         int32_t fl[2];
         AVR_CUDA(ctx, cudaMemcpyAsync(fl, flags, sizeof(fl), cudaMemcpyDeviceToHost, s));
+        AVR_CUDA(ctx, cudaStreamSynchronize(s));
+        *iters_done = fl[0] ? fl[1] : bounces;
+    }
+    return AVR_OK;
+}
+
+// ---- avr_graph_propagate_multi: ComputeFinalLight with the rows of T split over the ranks ----------------
+// 1-D vertex-range partition, equal chunks of ceil(n / world) rows; rank r multiplies rows
+// [r * chunk, (r + 1) * chunk) and writes them straight into its block of the gathered vector, ONE in-place
+// ncclAllGather per bounce makes that vector the next `cur` on every rank (rank-major blocks of equal size ARE
+// the row order, so nothing is repacked).  The reference's NaN/Inf stop (lighting_calculator.cpp:36-48) needs no
+// extra collective: after the gather every rank holds the whole vector and tests it itself (k_flag_nonfinite),
+// so all ranks reach the same verdict.  The bounce sequence is captured once in a CUDA graph: no host
+// synchronisation between bounces.
+namespace {
+
+__global__ void k_flag_nonfinite(const float *__restrict__ x, int n, int *flags, int iteration) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool bad = false;
+    for (; i < n; i += gridDim.x * blockDim.x) {
+        float v = x[i];
+        bad = bad || isnan(v) || isinf(v);
+    }
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {
+        atomicExch(&flags[0], 1);
+        atomicMin(&flags[1], iteration);
+    }
+}
+
+// cur = total = L0 (cur padded with zeros up to `padded`), flags = {0, INT_MAX}
+__global__ void k_multi_init(const float *__restrict__ L0, float *__restrict__ cur, float *__restrict__ total, int *flags,
+                             int n, int padded, int r0, int r1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { flags[0] = 0; flags[1] = 0x7fffffff; }
+    if (i < padded) {
+        float v = i < n ? L0[i] : 0.f;
+        cur[i] = v;
+        if (i >= r0 && i < r1) total[i] = v;
+    }
+}
+
+}  // namespace
+
+extern "C" avr_status avr_graph_propagate_multi(avr_comm *cm, avr_graph *g, const float *L0_dev, int32_t bounces,
+                                                float *total_dev, int32_t *iters_done, void *stream_) {
+    if (!cm || !g || !L0_dev || !total_dev)
+        return set_err(cm ? cm->ctx : nullptr, AVR_ERR_BAD_ARG, "avr_graph_propagate_multi: NULL argument");
+    avr_ctx *ctx = cm->ctx;
+    if (g->ctx != ctx) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_graph_propagate_multi: the graph belongs to another context");
+    if (bounces < 0) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_graph_propagate_multi: bounces must be >= 0");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = stream_ ? (cudaStream_t)stream_ : ctx->stream;
+    const int n = g->n, world = cm->world;
+    const int chunk = (n + world - 1) / world;
+    const size_t padded = size_t(chunk) * world;
+    const int r0 = std::min(cm->rank * chunk, n), r1 = std::min((cm->rank + 1) * chunk, n);
+    if (cm->gather_floats < padded) {
+        if (cm->exec) { cudaGraphExecDestroy(cm->exec); cm->exec = nullptr; }
+        cudaFree(cm->d_gather[0]); cudaFree(cm->d_gather[1]);
+        cm->d_gather[0] = cm->d_gather[1] = nullptr;
+        cm->gather_floats = 0;
+        AVR_CUDA(ctx, cudaMalloc(&cm->d_gather[0], padded * 4));
+        AVR_CUDA(ctx, cudaMalloc(&cm->d_gather[1], padded * 4));
+        cm->gather_floats = padded;
+    }
+    if (!cm->d_flags) AVR_CUDA(ctx, cudaMalloc(&cm->d_flags, 2 * sizeof(int32_t)));
+    // one captured graph per (CSR, vectors, bounce count); anything else re-captures
+    const void *key[5] = {g->d_val, L0_dev, total_dev, (const void *)(intptr_t)bounces, (const void *)s};
+    if (!cm->exec || std::memcmp(key, cm->exec_key, sizeof(key)) != 0) {
+        if (cm->exec) { cudaGraphExecDestroy(cm->exec); cm->exec = nullptr; }
+        AVR_CUDA(ctx, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+        avr_status st = AVR_OK;
+        ncclResult_t nr = ncclSuccess;
+        float *cur = cm->d_gather[0], *nxt = cm->d_gather[1];
+        k_multi_init<<<blocks_for((int64_t)padded, 256), 256, 0, s>>>(L0_dev, cur, total_dev, cm->d_flags, n, (int)padded, r0, r1);
+        for (int it = 0; it < bounces && nr == ncclSuccess; ++it) {
+            // rows [r0, r1) of T * cur into this rank's block of nxt; fused: total += cur for the previous bounce
+            if (r1 > r0)
+                k_spmv<<<blocks_for(r1 - r0, kRowsPerCta), kRowsPerCta, 0, s>>>(g->d_rowptr, g->d_col, g->d_val, cur, nxt, total_dev,
+                                                                                r0, r1, cm->d_flags, it, it > 0 ? 1 : 0);
+            if (world > 1)
+                nr = cm->api->AllGather(nxt + size_t(cm->rank) * chunk, nxt, (size_t)chunk, ncclFloat, cm->comm, s);
+            // the verdict on bounce `it`, from the whole vector, identical on every rank
+            k_flag_nonfinite<<<std::min(blocks_for(n, 256), 1184), 256, 0, s>>>(nxt, n, cm->d_flags, it);
+            std::swap(cur, nxt);
+        }
+        if (bounces > 0 && r1 > r0) k_axpy<<<blocks_for(r1 - r0, 256), 256, 0, s>>>(cur, total_dev, r0, r1, cm->d_flags);
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamEndCapture(s, &graph);
+        if (nr != ncclSuccess) st = set_err(ctx, AVR_ERR_NCCL, std::string("ncclAllGather: ") + cm->api->GetErrorString(nr));
+        else if (e != cudaSuccess) st = set_cuda_err(ctx, e, "cudaStreamEndCapture");
+        if (st == AVR_OK) {
+            e = cudaGraphInstantiate(&cm->exec, graph, 0);
+            if (e != cudaSuccess) st = set_cuda_err(ctx, e, "cudaGraphInstantiate");
+        }
+        if (graph) cudaGraphDestroy(graph);
+        if (st != AVR_OK) { cm->exec = nullptr; return st; }
+        std::memcpy(cm->exec_key, key, sizeof(key));
+    }
+    AVR_CUDA(ctx, cudaGraphLaunch(cm->exec, s));
+    if (iters_done) {
+        int32_t fl[2];
+        AVR_CUDA(ctx, cudaMemcpyAsync(fl, cm->d_flags, sizeof(fl), cudaMemcpyDeviceToHost, s));
         AVR_CUDA(ctx, cudaStreamSynchronize(s));
         *iters_done = fl[0] ? fl[1] : bounces;
     }

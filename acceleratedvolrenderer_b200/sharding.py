@@ -18,6 +18,16 @@ import torch
 import torch.distributed as dist
 
 
+def init_comm(ctx, group=None):
+    """The library's own communicator (avr_comm, NCCL behind the C ABI) for this rank of the torch.distributed job:
+    rank 0 creates the unique id, torch.distributed only carries its 128 bytes to the other ranks."""
+    from .api import Comm, comm_unique_id
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    box = [comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    return Comm(ctx, box[0], rank, world)
+
+
 def shard_samples(render_desc, rank: int, world: int, spp_per_rank: int):
     """Weak scaling by sample index: rank r owns samples [r*spp, (r+1)*spp) of a (world*spp)-sample render."""
     if not 0 <= rank < world:

@@ -6,10 +6,17 @@ workload (configs[1]); a "step" renders `--spp-per-step` samples per pixel of th
 
   python bench.py --gpus N --steps K --warmup W            # our arm (torchrun launches it for N > 1)
   python bench.py --impl reference ...                     # the reference's CPU path on host cores
+  python bench.py --workload graph-1e7 ...                 # config 4: radiance propagation (Mvertex-bounces/s)
 
-One JSON line on rank 0.  `value` = device-resident throughput (kernel timed with CUDA events on the
-launching stream, film reduce over NCCL included for N > 1); `e2e` = the same through the C-ABI
-entry point with HOST film buffers (tables H2D + film D2H inside the timed region).
+One JSON line on rank 0.
+  value      device-resident throughput of the arithmetic mode the adapter ships (FAST, exact_math = 0): render
+             kernel + film ncclReduce for N > 1, timed with CUDA events on the launching stream, max over ranks
+  exact      the same measurement with exact_math = 1 (the mode whose per-ray parity is pinned), same command
+  e2e        the same metric through the C-ABI call a host makes: avr_render_volpath (N = 1) /
+             avr_render_volpath_multi (N > 1) with a HOST film — tables H2D, render, reduce, film D2H + add
+  parity     GPU film (FAST and EXACT, >= 256 spp) against the reference's own pixels of the SAME workload:
+             z-scores of 16x16-pixel block means, from the reference's per-block sample variance
+  roofline   algorithmic bytes of the dominant kernel / its CUDA-event time, against the measured HBM peak
 """
 import argparse
 import ctypes as C
@@ -33,13 +40,21 @@ WORKLOADS = {
     # (media.cpp:521), high albedo, forward-peaked phase function, long paths.
     # sigma_t gives an optical depth of ~100 through the centre; camera framed so the
     # cloud fills about half of the frame as in the pbrt-v4-scenes disney-cloud view.
-    "disney-cloud-standin-720p": dict(grid=(512, 352, 624), width=1280, height=720, sigma_t=200.0, albedo=0.999,
-                                      g=0.877, max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4),
-                                      fov=16.0),
+    "disney-cloud-standin-720p": dict(kind="volpath", grid=(512, 352, 624), width=1280, height=720, sigma_t=200.0,
+                                      albedo=0.999, g=0.877, max_depth=100, majorant_res=(64, 64, 64),
+                                      eye=(0.0, 0.3, -2.4), fov=16.0, spp_per_step=16),
+    # configs[2]: "Disney cloud HD, high-albedo multiple scattering (long paths)": 1920x1080, depth 1000
+    "disney-cloud-standin-hd": dict(kind="volpath", grid=(512, 352, 624), width=1920, height=1080, sigma_t=200.0,
+                                    albedo=0.999, g=0.877, max_depth=1000, majorant_res=(64, 64, 64),
+                                    eye=(0.0, 0.3, -2.4), fov=16.0, spp_per_step=8),
     # small variant for smoke runs / CPU-box sanity
-    "cloud-small": dict(grid=(96, 80, 104), width=320, height=180, sigma_t=200.0, albedo=0.999, g=0.877,
-                        max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4), fov=16.0),
+    "cloud-small": dict(kind="volpath", grid=(96, 80, 104), width=320, height=180, sigma_t=200.0, albedo=0.999, g=0.877,
+                        max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4), fov=16.0, spp_per_step=16),
+    # configs[3]: src/graph propagation, 8 iterations, synthetic random-geometric transport matrix
+    "graph-1e7": dict(kind="graph", n=10_000_000, avg_deg=6, bounces=8),
+    "graph-1e5": dict(kind="graph", n=100_000, avg_deg=6, bounces=8),
 }
+BLOCK = 16  # parity statistic: block means over BLOCK x BLOCK pixels
 
 
 def fbm_density_torch(nx, ny, nz, device, seed=7, octaves=5, frequency=3.0, threshold=0.3, sharp=3.0):
@@ -141,7 +156,7 @@ def measured_peaks():
 
 def measured_traffic(workload, layout, exact, spp):
     """DRAM bytes per k_volpath launch from the committed ncu capture of this configuration (or None)."""
-    p = os.path.join(ROOT, "profiles", "r1_volpath_dram_traffic.json")
+    p = os.path.join(ROOT, "profiles", "volpath_dram_traffic.json")
     if not os.path.exists(p):
         return None, None
     for e in json.load(open(p))["entries"]:
@@ -152,74 +167,300 @@ def measured_traffic(workload, layout, exact, spp):
     return None, None
 
 
-def run_reference_arm(args, w, density):
-    """--impl reference / cpu_baseline: the CPU path on all host threads, each step a bounded sample of the
-    frame (a pixel lattice, 1 spp).  kind "reference": the reference's OWN NanoVDBMedium (over a real
-    nanovdb grid built with its vendored GridBuilder) and VolPathIntegrator::Li, compiled from
-    /root/reference into oracle/_ref/libavr_refprobe.so (shipped to the GPU box as a built artefact).
-    kind "port": the oracle restatement, when that library is not there."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
-    from cpu_checker import Checker, have_ref
-    threads = os.cpu_count() or 1
-    nd, rd = make_scene(w, density, 1, 1)
-    W, H = w["width"], w["height"]
-    kind = "reference" if have_ref() else "port"
-    if kind == "port":
-        orc = Checker("orc")
-        mo = orc.medium_nanovdb(nd)
+# ---- the reference's CPU path (--impl reference, cpu_baseline, and the reference pixels of `parity`) ---------
+def film_values(rd, out12):
+    """Per-sample sensor RGB exactly as RGBFilm::AddSample forms it before the sum (film.h:95-100,239-255, weight 1):
+    imagingRatio * mean_i(sensor_c(lambda_i) * L_i / pdf_i); NaN / Inf radiance -> black (cpu/integrators.cpp:286-296)."""
+    L = out12[:, 0:4].astype(np.float64); lam = out12[:, 4:8]; pdf = out12[:, 8:12].astype(np.float64)
+    bad = ~np.isfinite(L).all(axis=1)
+    idx = np.clip(np.rint(lam).astype(np.int64) - 360, 0, 470)
+    inside = (lam >= 360) & (lam <= 830) & (pdf != 0)
+    q = np.where(inside, L / np.where(pdf != 0, pdf, 1.0), 0.0)
+    sens = rd.sensor_rgb.astype(np.float64)
+    rgb = np.stack([(sens[c][idx] * q).mean(axis=1) for c in range(3)], axis=1) * float(rd.c.imaging_ratio)
+    rgb[bad] = 0.0
+    return rgb
 
-        def render(stride, seed):
-            orc.lib.orc_set_pixel_stride(C.c_int(stride))
-            mo.render(rd.with_(sampler_seed=seed), threads=threads)
-            orc.lib.orc_set_pixel_stride(C.c_int(1))
-    else:
-        ref = Checker("ref")
-        mo = ref.medium_nanovdb(nd)
 
-        def render(stride, seed):
-            xs, ys = np.arange(0, W, stride), np.arange(0, H, stride)
-            smp = np.stack([np.tile(xs, ys.size), np.repeat(ys, xs.size), np.zeros(xs.size * ys.size)], axis=1).astype(np.int32)
-            r = rd.with_(sampler_seed=seed)
-            smp, rays = mo.camera_rays(r, smp)
+class ReferenceArm:
+    """The reference's OWN NanoVDBMedium (over a real nanovdb grid built with its vendored GridBuilder) and
+    VolPathIntegrator::Li, compiled from /root/reference into oracle/_ref (shipped to the GPU box as a built
+    artefact): the timing flavour (-O3 -march=x86-64-v3, contraction on, as the reference's Release build) when it
+    is there, else the parity flavour; kind "port" (the oracle restatement) only when neither exists.  All host
+    threads, the medium and its grid built once, every sample goes through the film arithmetic (film_values)."""
+
+    def __init__(self, w, density, spp):
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
+        import cpu_checker
+        self.threads = os.cpu_count() or 1
+        self.w, self.W, self.H, self.spp = w, w["width"], w["height"], spp
+        self.nd, self.rd = make_scene(w, density, spp, 1)
+        timing = os.path.join(ROOT, "oracle", "_ref", "libavr_refprobe_timing.so")
+        parity_path = cpu_checker.REF_PATH
+        if os.path.exists(timing):
+            cpu_checker.REF_PATH = timing
+            self.kind, self.flags = "reference", "-O3 -march=x86-64-v3 -ffp-contract=fast"
+        elif cpu_checker.have_ref():
+            self.kind, self.flags = "reference", "-O2 -ffp-contract=off (parity build)"
+        else:
+            self.kind, self.flags = "port", "-O2 -ffp-contract=off (oracle restatement)"
+        try:
+            self.ck = cpu_checker.Checker("ref" if self.kind == "reference" else "orc")
+        finally:
+            cpu_checker.REF_PATH = parity_path
+        self.mo = self.ck.medium_nanovdb(self.nd)
+        nb = ((self.H + BLOCK - 1) // BLOCK) * ((self.W + BLOCK - 1) // BLOCK)
+        self.bsum = np.zeros(nb); self.bsq = np.zeros(nb); self.bcnt = np.zeros(nb)
+        self.lattice = None
+
+    def close(self):
+        self.mo.close()
+
+    def render(self, stride, seed):
+        """One step: `spp` samples of every `stride`-th pixel in x and y.  Returns the number of samples."""
+        W, H, spp = self.W, self.H, self.spp
+        xs, ys = np.arange(0, W, stride), np.arange(0, H, stride)
+        px = np.tile(np.repeat(xs, spp), ys.size); py = np.repeat(ys, xs.size * spp)
+        si = np.tile(np.arange(spp), xs.size * ys.size)
+        smp = np.stack([px, py, si], axis=1).astype(np.int32)
+        r = self.rd.with_(sampler_seed=seed)
+        if self.kind == "port":
+            # the restatement renders films, not sample lists: timing only, no pixels for `parity`
+            self.ck.lib.orc_set_pixel_stride(C.c_int(stride))
+            self.mo.render(r, threads=self.threads)
+            self.ck.lib.orc_set_pixel_stride(C.c_int(1))
+            return smp.shape[0]
+        else:
+            smp, rays = self.mo.camera_rays(r, smp)
+            out = np.zeros((smp.shape[0], 12), dtype=np.float32)
             # interleaved shares: neighbouring pixels cost alike, so every thread gets the same mix
-            parts = [(smp[k::threads * 4], rays[k::threads * 4]) for k in range(threads * 4)]
+            parts = list(range(self.threads * 4))
             it = iter(parts)
             lock = threading.Lock()
+            step = self.threads * 4
 
             def work():
                 while True:
                     with lock:
-                        job = next(it, None)
-                    if job is None:
+                        k = next(it, None)
+                    if k is None:
                         return
-                    mo.volpath_li(r, job[0], job[1])  # ctypes releases the GIL inside the reference code
-            pool = [threading.Thread(target=work) for _ in range(threads)]
+                    o, _ = self.mo.volpath_li(r, smp[k::step], rays[k::step])  # ctypes releases the GIL
+                    out[k::step] = o
+            pool = [threading.Thread(target=work) for _ in range(self.threads)]
             for t in pool:
                 t.start()
             for t in pool:
                 t.join()
+        # the film: sensor RGB of every sample, binned into BLOCK x BLOCK pixel blocks (Y channel) for `parity`
+        y = film_values(self.rd, out)[:, 1]
+        nbx = (W + BLOCK - 1) // BLOCK
+        b = (smp[:, 1] // BLOCK) * nbx + smp[:, 0] // BLOCK
+        n = self.bsum.size
+        self.bsum += np.bincount(b, weights=y, minlength=n)
+        self.bsq += np.bincount(b, weights=y * y, minlength=n)
+        self.bcnt += np.bincount(b, minlength=n)
+        self.lattice = (stride if self.lattice in (None, stride) else -1)
+        return smp.shape[0]
 
-    # bounded sample: every `stride`-th pixel in x and y of the whole frame, stride calibrated so that one
-    # step is a few seconds of CPU work
-    stride = 16
-    t = time.perf_counter(); render(stride, 0); cal = time.perf_counter() - t
-    while stride > 1 and cal * 4 < 4.0:
-        stride //= 2; cal *= 4
-    cw, ch = (W + stride - 1) // stride, (H + stride - 1) // stride
+    def calibrate(self, target_s):
+        """Lattice stride such that one step is about target_s seconds of CPU work."""
+        stride = 32
+        t = time.perf_counter(); self.render(stride, 900); cal = time.perf_counter() - t
+        while stride > 1 and cal * 4 < target_s:
+            stride //= 2; cal *= 4
+        self.bsum[:] = 0; self.bsq[:] = 0; self.bcnt[:] = 0; self.lattice = None
+        return stride
+
+    def describe(self, stride):
+        W, H = self.W, self.H
+        cw, ch = (W + stride - 1) // stride, (H + stride - 1) // stride
+        what = ("the reference's NanoVDBMedium + VolPathIntegrator::Li + film arithmetic (oracle/_ref, "
+                if self.kind == "reference" else "oracle port of the reference renderer (")
+        lattice = "every pixel" if stride == 1 else f"every {stride}th pixel in x and y"
+        return f"{lattice} of {W}x{H} ({cw}x{ch} pixels) x {self.spp} spp per step; {what}{self.flags})"
+
+
+def lattice_blocks(W, H, stride):
+    """Block index of every lattice pixel (row-major over ys x xs) and the lattice pixel count per block."""
+    nbx = (W + BLOCK - 1) // BLOCK
+    nb = nbx * ((H + BLOCK - 1) // BLOCK)
+    xs, ys = np.arange(0, W, stride), np.arange(0, H, stride)
+    bidx = ((ys // BLOCK)[:, None] * nbx + (xs // BLOCK)[None, :]).ravel()
+    return xs, ys, bidx, np.bincount(bidx, minlength=nb).astype(np.float64)
+
+
+def parity_block(ref: ReferenceArm, gpu_steps, spp_step):
+    """z-scores of the BLOCK x BLOCK block means (film Y) of the GPU renders against the reference's, over the pixel
+    lattice the reference rendered.  gpu_steps[name] = array (k, blocks): block means of k independent GPU steps.
+      z = (gpu - ref) / sqrt(var_ref / n_ref + SE_gpu^2): var_ref = the reference's own per-block sample variance,
+      SE_gpu^2 = the variance of the k GPU step means / k.  Under "same distribution" the z are N(0, 1): rms_z ~ 1,
+      max |z| over ~1500 lit blocks ~ 3.5; a relative bias b of the GPU estimator shows as global_mean_z = b / (the
+      relative standard error of the reference's global mean, global_mean_rel_se)."""
+    W, H, stride = ref.W, ref.H, ref.lattice
+    if not stride or stride < 0 or ref.bcnt.sum() == 0:
+        return None
+    _, _, _, npix = lattice_blocks(W, H, stride)
+    cnt = np.maximum(ref.bcnt, 1)
+    m_ref = ref.bsum / cnt
+    var_ref = np.maximum(ref.bsq / cnt - m_ref ** 2, 0) * cnt / np.maximum(cnt - 1, 1)
+    out = {"block": BLOCK, "lattice_stride": stride, "reference_samples": int(ref.bcnt.sum()),
+           "statistic": "film Y (sensor g-bar) block means over the reference's pixel lattice",
+           "reference": f"{ref.kind} ({ref.flags})"}
+    dump = {"m_ref": m_ref, "var_ref": var_ref, "cnt": ref.bcnt, "npix": npix}
+    for name, steps in gpu_steps.items():
+        k = steps.shape[0]
+        m_gpu = steps.mean(axis=0)
+        se2_gpu = steps.var(axis=0, ddof=1) / k
+        lit = (npix > 0) & ((var_ref > 0) | (se2_gpu > 0))
+        d = m_gpu[lit] - m_ref[lit]
+        se = np.sqrt(var_ref[lit] / cnt[lit] + se2_gpu[lit])
+        z = d / se
+        wgt = npix[lit] / npix[lit].sum()
+        gse = float(np.sqrt(((se * wgt) ** 2).sum()))
+        gref = float((m_ref[lit] * wgt).sum())
+        out[name] = {"gpu_spp": int(k * spp_step), "blocks": int(lit.sum()),
+                     "blocks_black_in_both": int(((npix > 0) & ~lit).sum()),
+                     "max_abs_z": float(np.abs(z).max()), "rms_z": float(np.sqrt((z * z).mean())),
+                     "frac_abs_z_lt_4": float((np.abs(z) < 4).mean()), "frac_abs_z_gt_2": float((np.abs(z) > 2).mean()),
+                     "global_mean_ratio": float((m_gpu[lit] * wgt).sum() / gref),
+                     "global_mean_z": float((d * wgt).sum() / gse), "global_mean_rel_se": gse / gref}
+        dump["m_" + name] = m_gpu; dump["se2_" + name] = se2_gpu
+    if os.environ.get("AVR_BENCH_DUMP"):
+        np.savez(os.environ["AVR_BENCH_DUMP"], **dump)
+    return out
+
+
+def run_reference_arm(args, w, density, spp):
+    """--impl reference: W warm-up + K timed steps, each a bounded lattice sample of the repo arm's step
+    (same spp per step) sized so that the run ends within a few minutes."""
+    ref = ReferenceArm(w, density, spp)
+    total = max(1, args.steps + args.warmup)
+    stride = ref.calibrate(min(8.0, 150.0 / total))
     for i in range(args.warmup):
-        render(stride, 1 + i)
+        ref.render(stride, 1 + i)
     t = time.perf_counter()
+    n = 0
     for i in range(args.steps):
-        render(stride, 100 + i)
+        n += ref.render(stride, 100 + i)
     dt = time.perf_counter() - t
-    mo.close()
-    value = cw * ch * args.steps / dt / 1e6
-    what = ("the reference's NanoVDBMedium + VolPathIntegrator::Li (oracle/_ref)" if kind == "reference"
-            else "oracle port of the reference renderer")
-    lattice = "every pixel" if stride == 1 else f"every {stride}th pixel in x and y"
-    sample_desc = f"{lattice} of {W}x{H} ({cw}x{ch} paths), 1 spp per step; {what}"
-    return value, dt / args.steps * 1e3, threads, sample_desc, kind
+    desc = ref.describe(stride)
+    ref.close()
+    return n / dt / 1e6, dt / max(args.steps, 1) * 1e3, ref.threads, desc, ref.kind
+
+
+# ---- config 4: graph propagation ------------------------------------------------------------------------------
+def run_graph(args, w, rank, world, local_rank, base):
+    import torch
+    import torch.distributed as dist
+    from acceleratedvolrenderer_b200.api import Context
+    n, bounces = w["n"], w["bounces"]
+    rowptr, col, val = scenes.random_graph(n, avg_deg=w["avg_deg"], seed=5)
+    L0h = np.random.default_rng(5).random(n, dtype=np.float32)
+    nnz = int(col.size)
+    base = dict(base)
+    base.update({"metric": "Mvertex-bounces/s on src/graph radiance propagation", "unit": "Mvertex-bounces/s",
+                 "scaling": "strong", "dtype": "f32",
+                 "config": {"workload": args.workload, "vertices": n, "nnz": nnz, "bounces": bounces,
+                            "matrix": "synthetic random-geometric transport graph (scenes.random_graph, seed 5)"}})
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
+        import cpu_checker
+        kind = "reference" if cpu_checker.have_ref() else "port"
+        ck = cpu_checker.Checker("ref" if kind == "reference" else "orc")
+        for _ in range(min(args.warmup, 1)):
+            ck.graph_propagate(rowptr, col, val, L0h, bounces)
+        steps = max(1, min(args.steps, 5))
+        t = time.perf_counter()
+        for _ in range(steps):
+            ck.graph_propagate(rowptr, col, val, L0h, bounces)
+        dt = time.perf_counter() - t
+        v = n * bounces * steps / dt / 1e6
+        out = dict(base)
+        out.update({"impl": "reference", "value": v, "ms_per_step": dt / steps * 1e3, "steps": steps, "gpu_launches": 0,
+                    "cpu_baseline": {"value": v, "unit": base["unit"], "cores": 1, "kind": kind,
+                                     "sample": f"{steps} full propagations; LightingCalculator::ComputeFinalLight "
+                                               "(Eigen sparse product, one core as in the reference)"},
+                    "e2e": {"value": v, "unit": base["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        print(json.dumps(out))
+        return 0
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = Context(local_rank)
+    g = ctx.create_graph(rowptr, col, val)
+    L0 = torch.from_numpy(L0h).to(dev)
+    total = torch.zeros(n, dtype=torch.float32, device=dev)
+    comm = sharding.init_comm(ctx) if world > 1 else None
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step():
+        if comm is not None:
+            comm.propagate(g, L0.data_ptr(), bounces, total.data_ptr(), want_iters=False)
+        else:
+            g.propagate_device(L0.data_ptr(), bounces, total.data_ptr())
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    sync_all()
+    dt = time.perf_counter() - t
+    clk = clocks.stop()
+    tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dt = float(tt[0])
+    value = n * bounces * args.steps / dt / 1e6
+    # e2e: host vectors through avr_graph_propagate (rank 0 alone: the host-buffer entry is single-GPU)
+    e2e = None
+    if rank == 0:
+        g.compute_final_light(L0h, bounces)
+        t = time.perf_counter()
+        k = max(1, min(args.steps, 5))
+        for _ in range(k):
+            g.compute_final_light(L0h, bounces)
+        e2e = n * bounces * k / (time.perf_counter() - t) / 1e6
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        peaks, peak_kind = measured_peaks()
+        alg = bounces * (12.0 * nnz + 16.0 * n) / max(world, 1)   # per GPU: its rows' share (SURVEY 8(d))
+        achieved = alg / (dt / args.steps) / 1e9
+        out = dict(base)
+        out.update({"impl": "avr_b200", "value": value, "ms_per_step": dt / args.steps * 1e3,
+                    "e2e": {"value": e2e, "unit": base["unit"], "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 4 * n,
+                            "note": "avr_graph_propagate on rank 0 (host L0 / total)"},
+                    "gpu_launches": args.steps * (bounces + 2),
+                    "roofline": {"bound": "hbm", "kernel": "k_spmv", "achieved": achieved, "peak": peaks["hbm_gbs"],
+                                 "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                                 "algorithmic_bytes": alg,
+                                 "note": "whole step (SpMV + all-gather + checks) / (12 nnz + 16 N) bytes per bounce per GPU"},
+                    "clocks": clk})
+        out["config"]["parallelism"] = (f"vertex-range rows x{world}, ncclAllGather per bounce, one CUDA graph per step"
+                                        if world > 1 else "1 gpu")
+        print(json.dumps(out))
+    if comm is not None:
+        comm.close()
+    g.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
 
 
 def main():
@@ -229,10 +470,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="avr_b200")
     ap.add_argument("--workload", default=os.environ.get("AVR_BENCH_WORKLOAD", "disney-cloud-standin-720p"))
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=0)
     ap.add_argument("--layout", default="octet32")
-    ap.add_argument("--exact", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-exact", action="store_true", help="skip the exact_math=1 measurement")
+    ap.add_argument("--parity-spp", type=int, default=256)
     args = ap.parse_args()
     w = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -240,12 +482,16 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     base = {"metric": "Msamples/s on Disney cloud 720p volpath", "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "medium": "nanovdb (dense fBm stand-in flattened over its index box)",
-                       "film": [w["width"], w["height"]], "grid": list(w["grid"]),
-                       "majorant_res": list(w["majorant_res"]), "sigma_t": w["sigma_t"], "albedo": w["albedo"],
-                       "g": w["g"], "max_depth": w["max_depth"], "sampler": "independent",
-                       "l2": "density store (octets, 3.6 GB at 720p workload) is far larger than the 126 MB L2"}}
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+    if w["kind"] == "graph":
+        return run_graph(args, w, rank, world, local_rank, base)
+    spp = args.spp_per_step or w["spp_per_step"]
+    # `config` names the workload only (identical in both arms); what is specific to our kernels is `kernel_config`
+    base["config"] = {"workload": args.workload, "medium": "nanovdb (dense fBm stand-in flattened over its index box)",
+                      "film": [w["width"], w["height"]], "grid": list(w["grid"]),
+                      "majorant_res": list(w["majorant_res"]), "sigma_t": w["sigma_t"], "albedo": w["albedo"],
+                      "g": w["g"], "max_depth": w["max_depth"], "sampler": "independent", "spp_per_step": spp,
+                      "l2": "inputs (3.6 GB octet store at this workload) are far larger than the 126 MB L2: no flush between steps"}
 
     if args.impl == "reference":
         if rank != 0:
@@ -253,14 +499,13 @@ def main():
         import torch  # only for the density generator when a GPU is around
         dev = "cuda:0" if torch.cuda.is_available() else None
         density = make_density(w, dev) if dev else scenes.fbm_density(*w["grid"])
-        value, ms, threads, sample_desc, kind = run_reference_arm(args, w, density)
+        value, ms, threads, sample_desc, kind = run_reference_arm(args, w, density, spp)
         out = dict(base)
         out.update({"impl": "reference", "value": value, "ms_per_step": ms, "n_gpus": args.gpus,
                     "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": threads, "kind": kind,
                                      "sample": sample_desc},
                     "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                     "gpu_launches": 0})
-        out["config"]["spp_per_step"] = 1
         print(json.dumps(out))
         return 0
 
@@ -274,16 +519,19 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     density = make_density(w, dev)
-    spp = args.spp_per_step
-    nd, rd = make_scene(w, density, spp, args.exact)
+    nd, rd = make_scene(w, density, spp, 0)
     ctx = Context(local_rank)
     t0 = time.perf_counter()
     med = ctx.create_medium("nanovdb", nd, layout=args.layout)
     build_s = time.perf_counter() - t0
+    comm = sharding.init_comm(ctx) if world > 1 else None
     W, H = w["width"], w["height"]
     film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
     # weak scaling by sample index: every rank renders its own `spp` samples of every pixel
     rdr = sharding.shard_samples(rd, rank, world, spp)
+    # a stream of our own: torch's default stream has handle 0, which the C ABI reads as "the context's stream"
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -291,89 +539,152 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    def device_step(step):
+    def device_step(step, exact, ev=None):
+        # everything on ONE stream (torch's current one): film clear -> render kernel -> ncclReduce
         film.zero_()
-        r = rdr.with_(sampler_seed=step)
-        st = ctx.render_volpath_device(med, r, film.data_ptr(), want_stats=True)  # syncs the library stream
+        r = rdr.with_(sampler_seed=step, exact_math=exact)
+        if ev:
+            ev[0].record(stream)
+        st = ctx.render_volpath_device(med, r, film.data_ptr(), stream=stream.cuda_stream, want_stats=True)
+        if ev:
+            ev[1].record(stream)
         sharding.reduce_film(film, dst=0)
         return st
 
-    for i in range(args.warmup):
-        device_step(i)
-    sync_all()
+    def timed(exact, steps, warmup):
+        for i in range(warmup):
+            device_step(i, exact)
+        sync_all()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        acc = {"camera_fetches": 0, "shadow_fetches": 0, "segments": 0, "camera_rays": 0}
+        ev0.record(stream)
+        for i in range(steps):
+            st = device_step(warmup + i, exact, kev[i])
+            for k in acc:
+                acc[k] += st[k]
+        ev1.record(stream)
+        sync_all()
+        # device time of the whole loop and of the render kernel alone (events on the launching stream); max over ranks
+        tt = torch.tensor([ev0.elapsed_time(ev1) / 1e3, sum(a.elapsed_time(b) for a, b in kev) / 1e3],
+                          dtype=torch.float64, device=dev)
+        cnt = torch.tensor([acc["camera_rays"], acc["camera_fetches"], acc["shadow_fetches"], acc["segments"]],
+                           dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        return float(tt[0]), float(tt[1]), [float(x) for x in cnt]
+
+    def e2e(exact, steps):
+        """The call a host makes: avr_render_volpath (N = 1) or avr_render_volpath_multi (N > 1, ncclReduce inside the
+        library), HOST film on rank 0; every step ADDS its samples to that film (progressive render)."""
+        host_film = np.zeros((H, W, 4), dtype=np.float64) if rank == 0 else None
+        full = rd.with_(spp=spp * world, exact_math=exact)
+
+        def one(seed):
+            if comm is not None:
+                comm.render_volpath(med, full.with_(sampler_seed=seed), film=host_film)
+            else:
+                ctx.render_volpath(med, full.with_(sampler_seed=seed), film=host_film)
+        one(99)
+        sync_all()
+        t = time.perf_counter()
+        for i in range(steps):
+            one(100 + i)
+        if world > 1:
+            dist.barrier()
+        dt = time.perf_counter() - t
+        te = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            assert float(host_film[..., 3].min()) == spp * world * (steps + 1), "e2e film is incomplete"
+        return samples_per_step * steps / float(te[0]) / 1e6
+
+    samples_per_step = W * H * spp * world
     clocks = ClockSampler(local_rank)
     clocks.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stats_acc = {"camera_fetches": 0, "shadow_fetches": 0, "segments": 0, "camera_rays": 0, "kernel_ms": 0.0}
-    t_wall = time.perf_counter()
-    ev0.record()
-    for i in range(args.steps):
-        st = device_step(args.warmup + i)
-        for k in stats_acc:
-            stats_acc[k] += st[k]
-    ev1.record()
-    sync_all()
-    wall = time.perf_counter() - t_wall
+    loop_s, kern_s, (rays, cam_f, sh_f, segs) = timed(0, args.steps, args.warmup)
     clk = clocks.stop()
-    # kernel time on the library's launching stream (CUDA events inside the library) + reduce, as wall
-    # between synchronised points; take the max over ranks
-    tt = torch.tensor([wall, stats_acc["kernel_ms"] / 1e3], dtype=torch.float64, device=dev)
-    cnt = torch.tensor([stats_acc["camera_rays"], stats_acc["camera_fetches"], stats_acc["shadow_fetches"],
-                        stats_acc["segments"]], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    wall_max, kern_max = float(tt[0]), float(tt[1])
-    rays, cam_f, sh_f, segs = [float(x) for x in cnt]
-    samples_per_step = W * H * spp * world
-    value = samples_per_step * args.steps / wall_max / 1e6
+    value = samples_per_step * args.steps / loop_s / 1e6
+    e2e_value = e2e(0, max(1, args.steps))
+    exact_out = None
+    if not args.no_exact:
+        xs = max(2, args.steps // 4)
+        xl, xk, (_, xcam, xsh, xseg) = timed(1, xs, 1)
+        exact_out = {"value": samples_per_step * xs / xl / 1e6, "ms_per_step": xl / xs * 1e3, "steps": xs,
+                     "e2e": e2e(1, max(1, xs // 2)), "fetches_per_step": (xcam + xsh) / xs, "segments_per_step": xseg / xs,
+                     "kernel_ms_per_step": xk / xs * 1e3}
 
-    # e2e through the host-buffer C-ABI call (rank-local partition; host film accumulate)
-    host_film = np.zeros((H, W, 4), dtype=np.float64)
-    ctx.render_volpath(med, rdr, film=host_film)  # warm
-    sync_all()
-    t = time.perf_counter()
-    e2e_steps = max(1, args.steps)
-    for i in range(e2e_steps):
-        # progressive accumulation: every step adds its samples to the same host film (the C entry ADDS)
-        ctx.render_volpath(med, rdr.with_(sampler_seed=100 + i), film=host_film)
-    if world > 1:
-        dist.barrier()
-    e2e_dt = time.perf_counter() - t
-    te = torch.tensor([e2e_dt], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = samples_per_step * e2e_steps / float(te[0]) / 1e6
+    # parity renders (rank 0's GPU, full frame, >= parity_spp samples per pixel in both modes): k independent steps,
+    # film Y of every step kept at full resolution until the reference's lattice is known
+    gpu_y = {}
+    if rank == 0 and not args.no_cpu_baseline and args.parity_spp > 0:
+        k = max(2, (args.parity_spp + spp - 1) // spp)
+        for name, exact in (("fast", 0), ("exact", 1)):
+            ys_ = []
+            for i in range(k):
+                film.zero_()
+                ctx.render_volpath_device(med, rd.with_(sampler_seed=5000 + i, exact_math=exact), film.data_ptr(),
+                                          stream=stream.cuda_stream, want_stats=False)
+                ys_.append((film[..., 1] / film[..., 3].clamp(min=1)).float().cpu().numpy())
+            gpu_y[name] = ys_
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
         fetch_bytes = 32 if args.layout != "octet16" else 16
-        alg_bytes = (cam_f + sh_f) * fetch_bytes + segs * 4
-        achieved = alg_bytes / max(kern_max, 1e-9) / 1e9 / max(world, 1)  # per-GPU GB/s of the dominant kernel
-        traffic, traffic_src = measured_traffic(args.workload, args.layout, args.exact, spp)
+
+        def roof(cam, sh, seg, ksec, steps, exact):
+            alg = (cam + sh) * fetch_bytes + seg * 4
+            ach = alg / max(ksec, 1e-9) / 1e9 / max(world, 1)  # per-GPU GB/s of the dominant kernel
+            traffic, src = measured_traffic(args.workload, args.layout, exact, spp)
+            return {"bound": "hbm", "kernel": "k_volpath", "achieved": ach, "peak": peaks["hbm_gbs"], "peak_kind": peak_kind,
+                    "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": traffic,
+                    "traffic_unit": "bytes per launch (ncu dram read+write)", "traffic_capture": src,
+                    "algorithmic_bytes": alg / steps / max(world, 1), "fetches_per_step": (cam + sh) / steps,
+                    "segments_per_step": seg / steps, "bytes_per_fetch": fetch_bytes,
+                    "kernel_ms_per_step": ksec / steps * 1e3}
         out = dict(base)
-        out.update({"impl": "avr_b200", "value": value, "ms_per_step": wall_max / args.steps * 1e3,
+        out.update({"impl": "avr_b200", "value": value, "ms_per_step": loop_s / args.steps * 1e3,
                     "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 4 * 471 * 4,
-                            "d2h_bytes_per_step": W * H * 4 * 8},
+                            "d2h_bytes_per_step": W * H * 4 * 8,
+                            "call": "avr_render_volpath_multi (ncclReduce of the film inside the library, one D2H on rank 0)"
+                                    if world > 1 else "avr_render_volpath"},
                     "gpu_launches": args.steps,
-                    "roofline": {"bound": "hbm", "kernel": "k_volpath", "achieved": achieved, "peak": peaks["hbm_gbs"],
-                                 "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                                 "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write)",
-                                 "traffic_capture": traffic_src, "algorithmic_bytes": alg_bytes / args.steps / max(world, 1),
-                                 "fetches_per_step": (cam_f + sh_f) / args.steps,
-                                 "segments_per_step": segs / args.steps, "bytes_per_fetch": fetch_bytes,
-                                 "kernel_ms_per_step": kern_max / args.steps * 1e3},
-                    "clocks": clk, "medium_build_s": build_s, "medium_bytes": med.bytes()})
-        out["config"].update({"spp_per_step": spp, "layout": args.layout, "exact_math": args.exact,
-                              "parallelism": f"sample-index sharded x{world} ({spp} spp per rank per step), film ncclReduce" if world > 1 else "1 gpu"})
+                    "roofline": roof(cam_f, sh_f, segs, kern_s, args.steps, 0),
+                    "clocks": clk, "medium_build_s": build_s, "medium_bytes": med.bytes(),
+                    "kernel_config": {"value_is": "exact_math=0 (FAST: the mode the adapter ships; per-ray parity is pinned "
+                                                  "for exact_math=1, reported under `exact`)",
+                                      "layout": args.layout, "exact_math": 0,
+                                      "parallelism": f"sample-index sharded x{world} ({spp} spp per rank per step), film ncclReduce"
+                                                     if world > 1 else "1 gpu"}})
+        if exact_out:
+            exact_out["roofline_frac"] = roof(xcam, xsh, xseg, xk, xs, 1)["frac"]
+            out["exact"] = exact_out
         if not args.no_cpu_baseline:
             try:
-                v, ms, threads, sample_desc, kind = run_reference_arm(argparse.Namespace(steps=1, warmup=0), w, density)
-                out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": kind,
-                                       "sample": sample_desc}
+                ref = ReferenceArm(w, density, spp)
+                stride = ref.calibrate(6.0)
+                t = time.perf_counter()
+                n, k = 0, 0
+                while k < 3 or (time.perf_counter() - t < 18.0 and k < 64):   # bounded: ~20 s of CPU work
+                    n += ref.render(stride, 100 + k)
+                    k += 1
+                dt = time.perf_counter() - t
+                out["cpu_baseline"] = {"value": n / dt / 1e6, "unit": "Msamples/s", "cores": ref.threads, "kind": ref.kind,
+                                       "sample": f"{k} steps of " + ref.describe(stride)}
+                if gpu_y:
+                    xs_, ys_, bidx, npix = lattice_blocks(W, H, stride)
+                    steps_ = {name: np.stack([np.bincount(bidx, weights=y[ys_][:, xs_].ravel().astype(np.float64),
+                                                          minlength=npix.size) / np.maximum(npix, 1) for y in lst])
+                              for name, lst in gpu_y.items()}
+                    out["parity"] = parity_block(ref, steps_, spp)
+                ref.close()
             except Exception as e:  # the GPU numbers stand on their own
-                out["cpu_baseline"] = {"value": None, "error": str(e)}
+                out["cpu_baseline"] = {"value": None, "error": repr(e)}
         print(json.dumps(out))
+    if comm is not None:
+        comm.close()
     med.close()
     ctx.close()
     if world > 1:

@@ -31,12 +31,14 @@ enum {
     AVR_ERR_BAD_ARG = 1,
     AVR_ERR_OOM = 2,
     AVR_ERR_CUDA = 3,
-    AVR_ERR_UNSUPPORTED = 4
+    AVR_ERR_UNSUPPORTED = 4,
+    AVR_ERR_NCCL = 5
 };
 
 typedef struct avr_ctx avr_ctx;
 typedef struct avr_medium avr_medium;
 typedef struct avr_graph avr_graph;
+typedef struct avr_comm avr_comm;
 
 /* ---- context -------------------------------------------------------------------------------- */
 /* One context per GPU/process.  Owns streams, scratch and the last error string. */
@@ -427,6 +429,42 @@ avr_status avr_graph_sidecar_write(const char *path, const avr_graph_sidecar *s)
  * (rowptr not monotone, col outside [0, n)) is AVR_ERR_BAD_ARG. */
 avr_status avr_graph_sidecar_read(const char *path, avr_graph_sidecar **out);
 void avr_graph_sidecar_free(avr_graph_sidecar *s);
+
+/* ---- multi-GPU (SURVEY.md 8(b) avr_comm_init, 8(e)) ------------------------------------------------------
+ * One rank per GPU: a process (MPI / torchrun) or a host thread, each with its own avr_ctx.  The reference
+ * fans its tile loop out over host threads that all add into one film (ParallelFor2D,
+ * cpu/integrators.cpp:168-226) and runs ComputeFinalLight on one core (src/graph/lighting_calculator.cpp:23-59);
+ * here the ranks talk through NCCL over NVLink / NVSwitch.  NCCL is bound at run time (libnccl.so.2, the copy
+ * already loaded in the process if there is one); a host without it gets AVR_ERR_NCCL from these entries and
+ * loses nothing else.
+ *   processes: rank 0 calls avr_comm_unique_id and hands the bytes to the others over any channel it has
+ *              (MPI_Bcast, a file, torch.distributed), then every rank calls avr_comm_init_rank;
+ *   threads:   avr_comm_init_all(ctx[], n, comm[]) (ncclCommInitAll), then thread i uses comm[i]. */
+#define AVR_COMM_ID_BYTES 128
+avr_status avr_comm_unique_id(uint8_t id[AVR_COMM_ID_BYTES]);
+avr_status avr_comm_init_rank(avr_ctx *ctx, const uint8_t id[AVR_COMM_ID_BYTES], int32_t rank, int32_t world,
+                              avr_comm **out);
+avr_status avr_comm_init_all(avr_ctx **ctx, int32_t n, avr_comm **out);
+void avr_comm_destroy(avr_comm *comm);
+int32_t avr_comm_rank(const avr_comm *comm);
+int32_t avr_comm_world(const avr_comm *comm);
+
+/* avr_render_volpath over all ranks of `comm` (every rank calls it with the SAME desc; desc->rank / world are
+ * overwritten): rank r renders the work items with item % world == r into its device film, one ncclReduce
+ * (fp64 sum) to rank 0, which ADDS the complete film into its host `film` (other ranks may pass NULL).
+ * stats: this rank's own counters. */
+avr_status avr_render_volpath_multi(avr_comm *comm, avr_medium *m, const avr_render_desc *desc, double *film,
+                                    avr_render_stats *stats);
+
+/* avr_graph_propagate_device with the rows of T split over the ranks (equal vertex ranges; every rank holds
+ * the whole CSR): per bounce one SpMV over the rank's rows, ONE in-place ncclAllGather of the new vector, and a
+ * finiteness test of the gathered vector on every rank (the reference's NaN/Inf stop needs no second
+ * collective).  The whole bounce sequence is captured in a CUDA graph on first use: no host synchronisation
+ * between bounces.  L0_dev: n floats (the same on every rank); total_dev: n floats of which THIS RANK'S rows
+ * [rank * ceil(n / world), ...) are written; iters_done as avr_graph_propagate_device.  Bit-identical to the
+ * single-GPU result. */
+avr_status avr_graph_propagate_multi(avr_comm *comm, avr_graph *g, const float *L0_dev, int32_t bounces,
+                                     float *total_dev, int32_t *iters_done, void *stream);
 
 /* Parity probe for the EXACT path's restated scalar functions: kind 0 = logf (glibc algorithm),
  * 1 = sinf, 2 = cosf (glibc), 3 = FastExp CPU branch (util/math.h:453-474).  Host buffers. */

@@ -64,6 +64,38 @@ def main():
             ok = ok and int(flag[0]) == 0
         if g2 is not g:
             g2.close()
+    # ---- the same two splits behind the C ABI (avr_comm_*, NCCL bound by the library itself) ------------
+    comm = sharding.init_comm(ctx)
+    med = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    for exact in (1, 0):
+        full = rd.with_(exact_math=exact, spp=3 * world)
+        film, _ = comm.render_volpath(med, full)
+        if rank == 0:
+            ref = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
+            ctx.render_volpath_device(med, full, ref.data_ptr())
+            torch.cuda.synchronize()
+            same = np.allclose(film, ref.cpu().numpy(), rtol=1e-12, atol=1e-300) and bool((film[..., 3] == 3 * world).all())
+            print(f"[C-ABI film] exact={exact} avr_render_volpath_multi == single-GPU: {same}")
+            ok = ok and same
+    med.close()
+    L0d = torch.from_numpy(L0).to(dev)
+    for bounces, scale in ((8, 1.0), (0, 1.0), (25, 3e7)):
+        g2 = g if scale == 1.0 else ctx.create_graph(rowptr, col, (val * scale).astype(np.float32))
+        total = torch.full((n,), float("nan"), device=dev)
+        for rep in range(2):   # second call: the cached CUDA graph
+            it = comm.propagate(g2, L0d.data_ptr(), bounces, total.data_ptr())
+        torch.cuda.synchronize()
+        want, want_it = g2.compute_final_light(L0, bounces)
+        r0, r1 = comm.row_range(n)
+        same = it == want_it and bool((total[r0:r1].cpu().numpy().view(np.uint32) == want[r0:r1].view(np.uint32)).all())
+        flag = torch.tensor([0 if same else 1], device=dev)
+        dist.all_reduce(flag)
+        if rank == 0:
+            print(f"[C-ABI graph] bounces={bounces} scale={scale} iterations={it}/{want_it} rows of every rank bit-identical: {int(flag[0]) == 0}")
+            ok = ok and int(flag[0]) == 0
+        if g2 is not g:
+            g2.close()
+    comm.close()
     g.close()
     ctx.close()
     dist.destroy_process_group()

@@ -88,6 +88,15 @@ class avr_graph_sidecar(C.Structure):
     ]
 
 
+class avr_light_vector_desc(C.Structure):
+    _fields_ = [
+        ("light_dir", C.c_float * 3), ("boundary_type", C.c_int32), ("boundary", C.c_float * 6),
+        ("max_dist_to_center", C.c_float), ("vertex_radius", C.c_float),
+        ("light_iterations", C.c_int32), ("points_on_radius", C.c_int32), ("sampler_seed", C.c_int32),
+        ("sampling_resolution", C.c_int32), ("lambda_", C.c_float * 4),
+    ]
+
+
 class avr_render_desc(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32),

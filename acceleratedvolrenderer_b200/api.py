@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-from ._abi import (avr_graph_sidecar, NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
+from ._abi import (avr_graph_sidecar, avr_light_vector_desc, NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
                    avr_grid_desc, avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
@@ -39,7 +39,7 @@ ABI_SYMBOLS = [
     "avr_graph_create", "avr_graph_create_from_edges", "avr_graph_get_csr", "avr_graph_file_read",
     "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
-    "avr_render_graph", "avr_graph_light_rays", "avr_debug_math",
+    "avr_render_graph", "avr_graph_light_rays", "avr_graph_light_vector", "avr_debug_math",
     "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world",
     "avr_render_volpath_multi", "avr_graph_propagate_multi",
 ]
@@ -456,6 +456,28 @@ class Medium:
         self.ctx.check(self.lib.avr_sample_tmaj_device(self.h, C.c_int(mode), C.c_int(1 if exact else 0),
                                                        C.c_void_p(rays_ptr), C.c_int64(n), C.c_void_p(rng_ptr),
                                                        C.c_void_p(u_ptr), _p(lam), C.c_void_p(out_ptr)))
+
+    def graph_light_vector(self, rdesc, pos, *, vertex_radius, max_dist_to_center, light_iterations, points_on_radius,
+                           sampling_resolution, lam, sampler_seed=0, list_index=None):
+        """LightingCalculator::GetLightVector: L0 per vertex (positions in render = world space); the light and the
+        medium's bounding shape come from the render desc."""
+        pos = _f32(pos); n = pos.size // 3
+        d = avr_light_vector_desc()
+        for i in range(3):
+            d.light_dir[i] = rdesc.c.light_dir[i]
+        d.boundary_type = rdesc.c.boundary_type
+        for i in range(6):
+            d.boundary[i] = rdesc.c.boundary[i]
+        d.max_dist_to_center, d.vertex_radius = max_dist_to_center, vertex_radius
+        d.light_iterations, d.points_on_radius = light_iterations, points_on_radius
+        d.sampler_seed, d.sampling_resolution = sampler_seed, sampling_resolution
+        for i in range(4):
+            d.lambda_[i] = float(lam[i])
+        li = None if list_index is None else np.ascontiguousarray(list_index, dtype=np.int32)
+        out = np.empty(n, dtype=np.float32)
+        self.ctx.check(self.lib.avr_graph_light_vector(self.h, C.byref(d), _p(pos), _p(li, i32p) if li is not None else None,
+                                                       C.c_int32(n), _p(out)))
+        return out
 
     def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):
         rays6 = _f32(rays6); pixel = np.ascontiguousarray(pixel, dtype=np.int32); ts = _f32(ts); lam = _f32(lam)

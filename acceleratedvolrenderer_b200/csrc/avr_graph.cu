@@ -142,24 +142,20 @@ __global__ void k_graph_connect(GraphView g, const float *pts, int64_t n, float 
 }
 
 // ---- light-vector estimator: ComputeRaysToSphere + SampleTransmittance ------------------------------
+// util::ComputeRaysToSphere (src/graph/util.h:814-839, rayInSphere absent) over one ray: `iterations`
+// ratio-tracking estimates (util::SampleTransmittance, :344-366) with IndependentSampler streams
+// StartPixelSample({px, py}, i) and tMax_i = start_scatter_t + dist_in_sphere * Get1D(); returns the mean.
 template <typename TR>
-__global__ void __launch_bounds__(128)
-k_light_rays(MediumView mv, const float *rays, const int32_t *pixel, const float *ts, int64_t n, int iterations,
-             int seed, float l0, float l1, float l2, float l3, float *out) {
+AVR_DEV float light_ray_estimate(const MediumView &mv, const LambdaCtx<TR::NCH> &lc, V3 o, V3 d, int px, int py,
+                                 float start_scatter_t, float dist_in_sphere, int iterations, int seed) {
     constexpr int N = TR::NCH;
-    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-    if (i >= n) return;
-    float lambda[4] = {l0, l1, l2, l3};
-    LambdaCtx<N> lc = make_lambda_ctx<N>(mv, lambda);
-    const float *r = rays + 6 * i;
-    V3 o = v3(r[0], r[1], r[2]), d = v3(r[3], r[4], r[5]);
     float average = 0, totalWeight = 0;
     for (int it = 0; it < iterations; ++it) {
         RNG srng;
-        srng.set_sequence(hash_3u32((uint32_t)pixel[2 * i], (uint32_t)pixel[2 * i + 1], (uint32_t)seed));
+        srng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)seed));
         srng.advance((long long)it * 65536ll);
-        float curDist = ts[2 * i + 1] * srng.uniform();
-        float tMax = ts[2 * i] + curDist;
+        float curDist = dist_in_sphere * srng.uniform();
+        float tMax = start_scatter_t + curDist;
         // unsequenced draws in the reference (util.h:346); GCC order: first draw -> offset
         uint64_t h1 = hash_float(srng.uniform());
         uint64_t h0 = hash_float(srng.uniform());
@@ -177,7 +173,136 @@ k_light_rays(MediumView mv, const float *rays, const int32_t *pixel, const float
         average += Tr * 1.f;
         totalWeight += 1.f;
     }
-    out[i] = (iterations == 0 || totalWeight == 0) ? 0.f : average / totalWeight;
+    return (iterations == 0 || totalWeight == 0) ? 0.f : average / totalWeight;
+}
+
+template <typename TR>
+__global__ void __launch_bounds__(128)
+k_light_rays(MediumView mv, const float *rays, const int32_t *pixel, const float *ts, int64_t n, int iterations,
+             int seed, float l0, float l1, float l2, float l3, float *out) {
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    float lambda[4] = {l0, l1, l2, l3};
+    LambdaCtx<TR::NCH> lc = make_lambda_ctx<TR::NCH>(mv, lambda);
+    const float *r = rays + 6 * i;
+    out[i] = light_ray_estimate<TR>(mv, lc, v3(r[0], r[1], r[2]), v3(r[3], r[4], r[5]), pixel[2 * i], pixel[2 * i + 1],
+                                    ts[2 * i], ts[2 * i + 1], iterations, seed);
+}
+
+// ---- LightingCalculator::GetLightVector (src/graph/lighting_calculator.cpp:84-155) -------------------------
+// Per vertex: a disk of rays along the light direction through the vertex sphere (util::GetDiskPoints,
+// src/graph/util.h:179-204), each clipped against the medium's bounding shape and the vertex sphere
+// (GetHits / GetStartEndT, :419-503), estimated by ComputeRaysToSphere, averaged over the rays that qualify,
+// times Inv4Pi.  One thread per (vertex, lattice slot of the (2n+1)^2 disk lattice); the slot's index among the
+// points INSIDE the disk (the reference's pointIndex, which selects the sampler pixel) is recounted by the
+// thread itself.  The analytic sphere / box hits stand in for Primitive::Intersect + SkipIntersection: hit
+// distances agree with the reference's to rounding, so parity of L0 is by tolerance (tests).
+struct LightVecParams {
+    float in_dir[3];       // direction the light travels (= -wi)
+    int boundary_type;
+    float boundary[6];
+    float max_dist_to_center, vertex_radius;
+    int iterations, points_on_radius, seed, resolution;
+    float lambda[4];
+};
+
+AVR_DEV bool sphere_hit2(V3 c, float r, V3 o, V3 d, float *t0, float *t1) {
+    double ox = double(o.x) - c.x, oy = double(o.y) - c.y, oz = double(o.z) - c.z;
+    double a = double(d.x) * d.x + double(d.y) * d.y + double(d.z) * d.z;
+    double b = 2 * (ox * d.x + oy * d.y + oz * d.z);
+    double cc = ox * ox + oy * oy + oz * oz - double(r) * r;
+    double disc = b * b - 4 * a * cc;
+    if (!(disc > 0) || a == 0) return false;  // tangent rays have one hit: not "OutsideTwoHits"
+    double s = sqrt(disc);
+    double q = (b < 0) ? -0.5 * (b - s) : -0.5 * (b + s);
+    double ta = q / a, tb = (q != 0) ? cc / q : ta;
+    if (ta > tb) { double t = ta; ta = tb; tb = t; }
+    *t0 = (float)ta;
+    *t1 = (float)tb;
+    return ta > 0;  // the origin lies outside, in front of the shape
+}
+
+template <typename TR>
+__global__ void __launch_bounds__(128)
+k_light_vector(MediumView mv, LightVecParams lp, const float *pos, const int32_t *list_index, int n, float *ray_val,
+               unsigned char *ray_ok) {
+    const int side = 2 * lp.points_on_radius + 1, slots = side * side;
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= (long long)n * slots) return;
+    int v = int(i / slots), slot = int(i % slots);
+    ray_ok[i] = 0;
+    V3 dir = v3(lp.in_dir[0], lp.in_dir[1], lp.in_dir[2]);
+    V3 vp = v3(pos[3 * v], pos[3 * v + 1], pos[3 * v + 2]);
+    // origin = vertex.point - inDirection * maxDistToCenter * 2
+    V3 center = vp - (dir * lp.max_dist_to_center) * 2.f;
+    // GetDiskPoints: CoordinateSystem(direction) (vecmath.h:1007-1013), step = radius / (n + 1)
+    float sign = copysignf(1.f, dir.z);
+    float a = -1 / (sign + dir.z);
+    float b = dir.x * dir.y * a;
+    V3 xv = v3(1 + sign * sqr(dir.x) * a, sign * b, -sign * dir.x);
+    V3 yv = v3(b, sign + sqr(dir.y) * a, -dir.y);
+    int point_index = 0, count = 0;
+    V3 disk_point = center;
+    bool inside = lp.points_on_radius == 0 ? slot == 0 : false;
+    if (lp.points_on_radius > 0) {
+        float step = lp.vertex_radius / float(lp.points_on_radius + 1);
+        xv = xv * step;
+        yv = yv * step;
+        for (int s = 0; s < slots; ++s) {
+            int x = s / side - lp.points_on_radius, y = s % side - lp.points_on_radius;
+            V3 p = (center + xv * float(x)) + yv * float(y);
+            V3 dd = p - center;
+            bool in = sqrtf(sqr(dd.x) + sqr(dd.y) + sqr(dd.z)) <= lp.vertex_radius;
+            if (s == slot) { inside = in; disk_point = p; point_index = count; }
+            count += in ? 1 : 0;
+        }
+    } else
+        count = 1;
+    if (!inside) { ray_ok[i] = 2; return; }  // not a disk point at all
+    // GetHits on the medium's bounding shape and on the vertex sphere: both must be entered and left
+    float m0, m1, s0, s1;
+    bool mh;
+    if (lp.boundary_type == 0)
+        mh = sphere_hit2(v3(lp.boundary[0], lp.boundary[1], lp.boundary[2]), lp.boundary[3], disk_point, dir, &m0, &m1);
+    else {
+        float t0 = __int_as_float(0xff800000), t1 = __int_as_float(0x7f800000);
+        mh = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            float inv = 1 / comp(dir, k);
+            float tn = (lp.boundary[k] - comp(disk_point, k)) * inv, tf = (lp.boundary[3 + k] - comp(disk_point, k)) * inv;
+            if (tn > tf) { float t = tn; tn = tf; tf = t; }
+            t0 = tn > t0 ? tn : t0;
+            t1 = tf < t1 ? tf : t1;
+        }
+        mh = t0 < t1 && t0 > 0;
+        m0 = t0; m1 = t1;
+    }
+    if (!mh || !sphere_hit2(vp, lp.vertex_radius, disk_point, dir, &s0, &s1)) return;
+    // GetStartEndT, then SkipIntersection to the medium entry and StartEndT::SkipForward(startT)
+    float startT = m0, endT = fminf(m1, s1), startScatterT = fmaxf(m0, s0), endScatterT = endT;
+    if (endT < startScatterT || endScatterT < startT) return;
+    V3 o = v3(disk_point.x + dir.x * startT, disk_point.y + dir.y * startT, disk_point.z + dir.z * startT);
+    startScatterT -= startT;
+    endScatterT -= startT;
+    LambdaCtx<TR::NCH> lc = make_lambda_ctx<TR::NCH>(mv, lp.lambda);
+    long long li = list_index ? list_index[v] : v;
+    unsigned long long cur = (unsigned long long)li * (unsigned)count + (unsigned)point_index;
+    int yCoor = int(cur / (unsigned)lp.resolution);
+    int xCoor = int(cur - (unsigned long long)yCoor * (unsigned)lp.resolution);
+    ray_val[i] = light_ray_estimate<TR>(mv, lc, o, dir, xCoor, yCoor, startScatterT, endScatterT - startScatterT,
+                                        lp.iterations, lp.seed);
+    ray_ok[i] = 1;
+}
+
+// util::Averager over the rays of a vertex in pointIndex order, then * Inv4Pi (lighting_calculator.cpp:147-152)
+__global__ void k_light_vector_mean(const float *ray_val, const unsigned char *ray_ok, int n, int slots, float *out) {
+    int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    float average = 0, total = 0;
+    for (int s = 0; s < slots; ++s)
+        if (ray_ok[(size_t)v * slots + s] == 1) { average += ray_val[(size_t)v * slots + s] * 1.f; total += 1.f; }
+    out[v] = (total == 0 ? 0.f : average / total) * kInv4Pi;
 }
 
 // ---- GraphIntegrator::Li, free-graph branch (graph_integrator.cpp:180-244) ---------------------------

@@ -368,6 +368,29 @@ avr_status avr_graph_light_rays(avr_medium *m, const float *rays, const int32_t 
                                 const float *ts, int64_t n, int32_t iterations, int32_t sampler_seed,
                                 const float lambda[4], float *out);
 
+/* LightingCalculator::GetLightVector (src/graph/lighting_calculator.cpp:84-155) whole: for every vertex the disk of
+ * rays along the light direction through the vertex sphere (util::GetDiskPoints, src/graph/util.h:179-204), each
+ * clipped against the medium's bounding shape and the vertex sphere (GetHits / GetStartEndT, :419-503), estimated
+ * by ComputeRaysToSphere (:814-839) with `light_iterations` ratio-tracking samples, averaged over the rays that
+ * qualify, times Inv4Pi.  pos: n vertex positions (render = world space); list_index: position of each vertex in the
+ * reference's iteration order over its vertex map (it picks the sampler pixel, lighting_calculator.cpp:103,115),
+ * NULL = the vertex id itself; L0: n floats.  The bounding shape is hit analytically (the reference intersects
+ * its Shape and respawns the ray): hit distances agree to rounding, parity of L0 is by tolerance. */
+typedef struct avr_light_vector_desc {
+    float light_dir[3];          /* direction TOWARDS the distant light (as avr_render_desc.light_dir)           */
+    int32_t boundary_type;       /* AVR_BOUNDARY_*: the medium's bounding primitive                             */
+    float boundary[6];
+    float max_dist_to_center;    /* util::PrimitiveData::maxDistToCenter = |bounds.Diagonal() / 2| (util.h:45-60) */
+    float vertex_radius;         /* FreeGraph::GetVertexRadius()                                                 */
+    int32_t light_iterations;    /* LightingCalculatorConfig::lightIterations                                    */
+    int32_t points_on_radius;    /* ...::pointsOnRadiusLight                                                     */
+    int32_t sampler_seed;        /* the IndependentSampler's seed                                                */
+    int32_t sampling_resolution; /* Options->graph.samplingResolution.x (cmd/graph_maker.cpp:86-107)             */
+    float lambda[4];             /* MediumData::defaultLambda                                                    */
+} avr_light_vector_desc;
+avr_status avr_graph_light_vector(avr_medium *m, const avr_light_vector_desc *desc, const float *pos,
+                                  const int32_t *list_index, int32_t n, float *L0);
+
 /* ---- graph text files (src/graph/graph.cpp:284-416 WriteToStream/ReadFromStream, :644-663 FreeGraph;
  * layout in files/format.txt) ----------------------------------------------------------------------
  *   line 1: description (one token, e.g. "basic")      line 2: "free" vertexRadius

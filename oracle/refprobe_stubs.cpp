@@ -45,7 +45,6 @@ PBRTOptions *Options = nullptr;  // options.cpp:14 (the probe points it at a loc
 // bluenoise.cpp is one of the blobs missing from the reference mount (.MISSING_LARGE_BLOBS); only the
 // PMJ02BN sampler reads it, which the probe never instantiates.
 const uint16_t BlueNoiseTextures[NumBlueNoiseTextures][BlueNoiseResolution][BlueNoiseResolution] = {};
-Float MLTSampler::Get1D() { std::abort(); }
 Float PiecewiseLinearSpectrum::operator()(Float) const {
     std::fprintf(stderr, "refprobe: PiecewiseLinearSpectrum is not part of the probe\n");
     std::abort();

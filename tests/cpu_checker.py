@@ -474,6 +474,37 @@ class CheckerMedium:
                                                dtype=np.int32), i32p))
         return out, info
 
+    def graph_pipeline(self, rdesc: RenderDesc, *, dimension_steps, iterations_per_step, max_depth, light_iterations,
+                       points_on_radius, bounces, radius_modifier=1.0, search_range_neighbours=0, sampler_seed=0):
+        """"ref" only: the reference's own graph pipeline (FreeGraphBuilder::BuildGraph -> GetLightVector ->
+        GetTransportMatrix -> ComputeFinalLight per bounce count; oracle/refprobe_graphbuild.cpp) on this medium
+        inside the render desc's sphere boundary, lit by its distant light.  Returns a dict of arrays."""
+        assert self.ck.kind == "ref" and int(rdesc.c.boundary_type) == 0
+        lib = self.ck.lib
+        lib.ref_graphpipe_run.restype = C.c_void_p
+        sphere = np.array(list(rdesc.c.boundary)[:4], dtype=np.float32)
+        wi = np.array(list(rdesc.c.light_dir), dtype=np.float32)
+        icfg = np.array([dimension_steps, iterations_per_step, max_depth, light_iterations, points_on_radius,
+                         1 if search_range_neighbours > 0 else 0, search_range_neighbours, sampler_seed], dtype=np.int32)
+        fcfg = np.array([radius_modifier], dtype=np.float32)
+        b = np.ascontiguousarray(bounces, dtype=np.int32)
+        h = C.c_void_p(lib.ref_graphpipe_run(self.h, _p(sphere, f32p), _p(wi, f32p), _p(icfg, i32p), _p(fcfg, f32p),
+                                             _p(b, i32p), C.c_int32(b.size)))
+        counts = np.zeros(4, dtype=np.int32); info = np.zeros(6, dtype=np.float32)
+        lib.ref_graphpipe_info(h, _p(counts, i32p), _p(info, f32p))
+        nv, ne = int(counts[0]), int(counts[1])
+        out = dict(pos=np.zeros((nv, 3), np.float32), vsamples=np.zeros(nv, np.int32), vrange=np.zeros(nv, np.float32),
+                   efrom=np.zeros(ne, np.int32), eto=np.zeros(ne, np.int32), esamples=np.zeros(ne, np.int32),
+                   L0=np.zeros(nv, np.float32), totals=np.zeros((b.size, nv), np.float32), iters=np.zeros(b.size, np.int32),
+                   list_index=np.zeros(nv, np.int32))
+        lib.ref_graphpipe_get(h, _p(out["pos"], f32p), _p(out["vsamples"], i32p), _p(out["vrange"], f32p),
+                              _p(out["efrom"], i32p), _p(out["eto"], i32p), _p(out["esamples"], i32p), _p(out["L0"], f32p),
+                              _p(out["totals"], f32p), _p(out["iters"], i32p), _p(out["list_index"], i32p))
+        lib.ref_graphpipe_free(h)
+        out.update(sampling_resolution=int(counts[2]), pixel_samples=int(counts[3]), vertex_radius=float(info[0]),
+                   max_dist_to_center=float(info[1]), lam=info[2:6].copy(), bounces=b)
+        return out
+
     def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):
         rays6 = f32(rays6); pixel = np.ascontiguousarray(pixel, dtype=np.int32); ts = f32(ts); lam = f32(lam)
         n = rays6.size // 6

@@ -1,0 +1,97 @@
+"""GPU: BASELINE config 4 as a PIPELINE, from a graph the REFERENCE builds.
+
+The reference's own FreeGraphBuilder::BuildGraph -> LightingCalculator::GetLightVector -> GetTransportMatrix ->
+ComputeFinalLight (oracle/refprobe_graphbuild.cpp, driven as cmd/graph_maker.cpp:86-197 drives them) produces
+vertices, edges, the light vector L0 and the per-vertex light after {0, 1, 3, 7} bounces.  The device then does
+the same steps through the C ABI on that graph:
+  (a) avr_graph_light_vector           vs GetLightVector      : >= 97 % of vertices within 1e-4 relative (the
+      reference intersects its Sphere shape and respawns the ray, the device hits the sphere analytically: ray
+      origins differ in the last bits, which now and then moves one tentative collision), means within 0.5 %;
+  (b) avr_graph_create_from_edges + avr_graph_propagate from the reference's L0 vs ComputeFinalLight: bit-exact,
+      identical iteration counts;
+  (c) avr_render_graph of the propagated graph vs avr_render_volpath at max_depth = bounces + 1: image means
+      within the band BASELINE.md section 3 records for the fork itself (graph_d1 / graph_d8 vs volpath < 0.5 %),
+      widened by the Monte Carlo standard error of the two renders and the clustering bias of a 2 300-vertex
+      graph: 4 %.
+"""
+import numpy as np
+import pytest
+
+from acceleratedvolrenderer_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+CFG = dict(dimension_steps=80, iterations_per_step=8, max_depth=40, light_iterations=8, points_on_radius=2,
+           radius_modifier=12.0, search_range_neighbours=4)
+BOUNCES = [0, 1, 3, 7]
+
+
+def test_config4_pipeline_from_a_reference_built_graph(ctx, ref):
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    gd, rd = scenes.cloud_scene(dens, width=48, height=36, spp=64, sigma_t=14.0, albedo=0.95, g=0.0, max_depth=8)
+    mo = ref.medium_uniformgrid(gd)
+    pipe = mo.graph_pipeline(rd, bounces=BOUNCES, **CFG)
+    mo.close()
+    nv = pipe["pos"].shape[0]
+    assert nv > 1500 and pipe["efrom"].size > nv
+
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    # (a) the light vector
+    L0 = md.graph_light_vector(rd, pipe["pos"], vertex_radius=pipe["vertex_radius"],
+                               max_dist_to_center=pipe["max_dist_to_center"], light_iterations=CFG["light_iterations"],
+                               points_on_radius=CFG["points_on_radius"], sampling_resolution=pipe["sampling_resolution"],
+                               lam=pipe["lam"], list_index=pipe["list_index"])
+    want = pipe["L0"]
+    ok = np.abs(L0 - want) <= 1e-4 * np.maximum(np.abs(want), 1e-6)
+    print(f"light vector: {ok.mean() * 100:.2f} % of {nv} vertices within 1e-4, mean {L0.mean():.6f} vs {want.mean():.6f}")
+    assert ok.mean() >= 0.97, ok.mean()
+    assert abs(L0.mean() - want.mean()) <= 5e-3 * want.mean(), (L0.mean(), want.mean())
+    assert np.all(L0 >= 0) and L0.max() <= 1 / (4 * np.pi) + 1e-6
+
+    # (b) transport matrix from the edge list + propagation
+    g = ctx.create_graph_from_edges(pipe["vsamples"], pipe["efrom"], pipe["eto"], pipe["esamples"])
+    totals = {}
+    for k, b in enumerate(BOUNCES):
+        got, it = g.compute_final_light(want, int(b))
+        assert it == int(pipe["iters"][k])
+        assert np.array_equal(got.view(np.uint32), pipe["totals"][k].view(np.uint32)), b
+        # the device's own L0 through the same propagation stays as close as L0 itself is
+        mine, _ = g.compute_final_light(L0, int(b))
+        assert abs(mine.mean() - got.mean()) <= 5e-3 * got.mean()
+        totals[int(b)] = mine
+
+    # (c) graph render vs path tracing of the same depth (both on the device; independent sampler)
+    means = {}
+    for b in BOUNCES:
+        g.set_vertices(pipe["pos"], totals[b], pipe["vrange"], pipe["vertex_radius"])
+        gf, _ = ctx.render_graph(md, g, rd)
+        vf, _ = ctx.render_volpath(md, rd.with_(max_depth=b + 1, spp=256))
+        mg = gf[..., :3].sum() / gf[..., 3].sum(); mv = vf[..., :3].sum() / vf[..., 3].sum()
+        means[b] = (float(mg), float(mv))
+        print(f"bounces {b}: graph render mean {mg:.6f} vs volpath max_depth {b + 1} mean {mv:.6f} ({(mg / mv - 1) * 100:+.2f} %)")
+        assert abs(mg - mv) <= 0.04 * mv, (b, mg, mv)
+    # more bounces, more light, in both renderers
+    assert means[0][0] < means[1][0] < means[3][0] < means[7][0]
+    assert means[0][1] < means[1][1] < means[3][1] < means[7][1]
+    g.close(); md.close()
+
+
+def test_light_vector_edge_cases(ctx):
+    from acceleratedvolrenderer_b200.api import AvrError
+    dens = scenes.fbm_density(16, 16, 16, seed=2)
+    gd, rd = scenes.cloud_scene(dens, width=8, height=8, spp=1, sigma_t=6.0)
+    md = ctx.create_medium("uniformgrid", gd, layout="dense")
+    kw = dict(vertex_radius=0.05, max_dist_to_center=1.3, light_iterations=2, points_on_radius=1, sampling_resolution=64,
+              lam=[400, 500, 600, 700])
+    # a vertex far outside the medium's bounding sphere: its disk rays never overlap the medium -> 0
+    pos = np.array([[0.0, 0.0, 0.0], [5.0, 5.0, 5.0]], dtype=np.float32)
+    L0 = md.graph_light_vector(rd, pos, **kw)
+    assert 0 < L0[0] <= 1 / (4 * np.pi) + 1e-6 and L0[1] == 0
+    assert md.graph_light_vector(rd, np.zeros((0, 3), np.float32), **kw).size == 0
+    # points_on_radius = 0: the single ray through the centre (util.h:180-181)
+    one = md.graph_light_vector(rd, pos[:1], **dict(kw, points_on_radius=0))
+    assert 0 < one[0] <= 1 / (4 * np.pi) + 1e-6
+    with pytest.raises(AvrError) as e:
+        md.graph_light_vector(rd, pos, **dict(kw, light_iterations=0))
+    assert "at least one light ray iteration" in str(e.value)   # the reference's ErrorExit text
+    md.close()

@@ -6,6 +6,7 @@ import numpy as np
 NSPEC = 471
 
 f32p = C.POINTER(C.c_float)
+i32p_ = C.POINTER(C.c_int32)
 
 
 def _f32(a):
@@ -62,9 +63,6 @@ class avr_nanovdb_desc(C.Structure):
     ]
 
 
-i32p_ = C.POINTER(C.c_int32)
-
-
 class avr_graph_file(C.Structure):
     _fields_ = [
         ("description", C.c_char * 64),
@@ -94,6 +92,25 @@ class avr_light_vector_desc(C.Structure):
         ("max_dist_to_center", C.c_float), ("vertex_radius", C.c_float),
         ("light_iterations", C.c_int32), ("points_on_radius", C.c_int32), ("sampler_seed", C.c_int32),
         ("sampling_resolution", C.c_int32), ("lambda_", C.c_float * 4),
+    ]
+
+
+class avr_graph_builder_desc(C.Structure):
+    _fields_ = [
+        ("light_dir", C.c_float * 3), ("boundary_type", C.c_int32), ("boundary", C.c_float * 6),
+        ("bounds_center", C.c_float * 3), ("max_dist_to_center", C.c_float), ("vertex_radius", C.c_float),
+        ("dimension_steps", C.c_int32), ("iterations_per_step", C.c_int32), ("max_depth", C.c_int32),
+        ("sampler_seed", C.c_int32), ("sampling_resolution", C.c_int32), ("search_range_neighbours", C.c_int32),
+        ("lambda_", C.c_float * 4),
+    ]
+
+
+class avr_built_graph(C.Structure):
+    _fields_ = [
+        ("n_vertices", C.c_int32), ("n_paths", C.c_int32), ("n_points", C.c_int32), ("cluster_rounds", C.c_int32),
+        ("n_edges", C.c_int64),
+        ("vertex_pos", f32p), ("vertex_samples", i32p_), ("search_range", f32p),
+        ("edge_from", i32p_), ("edge_to", i32p_), ("edge_samples", i32p_),
     ]
 
 

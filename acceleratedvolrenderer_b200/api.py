@@ -13,7 +13,7 @@ import os
 
 import numpy as np
 
-from ._abi import (avr_graph_sidecar, avr_light_vector_desc, NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
+from ._abi import (avr_graph_sidecar, avr_light_vector_desc, avr_graph_builder_desc, avr_built_graph, NSPEC, TMAJ_DTYPE, GridDesc, NanoVDBDesc, NanoVDBGrid, RenderDesc, RGBGridDesc, avr_graph_file,
                    avr_grid_desc, avr_render_desc, avr_render_stats, avr_rgbgrid_desc)
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
@@ -39,7 +39,7 @@ ABI_SYMBOLS = [
     "avr_graph_create", "avr_graph_create_from_edges", "avr_graph_get_csr", "avr_graph_file_read",
     "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
-    "avr_render_graph", "avr_graph_light_rays", "avr_graph_light_vector", "avr_debug_math",
+    "avr_render_graph", "avr_graph_light_rays", "avr_graph_light_vector", "avr_graph_build_free", "avr_built_graph_free", "avr_debug_math",
     "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world",
     "avr_render_volpath_multi", "avr_graph_propagate_multi",
 ]
@@ -67,7 +67,8 @@ def load_library():
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
-                        "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free", "avr_comm_destroy"):
+                        "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free", "avr_comm_destroy",
+                        "avr_built_graph_free"):
             fn.restype = C.c_int
     lib.avr_ctx_destroy.restype = None
     lib.avr_medium_destroy.restype = None
@@ -77,6 +78,8 @@ def load_library():
     lib.avr_graph_sidecar_free.restype = None
     lib.avr_graph_sidecar_free.argtypes = [C.c_void_p]
     lib.avr_comm_destroy.restype = None
+    lib.avr_built_graph_free.restype = None
+    lib.avr_built_graph_free.argtypes = [C.c_void_p]
     lib.avr_comm_destroy.argtypes = [C.c_void_p]
     _lib = lib
     return lib
@@ -477,6 +480,37 @@ class Medium:
         out = np.empty(n, dtype=np.float32)
         self.ctx.check(self.lib.avr_graph_light_vector(self.h, C.byref(d), _p(pos), _p(li, i32p) if li is not None else None,
                                                        C.c_int32(n), _p(out)))
+        return out
+
+    def build_free_graph(self, rdesc, *, vertex_radius, max_dist_to_center, bounds_center, dimension_steps,
+                         iterations_per_step, max_depth, sampling_resolution, lam, search_range_neighbours=0, sampler_seed=0):
+        """FreeGraphBuilder::BuildGraph on the device (avr_graph_build_free): dict of host arrays."""
+        d = avr_graph_builder_desc()
+        for i in range(3):
+            d.light_dir[i] = rdesc.c.light_dir[i]
+            d.bounds_center[i] = float(bounds_center[i])
+        d.boundary_type = rdesc.c.boundary_type
+        for i in range(6):
+            d.boundary[i] = rdesc.c.boundary[i]
+        d.max_dist_to_center, d.vertex_radius = max_dist_to_center, vertex_radius
+        d.dimension_steps, d.iterations_per_step, d.max_depth = dimension_steps, iterations_per_step, max_depth
+        d.sampler_seed, d.sampling_resolution, d.search_range_neighbours = sampler_seed, sampling_resolution, search_range_neighbours
+        for i in range(4):
+            d.lambda_[i] = float(lam[i])
+        h = C.POINTER(avr_built_graph)()
+        self.ctx.check(self.lib.avr_graph_build_free(self.h, C.byref(d), C.byref(h)))
+        c = h.contents
+        nv, ne = c.n_vertices, c.n_edges
+
+        def arr(ptr, n, dt):
+            if not ptr:
+                return None
+            return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True) if n else np.zeros(0, dt)
+        out = dict(pos=arr(c.vertex_pos, 3 * nv, np.float32).reshape(-1, 3), vsamples=arr(c.vertex_samples, nv, np.int32),
+                   vrange=arr(c.search_range, nv, np.float32), efrom=arr(c.edge_from, ne, np.int32),
+                   eto=arr(c.edge_to, ne, np.int32), esamples=arr(c.edge_samples, ne, np.int32),
+                   n_paths=c.n_paths, n_points=c.n_points, cluster_rounds=c.cluster_rounds)
+        self.lib.avr_built_graph_free(h)
         return out
 
     def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):

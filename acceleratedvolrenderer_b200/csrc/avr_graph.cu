@@ -410,6 +410,7 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
 }  // namespace avr
 
 #include "avr_graph_host.inc"
+#include "avr_graph_builder.inc"
 
 // ---- avr_graph_propagate_noalloc: ComputeFinalLight with its scratch in a static device array ---------
 // No counterpart in the reference; added for callers that

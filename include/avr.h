@@ -391,6 +391,38 @@ typedef struct avr_light_vector_desc {
 avr_status avr_graph_light_vector(avr_medium *m, const avr_light_vector_desc *desc, const float *pos,
                                   const int32_t *list_index, int32_t n, float *L0);
 
+/* FreeGraphBuilder::BuildGraph (src/graph/free/free_graph_builder.cpp:143-214) on the device: the light paths of
+ * TracePath (:19-141) traced one per thread under the reference's sampler streams, then the reference's first-come
+ * merge of scatter points into vertices (a point is a new vertex iff no EXISTING vertex lies within the vertex
+ * radius, else it joins the closest) computed exactly as a lexicographically-first maximal independent set in
+ * parallel rounds over a hash grid, edges = consecutive points of a path (samples 1 each; duplicates are merged by
+ * avr_graph_create_from_edges as Graph::AddEdge does), vertex samples = departures, and ComputeSearchRanges
+ * (:498-548).  ReinforceSparseVertices (:281-471) is not run (the reference's configs switch it off by default).
+ * Scatter positions differ from the reference's in the last bits (analytic boundary hits), so the graph is
+ * statistically, not vertex-for-vertex, the reference's.  *out is allocated by the library. */
+typedef struct avr_graph_builder_desc {
+    float light_dir[3];          /* direction TOWARDS the distant light                                          */
+    int32_t boundary_type;
+    float boundary[6];
+    float bounds_center[3];      /* util::PrimitiveData::boundsCenter                                            */
+    float max_dist_to_center;    /* util::PrimitiveData::maxDistToCenter                                         */
+    float vertex_radius;         /* GetSameSpotRadius(mediumData) * radiusModifier (or --node-radius)            */
+    int32_t dimension_steps, iterations_per_step, max_depth;   /* GraphBuilderConfig                             */
+    int32_t sampler_seed, sampling_resolution;
+    int32_t search_range_neighbours;   /* renderSearchRange.neighboursToUse; 0 = inactive                        */
+    float lambda[4];
+} avr_graph_builder_desc;
+typedef struct avr_built_graph {
+    int32_t n_vertices, n_paths, n_points, cluster_rounds;
+    int64_t n_edges;             /* unmerged: one per pair of consecutive scatter points                         */
+    float *vertex_pos;           /* 3 * n_vertices                                                               */
+    int32_t *vertex_samples;
+    float *search_range;         /* n_vertices, or NULL                                                          */
+    int32_t *edge_from, *edge_to, *edge_samples;
+} avr_built_graph;
+avr_status avr_graph_build_free(avr_medium *m, const avr_graph_builder_desc *desc, avr_built_graph **out);
+void avr_built_graph_free(avr_built_graph *g);
+
 /* ---- graph text files (src/graph/graph.cpp:284-416 WriteToStream/ReadFromStream, :644-663 FreeGraph;
  * layout in files/format.txt) ----------------------------------------------------------------------
  *   line 1: description (one token, e.g. "basic")      line 2: "free" vertexRadius

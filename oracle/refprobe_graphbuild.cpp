@@ -30,7 +30,7 @@ extern "C" const pbrt::Medium *ref_medium_ptr(void *m);  // refprobe.cpp
 namespace {
 struct Pipeline {
     int nv = 0, ne = 0, resolution = 0, pixel_samples = 0;
-    float vertex_radius = 0, max_dist_to_center = 0, lambda[4] = {0, 0, 0, 0};
+    float vertex_radius = 0, max_dist_to_center = 0, lambda[4] = {0, 0, 0, 0}, center[3] = {0, 0, 0};
     std::vector<float> pos, range, L0, totals;
     std::vector<int32_t> vsamples, efrom, eto, esamples, iters, list_index;
 };
@@ -107,6 +107,7 @@ void *ref_graphpipe_run(void *medium_h, const float sphere[4], const float light
     p->vertex_radius = g.GetVertexRadius();
     p->max_dist_to_center = mediumData.primitiveData.maxDistToCenter;
     for (int i = 0; i < 4; ++i) p->lambda[i] = mediumData.defaultLambda[i];
+    for (int i = 0; i < 3; ++i) p->center[i] = mediumData.primitiveData.boundsCenter[i];
     p->pos.resize(3 * size_t(p->nv)); p->range.resize(p->nv); p->L0.resize(p->nv); p->vsamples.resize(p->nv);
     for (auto &[id, v] : g.GetVertices()) {  // ids are sequential (CheckSequentialIds in the calculator's constructor)
         p->pos[3 * id] = v.point.x; p->pos[3 * id + 1] = v.point.y; p->pos[3 * id + 2] = v.point.z;
@@ -128,12 +129,13 @@ void *ref_graphpipe_run(void *medium_h, const float sphere[4], const float light
     return p;
 }
 
-// {vertices, edges, samplingResolution, pixelSamples}; info = {vertexRadius, maxDistToCenter, lambda[4]}
-void ref_graphpipe_info(void *h, int32_t counts[4], float info[6]) {
+// {vertices, edges, samplingResolution, pixelSamples}; info = {vertexRadius, maxDistToCenter, lambda[4], boundsCenter[3]}
+void ref_graphpipe_info(void *h, int32_t counts[4], float info[9]) {
     Pipeline *p = (Pipeline *)h;
     counts[0] = p->nv; counts[1] = p->ne; counts[2] = p->resolution; counts[3] = p->pixel_samples;
     info[0] = p->vertex_radius; info[1] = p->max_dist_to_center;
     for (int i = 0; i < 4; ++i) info[2 + i] = p->lambda[i];
+    for (int i = 0; i < 3; ++i) info[6 + i] = p->center[i];
 }
 
 void ref_graphpipe_get(void *h, float *pos, int32_t *vsamples, float *vrange, int32_t *efrom, int32_t *eto,

@@ -490,7 +490,7 @@ class CheckerMedium:
         b = np.ascontiguousarray(bounces, dtype=np.int32)
         h = C.c_void_p(lib.ref_graphpipe_run(self.h, _p(sphere, f32p), _p(wi, f32p), _p(icfg, i32p), _p(fcfg, f32p),
                                              _p(b, i32p), C.c_int32(b.size)))
-        counts = np.zeros(4, dtype=np.int32); info = np.zeros(6, dtype=np.float32)
+        counts = np.zeros(4, dtype=np.int32); info = np.zeros(9, dtype=np.float32)
         lib.ref_graphpipe_info(h, _p(counts, i32p), _p(info, f32p))
         nv, ne = int(counts[0]), int(counts[1])
         out = dict(pos=np.zeros((nv, 3), np.float32), vsamples=np.zeros(nv, np.int32), vrange=np.zeros(nv, np.float32),
@@ -502,7 +502,7 @@ class CheckerMedium:
                               _p(out["totals"], f32p), _p(out["iters"], i32p), _p(out["list_index"], i32p))
         lib.ref_graphpipe_free(h)
         out.update(sampling_resolution=int(counts[2]), pixel_samples=int(counts[3]), vertex_radius=float(info[0]),
-                   max_dist_to_center=float(info[1]), lam=info[2:6].copy(), bounces=b)
+                   max_dist_to_center=float(info[1]), lam=info[2:6].copy(), bounds_center=info[6:9].copy(), bounces=b)
         return out
 
     def graph_light_rays(self, rays6, pixel, ts, iterations, seed, lam):

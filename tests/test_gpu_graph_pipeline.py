@@ -76,6 +76,72 @@ def test_config4_pipeline_from_a_reference_built_graph(ctx, ref):
     g.close(); md.close()
 
 
+def _merged_edges(efrom, eto, n):
+    key = np.unique(efrom.astype(np.int64) * n + eto.astype(np.int64))
+    return key.size, np.bincount((key // n).astype(np.int64), minlength=n)
+
+
+def test_device_graph_builder_is_statistically_the_reference_builder(ctx, ref):
+    """avr_graph_build_free (light paths traced per thread, the first-come vertex merge as a lexicographically-first
+    independent set) against FreeGraphBuilder::BuildGraph on the same scene, sampler streams and configuration.
+    The paths are the reference's up to last-bit differences of the scatter positions, so the counts nearly
+    coincide; the bars are what "statistically the same graph" needs, each stated in place."""
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    gd, rd = scenes.cloud_scene(dens, width=48, height=36, spp=64, sigma_t=14.0, albedo=0.95, g=0.0, max_depth=8)
+    mo = ref.medium_uniformgrid(gd)
+    pipe = mo.graph_pipeline(rd, bounces=BOUNCES, **CFG)
+    mo.close()
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    built = md.build_free_graph(rd, vertex_radius=pipe["vertex_radius"], max_dist_to_center=pipe["max_dist_to_center"],
+                                bounds_center=pipe["bounds_center"], dimension_steps=CFG["dimension_steps"],
+                                iterations_per_step=CFG["iterations_per_step"], max_depth=CFG["max_depth"],
+                                sampling_resolution=pipe["sampling_resolution"], lam=pipe["lam"],
+                                search_range_neighbours=CFG["search_range_neighbours"])
+    nv_ref, nv = pipe["pos"].shape[0], built["pos"].shape[0]
+    ne_ref, deg_ref = _merged_edges(pipe["efrom"], pipe["eto"], nv_ref)
+    ne, deg = _merged_edges(built["efrom"], built["eto"], nv)
+    print(f"vertices {nv} vs {nv_ref}; merged edges {ne} vs {ne_ref}; departures {built['vsamples'].sum()} vs "
+          f"{pipe['vsamples'].sum()}; scatter points {built['n_points']}; rounds {built['cluster_rounds']}; "
+          f"range mean {built['vrange'].mean():.5f} vs {pipe['vrange'].mean():.5f}")
+    if nv == nv_ref:
+        same = np.all(np.abs(built["pos"] - pipe["pos"]) <= 1e-5, axis=1).mean()
+        ka = set((built["efrom"].astype(np.int64) * nv + built["eto"]).tolist())
+        kb = set((pipe["efrom"].astype(np.int64) * nv + pipe["eto"]).tolist())
+        print(f"vertices at the reference's position (1e-5): {same * 100:.2f} %; edge sets: Jaccard {len(ka & kb) / len(ka | kb):.4f}")
+    assert abs(nv - nv_ref) <= 0.02 * nv_ref                     # vertex count within 2 %
+    assert abs(ne - ne_ref) <= 0.03 * ne_ref                     # distinct edges within 3 %
+    assert abs(int(built["vsamples"].sum()) - int(pipe["vsamples"].sum())) <= 0.005 * pipe["vsamples"].sum()
+    assert abs(deg.mean() - deg_ref.mean()) <= 0.03 * deg_ref.mean()
+    # out-degree histogram: total variation distance below 6 % (two independent 2 300-vertex samples of ONE
+    # distribution over ~14 degree bins already differ by about 3 %)
+    hmax = int(max(deg.max(), deg_ref.max())) + 1
+    ha = np.bincount(deg, minlength=hmax) / nv; hb = np.bincount(deg_ref, minlength=hmax) / nv_ref
+    print(f"out-degree histogram TVD {0.5 * np.abs(ha - hb).sum():.4f}")
+    assert 0.5 * np.abs(ha - hb).sum() <= 0.06
+    assert abs(built["vrange"].mean() - pipe["vrange"].mean()) <= 0.03 * pipe["vrange"].mean()
+    # no two vertices closer than the vertex radius (what the first-come merge guarantees), every point merged
+    from scipy.spatial import cKDTree
+    pairs = cKDTree(built["pos"].astype(np.float64)).query_pairs(pipe["vertex_radius"] * 0.999)
+    assert len(pairs) == 0
+    assert built["efrom"].min() >= 0 and built["eto"].max() < nv
+    # the device-built graph through the rest of the pipeline: image means of the graph render, device-built vs
+    # reference-built graph, within 2 % at every bounce count
+    L0 = md.graph_light_vector(rd, built["pos"], vertex_radius=pipe["vertex_radius"], max_dist_to_center=pipe["max_dist_to_center"],
+                               light_iterations=CFG["light_iterations"], points_on_radius=CFG["points_on_radius"],
+                               sampling_resolution=pipe["sampling_resolution"], lam=pipe["lam"])
+    g = ctx.create_graph_from_edges(built["vsamples"], built["efrom"], built["eto"], built["esamples"])
+    gr = ctx.create_graph_from_edges(pipe["vsamples"], pipe["efrom"], pipe["eto"], pipe["esamples"])
+    for k, b in enumerate(BOUNCES):
+        tot, _ = g.compute_final_light(L0, int(b))
+        g.set_vertices(built["pos"], tot, built["vrange"], pipe["vertex_radius"])
+        gr.set_vertices(pipe["pos"], pipe["totals"][k], pipe["vrange"], pipe["vertex_radius"])
+        fa, _ = ctx.render_graph(md, g, rd); fb, _ = ctx.render_graph(md, gr, rd)
+        ma = fa[..., :3].sum() / fa[..., 3].sum(); mb = fb[..., :3].sum() / fb[..., 3].sum()
+        print(f"bounces {b}: graph render mean, device-built {ma:.6f} vs reference-built {mb:.6f} ({(ma / mb - 1) * 100:+.2f} %)")
+        assert abs(ma - mb) <= 0.02 * mb, (b, ma, mb)
+    g.close(); gr.close(); md.close()
+
+
 def test_light_vector_edge_cases(ctx):
     from acceleratedvolrenderer_b200.api import AvrError
     dens = scenes.fbm_density(16, 16, 16, seed=2)

@@ -91,8 +91,10 @@ AVR_DEV bool graph_search(const GraphView &g, V3 p, float r2, bool filter, float
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         float flo = floorf((pp[i] - r - g.gmin[i]) * g.inv_cell), fhi = floorf((pp[i] + r - g.gmin[i]) * g.inv_cell);
-        lo[i] = (int)fmaxf(flo, 0.f);
-        hi[i] = (int)fminf(fhi, float(g.gres[i] - 1));
+        // one cell wider on both sides than the rounded range: the exact d2 < r2 test below filters the extra
+        // candidates, and a vertex within an ulp of a cell face at distance ~r is never skipped
+        lo[i] = (int)fmaxf(flo - 1.f, 0.f);
+        hi[i] = (int)fminf(fhi + 1.f, float(g.gres[i] - 1));
         if (!(flo <= float(g.gres[i] - 1)) || !(fhi >= 0.f)) lo[i] = hi[i] + 1;  // outside the grid (or NaN)
     }
     float a = 0, w = 0;

@@ -138,6 +138,7 @@ extern "C" avr_status avr_graph_create_from_edges(avr_ctx *ctx, int32_t n, const
     A((void **)&g->d_cur, size_t(n) * 4);
     A((void **)&g->d_nxt, size_t(n) * 4);
     A((void **)&g->d_total, size_t(n) * 4);
+    A((void **)&g->d_l0, size_t(n) * 4);
     A((void **)&g->d_flag, 2 * 4);
     if (e != cudaSuccess) { avr_graph_destroy(g); return set_cuda_err(ctx, e, "avr_graph_create_from_edges alloc"); }
     if (nnz) k_fill_csr<<<blocks_for(nnz, 256), 256, 0, s>>>(d_ukeys, d_sums, d_vs, d_runs, g->d_col, g->d_val);

@@ -6,6 +6,8 @@
 // (precision 6, %g), "True"/"False" flags.
 #include <cerrno>
 #include <cstdio>
+#include <new>
+#include <stdexcept>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -29,6 +31,7 @@ struct Tokens {
         std::fseek(f, 0, SEEK_END);
         long n = std::ftell(f);
         std::fseek(f, 0, SEEK_SET);
+        if (n < 0) { std::fclose(f); return false; }  // not seekable
         buf.resize(size_t(n) + 1);
         size_t got = std::fread(buf.data(), 1, size_t(n), f);
         std::fclose(f);
@@ -51,8 +54,9 @@ struct Tokens {
         skip();
         if (p >= end) return false;
         char *q = nullptr;
+        errno = 0;
         long x = std::strtol(p, &q, 10);
-        if (q == p) return false;
+        if (q == p || errno == ERANGE || x < INT32_MIN || x > INT32_MAX) return false;
         *v = int32_t(x);
         p = q;
         return true;
@@ -91,72 +95,83 @@ extern "C" void avr_graph_file_free(avr_graph_file *g) {
 }
 
 extern "C" avr_status avr_graph_file_read(const char *path, avr_graph_file **out) {
-    if (!path || !out) return fail(AVR_ERR_BAD_ARG, "avr_graph_file_read: NULL argument");
-    *out = nullptr;
-    Tokens t;
-    if (!t.load(path)) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_file_read: cannot open ") + path);
-    std::string desc, name, flag[5];
-    float radius = -1;
-    // FreeGraph::ReadFromStream: in >> description >> name >> vertexRadius
-    if (!t.word(&desc) || !t.word(&name) || !t.f32(&radius))
-        return fail(AVR_ERR_BAD_ARG, "graph file: truncated header");
-    if (name != "free")
-        return fail(AVR_ERR_UNSUPPORTED, "graph file: only \"free\" graphs are on the path (got \"" + name + "\")");
-    for (int i = 0; i < 5; ++i)
-        if (!t.word(&flag[i])) return fail(AVR_ERR_BAD_ARG, "graph file: truncated flags line");
-    int32_t hdr[6];
-    for (int i = 0; i < 6; ++i)
-        if (!t.i32(&hdr[i])) return fail(AVR_ERR_BAD_ARG, "graph file: truncated counts line");
-    if (hdr[3] < 0 || hdr[4] < 0 || hdr[5] < 0) return fail(AVR_ERR_BAD_ARG, "graph file: negative count");
-    bool coors = flag[0] == "True", samples = flag[1] == "True", types = flag[2] == "True", light = flag[3] == "True",
-         range = flag[4] == "True";
-    size_t nv = size_t(hdr[3]), ne = size_t(hdr[4]), np = size_t(hdr[5]);
-    std::vector<int32_t> vid(nv), vtype, vsmp, vco, eid(ne), efrom(ne), eto(ne), esmp, pid(np), pverts;
-    std::vector<float> vpos(3 * nv), vlight, vrange;
-    std::vector<int64_t> poff(np + 1, 0);
-    if (types) vtype.resize(nv);
-    if (light) vlight.resize(nv);
-    if (samples) { vsmp.resize(nv); esmp.resize(ne); }
-    if (range) vrange.resize(nv);
-    if (coors) vco.resize(3 * nv);
-    bool ok = true;
-    for (size_t i = 0; i < nv && ok; ++i) {
-        ok = t.i32(&vid[i]) && t.f32(&vpos[3 * i]) && t.f32(&vpos[3 * i + 1]) && t.f32(&vpos[3 * i + 2]);
-        // ReadVertexData order: type, lightScalar, samples, renderSearchRange (graph.cpp:249-267)
-        if (ok && types) ok = t.i32(&vtype[i]);
-        if (ok && light) ok = t.f32(&vlight[i]);
-        if (ok && samples) ok = t.i32(&vsmp[i]);
-        if (ok && range) ok = t.f32(&vrange[i]);
-        if (ok && coors) ok = t.i32(&vco[3 * i]) && t.i32(&vco[3 * i + 1]) && t.i32(&vco[3 * i + 2]);
-    }
-    for (size_t i = 0; i < ne && ok; ++i) {
-        ok = t.i32(&eid[i]) && t.i32(&efrom[i]) && t.i32(&eto[i]);
-        if (ok && samples) ok = t.i32(&esmp[i]);
-    }
-    for (size_t i = 0; i < np && ok; ++i) {
-        int32_t len = 0;
-        ok = t.i32(&pid[i]) && t.i32(&len) && len >= 0;
-        for (int32_t j = 0; j < len && ok; ++j) {
-            int32_t v;
-            ok = t.i32(&v);
-            if (ok) pverts.push_back(v);
+    try {
+        if (!path || !out) return fail(AVR_ERR_BAD_ARG, "avr_graph_file_read: NULL argument");
+        *out = nullptr;
+        Tokens t;
+        if (!t.load(path)) return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_file_read: cannot open ") + path);
+        std::string desc, name, flag[5];
+        float radius = -1;
+        // FreeGraph::ReadFromStream: in >> description >> name >> vertexRadius
+        if (!t.word(&desc) || !t.word(&name) || !t.f32(&radius))
+            return fail(AVR_ERR_BAD_ARG, "graph file: truncated header");
+        if (name != "free")
+            return fail(AVR_ERR_UNSUPPORTED, "graph file: only \"free\" graphs are on the path (got \"" + name + "\")");
+        for (int i = 0; i < 5; ++i)
+            if (!t.word(&flag[i])) return fail(AVR_ERR_BAD_ARG, "graph file: truncated flags line");
+        int32_t hdr[6];
+        for (int i = 0; i < 6; ++i)
+            if (!t.i32(&hdr[i])) return fail(AVR_ERR_BAD_ARG, "graph file: truncated counts line");
+        if (hdr[3] < 0 || hdr[4] < 0 || hdr[5] < 0) return fail(AVR_ERR_BAD_ARG, "graph file: negative count");
+        bool coors = flag[0] == "True", samples = flag[1] == "True", types = flag[2] == "True", light = flag[3] == "True",
+             range = flag[4] == "True";
+        size_t nv = size_t(hdr[3]), ne = size_t(hdr[4]), np = size_t(hdr[5]);
+        // a record is at least "id x y z\n" / "id from to\n" / "id n\n": counts a file of this size cannot hold are a
+        // corrupt (or hostile) header, not a reason to allocate gigabytes
+        size_t file_bytes = size_t(t.end - t.buf.data());
+        if (nv > file_bytes / 8 || ne > file_bytes / 6 || np > file_bytes / 4)
+            return fail(AVR_ERR_BAD_ARG, "graph file: the header counts exceed what the file can hold");
+        std::vector<int32_t> vid(nv), vtype, vsmp, vco, eid(ne), efrom(ne), eto(ne), esmp, pid(np), pverts;
+        std::vector<float> vpos(3 * nv), vlight, vrange;
+        std::vector<int64_t> poff(np + 1, 0);
+        if (types) vtype.resize(nv);
+        if (light) vlight.resize(nv);
+        if (samples) { vsmp.resize(nv); esmp.resize(ne); }
+        if (range) vrange.resize(nv);
+        if (coors) vco.resize(3 * nv);
+        bool ok = true;
+        for (size_t i = 0; i < nv && ok; ++i) {
+            ok = t.i32(&vid[i]) && t.f32(&vpos[3 * i]) && t.f32(&vpos[3 * i + 1]) && t.f32(&vpos[3 * i + 2]);
+            // ReadVertexData order: type, lightScalar, samples, renderSearchRange (graph.cpp:249-267)
+            if (ok && types) ok = t.i32(&vtype[i]);
+            if (ok && light) ok = t.f32(&vlight[i]);
+            if (ok && samples) ok = t.i32(&vsmp[i]);
+            if (ok && range) ok = t.f32(&vrange[i]);
+            if (ok && coors) ok = t.i32(&vco[3 * i]) && t.i32(&vco[3 * i + 1]) && t.i32(&vco[3 * i + 2]);
         }
-        poff[i + 1] = int64_t(pverts.size());
+        for (size_t i = 0; i < ne && ok; ++i) {
+            ok = t.i32(&eid[i]) && t.i32(&efrom[i]) && t.i32(&eto[i]);
+            if (ok && samples) ok = t.i32(&esmp[i]);
+        }
+        for (size_t i = 0; i < np && ok; ++i) {
+            int32_t len = 0;
+            ok = t.i32(&pid[i]) && t.i32(&len) && len >= 0;
+            for (int32_t j = 0; j < len && ok; ++j) {
+                int32_t v;
+                ok = t.i32(&v);
+                if (ok) pverts.push_back(v);
+            }
+            poff[i + 1] = int64_t(pverts.size());
+        }
+        if (!ok) return fail(AVR_ERR_BAD_ARG, "graph file: truncated or malformed record");
+        avr_graph_file *g = (avr_graph_file *)std::calloc(1, sizeof(avr_graph_file));
+        std::snprintf(g->description, sizeof(g->description), "%s", desc.c_str());
+        g->vertex_radius = radius;
+        g->use_coors = coors; g->use_samples = samples; g->use_ray_vertex_types = types; g->use_lighting = light;
+        g->use_render_search_range = range;
+        g->cur_vertex_id = hdr[0]; g->cur_edge_id = hdr[1]; g->cur_path_id = hdr[2];
+        g->n_vertices = hdr[3]; g->n_edges = hdr[4]; g->n_paths = hdr[5];
+        g->vertex_id = take(vid); g->vertex_pos = take(vpos); g->vertex_type = take(vtype); g->vertex_light = take(vlight);
+        g->vertex_samples = take(vsmp); g->vertex_range = take(vrange); g->vertex_coors = take(vco);
+        g->edge_id = take(eid); g->edge_from = take(efrom); g->edge_to = take(eto); g->edge_samples = take(esmp);
+        g->path_id = take(pid); g->path_offset = take(poff); g->path_vertices = take(pverts);
+        *out = g;
+        return AVR_OK;
+    } catch (const std::bad_alloc &) {
+        return fail(AVR_ERR_OOM, "avr_graph_file_read: out of memory");
+    } catch (const std::exception &e) {
+        return fail(AVR_ERR_BAD_ARG, std::string("avr_graph_file_read: ") + e.what());
     }
-    if (!ok) return fail(AVR_ERR_BAD_ARG, "graph file: truncated or malformed record");
-    avr_graph_file *g = (avr_graph_file *)std::calloc(1, sizeof(avr_graph_file));
-    std::snprintf(g->description, sizeof(g->description), "%s", desc.c_str());
-    g->vertex_radius = radius;
-    g->use_coors = coors; g->use_samples = samples; g->use_ray_vertex_types = types; g->use_lighting = light;
-    g->use_render_search_range = range;
-    g->cur_vertex_id = hdr[0]; g->cur_edge_id = hdr[1]; g->cur_path_id = hdr[2];
-    g->n_vertices = hdr[3]; g->n_edges = hdr[4]; g->n_paths = hdr[5];
-    g->vertex_id = take(vid); g->vertex_pos = take(vpos); g->vertex_type = take(vtype); g->vertex_light = take(vlight);
-    g->vertex_samples = take(vsmp); g->vertex_range = take(vrange); g->vertex_coors = take(vco);
-    g->edge_id = take(eid); g->edge_from = take(efrom); g->edge_to = take(eto); g->edge_samples = take(esmp);
-    g->path_id = take(pid); g->path_offset = take(poff); g->path_vertices = take(pverts);
-    *out = g;
-    return AVR_OK;
 }
 
 extern "C" avr_status avr_graph_file_write(const char *path, const avr_graph_file *g) {

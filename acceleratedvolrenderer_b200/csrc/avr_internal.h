@@ -8,8 +8,28 @@
 #include "../../include/avr.h"
 #include "avr_medium.cuh"
 
+// Scheduling knobs of the render kernels' path pool (avr_volpath.cu): they order the work, never change a
+// result.  Read ONCE from the environment when the context is created (AVR_WALK_STEPS, AVR_COLLIDE_MIN,
+// AVR_REFILL_LANES, AVR_TRACK_MIN, AVR_YIELD_LANES, AVR_YIELD_LANES_FULL, AVR_EVENT_SMSP_MASK, AVR_BLOCKS_PER_SM,
+// AVR_THREADS, AVR_POOL); a render call reads no environment variable.
+struct avr_knobs {
+    int walk_steps = 4, collide_min = 1, refill_lanes = 16, track_min = 32, yield_lanes = 8, yield_lanes_full = 20;
+    int event_smsp_mask = 12;
+    int blocks_per_sm = 0, threads = 0, pool = 0;  // 0 = the kernel variant's default
+};
+// What launch_render settled on for one kernel variant (function pointer): shared-memory opt-in done, occupancy
+// queried, pool sized — once per context, not per call.
+struct avr_launch_plan {
+    const void *fn = nullptr;
+    int threads = 0, pool = 0, per_sm = 0;
+    unsigned maj_bytes = 0;  // majorant grid staged in shared memory (0 = read through L1 / L2)
+    size_t smem = 0;
+};
+
 struct avr_ctx {
     int device = 0;
+    avr_knobs knobs;
+    std::vector<avr_launch_plan> plans;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
@@ -42,7 +62,7 @@ struct avr_graph {
     int64_t *d_rowptr = nullptr;
     int32_t *d_col = nullptr;
     float *d_val = nullptr;
-    float *d_cur = nullptr, *d_nxt = nullptr, *d_total = nullptr;
+    float *d_cur = nullptr, *d_nxt = nullptr, *d_total = nullptr, *d_l0 = nullptr;  // propagation vectors, allocated once
     int32_t *d_flag = nullptr;
     // vertices + uniform hash grid for ConnectToGraph
     float4 *d_vert = nullptr;     // x,y,z,lightScalar  (sorted by cell)

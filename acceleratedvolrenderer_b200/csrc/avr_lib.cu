@@ -1,6 +1,7 @@
 // avr_lib.cu — context, media (upload, majorant-grid build, octet packing) and the small query
 // kernels behind include/avr.h.  sm_100a only; no CPU fallback: without a CUDA device every entry
 // point fails with AVR_ERR_CUDA.
+#include <cstdlib>
 #include <cuda_fp16.h>
 
 #include <cmath>
@@ -45,6 +46,25 @@ extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
     if (device < 0 || device >= count) return set_err(nullptr, AVR_ERR_BAD_ARG, "avr_ctx_create: bad device index");
     avr_ctx *ctx = new avr_ctx();
     ctx->device = device;
+    {
+        auto env_int = [](const char *name, int def, int lo, int hi) {
+            const char *e = getenv(name);
+            if (!e || !*e) return def;
+            int v = atoi(e);
+            return v < lo ? lo : (v > hi ? hi : v);
+        };
+        avr_knobs &k = ctx->knobs;
+        k.walk_steps = env_int("AVR_WALK_STEPS", k.walk_steps, 1, 1 << 20);
+        k.collide_min = env_int("AVR_COLLIDE_MIN", k.collide_min, 1, 32);
+        k.refill_lanes = env_int("AVR_REFILL_LANES", k.refill_lanes, 1, 32);
+        k.track_min = env_int("AVR_TRACK_MIN", k.track_min, 1, 1 << 20);
+        k.yield_lanes = env_int("AVR_YIELD_LANES", k.yield_lanes, 0, 32);
+        k.yield_lanes_full = env_int("AVR_YIELD_LANES_FULL", k.yield_lanes_full, 0, 32);
+        k.event_smsp_mask = env_int("AVR_EVENT_SMSP_MASK", k.event_smsp_mask, 0, 15);
+        k.blocks_per_sm = env_int("AVR_BLOCKS_PER_SM", 0, 0, 8);
+        k.threads = env_int("AVR_THREADS", 0, 0, 1024);
+        k.pool = env_int("AVR_POOL", 0, 0, 4096);
+    }
     AVR_CUDA(nullptr, cudaSetDevice(device));
     cudaDeviceProp prop;
     AVR_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));

@@ -140,6 +140,19 @@ def sidecar_case(orc, n=1500, ne=7000):
                         search_range=r["vrange"]), T
 
 
+def test_reader_survives_hostile_headers(tmp_path):
+    """Header counts a file of that size cannot hold, overflowing integers: an error status, never an allocation of
+    gigabytes or an exception through the C boundary (the library never aborts the host)."""
+    for counts in ("0 0 0 2000000000 0 0", "0 0 0 3 2000000000 0", "0 0 0 3 0 2000000000", "0 0 0 99999999999999999999 0 0"):
+        p = tmp_path / "bad.txt"
+        p.write_text(f"basic\nfree 0.1\nFalse False False False False\n{counts}\n0 0 0 0\n1 1 1 1\n2 2 2 2\n")
+        with pytest.raises(AvrError):
+            GraphFile.read(p)
+    ok = tmp_path / "ok.txt"
+    ok.write_text("basic\nfree 0.1\nFalse False False False False\n3 0 0 3 0 0\n0 0 0 0\n1 1 1 1\n2 2 2 2\n")
+    assert GraphFile.read(ok).vertex_pos.shape == (3, 3)
+
+
 def test_sidecar_round_trip_is_bit_exact(orc, tmp_path):
     from acceleratedvolrenderer_b200.api import GraphSidecar
     sc, T = sidecar_case(orc)

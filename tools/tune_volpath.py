@@ -33,17 +33,18 @@ def main():
     w = bench.WORKLOADS[args.workload]
     dev = torch.device("cuda", 0)
     density = bench.make_density(w, dev)
-    ctx = Context(0)
     W, H = w["width"], w["height"]
     film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
     for layout in args.layouts.split(","):
         gd, rd = bench.make_scene(w, density, args.spp, 0)
-        med = ctx.create_medium("nanovdb", gd, layout=layout)
         names = [e.split("=", 1)[0] for e in args.env]
         lists = [e.split("=", 1)[1].split(";") for e in args.env]
         for exact, *vals in itertools.product(args.exact.split(","), *lists):
             for n, v in zip(names, vals):
                 os.environ[n] = v
+            # the library reads its knobs when a context is created: one context (and medium) per configuration
+            ctx = Context(0)
+            med = ctx.create_medium("nanovdb", gd, layout=layout)
             r = rd.with_(exact_math=int(exact), sampler=1 if args.sampler == "zsobol" else 0, randomize=2)
             best = None
             for i in range(args.reps + 1):
@@ -59,8 +60,8 @@ def main():
                               "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1),
                               "stats": {k: v for k, v in best.items() if k != "kernel_ms"}}),
                   flush=True)
-        med.close()
-    ctx.close()
+            med.close()
+            ctx.close()
 
 
 if __name__ == "__main__":

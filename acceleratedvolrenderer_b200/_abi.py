@@ -52,6 +52,14 @@ class avr_nanovdb_grid(C.Structure):
     ]
 
 
+class avr_nvdb_info(C.Structure):
+    _fields_ = [
+        ("grids_in_file", C.c_int32), ("codec", C.c_int32),
+        ("leaf_nodes", C.c_int32), ("lower_nodes", C.c_int32), ("upper_nodes", C.c_int32),
+        ("active_voxels", C.c_int64), ("grid_bytes", C.c_int64), ("grid_name", C.c_char * 64),
+    ]
+
+
 class avr_nanovdb_desc(C.Structure):
     _fields_ = [
         ("density", avr_nanovdb_grid), ("temperature", avr_nanovdb_grid),

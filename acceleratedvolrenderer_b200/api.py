@@ -31,8 +31,9 @@ _lib = None
 
 # every symbol include/avr.h declares (tests check that the .so exports all of them)
 ABI_SYMBOLS = [
-    "avr_ctx_create", "avr_ctx_destroy", "avr_last_error", "avr_version",
+    "avr_ctx_create", "avr_ctx_destroy", "avr_last_error", "avr_version", "avr_measure_read_bandwidth",
     "avr_medium_create_uniformgrid", "avr_medium_create_rgbgrid", "avr_medium_create_nanovdb", "avr_medium_destroy",
+    "avr_nvdb_read_grid", "avr_nvdb_free_grid", "avr_medium_create_nanovdb_file",
     "avr_medium_is_emissive", "avr_medium_bounds", "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
@@ -68,7 +69,7 @@ def load_library():
         fn = getattr(lib, name)
         if name not in ("avr_last_error", "avr_version", "avr_medium_bytes", "avr_ctx_destroy", "avr_medium_destroy",
                         "avr_graph_destroy", "avr_graph_file_free", "avr_graph_sidecar_free", "avr_comm_destroy",
-                        "avr_built_graph_free"):
+                        "avr_built_graph_free", "avr_nvdb_free_grid"):
             fn.restype = C.c_int
     lib.avr_ctx_destroy.restype = None
     lib.avr_medium_destroy.restype = None
@@ -79,6 +80,8 @@ def load_library():
     lib.avr_graph_sidecar_free.argtypes = [C.c_void_p]
     lib.avr_comm_destroy.restype = None
     lib.avr_built_graph_free.restype = None
+    lib.avr_nvdb_free_grid.restype = None
+    lib.avr_nvdb_free_grid.argtypes = [C.c_void_p]
     lib.avr_built_graph_free.argtypes = [C.c_void_p]
     lib.avr_comm_destroy.argtypes = [C.c_void_p]
     _lib = lib
@@ -91,6 +94,26 @@ def _f32(a):
 
 def _p(a, t=f32p):
     return a.ctypes.data_as(t)
+
+
+def read_nvdb_grid(path, grid_name=None):
+    """avr_nvdb_read_grid: (NanoVDBGrid or None when the file has no such grid, info dict).  Host only."""
+    from ._abi import avr_nanovdb_grid, avr_nvdb_info
+    lib = load_library()
+    g = avr_nanovdb_grid(); info = avr_nvdb_info()
+    st = lib.avr_nvdb_read_grid(str(path).encode(), grid_name.encode() if grid_name else None, C.byref(g), C.byref(info))
+    if st != 0:
+        raise AvrError(st, lib.avr_last_error(None).decode())
+    meta = {k: getattr(info, k) for k, _ in avr_nvdb_info._fields_}
+    meta["grid_name"] = info.grid_name.decode()
+    if not g.values:
+        return None, meta
+    dims = list(g.dims)
+    n = dims[0] * dims[1] * dims[2]
+    vals = np.ctypeslib.as_array(g.values, shape=(n,)).astype(np.float32, copy=True).reshape(dims[2], dims[1], dims[0])
+    grid = NanoVDBGrid(vals, list(g.index_min), list(g.inv_mat), list(g.vec), list(g.world_bbox))
+    lib.avr_nvdb_free_grid(C.byref(g))
+    return grid, meta
 
 
 class Context:
@@ -120,6 +143,12 @@ class Context:
     def __exit__(self, *a):
         self.close()
 
+    def measure_read_bandwidth(self, nbytes, iters=20):
+        """GB/s of a streaming read kernel over `nbytes` (64 MiB: the L2 peak; several GB: the HBM read peak)."""
+        out = C.c_float(0)
+        self.check(self.lib.avr_measure_read_bandwidth(self.h, C.c_int64(nbytes), C.c_int32(iters), C.byref(out)))
+        return float(out.value)
+
     # Medium::Create(name, params...) — media.cpp:667-689
     def create_medium(self, name, desc, layout="dense"):
         h = C.c_void_p()
@@ -138,6 +167,15 @@ class Context:
             # the reference: ErrorExit(loc, "%s: medium unknown.", name)
             raise AvrError(1, f"{name}: medium unknown.")
         return Medium(self, h, desc)
+
+    # MakeNamedMedium "nanovdb" "string filename" ...: NanoVDBMedium::Create from the file (media.cpp:628-665)
+    def create_medium_nanovdb_file(self, filename, params: NanoVDBDesc, gridname=None, temperaturename=None, layout="dense"):
+        h = C.c_void_p()
+        self.check(self.lib.avr_medium_create_nanovdb_file(self.h, str(filename).encode(),
+                                                           gridname.encode() if gridname else None,
+                                                           temperaturename.encode() if temperaturename else None,
+                                                           C.byref(params.c), C.c_int(LAYOUTS[layout]), C.byref(h)))
+        return Medium(self, h, params)
 
     # Integrator::Create("volpath") -> Render(): returns the film [H, W, 4] float64 (rgbSum, weightSum)
     def render_volpath(self, medium, rdesc: RenderDesc, film=None):

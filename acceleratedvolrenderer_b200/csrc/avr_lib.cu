@@ -94,6 +94,54 @@ extern "C" void avr_ctx_destroy(avr_ctx *ctx) {
     delete ctx;
 }
 
+// ---- read-bandwidth probe: the L2 / HBM denominators of the density-fetch roofline ---------------------------
+// "L2 peak to be measured with a 64 MiB-resident read kernel".  Every thread streams 128-bit
+// loads over a buffer of `bytes` (grid-stride, 8 loads in flight), `iters` passes; a buffer that fits the 126 MB L2
+// is served from it after the first pass, a larger one from HBM.
+__global__ void __launch_bounds__(256) k_read_stream(const uint4 *__restrict__ buf, size_t n16, int iters, unsigned *sink) {
+    unsigned acc = 0;
+    const size_t stride = size_t(gridDim.x) * blockDim.x;
+    for (int it = 0; it < iters; ++it) {
+        size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+        for (; i + 7 * stride < n16; i += 8 * stride) {
+            uint4 v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = __ldcg(buf + i + k * stride);  // L2 only: L1 must not serve the re-reads
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc ^= v[k].x ^ v[k].y ^ v[k].z ^ v[k].w;
+        }
+        for (; i < n16; i += stride) { uint4 v = __ldcg(buf + i); acc ^= v.x ^ v.y ^ v.z ^ v.w; }
+    }
+    if (acc == 0x9e3779b9u) *sink = acc;  // keeps the loads alive, practically never taken
+}
+
+extern "C" avr_status avr_measure_read_bandwidth(avr_ctx *ctx, int64_t bytes, int32_t iters, float *gb_per_s) {
+    if (!ctx || !gb_per_s) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_measure_read_bandwidth: NULL argument");
+    if (bytes < 4096 || iters < 1) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_measure_read_bandwidth: bytes >= 4096, iters >= 1");
+    AVR_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint4 *buf = nullptr;
+    unsigned *sink = nullptr;
+    size_t n16 = size_t(bytes) / 16;
+    AVR_CUDA(ctx, cudaMalloc(&buf, n16 * 16));
+    cudaError_t e = cudaMalloc(&sink, 4);
+    if (e == cudaSuccess) e = cudaMemsetAsync(buf, 1, n16 * 16, ctx->stream);
+    float ms = 0;
+    if (e == cudaSuccess) {
+        int blocks = ctx->sm_count * 8;
+        k_read_stream<<<blocks, 256, 0, ctx->stream>>>(buf, n16, 2, sink);  // warm-up: the buffer settles in L2
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        k_read_stream<<<blocks, 256, 0, ctx->stream>>>(buf, n16, iters, sink);
+        cudaEventRecord(ctx->ev1, ctx->stream);
+        e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    }
+    cudaFree(buf);
+    cudaFree(sink);
+    if (e != cudaSuccess) return set_cuda_err(ctx, e, "avr_measure_read_bandwidth");
+    *gb_per_s = float(double(n16) * 16 * iters / (double(ms) * 1e6));
+    return AVR_OK;
+}
+
 // ---- build kernels -----------------------------------------------------------------------------------
 // MajorantGrid construction, media.cpp:240-246 (GridMedium) / :364-377 (RGBGridMedium):
 // one CTA per majorant voxel, max over the density voxels SampledGrid::MaxValue(bounds) visits

@@ -49,6 +49,11 @@ const char *avr_last_error(const avr_ctx *ctx);
 /* Library version / build string ("avr_b200 <n> sm_100a ..."). */
 const char *avr_version(void);
 
+/* Measurement aid (no counterpart in the reference): read bandwidth of a streaming 128-bit-load kernel over a
+ * buffer of `bytes`, `iters` passes after a warm-up pass — the L2 peak of the density-fetch roofline with a
+ * 64 MiB buffer (resident in the 126 MB L2), the HBM read peak with a multi-GB one. */
+avr_status avr_measure_read_bandwidth(avr_ctx *ctx, int64_t bytes, int32_t iters, float *gb_per_s);
+
 /* ---- media ---------------------------------------------------------------------------------- */
 /* HBM layouts for scalar grids.  All three give the same SampledGrid::Lookup tap values
  * (util/containers.h:804-835); the octet layouts store, per interpolation cell, its 8 corner taps
@@ -137,6 +142,27 @@ avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid_desc *desc
 avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_desc *desc, int layout,
                                      avr_medium **out);
 avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_desc *desc, avr_medium **out);
+
+/* ".nvdb" ingest: the file part of NanoVDBMedium::Create (media.cpp:628-665) and its readGrid (:487-509).
+ * avr_nvdb_read_grid finds the FloatGrid called `grid_name` (NULL or "" = the first grid) in a NanoVDB file
+ * (file-format major version 32, the one the reference vendors; codecs NONE and ZIP) and flattens it over its index
+ * bounding box — the result the fork's cmd/nanovdb2pbrt.cpp:100-110 gets from tree().getValue() per voxel, produced
+ * by one walk over the tree (leaves copied, value tiles filled).  grid->values is allocated by the library
+ * (avr_nvdb_free_grid); a file without that grid leaves grid->values == NULL and returns AVR_OK, as the reference's
+ * empty GridHandle.  Grids that are not fog volumes are refused with the reference's message.  Host code only. */
+typedef struct avr_nvdb_info {
+    int32_t grids_in_file, codec;
+    int32_t leaf_nodes, lower_nodes, upper_nodes;
+    int64_t active_voxels, grid_bytes;
+    char grid_name[64];
+} avr_nvdb_info;
+avr_status avr_nvdb_read_grid(const char *path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info /* or NULL */);
+void avr_nvdb_free_grid(avr_nanovdb_grid *grid);
+/* NanoVDBMedium::Create from the file: "filename", "gridname" (NULL = "density"), "temperaturename" (NULL =
+ * "temperature"; the grid may be absent); every other parameter comes from `params`, whose two grids are ignored. */
+avr_status avr_medium_create_nanovdb_file(avr_ctx *ctx, const char *filename, const char *gridname,
+                                          const char *temperaturename, const avr_nanovdb_desc *params, int layout,
+                                          avr_medium **out);
 void avr_medium_destroy(avr_medium *m);
 
 /* Medium::IsEmissive, media.h:284/374. */

@@ -19,7 +19,10 @@
 #include <pbrt/util/spectrum.h>
 #include <pbrt/util/transform.h>
 
+#define NANOVDB_USE_ZIP
 #include <nanovdb/util/GridBuilder.h>
+#include <nanovdb/util/IO.h>
+#include <fstream>
 
 #include <Eigen/Sparse>
 #include <graph/util.h>
@@ -264,6 +267,38 @@ void *ref_nanovdb_grid_build(const float *dense, const int32_t dims[3], const in
         voxel_size, nanovdb::Vec3d(origin_world[0], origin_world[1], origin_world[2]), "density", nanovdb::AbsDiff(),
         NanoVDBBuffer(Allocator()));
     return new NvHandle(std::move(h));
+}
+// the same with a grid name ("density" / "temperature": what NanoVDBMedium::Create looks up, media.cpp:636-645)
+void *ref_nanovdb_grid_build_named(const float *dense, const int32_t dims[3], const int32_t origin_ijk[3],
+                                   double voxel_size, const double origin_world[3], const char *name) {
+    nanovdb::GridBuilder<float> builder(0.f, nanovdb::GridClass::FogVolume);
+    nanovdb::CoordBBox box(nanovdb::Coord(origin_ijk[0], origin_ijk[1], origin_ijk[2]),
+                           nanovdb::Coord(origin_ijk[0] + dims[0] - 1, origin_ijk[1] + dims[1] - 1,
+                                          origin_ijk[2] + dims[2] - 1));
+    builder([&](const nanovdb::Coord &c) -> float {
+        int i = c[0] - origin_ijk[0], j = c[1] - origin_ijk[1], k = c[2] - origin_ijk[2];
+        return dense[(size_t(k) * dims[1] + j) * dims[0] + i];
+    }, box);
+    NvHandle h = builder.getHandle<nanovdb::AbsDiff, NanoVDBBuffer>(
+        voxel_size, nanovdb::Vec3d(origin_world[0], origin_world[1], origin_world[2]), name, nanovdb::AbsDiff(),
+        NanoVDBBuffer(Allocator()));
+    return new NvHandle(std::move(h));
+}
+// nanovdb::io::writeGrids of the reference's vendored NanoVDB: the .nvdb files the product's reader is tested on.
+// codec 0 = NONE, 1 = ZIP.  Returns 0 on success.
+int32_t ref_nanovdb_write_file(const char *path, void **handles, int32_t n, int32_t codec) {
+    try {
+        std::ofstream os(path, std::ios::out | std::ios::binary | std::ios::trunc);
+        if (!os.is_open()) return 1;
+        // writeGrids wants a vector of handles; write segment by segment instead (one grid each), which the file
+        // format allows (readGrid scans all segments)
+        for (int32_t i = 0; i < n; ++i)
+            nanovdb::io::writeGrid(os, *(NvHandle *)handles[i], codec == 1 ? nanovdb::io::Codec::ZIP : nanovdb::io::Codec::NONE);
+        return os ? 0 : 2;
+    } catch (const std::exception &e) {
+        std::fprintf(stderr, "refprobe: nanovdb write: %s\n", e.what());
+        return 3;
+    }
 }
 void ref_nanovdb_grid_free(void *h) { delete (NvHandle *)h; }
 // what the host adapter reads off the grid to fill avr_nanovdb_grid

@@ -204,6 +204,24 @@ class Checker:
         self.lib.ref_nanovdb_grid_free(h)
         return NanoVDBGrid(vals, imin, inv, vec, wb, source=py.source)
 
+    def write_nvdb(self, path, grids, codec=0):
+        """"ref" only: writes a .nvdb file with the reference's vendored nanovdb::io::writeGrid (one segment per grid).
+        grids: list of (name, dense [nz, ny, nx], origin_ijk, voxel_size, origin_world)."""
+        assert self.kind == "ref"
+        self.lib.ref_nanovdb_grid_build_named.restype = C.c_void_p
+        hs = []
+        for name, dense, origin_ijk, voxel_size, origin_world in grids:
+            d = f32(dense)
+            dims = np.array(d.shape[::-1], dtype=np.int32); org = np.array(origin_ijk, dtype=np.int32)
+            ow = np.array(origin_world, dtype=np.float64)
+            hs.append(C.c_void_p(self.lib.ref_nanovdb_grid_build_named(_p(d, f32p), _p(dims, i32p), _p(org, i32p),
+                                                                       C.c_double(voxel_size), _p(ow, f64p), name.encode())))
+        arr = (C.c_void_p * len(hs))(*hs)
+        rc = self.lib.ref_nanovdb_write_file(str(path).encode(), arr, C.c_int32(len(hs)), C.c_int32(codec))
+        for h in hs:
+            self.lib.ref_nanovdb_grid_free(h)
+        assert rc == 0, f"ref_nanovdb_write_file failed ({rc})"
+
     def medium_nanovdb(self, desc: NanoVDBDesc):
         if self.kind == "ref":
             dh = self._ref_grid_handle(desc.density.source)

@@ -1,0 +1,84 @@
+""".nvdb ingest: avr_nvdb_read_grid / avr_medium_create_nanovdb_file against files written by the
+REFERENCE's vendored nanovdb::io::writeGrid from grids built with its GridBuilder (oracle/refprobe.cpp), and against
+the flattening the reference's own tree().getValue() gives (Checker.nanovdb_grid).  Bit-exact: the reader moves
+floats, it computes nothing."""
+import numpy as np
+import pytest
+
+from acceleratedvolrenderer_b200 import scenes
+from acceleratedvolrenderer_b200.api import AvrError, read_nvdb_grid
+
+
+def sparse_cloud(shape=(70, 50, 90), seed=5):
+    """A grid with empty 8^3 leaves, constant regions (tiles after pruning) and a negative index origin."""
+    d = scenes.fbm_density(shape[2], shape[1], shape[0], seed=seed)
+    d[d < 0.15] = 0
+    d[10:26, 8:24, 16:32] = 0.75        # a constant block spanning whole leaves
+    return d
+
+
+@pytest.mark.parametrize("codec", [0, 1])
+def test_reader_matches_the_reference_flattening(ref, tmp_path, codec):
+    dens = sparse_cloud()
+    temp = (dens * 900 + 100).astype(np.float32) * (dens > 0.3)
+    origin_ijk, vs, ow = (-13, 5, -40), 0.0125, (0.25, -0.5, 1.0)
+    path = tmp_path / "cloud.nvdb"
+    ref.write_nvdb(path, [("density", dens, origin_ijk, vs, ow), ("temperature", temp, origin_ijk, vs, ow)], codec=codec)
+    for name, arr in (("density", dens), ("temperature", temp)):
+        got, info = read_nvdb_grid(path, name)
+        want = ref.nanovdb_grid(arr, origin_ijk, vs, ow)       # the reference's grid read back voxel by voxel
+        assert info["grids_in_file"] == 2 and info["grid_name"] == name and info["codec"] == codec
+        assert info["leaf_nodes"] > 0 and info["active_voxels"] == int((arr != 0).sum())
+        assert list(got.index_min) == list(want.index_min) and list(got.dims) == list(want.dims)
+        assert np.array_equal(got.values.view(np.uint32), want.values.view(np.uint32))
+        assert np.array_equal(got.inv_mat, want.inv_mat) and np.array_equal(got.vec, want.vec)
+        assert np.array_equal(got.world_bbox, want.world_bbox)
+    # the first grid when no name is given; a name the file does not hold is "absent", not an error (media.cpp:641-645)
+    first, info = read_nvdb_grid(path, None)
+    assert info["grid_name"] == "density" and first is not None
+    none, info = read_nvdb_grid(path, "velocity")
+    assert none is None and info["grids_in_file"] == 2
+
+
+def test_reader_error_behaviour(tmp_path):
+    with pytest.raises(AvrError) as e:
+        read_nvdb_grid(tmp_path / "missing.nvdb", "density")
+    assert "Unable to open file" in str(e.value)
+    junk = tmp_path / "junk.nvdb"
+    junk.write_bytes(b"not a nanovdb file at all" * 10)
+    with pytest.raises(AvrError) as e:
+        read_nvdb_grid(junk, "density")
+    assert "not a valid nvdb file" in str(e.value)            # the reference's message (IO.h Segment::read)
+    # a truncated file
+    good = tmp_path / "t.nvdb"
+    good.write_bytes(b"NanoVDB0" + (32 << 21 | 3 << 10 | 3).to_bytes(4, "little") + (1).to_bytes(2, "little") + b"\0\0" + b"\1" * 40)
+    with pytest.raises(AvrError):
+        read_nvdb_grid(good, "density")
+
+
+@pytest.mark.gpu
+def test_medium_from_file_is_the_medium_from_arrays(ctx, ref, tmp_path):
+    """MakeNamedMedium "nanovdb" "string filename": the medium built from the file equals the one built from the
+    flattened arrays — majorant grid, bounds and SamplePoint bit for bit, density and temperature grids both."""
+    dens = sparse_cloud((40, 36, 44), seed=9)
+    temp = (dens * 2500 + 200).astype(np.float32) * (dens > 0)
+    vs = 1.0 / 44
+    nd, rd = scenes.cloud_scene_nanovdb(dens, temperature=temp, voxel_size=vs, le_scale=0.4, width=16, height=12, spp=1,
+                                        sigma_t=11.0, albedo=0.9, g=0.3)
+    path = tmp_path / "m.nvdb"
+    ref.write_nvdb(path, [("density", dens, (0, 0, 0), vs, (0.0, 0.0, 0.0)), ("temperature", temp, (0, 0, 0), vs, (0.0, 0.0, 0.0))])
+    a = ctx.create_medium("nanovdb", nd, layout="octet32")
+    b = ctx.create_medium_nanovdb_file(path, nd, layout="octet32")
+    assert np.array_equal(a.majorants(), b.majorants())
+    assert np.array_equal(a.bounds(), b.bounds()) and a.is_emissive() == b.is_emissive()
+    rng = np.random.default_rng(2)
+    p = rng.uniform(-0.5, 0.5, (5000, 3)).astype(np.float32)
+    lam = np.array([420, 520, 610, 700], dtype=np.float32)
+    assert np.array_equal(a.sample_point(p, lam).view(np.uint32), b.sample_point(p, lam).view(np.uint32))
+    with pytest.raises(AvrError) as e:
+        ctx.create_medium_nanovdb_file(path, nd, gridname="smoke")
+    assert 'didn\'t find "density" grid' in str(e.value)       # media.cpp:637-638
+    with pytest.raises(AvrError) as e:
+        ctx.create_medium_nanovdb_file("", nd)
+    assert 'Must supply "filename"' in str(e.value)            # media.cpp:632-633
+    a.close(); b.close()

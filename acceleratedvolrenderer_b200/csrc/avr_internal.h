@@ -16,6 +16,9 @@ struct avr_knobs {
     int walk_steps = 4, collide_min = 1, refill_lanes = 16, track_min = 32, yield_lanes = 8, yield_lanes_full = 20;
     int event_smsp_mask = 12;
     int blocks_per_sm = 0, threads = 0, pool = 0;  // 0 = the kernel variant's default
+    // FAST majorant grid of a medium created under this context: c x c x c reference cells per FAST cell
+    // (AVR_FAST_MAJ_COARSEN; 1 = the reference's grid)
+    int fast_maj_coarsen = 2;
 };
 // What launch_render settled on for one kernel variant (function pointer): shared-memory opt-in done, occupancy
 // queried, pool sized — once per context, not per call.

@@ -64,6 +64,7 @@ extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
         k.blocks_per_sm = env_int("AVR_BLOCKS_PER_SM", 0, 0, 8);
         k.threads = env_int("AVR_THREADS", 0, 0, 1024);
         k.pool = env_int("AVR_POOL", 0, 0, 4096);
+        k.fast_maj_coarsen = env_int("AVR_FAST_MAJ_COARSEN", k.fast_maj_coarsen, 1, 16);
     }
     AVR_CUDA(nullptr, cudaSetDevice(device));
     cudaDeviceProp prop;
@@ -411,23 +412,47 @@ avr_status finish_majorants(avr_medium *m) {
         v.nz_lo[i] = lo[i];
         v.nz_hi[i] = hi[i];
     }
-    // FAST kernels: majorants with the empty-space distance field folded in
-    float *mf = nullptr;
+    // FAST kernels: their own majorant grid — c x c x c reference cells per cell (max), with the empty-space
+    // distance field folded in
+    const int c = m->ctx->knobs.fast_maj_coarsen;
+    int fr[3];
+    for (int i = 0; i < 3; ++i) {
+        fr[i] = (v.mres[i] + c - 1) / c;
+        v.fmres[i] = fr[i];
+        v.fcell[i] = v.cell[i] * float(c);
+        v.finv_cell[i] = v.fcell[i] > 0 ? 1.f / v.fcell[i] : 0.f;
+        v.fnz_lo[i] = hi[i] < lo[i] ? 0 : lo[i] / c;
+        v.fnz_hi[i] = hi[i] < lo[i] ? -1 : hi[i] / c;
+    }
+    const size_t nf = size_t(fr[0]) * fr[1] * fr[2];
+    std::vector<float> hc(nf, 0.f);
+    for (int z = 0; z < v.mres[2]; ++z)
+        for (int y = 0; y < v.mres[1]; ++y)
+            for (int x = 0; x < v.mres[0]; ++x) {
+                float f = h[(size_t(z) * v.mres[1] + y) * v.mres[0] + x];
+                float &dst = hc[(size_t(z / c) * fr[1] + y / c) * fr[0] + x / c];
+                if (f != f) dst = f;                 // NaN stays visible
+                else if (!(dst != dst) && f > dst) dst = f;
+            }
+    float *mf = nullptr, *mc = nullptr;
     unsigned char *d0 = nullptr, *d1 = nullptr;
-    AVR_CUDA(m->ctx, cudaMalloc(&mf, nm * sizeof(float)));
+    AVR_CUDA(m->ctx, cudaMalloc(&mf, nf * sizeof(float)));
     m->allocs.push_back(mf);
-    m->bytes += int64_t(nm * sizeof(float));
-    AVR_CUDA(m->ctx, cudaMalloc(&d0, nm));
-    cudaError_t e = cudaMalloc(&d1, nm);
-    if (e != cudaSuccess) { cudaFree(d0); return set_cuda_err(m->ctx, e, "cudaMalloc(distance field)"); }
-    int nb = int((nm + 255) / 256), rx = v.mres[0], ry = v.mres[1], rz = v.mres[2];
+    m->bytes += int64_t(nf * sizeof(float));
+    AVR_CUDA(m->ctx, cudaMalloc(&mc, nf * sizeof(float)));
+    cudaError_t e = cudaMalloc(&d0, nf);
+    if (e == cudaSuccess) e = cudaMalloc(&d1, nf);
+    if (e != cudaSuccess) { cudaFree(mc); cudaFree(d0); return set_cuda_err(m->ctx, e, "cudaMalloc(distance field)"); }
+    int nb = int((nf + 255) / 256), rx = fr[0], ry = fr[1], rz = fr[2];
     cudaStream_t s = m->ctx->stream;
-    k_empty_dist_x<<<nb, 256, 0, s>>>(m->d_maj, rx, ry, rz, d0);
-    k_empty_dist_next<<<nb, 256, 0, s>>>(d0, int(nm), rx, ry, d1);
-    k_empty_dist_next<<<nb, 256, 0, s>>>(d1, int(nm), rx * ry, rz, d0);
-    k_maj_fast<<<nb, 256, 0, s>>>(m->d_maj, d0, int(nm), mf);
-    e = cudaGetLastError();
+    e = cudaMemcpyAsync(mc, hc.data(), nf * sizeof(float), cudaMemcpyHostToDevice, s);
+    k_empty_dist_x<<<nb, 256, 0, s>>>(mc, rx, ry, rz, d0);
+    k_empty_dist_next<<<nb, 256, 0, s>>>(d0, int(nf), rx, ry, d1);
+    k_empty_dist_next<<<nb, 256, 0, s>>>(d1, int(nf), rx * ry, rz, d0);
+    k_maj_fast<<<nb, 256, 0, s>>>(mc, d0, int(nf), mf);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(mc);
     cudaFree(d0);
     cudaFree(d1);
     if (e != cudaSuccess) return set_cuda_err(m->ctx, e, "empty-space distance field");

@@ -373,15 +373,36 @@ AVR_DEV V3 sample_hg(V3 wo, float g, float u0, float u1, float *pdf) {
 }
 
 // util/sampling.h:163-171 + util/spectrum.h:334-346: SampledWavelengths::SampleVisible
+// One wavelength at a time through NON-inlined helpers: atanhf / coshf are a few hundred instructions each, and
+// four inlined copies of both in the once-per-path code evict the tracking loop from the 32 KB instruction cache.
+// FAST: the same functions through lg2 / ex2.
+template <bool EXACT>
+static __device__ __noinline__ float visible_wavelength(float up) {
+    float x = 0.85691062f - 1.82750197f * up;
+    if (EXACT) return 538 - 138.888889f * atanhf(x);
+    return 538 - 138.888889f * (0.5f * 0.6931471805599453f) * ftz_lg2(__fdividef(1 + x, 1 - x));
+}
+template <bool EXACT>
+static __device__ __noinline__ float visible_wavelength_pdf(float l) {
+    if (l < 360 || l > 830) return 0.f;
+    float y = 0.0072f * (l - 538);
+    float c = EXACT ? coshf(y) : 0.5f * (ftz_ex2(y * 1.4426950408889634f) + ftz_ex2(-y * 1.4426950408889634f));
+    return 0.0039398042f / sqr(c);
+}
+template <bool EXACT = true>
+AVR_DEV void visible_wavelengths_pdf(const float lambda[4], float pdf[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) pdf[i] = visible_wavelength_pdf<EXACT>(lambda[i]);
+}
+template <bool EXACT = true>
 AVR_DEV void sample_visible_wavelengths(float u, float lambda[4], float pdf[4]) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         float up = u + float(i) / 4;
         if (up > 1) up -= 1;
-        float l = 538 - 138.888889f * atanhf(0.85691062f - 1.82750197f * up);
-        lambda[i] = l;
-        pdf[i] = (l < 360 || l > 830) ? 0.f : 0.0039398042f / sqr(coshf(0.0072f * (l - 538)));
+        lambda[i] = visible_wavelength<EXACT>(up);
     }
+    visible_wavelengths_pdf<EXACT>(lambda, pdf);
 }
 // DenselySampledSpectrum::Sample, util/spectrum.h:390-399 (std::lround: half away from zero)
 AVR_DEV float sample_dense1(const float *tab, float lambda) {

@@ -38,6 +38,13 @@ struct MediumView {
     // distance in cells to the nearest non-empty cell (cells closer than d are all empty: the walk leaps to
     // the face of that cube, DDA::leap); non-empty cells hold their majorant
     const float *maj_fast;
+    // The FAST grid may also be COARSER than the reference's (any grid of upper bounds of the density is a valid
+    // majorant: the estimator stays unbiased, only the split between DDA steps and null collisions moves): cell
+    // (i, j, k) of the FAST grid is the max over a c x c x c block of reference cells.  Its own resolution, cell
+    // size and non-empty box:
+    int fmres[3];
+    float fcell[3], finv_cell[3];
+    int fnz_lo[3], fnz_hi[3];
     float ach_sig_a, ach_sig_s;  // achromatic media: the constant sigma_a / sigma_s (already * "scale")
     // FAST path: sample coordinates straight from render space, s = gfr * p + gfr[.][3]  (s = p_grid*n - .5)
     float gfr[12];
@@ -396,15 +403,17 @@ struct DDA {
 
     AVR_DEV void invalidate() { tMin = __int_as_float(0x7f800000); tMax = __int_as_float(0xff800000); }
     // finish init from per-axis voxel / direction sign; returns false if no voxel can be visited
-    template <bool TRIM>
+    // F: the walk runs over the FAST majorant grid (MediumView::maj_fast, fmres ...) instead of the reference's
+    template <bool TRIM, bool F = false>
     AVR_DEV bool set_voxels(const MediumView &mv, const int vx[3], const bool pos[3]) {
-        lin = vx[0] + mv.mres[0] * (vx[1] + mv.mres[1] * vx[2]);
+        const int *mres = F ? mv.fmres : mv.mres, *nz_hi = F ? mv.fnz_hi : mv.nz_hi, *nz_lo = F ? mv.fnz_lo : mv.nz_lo;
+        lin = vx[0] + mres[0] * (vx[1] + mres[1] * vx[2]);
         rem = 0;
         bool ok = true;
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-            int hi = TRIM ? mv.nz_hi[a] + 1 : mv.mres[a];  // leaving towards + when voxel == hi
-            int lo = TRIM ? mv.nz_lo[a] - 1 : -1;          // leaving towards - when voxel == lo
+            int hi = TRIM ? nz_hi[a] + 1 : mres[a];  // leaving towards + when voxel == hi
+            int lo = TRIM ? nz_lo[a] - 1 : -1;       // leaving towards - when voxel == lo
             int r = pos[a] ? hi - vx[a] : vx[a] - lo;
             ok = ok && r > 0;
             rem |= (unsigned)(r & 1023) << (10 * a);
@@ -453,20 +462,20 @@ struct DDA {
         bool pos[3];
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-            int r = mv.mres[a];
+            int r = mv.fmres[a];
             float p = __fmaf_rn(comp(d, a), tMin, comp(o, a)) - mv.bmin[a];
-            int v = (int)(p * mv.inv_cell[a]);
+            int v = (int)(p * mv.finv_cell[a]);
             v = v < 0 ? 0 : (v > r - 1 ? r - 1 : v);
             vx[a] = v;
             float id = comp(inv_d, a);
             pos[a] = !(comp(d, a) < 0);
-            float edge = mv.bmin[a] + float(pos[a] ? v + 1 : v) * mv.cell[a];
+            float edge = mv.bmin[a] + float(pos[a] ? v + 1 : v) * mv.fcell[a];
             nct[a] = (edge - comp(o, a)) * id;
             if (comp(d, a) == 0) nct[a] = __int_as_float(0x7f800000);
-            float dT = fminf(fabsf(id) * mv.cell[a], 1e30f);  // finite: leap() multiplies it by a cell count
+            float dT = fminf(fabsf(id) * mv.fcell[a], 1e30f);  // finite: leap() multiplies it by a cell count
             dTs[a] = pos[a] ? dT : -dT;
         }
-        if (!set_voxels<TRIM>(mv, vx, pos)) invalidate();
+        if (!set_voxels<TRIM, true>(mv, vx, pos)) invalidate();
     }
     // FAST variant only.  The current voxel and every voxel at Chebyshev distance < d (d >= 2) are empty
     // (sigma_maj = 0: nothing can happen there): advance straight to the first crossing that leaves that
@@ -487,7 +496,7 @@ struct DDA {
         if (!(T < tMax)) { tMin = tMax; return; }  // the ray ends inside the cube
         bool e0 = tb[0] <= tb[1] && tb[0] <= tb[2], e1 = !e0 && tb[1] <= tb[2];
         bool ex[3] = {e0, e1, !e0 && !e1};
-        int stride[3] = {1, mv.mres[0], mv.mres[0] * mv.mres[1]};
+        int stride[3] = {1, mv.fmres[0], mv.fmres[0] * mv.fmres[1]};
         bool out = false;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
@@ -504,7 +513,9 @@ struct DDA {
         tMin = out ? tMax : T;  // left the (trimmed) grid: every voxel beyond is empty
     }
     // Returns false when the iterator is exhausted.  *vox = linear voxel index of the segment.
+    template <bool F = false>
     AVR_DEV bool next(const MediumView &mv, float *segMin, float *segMax, int *vox) {
+        const int *mres = F ? mv.fmres : mv.mres;
         if (tMin >= tMax) return false;
         // stepAxis = cmpToAxis[bits], cmpToAxis = {2,1,2,1,2,2,0,0}: 0 iff c01 & c02, 1 iff !c01 & c12
         bool c01 = nct[0] < nct[1], c02 = nct[0] < nct[2], c12 = nct[1] < nct[2];
@@ -516,7 +527,7 @@ struct DDA {
         *segMin = tMin;
         *segMax = tVoxelExit;
         tMin = tVoxelExit;
-        int stride = p0 ? 1 : (p1 ? mv.mres[0] : mv.mres[0] * mv.mres[1]);
+        int stride = p0 ? 1 : (p1 ? mres[0] : mres[0] * mres[1]);
         lin += ds >= 0 ? stride : -stride;
         unsigned sh = p0 ? 0u : (p1 ? 10u : 20u);
         rem -= 1u << sh;

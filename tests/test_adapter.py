@@ -165,8 +165,8 @@ def test_adapter_fallback_rule_for_other_pixel_filters(ref):
 @pytest.mark.gpu
 def test_device_renders_through_the_adapter(ctx, ref):
     """Medium and render descriptors as the adapter fills them from the reference's objects, handed to the C ABI as they
-    are: the medium is the one scenes.py describes (majorants bit-equal), the film of the same samples agrees with
-    the scenes.py render to the camera matrices' 2e-6 (>= 99 % of pixels within 1e-3)."""
+    are: the medium is the one scenes.py describes (majorants bit-equal), the film is bit-equal to the
+    scenes.py render once both use the adapter's camera rays (the matrices differ by 2e-6 otherwise)."""
     from acceleratedvolrenderer_b200.api import Medium
     W, H, fov, eye = 40, 30, 20.0, (0.0, 0.35, -3.2)
     dens, (gd, rd) = _scene(width=W, height=H, fov=fov, eye=eye, spp=8)
@@ -183,9 +183,19 @@ def test_device_renders_through_the_adapter(ctx, ref):
     ctx.check(ctx.lib.avr_render_volpath(ctx.h, via.h, C.byref(d), film.ctypes.data_as(C.POINTER(C.c_double)), C.byref(stats)))
     want, _ = ctx.render_volpath(direct, rd)
     assert np.array_equal(film[..., 3], want[..., 3]) and film[..., 3].min() == 8
+    # The camera matrices and the light direction differ in the last bits (scenes.py composes them in float64, pbrt in
+    # fp32), and delta tracking amplifies a last-bit change of a ray into a different path wherever a comparison
+    # flips, so per-pixel agreement of 8 samples is not a meaningful bar.  What IS exact: give the scenes.py
+    # descriptor the adapter's rays and every other field must already be equivalent -- the films are bit-equal.
+    for name in ("camera_from_raster", "render_from_camera", "light_dir"):
+        src, dst = getattr(d, name), getattr(rd.c, name)
+        for i in range(len(src)):
+            dst[i] = src[i]
+    same_rays, _ = ctx.render_volpath(direct, rd)
+    assert np.array_equal(film, same_rays)
+    # and the two renders of the unmodified descriptors are the same image statistically
     a, b = film[..., :3].sum(axis=2), want[..., :3].sum(axis=2)
-    ok = np.abs(a - b) <= 1e-3 * np.maximum(b, 1e-3 * b.max())
-    assert ok.mean() >= 0.99, ok.mean()
+    assert abs(a.mean() / b.mean() - 1) < 0.02, (a.mean(), b.mean())
     ref.lib.ref_adapter_free_render(hr)
     ref.lib.ref_adapter_free_medium(hm, C.c_int32(kind))
     via.close(); direct.close(); mo.close()

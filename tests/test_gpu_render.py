@@ -297,8 +297,8 @@ def test_full_size_properties(ctx):
     1280x720, depth 100), where the CPU oracle would take hours: size-independent properties instead.
     (1) every pixel sample is accounted for (weightSum == spp everywhere, camera_rays == W*H*spp);
     (2) sample shards add up to the whole render to 1e-12 (the multi-GPU contract); (3) so do rank partitions;
-    (4) FAST and EXACT arithmetic are the same estimator: image means within 1.5 %, density fetches per sample
-    within 1 %; (5) energy: with a black light and no emission the film is exactly zero."""
+    (4) FAST and EXACT arithmetic are the same estimator: image means within 4 sigma, density fetches per sample
+    of FAST within [1, 1.3] of EXACT's (coarser majorant grid); (5) energy: with a black light and no emission the film is exactly zero."""
     import os
     import sys
     import torch
@@ -340,7 +340,10 @@ def test_full_size_properties(ctx):
     assert abs(z) < MEAN_Z_BAR, (z, rel_se)
     assert rel_se < 2e-3, rel_se   # 2 x 177 M samples: the test resolves a relative FAST bias of 0.8 % at 4 sigma
     f_fast = st["camera_fetches"] + st["shadow_fetches"]; f_exact = ste["camera_fetches"] + ste["shadow_fetches"]
-    assert abs(f_fast - f_exact) <= 0.01 * f_exact, (f_fast, f_exact)
+    # FAST walks a majorant grid coarsened 2x per axis (max over 2^3 reference cells, avr_knobs.fast_maj_coarsen): a
+    # looser bound buys fewer DDA steps with more null collisions, so FAST fetches MORE than EXACT -- never fewer
+    # (the estimator is unbiased for any bound, which the z-test above checks) and, on this cloud, under +30 %
+    assert f_exact <= f_fast <= 1.30 * f_exact, (f_fast, f_exact)
     black = rd.with_()
     dark = np.zeros(len(rd.light_spectrum), dtype=np.float32)
     black.light_spectrum = dark
@@ -466,6 +469,23 @@ def test_volpath_matches_reference_integrator(ctx):
                 assert rel_mse(img, w1) <= 3 * rel_mse(w0, w1), (name, exact)
                 assert abs(img.mean() - w0.mean()) <= max(0.05 * w0.mean(), 3 * abs(w0.mean() - w1.mean())), (name, exact)
         md.close()
+
+
+def test_launch_plans_of_one_kernel_variant_coexist(ctx):
+    """A context caches one launch plan per (kernel variant, majorant bytes in shared memory).  Two media rendered by
+    the SAME variant with different shared-memory footprints (16^3 majorants staged in shared memory, 32^3 read
+    through L1) must keep working in any order: the dynamic-shared-memory opt-in is a property of the function, so a
+    second plan may not lower it under the first (regression: 'invalid argument' on the third render)."""
+    dens, (g16, rd) = small_scene(width=24, height=20, spp=2)
+    _, (g32, _) = small_scene(width=24, height=20, spp=2, majorant_res=(32, 32, 32))
+    m16 = ctx.create_medium("uniformgrid", g16, layout="octet32")
+    m32 = ctx.create_medium("uniformgrid", g32, layout="octet32")
+    films = []
+    for em in (1, 0):
+        for m in (m16, m32, m16, m32):
+            films.append(ctx.render_volpath(m, rd.with_(exact_math=em))[0])
+        assert np.array_equal(films[-4], films[-2]) and np.array_equal(films[-3], films[-1])
+    m16.close(); m32.close()
 
 
 def test_sample_sharding_is_additive(ctx):

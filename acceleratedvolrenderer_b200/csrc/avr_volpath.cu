@@ -184,23 +184,6 @@ AVR_DEV int pool_fill(const PoolView &pv, int qi) {
     return (int)(t - h);
 }
 
-// Push the slot ids of the lanes in `mask` (a subset of the converged lanes calling this) to queue qi.
-// The callers' slot stores and a __threadfence_block() must precede the call.
-AVR_DEV void pool_push(const PoolView &pv, int qi, unsigned mask, unsigned lane, int slot) {
-    if (mask == 0) return;
-    int leader = __ffs(mask) - 1;
-    unsigned pos0 = 0;
-    if ((int)lane == leader) pos0 = atomicAdd(&pv.q[qi].tail, (unsigned)__popc(mask));
-    pos0 = __shfl_sync(0xffffffffu, pos0, leader);
-    if (mask >> lane & 1u) {
-        unsigned pos = pos0 + __popc(mask & ((1u << lane) - 1));
-        unsigned cell = ((unsigned)qi << pv.cap_log2) + (pos & pv.cap_mask);
-        unsigned round = (pos >> pv.cap_log2) << 16;
-        while (pv.cells[cell] != (round | 0xffffu)) {}
-        pv.cells[cell] = round | (unsigned)slot;
-    }
-}
-
 // Pop up to popc(takers) slot ids from queue qi.  Returns n; the k-th taker lane (k < n) receives an
 // id in *slot.  All 32 lanes must call.  A __threadfence_block() must follow before the slots are read.
 AVR_DEV int pool_pop(const PoolView &pv, int qi, unsigned takers, unsigned lane, int *slot) {
@@ -392,9 +375,6 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 #ifndef AVR_LEAP_MIN
 #define AVR_LEAP_MIN 4  // FAST: smallest empty-cube radius (in cells) worth a DDA::leap instead of single steps
 #endif
-#ifndef AVR_WALK_CHECK
-#define AVR_WALK_CHECK 1  // 1: leave the walk phase as soon as no lane walks (every step); 2: test every other step; 0: first step only
-#endif
 #ifndef AVR_CTA_THREADS
 #define AVR_CTA_THREADS 512  // one 512-thread CTA per SM with one pool: 1.6 % faster than two of 256 (fuller batches)
 #endif
@@ -428,19 +408,29 @@ AVR_DEV void requeue(const PoolView &pv, unsigned lane, bool have, int slot, Pat
     if (have && ln.state != ST_RETIRED)
         SlotIO<TR>::template store<GROUPS>(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln, lc, pending);
     __threadfence_block();  // slot contents before the queue cells that publish them
-    unsigned m_tr = __ballot_sync(0xffffffffu, have && ln.state >= ST_WALK);
-    unsigned m_sc = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SCATTER);
-    unsigned m_se = __ballot_sync(0xffffffffu, have && ln.state == ST_EV_SHADOW_END);
-    unsigned m_dd = __ballot_sync(0xffffffffu, have && ln.state == ST_DEAD);
-    unsigned m_rt = __ballot_sync(0xffffffffu, have && ln.state == ST_RETIRED);
-    // ONE copy of the push code per call site, looped over the queues (the four unrolled copies cost
-    // instruction-cache footprint: 24.9 -> 24.1 ms FAST, 65.0 -> 57.4 ms EXACT per 8 spp)
-#pragma unroll 1
-    for (int qi = 0; qi < kNumQueues; ++qi) {
-        unsigned mq = qi == Q_TRACK ? m_tr : (qi == Q_SCATTER ? m_sc : (qi == Q_SHADOW_END ? m_se : m_dd));
-        pool_push(pv, qi, mq, lane, slot);
+    // queue the path of this lane goes to (4: none).  All queues are served by ONE shared-memory atomic
+    // instruction: the first lane of every group of lanes with the same target reserves the group's cells
+    // (four pool_push calls in a row cost four dependent atomic round trips per requeue)
+    int tq = 4;
+    if (have) {
+        const int s = ln.state;
+        tq = s >= ST_WALK ? Q_TRACK : (s == ST_EV_SCATTER ? Q_SCATTER : (s == ST_EV_SHADOW_END ? Q_SHADOW_END : (s == ST_DEAD ? Q_DEAD : 5)));
     }
-    if (m_rt && lane == 0) atomicSub((int *)pv.live, __popc(m_rt));
+    const unsigned peers = __match_any_sync(0xffffffffu, tq);
+    const int leader = __ffs(peers) - 1;
+    unsigned pos0 = 0;
+    if ((int)lane == leader) {
+        if (tq < 4) pos0 = atomicAdd(&pv.q[tq].tail, (unsigned)__popc(peers));
+        else if (tq == 5) atomicSub((int *)pv.live, __popc(peers));  // retired slots
+    }
+    pos0 = __shfl_sync(0xffffffffu, pos0, leader);
+    if (tq < 4) {
+        unsigned pos = pos0 + __popc(peers & ((1u << lane) - 1));
+        unsigned cell = ((unsigned)tq << pv.cap_log2) + (pos & pv.cap_mask);
+        unsigned round = (pos >> pv.cap_log2) << 16;
+        while (pv.cells[cell] != (round | 0xffffu)) {}
+        pv.cells[cell] = round | (unsigned)slot;
+    }
 }
 
 // One batch of an event op (R, E1 or E2, chosen warp-uniformly by the queue served), followed by the
@@ -723,15 +713,9 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
         // ---- A. DDA steps to the next majorant segment with sigma_maj[0] != 0, each followed by A': the
         //      draw of the next tentative-collision distance inside the current segment.  Leaving a
         //      segment without a collision costs no B op -----------------------------------------------
-        for (int k = 0; k < rp.walk_steps; ++k) {
-#if AVR_WALK_CHECK == 1
-            if (!__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
-#elif AVR_WALK_CHECK == 2
-            if ((k & 1) == 0 && !__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
-#else
-            if (k == 0 && !__any_sync(0xffffffffu, have && (ln.state == ST_WALK || ln.state == ST_SAMPLE))) break;
-#endif
-            if (!EX && have && ln.state == ST_WALK && ln.mj < -(AVR_LEAP_MIN - 0.5f)) {
+        // (a lane without a path is ST_DEAD, so the state alone tells whether it walks)
+        for (int k = 0; k < rp.walk_steps && __any_sync(0xffffffffu, (unsigned)(ln.state - ST_WALK) < 2u); ++k) {
+            if (!EX && ln.state == ST_WALK && ln.mj < -(AVR_LEAP_MIN - 0.5f)) {
                 // FAST: the walk stands inside an empty cube of the majorant grid (MediumView::maj_fast):
                 // one leap to the face of the cube instead of a step per cell
                 ln.dda.leap(mv, (int)(-ln.mj));
@@ -741,7 +725,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
 #endif
                 if (ln.dda.tMin < ln.dda.tMax) ln.mj = maj[ln.dda.lin];
                 else ln.state = ln.shadow ? ST_EV_SHADOW_END : ST_EV_PATH_END;
-            } else if (have && ln.state == ST_WALK) {
+            } else if (ln.state == ST_WALK) {
                 float a, b;
                 int vox;
                 if (!ln.dda.template next<!EX>(mv, &a, &b, &vox)) {
@@ -801,7 +785,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     }
                 }
             }
-            if (!EX && have && ln.state == ST_SAMPLE) {
+            if (!EX && ln.state == ST_SAMPLE) {
                 // FAST, after a null collision: fresh tau, tested against the rest of the current segment
                 float tau = neg_log1m(ln.trng.uniform());
                 float dtau = ln.sigma_maj[0] * (ln.seg_tMax - ln.cur_tMin);
@@ -817,7 +801,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     ln.u = tau - dtau;
                 ln.state = hit ? ST_COLLIDE : ST_WALK;
             }
-            if (EX && have && ln.state == ST_SAMPLE) {
+            if (EX && ln.state == ST_SAMPLE) {
                 // media.h:779-803: t = tMin + SampleExponential(u, sigma_maj[0]); u = rng.Uniform();
                 // T_maj *= FastExp(-(t - tMin) sigma_maj) at a collision, FastExp(-(tMax - tMin) sigma_maj) at the exit
                 float t = ln.cur_tMin + sample_exponential<EX>(ln.u, ln.sigma_maj[0]);
@@ -834,11 +818,11 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
         // ---- B. the tentative collision at t = cur_tMin (medium lookup, event, weight update): runs when
         //      enough lanes wait for it, or when no lane is left walking -------------------------------
         {
-            unsigned mc = __ballot_sync(0xffffffffu, have && ln.state == ST_COLLIDE);
+            unsigned mc = __ballot_sync(0xffffffffu, ln.state == ST_COLLIDE);
             if (mc == 0) continue;
-            if (__popc(mc) < rp.collide_min && __any_sync(0xffffffffu, have && ln.state == ST_WALK)) continue;
+            if (__popc(mc) < rp.collide_min && __any_sync(0xffffffffu, ln.state == ST_WALK)) continue;
         }
-        if (TR::LEAN && have && ln.state == ST_COLLIDE) {
+        if (TR::LEAN && ln.state == ST_COLLIDE) {
             // one channel, fast arithmetic: the event probabilities are all that is left of
             // cpu/integrators.cpp:990-1074 (camera) and :1352-1380 (shadow) — see Traits::LEAN
             const float t = ln.cur_tMin;
@@ -869,7 +853,7 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 ln.state = T != 0 ? ST_SAMPLE : ST_EV_SHADOW_END;
             }
         }
-        if (!TR::LEAN && have && ln.state == ST_COLLIDE) {
+        if (!TR::LEAN && ln.state == ST_COLLIDE) {
             {
                 const float t = ln.cur_tMin;
                 Spec<N> T_maj = ln.T_maj;

@@ -30,6 +30,11 @@ struct Traits {
     // exact ratio x / x = 1 (beta, r_u, r_l of the camera path, r_l of a shadow ray), so they are not carried
     // at all: analog delta tracking for the camera segments, plain ratio tracking for the shadow rays
     static constexpr bool LEAN = !EXACT_ && NCH_ == 1 && !GENERAL_;
+    // One event op per real scattering event: the NEE shadow ray AND the next camera segment are set up together
+    // (nothing the phase sampling draws or computes depends on the shadow ray's result: cpu/integrators.cpp:1041-1060
+    // follows :1037 SampleLd unconditionally), the tracking loop walks the shadow ray, adds its contribution and
+    // switches to the waiting camera ray by itself.  Halves the trips of a path through the pool's queues.
+    static constexpr bool FUSED = LEAN;
 };
 
 template <int NCH>

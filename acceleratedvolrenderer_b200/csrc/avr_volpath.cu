@@ -50,6 +50,10 @@ enum {
 template <typename TR>
 AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double *film, float *samples_out) {
     float L[4] = {ln.L[0], ln.L[1], ln.L[2], ln.L[3]};
+    if (TR::LEAN) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) L[i] = ln.Lsum * sample_dense1(rp.light_spec, ln.lambda[i]);
+    }
     bool bad = false;
 #pragma unroll
     for (int i = 0; i < 4; ++i) bad = bad || isnan(L[i]) || isinf(L[i]);
@@ -135,6 +139,9 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     ln.r_l = sconst<TR::NCH>(1.f);
     ln.depth = 0;
     ln.shadow = false;
+    ln.cam_wait = false;
+    ln.Lsum = 0.f;
+    ln.rr_k = 0;
     if (!TR::EXACT && !TR::ZSOBOL) {
         // FAST: one tracking stream per path (raw draws as PCG32 sequence / seed give correlated streams:
         // they go through the hash)
@@ -231,14 +238,17 @@ enum { GRP_A = 1, GRP_B = 2, GRP_C = 4, GRP_ALL = 7 };
 template <typename TR>
 struct SlotIO {
     static constexpr int N = TR::NCH;
-    static constexpr int kQuadsA = 6;
+    static constexpr int kQuadsA = TR::LEAN ? 4 : 6;
     // FAST kernels with the independent sampler seed the tracking RNG once per path (start_path) instead of
     // once per ray: it then belongs to the state every op touches (group B), not to the per-ray group C
     static constexpr bool kTrngInB = !TR::EXACT && !TR::ZSOBOL;
-    static constexpr int kWordsB = (TR::LEAN ? 7 : 4 + 10 * N) + (kTrngInB ? 4 : 0);
+    static constexpr int kWordsB = (TR::LEAN ? 8 : 4 + 10 * N) + (kTrngInB ? 4 : 0);
     static constexpr int kQuadsB = (kWordsB + 3) / 4;
     static constexpr int kQuadsC = kTrngInB ? 4 : 5;
-    static constexpr int kSlotQuads = (kQuadsA + kQuadsB + kQuadsC) | 1;  // odd: consecutive slots start in different bank groups
+    // Traits::FUSED: a second ray block (the camera ray that waits while the shadow ray is tracked)
+    static constexpr int kQuadsC2 = TR::FUSED ? kQuadsC : 0;
+    static constexpr int kOffC = kQuadsA + kQuadsB;
+    static constexpr int kSlotQuads = (kQuadsA + kQuadsB + kQuadsC + kQuadsC2) | 1;  // odd: consecutive slots start in different bank groups
     // groups the tracking loop needs besides B and C, and what it must write back when parking
     static constexpr int kTrackLoad = GRP_B | GRP_C | ((TR::EXACT || TR::GENERAL) ? GRP_A : 0);
     static constexpr int kTrackPark = GRP_B | (TR::GENERAL ? GRP_A : 0);
@@ -281,6 +291,13 @@ struct SlotIO {
         f(pxy); f(sm); f(lo); f(hi); f(lo2); f(hi2);
         ln.px = int(pxy & 0xffffu); ln.py = int(pxy >> 16); ln.samp = (int)sm;
         ln.srng.state = join64(lo, hi); ln.srng.inc = join64(lo2, hi2);
+        if (TR::LEAN) {
+            // the render-space camera ray (wo = -d; f_hat and the radiance sum live in group B)
+            f(ln.fe.o.x); f(ln.fe.o.y); f(ln.fe.o.z); f(ln.fe.d.x); f(ln.fe.d.y); f(ln.fe.d.z);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) f(ln.lambda[i]);
+            return;
+        }
         f(ln.wo.x); f(ln.wo.y); f(ln.wo.z); f(ln.f_hat);
         f(ln.fe.o.x); f(ln.fe.o.y); f(ln.fe.o.z); f(ln.fe.d.x); f(ln.fe.d.y); f(ln.fe.d.z);
 #pragma unroll
@@ -291,13 +308,17 @@ struct SlotIO {
     template <typename F>
     AVR_DEV static void visit_b(PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending, F &f) {
         unsigned fl = (unsigned)ln.state | ((unsigned)ln.shadow << 8) | ((unsigned)pending << 9) | ((unsigned)ln.depth << 16);
+        if (TR::FUSED) fl |= (unsigned)ln.cam_wait << 10;
+        if (TR::LEAN) fl |= (unsigned)min(ln.rr_k, 31) << 11;
         f(fl);
         ln.state = int(fl & 0xffu); ln.shadow = (fl >> 8) & 1u; pending = (fl >> 9) & 1u; ln.depth = int(fl >> 16);
+        if (TR::FUSED) ln.cam_wait = (fl >> 10) & 1u;
+        if (TR::LEAN) ln.rr_k = int((fl >> 11) & 31u);
         f(ln.cur_tMin); f(ln.seg_tMax); f(ln.u);
         if (kTrngInB) visit_rng(ln.trng, f);
         if (TR::LEAN) {
             // the medium's sigma_a / sigma_s are constants of the MediumView, the path weights are not carried
-            f(ln.T_ray.v[0]); f(ln.s_ru.v[0]); f(ln.sigma_maj.v[0]);
+            f(ln.T_ray.v[0]); f(ln.sigma_maj.v[0]); f(ln.f_hat); f(ln.Lsum);
             return;
         }
 #pragma unroll
@@ -332,7 +353,14 @@ struct SlotIO {
     AVR_DEV static void store(uint4 *sp, PathLane<TR> &ln, LambdaCtx<N> &lc, bool pending) {
         if (GROUPS & GRP_A) { Packer<kQuadsA> p; visit_a(ln, p); p.flush(sp); }
         if (GROUPS & GRP_B) { Packer<kQuadsB> p; visit_b(ln, lc, pending, p); p.flush(sp + kQuadsA); }
-        if (GROUPS & GRP_C) { Packer<kQuadsC> p; visit_c(ln, p); p.flush(sp + kQuadsA + kQuadsB); }
+        if (GROUPS & GRP_C) { Packer<kQuadsC> p; visit_c(ln, p); p.flush(sp + kOffC); }
+    }
+    // the ray block alone: `second` selects the waiting-ray block of Traits::FUSED
+    AVR_DEV static void store_ray(uint4 *sp, PathLane<TR> &ln, bool second) {
+        Packer<kQuadsC> p; visit_c(ln, p); p.flush(sp + kOffC + (second ? kQuadsC : 0));
+    }
+    AVR_DEV static void load_waiting_ray(const uint4 *sp, PathLane<TR> &ln) {
+        Unpacker<kQuadsC> u; u.fill(sp + kOffC + kQuadsC); visit_c(ln, u);
     }
     template <int GROUPS>
     AVR_DEV static void load(const uint4 *sp, const MediumView &mv, PathLane<TR> &ln, LambdaCtx<N> &lc, bool &pending) {
@@ -351,7 +379,7 @@ struct SlotIO {
             if (mv.kind == KIND_RGB) lc.sigma_t = sconst<N>(1.f);
             else lc.sigma_t = lc.sig_a + lc.sig_s;
         }
-        if (GROUPS & GRP_C) { Unpacker<kQuadsC> u; u.fill(sp + kQuadsA + kQuadsB); visit_c(ln, u); }
+        if (GROUPS & GRP_C) { Unpacker<kQuadsC> u; u.fill(sp + kOffC); visit_c(ln, u); }
     }
 };
 
@@ -446,6 +474,8 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
     __threadfence_block();
     bool have = (int)lane < n;
     bool pending = false;
+    bool sh_ray = false;        // Traits::FUSED: a shadow ray to set up (and track) before the pending camera ray
+    V3 sh_d = v3(0.f, 0.f, 0.f);
     if (have) SlotIO<TR>::template load<GRP_A | GRP_B>(pv.slots + slot * SlotIO<TR>::kSlotQuads, mv, ln, lc, pending);
 
     if (qi == Q_DEAD) {
@@ -467,7 +497,45 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             } else
                 ln.state = ST_RETIRED;
         }
-    } else if (qi == Q_SCATTER) {
+    } else if (TR::FUSED && qi == Q_SCATTER) {
+        // ---- E1 + E2 in one op (Traits::FUSED): SampleLd prologue (cpu/integrators.cpp:1300-1338) and the phase
+        //      sampling that follows SampleLd (:1041-1060).  Leaves the shadow ray in sh_d and the next camera
+        //      segment pending in fe.o / fe.d; the sampler draws keep the reference's order (light, then phase,
+        //      then the camera ray's three) --------------------------------------------------------------------
+        if (have) {
+            cn.sc++;
+            const V3 p = ln.fe.point(ln.cur_tMin);
+            const V3 wo = -ln.fe.d;
+            PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+            float ul0, ul1, ua, ub;
+            smp.get1d();            // light choice (single light, p = 1)
+            smp.get2d(&ul0, &ul1);  // uLight
+            const V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
+            const float two_r = 2 * rp.scene_radius;
+            bool lit = false;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) lit = lit || sample_dense1(rp.light_spec, ln.lambda[i]) != 0;
+            const float ph = hg_phase<TR::EXACT>(dot(wo, wi), mv.g);
+            sh_d = v3(wi.x * two_r, wi.y * two_r, wi.z * two_r);  // pLight - p
+            sh_ray = lit && ph != 0 && two_r != 0;
+            if (sh_ray) {
+                ln.f_hat = ph;
+                ln.T_ray = sconst<N>(1.f);
+                ln.rr_k = 0;
+            }
+            smp.get2d(&ua, &ub);
+            float pdf;
+            const V3 wi2 = sample_hg<TR::EXACT>(wo, mv.g, ua, ub, &pdf);
+            ln.fe.o = p;  // scatter point: origin of both rays
+            ln.cam_wait = false;
+            if (pdf == 0) {
+                ln.state = ST_EV_PATH_END;  // no camera continuation (the shadow ray may still contribute)
+            } else {
+                ln.fe.d = wi2;
+                ln.state = ST_SETUP;
+            }
+        }
+    } else if (!TR::FUSED && qi == Q_SCATTER) {
         // ---- E1. real scattering: SampleLd prologue (cpu/integrators.cpp:1300-1338) -> shadow ray ----
         if (have) {
             cn.sc++;
@@ -501,17 +569,10 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                 ln.state = ST_EV_SHADOW_END;
             }
         }
-    } else {
+    } else if (!TR::FUSED) {
         // ---- E2. end of the shadow ray: SampleLd epilogue (cpu/integrators.cpp:1382-1398), then phase
         //      sampling and the next camera segment (cpu/integrators.cpp:1041-1060) -------------------
-        if (have && TR::LEAN) {
-            // one channel: T_maj / T_maj[0] = 1, r_l = r_u = beta = 1 (see Traits::LEAN)
-            if (ln.T_ray[0] != 0) {
-                float w = ln.f_hat * ln.T_ray[0];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) ln.L[i] += w * sample_dense1(rp.light_spec, ln.lambda[i]);
-            }
-        } else if (have) {
+        if (have) {
             Spec<N> T_ray = ln.T_ray * (ln.T_maj / ln.T_maj[0]);
             if (nonzero(T_ray)) {
                 Spec<N> r_l = ln.s_rl * (ln.T_maj / ln.T_maj[0]);
@@ -545,101 +606,130 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
         }
     }
 
-    // ---- S. setup of the pending ray (camera segment or shadow ray) ------------------------------------
-    if (have && ln.state == ST_SETUP) {
-        V3 o = ln.fe.o, d = ln.fe.d;
-        float t0, t1, tMax;
-        bool hit;
-        if (TR::EXACT) {
-            hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
-            if (ln.shadow) {
-                // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
-                ln.trng.set_sequence(hash_v3(o), hash_v3(d));
-                tMax = 1 - kShadowEps;
-                if (hit && t1 < tMax) tMax = t1;
-                ln.u = ln.trng.uniform();
-                hit = true;
-            } else {
-                // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
-                ln.wo = -d;
-                tMax = t1;
-                if (hit) {
-                    PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
-                    uint64_t hash0 = hash_float(smp.get1d());
-                    uint64_t hash1 = hash_float(smp.get1d());
-                    ln.trng.set_sequence(hash0, hash1);
-                    ln.u = smp.get1d();
-                }
-            }
-        } else {
-            // FAST: same estimator; the tracking stream of either ray kind is seeded from two hashed sampler draws
-            hit = boundary_hit_fast(rp, o, d, &t0, &t1) && t1 > 0;
-            // (raw draws as PCG32 sequence / seed give correlated streams: they must go through the hash)
-            uint64_t hash0, hash1;
-            if (TR::ZSOBOL) {
-                // zsobol keeps the reference's dimension layout: camera rays take the three draws of
-                // cpu/integrators.cpp:985-988, shadow rays hash their origin and direction (:1338)
+    // ---- S. setup of the pending ray (camera segment or shadow ray).  Traits::FUSED: two passes over ONE copy of
+    //      the code, the shadow ray of a scattering event first (it is the ray the tracking loop walks first), then
+    //      the pending camera ray; a ray block goes to the slot as soon as it is complete -------------------------
+    uint4 *const sp = pv.slots + slot * SlotIO<TR>::kSlotQuads;
+#pragma unroll 1
+    for (int pass = (TR::FUSED && qi == Q_SCATTER) ? 0 : 1; pass < 2; ++pass) {
+        if (have && (pass == 0 ? sh_ray : ln.state == ST_SETUP)) {
+            const V3 cam_o = ln.fe.o, cam_d = ln.fe.d;
+            const int cam_state = ln.state;
+            if (TR::FUSED) ln.shadow = pass == 0;
+            V3 o = ln.fe.o, d = (TR::FUSED && pass == 0) ? sh_d : ln.fe.d;
+            float t0, t1, tMax;
+            bool hit;
+            if (TR::EXACT) {
+                hit = boundary_hit(rp, o, d, &t0, &t1) && t1 > 0;
                 if (ln.shadow) {
-                    hash0 = hash_v3(o);
-                    hash1 = hash_v3(d);
+                    // cpu/integrators.cpp:1336-1350: RNG(Hash(o), Hash(d)); tMax = exit or 1 - ShadowEpsilon
+                    ln.trng.set_sequence(hash_v3(o), hash_v3(d));
+                    tMax = 1 - kShadowEps;
+                    if (hit && t1 < tMax) tMax = t1;
+                    ln.u = ln.trng.uniform();
+                    hit = true;
                 } else {
-                    PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
-                    hash0 = hash_float(smp.get1d());
-                    hash1 = hash_float(smp.get1d());
-                    smp.get1d();
+                    // cpu/integrators.cpp:976-988: tMax = boundary exit, tracking RNG seeded from the sampler
+                    ln.wo = -d;
+                    tMax = t1;
+                    if (hit) {
+                        PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+                        uint64_t hash0 = hash_float(smp.get1d());
+                        uint64_t hash1 = hash_float(smp.get1d());
+                        ln.trng.set_sequence(hash0, hash1);
+                        ln.u = smp.get1d();
+                    }
                 }
-                ln.trng.set_sequence(hash0, hash1);
-            }
-            // (independent sampler: the path's tracking stream, seeded in start_path, simply continues)
-            ln.u = neg_log1m(ln.trng.uniform());  // remaining optical depth to the first tentative collision
-            if (ln.shadow) {
-                tMax = 1 - kShadowEps;
-                if (hit && t1 < tMax) tMax = t1;
-                hit = true;
             } else {
-                ln.wo = -d;
-                tMax = t1;
+                // FAST: same estimator; the tracking stream of either ray kind is seeded from two hashed sampler draws
+                hit = boundary_hit_fast(rp, o, d, &t0, &t1) && t1 > 0;
+                // (raw draws as PCG32 sequence / seed give correlated streams: they must go through the hash)
+                uint64_t hash0, hash1;
+                if (TR::ZSOBOL) {
+                    // zsobol keeps the reference's dimension layout: camera rays take the three draws of
+                    // cpu/integrators.cpp:985-988, shadow rays hash their origin and direction (:1338)
+                    if (ln.shadow) {
+                        hash0 = hash_v3(o);
+                        hash1 = hash_v3(d);
+                    } else {
+                        PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
+                        hash0 = hash_float(smp.get1d());
+                        hash1 = hash_float(smp.get1d());
+                        smp.get1d();
+                    }
+                    ln.trng.set_sequence(hash0, hash1);
+                }
+                // (independent sampler: the path's tracking stream, seeded in start_path, simply continues)
+                if (!(TR::FUSED && pass == 1 && sh_ray)) ln.u = neg_log1m(ln.trng.uniform());  // remaining optical depth to the first tentative collision
+                if (ln.shadow) {
+                    tMax = 1 - kShadowEps;
+                    if (hit && t1 < tMax) tMax = t1;
+                    hit = true;
+                } else {
+                    ln.wo = -d;
+                    tMax = t1;
+                }
             }
-        }
-        if (!hit) {
-            ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
-        } else if (TR::EXACT) {
-            // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
-            float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
-            tMax *= len;
-            d = d / len;
-            MRay mr = ray_to_medium(mv, o, d, tMax);
-            if (mr.hit) ln.dda.template init<true>(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
-            ln.fe.bind(mv, o, d);
-            ln.T_maj = sconst<N>(1.f);
-            ln.state = ST_WALK;
-        } else {
-            float l2 = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, d.z * d.z));
-            float rl = rsqrtf(l2);
-            tMax *= l2 * rl;
-            d = d * rl;
-            const float *a = mv.minv;
-            V3 mo = v3(__fmaf_rn(a[0], o.x, __fmaf_rn(a[1], o.y, __fmaf_rn(a[2], o.z, a[3]))),
-                       __fmaf_rn(a[4], o.x, __fmaf_rn(a[5], o.y, __fmaf_rn(a[6], o.z, a[7]))),
-                       __fmaf_rn(a[8], o.x, __fmaf_rn(a[9], o.y, __fmaf_rn(a[10], o.z, a[11]))));
-            V3 md = v3(__fmaf_rn(a[0], d.x, __fmaf_rn(a[1], d.y, a[2] * d.z)),
-                       __fmaf_rn(a[4], d.x, __fmaf_rn(a[5], d.y, a[6] * d.z)),
-                       __fmaf_rn(a[8], d.x, __fmaf_rn(a[9], d.y, a[10] * d.z)));
-            V3 inv = v3(ftz_rcp(md.x), ftz_rcp(md.y), ftz_rcp(md.z));
-            float h0 = 0.f, h1 = tMax;
+            if (!hit) {
+                ln.state = ST_EV_PATH_END;  // the ray leaves without touching the boundary
+            } else if (TR::EXACT) {
+                // SampleT_maj prologue (media.h:744-749) + SampleRay (media.h:322-337)
+                float len = sqrtf(sqr(d.x) + sqr(d.y) + sqr(d.z));
+                tMax *= len;
+                d = d / len;
+                MRay mr = ray_to_medium(mv, o, d, tMax);
+                if (mr.hit) ln.dda.template init<true>(mv, mr.o, mr.d, mr.tMin, mr.tMax); else ln.dda.invalidate();
+                ln.fe.bind(mv, o, d);
+                ln.T_maj = sconst<N>(1.f);
+                ln.state = ST_WALK;
+            } else {
+                float l2 = __fmaf_rn(d.x, d.x, __fmaf_rn(d.y, d.y, d.z * d.z));
+                float rl = rsqrtf(l2);
+                tMax *= l2 * rl;
+                d = d * rl;
+                const float *a = mv.minv;
+                V3 mo = v3(__fmaf_rn(a[0], o.x, __fmaf_rn(a[1], o.y, __fmaf_rn(a[2], o.z, a[3]))),
+                           __fmaf_rn(a[4], o.x, __fmaf_rn(a[5], o.y, __fmaf_rn(a[6], o.z, a[7]))),
+                           __fmaf_rn(a[8], o.x, __fmaf_rn(a[9], o.y, __fmaf_rn(a[10], o.z, a[11]))));
+                V3 md = v3(__fmaf_rn(a[0], d.x, __fmaf_rn(a[1], d.y, a[2] * d.z)),
+                           __fmaf_rn(a[4], d.x, __fmaf_rn(a[5], d.y, a[6] * d.z)),
+                           __fmaf_rn(a[8], d.x, __fmaf_rn(a[9], d.y, a[10] * d.z)));
+                V3 inv = v3(ftz_rcp(md.x), ftz_rcp(md.y), ftz_rcp(md.z));
+                float h0 = 0.f, h1 = tMax;
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                float tn = (mv.bmin[i] - comp(mo, i)) * comp(inv, i), tf = (mv.bmax[i] - comp(mo, i)) * comp(inv, i);
-                h0 = fmaxf(h0, fminf(tn, tf));
-                h1 = fminf(h1, fmaxf(tn, tf));
+                for (int i = 0; i < 3; ++i) {
+                    float tn = (mv.bmin[i] - comp(mo, i)) * comp(inv, i), tf = (mv.bmax[i] - comp(mo, i)) * comp(inv, i);
+                    h0 = fmaxf(h0, fminf(tn, tf));
+                    h1 = fminf(h1, fmaxf(tn, tf));
+                }
+                if (h0 <= h1) ln.dda.template init_fast<true>(mv, mo, inv, md, h0, h1); else ln.dda.invalidate();
+                ln.fe.bind(mv, o, d);
+                ln.T_maj = sconst<N>(1.f);
+                ln.state = ST_WALK;
             }
-            if (h0 <= h1) ln.dda.template init_fast<true>(mv, mo, inv, md, h0, h1); else ln.dda.invalidate();
-            ln.fe.bind(mv, o, d);
-            ln.T_maj = sconst<N>(1.f);
-            ln.state = ST_WALK;
+            if (TR::FUSED) {
+                if (pass == 0) {
+                    SlotIO<TR>::store_ray(sp, ln, false);
+                    ln.fe.o = cam_o;  // the camera ray is still pending
+                    ln.fe.d = cam_d;
+                    ln.state = cam_state;
+                } else if (ln.state == ST_WALK) {
+                    SlotIO<TR>::store_ray(sp, ln, sh_ray);
+                    ln.cam_wait = sh_ray;
+                }
+            }
         }
     }
-    requeue<TR, GRP_ALL>(pv, lane, have, slot, ln, lc, pending);
+    if (TR::FUSED) {
+        if (have && sh_ray) {
+            // tracked first: the shadow ray (its u was drawn in pass 0; a camera ray that left without touching the
+            // boundary, or pdf = 0, simply leaves nothing waiting)
+            ln.shadow = true;
+            ln.state = ST_WALK;
+        }
+        requeue<TR, GRP_A | GRP_B>(pv, lane, have, slot, ln, lc, pending);
+    } else
+        requeue<TR, GRP_ALL>(pv, lane, have, slot, ln, lc, pending);
 }
 
 // Inside the tracking loop a shadow-ray lane carries (T_ray, r_u, r_l of the shadow ray) in the fields
@@ -667,6 +757,21 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
     int slot = 0;
     ln.state = ST_DEAD;
     while (true) {
+        if (TR::FUSED && ln.state == ST_EV_SHADOW_END) {
+            // end of the NEE shadow ray, SampleLd epilogue (cpu/integrators.cpp:1382-1398; one channel: every weight
+            // but f_hat * T_ray is 1, the light's spectrum is applied in write_sample), then on to the camera ray
+            // that was set up together with it -- without a trip through the queues
+            if (ln.T_ray[0] != 0) ln.Lsum = __fmaf_rn(ln.f_hat, ln.T_ray[0], ln.Lsum);
+            if (ln.cam_wait) {
+                SlotIO<TR>::load_waiting_ray(pv.slots + slot * SlotIO<TR>::kSlotQuads, ln);
+                ln.cam_wait = false;
+                ln.shadow = false;
+                ln.u = neg_log1m(ln.trng.uniform());
+                ln.state = ST_WALK;
+                ln.mj = ln.dda.tMin < ln.dda.tMax ? maj[ln.dda.lin] : 0.f;
+            } else
+                ln.state = ST_EV_PATH_END;
+        }
         // ---- park finished paths and refill from Q_TRACK, both in batches of >= refill_lanes -------
         bool fin = have && ln.state < ST_WALK;
         unsigned idle = __ballot_sync(0xffffffffu, !have || fin);
@@ -846,10 +951,15 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 // Tr = T_ray / Average(r_l + r_u)
                 const float ratio = fmaxf(0.f, smj - sa - ss) * inv;
                 float T = ln.T_ray[0] * ratio;
-                const float ru = ln.s_ru[0] * ratio;
-                if (T * ftz_rcp(1 + ru) < 0.05f) T = ln.trng.uniform() < 0.75f ? 0.f : T * 4.f;
+                const float ru = T * __int_as_float((127 - 2 * ln.rr_k) << 23);  // T / 4^rr_k
+                if (T * ftz_rcp(1 + ru) < 0.05f) {
+                    if (ln.trng.uniform() < 0.75f) T = 0.f;
+                    else {
+                        T *= 4.f;
+                        ln.rr_k = min(ln.rr_k + 1, 31);
+                    }
+                }
                 ln.T_ray.v[0] = T;
-                ln.s_ru.v[0] = ru;
                 ln.state = T != 0 ? ST_SAMPLE : ST_EV_SHADOW_END;
             }
         }

@@ -133,6 +133,12 @@ struct PathLane {
     Spec<N> T_ray, s_rl, s_ru;
     float f_hat;
     V3 wo;
+    // Traits::FUSED: the camera ray set up together with the shadow ray waits in the slot's second ray block
+    bool cam_wait;
+    // Traits::LEAN: L[i] = Lsum * Le_light(lambda_i) (one channel: every NEE term has the same scalar weight), and
+    // the shadow ray's r_u is T_ray / 4^rr_k (both take the same ratios; T_ray also takes the roulette's x 4)
+    float Lsum;
+    int rr_k;
 };
 
 }  // namespace avr

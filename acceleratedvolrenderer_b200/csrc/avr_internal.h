@@ -13,7 +13,7 @@
 // AVR_REFILL_LANES, AVR_TRACK_MIN, AVR_YIELD_LANES, AVR_YIELD_LANES_FULL, AVR_EVENT_SMSP_MASK, AVR_BLOCKS_PER_SM,
 // AVR_THREADS, AVR_POOL); a render call reads no environment variable.
 struct avr_knobs {
-    int walk_steps = 4, collide_min = 1, refill_lanes = 16, track_min = 32, yield_lanes = 8, yield_lanes_full = 20;
+    int walk_steps = 0 /* 0: 3 for FAST, 4 for EXACT kernels */, collide_min = 1, refill_lanes = 16, track_min = 32, yield_lanes = 8, yield_lanes_full = 20;
     int event_smsp_mask = 12;
     int blocks_per_sm = 0, threads = 0, pool = 0;  // 0 = the kernel variant's default
     // FAST majorant grid of a medium created under this context: c x c x c reference cells per FAST cell

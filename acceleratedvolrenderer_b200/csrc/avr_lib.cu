@@ -54,7 +54,7 @@ extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
             return v < lo ? lo : (v > hi ? hi : v);
         };
         avr_knobs &k = ctx->knobs;
-        k.walk_steps = env_int("AVR_WALK_STEPS", k.walk_steps, 1, 1 << 20);
+        k.walk_steps = env_int("AVR_WALK_STEPS", k.walk_steps, 0, 1 << 20);
         k.collide_min = env_int("AVR_COLLIDE_MIN", k.collide_min, 1, 32);
         k.refill_lanes = env_int("AVR_REFILL_LANES", k.refill_lanes, 1, 32);
         k.track_min = env_int("AVR_TRACK_MIN", k.track_min, 1, 1 << 20);

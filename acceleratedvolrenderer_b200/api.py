@@ -18,7 +18,7 @@ from ._abi import (avr_graph_sidecar, avr_light_vector_desc, avr_graph_builder_d
 
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libavr_b200.so")
 
-LAYOUTS = {"dense": 0, "octet32": 1, "octet16": 2}
+LAYOUTS = {"dense": 0, "octet32": 1, "octet16": 2, "brick16": 3}
 TMAJ_RATIO, TMAJ_DELTA, TMAJ_SHADOW = 0, 1, 2
 
 f32p = C.POINTER(C.c_float)

@@ -278,6 +278,36 @@ __global__ void k_pack_octets(MediumView mv, float4 *out32, uint4 *out16) {
     }
 }
 
+// Sparse brick pool (LAYOUT_BRICK_F16, avr_medium.cuh brick16_taps).  One CTA per brick of 8x8x8 cells.
+// flags: does any voxel the brick's cells touch (x in [8 bx - 1, 8 bx + 7], ...) hold a non-zero value?
+__global__ void k_brick_flags(MediumView mv, int *flags) {
+    const int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z;
+    int any = 0;
+    for (int i = threadIdx.x; i < 729; i += blockDim.x) {
+        int x = 8 * bx - 1 + i % 9, y = 8 * by - 1 + (i / 9) % 9, z = 8 * bz - 1 + i / 81;
+        any |= dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y, z) != 0.f;
+    }
+    any = __syncthreads_or(any);
+    if (threadIdx.x == 0) flags[(size_t(bz) * gridDim.y + by) * gridDim.x + bx] = any;
+}
+// fill: CTA b writes the 576 entries of pool slot b (bricks lists the non-empty bricks' linear ids)
+__global__ void k_brick_fill(MediumView mv, const int *bricks, int sbx, int sby, uint2 *pool) {
+    const int id = bricks[blockIdx.x];
+    const int bx = id % sbx, by = (id / sbx) % sby, bz = id / (sbx * sby);
+    for (int i = threadIdx.x; i < kBrickEntries; i += blockDim.x) {
+        int r = i % 9, lx = (i / 9) & 7, ly = i / 72;
+        int x = 8 * bx + lx, y = 8 * by + ly, z = 8 * bz - 1 + r;  // cell column (x, y): taps x-1, x / y-1, y
+        __half2 h0 = __floats2half2_rn(dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x - 1, y - 1, z),
+                                       dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y - 1, z));
+        __half2 h1 = __floats2half2_rn(dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x - 1, y, z),
+                                       dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y, z));
+        uint2 q;
+        q.x = *reinterpret_cast<uint32_t *>(&h0);
+        q.y = *reinterpret_cast<uint32_t *>(&h1);
+        pool[size_t(blockIdx.x) * kBrickEntries + i] = q;
+    }
+}
+
 // ---- empty-space distance field of the majorant grid (FAST render kernels, MediumView::maj_fast) --------
 // Chebyshev distance in cells from every EMPTY majorant cell to the nearest non-empty one, by three 1-D
 // passes: d1 = distance along x; d2 = min over y' of max(|y - y'|, d1(y')); d3 the same along z.
@@ -461,8 +491,10 @@ avr_status finish_majorants(avr_medium *m) {
 }
 
 // Octet store of the scalar density grid (layouts 1, 2): cell c holds taps c-1, c on every axis.
+avr_status build_bricks(avr_medium *m);
 avr_status build_octets(avr_medium *m, int layout) {
     if (layout == LAYOUT_DENSE_F32) return AVR_OK;
+    if (layout == LAYOUT_BRICK_F16) return build_bricks(m);
     avr_ctx *ctx = m->ctx;
     MediumView &v = m->view;
     v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
@@ -487,6 +519,67 @@ avr_status build_octets(avr_medium *m, int layout) {
     return AVR_OK;
 }
 
+// Sparse fp16 brick pool (layout 3): flags -> host prefix sum over the (small) brick grid -> pool fill; the dense
+// fp32 grid is released afterwards (every lookup of this medium goes through the pool from then on).
+avr_status build_bricks(avr_medium *m) {
+    avr_ctx *ctx = m->ctx;
+    MediumView &v = m->view;
+    v.sbx = (v.nx + 1 + 7) / 8; v.sby = (v.ny + 1 + 7) / 8; v.sbz = (v.nz + 1 + 7) / 8;
+    const size_t nb = size_t(v.sbx) * v.sby * v.sbz;
+    if (nb >= (size_t(1) << 31) || v.sby > 65535 || v.sbz > 65535)
+        return set_err(ctx, AVR_ERR_UNSUPPORTED, "brick layout: too many bricks");
+    int *d_flags = nullptr;
+    AVR_CUDA(ctx, cudaMalloc(&d_flags, nb * sizeof(int)));
+    k_brick_flags<<<dim3(v.sbx, v.sby, v.sbz), 128, 0, ctx->stream>>>(v, d_flags);
+    std::vector<int> tab(nb), list;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tab.data(), d_flags, nb * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { cudaFree(d_flags); return set_cuda_err(ctx, e, "brick flags"); }
+    for (size_t i = 0; i < nb; ++i) {
+        if (tab[i]) { tab[i] = (int)list.size(); list.push_back((int)i); }
+        else tab[i] = -1;
+    }
+    int *d_tab = d_flags;  // reused as the indirection grid
+    m->allocs.push_back(d_tab);
+    m->bytes += int64_t(nb * sizeof(int));
+    AVR_CUDA(ctx, cudaMemcpyAsync(d_tab, tab.data(), nb * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    v.brick_tab = d_tab;
+    uint2 *pool = nullptr;
+    const size_t slots = list.size() ? list.size() : 1;
+    AVR_CUDA(ctx, cudaMalloc(&pool, slots * kBrickEntries * sizeof(uint2)));
+    m->allocs.push_back(pool);
+    m->bytes += int64_t(slots * kBrickEntries * sizeof(uint2));
+    v.brick16 = pool;
+    if (!list.empty()) {
+        int *d_list = nullptr;
+        AVR_CUDA(ctx, cudaMalloc(&d_list, list.size() * sizeof(int)));
+        e = cudaMemcpyAsync(d_list, list.data(), list.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) {
+            k_brick_fill<<<(unsigned)list.size(), 192, 0, ctx->stream>>>(v, d_list, v.sbx, v.sby, pool);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_list);
+        if (e != cudaSuccess) return set_cuda_err(ctx, e, "brick fill");
+    } else
+        AVR_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return AVR_OK;
+}
+// after every consumer of the dense grid has run (majorants, FAST majorants): give it back
+void release_dense(avr_medium *m) {
+    MediumView &v = m->view;
+    if (v.layout != LAYOUT_BRICK_F16 || !v.dense) return;
+    for (size_t i = 0; i < m->allocs.size(); ++i)
+        if (m->allocs[i] == (const void *)v.dense) {
+            cudaFree(m->allocs[i]);
+            m->allocs.erase(m->allocs.begin() + i);
+            m->bytes -= int64_t(size_t(v.nx) * v.ny * v.nz * sizeof(float));
+            break;
+        }
+    v.dense = nullptr;
+}
+
 void free_medium(avr_medium *m) {
     if (!m) return;
     cudaSetDevice(m->ctx->device);
@@ -506,7 +599,7 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     if (!d->sigma_a || !d->sigma_s) return set_err(ctx, AVR_ERR_BAD_ARG, "grid medium: sigma_a / sigma_s tables missing");
     if (d->le && d->temperature)
         return set_err(ctx, AVR_ERR_BAD_ARG, "Both \"Le\" and \"temperature\" values were provided.");
-    if (layout < 0 || layout > 2) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
+    if (layout < 0 || layout > 3) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
     AVR_CUDA(ctx, cudaSetDevice(ctx->device));
     avr_medium *m = new avr_medium();
     m->ctx = ctx;
@@ -561,6 +654,7 @@ extern "C" avr_status avr_medium_create_uniformgrid(avr_ctx *ctx, const avr_grid
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "medium build"); }
     TRY(finish_majorants(m));
+    release_dense(m);
     *out = m;
     return AVR_OK;
 }
@@ -574,7 +668,7 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
         if (d->density.dims[i] < 1 || (d->temperature.values && d->temperature.dims[i] < 1))
             return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: empty index bounding box");
     if (!d->sigma_a || !d->sigma_s) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb medium: sigma_a / sigma_s tables missing");
-    if (layout < 0 || layout > 2) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
+    if (layout < 0 || layout > 3) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
     AVR_CUDA(ctx, cudaSetDevice(ctx->device));
     avr_medium *m = new avr_medium();
     m->ctx = ctx;
@@ -635,6 +729,7 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "nanovdb medium build"); }
     TRY(finish_majorants(m));
+    release_dense(m);
     *out = m;
     return AVR_OK;
 }
@@ -674,6 +769,7 @@ extern "C" avr_status avr_medium_create_rgbgrid(avr_ctx *ctx, const avr_rgbgrid_
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "rgb medium build"); }
     TRY(finish_majorants(m));
+    release_dense(m);
     *out = m;
     return AVR_OK;
 #undef TRY

@@ -102,7 +102,8 @@ struct Fetcher {
     }
     // FAST octet layouts: the fetch split in two, so that the render kernel can request the 8 taps of a
     // tentative collision as soon as its distance is known and consume them one loop trip later.
-    static constexpr bool kSplitFetch = AVR_SPLIT_FETCH && !TR::EXACT && !TR::GENERAL && TR::LAYOUT != LAYOUT_DENSE_F32;
+    static constexpr bool kOctets = TR::LAYOUT == LAYOUT_OCTET_F32 || TR::LAYOUT == LAYOUT_OCTET_F16;
+    static constexpr bool kSplitFetch = AVR_SPLIT_FETCH && !TR::EXACT && !TR::GENERAL && kOctets;
     AVR_DEV void request(const MediumView &mv, float t, float4 &a, float4 &b) const {
         float sx = __fmaf_rn(sd.x, t, so.x), sy = __fmaf_rn(sd.y, t, so.y), sz = __fmaf_rn(sd.z, t, so.z);
         int cx = (int)floorf(sx) + 1, cy = (int)floorf(sy) + 1, cz = (int)floorf(sz) + 1;
@@ -118,7 +119,7 @@ struct Fetcher {
     // FAST octet layouts: fire-and-forget prefetch of the octet a tentative collision at t will read; the
     // render kernel issues it when the collision distance becomes known, up to walk_steps DDA steps
     // before op B consumes the octet.  No register is held across the gap.
-    static constexpr int kPrefetch = (!TR::EXACT && !TR::GENERAL && TR::LAYOUT != LAYOUT_DENSE_F32) ? AVR_PREFETCH : 0;
+    static constexpr int kPrefetch = (!TR::EXACT && !TR::GENERAL && kOctets) ? AVR_PREFETCH : 0;
     AVR_DEV void prefetch(const MediumView &mv, float t) const {
         float sx = __fmaf_rn(sd.x, t, so.x), sy = __fmaf_rn(sd.y, t, so.y), sz = __fmaf_rn(sd.z, t, so.z);
         int cx = (int)floorf(sx) + 1, cy = (int)floorf(sy) + 1, cz = (int)floorf(sz) + 1;

@@ -632,7 +632,9 @@ def main():
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
-        fetch_bytes = 32 if args.layout != "octet16" else 16
+        # algorithmic bytes of one trilinear fetch: the 32-byte octet, the 16-byte fp16 octet, or (sparse brick pool)
+        # two 8-byte tap rows + the 4-byte indirection entry
+        fetch_bytes = {"octet16": 16, "brick16": 20}.get(args.layout, 32)
         # the L2 half of the metric ("density-fetch GB/s vs HBM/L2 roofline"): measured here, with the 64 MiB-resident
         # read kernel BASELINE.md promises; it is the denominator when the medium's store fits the L2
         l2_peak = ctx.measure_read_bandwidth(64 << 20, iters=40)

@@ -55,13 +55,16 @@ const char *avr_version(void);
 avr_status avr_measure_read_bandwidth(avr_ctx *ctx, int64_t bytes, int32_t iters, float *gb_per_s);
 
 /* ---- media ---------------------------------------------------------------------------------- */
-/* HBM layouts for scalar grids.  All three give the same SampledGrid::Lookup tap values
+/* HBM layouts for scalar grids.  All give the same SampledGrid::Lookup tap values (fp16 layouts: rounded)
  * (util/containers.h:804-835); the octet layouts store, per interpolation cell, its 8 corner taps
  * contiguously (one 32-byte sector for fp32, one 16-byte vector for fp16) in 4x4x4-cell bricks. */
 enum {
     AVR_LAYOUT_DENSE_F32 = 0,  /* reference layout: values[(z*ny+y)*nx+x], 8 bounds-checked taps */
     AVR_LAYOUT_OCTET_F32 = 1,  /* bit-identical taps, 1 sector per fetch                       */
-    AVR_LAYOUT_OCTET_F16 = 2   /* taps rounded to fp16 (perf option; NOT per-ray bit-parity)   */
+    AVR_LAYOUT_OCTET_F16 = 2,  /* taps rounded to fp16 (perf option; NOT per-ray bit-parity)   */
+    AVR_LAYOUT_BRICK_F16 = 3   /* sparse pool of 8x8x8-cell fp16 bricks behind an indirection grid: empty bricks cost
+                                * nothing, ~1.1x the fp32 grid where occupied, no 2^32-cell limit, the dense grid is
+                                * released after the build; taps rounded to fp16 like layout 2                    */
 };
 
 /* Replaces GridMedium::Create + ctor, media.cpp:212-336 ("uniformgrid").  Host pointers; the

@@ -80,6 +80,38 @@ def test_octet16_lookup_is_fp16_rounding_of_taps(ctx, orc):
     md.close()
 
 
+@pytest.mark.parametrize("dims", [(24, 20, 28), (7, 8, 9), (65, 33, 17), (1, 1, 1), (96, 80, 72)])
+def test_brick16_pool_is_the_fp16_grid_with_empty_bricks_dropped(ctx, orc, dims):
+    """Sparse fp16 brick pool (AVR_LAYOUT_BRICK_F16, SURVEY 8(f) n4): every lookup equals SampledGrid::Lookup over
+    the fp16-rounded grid bit for bit (the same taps octet16 holds), the majorant grid is the dense one's, and a
+    grid that is mostly empty is stored in a fraction of its dense size (the dense copy is released)."""
+    nx, ny, nz = dims
+    rng = np.random.default_rng(nx * 100 + ny)
+    dens = scenes.fbm_density(nx, ny, nz, seed=5) if min(dims) > 1 else np.full((nz, ny, nx), 0.7, dtype=np.float32)
+    # carve most of the volume empty: only a corner blob survives (dims permitting)
+    z, y, x = np.meshgrid(np.arange(nz), np.arange(ny), np.arange(nx), indexing="ij")
+    keep = (x < max(1, nx // 3)) & (y < max(1, ny // 2)) & (z >= nz // 2)
+    sparse = np.where(keep, dens + 0.05, 0).astype(np.float32)
+    for field in (dens, sparse):
+        gd = GridDesc(field, scenes.const_spectrum(0.4), scenes.const_spectrum(11.0))
+        md = ctx.create_medium("uniformgrid", gd, layout="brick16")
+        ref = ctx.create_medium("uniformgrid", gd, layout="dense")
+        pg = rng.uniform(-0.1, 1.1, (30000, 3)).astype(np.float32)
+        pg[:2000] = rng.integers(0, 2, (2000, 3)).astype(np.float32)          # corners and faces of the box
+        want = orc.grid_lookup(field.astype(np.float16).astype(np.float32), pg)
+        assert bits_equal(md.lookup_density(pg), want)
+        assert bits_equal(md.majorants(), ref.majorants())
+        # pool + indirection grid alone (both media carry the same majorant grids and spectra tables)
+        pool_bytes = md.bytes() - (ref.bytes() - field.nbytes)
+        if field is sparse and nx * ny * nz > 200000:     # (8^3-cell bricks: small grids have nothing to drop)
+            assert pool_bytes < 0.6 * field.nbytes, (pool_bytes, field.nbytes)
+        md.close(); ref.close()
+    empty = GridDesc(np.zeros((nz, ny, nx), dtype=np.float32), scenes.const_spectrum(0.4), scenes.const_spectrum(1.0))
+    md = ctx.create_medium("uniformgrid", empty, layout="brick16")
+    assert not md.lookup_density(rng.uniform(0, 1, (1000, 3)).astype(np.float32)).any()
+    md.close()
+
+
 @pytest.mark.parametrize("res", [(16, 16, 16), (64, 64, 64), (5, 7, 3)])
 def test_dda_bit_exact(ctx, orc, res):
     """Kernel 2: voxel indices, segment bounds and majorants bit-exact, 2^18 rays incl. axis-parallel,
@@ -220,10 +252,12 @@ def test_nanovdb_index_space_lookup(ctx, orc):
     md0 = ctx.create_medium("nanovdb", unit, layout="dense")
     md1 = ctx.create_medium("nanovdb", unit, layout="octet32")
     md2 = ctx.create_medium("nanovdb", unit, layout="octet16")
-    d0, d1, d2 = md0.lookup_density(xyz), md1.lookup_density(xyz), md2.lookup_density(xyz)
+    md3 = ctx.create_medium("nanovdb", unit, layout="brick16")
+    d0, d1, d2, d3 = md0.lookup_density(xyz), md1.lookup_density(xyz), md2.lookup_density(xyz), md3.lookup_density(xyz)
     assert bits_equal(d0, d1)
     assert d0.max() > 0.1 and np.abs(d2 - d0).max() <= 1e-3 * d0.max()
-    for m in (md0, md1, md2):
+    assert bits_equal(d2, d3)   # the two fp16 stores hold the same rounded taps
+    for m in (md0, md1, md2, md3):
         m.close()
 
 

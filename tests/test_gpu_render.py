@@ -110,7 +110,7 @@ def rel_mse(a, b):
     return float(np.mean((a - b) ** 2 / (b ** 2 + (0.05 * b.mean()) ** 2)))
 
 
-@pytest.mark.parametrize("exact,layout", [(1, "octet32"), (0, "dense"), (0, "octet32"), (0, "octet16")])
+@pytest.mark.parametrize("exact,layout", [(1, "octet32"), (0, "dense"), (0, "octet32"), (0, "octet16"), (0, "brick16"), (1, "brick16")])
 def test_converged_image_matches_oracle(ctx, orc, exact, layout):
     dens, (gd, rd) = small_scene(width=32, height=24, spp=128, max_depth=6)
     mo = orc.medium_uniformgrid(gd)
@@ -131,7 +131,7 @@ def test_converged_image_matches_oracle(ctx, orc, exact, layout):
     assert err <= 1.5 * noise + 1e-6, (err, noise)
     # image means: a standard-error bar, not a band (fp16 taps are a different medium: rounding moves the mean)
     z, rel_se = mean_z(gpus, refs)
-    assert abs(z) < MEAN_Z_BAR or (layout == "octet16" and abs(z) * rel_se < 2e-3), (z, rel_se)
+    assert abs(z) < MEAN_Z_BAR or (layout in ("octet16", "brick16") and abs(z) * rel_se < 2e-3), (z, rel_se)
 
 
 @pytest.mark.parametrize("randomize", ["none", "permutedigits", "fastowen", "owen"])
@@ -426,7 +426,7 @@ def test_nanovdb_render_matches_oracle(ctx, orc, emissive):
     mo.close()
     img_a = ctx.film_resolve(rd, sum(refs[:4])); img_b = ctx.film_resolve(rd, sum(refs[4:]))
     noise = noise_floor(img_a, img_b)
-    for layout in (["dense"] if emissive else ["dense", "octet32", "octet16"]):
+    for layout in (["dense"] if emissive else ["dense", "octet32", "octet16", "brick16"]):
         md = ctx.create_medium("nanovdb", nd, layout=layout)
         gpus = gpu_renders(ctx, md, rd.with_(exact_math=0, spp=rd.spp * GPU_SPP_FACTOR), k=8)
         md.close()
@@ -438,7 +438,7 @@ def test_nanovdb_render_matches_oracle(ctx, orc, emissive):
         # image means in standard errors (blackbody spikes widen the SE by themselves); fp16 taps are a slightly
         # different medium, held to 0.2 % instead
         z, rel_se = mean_z(gpus, refs)
-        assert abs(z) < MEAN_Z_BAR or (layout == "octet16" and abs(z) * rel_se < 2e-3), (layout, z, rel_se)
+        assert abs(z) < MEAN_Z_BAR or (layout in ("octet16", "brick16") and abs(z) * rel_se < 2e-3), (layout, z, rel_se)
 
 
 def test_volpath_matches_reference_integrator(ctx):

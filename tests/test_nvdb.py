@@ -82,3 +82,36 @@ def test_medium_from_file_is_the_medium_from_arrays(ctx, ref, tmp_path):
         ctx.create_medium_nanovdb_file("", nd)
     assert 'Must supply "filename"' in str(e.value)            # media.cpp:632-633
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+def test_sparse_nvdb_file_into_the_brick_pool(ctx, ref, tmp_path):
+    """SURVEY 8(f) n4 as a whole: a SPARSE grid built with the vendored GridBuilder, written as a .nvdb file (ZIP
+    codec), read by avr_medium_create_nanovdb_file into the sparse fp16 brick pool: lookups equal the fp16-rounded
+    flattened grid (the octet16 medium from the same arrays, bit for bit), the pool is a fraction of the dense box,
+    and a FAST render through it agrees with the octet32 render of the same medium to the fp16 rounding of the taps."""
+    dens = sparse_cloud((72, 64, 80), seed=4)
+    dens[:, :, 24:] = 0          # 70 % of the index box is empty on top of the cloud's own holes
+    dens[0, 0, 79] = 0.01        # ... but the box still spans it
+    vs = 1.0 / 80
+    nd, rd = scenes.cloud_scene_nanovdb(dens, voxel_size=vs, width=32, height=24, spp=64, sigma_t=30.0, albedo=0.9, g=0.3)
+    path = tmp_path / "sparse.nvdb"
+    ref.write_nvdb(path, [("density", dens, (0, 0, 0), vs, (0.0, 0.0, 0.0))], codec=1)
+    brick = ctx.create_medium_nanovdb_file(path, nd, layout="brick16")
+    half = ctx.create_medium("nanovdb", nd, layout="octet16")
+    full = ctx.create_medium("nanovdb", nd, layout="octet32")
+    assert np.array_equal(brick.majorants(), full.majorants())
+    rng = np.random.default_rng(3)
+    xyz = rng.uniform(-2, np.array(dens.shape[::-1]) + 2, (40000, 3)).astype(np.float32)
+    assert np.array_equal(brick.lookup_density(xyz).view(np.uint32), half.lookup_density(xyz).view(np.uint32))
+    dense = ctx.create_medium("nanovdb", nd, layout="dense")
+    pool_bytes = brick.bytes() - (dense.bytes() - dens.nbytes)   # both carry the same majorant grids and tables
+    dense.close()
+    assert pool_bytes < 0.6 * dens.nbytes and brick.bytes() < 0.25 * full.bytes(), (pool_bytes, dens.nbytes, full.bytes())
+    a = np.zeros((24, 32, 4)); b = np.zeros_like(a)
+    for seed in range(4):
+        ctx.render_volpath(brick, rd.with_(exact_math=0, sampler_seed=seed), film=a)
+        ctx.render_volpath(full, rd.with_(exact_math=0, sampler_seed=100 + seed), film=b)
+    ma, mb = a[..., :3].sum() / a[..., 3].sum(), b[..., :3].sum() / b[..., 3].sum()
+    assert abs(ma / mb - 1) < 0.02, (ma, mb)
+    brick.close(); half.close(); full.close()

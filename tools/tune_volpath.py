@@ -53,11 +53,12 @@ def main():
                 if i > 0 and (best is None or st["kernel_ms"] < best["kernel_ms"]):
                     best = st
             f = best["camera_fetches"] + best["shadow_fetches"]
-            bpf = 16 if layout == "octet16" else 32
+            bpf = {"octet16": 16, "brick16": 20}.get(layout, 32)
             print(json.dumps({"layout": layout, "exact": int(exact), "sampler": args.sampler, "env": dict(zip(names, vals)),
                               "kernel_ms": round(best["kernel_ms"], 2),
                               "Msamples_s": round(W * H * args.spp / best["kernel_ms"] / 1e3, 2),
                               "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1),
+                              "medium_MB": round(med.bytes() / 1e6, 1),
                               "stats": {k: v for k, v in best.items() if k != "kernel_ms"}}),
                   flush=True)
             med.close()

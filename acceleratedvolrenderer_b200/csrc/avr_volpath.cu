@@ -406,17 +406,24 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 #ifndef AVR_CTA_THREADS
 #define AVR_CTA_THREADS 512  // one 512-thread CTA per SM with one pool: 1.6 % faster than two of 256 (fuller batches)
 #endif
+#ifndef AVR_CTA_THREADS_FAST
+// FAST scalar kernels with the independent sampler fit 96 registers without a spill: 5 warps per scheduler instead
+// of 4 hide more of the fetch latency (8 spp: 512 threads 19.1 ms, 576 17.9, 640 17.05, 704 17.9 (spills), 768 17.9);
+// the EXACT kernels spill below 123 registers and lose (512: 52.1 ms, 576: 55.7, 640: 53.6, 704: 59.3)
+#define AVR_CTA_THREADS_FAST 640
+#endif
 template <typename TR>
 struct KernelCfg {
     // achromatic scalar grids: AVR_MIN_BLOCKS CTAs of 256 threads (<= 128 registers); the chromatic and general
     // kernels need 144..181 registers: one CTA per SM with as many warps as the register file holds
     static constexpr bool kLean = TR::NCH == 1 && !TR::GENERAL;
-    static constexpr int kThreads = kLean ? AVR_CTA_THREADS : 384;  // 3 warps per scheduler: 168-register cap
+    static constexpr int kLeanThreads = (!TR::EXACT && !TR::ZSOBOL) ? AVR_CTA_THREADS_FAST : AVR_CTA_THREADS;
+    static constexpr int kThreads = kLean ? kLeanThreads : 384;  // (not lean) 3 warps per scheduler: 168-register cap
 #ifdef AVR_LEAN_MIN_BLOCKS
     static constexpr int kMinBlocks = kLean ? AVR_LEAN_MIN_BLOCKS : 1;
 #else
     static constexpr int kMinBlocks =
-        (kLean && AVR_MIN_BLOCKS * 256 >= AVR_CTA_THREADS) ? AVR_MIN_BLOCKS * 256 / AVR_CTA_THREADS : 1;
+        (kLean && AVR_MIN_BLOCKS * 256 >= kLeanThreads) ? AVR_MIN_BLOCKS * 256 / kLeanThreads : 1;
 #endif
 };
 

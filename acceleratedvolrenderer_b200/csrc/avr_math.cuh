@@ -427,5 +427,11 @@ AVR_DEV float sigmoid_s(float x) {
 AVR_DEV float rsp_eval(float c0, float c1, float c2, float lambda) {
     return sigmoid_s(__fmaf_rn(lambda, __fmaf_rn(lambda, c0, c1), c2));
 }
+// FAST: the same sigmoid through one approximate reciprocal square root (x clamped so that x^2 stays finite)
+AVR_DEV float rsp_eval_fast(float c0, float c1, float c2, float lambda) {
+    float x = __fmaf_rn(lambda, __fmaf_rn(lambda, c0, c1), c2);
+    x = fminf(fmaxf(x, -1e18f), 1e18f);
+    return __fmaf_rn(0.5f * x, __frsqrt_rn(__fmaf_rn(x, x, 1.f)), 0.5f);
+}
 
 }  // namespace avr

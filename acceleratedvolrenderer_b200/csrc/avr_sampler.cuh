@@ -179,6 +179,13 @@ struct PathSamplerRef {
             rng.advance((long long)samp * 65536ll);
         }
     }
+    // n dimensions whose values nobody reads (the light choice among ONE light, uLight of a delta light, time and
+    // lens of a pinhole camera): the stream advances exactly as the reference's, the samples are not computed
+    AVR_DEV void skip(int n) {
+        if (ZS) rng.state += uint64_t(n);
+        else
+            for (int i = 0; i < n; ++i) rng.u32();
+    }
     AVR_DEV float get1d() {
         if (!ZS) return rng.uniform();
         int dim = int(rng.state);

@@ -146,7 +146,12 @@ struct Fetcher {
             Spec<4> a4, s4;
 #pragma unroll
             for (int i = 0; i < 4; ++i) { a4.v[i] = lc.sig_a.v[i % NCH]; s4.v[i] = lc.sig_s.v[i % NCH]; }
-            Props4 g = sample_point_general(mv, point(t), lc.lambda, a4, s4);
+            // FAST general kernels of grid / RGB media: sample coordinates from the folded affine map, fast lookups
+            // (the illuminant-weighted Le of an RGB grid multiplies per tap in the reference: linear, so once here)
+            Props4 g = (!TR::EXACT && mv.kind != KIND_NVDB)
+                           ? sample_point_general_fast(mv, __fmaf_rn(sd.x, t, so.x), __fmaf_rn(sd.y, t, so.y),
+                                                       __fmaf_rn(sd.z, t, so.z), lc.lambda, a4, s4)
+                           : sample_point_general(mv, point(t), lc.lambda, a4, s4);
 #pragma unroll
             for (int i = 0; i < NCH; ++i) { mp.sigma_a.v[i] = g.sigma_a.v[i]; mp.sigma_s.v[i] = g.sigma_s.v[i]; }
             mp.Le = g.Le;

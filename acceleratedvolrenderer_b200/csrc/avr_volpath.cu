@@ -1,18 +1,22 @@
 // avr_volpath.cu — kernel 1b (see avr_volpath.cuh) and its C entry points.
 //
-// Per-lane state machine under a warp-level scheduler: every lane holds one path and waits for
-// exactly one of six ops; each trip the warp counts the waiting lanes per op (one REDUX) and runs the
-// op with the best lanes x weight score for the lanes that want it.  Every op has ONE call site, so
-// lanes execute it convergently and the SASS stays small:
+// Persistent kernel, one CTA per SM.  The CTA owns a pool of paths in shared memory (slots of 16-byte quads,
+// SlotIO) and four MPMC queues of slot ids; a warp serves ONE queue at a time, so every op has one call site and
+// runs convergently:
 //   R  regenerate : flush the finished sample to the film, pull new (pixel, sample) work with one
-//                   warp-aggregated atomic, generate the camera ray
-//   S  setup      : boundary hit, RNG seeding, ray -> medium space, slab test, DDA init
-//                   (camera segment or NEE shadow ray: same code, a mode bit apart)
-//   A  walk       : DDA steps to the next majorant segment with sigma_maj != 0
-//   B  collide    : one tentative collision = one log, one exp, one 32-byte density fetch, then the
-//                   delta-tracking (camera) or ratio-tracking (shadow) update
-//   E1 scatter    : NEE preparation -> shadow ray pending
-//   E2 shadow end : NEE accumulate + phase sampling -> next camera segment pending
+//                   warp-aggregated atomic, generate the camera ray                         (queue Q_DEAD)
+//   E1 scatter    : NEE preparation -> shadow ray pending                                   (queue Q_SCATTER)
+//   E2 shadow end : NEE accumulate + phase sampling -> next camera segment pending          (queue Q_SHADOW_END)
+//                   (Traits::FUSED: E1 and E2 are one op on Q_SCATTER, both rays are set up together and the
+//                   tracking loop switches from the shadow ray to the waiting camera ray by itself)
+//   S  setup      : boundary hit, RNG seeding, ray -> medium space, slab test, DDA init; runs at the end of
+//                   every event batch (camera segment or NEE shadow ray: same code, a mode bit apart)
+//   tracking loop (queue Q_TRACK, track_mode): every lane holds a path in registers and alternates
+//   A  walk       : DDA steps to the next majorant segment with sigma_maj != 0, each followed by
+//   A' sample     : the draw of the next tentative-collision distance, and
+//   B  collide    : one tentative collision = one 32-byte density fetch, then the delta-tracking (camera) or
+//                   ratio-tracking (shadow) update;
+//   a lane whose path reaches an event parks it in its slot and is refilled from Q_TRACK.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -114,12 +118,11 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     float pdf[4];
     sample_visible_wavelengths<TR::EXACT>(lu, ln.lambda, pdf);
     lc = make_lambda_ctx<TR::NCH>(mv, ln.lambda);
-    float f0, f1, l0, l1;
+    float f0, f1;
     smp.get2d(&f0, &f1);  // GetCameraSample: GetPixel2D, samplers.h:797-814
     float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
-    smp.get1d();          // time
-    smp.get2d(&l0, &l1);  // lens
+    smp.skip(3);          // time (Get1D), lens (Get2D): a pinhole camera reads neither
     // cameraFromRaster(pFilm): Transform::operator()(Point3f), util/transform.h:314-323
     const float *c = rp.cfr;
     float xp = c[0] * pfx + c[1] * pfy + c[2] * 0.f + c[3];
@@ -407,7 +410,7 @@ __host__ __device__ inline PoolLayout pool_layout(unsigned maj_bytes, unsigned p
 #define AVR_CTA_THREADS 512  // one 512-thread CTA per SM with one pool: 1.6 % faster than two of 256 (fuller batches)
 #endif
 #ifndef AVR_CTA_THREADS_FAST
-// FAST scalar kernels with the independent sampler fit 96 registers without a spill: 5 warps per scheduler instead
+// FAST scalar kernels (either sampler) fit 96 registers without a spill: 5 warps per scheduler instead
 // of 4 hide more of the fetch latency (8 spp: 512 threads 19.1 ms, 576 17.9, 640 17.05, 704 17.9 (spills), 768 17.9);
 // the EXACT kernels spill below 123 registers and lose (512: 52.1 ms, 576: 55.7, 640: 53.6, 704: 59.3)
 #define AVR_CTA_THREADS_FAST 640
@@ -417,7 +420,7 @@ struct KernelCfg {
     // achromatic scalar grids: AVR_MIN_BLOCKS CTAs of 256 threads (<= 128 registers); the chromatic and general
     // kernels need 144..181 registers: one CTA per SM with as many warps as the register file holds
     static constexpr bool kLean = TR::NCH == 1 && !TR::GENERAL;
-    static constexpr int kLeanThreads = (!TR::EXACT && !TR::ZSOBOL) ? AVR_CTA_THREADS_FAST : AVR_CTA_THREADS;
+    static constexpr int kLeanThreads = !TR::EXACT ? AVR_CTA_THREADS_FAST : AVR_CTA_THREADS;
     static constexpr int kThreads = kLean ? kLeanThreads : 384;  // (not lean) 3 warps per scheduler: 168-register cap
 #ifdef AVR_LEAN_MIN_BLOCKS
     static constexpr int kMinBlocks = kLean ? AVR_LEAN_MIN_BLOCKS : 1;
@@ -514,9 +517,8 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             const V3 p = ln.fe.point(ln.cur_tMin);
             const V3 wo = -ln.fe.d;
             PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
-            float ul0, ul1, ua, ub;
-            smp.get1d();            // light choice (single light, p = 1)
-            smp.get2d(&ul0, &ul1);  // uLight
+            float ua, ub;
+            smp.skip(3);  // light choice (Get1D: one light, p = 1) and uLight (Get2D: unused by a delta light)
             const V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
             const float two_r = 2 * rp.scene_radius;
             bool lit = false;
@@ -549,9 +551,7 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
             V3 p = ln.fe.point(ln.cur_tMin);
             {
                 PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
-                float ul0, ul1;
-                smp.get1d();            // light choice (single light, p = 1)
-                smp.get2d(&ul0, &ul1);  // uLight
+                smp.skip(3);  // light choice (Get1D: one light, p = 1) and uLight (Get2D: unused by a delta light)
             }
             V3 wi = v3(rp.light_dir[0], rp.light_dir[1], rp.light_dir[2]);
             float two_r = 2 * rp.scene_radius;
@@ -659,10 +659,15 @@ AVR_DEV void event_batch(const MediumView &mv, const RenderParams &rp, const Poo
                         hash0 = hash_v3(o);
                         hash1 = hash_v3(d);
                     } else {
+                        // the reference seeds the tracking RNG with Hash() of two sampler draws and takes u from a
+                        // third (:985-988): the hash throws the draws' stratification away, so FAST hashes the
+                        // path's identity and dimension instead of paying three ZSobol sample-index computations
                         PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, ln.px, ln.py, ln.samp};
-                        hash0 = hash_float(smp.get1d());
-                        hash1 = hash_float(smp.get1d());
-                        smp.get1d();
+                        const uint64_t id = ((uint64_t)(uint32_t)ln.py << 44) ^ ((uint64_t)(uint32_t)ln.px << 24) ^
+                                            (uint64_t)(uint32_t)ln.samp ^ ((uint64_t)(uint32_t)rp.smp.seed << 52);
+                        hash0 = mix_bits(id ^ (ln.srng.state * 0x9e3779b97f4a7c15ull));
+                        hash1 = mix_bits(hash0 + 0xda942042e4dd58b5ull);
+                        smp.skip(3);
                     }
                     ln.trng.set_sequence(hash0, hash1);
                 }

@@ -121,6 +121,12 @@ AVR_DEV void ldg256(const float4 *p, float4 &a, float4 &b) {
     asm volatile("ld.global.nc.L2::256B.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
                  : "l"(p));
+#elif AVR_USE_LDG256 == 3
+    // as 1, and the octet does not allocate in L1: a random 32-byte fetch is never reused, while the (small, hot)
+    // majorant grid is served from the ~28 KB of L1 the path pool leaves
+    asm volatile("ld.global.nc.L1::no_allocate.L2::256B.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
 #elif AVR_USE_LDG256 == 2
     // one 256-bit load, no prefetch hint: DRAM traffic = the 32-byte sector of the cell
     asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"

@@ -426,6 +426,24 @@ def run_graph(args, w, rank, world, local_rank, base):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     dt = float(tt[0])
     value = n * bounces * args.steps / dt / 1e6
+    # N > 1: what the step costs WITHOUT the collective — the same `bounces` SpMVs over this rank's rows, no
+    # all-gather, no finiteness pass (max over ranks) — so that the line names the all-gather's share of the step
+    spmv_only_ms = None
+    if world > 1:
+        chunk = (n + world - 1) // world
+        r0, r1 = min(rank * chunk, n), min((rank + 1) * chunk, n)
+        nxt = torch.empty(n, dtype=torch.float32, device=dev)
+        flag = torch.tensor([0, 2 ** 31 - 1], dtype=torch.int32, device=dev)
+        for _ in range(3):
+            g.spmv_rows_device(L0.data_ptr(), nxt.data_ptr(), r0, r1, flag.data_ptr())
+        sync_all()
+        t = time.perf_counter()
+        for _ in range(args.steps * bounces):
+            g.spmv_rows_device(L0.data_ptr(), nxt.data_ptr(), r0, r1, flag.data_ptr())
+        torch.cuda.synchronize()
+        ts = torch.tensor([time.perf_counter() - t], dtype=torch.float64, device=dev)
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        spmv_only_ms = float(ts[0]) / args.steps * 1e3
     # e2e: host vectors through avr_graph_propagate (rank 0 alone: the host-buffer entry is single-GPU)
     e2e = None
     if rank == 0:
@@ -446,6 +464,12 @@ def run_graph(args, w, rank, world, local_rank, base):
                     "e2e": {"value": e2e, "unit": base["unit"], "h2d_bytes_per_step": 4 * n, "d2h_bytes_per_step": 4 * n,
                             "note": "avr_graph_propagate on rank 0 (host L0 / total)"},
                     "gpu_launches": args.steps * (bounces + 2),
+                    "collective": None if spmv_only_ms is None else {
+                        "spmv_only_ms_per_step": spmv_only_ms,
+                        "allgather_and_checks_share": max(0.0, 1.0 - spmv_only_ms / (dt / args.steps * 1e3)),
+                        "bytes_gathered_per_bounce": 4 * n,
+                        "note": "share of the step that is not this rank's SpMV rows: one in-place ncclAllGather of "
+                                "the 4 n-byte vector per bounce plus the finiteness pass over it"},
                     "roofline": {"bound": "hbm", "kernel": "k_spmv", "achieved": achieved, "peak": peaks["hbm_gbs"],
                                  "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
                                  "algorithmic_bytes": alg,

@@ -35,11 +35,13 @@ def main():
     H, W = rd.height, rd.width
     for exact in (1, 0):
         film = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
+        torch.cuda.synchronize()   # the fill runs on torch's stream, the render on the library's: order them
         ctx.render_volpath_device(med, sharding.shard_samples(rd.with_(exact_math=exact), rank, world, 3), film.data_ptr())
         torch.cuda.synchronize()
         sharding.reduce_film(film, dst=0)
         if rank == 0:
             ref = torch.zeros_like(film)
+            torch.cuda.synchronize()
             ctx.render_volpath_device(med, rd.with_(exact_math=exact, spp=3 * world), ref.data_ptr())
             torch.cuda.synchronize()
             same = torch.allclose(film, ref, rtol=1e-12, atol=1e-300) and bool((film[..., 3] == 3 * world).all())
@@ -72,6 +74,7 @@ def main():
         film, _ = comm.render_volpath(med, full)
         if rank == 0:
             ref = torch.zeros((H, W, 4), dtype=torch.float64, device=dev)
+            torch.cuda.synchronize()
             ctx.render_volpath_device(med, full, ref.data_ptr())
             torch.cuda.synchronize()
             same = np.allclose(film, ref.cpu().numpy(), rtol=1e-12, atol=1e-300) and bool((film[..., 3] == 3 * world).all())
@@ -82,6 +85,7 @@ def main():
     for bounces, scale in ((8, 1.0), (0, 1.0), (25, 3e7)):
         g2 = g if scale == 1.0 else ctx.create_graph(rowptr, col, (val * scale).astype(np.float32))
         total = torch.full((n,), float("nan"), device=dev)
+        torch.cuda.synchronize()
         for rep in range(2):   # second call: the cached CUDA graph
             it = comm.propagate(g2, L0d.data_ptr(), bounces, total.data_ptr())
         torch.cuda.synchronize()

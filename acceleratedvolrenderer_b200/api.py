@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_graph_light_vector", "avr_graph_build_free", "avr_built_graph_free", "avr_debug_math",
-    "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world",
+    "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world", "avr_comm_graph_exchange",
     "avr_render_volpath_multi", "avr_graph_propagate_multi",
 ]
 
@@ -287,6 +287,10 @@ class Comm:
                                                           C.c_void_p(total_ptr), C.byref(it) if want_iters else None,
                                                           C.c_void_p(stream or 0)))
         return int(it.value)
+
+    def graph_exchange(self):
+        """1: SpMV writes into the peers' memory; -1: ncclAllGather per bounce; 0: not decided yet."""
+        return int(self.lib.avr_comm_graph_exchange(self.h))
 
     def row_range(self, n):
         chunk = (n + self.world - 1) // self.world

@@ -119,6 +119,9 @@ extern "C" void avr_comm_destroy(avr_comm *cm) {
     if (!cm) return;
     cudaSetDevice(cm->ctx->device);
     if (cm->exec) cudaGraphExecDestroy(cm->exec);
+    for (int p = 0; p < AVR_P2P_MAX_WORLD; ++p)
+        if (cm->p2p_base[p] && p != cm->rank && cm->p2p_ipc[p]) cudaIpcCloseMemHandle(cm->p2p_base[p]);
+    if (cm->rank < AVR_P2P_MAX_WORLD) cudaFree(cm->p2p_base[cm->rank]);
     cudaFree(cm->d_gather[0]);
     cudaFree(cm->d_gather[1]);
     cudaFree(cm->d_flags);
@@ -128,6 +131,7 @@ extern "C" void avr_comm_destroy(avr_comm *cm) {
 
 extern "C" int32_t avr_comm_rank(const avr_comm *cm) { return cm ? cm->rank : -1; }
 extern "C" int32_t avr_comm_world(const avr_comm *cm) { return cm ? cm->world : 0; }
+extern "C" int32_t avr_comm_graph_exchange(const avr_comm *cm) { return cm ? cm->p2p_state : 0; }
 
 extern "C" avr_status avr_render_volpath_multi(avr_comm *cm, avr_medium *m, const avr_render_desc *d, double *film,
                                                avr_render_stats *stats) {

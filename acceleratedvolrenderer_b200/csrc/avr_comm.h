@@ -6,6 +6,8 @@
 
 #include "avr_internal.h"
 
+#define AVR_P2P_MAX_WORLD 16
+
 namespace avr {
 
 struct NcclApi {
@@ -36,6 +38,13 @@ struct avr_comm {
     int32_t *d_flags = nullptr;
     cudaGraphExec_t exec = nullptr;
     const void *exec_key[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // Fused SpMV + exchange over peer memory (avr_graph.cu, k_spmv_p2p): ONE allocation per rank
+    // {vector[2][padded], sync words}, mapped into every peer (cudaIpc* between processes, direct peer access
+    // between the threads of one process).  p2p_state: 0 untried, 1 in use, -1 unavailable (NCCL all-gather path).
+    int p2p_state = 0;
+    char *p2p_base[AVR_P2P_MAX_WORLD] = {};   // [rank] = own block (cudaMalloc), others = mapped peers
+    bool p2p_ipc[AVR_P2P_MAX_WORLD] = {};     // opened with cudaIpcOpenMemHandle (to be closed)
+    size_t p2p_padded = 0;
 };
 
 #define AVR_NCCL(cm, call)                                                                              \

@@ -9,6 +9,8 @@
 #include <numeric>
 #include <string>
 
+#include <unistd.h>
+
 #include "avr_comm.h"
 #include "avr_render_host.h"
 
@@ -531,6 +533,222 @@ __global__ void k_multi_init(const float *__restrict__ L0, float *__restrict__ c
     }
 }
 
+
+// ---- SpMV fused with its exchange: the new vector is written straight into every peer's copy ------------------
+// Every rank owns ONE block {vector[2][padded] floats, SYNC_WORDS ints} that all peers have mapped (NVLink /
+// NVSwitch peer memory).  A bounce is k_spmv_p2p (rows of this rank; each row's result is stored into the `next`
+// vector of EVERY rank, so the transfer rides along with the arithmetic, 128 bytes per warp store) followed by
+// k_p2p_barrier (a release/acquire handshake over the peers' sync words).  No NCCL call, no staging copy, no
+// separate finiteness pass: a rank that produces a NaN/Inf posts the iteration into slot [rank] of every peer's
+// `bad` words, which all ranks read after the barrier — the same verdict everywhere, as the reference's stop needs.
+struct PeerTable {
+    char *base[AVR_P2P_MAX_WORLD];
+    int world, rank;
+    unsigned long long padded;
+};
+enum { SYNC_ARRIVE = 0, SYNC_BAD = AVR_P2P_MAX_WORLD, SYNC_EPOCH = 2 * AVR_P2P_MAX_WORLD, SYNC_TIMEOUT = SYNC_EPOCH + 1,
+       SYNC_WORDS = 64 };
+AVR_DEV float *p2p_vec(const PeerTable &t, int p, int which) {
+    return reinterpret_cast<float *>(t.base[p]) + size_t(which) * t.padded;
+}
+AVR_DEV int *p2p_sync(const PeerTable &t, int p) { return reinterpret_cast<int *>(reinterpret_cast<float *>(t.base[p]) + 2 * t.padded); }
+AVR_DEV int p2p_first_bad(const PeerTable &t) {
+    const volatile int *s = p2p_sync(t, t.rank) + SYNC_BAD;
+    int m = 0x7fffffff;
+    for (int p = 0; p < t.world; ++p) m = min(m, s[p]);
+    return m;
+}
+AVR_DEV void st_release_sys(int *p, int v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+AVR_DEV int ld_acquire_sys(const int *p) {
+    int v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+AVR_DEV unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// One warp.  Everything this GPU wrote before (earlier kernels of the stream included) is released to the peers with
+// the arrival word; passing means every peer has arrived, i.e. all their stores into this GPU's block are visible.
+// A peer that never arrives (dead process) trips the 10 s timeout instead of hanging the GPU.
+__global__ void k_p2p_barrier(PeerTable t) {
+    const int lane = threadIdx.x;
+    int *mine = p2p_sync(t, t.rank);
+    const int e = *(volatile int *)(mine + SYNC_EPOCH) + 1;
+    __threadfence_system();
+    if (lane < t.world) st_release_sys(p2p_sync(t, lane) + SYNC_ARRIVE + t.rank, e);
+    if (lane < t.world) {
+        const unsigned long long t0 = global_timer_ns();
+        while (ld_acquire_sys(mine + SYNC_ARRIVE + lane) - e < 0) {
+            if (global_timer_ns() - t0 > 10000000000ull) {
+                mine[SYNC_TIMEOUT] = 1;
+                break;
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncwarp();
+    if (lane == 0) *(volatile int *)(mine + SYNC_EPOCH) = e;
+}
+
+// total rows = L0 (bounce 0 reads L0 itself: no copy into the exchanged vectors), and this rank's `bad` slot reset on
+// every peer (the writer of a slot resets it: a later post of the same call follows it on the same path)
+__global__ void k_p2p_init(PeerTable t, const float *__restrict__ L0, float *__restrict__ total, int r0, int r1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < t.world) {
+        p2p_sync(t, i)[SYNC_BAD + t.rank] = 0x7fffffff;
+        __threadfence_system();
+    }
+    if (r0 + i < r1) total[r0 + i] = L0[r0 + i];
+}
+
+__global__ void __launch_bounds__(kRowsPerCta)
+k_spmv_p2p(PeerTable t, const float *__restrict__ L0, const int64_t *__restrict__ rowptr, const int32_t *__restrict__ col,
+           const float *__restrict__ val, float *__restrict__ total, int row_begin, int row_end, int iteration, int add_prev) {
+    __shared__ float s_prod[kChunk];
+    if (p2p_first_bad(t) < iteration) return;  // an EARLIER iteration was invalid: the reference has stopped
+    const float *__restrict__ x = iteration == 0 ? L0 : p2p_vec(t, t.rank, iteration & 1);
+    int r0 = row_begin + blockIdx.x * kRowsPerCta;
+    int r1 = min(r0 + kRowsPerCta, row_end);
+    int r = r0 + threadIdx.x;
+    bool have = r < r1;
+    int64_t rs = 0, re = 0;
+    if (have) { rs = rowptr[r]; re = rowptr[r + 1]; }
+    int64_t k0 = rowptr[r0], k1 = rowptr[r1];
+    float acc = 0;
+    for (int64_t c0 = k0; c0 < k1; c0 += kChunk) {
+        int64_t c1 = min(c0 + (int64_t)kChunk, k1);
+        for (int64_t k = c0 + threadIdx.x; k < c1; k += kRowsPerCta) s_prod[k - c0] = val[k] * x[col[k]];
+        __syncthreads();
+        if (have) {
+            int64_t a = max(rs, c0), b = min(re, c1);
+            for (int64_t k = a; k < b; ++k) acc += s_prod[k - c0];
+        }
+        __syncthreads();
+    }
+    if (have) {
+        const int nxt = (iteration + 1) & 1;
+        for (int p = 0; p < t.world; ++p) p2p_vec(t, p, nxt)[r] = acc;  // the exchange: one coalesced store per peer
+        if (isnan(acc) || isinf(acc))
+            for (int p = 0; p < t.world; ++p) atomicMin_system(p2p_sync(t, p) + SYNC_BAD + t.rank, iteration);
+        if (add_prev) total[r] += x[r];
+    }
+}
+
+__global__ void k_axpy_p2p(PeerTable t, int which, float *__restrict__ total, int row_begin, int row_end) {
+    if (p2p_first_bad(t) != 0x7fffffff) return;
+    int r = row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < row_end) total[r] += p2p_vec(t, t.rank, which)[r];
+}
+
+}  // namespace
+
+namespace {
+
+struct P2pInfo {  // what a rank tells the others about its block
+    cudaIpcMemHandle_t handle;
+    long long pid;
+    void *ptr;
+    int device, ok;
+    char pad[128 - sizeof(cudaIpcMemHandle_t) - sizeof(long long) - sizeof(void *) - 2 * sizeof(int)];
+};
+static_assert(sizeof(P2pInfo) == 128, "P2pInfo is exchanged as 128 bytes");
+
+void p2p_release(avr_comm *cm) {
+    for (int p = 0; p < AVR_P2P_MAX_WORLD; ++p) {
+        if (cm->p2p_base[p] && p != cm->rank && cm->p2p_ipc[p]) cudaIpcCloseMemHandle(cm->p2p_base[p]);
+        if (p != cm->rank) cm->p2p_base[p] = nullptr;
+        cm->p2p_ipc[p] = false;
+    }
+    if (cm->rank < AVR_P2P_MAX_WORLD) {
+        cudaFree(cm->p2p_base[cm->rank]);
+        cm->p2p_base[cm->rank] = nullptr;
+    }
+    cm->p2p_padded = 0;
+}
+
+// Allocate this rank's block, exchange IPC handles through the communicator, map every peer.  Collective: every rank
+// calls it with the same `padded`, and all ranks reach the same verdict (p2p_state 1 or -1).
+avr_status p2p_setup(avr_comm *cm, size_t padded, cudaStream_t s) {
+    avr_ctx *ctx = cm->ctx;
+    const int world = cm->world;
+    if (cm->p2p_state == 1 && cm->p2p_padded >= padded) return AVR_OK;
+    if (cm->p2p_state == -1) return AVR_OK;
+    if (cm->exec) { cudaGraphExecDestroy(cm->exec); cm->exec = nullptr; }
+    p2p_release(cm);
+    int ok = (ctx->knobs.graph_p2p && world > 1 && world <= AVR_P2P_MAX_WORLD) ? 1 : 0;
+    const size_t bytes = 2 * padded * sizeof(float) + SYNC_WORDS * sizeof(int);
+    char *own = nullptr;
+    P2pInfo mine{};
+    if (ok) {
+        if (cudaMalloc(&own, bytes) != cudaSuccess) { cudaGetLastError(); ok = 0; own = nullptr; }
+        else {
+            cudaMemsetAsync(own, 0, bytes, s);
+            if (cudaIpcGetMemHandle(&mine.handle, own) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+        }
+    }
+    mine.pid = (long long)getpid();
+    mine.ptr = own;
+    mine.device = ctx->device;
+    mine.ok = ok;
+    // exchange (device staging: NCCL moves device memory)
+    std::vector<P2pInfo> all(world);
+    char *d_info = nullptr;
+    AVR_CUDA(ctx, cudaMalloc(&d_info, sizeof(P2pInfo) * world));
+    cudaError_t e = cudaMemcpyAsync(d_info + sizeof(P2pInfo) * cm->rank, &mine, sizeof(P2pInfo), cudaMemcpyHostToDevice, s);
+    ncclResult_t nr = ncclSuccess;
+    if (e == cudaSuccess) nr = cm->api->AllGather(d_info + sizeof(P2pInfo) * cm->rank, d_info, sizeof(P2pInfo), ncclChar, cm->comm, s);
+    if (e == cudaSuccess && nr == ncclSuccess) e = cudaMemcpyAsync(all.data(), d_info, sizeof(P2pInfo) * world, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess || nr != ncclSuccess) {
+        cudaFree(d_info); cudaFree(own);
+        if (nr != ncclSuccess) return set_err(ctx, AVR_ERR_NCCL, std::string("ncclAllGather (peer handles): ") + cm->api->GetErrorString(nr));
+        return set_cuda_err(ctx, e, "peer handle exchange");
+    }
+    for (int p = 0; p < world && ok; ++p) ok = ok && all[p].ok;
+    if (ok) {
+        cm->p2p_base[cm->rank] = own;
+        for (int p = 0; p < world && ok; ++p) {
+            if (p == cm->rank) continue;
+            if (all[p].pid == mine.pid) {  // a thread of this process (avr_comm_init_all): direct peer access
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, ctx->device, all[p].device);
+                cudaError_t pe = can ? cudaDeviceEnablePeerAccess(all[p].device, 0) : cudaErrorInvalidDevice;
+                if (pe == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); pe = cudaSuccess; }
+                if (pe != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+                cm->p2p_base[p] = (char *)all[p].ptr;
+            } else {
+                void *mapped = nullptr;
+                if (cudaIpcOpenMemHandle(&mapped, all[p].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError(); ok = 0; break;
+                }
+                cm->p2p_base[p] = (char *)mapped;
+                cm->p2p_ipc[p] = true;
+            }
+        }
+    }
+    // all ranks must take the same path: the minimum of the local verdicts
+    int *d_ok = reinterpret_cast<int *>(d_info);
+    e = cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) nr = cm->api->AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, cm->comm, s);
+    if (e == cudaSuccess && nr == ncclSuccess) e = cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d_info);
+    if (nr != ncclSuccess) return set_err(ctx, AVR_ERR_NCCL, std::string("ncclAllReduce (peer verdict): ") + cm->api->GetErrorString(nr));
+    if (e != cudaSuccess) return set_cuda_err(ctx, e, "peer verdict");
+    if (!ok) {
+        if (!cm->p2p_base[cm->rank]) cudaFree(own);
+        p2p_release(cm);
+        cm->p2p_state = -1;
+        return AVR_OK;
+    }
+    cm->p2p_padded = padded;
+    cm->p2p_state = 1;
+    return AVR_OK;
+}
+
 }  // namespace
 
 extern "C" avr_status avr_graph_propagate_multi(avr_comm *cm, avr_graph *g, const float *L0_dev, int32_t bounces,
@@ -546,6 +764,55 @@ extern "C" avr_status avr_graph_propagate_multi(avr_comm *cm, avr_graph *g, cons
     const int chunk = (n + world - 1) / world;
     const size_t padded = size_t(chunk) * world;
     const int r0 = std::min(cm->rank * chunk, n), r1 = std::min((cm->rank + 1) * chunk, n);
+    // the fused path: SpMV writes the new vector into every peer's block (p2p_setup is collective; all ranks agree)
+    if (world > 1 && cm->p2p_state >= 0) {
+        avr_status pst = p2p_setup(cm, padded, s);
+        if (pst != AVR_OK) return pst;
+    }
+    if (cm->p2p_state == 1 && world > 1) {
+        PeerTable t{};
+        for (int p = 0; p < world; ++p) t.base[p] = cm->p2p_base[p];
+        t.world = world; t.rank = cm->rank; t.padded = cm->p2p_padded;
+        const void *key[5] = {g->d_val, L0_dev, total_dev, (const void *)(intptr_t)(bounces + (1 << 20)), (const void *)s};
+        if (!cm->exec || std::memcmp(key, cm->exec_key, sizeof(key)) != 0) {
+            if (cm->exec) { cudaGraphExecDestroy(cm->exec); cm->exec = nullptr; }
+            AVR_CUDA(ctx, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+            // nobody may still read or write the previous call's vectors once this one starts
+            k_p2p_barrier<<<1, 32, 0, s>>>(t);
+            k_p2p_init<<<blocks_for(std::max(r1 - r0, world), 256), 256, 0, s>>>(t, L0_dev, total_dev, r0, r1);
+            for (int it = 0; it < bounces; ++it) {
+                if (r1 > r0)
+                    k_spmv_p2p<<<blocks_for(r1 - r0, kRowsPerCta), kRowsPerCta, 0, s>>>(t, L0_dev, g->d_rowptr, g->d_col, g->d_val, total_dev,
+                                                                                        r0, r1, it, it > 0 ? 1 : 0);
+                k_p2p_barrier<<<1, 32, 0, s>>>(t);
+            }
+            if (bounces > 0 && r1 > r0) k_axpy_p2p<<<blocks_for(r1 - r0, 256), 256, 0, s>>>(t, bounces & 1, total_dev, r0, r1);
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamEndCapture(s, &graph);
+            avr_status st = AVR_OK;
+            if (e != cudaSuccess) st = set_cuda_err(ctx, e, "cudaStreamEndCapture");
+            if (st == AVR_OK) {
+                e = cudaGraphInstantiate(&cm->exec, graph, 0);
+                if (e != cudaSuccess) st = set_cuda_err(ctx, e, "cudaGraphInstantiate");
+            }
+            if (graph) cudaGraphDestroy(graph);
+            if (st != AVR_OK) { cm->exec = nullptr; return st; }
+            std::memcpy(cm->exec_key, key, sizeof(key));
+        }
+        AVR_CUDA(ctx, cudaGraphLaunch(cm->exec, s));
+        if (iters_done) {
+            int32_t sync[SYNC_WORDS];
+            AVR_CUDA(ctx, cudaMemcpyAsync(sync, cm->p2p_base[cm->rank] + 2 * cm->p2p_padded * sizeof(float), sizeof(sync),
+                                          cudaMemcpyDeviceToHost, s));
+            AVR_CUDA(ctx, cudaStreamSynchronize(s));
+            if (sync[SYNC_TIMEOUT])
+                return set_err(ctx, AVR_ERR_NCCL, "avr_graph_propagate_multi: a peer GPU did not reach the exchange barrier within 10 s");
+            int first_bad = 0x7fffffff;
+            for (int p = 0; p < world; ++p) first_bad = std::min(first_bad, sync[SYNC_BAD + p]);
+            *iters_done = first_bad == 0x7fffffff ? bounces : first_bad;
+        }
+        return AVR_OK;
+    }
     if (cm->gather_floats < padded) {
         if (cm->exec) { cudaGraphExecDestroy(cm->exec); cm->exec = nullptr; }
         cudaFree(cm->d_gather[0]); cudaFree(cm->d_gather[1]);

@@ -19,6 +19,9 @@ struct avr_knobs {
     // FAST majorant grid of a medium created under this context: c x c x c reference cells per FAST cell
     // (AVR_FAST_MAJ_COARSEN; 1 = the reference's grid)
     int fast_maj_coarsen = 2;
+    // avr_graph_propagate_multi: 1 = exchange the vector inside the SpMV kernel over peer memory when the GPUs can
+    // map each other (AVR_GRAPH_P2P, default 1); 0 = always ncclAllGather
+    int graph_p2p = 1;
 };
 // What launch_render settled on for one kernel variant (function pointer): shared-memory opt-in done, occupancy
 // queried, pool sized — once per context, not per call.

@@ -65,6 +65,7 @@ extern "C" avr_status avr_ctx_create(int device, avr_ctx **out) {
         k.threads = env_int("AVR_THREADS", 0, 0, 1024);
         k.pool = env_int("AVR_POOL", 0, 0, 4096);
         k.fast_maj_coarsen = env_int("AVR_FAST_MAJ_COARSEN", k.fast_maj_coarsen, 1, 16);
+        k.graph_p2p = env_int("AVR_GRAPH_P2P", k.graph_p2p, 0, 1);
     }
     AVR_CUDA(nullptr, cudaSetDevice(device));
     cudaDeviceProp prop;

@@ -466,17 +466,20 @@ def run_graph(args, w, rank, world, local_rank, base):
                     "gpu_launches": args.steps * (bounces + 2),
                     "collective": None if spmv_only_ms is None else {
                         "spmv_only_ms_per_step": spmv_only_ms,
-                        "allgather_and_checks_share": max(0.0, 1.0 - spmv_only_ms / (dt / args.steps * 1e3)),
+                        "exchange_share": max(0.0, 1.0 - spmv_only_ms / (dt / args.steps * 1e3)),
                         "bytes_gathered_per_bounce": 4 * n,
-                        "note": "share of the step that is not this rank's SpMV rows: one in-place ncclAllGather of "
-                                "the 4 n-byte vector per bounce plus the finiteness pass over it"},
+                        "exchange": {1: "peer memory: k_spmv_p2p stores every row into all ranks' vectors, "
+                                        "k_p2p_barrier between bounces", -1: "ncclAllGather per bounce"}.get(comm.graph_exchange(), "?"),
+                        "note": "share of the step that is not this rank's SpMV arithmetic (the exchange and its "
+                                "synchronisation); spmv_only = the same SpMVs writing to local memory alone"},
                     "roofline": {"bound": "hbm", "kernel": "k_spmv", "achieved": achieved, "peak": peaks["hbm_gbs"],
                                  "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
                                  "algorithmic_bytes": alg,
-                                 "note": "whole step (SpMV + all-gather + checks) / (12 nnz + 16 N) bytes per bounce per GPU"},
+                                 "note": "whole step (SpMV + exchange + checks) / (12 nnz + 16 N) bytes per bounce per GPU"},
                     "clocks": clk})
-        out["config"]["parallelism"] = (f"vertex-range rows x{world}, ncclAllGather per bounce, one CUDA graph per step"
-                                        if world > 1 else "1 gpu")
+        how = "the exchange fused into the SpMV kernel over peer memory" if comm is not None and comm.graph_exchange() == 1 \
+            else "ncclAllGather per bounce"
+        out["config"]["parallelism"] = (f"vertex-range rows x{world}, {how}, one CUDA graph per step" if world > 1 else "1 gpu")
         print(json.dumps(out))
     if comm is not None:
         comm.close()

@@ -532,6 +532,11 @@ avr_status avr_comm_init_all(avr_ctx **ctx, int32_t n, avr_comm **out);
 void avr_comm_destroy(avr_comm *comm);
 int32_t avr_comm_rank(const avr_comm *comm);
 int32_t avr_comm_world(const avr_comm *comm);
+/* How avr_graph_propagate_multi exchanges the vector on this communicator: 1 = inside the SpMV kernel, over peer
+ * memory (every rank's vector block is mapped into every peer: cudaIpc* between processes, direct peer access
+ * between threads of one process); -1 = ncclAllGather per bounce (peer mapping unavailable, more than 16 ranks, or
+ * AVR_GRAPH_P2P=0 when the context was created); 0 = not decided yet (decided by the first propagation). */
+int32_t avr_comm_graph_exchange(const avr_comm *comm);
 
 /* avr_render_volpath over all ranks of `comm` (every rank calls it with the SAME desc; desc->rank / world are
  * overwritten): rank r renders the work items with item % world == r into its device film, one ncclReduce

@@ -161,3 +161,42 @@ def test_light_vector_edge_cases(ctx):
         md.graph_light_vector(rd, pos, **dict(kw, light_iterations=0))
     assert "at least one light ray iteration" in str(e.value)   # the reference's ErrorExit text
     md.close()
+
+
+def test_graph_side_work_shards_by_construction(ctx):
+    """the light vector shards by vertex range (a rank computes a slice of the
+    vertices, numbered for the sampler by `list_index`, and the slices ARE the whole vector, bit for bit), the graph
+    render by sample index or by rank partition like the volpath render (partial host films add up to the whole)."""
+    import math
+    dens = scenes.fbm_density(32, 32, 32, seed=4)
+    gd, rd = scenes.cloud_scene(dens, width=40, height=30, spp=6, sigma_t=14.0, albedo=0.95, g=0.0, max_depth=8)
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    radius = float(rd.c.boundary[3])
+    max_dist = radius * math.sqrt(3.0)
+    vr = max_dist * 2 / 1000 * 12.0
+    kw = dict(vertex_radius=vr, max_dist_to_center=max_dist, sampling_resolution=1024, lam=[450, 520, 610, 700])
+    built = md.build_free_graph(rd, bounds_center=[float(rd.c.boundary[i]) for i in range(3)], dimension_steps=60,
+                                iterations_per_step=4, max_depth=30, search_range_neighbours=4, **kw)
+    pos = built["pos"]; nv = pos.shape[0]
+    assert nv > 500
+    lkw = dict(light_iterations=4, points_on_radius=2, **kw)
+    idx = np.arange(nv, dtype=np.int32)
+    whole = md.graph_light_vector(rd, pos, list_index=idx, **lkw)
+    parts = [md.graph_light_vector(rd, pos[a:b], list_index=idx[a:b], **lkw) for a, b in ((0, nv // 3), (nv // 3, nv))]
+    assert np.array_equal(np.concatenate(parts).view(np.uint32), whole.view(np.uint32))
+    g = ctx.create_graph_from_edges(built["vsamples"], built["efrom"], built["eto"], built["esamples"])
+    tot, _ = g.compute_final_light(whole, 3)
+    g.set_vertices(pos, tot, built["vrange"], vr)
+    full, _ = ctx.render_graph(md, g, rd)
+    assert full[..., :3].sum() > 0 and np.all(full[..., 3] == rd.spp)
+    acc = np.zeros_like(full)
+    for r in range(3):
+        f, _ = ctx.render_graph(md, g, rd.with_(rank=r, world=3))
+        acc += f
+    assert np.allclose(acc, full, rtol=1e-12, atol=1e-300)
+    acc = np.zeros_like(full)
+    for a, b in ((0, 2), (2, 6)):
+        f, _ = ctx.render_graph(md, g, rd.with_(sample_begin=a, sample_end=b))
+        acc += f
+    assert np.allclose(acc, full, rtol=1e-12, atol=1e-300)
+    g.close(); md.close()

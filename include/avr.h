@@ -546,10 +546,13 @@ avr_status avr_render_volpath_multi(avr_comm *comm, avr_medium *m, const avr_ren
                                     avr_render_stats *stats);
 
 /* avr_graph_propagate_device with the rows of T split over the ranks (equal vertex ranges; every rank holds
- * the whole CSR): per bounce one SpMV over the rank's rows, ONE in-place ncclAllGather of the new vector, and a
- * finiteness test of the gathered vector on every rank (the reference's NaN/Inf stop needs no second
- * collective).  The whole bounce sequence is captured in a CUDA graph on first use: no host synchronisation
- * between bounces.  L0_dev: n floats (the same on every rank); total_dev: n floats of which THIS RANK'S rows
+ * the whole CSR).  Per bounce one SpMV over the rank's rows whose results are stored straight into EVERY rank's
+ * copy of the new vector over peer memory (NVLink / NVSwitch; the blocks are mapped once with cudaIpc*), then a
+ * release / acquire handshake between the GPUs; a rank that produces a NaN/Inf posts the iteration to all peers,
+ * so every rank reaches the reference's stop verdict without a collective.  Where peers cannot map each other
+ * (or with AVR_GRAPH_P2P=0): SpMV + one in-place ncclAllGather + a finiteness pass per bounce
+ * (avr_comm_graph_exchange tells which).  The whole bounce sequence is captured in a CUDA graph on first use: no
+ * host synchronisation between bounces.  Collective: every rank calls it with the same graph and bounce count.  L0_dev: n floats (the same on every rank); total_dev: n floats of which THIS RANK'S rows
  * [rank * ceil(n / world), ...) are written; iters_done as avr_graph_propagate_device.  Bit-identical to the
  * single-GPU result. */
 avr_status avr_graph_propagate_multi(avr_comm *comm, avr_graph *g, const float *L0_dev, int32_t bounces,

@@ -902,22 +902,6 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                     }
                 }
             }
-            if (!EX && ln.state == ST_SAMPLE) {
-                // FAST, after a null collision: fresh tau, tested against the rest of the current segment
-                float tau = neg_log1m(ln.trng.uniform());
-                float dtau = ln.sigma_maj[0] * (ln.seg_tMax - ln.cur_tMin);
-                bool hit = tau <= dtau;
-                float tt = ln.seg_tMax;
-                if (hit) tt = __fmaf_rn(tau, ftz_rcp(ln.sigma_maj[0]), ln.cur_tMin);
-                if (N > 1) ln.T_maj = ln.T_maj * exp_neg<false>(tt - ln.cur_tMin, ln.sigma_maj);
-                if (hit) {
-                    ln.cur_tMin = tt;
-                    if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
-                    if (Fetcher<TR>::kPrefetch) ln.fe.prefetch(mv, tt);
-                } else
-                    ln.u = tau - dtau;
-                ln.state = hit ? ST_COLLIDE : ST_WALK;
-            }
             if (EX && ln.state == ST_SAMPLE) {
                 // media.h:779-803: t = tMin + SampleExponential(u, sigma_maj[0]); u = rng.Uniform();
                 // T_maj *= FastExp(-(t - tMin) sigma_maj) at a collision, FastExp(-(tMax - tMin) sigma_maj) at the exit
@@ -1064,7 +1048,23 @@ AVR_DEV void track_mode(const MediumView &mv, const RenderParams &rp, const Pool
                 }
             }
         }
-
+        if (!EX && ln.state == ST_SAMPLE) {
+            // FAST, right after a null collision (same lanes, same trip): fresh tau, tested against the rest of the current
+            // segment.  A lane that goes back to walking has all the walk rounds of the next trip
+            float tau = neg_log1m(ln.trng.uniform());
+            float dtau = ln.sigma_maj[0] * (ln.seg_tMax - ln.cur_tMin);
+            bool hit = tau <= dtau;
+            float tt = ln.seg_tMax;
+            if (hit) tt = __fmaf_rn(tau, ftz_rcp(ln.sigma_maj[0]), ln.cur_tMin);
+            if (N > 1) ln.T_maj = ln.T_maj * exp_neg<false>(tt - ln.cur_tMin, ln.sigma_maj);
+            if (hit) {
+                ln.cur_tMin = tt;
+                if (Fetcher<TR>::kSplitFetch) ln.fe.request(mv, tt, ln.tapA, ln.tapB);
+                if (Fetcher<TR>::kPrefetch) ln.fe.prefetch(mv, tt);
+            } else
+                ln.u = tau - dtau;
+            ln.state = hit ? ST_COLLIDE : ST_WALK;
+        }
     }
 }
 

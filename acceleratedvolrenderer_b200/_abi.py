@@ -122,6 +122,10 @@ class avr_built_graph(C.Structure):
     ]
 
 
+class avr_filter_table(C.Structure):
+    _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("f", f32p)]
+
+
 class avr_render_desc(C.Structure):
     _fields_ = [
         ("width", C.c_int32), ("height", C.c_int32),
@@ -141,6 +145,7 @@ class avr_render_desc(C.Structure):
         ("max_component_value", C.c_float),
         ("rank", C.c_int32), ("world", C.c_int32),
         ("sampler", C.c_int32), ("randomize", C.c_int32),
+        ("filter", C.POINTER(avr_filter_table)),
     ]
 
 
@@ -330,6 +335,24 @@ SAMPLERS = {"independent": 0, "zsobol": 1}
 RANDOMIZE = {"none": 0, "permutedigits": 1, "fastowen": 2, "owen": 3}
 
 
+def gaussian_filter_table(radius=(1.5, 1.5), sigma=0.5):
+    """GaussianFilter (filters.h:84-120: Evaluate(p) = max(0, G(p.x) - G(r.x)) * max(0, G(p.y) - G(r.y)), G = the
+    normal density of std sigma) tabulated as FilterSampler's constructor does (filters.cpp:133-143), in fp32."""
+    f32 = np.float32
+    rx, ry = f32(radius[0]), f32(radius[1])
+    nx, ny = int(f32(32) * rx), int(f32(32) * ry)
+
+    def gauss(x, s):
+        # util/math.h Gaussian(x, mu = 0, sigma): 1 / sqrt(2 pi sigma^2) * FastExp(-x^2 / (2 sigma^2)) -- evaluated by
+        # the caller's checker where bit-exactness matters; here a float64 evaluation rounded to fp32
+        return 1.0 / np.sqrt(2 * np.pi * s * s) * np.exp(-(x * x) / (2 * s * s))
+    xs = (-rx + (np.arange(nx, dtype=f32) + f32(0.5)) / f32(nx) * (rx + rx)).astype(np.float64)
+    ys = (-ry + (np.arange(ny, dtype=f32) + f32(0.5)) / f32(ny) * (ry + ry)).astype(np.float64)
+    gx = np.maximum(0.0, gauss(xs, sigma) - gauss(float(rx), sigma))
+    gy = np.maximum(0.0, gauss(ys, sigma) - gauss(float(ry), sigma))
+    return np.outer(gy, gx).astype(f32)
+
+
 class RenderDesc:
     """Camera / light / film / sampler parameters of one volpath render (see avr_render_desc)."""
 
@@ -385,6 +408,20 @@ class RenderDesc:
         if s0 == 0 and s1 == 0:
             s1 = c.spp
         return x0, y0, x1, y1, s0, s1
+
+    def with_filter(self, table, radius):
+        """Variant with a tabulated pixel filter (avr_filter_table): table = [ny, nx] float32 values of the filter as
+        FilterSampler tabulates them (see filter_table()), radius = the filter's radius; table None = box filter."""
+        r = self.with_()
+        _set_arr(r.c.filter_radius, radius)
+        if table is None:
+            r.c.filter = None
+            r.filter_values = r.filter_c = None
+        else:
+            r.filter_values = _f32(table)
+            r.filter_c = avr_filter_table(int(r.filter_values.shape[1]), int(r.filter_values.shape[0]), _ptr(r.filter_values))
+            r.c.filter = C.pointer(r.filter_c)
+        return r
 
     def with_(self, **kw):
         """Shallow variant with some scalar fields of the C struct replaced."""

@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "avr_graph_file_write", "avr_graph_file_free", "avr_graph_sidecar_read", "avr_graph_sidecar_write", "avr_graph_sidecar_free", "avr_graph_destroy", "avr_graph_propagate", "avr_graph_propagate_device", "avr_graph_propagate_noalloc",
     "avr_graph_spmv_rows_device", "avr_graph_axpy_rows_device", "avr_graph_set_vertices", "avr_graph_connect",
     "avr_render_graph", "avr_graph_light_rays", "avr_graph_light_vector", "avr_graph_build_free", "avr_built_graph_free", "avr_debug_math",
-    "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world", "avr_comm_graph_exchange",
+    "avr_comm_unique_id", "avr_comm_init_rank", "avr_comm_init_all", "avr_comm_destroy", "avr_comm_rank", "avr_comm_world", "avr_comm_graph_exchange", "avr_filter_sample",
     "avr_render_volpath_multi", "avr_graph_propagate_multi",
 ]
 
@@ -207,6 +207,16 @@ class Context:
         self.check(self.lib.avr_render_graph(self.h, medium.h, graph.h, C.byref(rdesc.c), _p(wfr), _p(film, f64p),
                                              C.byref(stats)))
         return film, stats.as_dict()
+
+    def filter_sample(self, table, radius, u):
+        """FilterSampler::Sample through the render kernels' device code: (n, 3) = p.x, p.y, weight."""
+        from ._abi import avr_filter_table
+        table = _f32(table); u = _f32(u); n = u.size // 2
+        t = avr_filter_table(int(table.shape[1]), int(table.shape[0]), _p(table))
+        rad = (C.c_float * 2)(float(radius[0]), float(radius[1]))
+        out = np.empty((n, 3), dtype=np.float32)
+        self.check(self.lib.avr_filter_sample(self.h, C.byref(t), rad, _p(u), C.c_int64(n), _p(out)))
+        return out
 
     def film_resolve(self, rdesc: RenderDesc, film):
         rgb = np.zeros((rdesc.c.height, rdesc.c.width, 3), dtype=np.float32)

@@ -49,6 +49,12 @@ struct avr_ctx {
     size_t h_film_bytes = 0;
     cudaEvent_t ev_chunk[8] = {};
     float *d_tables = nullptr;  // light spectrum + sensor tables for the current render
+    // tabulated pixel filter of the current render (avr_filter_table -> packed sampling tables, avr_volpath.cuh)
+    float *d_filter = nullptr;
+    size_t d_filter_floats = 0;
+    std::vector<float> h_filter;
+    float4 *d_fsamples = nullptr;  // filter sample {p.x, p.y, weight, 0} per pixel sample of the current launch
+    size_t d_fsamples_count = 0;
 };
 
 struct avr_medium {

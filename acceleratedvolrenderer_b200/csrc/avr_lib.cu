@@ -90,6 +90,8 @@ extern "C" void avr_ctx_destroy(avr_ctx *ctx) {
     if (ctx->h_film) cudaFreeHost(ctx->h_film);
     for (cudaEvent_t e : ctx->ev_chunk) if (e) cudaEventDestroy(e);
     cudaFree(ctx->d_tables);
+    cudaFree(ctx->d_filter);
+    cudaFree(ctx->d_fsamples);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -67,9 +67,7 @@ AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double
     for (int i = 0; i < 4; ++i) lam[i] = ln.lambda[i];
     visible_wavelengths_pdf<TR::EXACT>(lam, pdf);
     if (rp.dump_samples) {
-        long long nsamp = rp.s1 - rp.s0;
-        long long idx = ((long long)(ln.py - rp.y0) * (rp.x1 - rp.x0) + (ln.px - rp.x0)) * nsamp + (ln.samp - rp.s0);
-        float *o = samples_out + idx * 12;
+        float *o = samples_out + sample_slot(rp, ln.px, ln.py, ln.samp) * 12;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { o[i] = L[i]; o[4 + i] = lam[i]; o[8 + i] = pdf[i]; }
         return;
@@ -92,10 +90,13 @@ AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double
         rgb[0] *= k; rgb[1] *= k; rgb[2] *= k;
     }
     double *px = film + 4 * ((size_t)ln.py * rp.width + ln.px);
-    if (rgb[0] != 0) atomicAdd(px + 0, (double)(1.f * rgb[0]));  // adding +-0 leaves the sum unchanged
-    if (rgb[1] != 0) atomicAdd(px + 1, (double)(1.f * rgb[1]));
-    if (rgb[2] != 0) atomicAdd(px + 2, (double)(1.f * rgb[2]));
-    atomicAdd(px + 3, 1.0);
+    // RGBFilm::AddSample: rgbSum[c] += weight * rgb[c] (a float product), weightSum += weight; box filter: weight 1
+    float w = 1.f;
+    if (__builtin_expect(rp.fsamples != nullptr, 0)) w = rp.fsamples[sample_slot(rp, ln.px, ln.py, ln.samp)].z;
+    if (rgb[0] != 0) atomicAdd(px + 0, (double)(w * rgb[0]));  // adding +-0 leaves the sum unchanged
+    if (rgb[1] != 0) atomicAdd(px + 1, (double)(w * rgb[1]));
+    if (rgb[2] != 0) atomicAdd(px + 2, (double)(w * rgb[2]));
+    atomicAdd(px + 3, (double)w);
 }
 
 // RayIntegrator::EvaluatePixelSample prologue (cpu/integrators.cpp:235-262): sampler start,
@@ -120,7 +121,16 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     lc = make_lambda_ctx<TR::NCH>(mv, ln.lambda);
     float f0, f1;
     smp.get2d(&f0, &f1);  // GetCameraSample: GetPixel2D, samplers.h:797-814
-    float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
+    float fx, fy;
+    if (__builtin_expect(rp.fsamples != nullptr, 0)) {
+        // tabulated filter (FilterSampler::Sample): sampled by the pre-pass from these same two draws
+        const float4 fs = rp.fsamples[sample_slot(rp, px, py, s)];
+        fx = fs.x;
+        fy = fs.y;
+    } else {
+        fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx);  // BoxFilter::Sample, filters.h:67-70
+        fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
+    }
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     smp.skip(3);          // time (Get1D), lens (Get2D): a pinhole camera reads neither
     // cameraFromRaster(pFilm): Transform::operator()(Point3f), util/transform.h:314-323

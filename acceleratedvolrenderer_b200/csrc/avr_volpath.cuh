@@ -16,6 +16,14 @@ struct RenderParams {
     int max_depth, seed;
     SamplerCfg smp;           // the integrator's sampler (independent | zsobol)
     float filter_rx, filter_ry;
+    // pixel filter sampled through a table (FilterSampler; avr_filter_table) or null = box.  Packed floats:
+    // f[ny*nx] | func = |f| [ny*nx] | conditional cdf [ny*(nx+1)] | conditional integrals [ny] | marginal func [ny] |
+    // marginal cdf [ny+1] | marginal integral [1]
+    const float *flt;
+    int fnx, fny;
+    // ... sampled for every pixel sample of the launch by a pre-pass (k_filter_prepass): {p.x, p.y, weight, 0} at
+    // sample_slot(px, py, samp); the render kernels only load it (no binary search in their instruction stream)
+    const float4 *fsamples;
     float cfr[16];   // cameraFromRaster (projective)
     float rfc[12];   // renderFromCamera (affine rows)
     float light_dir[3];
@@ -106,6 +114,49 @@ AVR_DEV bool boundary_hit_fast(const RenderParams &rp, V3 o, V3 d, float *t0, fl
     *t0 = a0;
     *t1 = a1;
     return a0 <= a1;
+}
+
+// FindInterval (util/math.h) over a CDF of `sz` entries: the last index with cdf[index] <= u, clamped to [0, sz - 2]
+AVR_DEV int find_interval_cdf(const float *cdf, int sz, float u) {
+    int size = sz - 2, first = 1;
+    while (size > 0) {
+        int half = size >> 1, middle = first + half;
+        bool pr = cdf[middle] <= u;
+        first = pr ? middle + 1 : first;
+        size = pr ? size - (half + 1) : half;
+    }
+    return min(max(first - 1, 0), sz - 2);
+}
+// PiecewiseConstant1D::Sample, util/sampling.h:657-675
+AVR_DEV float pc1d_sample(const float *func, const float *cdf, float func_int, int n, float lo, float hi, float u,
+                          float *pdf, int *offset) {
+    int o = find_interval_cdf(cdf, n + 1, u);
+    *offset = o;
+    float du = u - cdf[o];
+    if (cdf[o + 1] - cdf[o] > 0) du /= cdf[o + 1] - cdf[o];
+    *pdf = func_int > 0 ? func[o] / func_int : 0.f;
+    return lerp_exact((float(o) + du) / float(n), lo, hi);
+}
+// FilterSampler::Sample (filters.h:33-38) over PiecewiseConstant2D::Sample (util/sampling.h:760-769): the marginal
+// in y first, then the row's conditional in x; weight = f[pi] / (pdf_x * pdf_y)
+AVR_DEV void filter_sample(const float *flt, int nx, int ny, float rx, float ry, float u0, float u1, float *px, float *py,
+                           float *weight) {
+    const float *f = flt, *func = f + nx * ny, *ccdf = func + nx * ny, *cint = ccdf + ny * (nx + 1);
+    const float *mfunc = cint + ny, *mcdf = mfunc + ny, *mint = mcdf + ny + 1;
+    float pdf0, pdf1;
+    int ox, oy;
+    float d1 = pc1d_sample(mfunc, mcdf, mint[0], ny, -ry, ry, u1, &pdf1, &oy);
+    float d0 = pc1d_sample(func + oy * nx, ccdf + oy * (nx + 1), cint[oy], nx, -rx, rx, u0, &pdf0, &ox);
+    float pdf = pdf0 * pdf1;
+    *px = d0;
+    *py = d1;
+    *weight = f[oy * nx + ox] / pdf;
+}
+
+// index of pixel sample (px, py, samp) in per-sample buffers of a launch (sample dump, filter samples)
+AVR_DEV long long sample_slot(const RenderParams &rp, int px, int py, int samp) {
+    long long nsamp = rp.s1 - rp.s0;
+    return ((long long)(py - rp.y0) * (rp.x1 - rp.x0) + (px - rp.x0)) * nsamp + (samp - rp.s0);
 }
 
 template <typename TR>

@@ -253,12 +253,26 @@ avr_status avr_sample_tmaj_device(avr_medium *m, int mode, int exact_math, const
  * (cpu/integrators.cpp:72-232), RayIntegrator::EvaluatePixelSample (:235-298),
  * VolPathIntegrator::Li volume branch (:962-1106) and SampleLd (:1282-1399) for the scene class the
  * fork's graph pipeline accepts (src/graph/util.h:61-132): ONE grid medium inside ONE convex
- * boundary shape with Material "interface", ONE distant light, perspective camera, box pixel filter,
+ * boundary shape with Material "interface", ONE distant light, perspective camera, box pixel filter or a
+ * FilterSampler-tabulated one (gaussian / mitchell / sinc),
  * Sampler "independent" or "zsobol". */
 enum { AVR_BOUNDARY_SPHERE = 0, AVR_BOUNDARY_BOX = 1 };
 enum { AVR_SAMPLER_INDEPENDENT = 0, AVR_SAMPLER_ZSOBOL = 1 };
 /* RandomizeStrategy, util/lowdiscrepancy.h:261 (same order) */
 enum { AVR_RANDOMIZE_NONE = 0, AVR_RANDOMIZE_PERMUTE_DIGITS = 1, AVR_RANDOMIZE_FAST_OWEN = 2, AVR_RANDOMIZE_OWEN = 3 };
+
+/* A pixel filter that pbrt samples through its FilterSampler (filters.h:26-45, filters.cpp:133-147): "gaussian"
+ * (pbrt's default, scene.cpp:94), "mitchell", "sinc".  f = the filter tabulated as the FilterSampler constructor
+ * does it: nx = int(32 * radius.x), ny = int(32 * radius.y) values f(x, y) = filter.Evaluate(p) at
+ * p = domain.Lerp(((x + .5) / nx, (y + .5) / ny)), domain = [-radius, radius]^2, row-major (x fastest); the
+ * radius is avr_render_desc.filter_radius.  The library builds the PiecewiseConstant2D distribution from it
+ * (util/sampling.h:625-649,737-754) and samples it per camera sample exactly as FilterSampler::Sample /
+ * GetCameraSample do (samplers.h:797-814): pFilm = pPixel + p + 0.5, the sample is added to pixel pPixel alone with
+ * weight f[pi] / pdf (RGBFilm::AddSample, film.h:239-255: rgbSum += weight * rgb, weightSum += weight). */
+typedef struct avr_filter_table {
+    int32_t nx, ny;
+    const float *f;                  /* ny * nx floats, host memory */
+} avr_filter_table;
 
 typedef struct avr_render_desc {
     int32_t width, height;           /* full film resolution                                   */
@@ -271,7 +285,7 @@ typedef struct avr_render_desc {
     int32_t exact_math;              /* 1: restated CPU FastExp/logf/IEEE div (parity mode);
                                         0: ex2.approx / lg2.approx (reference's own GPU branch,
                                         util/math.h:451-452)                                   */
-    float filter_radius[2];          /* box filter radius (default 0.5)                        */
+    float filter_radius[2];          /* pixel filter radius (box default 0.5; gaussian default 1.5) */
     float camera_from_raster[16];    /* PerspectiveCamera, cameras.cpp:404-460                 */
     float render_from_camera[16];
     float light_dir[3];              /* direction TOWARDS the distant light (wi), render space */
@@ -291,7 +305,13 @@ typedef struct avr_render_desc {
                                         resolution, `randomize` and sampler_seed)               */
     int32_t randomize;               /* zsobol "randomization": AVR_RANDOMIZE_* (pbrt's default
                                         is fastowen, samplers.cpp:157); ignored for independent */
+    const avr_filter_table *filter;  /* NULL: BoxFilter of filter_radius (weight 1); else the tabulated filter */
 } avr_render_desc;
+
+/* FilterSampler::Sample for n points u (2 floats each) under `filter` / radius: out = {p.x, p.y, weight} per
+ * point, computed by the device code the render kernels run (parity probe). */
+avr_status avr_filter_sample(avr_ctx *ctx, const avr_filter_table *filter, const float radius[2], const float *u,
+                             int64_t n, float *out);
 
 typedef struct avr_render_stats {
     int64_t camera_rays;       /* pixel samples evaluated                                       */

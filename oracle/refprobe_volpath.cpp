@@ -180,15 +180,53 @@ void ref_film_add_samples(int32_t width, int32_t height, const float *sensor_rgb
 // camera.GenerateRayDifferential (cameras.cpp:428-490).
 // world_from_camera: row-major 4x4; screen_window = {xmin, ymin, xmax, ymax}.  rays: {o, d} per sample;
 // matrices: cameraFromRaster then renderFromCamera, row-major 4x4 each.
+// filter_cfg (may be NULL = box 0.5): {kind, radius.x, radius.y, p0, p1} as make_filter below; weights (may be NULL):
+// CameraSample::filterWeight per sample.
+static Filter make_filter(const float *cfg) {
+    if (!cfg) return new BoxFilter(Vector2f(0.5f, 0.5f));
+    Vector2f radius(cfg[1], cfg[2]);
+    switch (int(cfg[0])) {
+    case 1: return new GaussianFilter(radius, cfg[3]);         // "gaussian": sigma (filters.cpp:114, default 0.5)
+    case 2: return new MitchellFilter(radius, cfg[3], cfg[4]);  // "mitchell": B, C
+    case 3: return new LanczosSincFilter(radius, cfg[3]);      // "sinc": tau
+    default: return new BoxFilter(radius);
+    }
+}
+
+// Filter::Sample(u) of the reference's own filter objects: out = {p.x, p.y, weight} per point.
+void ref_filter_sample(const float *filter_cfg, const float *u, int64_t n, float *out) {
+    Filter filter = make_filter(filter_cfg);
+    for (int64_t i = 0; i < n; ++i) {
+        FilterSample fs = filter.Sample(Point2f(u[2 * i], u[2 * i + 1]));
+        out[3 * i] = fs.p.x; out[3 * i + 1] = fs.p.y; out[3 * i + 2] = fs.weight;
+    }
+}
+
+// The table FilterSampler's constructor builds (filters.cpp:133-143): nxny = {int(32 rx), int(32 ry)}; f may be NULL
+// to query the size first.
+void ref_filter_table(const float *filter_cfg, int32_t nxny[2], float *f) {
+    Filter filter = make_filter(filter_cfg);
+    Vector2f r = filter.Radius();
+    Bounds2f domain(Point2f(-r.x, -r.y), Point2f(r.x, r.y));
+    int nx = int(32 * r.x), ny = int(32 * r.y);
+    nxny[0] = nx; nxny[1] = ny;
+    if (!f) return;
+    for (int y = 0; y < ny; ++y)
+        for (int x = 0; x < nx; ++x) {
+            Point2f p = domain.Lerp(Point2f((x + 0.5f) / nx, (y + 0.5f) / ny));
+            f[y * nx + x] = filter.Evaluate(p);
+        }
+}
+
 void ref_camera_rays(const float world_from_camera[16], float fov, const float screen_window[4], int32_t width,
                      int32_t height, int32_t sampler_seed, int32_t spp, const int32_t *samples, int64_t n, float *rays,
-                     float *matrices) {
+                     float *matrices, const float *filter_cfg, float *weights) {
     static PBRTOptions opts;
     opts.disableTextureFiltering = true;
     opts.renderingSpace = RenderingCoordinateSystem::World;
     Options = &opts;
     Allocator alloc;
-    Filter filter = new BoxFilter(Vector2f(0.5f, 0.5f));
+    Filter filter = make_filter(filter_cfg);
     RGBFilm *f = (RGBFilm *)::operator new(sizeof(RGBFilm));
     std::memset((void *)f, 0, sizeof(RGBFilm));
     f->fullResolution = Point2i(width, height);
@@ -217,6 +255,7 @@ void ref_camera_rays(const float world_from_camera[16], float fov, const float s
         Float lu = sampler.Get1D();
         SampledWavelengths lambda = SampledWavelengths::SampleVisible(lu);
         CameraSample cs = GetCameraSample(sampler, pPixel, filter);
+        if (weights) weights[i] = cs.filterWeight;
         pstd::optional<CameraRayDifferential> cr = camera.GenerateRayDifferential(cs, lambda);
         float *q = rays + 6 * i;
         q[0] = cr->ray.o.x; q[1] = cr->ray.o.y; q[2] = cr->ray.o.z;

@@ -17,6 +17,7 @@
 //    re-spawned at o + d*tHit without pbrt's error-bound offset (interaction.cpp:91-97);
 //  * "IsInf(L.y(lambda))" (cpu/integrators.cpp:277) is evaluated as "any component of L is inf".
 #pragma once
+#include "restate_filter.hpp"
 #include "restate_graph.hpp"
 #include "restate_sampler.hpp"
 #include "restate_tmaj.hpp"
@@ -27,6 +28,7 @@ struct Scene {
     int width = 0, height = 0, spp = 1, max_depth = 5, sampler_seed = 0;
     int sampler_kind = SAMPLER_INDEPENDENT, sampler_randomize = RANDOMIZE_FAST_OWEN;  // "independent" | "zsobol"
     float filter_radius[2] = {0.5f, 0.5f};
+    FilterTable filter;  // active: a FilterSampler-tabulated pixel filter instead of the box
     Xform camera_from_raster, render_from_camera;  // only .m is used
     V3 light_dir;                                  // wi towards the light, normalised
     std::vector<float> light_spec;                 // NSPEC, includes scale
@@ -272,8 +274,12 @@ inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro,
     sampler.get1d();
     float f0, f1;
     sampler.get2d(&f0, &f1);
-    float fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
-    float fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
+    float fx, fy, fw = 1;
+    if (sc.filter.active()) sc.filter.sample(f0, f1, &fx, &fy, &fw);
+    else {
+        fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
+        fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
+    }
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     V3 pCamera = apply_point(sc.camera_from_raster, {pfx, pfy, 0});
     apply_ray(sc.render_from_camera, {0, 0, 0}, normalize(pCamera), nullptr, ro, rd);
@@ -297,15 +303,19 @@ inline PixelSampleOut evaluate_pixel_sample(const Scene &sc, const Medium &med, 
     float lu = sampler.get1d();
     PixelSampleOut out;
     out.lambda = sample_visible_wavelengths(lu);
-    // GetCameraSample with BoxFilter::Sample (filters.h:67-70)
+    // GetCameraSample (samplers.h:797-814) with BoxFilter::Sample (filters.h:67-70) or FilterSampler::Sample
     float f0, f1, l0, l1;
     sampler.get2d(&f0, &f1);  // GetPixel2D
-    float fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
-    float fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
+    float fx, fy;
+    out.weight = 1;
+    if (sc.filter.active()) sc.filter.sample(f0, f1, &fx, &fy, &out.weight);
+    else {
+        fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
+        fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
+    }
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     sampler.get1d();          // time
     sampler.get2d(&l0, &l1);  // lens
-    out.weight = 1;
     V3 pCamera = apply_point(sc.camera_from_raster, {pfx, pfy, 0});
     V3 dir = normalize(pCamera);
     V3 ro, rd;

@@ -291,16 +291,46 @@ class Checker:
         self.lib.orc_film_resolve(C.byref(rdesc.c), _p(film, f64p), _p(rgb, f32p))
         return film, rgb
 
-    def camera_rays_reference(self, world_from_camera, fov, screen_window, width, height, seed, spp, samples):
+    def filter_sample(self, u, filter_cfg=None, table=None, radius=None):
+        """Filter::Sample per point u: (n, 3) = p.x, p.y, weight.  "ref": the reference's own filter object described by
+        filter_cfg = (kind, rx, ry, p0, p1) (1 gaussian sigma, 2 mitchell B C, 3 sinc tau, 0 box); "orc": the
+        restatement over the tabulated filter `table` [ny, nx] and `radius`."""
+        u = f32(u); n = u.size // 2
+        out = np.zeros((n, 3), dtype=np.float32)
+        if self.kind == "ref":
+            cfg = f32(filter_cfg)
+            self.lib.ref_filter_sample(_p(cfg, f32p), _p(u, f32p), C.c_int64(n), _p(out, f32p))
+        else:
+            t = f32(table)
+            self.lib.orc_filter_sample(_p(t, f32p), C.c_int32(t.shape[1]), C.c_int32(t.shape[0]), C.c_float(radius[0]),
+                                       C.c_float(radius[1]), _p(u, f32p), C.c_int64(n), _p(out, f32p))
+        return out
+
+    def filter_table(self, filter_cfg):
+        """"ref" only: the table FilterSampler's constructor builds for the filter, [ny, nx] float32."""
+        assert self.kind == "ref"
+        cfg = f32(filter_cfg); nxny = np.zeros(2, dtype=np.int32)
+        self.lib.ref_filter_table(_p(cfg, f32p), _p(nxny, i32p), None)
+        t = np.zeros((int(nxny[1]), int(nxny[0])), dtype=np.float32)
+        self.lib.ref_filter_table(_p(cfg, f32p), _p(nxny, i32p), _p(t, f32p))
+        return t
+
+    def camera_rays_reference(self, world_from_camera, fov, screen_window, width, height, seed, spp, samples,
+                              filter_cfg=None, want_weights=False):
         """"ref" only: the reference's real PerspectiveCamera (constructor + GenerateRayDifferential) driven like
-        EvaluatePixelSample.  Returns rays (n, 6) and {cameraFromRaster, renderFromCamera} (2, 4, 4)."""
+        EvaluatePixelSample.  Returns rays (n, 6) and {cameraFromRaster, renderFromCamera} (2, 4, 4)
+        (+ CameraSample::filterWeight per sample with want_weights)."""
         assert self.kind == "ref"
         wfc = f32(np.asarray(world_from_camera).ravel()); sw = f32(screen_window)
         samples = np.ascontiguousarray(samples, dtype=np.int32); n = samples.shape[0]
         rays = np.zeros((n, 6), dtype=np.float32); mats = np.zeros((2, 4, 4), dtype=np.float32)
+        cfg = None if filter_cfg is None else f32(filter_cfg)
+        weights = np.zeros(n, dtype=np.float32)
         self.lib.ref_camera_rays(_p(wfc, f32p), C.c_float(fov), _p(sw, f32p), C.c_int32(width), C.c_int32(height),
                                  C.c_int32(seed), C.c_int32(spp), _p(samples, i32p), C.c_int64(n), _p(rays, f32p),
-                                 _p(mats, f32p))
+                                 _p(mats, f32p), _p(cfg, f32p) if cfg is not None else None, _p(weights, f32p))
+        if want_weights:
+            return rays, mats, weights
         return rays, mats
 
     def graph_connect_info(self, search_range, n, vertex_radius):

@@ -4,7 +4,7 @@
 //
 // It fills the C-ABI descriptors of include/avr.h from the reference's OWN constructed objects, so whatever the
 // scene parser produced is what the device gets.  The members read here are private in the reference: in the
-// reference tree add `friend struct avr_adapter::Access;` to GridMedium, NanoVDBMedium, HGPhaseFunction,
+// reference tree add `friend struct avr_adapter::Access;` to GridMedium, NanoVDBMedium, HGPhaseFunction, GaussianFilter, MitchellFilter, LanczosSincFilter, FilterSampler,
 // DistantLight, IndependentSampler, ZSobolSampler and PixelSensor (this repository's test compiles the header
 // with -fno-access-control instead, oracle/Makefile).  No CUDA headers are needed on the pbrt side.
 //
@@ -119,6 +119,8 @@ struct Access {
     struct RenderDesc {
         avr_render_desc d{};
         std::vector<float> light, sensor;
+        avr_filter_table filter{};       // referenced by d.filter when the pixel filter is a tabulated one
+        std::vector<float> filter_values;
     };
     // PerspectiveCamera (cameras.h:343-370, cameras.cpp:404-460) over an RGBFilm (film.h:214-300)
     static void DescribeCamera(const pbrt::PerspectiveCamera &cam, RenderDesc *o) {
@@ -131,11 +133,26 @@ struct Access {
         Matrix(cam.cameraFromRaster.GetMatrix(), d.camera_from_raster);
         Matrix(cam.cameraTransform.RenderFromCamera().startTransform.GetMatrix(), d.render_from_camera);
     }
-    // PixelFilter: "box" (filters.h:60-85) is what the device implements; anything else is refused by the caller
+    // PixelFilter.  "box" (filters.h:48-82): analytic, weight 1.  "gaussian" (pbrt's default, scene.cpp:94), "mitchell",
+    // "sinc": pbrt samples them through a FilterSampler (filters.h:26-45); its table `f` — the filter evaluated at the
+    // cell centres of [-radius, radius]^2, filters.cpp:133-143 — goes over as it is and the library rebuilds the
+    // sampling distribution from it.  "triangle" (analytic tent sampling) is not on the device: false = the caller
+    // keeps the stock integrator.
     static bool DescribeFilter(pbrt::Filter filter, RenderDesc *o) {
-        if (!filter.Is<pbrt::BoxFilter>()) return false;
         pbrt::Vector2f r = filter.Radius();
         o->d.filter_radius[0] = r.x; o->d.filter_radius[1] = r.y;
+        o->d.filter = nullptr;
+        if (filter.Is<pbrt::BoxFilter>()) return true;
+        const pbrt::FilterSampler *fs = nullptr;
+        if (filter.Is<pbrt::GaussianFilter>()) fs = &filter.Cast<pbrt::GaussianFilter>()->sampler;
+        else if (filter.Is<pbrt::MitchellFilter>()) fs = &filter.Cast<pbrt::MitchellFilter>()->sampler;
+        else if (filter.Is<pbrt::LanczosSincFilter>()) fs = &filter.Cast<pbrt::LanczosSincFilter>()->sampler;
+        if (!fs) return false;
+        o->filter_values.assign(fs->f.begin(), fs->f.end());
+        o->filter.nx = fs->f.XSize();
+        o->filter.ny = fs->f.YSize();
+        o->filter.f = o->filter_values.data();
+        o->d.filter = &o->filter;
         return true;
     }
     // PixelSensor (film.h:60-130) + RGBFilm's outputRGBFromSensorRGB and maxComponentValue (film.h:239-275)

@@ -41,7 +41,7 @@ void ref_adapter_free_medium(void *h, int32_t kind) {
 }
 
 // Builds the reference objects of a scene the way the scene loader would and lets the adapter describe them.
-// cfg = {width, height, spp, sampler (0 independent, 1 zsobol), randomize, seed, filter (0 box, 1 gaussian = pbrt's default)}
+// cfg = {width, height, spp, sampler (0 independent, 1 zsobol), randomize, seed, filter (0 box, 1 gaussian = pbrt's default, 2 triangle, 3 mitchell)}
 void *ref_adapter_describe_render(const float world_from_camera[16], float fov, const float screen_window[4],
                                   const int32_t cfg[7], const float light_wi[3], const float *light_spec, float light_scale,
                                   const float sphere[4], const float *sensor_rgb, float imaging_ratio,
@@ -54,7 +54,9 @@ void *ref_adapter_describe_render(const float world_from_camera[16], float fov, 
     int width = cfg[0], height = cfg[1];
     Filter filter;
     if (cfg[6] == 0) filter = new BoxFilter(Vector2f(0.5f, 0.5f));
-    else filter = new GaussianFilter(Vector2f(1.5f, 1.5f), 0.5f, alloc);  // filters.cpp:114 defaults
+    else if (cfg[6] == 1) filter = new GaussianFilter(Vector2f(1.5f, 1.5f), 0.5f, alloc);  // filters.cpp:114 defaults
+    else if (cfg[6] == 2) filter = new TriangleFilter(Vector2f(2.f, 2.f));
+    else filter = new MitchellFilter(Vector2f(2.f, 2.f), 1.f / 3.f, 1.f / 3.f, alloc);
     // RGBFilm / PixelSensor want RGBColorSpace objects (rgb2spec tables: not buildable here): laid out in zeroed
     // storage with the members the adapter reads constructed, as oracle/refprobe_volpath.cpp does for the film tests
     RGBFilm *f = (RGBFilm *)::operator new(sizeof(RGBFilm));

@@ -148,17 +148,27 @@ def test_adapter_describes_camera_light_sensor_sampler(ref, sampler):
     ref.lib.ref_adapter_free_render(h)
 
 
-def test_adapter_fallback_rule_for_other_pixel_filters(ref):
-    """The device implements the box pixel filter.  pbrt's default is "gaussian" (scene.cpp:94, filters.cpp:114):
-    for it (and any other filter) DescribeFilter returns false and the adapter hands the job back to the stock
-    integrator instead of rendering with the wrong filter."""
+def test_adapter_describes_pixel_filters_and_falls_back_for_the_rest(ref):
+    """pbrt's default pixel filter is "gaussian" (scene.cpp:94, filters.cpp:114): DescribeFilter hands the device the
+    FilterSampler's own table (bit-equal to the one the probe tabulates from GaussianFilter::Evaluate) and the radius;
+    "mitchell" the same; the box filter has no table; for "triangle" (analytic tent sampling, not on the device)
+    DescribeFilter returns false and the adapter hands the job back to the stock integrator."""
     W, H, fov, eye = 40, 30, 20.0, (0.0, 0.35, -3.2)
     dens, (gd, rd) = _scene(width=W, height=H, fov=fov, eye=eye)
-    h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=1)
-    assert d is None
-    ref.lib.ref_adapter_free_render(h)
     h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=0)
-    assert d is not None
+    assert d is not None and not d.filter and list(d.filter_radius) == [0.5, 0.5]
+    ref.lib.ref_adapter_free_render(h)
+    for filt, cfg in ((1, (1, 1.5, 1.5, 0.5, 0.0)), (3, (2, 2.0, 2.0, 1.0 / 3.0, 1.0 / 3.0))):
+        h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=filt)
+        assert d is not None and d.filter
+        t = d.filter.contents
+        want = ref.filter_table(cfg)
+        assert (t.ny, t.nx) == want.shape and list(d.filter_radius) == [cfg[1], cfg[2]]
+        got = np.ctypeslib.as_array(t.f, shape=(t.ny * t.nx,)).reshape(t.ny, t.nx)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        ref.lib.ref_adapter_free_render(h)
+    h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=2)
+    assert d is None
     ref.lib.ref_adapter_free_render(h)
 
 
@@ -196,6 +206,20 @@ def test_device_renders_through_the_adapter(ctx, ref):
     # and the two renders of the unmodified descriptors are the same image statistically
     a, b = film[..., :3].sum(axis=2), want[..., :3].sum(axis=2)
     assert abs(a.mean() / b.mean() - 1) < 0.02, (a.mean(), b.mean())
+    # pbrt's default pixel filter through the adapter: the FilterSampler table it hands over gives the film the
+    # scenes.py descriptor gives with the same table and radius
+    hg, dg, keepg = describe_render(ref, rd, W, H, fov, eye, light_scale=3.0, filt=1)
+    dg.max_depth = rd.c.max_depth
+    for name in ("camera_from_raster", "render_from_camera", "light_dir"):
+        src, dst = getattr(d, name), getattr(dg, name)
+        for i in range(len(src)):
+            dst[i] = src[i]
+    gfilm = np.zeros((H, W, 4)); gstats = _abi.avr_render_stats()
+    ctx.check(ctx.lib.avr_render_volpath(ctx.h, via.h, C.byref(dg), gfilm.ctypes.data_as(C.POINTER(C.c_double)), C.byref(gstats)))
+    want_g, _ = ctx.render_volpath(direct, rd.with_filter(ref.filter_table((1, 1.5, 1.5, 0.5, 0.0)), (1.5, 1.5)))
+    assert np.array_equal(gfilm, want_g) and not np.array_equal(gfilm, film)
+    assert abs(gfilm[..., 3].mean() / 8 - 1) < 0.1 and gfilm[..., 3].min() > 0
+    ref.lib.ref_adapter_free_render(hg)
     ref.lib.ref_adapter_free_render(hr)
     ref.lib.ref_adapter_free_medium(hm, C.c_int32(kind))
     via.close(); direct.close(); mo.close()

@@ -50,6 +50,17 @@ WORKLOADS = {
     # small variant for smoke runs / CPU-box sanity
     "cloud-small": dict(kind="volpath", grid=(96, 80, 104), width=320, height=180, sigma_t=200.0, albedo=0.999, g=0.877,
                         max_depth=100, majorant_res=(64, 64, 64), eye=(0.0, 0.3, -2.4), fov=16.0, spp_per_step=16),
+    # configs[4] (C5): synthetic cubes with the media the general / chromatic kernels serve: RGB grids
+    # ({scale,c0,c1,c2} sigmoid-polynomial voxels for sigma_a and sigma_s), an emissive grid (blackbody from a
+    # temperature grid) and a scalar grid with wavelength-dependent sigma_a / sigma_s.  Same parameters as
+    # tools/config_sweep.py; the CPU arm of these workloads is the oracle port on a pixel crop.
+    "c5-rgbgrid-512": dict(kind="volpath", medium="rgbgrid", grid=(512, 512, 512), width=1280, height=720, sigma_t=8.08,
+                           albedo=1 / 1.01, g=0.0, max_depth=100, majorant_res=(16, 16, 16), fov=24.0, spp_per_step=4),
+    "c5-emissive-512": dict(kind="volpath", medium="emissive", grid=(512, 512, 512), width=1280, height=720, sigma_t=8.08,
+                            albedo=1 / 1.01, g=0.0, max_depth=100, majorant_res=(16, 16, 16), fov=24.0, spp_per_step=4),
+    "c5-chromatic-512": dict(kind="volpath", medium="chromatic", grid=(512, 512, 512), width=1280, height=720,
+                             sigma_t=64.64, albedo=1 / 1.01, g=0.877, max_depth=100, majorant_res=(16, 16, 16), fov=24.0,
+                             spp_per_step=4),
     # configs[3]: src/graph propagation, 8 iterations, synthetic random-geometric transport matrix
     "graph-1e7": dict(kind="graph", n=10_000_000, avg_deg=6, bounces=8),
     "graph-1e5": dict(kind="graph", n=100_000, avg_deg=6, bounces=8),
@@ -108,6 +119,46 @@ def make_scene(w, density, spp, exact):
                                       spp=spp, sigma_t=w["sigma_t"], albedo=w["albedo"], g=w["g"],
                                       max_depth=w["max_depth"], exact_math=exact, eye=w.get("eye", (0.0, 0.35, -3.2)),
                                       fov=w.get("fov", 20.0))
+
+
+def c5_scene(w, dens, spp):
+    """(medium kind, medium desc, render desc, layout, algorithmic bytes per fetch) of a C5 workload; dens: numpy."""
+    from acceleratedvolrenderer_b200._abi import GridDesc, RGBGridDesc
+    kw = dict(width=w["width"], height=w["height"], spp=spp, sigma_t=w["sigma_t"], albedo=w["albedo"], g=w["g"],
+              max_depth=w["max_depth"], exact_math=0, fov=w["fov"])
+    if w["medium"] == "chromatic":
+        gd, rd = scenes.cloud_scene(dens, chromatic=True, **kw)
+        return "uniformgrid", gd, rd, "octet32", 32
+    gd, rd = scenes.cloud_scene(dens, **kw)
+    if w["medium"] == "emissive":   # temperature = 300 + 2000 d, Lescale = 1: density + temperature + Lescale taps
+        ge = GridDesc(dens, gd.sigma_a, gd.sigma_s, render_from_medium=gd.m, g=w["g"], temperature=300 + 2000 * dens,
+                      lescale=np.ones_like(dens), le_norm=1.0)
+        return "uniformgrid", ge, rd, "dense", 96
+    r2 = np.random.default_rng(7)   # sigma_s = d (1, .9, .8) k, sigma_a = d (.02, .05, .1) k as sigmoid-polynomial voxels
+    ss = scenes.rgb_voxels(dens * 8.0, r2); sa = scenes.rgb_voxels(dens * 0.4, r2)
+    return "rgbgrid", RGBGridDesc(sigma_a=sa, sigma_s=ss, render_from_medium=gd.m, g=w["g"]), rd, "dense", 256
+
+
+def c5_cpu_arm(kind, desc, rd, seconds):
+    """The oracle port (kind "port") on a centred crop of the frame, all host threads, ~`seconds` of work."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
+    import cpu_checker
+    ck = cpu_checker.Checker("orc")
+    mo = ck.medium_rgbgrid(desc) if kind == "rgbgrid" else ck.medium_uniformgrid(desc)
+    threads = os.cpu_count() or 1
+    W, H = rd.c.width, rd.c.height
+    cw, ch = 64, 36
+    n, k, t = 0, 0, time.perf_counter()
+    while k < 2 or (time.perf_counter() - t < seconds and k < 64):
+        r = rd.with_(pixel_bounds=(W // 2 - cw // 2, H // 2 - ch // 2, W // 2 + cw // 2, H // 2 + ch // 2), sampler_seed=100 + k,
+                     exact_math=1)
+        mo.render(r, threads=threads)
+        n += cw * ch * rd.c.spp
+        k += 1
+    dt = time.perf_counter() - t
+    mo.close()
+    return n / dt / 1e6, threads, f"{k} steps of a centred {cw}x{ch} pixel crop x {rd.c.spp} spp; oracle/ CPU restatement (port)"
 
 
 class ClockSampler:
@@ -520,6 +571,26 @@ def main():
                       "g": w["g"], "max_depth": w["max_depth"], "sampler": "independent", "spp_per_step": spp,
                       "l2": "inputs (3.6 GB octet store at this workload) are far larger than the 126 MB L2: no flush between steps"}
 
+    c5 = w.get("medium", "nanovdb") != "nanovdb"
+    if c5:
+        base["metric"] = "Msamples/s on synthetic C5 cube volpath"
+        base["config"]["medium"] = {"rgbgrid": "rgbgrid: sigma_a, sigma_s as RGBUnboundedSpectrum voxels (general kernel)",
+                                    "emissive": "uniformgrid + temperature grid, blackbody Le (general kernel)",
+                                    "chromatic": "uniformgrid, wavelength-dependent sigma_a / sigma_s (4-channel kernel)"}[w["medium"]]
+        base["config"]["l2"] = "inputs are far larger than the 126 MB L2: no flush between steps"
+    if args.impl == "reference" and c5:
+        if rank != 0:
+            return 0
+        import torch
+        kind, desc, rdc, _, _ = c5_scene(w, np.asarray(make_density(w, "cuda:0" if torch.cuda.is_available() else None)), spp)
+        v, threads, sample = c5_cpu_arm(kind, desc, rdc, 25.0 * max(1, args.steps + args.warmup) / 11)
+        out = dict(base)
+        out.update({"impl": "reference", "value": v, "ms_per_step": None, "n_gpus": args.gpus,
+                    "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
+                    "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    "gpu_launches": 0})
+        print(json.dumps(out))
+        return 0
     if args.impl == "reference":
         if rank != 0:
             return 0
@@ -546,10 +617,16 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     density = make_density(w, dev)
-    nd, rd = make_scene(w, density, spp, 0)
     ctx = Context(local_rank)
-    t0 = time.perf_counter()
-    med = ctx.create_medium("nanovdb", nd, layout=args.layout)
+    c5_fetch_bytes = None
+    if c5:
+        c5_kind, c5_desc, rd, args.layout, c5_fetch_bytes = c5_scene(w, np.asarray(density), spp)
+        t0 = time.perf_counter()
+        med = ctx.create_medium(c5_kind, c5_desc) if c5_kind == "rgbgrid" else ctx.create_medium(c5_kind, c5_desc, layout=args.layout)
+    else:
+        nd, rd = make_scene(w, density, spp, 0)
+        t0 = time.perf_counter()
+        med = ctx.create_medium("nanovdb", nd, layout=args.layout)
     build_s = time.perf_counter() - t0
     comm = sharding.init_comm(ctx) if world > 1 else None
     W, H = w["width"], w["height"]
@@ -646,7 +723,7 @@ def main():
     # parity renders (rank 0's GPU, full frame, >= parity_spp samples per pixel in both modes): k independent steps,
     # film Y of every step kept at full resolution until the reference's lattice is known
     gpu_y = {}
-    if rank == 0 and not args.no_cpu_baseline and args.parity_spp > 0:
+    if rank == 0 and not args.no_cpu_baseline and args.parity_spp > 0 and not c5:
         k = max(2, (args.parity_spp + spp - 1) // spp)
         for name, exact in (("fast", 0), ("exact", 1)):
             ys_ = []
@@ -662,6 +739,8 @@ def main():
         # algorithmic bytes of one trilinear fetch: the 32-byte octet, the 16-byte fp16 octet, or (sparse brick pool)
         # two 8-byte tap rows + the 4-byte indirection entry
         fetch_bytes = {"octet16": 16, "brick16": 20}.get(args.layout, 32)
+        if c5_fetch_bytes:
+            fetch_bytes = c5_fetch_bytes  # emissive: density + temperature + Lescale taps; rgbgrid: 2 grids x 8 x 16 B
         # the L2 half of the metric ("density-fetch GB/s vs HBM/L2 roofline"): measured here, with the 64 MiB-resident
         # read kernel BASELINE.md promises; it is the denominator when the medium's store fits the L2
         l2_peak = ctx.measure_read_bandwidth(64 << 20, iters=40)
@@ -699,7 +778,13 @@ def main():
         if exact_out:
             exact_out["roofline_frac"] = roof(xcam, xsh, xseg, xk, xs, 1)["frac"]
             out["exact"] = exact_out
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and c5:
+            try:
+                v, threads, sample = c5_cpu_arm(c5_kind, c5_desc, rd, 20.0)
+                out["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample}
+            except Exception as e:
+                out["cpu_baseline"] = {"value": None, "error": repr(e)}
+        elif not args.no_cpu_baseline:
             try:
                 ref = ReferenceArm(w, density, spp)
                 stride = ref.calibrate(6.0)

@@ -327,16 +327,25 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
     int px = rp.x0 + pi % (rp.x1 - rp.x0), py = rp.y0 + pi / (rp.x1 - rp.x0);
     PathLane<TR> ln;  // reuse start-of-path arithmetic
     ln.px = px; ln.py = py; ln.samp = s;
-    ln.srng.set_sequence(hash_3u32((uint32_t)px, (uint32_t)py, (uint32_t)rp.seed));
-    ln.srng.advance((long long)s * 65536ll);
-    float lu = ln.srng.uniform();
+    // the scene's sampler (a run-time switch: this kernel is not worth a second set of instantiations)
+    const bool zs = rp.smp.kind == AVR_SAMPLER_ZSOBOL;
+    auto draw1 = [&]() -> float {
+        if (zs) return PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.get1d();
+        return ln.srng.uniform();
+    };
+    if (zs) PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.start_pixel_sample();
+    else PathSamplerRef<false>{rp.smp, ln.srng, px, py, s}.start_pixel_sample();
+    float lu = draw1();
     float pdf[4];
     sample_visible_wavelengths(lu, ln.lambda, pdf);
     LambdaCtx<N> lc = make_lambda_ctx<N>(mv, ln.lambda);
-    float f0 = ln.srng.uniform(), f1 = ln.srng.uniform();
+    float f0, f1;
+    if (zs) PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.get2d(&f0, &f1);
+    else PathSamplerRef<false>{rp.smp, ln.srng, px, py, s}.get2d(&f0, &f1);
     float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
-    ln.srng.uniform(); ln.srng.uniform(); ln.srng.uniform();
+    if (zs) PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.skip(3);  // time, lens
+    else PathSamplerRef<false>{rp.smp, ln.srng, px, py, s}.skip(3);
     const float *c = rp.cfr;
     float xp = c[0] * pfx + c[1] * pfy + c[2] * 0.f + c[3];
     float yp = c[4] * pfx + c[5] * pfy + c[6] * 0.f + c[7];
@@ -352,11 +361,11 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
     if (boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0) {
         if (t0 > 0) ro = v3(ro.x + rd.x * t0, ro.y + rd.y * t0, ro.z + rd.z * t0);
         if (boundary_hit(rp, ro, rd, &t0, &t1) && t1 > 0) {
-            uint64_t hash0 = hash_float(ln.srng.uniform());
-            uint64_t hash1 = hash_float(ln.srng.uniform());
+            uint64_t hash0 = hash_float(draw1());
+            uint64_t hash1 = hash_float(draw1());
             RNG rng;
             rng.set_sequence(hash0, hash1);
-            float u = ln.srng.uniform();
+            float u = draw1();
             TmajCount cnt = {0, 0};
             float len = sqrtf(sqr(rd.x) + sqr(rd.y) + sqr(rd.z));
             V3 dn = rd / len;

@@ -403,8 +403,8 @@ avr_status avr_graph_set_vertices(avr_graph *g, const float *pos, const float *l
  * perc99 / max fallbacks and 1/dist^2 weighted mean.  points in WORLD space, 3 floats each. */
 avr_status avr_graph_connect(avr_graph *g, const float *points, int64_t n, float *out);
 /* GraphIntegrator::Li free-graph branch (src/graph/graph_integrator.cpp:180-244) rendered over the
- * same scene class as avr_render_volpath; world_from_render: 16 floats row-major.  Draws from the
- * independent sampler; desc->sampler = zsobol is AVR_ERR_UNSUPPORTED here. */
+ * same scene class as avr_render_volpath (Sampler "independent" or "zsobol"); world_from_render: 16 floats row-major.
+ * Box pixel filter only: desc->filter != NULL is AVR_ERR_UNSUPPORTED here. */
 avr_status avr_render_graph(avr_ctx *ctx, avr_medium *m, avr_graph *g, const avr_render_desc *desc,
                             const float *world_from_render, double *film, avr_render_stats *stats);
 

@@ -606,13 +606,15 @@ def test_graph_connect(ctx, orc):
     g.close()
 
 
-def test_graph_render_matches_oracle(ctx, orc):
+@pytest.mark.parametrize("sampler", ["independent", "zsobol"])
+def test_graph_render_matches_oracle(ctx, orc, sampler):
     """avr_render_graph = GraphIntegrator::Li, free-graph branch (graph/graph_integrator.cpp:180-246): camera ray,
     one SampleT_maj to the first real collision, ConnectToGraph there, spectrum * L into the film.  Against the
     restated Li pushed through the film arithmetic that is pinned to the reference (case "film"): the only
     difference is the summation order of ConnectToGraph's weighted average (hash grid vs sorted kd-tree
     result), so the bar is 1e-4 relative per pixel; both search-range modes; a non-trivial worldFromRender."""
     dens, (gd, rd) = small_scene(width=40, height=30, spp=3, sigma_t=10.0)
+    rd = rd.with_(sampler={"independent": 0, "zsobol": 1}[sampler], randomize=2)   # zsobol: pbrt's default sampler, fastowen
     rng = np.random.default_rng(6)
     n = 6000
     pos = rng.uniform(-0.55, 0.55, (n, 3)).astype(np.float32)
@@ -637,10 +639,11 @@ def test_graph_render_matches_oracle(ctx, orc):
         err = np.abs(film[..., :3] - want[..., :3]).max(axis=2)
         ok = err <= 1e-4 * np.maximum(want[..., :3].max(axis=2), 1e-6)
         assert ok.mean() >= 0.995, ok.mean()
-    # the graph render draws from the independent sampler only: anything else is refused, not ignored
+    # the graph render has the box pixel filter only: a tabulated filter is refused, not ignored
+    from acceleratedvolrenderer_b200._abi import gaussian_filter_table
     from acceleratedvolrenderer_b200.api import AvrError
     with pytest.raises(AvrError):
-        ctx.render_graph(md, g, rd.with_(sampler=1), world_from_render=wfr)
+        ctx.render_graph(md, g, rd.with_filter(gaussian_filter_table(), (1.5, 1.5)), world_from_render=wfr)
     md.close(); mo.close(); g.close()
 
 

@@ -90,13 +90,21 @@ AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double
         rgb[0] *= k; rgb[1] *= k; rgb[2] *= k;
     }
     double *px = film + 4 * ((size_t)ln.py * rp.width + ln.px);
-    // RGBFilm::AddSample: rgbSum[c] += weight * rgb[c] (a float product), weightSum += weight; box filter: weight 1
-    float w = 1.f;
-    if (__builtin_expect(rp.fsamples != nullptr, 0)) w = rp.fsamples[sample_slot(rp, ln.px, ln.py, ln.samp)].z;
-    if (rgb[0] != 0) atomicAdd(px + 0, (double)(w * rgb[0]));  // adding +-0 leaves the sum unchanged
-    if (rgb[1] != 0) atomicAdd(px + 1, (double)(w * rgb[1]));
-    if (rgb[2] != 0) atomicAdd(px + 2, (double)(w * rgb[2]));
-    atomicAdd(px + 3, (double)w);
+    // RGBFilm::AddSample: rgbSum[c] += weight * rgb[c] (a float product), weightSum += weight.  Box filter: weight 1
+    // (adding +-0 leaves a sum unchanged); the tabulated-filter case is a branch of its own so that the common one
+    // carries no weight at all
+    if (__builtin_expect(rp.fsamples != nullptr, 0)) {
+        const float w = rp.fsamples[sample_slot(rp, ln.px, ln.py, ln.samp)].z;
+        atomicAdd(px + 0, (double)(w * rgb[0]));
+        atomicAdd(px + 1, (double)(w * rgb[1]));
+        atomicAdd(px + 2, (double)(w * rgb[2]));
+        atomicAdd(px + 3, (double)w);
+        return;
+    }
+    if (rgb[0] != 0) atomicAdd(px + 0, (double)(1.f * rgb[0]));
+    if (rgb[1] != 0) atomicAdd(px + 1, (double)(1.f * rgb[1]));
+    if (rgb[2] != 0) atomicAdd(px + 2, (double)(1.f * rgb[2]));
+    atomicAdd(px + 3, 1.0);
 }
 
 // RayIntegrator::EvaluatePixelSample prologue (cpu/integrators.cpp:235-262): sampler start,

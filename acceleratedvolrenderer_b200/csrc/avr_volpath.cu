@@ -1105,9 +1105,26 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
     pv.cap_log2 = lay.cap_log2;
     pv.cap_mask = lay.cap - 1;
     {
+        // The majorant grid, when it is small enough to live in shared memory (<= 16 KB: the 16^3 grid of GridMedium /
+        // RGBGridMedium), is staged by ONE bulk asynchronous copy (TMA, cp.async.bulk) that completes on an mbarrier
+        // while all threads initialise the pool; a size that is not a multiple of 16 bytes takes the plain loop.
+        __shared__ __align__(8) unsigned long long s_maj_bar;
+        const bool bulk = rp.maj_in_smem && (maj_bytes & 15u) == 0 && ((size_t)maj & 15u) == 0;
         if (rp.maj_in_smem) {
             float *s_maj = reinterpret_cast<float *>(smem);
-            for (unsigned i = threadIdx.x; i < maj_bytes / 4; i += blockDim.x) s_maj[i] = maj[i];
+            if (bulk) {
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_maj_bar);
+                if (threadIdx.x == 0) {
+                    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1));
+                    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(maj_bytes) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                     (unsigned)__cvta_generic_to_shared(s_maj)),
+                                 "l"(maj), "r"(maj_bytes), "r"(bar)
+                                 : "memory");
+                }
+            } else
+                for (unsigned i = threadIdx.x; i < maj_bytes / 4; i += blockDim.x) s_maj[i] = maj[i];
             maj = s_maj;
         }
         // all slots start dead (state word 0 = ST_DEAD, nothing pending) and queued in Q_DEAD
@@ -1123,7 +1140,19 @@ k_volpath(MediumView mv, RenderParams rp, unsigned long long *counters, double *
             pv.q[threadIdx.x].tail = threadIdx.x == Q_DEAD ? (unsigned)rp.pool : 0u;
         }
         if (threadIdx.x == 0) *pv.live = rp.pool;
-        __syncthreads();
+        __syncthreads();  // (also orders thread 0's mbarrier.init before everybody's wait)
+        if (bulk) {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_maj_bar);
+            asm volatile(
+                "{\n"
+                ".reg .pred p;\n"
+                "AVR_MAJ_WAIT:\n"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                "@!p bra AVR_MAJ_WAIT;\n"
+                "}\n" ::"r"(bar),
+                "r"(0)
+                : "memory");
+        }
     }
     const unsigned lane = threadIdx.x & 31;
     PathLane<TR> ln;

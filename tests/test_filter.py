@@ -142,3 +142,21 @@ def test_render_under_a_gaussian_filter_matches_oracle(ctx, orc, sampler):
     se = np.sqrt(means.var(ddof=1) / 16 + ref_means.var(ddof=1) / 16)
     assert abs(means.mean() - ref_means.mean()) < 4 * se, (means.mean(), ref_means.mean(), se)
     md.close(); mo.close()
+
+
+@pytest.mark.gpu
+def test_filter_table_argument_errors(ctx):
+    """A malformed avr_filter_table is refused with a message, never read out of bounds."""
+    from acceleratedvolrenderer_b200.api import AvrError
+    u = np.zeros((4, 2), dtype=np.float32)
+    good = gaussian_filter_table()
+    assert ctx.filter_sample(good, (1.5, 1.5), u).shape == (4, 3)
+    with pytest.raises(AvrError) as e:
+        ctx.filter_sample(good, (0.0, 1.5), u)
+    assert "radius" in str(e.value)
+    with pytest.raises(AvrError) as e:
+        ctx.filter_sample(np.zeros((0, 48), dtype=np.float32), (1.5, 1.5), u)
+    assert "nx, ny" in str(e.value)
+    # an all-zero table: the reference's distribution falls back to uniform CDFs and the weight is 0 / 0
+    z = ctx.filter_sample(np.zeros((8, 8), dtype=np.float32), (1.0, 1.0), np.full((4, 2), 0.5, dtype=np.float32))
+    assert np.all(np.abs(z[:, :2]) <= 1.0)

@@ -123,7 +123,10 @@ class avr_built_graph(C.Structure):
 
 
 class avr_filter_table(C.Structure):
-    _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("f", f32p)]
+    _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("f", f32p), ("kind", C.c_int32)]
+
+
+FILTER_TABULATED, FILTER_TRIANGLE = 0, 1
 
 
 class avr_render_desc(C.Structure):
@@ -411,12 +414,18 @@ class RenderDesc:
 
     def with_filter(self, table, radius):
         """Variant with a tabulated pixel filter (avr_filter_table): table = [ny, nx] float32 values of the filter as
-        FilterSampler tabulates them (see filter_table()), radius = the filter's radius; table None = box filter."""
+        FilterSampler tabulates them (see filter_table()), radius = the filter's radius; table None = box filter,
+        table "triangle" = pbrt's triangle filter (sampled analytically, no table)."""
         r = self.with_()
         _set_arr(r.c.filter_radius, radius)
         if table is None:
             r.c.filter = None
             r.filter_values = r.filter_c = None
+        elif isinstance(table, str):
+            assert table == "triangle"
+            r.filter_values = None
+            r.filter_c = avr_filter_table(0, 0, None, FILTER_TRIANGLE)
+            r.c.filter = C.pointer(r.filter_c)
         else:
             r.filter_values = _f32(table)
             r.filter_c = avr_filter_table(int(r.filter_values.shape[1]), int(r.filter_values.shape[0]), _ptr(r.filter_values))

@@ -209,10 +209,16 @@ class Context:
         return film, stats.as_dict()
 
     def filter_sample(self, table, radius, u):
-        """FilterSampler::Sample through the render kernels' device code: (n, 3) = p.x, p.y, weight."""
-        from ._abi import avr_filter_table
-        table = _f32(table); u = _f32(u); n = u.size // 2
-        t = avr_filter_table(int(table.shape[1]), int(table.shape[0]), _p(table))
+        """FilterSampler::Sample (table = "triangle": TriangleFilter::Sample) through the render kernels' device code:
+        (n, 3) = p.x, p.y, weight."""
+        from ._abi import FILTER_TRIANGLE, avr_filter_table
+        u = _f32(u); n = u.size // 2
+        if isinstance(table, str):
+            assert table == "triangle"
+            t = avr_filter_table(0, 0, None, FILTER_TRIANGLE)
+        else:
+            table = _f32(table)
+            t = avr_filter_table(int(table.shape[1]), int(table.shape[0]), _p(table))
         rad = (C.c_float * 2)(float(radius[0]), float(radius[1]))
         out = np.empty((n, 3), dtype=np.float32)
         self.check(self.lib.avr_filter_sample(self.h, C.byref(t), rad, _p(u), C.c_int64(n), _p(out)))

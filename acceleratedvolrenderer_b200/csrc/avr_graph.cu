@@ -343,6 +343,11 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
     if (zs) PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.get2d(&f0, &f1);
     else PathSamplerRef<false>{rp.smp, ln.srng, px, py, s}.get2d(&f0, &f1);
     float fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx), fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
+    float fw = 1.f;
+    if (rp.fsamples) {  // tabulated filter: offset and weight from the pre-pass (same two draws), as in k_volpath
+        const float4 fs = rp.fsamples[sample_slot(rp, px, py, s)];
+        fx = fs.x; fy = fs.y; fw = fs.z;
+    }
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     if (zs) PathSamplerRef<true>{rp.smp, ln.srng, px, py, s}.skip(3);  // time, lens
     else PathSamplerRef<false>{rp.smp, ln.srng, px, py, s}.skip(3);
@@ -414,10 +419,11 @@ k_render_graph(MediumView mv, RenderParams rp, GraphView g, XfRows wfr, double *
     float m = fmaxf(rgb[0], fmaxf(rgb[1], rgb[2]));
     if (m > rp.max_component) { float k = rp.max_component / m; rgb[0] *= k; rgb[1] *= k; rgb[2] *= k; }
     double *pxl = film + 4 * ((size_t)py * rp.width + px);
-    atomicAdd(pxl + 0, (double)rgb[0]);
-    atomicAdd(pxl + 1, (double)rgb[1]);
-    atomicAdd(pxl + 2, (double)rgb[2]);
-    atomicAdd(pxl + 3, 1.0);
+    // RGBFilm::AddSample: rgbSum += weight * rgb, weightSum += weight (weight 1 for the box filter)
+    atomicAdd(pxl + 0, (double)(fw * rgb[0]));
+    atomicAdd(pxl + 1, (double)(fw * rgb[1]));
+    atomicAdd(pxl + 2, (double)(fw * rgb[2]));
+    atomicAdd(pxl + 3, (double)fw);
 }
 
 }  // namespace avr

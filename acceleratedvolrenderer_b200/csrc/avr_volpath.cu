@@ -22,6 +22,7 @@
 #include <cstdlib>
 #include <algorithm>
 #include <cstring>
+#include <atomic>
 #include <thread>
 
 #include "avr_render_host.h"

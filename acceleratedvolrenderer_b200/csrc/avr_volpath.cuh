@@ -137,10 +137,33 @@ AVR_DEV float pc1d_sample(const float *func, const float *cdf, float func_int, i
     *pdf = func_int > 0 ? func[o] / func_int : 0.f;
     return lerp_exact((float(o) + du) / float(n), lo, hi);
 }
+// SampleTent (util/sampling.h:196-201): SampleDiscrete({.5, .5}, u) picks the half and remaps u (:79-113, the weights
+// sum to 1 exactly), SampleLinear (:122-128) draws from the ramp of that half
+AVR_DEV float sample_linear(float u, float a, float b) {
+    if (u == 0 && a == 0) return 0;
+    float x = u * (a + b) / (a + sqrtf((1 - u) * (a * a) + u * (b * b)));
+    return fminf(x, kOneMinusEps);
+}
+AVR_DEV float sample_tent(float u, float r) {
+    float up = u * 1.f;
+    if (up == 1.f) up = kOneMinusEps;
+    if (0.f + 0.5f <= up) {
+        float ur = fminf((up - 0.5f) / 0.5f, kOneMinusEps);
+        return r * sample_linear(ur, 1, 0);
+    }
+    float ur = fminf((up - 0.f) / 0.5f, kOneMinusEps);
+    return -r + r * sample_linear(ur, 0, 1);
+}
 // FilterSampler::Sample (filters.h:33-38) over PiecewiseConstant2D::Sample (util/sampling.h:760-769): the marginal
 // in y first, then the row's conditional in x; weight = f[pi] / (pdf_x * pdf_y)
 AVR_DEV void filter_sample(const float *flt, int nx, int ny, float rx, float ry, float u0, float u1, float *px, float *py,
                            float *weight) {
+    if (nx < 0) {  // TriangleFilter::Sample, filters.h:224-227
+        *px = sample_tent(u0, rx);
+        *py = sample_tent(u1, ry);
+        *weight = 1.f;
+        return;
+    }
     const float *f = flt, *func = f + nx * ny, *ccdf = func + nx * ny, *cint = ccdf + ny * (nx + 1);
     const float *mfunc = cint + ny, *mcdf = mfunc + ny, *mint = mcdf + ny + 1;
     float pdf0, pdf1;

@@ -269,9 +269,13 @@ enum { AVR_RANDOMIZE_NONE = 0, AVR_RANDOMIZE_PERMUTE_DIGITS = 1, AVR_RANDOMIZE_F
  * (util/sampling.h:625-649,737-754) and samples it per camera sample exactly as FilterSampler::Sample /
  * GetCameraSample do (samplers.h:797-814): pFilm = pPixel + p + 0.5, the sample is added to pixel pPixel alone with
  * weight f[pi] / pdf (RGBFilm::AddSample, film.h:239-255: rgbSum += weight * rgb, weightSum += weight). */
+/* kind AVR_FILTER_TRIANGLE: pbrt's "triangle" filter, sampled analytically (TriangleFilter::Sample, filters.h:224-227:
+ * SampleTent per axis, util/sampling.h:196-201, weight 1); nx, ny and f are not read. */
+enum { AVR_FILTER_TABULATED = 0, AVR_FILTER_TRIANGLE = 1 };
 typedef struct avr_filter_table {
     int32_t nx, ny;
     const float *f;                  /* ny * nx floats, host memory */
+    int32_t kind;                    /* AVR_FILTER_TABULATED (0) or AVR_FILTER_TRIANGLE */
 } avr_filter_table;
 
 typedef struct avr_render_desc {
@@ -305,7 +309,7 @@ typedef struct avr_render_desc {
                                         resolution, `randomize` and sampler_seed)               */
     int32_t randomize;               /* zsobol "randomization": AVR_RANDOMIZE_* (pbrt's default
                                         is fastowen, samplers.cpp:157); ignored for independent */
-    const avr_filter_table *filter;  /* NULL: BoxFilter of filter_radius (weight 1); else the tabulated filter */
+    const avr_filter_table *filter;  /* NULL: BoxFilter of filter_radius (weight 1); else a tabulated or triangle filter */
 } avr_render_desc;
 
 /* FilterSampler::Sample for n points u (2 floats each) under `filter` / radius: out = {p.x, p.y, weight} per
@@ -404,7 +408,7 @@ avr_status avr_graph_set_vertices(avr_graph *g, const float *pos, const float *l
 avr_status avr_graph_connect(avr_graph *g, const float *points, int64_t n, float *out);
 /* GraphIntegrator::Li free-graph branch (src/graph/graph_integrator.cpp:180-244) rendered over the
  * same scene class as avr_render_volpath (Sampler "independent" or "zsobol"); world_from_render: 16 floats row-major.
- * Box pixel filter only: desc->filter != NULL is AVR_ERR_UNSUPPORTED here. */
+ * desc->filter (a tabulated pixel filter) is honoured as in avr_render_volpath. */
 avr_status avr_render_graph(avr_ctx *ctx, avr_medium *m, avr_graph *g, const avr_render_desc *desc,
                             const float *world_from_render, double *film, avr_render_stats *stats);
 

@@ -136,13 +136,19 @@ struct Access {
     // PixelFilter.  "box" (filters.h:48-82): analytic, weight 1.  "gaussian" (pbrt's default, scene.cpp:94), "mitchell",
     // "sinc": pbrt samples them through a FilterSampler (filters.h:26-45); its table `f` — the filter evaluated at the
     // cell centres of [-radius, radius]^2, filters.cpp:133-143 — goes over as it is and the library rebuilds the
-    // sampling distribution from it.  "triangle" (analytic tent sampling) is not on the device: false = the caller
-    // keeps the stock integrator.
+    // sampling distribution from it.  "triangle" (filters.h:208-231): analytic tent sampling with weight 1, a `kind`
+    // of the same descriptor.  Anything else: false = the caller keeps the stock integrator.
     static bool DescribeFilter(pbrt::Filter filter, RenderDesc *o) {
         pbrt::Vector2f r = filter.Radius();
         o->d.filter_radius[0] = r.x; o->d.filter_radius[1] = r.y;
         o->d.filter = nullptr;
         if (filter.Is<pbrt::BoxFilter>()) return true;
+        o->filter = avr_filter_table{};
+        if (filter.Is<pbrt::TriangleFilter>()) {
+            o->filter.kind = AVR_FILTER_TRIANGLE;
+            o->d.filter = &o->filter;
+            return true;
+        }
         const pbrt::FilterSampler *fs = nullptr;
         if (filter.Is<pbrt::GaussianFilter>()) fs = &filter.Cast<pbrt::GaussianFilter>()->sampler;
         else if (filter.Is<pbrt::MitchellFilter>()) fs = &filter.Cast<pbrt::MitchellFilter>()->sampler;

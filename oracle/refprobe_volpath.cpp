@@ -189,6 +189,7 @@ static Filter make_filter(const float *cfg) {
     case 1: return new GaussianFilter(radius, cfg[3]);         // "gaussian": sigma (filters.cpp:114, default 0.5)
     case 2: return new MitchellFilter(radius, cfg[3], cfg[4]);  // "mitchell": B, C
     case 3: return new LanczosSincFilter(radius, cfg[3]);      // "sinc": tau
+    case 4: return new TriangleFilter(radius);                 // "triangle"
     default: return new BoxFilter(radius);
     }
 }

@@ -45,12 +45,36 @@ struct Pc1d {  // PiecewiseConstant1D, util/sampling.h:625-649
     }
 };
 
+// SampleLinear / SampleTent, util/sampling.h:122-128,196-201; SampleDiscrete({.5, .5}, u, nullptr, &u) (:79-113) is
+// written out: the weights sum to 1, the first is passed over when .5 <= u
+inline float sample_linear(float u, float a, float b) {
+    if (u == 0 && a == 0) return 0;
+    float x = u * (a + b) / (a + std::sqrt(lerp(u, a * a, b * b)));
+    return std::min(x, kOneMinusEps);
+}
+inline float sample_tent(float u, float r) {
+    float sum_w = 0.f;
+    sum_w += 0.5f; sum_w += 0.5f;
+    float up = u * sum_w;
+    if (up == sum_w) up = std::nextafter(up, 0.f);
+    int offset = 0;
+    float sum = 0;
+    const float w[2] = {0.5f, 0.5f};
+    while (sum + w[offset] <= up) sum += w[offset++];
+    float ur = std::min((up - sum) / w[offset], kOneMinusEps);
+    if (offset == 0) return -r + r * sample_linear(ur, 0, 1);
+    return r * sample_linear(ur, 1, 0);
+}
+
 struct FilterTable {  // FilterSampler: domain [-radius, radius]^2, f tabulated nx x ny, distrib = PiecewiseConstant2D(f)
     int nx = 0, ny = 0;
+    bool triangle = false;  // TriangleFilter (filters.h:224-227): analytic, weight 1
+    float trx = 0, try_ = 0;
     std::vector<float> f;
     std::vector<Pc1d> rows;
     Pc1d marginal;
-    bool active() const { return nx > 0; }
+    bool active() const { return nx > 0 || triangle; }
+    void build_triangle(float rx, float ry) { triangle = true; trx = rx; try_ = ry; }
     void build(const float *values, int nx_, int ny_, float rx, float ry) {
         nx = nx_; ny = ny_;
         f.assign(values, values + size_t(nx) * ny);
@@ -64,6 +88,12 @@ struct FilterTable {  // FilterSampler: domain [-radius, radius]^2, f tabulated 
     }
     // FilterSampler::Sample (filters.h:33-38) = PiecewiseConstant2D::Sample (util/sampling.h:760-769) + f[pi] / pdf
     void sample(float u0, float u1, float *px, float *py, float *weight) const {
+        if (triangle) {
+            *px = sample_tent(u0, trx);
+            *py = sample_tent(u1, try_);
+            *weight = 1.f;
+            return;
+        }
         float pdf0, pdf1;
         int ox, oy;
         float d1 = marginal.sample(u1, &pdf1, &oy);

@@ -268,7 +268,7 @@ inline PathSampler make_sampler(const Scene &sc) {
 
 // Camera ray of one pixel sample (GetCameraSample + PerspectiveCamera::GenerateRay), as
 // evaluate_pixel_sample below forms it; exported so that the reference probe traces the same rays.
-inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro, V3 *rd) {
+inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro, V3 *rd, float *weight = nullptr) {
     PathSampler sampler = make_sampler(sc);
     sampler.start_pixel_sample(px, py, sampleIndex);
     sampler.get1d();
@@ -280,6 +280,7 @@ inline void camera_ray(const Scene &sc, int px, int py, int sampleIndex, V3 *ro,
         fx = lerp(f0, -sc.filter_radius[0], sc.filter_radius[0]);
         fy = lerp(f1, -sc.filter_radius[1], sc.filter_radius[1]);
     }
+    if (weight) *weight = fw;
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     V3 pCamera = apply_point(sc.camera_from_raster, {pfx, pfy, 0});
     apply_ray(sc.render_from_camera, {0, 0, 0}, normalize(pCamera), nullptr, ro, rd);

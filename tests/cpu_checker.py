@@ -273,12 +273,28 @@ class Checker:
         return out
 
 
-    def film_add_samples(self, rdesc, pixels, vals):
-        """RGBFilm::AddSample over explicit samples (pixels {px, py}; vals {L[4], lambda[4], pdf[4]}), in order.
+    def camera_weights(self, rdesc):
+        """CameraSample::filterWeight of every pixel sample of the descriptor's ranges, pixel-major (oracle only)."""
+        x0, y0, x1, y1, s0, s1 = rdesc.ranges()
+        out = np.zeros((x1 - x0) * (y1 - y0) * (s1 - s0), dtype=np.float32)
+        self.lib.orc_camera_weights(C.byref(rdesc.c), _p(out, f32p))
+        return out
+
+    def film_add_samples(self, rdesc, pixels, vals, weights=None):
+        """RGBFilm::AddSample over explicit samples (pixels {px, py}; vals {L[4], lambda[4], pdf[4]}), in order;
+        `weights` (oracle only): the filter weight of each sample, 1 when None.
         Returns the film sums (H, W, 4) doubles and RGBFilm::GetPixelRGB (H, W, 3)."""
         pixels = np.ascontiguousarray(pixels, dtype=np.int32); vals = f32(vals); n = pixels.shape[0]
         W, H = rdesc.c.width, rdesc.c.height
         film = np.zeros((H, W, 4), dtype=np.float64)
+        if weights is not None:
+            assert self.kind == "orc"
+            weights = f32(weights)
+            self.lib.orc_film_add_samples_w(C.byref(rdesc.c), _p(pixels, i32p), _p(vals, f32p), _p(weights, f32p),
+                                            C.c_int64(n), _p(film, f64p))
+            rgb = np.zeros((H, W, 3), dtype=np.float32)
+            self.lib.orc_film_resolve(C.byref(rdesc.c), _p(film, f64p), _p(rgb, f32p))
+            return film, rgb
         if self.kind == "ref":
             rgb = np.zeros((H, W, 3), dtype=np.float32)
             M = np.array(list(rdesc.c.output_rgb_from_sensor), dtype=np.float32)
@@ -293,13 +309,16 @@ class Checker:
 
     def filter_sample(self, u, filter_cfg=None, table=None, radius=None):
         """Filter::Sample per point u: (n, 3) = p.x, p.y, weight.  "ref": the reference's own filter object described by
-        filter_cfg = (kind, rx, ry, p0, p1) (1 gaussian sigma, 2 mitchell B C, 3 sinc tau, 0 box); "orc": the
-        restatement over the tabulated filter `table` [ny, nx] and `radius`."""
+        filter_cfg = (kind, rx, ry, p0, p1) (1 gaussian sigma, 2 mitchell B C, 3 sinc tau, 4 triangle, 0 box); "orc":
+        the restatement over the tabulated filter `table` [ny, nx] and `radius` (table None: the triangle filter)."""
         u = f32(u); n = u.size // 2
         out = np.zeros((n, 3), dtype=np.float32)
         if self.kind == "ref":
             cfg = f32(filter_cfg)
             self.lib.ref_filter_sample(_p(cfg, f32p), _p(u, f32p), C.c_int64(n), _p(out, f32p))
+        elif table is None:
+            self.lib.orc_filter_sample(None, C.c_int32(0), C.c_int32(0), C.c_float(radius[0]),
+                                       C.c_float(radius[1]), _p(u, f32p), C.c_int64(n), _p(out, f32p))
         else:
             t = f32(table)
             self.lib.orc_filter_sample(_p(t, f32p), C.c_int32(t.shape[1]), C.c_int32(t.shape[0]), C.c_float(radius[0]),

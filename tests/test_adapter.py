@@ -148,11 +148,11 @@ def test_adapter_describes_camera_light_sensor_sampler(ref, sampler):
     ref.lib.ref_adapter_free_render(h)
 
 
-def test_adapter_describes_pixel_filters_and_falls_back_for_the_rest(ref):
+def test_adapter_describes_every_pixel_filter(ref):
     """pbrt's default pixel filter is "gaussian" (scene.cpp:94, filters.cpp:114): DescribeFilter hands the device the
     FilterSampler's own table (bit-equal to the one the probe tabulates from GaussianFilter::Evaluate) and the radius;
-    "mitchell" the same; the box filter has no table; for "triangle" (analytic tent sampling, not on the device)
-    DescribeFilter returns false and the adapter hands the job back to the stock integrator."""
+    "mitchell" the same; the box filter has no table; "triangle" (analytic tent sampling) is a kind of the descriptor
+    without a table."""
     W, H, fov, eye = 40, 30, 20.0, (0.0, 0.35, -3.2)
     dens, (gd, rd) = _scene(width=W, height=H, fov=fov, eye=eye)
     h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=0)
@@ -168,7 +168,8 @@ def test_adapter_describes_pixel_filters_and_falls_back_for_the_rest(ref):
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
         ref.lib.ref_adapter_free_render(h)
     h, d, keep = describe_render(ref, rd, W, H, fov, eye, filt=2)
-    assert d is None
+    assert d is not None and d.filter and d.filter.contents.kind == _abi.FILTER_TRIANGLE
+    assert list(d.filter_radius) == [2.0, 2.0]
     ref.lib.ref_adapter_free_render(h)
 
 

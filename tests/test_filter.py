@@ -1,5 +1,6 @@
 """Pixel filters that pbrt samples through its FilterSampler ("gaussian" = pbrt's default, "mitchell", "sinc"):
-src/pbrt/filters.h:26-45, filters.cpp:133-147, util/sampling.h:603-790, GetCameraSample samplers.h:797-814.
+src/pbrt/filters.h:26-45, filters.cpp:133-147, util/sampling.h:603-790, GetCameraSample samplers.h:797-814; and the
+"triangle" filter (filters.h:208-231), sampled analytically.
 
 CPU: the restatement (oracle/restate_filter.hpp) against the reference's OWN filter objects through the probe, bit for
 bit: the tabulated filter, Filter::Sample over random and edge-case u, and the camera rays + CameraSample::filterWeight
@@ -44,6 +45,18 @@ def test_filter_sampling_restated_matches_the_reference_filters(orc, ref, name):
         assert want[:, 2].min() > 0 and np.ptp(want[:, 2]) < 1e-3 * want[:, 2].mean()   # importance sampled: ~constant weight
     else:
         assert (want[:, 2] < 0).any()                                                  # negative lobes keep their sign
+
+
+@pytest.mark.parametrize("radius", [(2.0, 2.0), (0.7, 3.25)])
+def test_triangle_filter_restated_matches_the_reference_filter(orc, ref, radius):
+    """TriangleFilter::Sample (filters.h:224-227): SampleTent per axis, weight 1 — the one pbrt filter that is neither
+    the box nor tabulated.  Bit for bit against the reference's object, incl. u = 0, 0.5 and 1 - ulp."""
+    u = sample_points()
+    want = ref.filter_sample(u, filter_cfg=(4, radius[0], radius[1], 0, 0))
+    got = orc.filter_sample(u, table=None, radius=radius)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.all(want[:, 2] == 1) and np.all(np.abs(want[:, 0]) <= radius[0]) and np.all(np.abs(want[:, 1]) <= radius[1])
+    assert abs(np.abs(want[:, 0]).mean() / radius[0] - 1 / 3) < 0.01      # a tent: E|x| = r / 3
 
 
 def test_gaussian_table_helper_is_the_reference_table(ref):
@@ -100,6 +113,36 @@ def test_device_filter_sampling_is_bit_exact(ctx, orc, name):
     want = orc.filter_sample(u, table=table, radius=(cfg[1], cfg[2]))
     got = ctx.filter_sample(table, (cfg[1], cfg[2]), u)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_device_triangle_filter_is_bit_exact_and_renders(ctx, orc):
+    """kind AVR_FILTER_TRIANGLE: the device tent sampling against the restatement bit for bit; a render under it has
+    unit weights (weightSum = spp) and the oracle's per-sample radiance."""
+    u = sample_points(seed=11)
+    for radius in ((2.0, 2.0), (0.7, 3.25)):
+        want = orc.filter_sample(u, table=None, radius=radius)
+        got = ctx.filter_sample("triangle", radius, u)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    dens = scenes.fbm_density(48, 40, 52, seed=4)
+    gd, rd = scenes.cloud_scene(dens, width=40, height=30, spp=4, sigma_t=14.0, albedo=0.95, g=0.4, max_depth=8)
+    rt = rd.with_filter("triangle", (2.0, 2.0))
+    mo = orc.medium_uniformgrid(gd)
+    md = ctx.create_medium("uniformgrid", gd, layout="octet32")
+    want, _ = mo.render_samples(rt)
+    got, _ = ctx.render_volpath_samples(md, rt)
+    L, Lw = got[:, :4].astype(np.float64), want[:, :4].astype(np.float64)
+    ok = np.abs(L - Lw).max(axis=1) <= 1e-3 * np.maximum(np.abs(Lw).max(axis=1), 1e-6)
+    assert ok.mean() >= 0.99, ok.mean()
+    boxed, _ = ctx.render_volpath_samples(md, rd)
+    assert not np.allclose(boxed[:, :4], got[:, :4])
+    film, _ = ctx.render_volpath(md, rt)
+    assert np.all(film[..., 3] == 4)
+    ofilm, _ = mo.render(rt, threads=8)
+    a = film[..., :3].sum(axis=2); b = ofilm[..., :3].sum(axis=2)
+    good = np.abs(a - b) <= 2e-3 * np.maximum(b, 1e-3 * b.max())
+    assert good.mean() >= 0.97, good.mean()
+    md.close(); mo.close()
 
 
 @pytest.mark.gpu

@@ -639,11 +639,25 @@ def test_graph_render_matches_oracle(ctx, orc, sampler):
         err = np.abs(film[..., :3] - want[..., :3]).max(axis=2)
         ok = err <= 1e-4 * np.maximum(want[..., :3].max(axis=2), 1e-6)
         assert ok.mean() >= 0.995, ok.mean()
-    # the graph render has the box pixel filter only: a tabulated filter is refused, not ignored
+    # tabulated pixel filters: camera offsets and film weights from the same FilterSampler::Sample as the path tracer's
+    # (tests/test_filter.py), so film = sum w * rgb and weightSum = sum w.  pbrt's default Gaussian (weights ~constant)
+    # and a table with negative lobes (weights of both signs)
     from acceleratedvolrenderer_b200._abi import gaussian_filter_table
-    from acceleratedvolrenderer_b200.api import AvrError
-    with pytest.raises(AvrError):
-        ctx.render_graph(md, g, rd.with_filter(gaussian_filter_table(), (1.5, 1.5)), world_from_render=wfr)
+    yy, xx = np.meshgrid(np.linspace(-1, 1, 64), np.linspace(-1, 1, 64), indexing="ij")
+    lobes = (np.cos(3 * xx) * np.cos(2 * yy) * np.exp(-xx * xx - yy * yy)).astype(np.float32)
+    for table, radius in ((gaussian_filter_table((1.5, 1.5), 0.5), (1.5, 1.5)), (lobes, (2.0, 2.0))):
+        rg = rd.with_filter(table, radius)
+        film, _ = ctx.render_graph(md, g, rg, world_from_render=wfr)
+        samples = mo.render_graph_samples(rg, pos, light, None, 0.06, world_from_render=wfr)
+        w = orc.camera_weights(rg)
+        assert (w.min() > 0) == (table is not lobes)
+        want, _ = orc.film_add_samples(rg, pixels, samples, weights=w)
+        assert np.allclose(film[..., 3], want[..., 3], rtol=1e-5, atol=1e-6)
+        err = np.abs(film[..., :3] - want[..., :3]).max(axis=2)
+        ok = err <= 1e-4 * np.maximum(np.abs(want[..., :3]).max(axis=2), 1e-6) + 1e-7
+        assert ok.mean() >= 0.995, ok.mean()
+    box, _ = ctx.render_graph(md, g, rd, world_from_render=wfr)
+    assert not np.allclose(box[..., :3], film[..., :3])
     md.close(); mo.close(); g.close()
 
 

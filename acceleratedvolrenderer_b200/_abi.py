@@ -49,6 +49,7 @@ class avr_nanovdb_grid(C.Structure):
         ("index_min", C.c_int32 * 3), ("dims", C.c_int32 * 3),
         ("inv_mat", C.c_float * 9), ("vec", C.c_float * 3),
         ("world_bbox", C.c_double * 6),
+        ("n_blocks", C.c_int64), ("block_origin", C.POINTER(C.c_int32)), ("block_values", f32p),
     ]
 
 

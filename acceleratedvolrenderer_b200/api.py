@@ -33,7 +33,7 @@ _lib = None
 ABI_SYMBOLS = [
     "avr_ctx_create", "avr_ctx_destroy", "avr_last_error", "avr_version", "avr_measure_read_bandwidth",
     "avr_medium_create_uniformgrid", "avr_medium_create_rgbgrid", "avr_medium_create_nanovdb", "avr_medium_destroy",
-    "avr_nvdb_read_grid", "avr_nvdb_free_grid", "avr_medium_create_nanovdb_file",
+    "avr_nvdb_read_grid", "avr_nvdb_read_blocks", "avr_nvdb_free_grid", "avr_medium_create_nanovdb_file",
     "avr_medium_is_emissive", "avr_medium_bounds", "avr_medium_bytes", "avr_medium_majorants", "avr_medium_lookup_density", "avr_medium_sample_point",
     "avr_dda_segments", "avr_medium_ray_to_medium", "avr_sample_tmaj", "avr_sample_tmaj_device",
     "avr_render_volpath", "avr_render_volpath_device", "avr_render_volpath_samples", "avr_film_resolve",
@@ -114,6 +114,32 @@ def read_nvdb_grid(path, grid_name=None):
     grid = NanoVDBGrid(vals, list(g.index_min), list(g.inv_mat), list(g.vec), list(g.world_bbox))
     lib.avr_nvdb_free_grid(C.byref(g))
     return grid, meta
+
+
+def read_nvdb_blocks(path, grid_name=None):
+    """avr_nvdb_read_blocks: the grid without flattening.  Returns (dict or None when the file has no such grid, info):
+    origins (n, 3) int32 — multiples of 8 in index space —, values (n, 8, 8, 8) float32 indexed [z, y, x], index_min,
+    dims, inv_mat, vec, world_bbox.  Host only."""
+    from ._abi import avr_nanovdb_grid, avr_nvdb_info
+    lib = load_library()
+    g = avr_nanovdb_grid(); info = avr_nvdb_info()
+    st = lib.avr_nvdb_read_blocks(str(path).encode(), grid_name.encode() if grid_name else None, C.byref(g), C.byref(info))
+    if st != 0:
+        raise AvrError(st, lib.avr_last_error(None).decode())
+    meta = {k: getattr(info, k) for k, _ in avr_nvdb_info._fields_}
+    meta["grid_name"] = info.grid_name.decode()
+    if not g.block_values:
+        return None, meta
+    n = int(g.n_blocks)
+    out = {
+        "origins": np.ctypeslib.as_array(g.block_origin, shape=(max(n, 1) * 3,))[:3 * n].astype(np.int32, copy=True).reshape(n, 3),
+        "values": np.ctypeslib.as_array(g.block_values, shape=(max(n, 1) * 512,))[:512 * n].astype(np.float32, copy=True).reshape(n, 8, 8, 8),
+        "index_min": np.array(list(g.index_min), dtype=np.int32), "dims": np.array(list(g.dims), dtype=np.int32),
+        "inv_mat": np.array(list(g.inv_mat), dtype=np.float32), "vec": np.array(list(g.vec), dtype=np.float32),
+        "world_bbox": np.array(list(g.world_bbox), dtype=np.float64),
+    }
+    lib.avr_nvdb_free_grid(C.byref(g))
+    return out, meta
 
 
 class Context:

@@ -206,11 +206,33 @@ __global__ void k_build_majorants(MediumView mv, float *out) {
     if (threadIdx.x == 0) out[mx + r[0] * (my + r[1] * mz)] = res;
 }
 
+// Where the build kernels of a scalar grid read voxel (x, y, z) of the index box from: the dense array, or — the
+// leaf-direct .nvdb ingest — 8^3 blocks behind a table over block coordinates (avr_nanovdb_grid's sparse form).
+struct VoxelSrc {
+    const float *dense;
+    const float *bvals;   // 512 floats per block, x fastest
+    const int *btab;      // block index or -1, over tb[0] x tb[1] x tb[2] block coordinates
+    int n[3], imin[3], bo[3], tb[3];
+    __device__ float at(int x, int y, int z) const {
+        if (x < 0 || y < 0 || z < 0 || x >= n[0] || y >= n[1] || z >= n[2]) return 0.f;
+        if (!bvals) return dense[(size_t(z) * n[1] + y) * n[0] + x];
+        const int X = x + imin[0], Y = y + imin[1], Z = z + imin[2];
+        const int b = btab[(size_t((Z >> 3) - bo[2]) * tb[1] + ((Y >> 3) - bo[1])) * tb[0] + ((X >> 3) - bo[0])];
+        return b < 0 ? 0.f : bvals[size_t(b) * 512 + (X & 7) + 8 * (Y & 7) + 64 * (Z & 7)];
+    }
+};
+VoxelSrc dense_src(const MediumView &v) {
+    VoxelSrc s{};
+    s.dense = v.dense;
+    s.n[0] = v.nx; s.n[1] = v.ny; s.n[2] = v.nz;
+    return s;
+}
+
 // NanoVDBMedium majorants, media.cpp:560-616: per majorant cell, Bounds3::Lerp of the cell corners ->
 // worldToIndexF(Vec3R) (subtraction and innermost product in double, fmaf arguments narrowed to float:
 // NanoVDB.h:1409-1414 instantiated for Vec3<double>) -> int(i0 - 1) .. int(i1 + 1) clipped to the index
 // box -> max of the voxel values, starting from 0.
-__global__ void k_build_majorants_nvdb(MediumView mv, float *out) {
+__global__ void k_build_majorants_nvdb(MediumView mv, VoxelSrc src, float *out) {
     __shared__ float sm[32];
     int idx[3] = {(int)blockIdx.x, (int)blockIdx.y, (int)blockIdx.z};
     int n[3] = {mv.nx, mv.ny, mv.nz};
@@ -238,7 +260,7 @@ __global__ void k_build_majorants_nvdb(MediumView mv, float *out) {
         int tot = ex * ey * ez;
         for (int i = threadIdx.x; i < tot; i += blockDim.x) {
             int x = lo[0] + i % ex, y = lo[1] + (i / ex) % ey, z = lo[2] + i / (ex * ey);
-            m = fmaxf(m, mv.dense[(size_t(z) * mv.ny + y) * mv.nx + x]);
+            m = fmaxf(m, src.at(x, y, z));
         }
     }
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
@@ -283,27 +305,25 @@ __global__ void k_pack_octets(MediumView mv, float4 *out32, uint4 *out16) {
 
 // Sparse brick pool (LAYOUT_BRICK_F16, avr_medium.cuh brick16_taps).  One CTA per brick of 8x8x8 cells.
 // flags: does any voxel the brick's cells touch (x in [8 bx - 1, 8 bx + 7], ...) hold a non-zero value?
-__global__ void k_brick_flags(MediumView mv, int *flags) {
+__global__ void k_brick_flags(VoxelSrc src, int *flags) {
     const int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z;
     int any = 0;
     for (int i = threadIdx.x; i < 729; i += blockDim.x) {
         int x = 8 * bx - 1 + i % 9, y = 8 * by - 1 + (i / 9) % 9, z = 8 * bz - 1 + i / 81;
-        any |= dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y, z) != 0.f;
+        any |= src.at(x, y, z) != 0.f;
     }
     any = __syncthreads_or(any);
     if (threadIdx.x == 0) flags[(size_t(bz) * gridDim.y + by) * gridDim.x + bx] = any;
 }
 // fill: CTA b writes the 576 entries of pool slot b (bricks lists the non-empty bricks' linear ids)
-__global__ void k_brick_fill(MediumView mv, const int *bricks, int sbx, int sby, uint2 *pool) {
+__global__ void k_brick_fill(VoxelSrc src, const int *bricks, int sbx, int sby, uint2 *pool) {
     const int id = bricks[blockIdx.x];
     const int bx = id % sbx, by = (id / sbx) % sby, bz = id / (sbx * sby);
     for (int i = threadIdx.x; i < kBrickEntries; i += blockDim.x) {
         int r = i % 9, lx = (i / 9) & 7, ly = i / 72;
         int x = 8 * bx + lx, y = 8 * by + ly, z = 8 * bz - 1 + r;  // cell column (x, y): taps x-1, x / y-1, y
-        __half2 h0 = __floats2half2_rn(dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x - 1, y - 1, z),
-                                       dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y - 1, z));
-        __half2 h1 = __floats2half2_rn(dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x - 1, y, z),
-                                       dense_at(mv.dense, mv.nx, mv.ny, mv.nz, x, y, z));
+        __half2 h0 = __floats2half2_rn(src.at(x - 1, y - 1, z), src.at(x, y - 1, z));
+        __half2 h1 = __floats2half2_rn(src.at(x - 1, y, z), src.at(x, y, z));
         uint2 q;
         q.x = *reinterpret_cast<uint32_t *>(&h0);
         q.y = *reinterpret_cast<uint32_t *>(&h1);
@@ -494,10 +514,10 @@ avr_status finish_majorants(avr_medium *m) {
 }
 
 // Octet store of the scalar density grid (layouts 1, 2): cell c holds taps c-1, c on every axis.
-avr_status build_bricks(avr_medium *m);
+avr_status build_bricks(avr_medium *m, const VoxelSrc &src);
 avr_status build_octets(avr_medium *m, int layout) {
     if (layout == LAYOUT_DENSE_F32) return AVR_OK;
-    if (layout == LAYOUT_BRICK_F16) return build_bricks(m);
+    if (layout == LAYOUT_BRICK_F16) return build_bricks(m, dense_src(m->view));
     avr_ctx *ctx = m->ctx;
     MediumView &v = m->view;
     v.nbx = (v.nx + 1 + 3) / 4; v.nby = (v.ny + 1 + 3) / 4; v.nbz = (v.nz + 1 + 3) / 4;
@@ -524,7 +544,7 @@ avr_status build_octets(avr_medium *m, int layout) {
 
 // Sparse fp16 brick pool (layout 3): flags -> host prefix sum over the (small) brick grid -> pool fill; the dense
 // fp32 grid is released afterwards (every lookup of this medium goes through the pool from then on).
-avr_status build_bricks(avr_medium *m) {
+avr_status build_bricks(avr_medium *m, const VoxelSrc &src) {
     avr_ctx *ctx = m->ctx;
     MediumView &v = m->view;
     v.sbx = (v.nx + 1 + 7) / 8; v.sby = (v.ny + 1 + 7) / 8; v.sbz = (v.nz + 1 + 7) / 8;
@@ -533,7 +553,7 @@ avr_status build_bricks(avr_medium *m) {
         return set_err(ctx, AVR_ERR_UNSUPPORTED, "brick layout: too many bricks");
     int *d_flags = nullptr;
     AVR_CUDA(ctx, cudaMalloc(&d_flags, nb * sizeof(int)));
-    k_brick_flags<<<dim3(v.sbx, v.sby, v.sbz), 128, 0, ctx->stream>>>(v, d_flags);
+    k_brick_flags<<<dim3(v.sbx, v.sby, v.sbz), 128, 0, ctx->stream>>>(src, d_flags);
     std::vector<int> tab(nb), list;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(tab.data(), d_flags, nb * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
@@ -559,7 +579,7 @@ avr_status build_bricks(avr_medium *m) {
         AVR_CUDA(ctx, cudaMalloc(&d_list, list.size() * sizeof(int)));
         e = cudaMemcpyAsync(d_list, list.data(), list.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
         if (e == cudaSuccess) {
-            k_brick_fill<<<(unsigned)list.size(), 192, 0, ctx->stream>>>(v, d_list, v.sbx, v.sby, pool);
+            k_brick_fill<<<(unsigned)list.size(), 192, 0, ctx->stream>>>(src, d_list, v.sbx, v.sby, pool);
             e = cudaGetLastError();
         }
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -666,12 +686,19 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
     if (!ctx || !d || !out) return set_err(ctx, AVR_ERR_BAD_ARG, "avr_medium_create_nanovdb: NULL argument");
     *out = nullptr;
     // NanoVDBMedium::Create ErrorExit()s when the density grid is missing (media.cpp:636-637)
-    if (!d->density.values) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: didn't find \"density\" grid.");
+    const bool sparse = !d->density.values && d->density.block_values;
+    if (!d->density.values && !sparse) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: didn't find \"density\" grid.");
     for (int i = 0; i < 3; ++i)
         if (d->density.dims[i] < 1 || (d->temperature.values && d->temperature.dims[i] < 1))
             return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: empty index bounding box");
     if (!d->sigma_a || !d->sigma_s) return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb medium: sigma_a / sigma_s tables missing");
     if (layout < 0 || layout > 3) return set_err(ctx, AVR_ERR_BAD_ARG, "unknown grid layout");
+    if (sparse && (layout != LAYOUT_BRICK_F16 || d->temperature.values || d->temperature.block_values))
+        return set_err(ctx, AVR_ERR_UNSUPPORTED, "nanovdb: a grid given as 8^3 blocks needs layout brick16 and no temperature grid");
+    if (sparse && (d->density.n_blocks < 0 || d->density.n_blocks >= (int64_t(1) << 31) || (d->density.n_blocks > 0 && !d->density.block_origin)))
+        return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: n_blocks / block_origin inconsistent");
+    if (d->temperature.block_values && !d->temperature.values)
+        return set_err(ctx, AVR_ERR_UNSUPPORTED, "nanovdb: the temperature grid must be given flattened");
     AVR_CUDA(ctx, cudaSetDevice(ctx->device));
     avr_medium *m = new avr_medium();
     m->ctx = ctx;
@@ -681,7 +708,48 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
     const avr_nanovdb_grid &dg = d->density, &tg = d->temperature;
     v.nx = dg.dims[0]; v.ny = dg.dims[1]; v.nz = dg.dims[2];
     avr_status st;
-    TRY(upload(m, dg.values, size_t(v.nx) * v.ny * v.nz, &v.dense));
+    VoxelSrc src{};
+    float *d_bvals = nullptr;   // the blocks and their table live only until the pool and the majorants are built
+    int *d_btab = nullptr;
+    if (!sparse) {
+        TRY(upload(m, dg.values, size_t(v.nx) * v.ny * v.nz, &v.dense));
+        src = dense_src(v);
+    } else {
+        src.n[0] = v.nx; src.n[1] = v.ny; src.n[2] = v.nz;
+        size_t cells = 1;
+        for (int i = 0; i < 3; ++i) {
+            src.imin[i] = dg.index_min[i];
+            src.bo[i] = dg.index_min[i] >> 3;
+            src.tb[i] = ((dg.index_min[i] + dg.dims[i] - 1) >> 3) - src.bo[i] + 1;
+            cells *= size_t(src.tb[i]);
+        }
+        std::vector<int> tab(cells, -1);
+        for (int64_t b = 0; b < dg.n_blocks; ++b) {
+            const int32_t *o = dg.block_origin + 3 * b;
+            int c[3];
+            bool inside = true;
+            for (int i = 0; i < 3; ++i) {
+                if (o[i] & 7) { free_medium(m); return set_err(ctx, AVR_ERR_BAD_ARG, "nanovdb: block origins must be multiples of 8"); }
+                c[i] = (o[i] >> 3) - src.bo[i];
+                inside = inside && c[i] >= 0 && c[i] < src.tb[i];
+            }
+            if (inside) tab[(size_t(c[2]) * src.tb[1] + c[1]) * src.tb[0] + c[0]] = int(b);   // blocks off the index box are never read
+        }
+        const size_t nv = size_t(dg.n_blocks > 0 ? dg.n_blocks : 1) * 512;
+        cudaError_t e = cudaMalloc(&d_bvals, nv * sizeof(float));
+        if (e == cudaSuccess) e = cudaMalloc(&d_btab, cells * sizeof(int));
+        if (e == cudaSuccess && dg.n_blocks > 0)
+            e = cudaMemcpyAsync(d_bvals, dg.block_values, size_t(dg.n_blocks) * 512 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_btab, tab.data(), cells * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // `tab` leaves scope
+        if (e != cudaSuccess) { cudaFree(d_bvals); cudaFree(d_btab); free_medium(m); return set_cuda_err(ctx, e, "nanovdb blocks"); }
+        src.bvals = d_bvals;
+        src.btab = d_btab;
+    }
+    struct SrcGuard {   // freed on every way out
+        float *a; int *b;
+        ~SrcGuard() { cudaFree(a); cudaFree(b); }
+    } guard{d_bvals, d_btab};
     float p0[3], p1[3];
     for (int i = 0; i < 3; ++i) {
         v.nv_imin[i] = dg.index_min[i];
@@ -726,9 +794,10 @@ extern "C" avr_status avr_medium_create_nanovdb(avr_ctx *ctx, const avr_nanovdb_
     v.temp_scale = d->temperature_scale;
     v.sigma_scale = 1.f;
     TRY(finish_common(m, p0, p1, d->render_from_medium, d->medium_from_render, d->majorant_res, 64));
-    k_build_majorants_nvdb<<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, m->d_maj);
+    k_build_majorants_nvdb<<<dim3(v.mres[0], v.mres[1], v.mres[2]), 128, 0, ctx->stream>>>(v, src, m->d_maj);
     AVR_CUDA(ctx, cudaGetLastError());
-    TRY(build_octets(m, layout));
+    if (sparse) TRY(build_bricks(m, src));
+    else TRY(build_octets(m, layout));
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { free_medium(m); return set_cuda_err(ctx, e, "nanovdb medium build"); }
     TRY(finish_majorants(m));

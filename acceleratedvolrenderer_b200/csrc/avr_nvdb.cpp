@@ -20,6 +20,8 @@
 // Instead of 10^8 getValue() calls the tree is walked once: leaves are copied, value tiles are filled.
 #include <dlfcn.h>
 
+#include <algorithm>
+
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -150,6 +152,12 @@ struct Walker {
     int64_t dims[3];
     float *out;
     bool ok = true;
+    // sparse sink (avr_nvdb_read_blocks): 8^3 blocks instead of the dense array
+    bool sparse = false, too_many = false;
+    std::vector<int32_t> *origins = nullptr;
+    std::vector<float> *blocks = nullptr;
+    size_t tile_blocks = 0;
+    static constexpr size_t kMaxTileBlocks = size_t(1) << 22;
 
     bool in_buf(const unsigned char *p, size_t n) const { return p >= base && size_t(p - base) + n <= size; }
     // constant value over [o, o + side)^3 clipped to the box
@@ -162,6 +170,17 @@ struct Walker {
             b[i] = e < hi[i] ? int32_t(e) : hi[i];
             if (a[i] > b[i]) return;
         }
+        if (sparse) {
+            // the tile cut into the 8^3 blocks that meet the index box (tiles are aligned to their own extent >= 8)
+            for (int32_t z = a[2] & ~7; z <= b[2] && !too_many; z += 8)
+                for (int32_t y = a[1] & ~7; y <= b[1] && !too_many; y += 8)
+                    for (int32_t x = a[0] & ~7; x <= b[0]; x += 8) {
+                        if (++tile_blocks > kMaxTileBlocks) { too_many = true; break; }
+                        origins->insert(origins->end(), {x, y, z});
+                        blocks->insert(blocks->end(), 512, v);
+                    }
+            return;
+        }
         for (int32_t z = a[2]; z <= b[2]; ++z)
             for (int32_t y = a[1]; y <= b[1]; ++y) {
                 float *row = out + ((int64_t(z) - lo[2]) * dims[1] + (y - lo[1])) * dims[0];
@@ -171,6 +190,23 @@ struct Walker {
     void leaf(const unsigned char *p, const int32_t o[3]) {
         if (!in_buf(p, kLeafSize)) { ok = false; return; }
         const unsigned char *vals = p + kLeafValues;
+        if (sparse) {
+            // the leaf as it is, transposed to x-fastest; leaves that hold nothing but zeros are dropped
+            float tmp[512];
+            bool any = false;
+            for (int x = 0; x < 8; ++x)
+                for (int y = 0; y < 8; ++y)
+                    for (int z = 0; z < 8; ++z) {
+                        float v = rd<float>(vals + 4 * ((x << 6) | (y << 3) | z));
+                        tmp[x + 8 * y + 64 * z] = v;
+                        any |= v != 0.f;
+                    }
+            if (any) {
+                origins->insert(origins->end(), {o[0], o[1], o[2]});
+                blocks->insert(blocks->end(), tmp, tmp + 512);
+            }
+            return;
+        }
         for (int x = 0; x < 8; ++x) {
             int32_t X = o[0] + x;
             if (X < lo[0] || X > hi[0]) continue;
@@ -213,7 +249,7 @@ struct Walker {
     }
 };
 
-avr_status read_grid(const std::string &path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info) {
+avr_status read_grid(const std::string &path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info, bool sparse) {
     FILE *f = std::fopen(path.c_str(), "rb");
     if (!f) return fail(AVR_ERR_BAD_ARG, "nanovdb: " + path + ": Unable to open file named \"" + path + "\" for input");
     std::vector<GridEntry> grids;
@@ -260,12 +296,19 @@ avr_status read_grid(const std::string &path, const char *grid_name, avr_nanovdb
         if (w.dims[i] < 1 || w.dims[i] > (1 << 20)) return fail(AVR_ERR_BAD_ARG, "nanovdb: " + path + ": empty or implausible index bounding box");
         total *= w.dims[i];
     }
-    if (total > (int64_t(1) << 36)) return fail(AVR_ERR_OOM, "nanovdb: " + path + ": index bounding box too large to flatten");
-    float *values = (float *)std::calloc(size_t(total), sizeof(float));
-    if (!values) return fail(AVR_ERR_OOM, "nanovdb: out of memory flattening the grid");
+    if (!sparse && total > (int64_t(1) << 36)) return fail(AVR_ERR_OOM, "nanovdb: " + path + ": index bounding box too large to flatten");
+    float *values = nullptr;
+    std::vector<int32_t> origins;
+    std::vector<float> blocks;
+    if (sparse) {
+        w.sparse = true; w.origins = &origins; w.blocks = &blocks;
+    } else {
+        values = (float *)std::calloc(size_t(total), sizeof(float));
+        if (!values) return fail(AVR_ERR_OOM, "nanovdb: out of memory flattening the grid");
+    }
     w.out = values;
     if (size_t(root - b) + kRootData + size_t(table_size) * kRootTile > buf.size()) { std::free(values); return fail(AVR_ERR_BAD_ARG, "nanovdb: " + path + ": corrupt root table"); }
-    for (uint32_t t = 0; t < table_size && w.ok; ++t) {
+    for (uint32_t t = 0; t < table_size && w.ok && !w.too_many; ++t) {
         const unsigned char *tile = root + kRootData + size_t(t) * kRootTile;
         uint64_t key = rd<uint64_t>(tile);
         int64_t child = rd<int64_t>(tile + 8);
@@ -276,7 +319,23 @@ avr_status read_grid(const std::string &path, const char *grid_name, avr_nanovdb
         else w.fill(o, 4096, rd<float>(tile + 20));
     }
     if (!w.ok) { std::free(values); return fail(AVR_ERR_BAD_ARG, "nanovdb: " + path + ": node offset outside the grid buffer"); }
+    if (w.too_many)
+        return fail(AVR_ERR_UNSUPPORTED, "nanovdb: " + path + ": value tiles expand to more than 2^22 blocks (read the grid flattened instead)");
+    std::memset(grid, 0, sizeof(*grid));
     grid->values = values;
+    if (sparse) {
+        const size_t nb = origins.size() / 3;
+        int32_t *po = (int32_t *)std::malloc(std::max<size_t>(1, nb) * 3 * sizeof(int32_t));
+        float *pv = (float *)std::malloc(std::max<size_t>(1, nb) * 512 * sizeof(float));
+        if (!po || !pv) { std::free(po); std::free(pv); return fail(AVR_ERR_OOM, "nanovdb: out of memory collecting the leaves"); }
+        if (nb) {
+            std::memcpy(po, origins.data(), nb * 3 * sizeof(int32_t));
+            std::memcpy(pv, blocks.data(), nb * 512 * sizeof(float));
+        }
+        grid->n_blocks = int64_t(nb);
+        grid->block_origin = po;
+        grid->block_values = pv;
+    }
     for (int i = 0; i < 3; ++i) {
         grid->index_min[i] = w.lo[i];
         grid->dims[i] = int32_t(w.dims[i]);
@@ -299,16 +358,30 @@ avr_status read_grid(const std::string &path, const char *grid_name, avr_nanovdb
 extern "C" avr_status avr_nvdb_read_grid(const char *path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info) {
     if (!path || !grid) return fail(AVR_ERR_BAD_ARG, "avr_nvdb_read_grid: NULL argument");
     try {
-        return read_grid(path, grid_name, grid, info);
+        return read_grid(path, grid_name, grid, info, false);
     } catch (const std::bad_alloc &) {
         return fail(AVR_ERR_OOM, "avr_nvdb_read_grid: out of memory");
+    }
+}
+
+extern "C" avr_status avr_nvdb_read_blocks(const char *path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info) {
+    if (!path || !grid) return fail(AVR_ERR_BAD_ARG, "avr_nvdb_read_blocks: NULL argument");
+    try {
+        return read_grid(path, grid_name, grid, info, true);
+    } catch (const std::bad_alloc &) {
+        return fail(AVR_ERR_OOM, "avr_nvdb_read_blocks: out of memory");
     }
 }
 
 extern "C" void avr_nvdb_free_grid(avr_nanovdb_grid *grid) {
     if (!grid) return;
     std::free((void *)grid->values);
+    std::free((void *)grid->block_origin);
+    std::free((void *)grid->block_values);
     grid->values = nullptr;
+    grid->block_origin = nullptr;
+    grid->block_values = nullptr;
+    grid->n_blocks = 0;
 }
 
 extern "C" avr_status avr_medium_create_nanovdb_file(avr_ctx *ctx, const char *filename, const char *gridname,
@@ -319,11 +392,28 @@ extern "C" avr_status avr_medium_create_nanovdb_file(avr_ctx *ctx, const char *f
     // NanoVDBMedium::Create, media.cpp:631-633
     if (!filename || !*filename) return avr::set_err(ctx, AVR_ERR_BAD_ARG, "Must supply \"filename\" to \"nanovdb\" medium.");
     avr_nanovdb_desc d = *params;
-    avr_status st = avr_nvdb_read_grid(filename, gridname && *gridname ? gridname : "density", &d.density, nullptr);
+    std::memset(&d.density, 0, sizeof(d.density));
+    std::memset(&d.temperature, 0, sizeof(d.temperature));
+    avr_status st = avr_nvdb_read_grid(filename, temperaturename && *temperaturename ? temperaturename : "temperature", &d.temperature, nullptr);
     if (st != AVR_OK) return avr::set_err(ctx, st, avr_last_error(nullptr));
-    if (!d.density.values) return avr::set_err(ctx, AVR_ERR_BAD_ARG, std::string(filename) + ": didn't find \"density\" grid.");
-    st = avr_nvdb_read_grid(filename, temperaturename && *temperaturename ? temperaturename : "temperature", &d.temperature, nullptr);
-    if (st != AVR_OK) { avr_nvdb_free_grid(&d.density); return avr::set_err(ctx, st, avr_last_error(nullptr)); }
+    // the brick pool is built from the leaves when nothing else needs the box (AVR_NVDB_FLATTEN=1: the flattened
+    // route, for comparisons)
+    const char *env = std::getenv("AVR_NVDB_FLATTEN");
+    bool from_leaves = layout == AVR_LAYOUT_BRICK_F16 && !d.temperature.values && !(env && *env == '1');
+    const char *dname = gridname && *gridname ? gridname : "density";
+    if (from_leaves) {
+        st = avr_nvdb_read_blocks(filename, dname, &d.density, nullptr);
+        if (st == AVR_ERR_UNSUPPORTED) from_leaves = false;   // huge value tiles: flatten after all
+        else if (st != AVR_OK) { avr_nvdb_free_grid(&d.temperature); return avr::set_err(ctx, st, avr_last_error(nullptr)); }
+    }
+    if (!from_leaves) {
+        st = avr_nvdb_read_grid(filename, dname, &d.density, nullptr);
+        if (st != AVR_OK) { avr_nvdb_free_grid(&d.temperature); return avr::set_err(ctx, st, avr_last_error(nullptr)); }
+    }
+    if (!d.density.values && !d.density.block_values) {
+        avr_nvdb_free_grid(&d.temperature);
+        return avr::set_err(ctx, AVR_ERR_BAD_ARG, std::string(filename) + ": didn't find \"density\" grid.");
+    }
     st = avr_medium_create_nanovdb(ctx, &d, layout, out);
     avr_nvdb_free_grid(&d.density);
     avr_nvdb_free_grid(&d.temperature);

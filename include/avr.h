@@ -118,6 +118,16 @@ typedef struct avr_nanovdb_grid {
     float inv_mat[9];          /* Map::mInvMatF, row-major                                        */
     float vec[3];              /* Map::mVecF                                                      */
     double world_bbox[6];      /* worldBBox(): min xyz, max xyz                                   */
+    /* Sparse alternative to `values` (values == NULL, block_values != NULL): the grid as n_blocks blocks of 8^3
+     * voxels aligned to multiples of 8 in index space — NanoVDB's leaf nodes as they are, plus its non-zero value
+     * tiles cut into such blocks.  Block b covers [block_origin[3 b + i], + 8) on axis i and holds
+     * block_values[512 b + x + 8 y + 64 z]; voxels no block covers are 0; what lies outside the index box is not
+     * read.  Accepted by avr_medium_create_nanovdb for the density grid with layout AVR_LAYOUT_BRICK_F16 and no
+     * temperature grid: the brick pool and the majorant grid are then built straight from the blocks and the
+     * index box is never held as a dense array, on the host or on the device. */
+    int64_t n_blocks;
+    const int32_t *block_origin;
+    const float *block_values;
 } avr_nanovdb_grid;
 
 /* Replaces NanoVDBMedium::Create + ctor, media.cpp:511-665 ("nanovdb"; what pbrt-v4-scenes' Disney
@@ -160,9 +170,17 @@ typedef struct avr_nvdb_info {
     char grid_name[64];
 } avr_nvdb_info;
 avr_status avr_nvdb_read_grid(const char *path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info /* or NULL */);
+/* The same grid WITHOUT flattening: grid->values stays NULL and the sparse fields of avr_nanovdb_grid are filled —
+ * one block per leaf node that holds a non-zero value (transposed from NanoVDB's z-fastest order), value tiles with a
+ * non-zero value cut into 8^3 blocks (at most 2^22 of them: AVR_ERR_UNSUPPORTED beyond, use avr_nvdb_read_grid).  A
+ * file without that grid leaves block_values == NULL too.  Host memory is proportional to the leaves, not to the
+ * index box. */
+avr_status avr_nvdb_read_blocks(const char *path, const char *grid_name, avr_nanovdb_grid *grid, avr_nvdb_info *info /* or NULL */);
 void avr_nvdb_free_grid(avr_nanovdb_grid *grid);
 /* NanoVDBMedium::Create from the file: "filename", "gridname" (NULL = "density"), "temperaturename" (NULL =
- * "temperature"; the grid may be absent); every other parameter comes from `params`, whose two grids are ignored. */
+ * "temperature"; the grid may be absent); every other parameter comes from `params`, whose two grids are ignored.
+ * With layout AVR_LAYOUT_BRICK_F16 and no temperature grid in the file the density grid goes from the file's leaf
+ * nodes into the brick pool (avr_nvdb_read_blocks); otherwise through the flattened box (avr_nvdb_read_grid). */
 avr_status avr_medium_create_nanovdb_file(avr_ctx *ctx, const char *filename, const char *gridname,
                                           const char *temperaturename, const avr_nanovdb_desc *params, int layout,
                                           avr_medium **out);

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from acceleratedvolrenderer_b200 import scenes
-from acceleratedvolrenderer_b200.api import AvrError, read_nvdb_grid
+from acceleratedvolrenderer_b200.api import AvrError, read_nvdb_blocks, read_nvdb_grid
 
 
 def sparse_cloud(shape=(70, 50, 90), seed=5):
@@ -38,6 +38,36 @@ def test_reader_matches_the_reference_flattening(ref, tmp_path, codec):
     assert info["grid_name"] == "density" and first is not None
     none, info = read_nvdb_grid(path, "velocity")
     assert none is None and info["grids_in_file"] == 2
+
+
+@pytest.mark.parametrize("codec", [0, 1])
+def test_block_reader_is_the_flattening_cut_into_leaves(ref, tmp_path, codec):
+    """avr_nvdb_read_blocks (no flattening): the 8^3 blocks, put back into the index box, ARE the flattened grid bit for
+    bit; origins are multiples of 8, no block is empty, every leaf that holds a value and every value tile shows up."""
+    dens = sparse_cloud()
+    dens[40:48, 16:24, 8:16] = 0                    # one whole leaf of zeros in the middle of the cloud
+    origin_ijk, vs, ow = (-13, 5, -40), 0.0125, (0.25, -0.5, 1.0)
+    path = tmp_path / "cloud.nvdb"
+    ref.write_nvdb(path, [("density", dens, origin_ijk, vs, ow)], codec=codec)
+    flat, info = read_nvdb_grid(path, "density")
+    blk, info2 = read_nvdb_blocks(path, "density")
+    assert info == info2
+    for k in ("index_min", "dims", "inv_mat", "vec", "world_bbox"):
+        assert np.array_equal(blk[k], getattr(flat, k))
+    org, vals = blk["origins"], blk["values"]
+    assert org.shape[0] > 50 and np.all(org % 8 == 0) and np.all((vals != 0).any(axis=(1, 2, 3)))
+    assert len({tuple(o) for o in org}) == org.shape[0]
+    lo = np.asarray(flat.index_min); dims = np.asarray(flat.dims)
+    box = np.zeros(flat.values.shape, dtype=np.float32)
+    for o, v in zip(org, vals):
+        a = np.maximum(o, lo); b = np.minimum(o + 8, lo + dims)
+        assert np.all(a < b)                                   # every block meets the index box
+        box[a[2] - lo[2]:b[2] - lo[2], a[1] - lo[1]:b[1] - lo[1], a[0] - lo[0]:b[0] - lo[0]] = \
+            v[a[2] - o[2]:b[2] - o[2], a[1] - o[1]:b[1] - o[1], a[0] - o[0]:b[0] - o[0]]
+    assert np.array_equal(box.view(np.uint32), flat.values.view(np.uint32))
+    assert org.shape[0] * 512 < 0.8 * box.size                 # sparse: fewer voxels held than the box has
+    none, _ = read_nvdb_blocks(path, "velocity")
+    assert none is None
 
 
 def test_reader_error_behaviour(tmp_path):
@@ -114,4 +144,40 @@ def test_sparse_nvdb_file_into_the_brick_pool(ctx, ref, tmp_path):
         ctx.render_volpath(full, rd.with_(exact_math=0, sampler_seed=100 + seed), film=b)
     ma, mb = a[..., :3].sum() / a[..., 3].sum(), b[..., :3].sum() / b[..., 3].sum()
     assert abs(ma / mb - 1) < 0.02, (ma, mb)
+    # the pool above came straight from the file's leaves (avr_nvdb_read_blocks); through the flattened box it is the
+    # same medium: size, majorants, every lookup
+    import os
+    os.environ["AVR_NVDB_FLATTEN"] = "1"
+    try:
+        flat = ctx.create_medium_nanovdb_file(path, nd, layout="brick16")
+    finally:
+        del os.environ["AVR_NVDB_FLATTEN"]
+    assert flat.bytes() == brick.bytes() and np.array_equal(flat.majorants(), brick.majorants())
+    assert np.array_equal(flat.lookup_density(xyz).view(np.uint32), brick.lookup_density(xyz).view(np.uint32))
+    flat.close()
     brick.close(); half.close(); full.close()
+
+
+@pytest.mark.gpu
+def test_blocks_with_a_negative_origin_and_value_tiles(ctx, ref, tmp_path):
+    """Leaf-direct ingest where the index box does not start on a block boundary (negative, odd origin) and the grid
+    holds constant regions that NanoVDB may store as value tiles: equal to the flattened route, lookup by lookup."""
+    import os
+    dens = sparse_cloud((70, 50, 90), seed=5)
+    origin_ijk, vs = (-13, 5, -40), 1.0 / 90
+    nd, rd = scenes.cloud_scene_nanovdb(dens, voxel_size=vs, width=16, height=12, spp=1, sigma_t=11.0, albedo=0.9, g=0.3)
+    path = tmp_path / "neg.nvdb"
+    ref.write_nvdb(path, [("density", dens, origin_ijk, vs, (0.0, 0.0, 0.0))], codec=1)
+    a = ctx.create_medium_nanovdb_file(path, nd, layout="brick16")
+    os.environ["AVR_NVDB_FLATTEN"] = "1"
+    try:
+        b = ctx.create_medium_nanovdb_file(path, nd, layout="brick16")
+    finally:
+        del os.environ["AVR_NVDB_FLATTEN"]
+    assert a.bytes() == b.bytes() and np.array_equal(a.majorants(), b.majorants()) and a.majorants().max() > 0
+    rng = np.random.default_rng(8)
+    lo = np.array(origin_ijk, dtype=np.float32)
+    xyz = (lo + rng.uniform(-2, np.array(dens.shape[::-1]) + 2, (40000, 3))).astype(np.float32)
+    la, lb = a.lookup_density(xyz), b.lookup_density(xyz)
+    assert np.array_equal(la.view(np.uint32), lb.view(np.uint32)) and (la > 0).mean() > 0.1
+    a.close(); b.close()

@@ -21,6 +21,7 @@
 #include <pbrt/media.h>
 #include <pbrt/samplers.h>
 
+#include <algorithm>
 #include <cstring>
 #include <vector>
 
@@ -85,6 +86,7 @@ struct Access {
     struct NanoVDBDesc {
         avr_nanovdb_desc d{};
         std::vector<float> density, temperature, sigma_a, sigma_s;
+        std::vector<int32_t> block_origin;   // density as 8^3 blocks (Describe(..., blocks = true))
     };
     static void FillGrid(const nanovdb::FloatGrid *fg, avr_nanovdb_grid *g, std::vector<float> *values) {
         auto ib = fg->indexBBox();  // inclusive on both ends
@@ -102,9 +104,82 @@ struct Access {
         }
         for (int i = 0; i < 9; ++i) g->inv_mat[i] = fg->map().mInvMatF[i];
     }
-    static void Describe(const pbrt::NanoVDBMedium &m, NanoVDBDesc *o) {
+    // The grid WITHOUT flattening (avr_nanovdb_grid.block_*): every leaf node that holds a non-zero value as it is
+    // (transposed from NanoVDB's z-fastest order), and the non-zero value tiles of the internal nodes and of the root
+    // cut into 8^3 blocks where they meet the index box.  For layout AVR_LAYOUT_BRICK_F16: host memory and upload are
+    // proportional to the leaves, not to the box.
+    static void FillBlocks(const nanovdb::FloatGrid *fg, avr_nanovdb_grid *g, std::vector<int32_t> *origins,
+                           std::vector<float> *values) {
+        using Tree = nanovdb::FloatGrid::TreeType;
+        using Leaf = Tree::Node0;
+        using Lower = Tree::Node1;
+        using Upper = Tree::Node2;
+        const Tree &tree = fg->tree();
+        auto ib = fg->indexBBox();
+        auto tile = [&](nanovdb::Coord o, int extent, float v) {
+            if (v == 0) return;
+            int a[3], b[3];
+            for (int i = 0; i < 3; ++i) {
+                a[i] = std::max(o[i], ib.min()[i]);
+                b[i] = std::min(o[i] + extent - 1, ib.max()[i]);
+                if (a[i] > b[i]) return;
+            }
+            for (int z = a[2] & ~7; z <= b[2]; z += 8)
+                for (int y = a[1] & ~7; y <= b[1]; y += 8)
+                    for (int x = a[0] & ~7; x <= b[0]; x += 8) {
+                        origins->insert(origins->end(), {x, y, z});
+                        values->insert(values->end(), 512, v);
+                    }
+        };
+        const Leaf *leaf = tree.getFirstNode<Leaf>();
+        for (uint32_t i = 0; leaf && i < tree.nodeCount<Leaf>(); ++i) {
+            float tmp[512];
+            bool any = false;
+            for (int x = 0; x < 8; ++x)
+                for (int y = 0; y < 8; ++y)
+                    for (int z = 0; z < 8; ++z) {
+                        float v = leaf[i].getValue(uint32_t((x << 6) | (y << 3) | z));
+                        tmp[x + 8 * y + 64 * z] = v;
+                        any |= v != 0;
+                    }
+            if (!any) continue;
+            nanovdb::Coord o = leaf[i].origin();
+            origins->insert(origins->end(), {o[0], o[1], o[2]});
+            values->insert(values->end(), tmp, tmp + 512);
+        }
+        const Lower *lower = tree.getFirstNode<Lower>();
+        for (uint32_t i = 0; lower && i < tree.nodeCount<Lower>(); ++i)
+            for (uint32_t n = 0; n < 4096; ++n)
+                if (!lower[i].childMask().isOn(n)) tile(lower[i].offsetToGlobalCoord(n), 8, lower[i].data()->mTable[n].value);
+        const Upper *upper = tree.getFirstNode<Upper>();
+        for (uint32_t i = 0; upper && i < tree.nodeCount<Upper>(); ++i)
+            for (uint32_t n = 0; n < 32768; ++n)
+                if (!upper[i].childMask().isOn(n)) tile(upper[i].offsetToGlobalCoord(n), 128, upper[i].data()->mTable[n].value);
+        const auto &root = tree.root();
+        for (uint32_t t = 0; t < root.tileCount(); ++t) {
+            const auto *rt = root.data()->tile(t);
+            if (!rt->isChild()) tile(rt->origin(), 4096, rt->value);
+        }
+        if (values->empty()) values->push_back(0.f);   // block_values != NULL marks the grid as present
+        g->values = nullptr;
+        g->n_blocks = int64_t(origins->size() / 3);
+        g->block_origin = origins->data();
+        g->block_values = values->data();
+        for (int i = 0; i < 3; ++i) {
+            g->index_min[i] = ib.min()[i];
+            g->dims[i] = ib.max()[i] - ib.min()[i] + 1;
+            g->vec[i] = fg->map().mVecF[i];
+            g->world_bbox[i] = fg->worldBBox().min()[i];
+            g->world_bbox[3 + i] = fg->worldBBox().max()[i];
+        }
+        for (int i = 0; i < 9; ++i) g->inv_mat[i] = fg->map().mInvMatF[i];
+    }
+    // blocks = true: the density grid as 8^3 blocks when the medium has no temperature grid (for
+    // AVR_LAYOUT_BRICK_F16); the flattened box otherwise
+    static void Describe(const pbrt::NanoVDBMedium &m, NanoVDBDesc *o, bool blocks = false) {
         avr_nanovdb_desc &d = o->d;
-        FillGrid(m.densityFloatGrid, &d.density, &o->density);
+        if (blocks && !m.temperatureFloatGrid) FillBlocks(m.densityFloatGrid, &d.density, &o->block_origin, &o->density);
+        else FillGrid(m.densityFloatGrid, &d.density, &o->density);
         if (m.temperatureFloatGrid) FillGrid(m.temperatureFloatGrid, &d.temperature, &o->temperature);
         Transforms(m.renderFromMedium, &d);
         o->sigma_a = Table(m.sigma_a_spec); o->sigma_s = Table(m.sigma_s_spec);

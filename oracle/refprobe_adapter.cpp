@@ -35,6 +35,15 @@ void *ref_adapter_describe_medium(void *medium_h, int32_t *kind, const void **de
     *kind = -1; *desc = nullptr;
     return nullptr;
 }
+// the NanoVDBMedium with its density grid as 8^3 blocks (A::FillBlocks)
+void *ref_adapter_describe_medium_blocks(void *medium_h, const void **desc) {
+    const Medium &m = *ref_medium_ptr(medium_h);
+    if (!m.Is<NanoVDBMedium>()) { *desc = nullptr; return nullptr; }
+    auto *h = new A::NanoVDBDesc();
+    A::Describe(*m.Cast<NanoVDBMedium>(), h, true);
+    *desc = &h->d;
+    return h;
+}
 void ref_adapter_free_medium(void *h, int32_t kind) {
     if (kind == 0) delete (A::GridDesc *)h;
     else if (kind == 2) delete (A::NanoVDBDesc *)h;

@@ -148,6 +148,45 @@ def test_adapter_describes_camera_light_sensor_sampler(ref, sampler):
     ref.lib.ref_adapter_free_render(h)
 
 
+def test_adapter_hands_over_a_nanovdb_grid_as_blocks(ref, tmp_path):
+    """Describe(NanoVDBMedium, blocks = true): the in-memory FloatGrid as its leaf nodes (+ value tiles) instead of the
+    flattened box — the same blocks the library's own .nvdb walker reads from the file of that grid, and, put back
+    into the index box, the flattened grid bit for bit."""
+    from acceleratedvolrenderer_b200.api import read_nvdb_blocks
+    dens = scenes.fbm_density(44, 36, 40, seed=9)
+    dens[dens < 0.15] = 0
+    dens[8:24, 8:24, 16:32] = 0.75                  # whole leaves of one value: tiles if the builder prunes
+    vs = 1.0 / 44
+    nd, rd = scenes.cloud_scene_nanovdb(dens, voxel_size=vs, width=16, height=12, spp=1, sigma_t=7.0, albedo=0.9, g=0.2)
+    mo = ref.medium_nanovdb(nd)
+    lib = ref.lib
+    lib.ref_adapter_describe_medium_blocks.restype = C.c_void_p
+    desc = C.c_void_p()
+    h = C.c_void_p(lib.ref_adapter_describe_medium_blocks(mo.h, C.byref(desc)))
+    d = C.cast(desc, C.POINTER(_abi.avr_nanovdb_desc)).contents
+    g = d.density
+    assert not g.values and g.block_values and g.n_blocks > 20
+    n = int(g.n_blocks)
+    org = np.ctypeslib.as_array(g.block_origin, shape=(3 * n,)).reshape(n, 3).copy()
+    vals = _arr(g.block_values, 512 * n).reshape(n, 8, 8, 8).copy()
+    assert list(g.index_min) == list(nd.c.density.index_min) and list(g.dims) == list(nd.c.density.dims)
+    path = tmp_path / "same.nvdb"
+    ref.write_nvdb(path, [("density", dens, (0, 0, 0), vs, (0.0, 0.0, 0.0))])
+    blk, _ = read_nvdb_blocks(path, "density")
+    ka = np.lexsort(org.T[::-1]); kb = np.lexsort(blk["origins"].T[::-1])
+    assert np.array_equal(org[ka], blk["origins"][kb])
+    assert np.array_equal(vals[ka].view(np.uint32), blk["values"][kb].view(np.uint32))
+    lo = np.asarray(list(g.index_min)); dims = np.asarray(list(g.dims))
+    box = np.zeros(nd.density.values.shape, dtype=np.float32)
+    for o, v in zip(org, vals):
+        a = np.maximum(o, lo); b = np.minimum(o + 8, lo + dims)
+        box[a[2] - lo[2]:b[2] - lo[2], a[1] - lo[1]:b[1] - lo[1], a[0] - lo[0]:b[0] - lo[0]] = \
+            v[a[2] - o[2]:b[2] - o[2], a[1] - o[1]:b[1] - o[1], a[0] - o[0]:b[0] - o[0]]
+    assert np.array_equal(box.view(np.uint32), nd.density.values.view(np.uint32))
+    lib.ref_adapter_free_medium(h, C.c_int32(2))
+    mo.close()
+
+
 def test_adapter_describes_every_pixel_filter(ref):
     """pbrt's default pixel filter is "gaussian" (scene.cpp:94, filters.cpp:114): DescribeFilter hands the device the
     FilterSampler's own table (bit-equal to the one the probe tabulates from GaussianFilter::Evaluate) and the radius;
@@ -171,6 +210,36 @@ def test_adapter_describes_every_pixel_filter(ref):
     assert d is not None and d.filter and d.filter.contents.kind == _abi.FILTER_TRIANGLE
     assert list(d.filter_radius) == [2.0, 2.0]
     ref.lib.ref_adapter_free_render(h)
+
+
+@pytest.mark.gpu
+def test_device_builds_the_brick_pool_from_the_adapters_blocks(ctx, ref):
+    """The block descriptor of the reference's in-memory NanoVDBMedium, handed to avr_medium_create_nanovdb as it is:
+    the same brick pool as the one built from the flattened arrays (size, majorants, every lookup)."""
+    from acceleratedvolrenderer_b200.api import AvrError, Medium
+    dens = scenes.fbm_density(44, 36, 40, seed=9)
+    dens[dens < 0.15] = 0
+    nd, rd = scenes.cloud_scene_nanovdb(dens, voxel_size=1.0 / 44, width=16, height=12, spp=1, sigma_t=7.0, albedo=0.9, g=0.2)
+    mo = ref.medium_nanovdb(nd)
+    lib = ref.lib
+    lib.ref_adapter_describe_medium_blocks.restype = C.c_void_p
+    desc = C.c_void_p()
+    h = C.c_void_p(lib.ref_adapter_describe_medium_blocks(mo.h, C.byref(desc)))
+    mh = C.c_void_p()
+    ctx.check(ctx.lib.avr_medium_create_nanovdb(ctx.h, desc, C.c_int(3), C.byref(mh)))
+    via = Medium(ctx, mh, nd)
+    direct = ctx.create_medium("nanovdb", nd, layout="brick16")
+    assert via.bytes() == direct.bytes() and np.array_equal(via.majorants(), direct.majorants())
+    rng = np.random.default_rng(4)
+    xyz = rng.uniform(-2, np.array(dens.shape[::-1]) + 2, (30000, 3)).astype(np.float32)
+    assert np.array_equal(via.lookup_density(xyz).view(np.uint32), direct.lookup_density(xyz).view(np.uint32))
+    # blocks feed the brick pool only: any other layout is refused with a message
+    with pytest.raises(AvrError) as e:
+        ctx.check(ctx.lib.avr_medium_create_nanovdb(ctx.h, desc, C.c_int(1), C.byref(mh)))
+    assert "brick16" in str(e.value)
+    via.close(); direct.close()
+    lib.ref_adapter_free_medium(h, C.c_int32(2))
+    mo.close()
 
 
 @pytest.mark.gpu

@@ -63,6 +63,12 @@ def volpath_case(ctx, peak, name, med, rd, bytes_per_fetch, reps, **extra):
 
 def run_volpath(ctx, peak, args):
     dev = torch.device("cuda", 0)
+    if not args.c5_only:
+        run_c1_c3(ctx, peak, args, dev)
+    run_c5(ctx, peak, args, dev)
+
+
+def run_c1_c3(ctx, peak, args, dev):
     # C1: cube.pbrt-like, 32^3 uniform-random density, 640x480
     rng = np.random.default_rng(1)
     dens = rng.random((32, 32, 32), dtype=np.float32)
@@ -85,6 +91,9 @@ def run_volpath(ctx, peak, args):
                 volpath_case(ctx, peak, f"{name} {spp}spp", med, rd, bpf, args.reps, layout=layout, exact_math=exact)
                 med.close()
     del density
+
+
+def run_c5(ctx, peak, args, dev):
     # C5: synthetic cubes
     for n in args.cubes:
         dens = density_cube(n, dev)
@@ -202,6 +211,7 @@ def main():
     ap.add_argument("--general-max", type=int, default=512, help="largest cube for the RGB / emissive variants")
     ap.add_argument("--graph-sizes", default="100000,1000000,10000000")
     ap.add_argument("--reps", type=int, default=2)
+    ap.add_argument("--c5-only", action="store_true", help="volpath: only the synthetic cubes (C5)")
     args = ap.parse_args()
     args.cubes = [int(x) for x in args.cubes.split(",") if x]
     args.graph_sizes = [int(x) for x in args.graph_sizes.split(",") if x]

@@ -29,6 +29,7 @@ def main():
                     help="NAME=v1;v2;... (repeatable); the product of all lists is swept")
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--sampler", default="independent", help="independent | zsobol (fastowen)")
+    ap.add_argument("--filter", default="box", help="box | gaussian (pbrt's default pixel filter: radius 1.5, sigma 0.5) | triangle")
     args = ap.parse_args()
     w = bench.WORKLOADS[args.workload]
     dev = torch.device("cuda", 0)
@@ -46,6 +47,11 @@ def main():
             ctx = Context(0)
             med = ctx.create_medium("nanovdb", gd, layout=layout)
             r = rd.with_(exact_math=int(exact), sampler=1 if args.sampler == "zsobol" else 0, randomize=2)
+            if args.filter == "gaussian":
+                from acceleratedvolrenderer_b200._abi import gaussian_filter_table
+                r = r.with_filter(gaussian_filter_table((1.5, 1.5), 0.5), (1.5, 1.5))
+            elif args.filter == "triangle":
+                r = r.with_filter("triangle", (2.0, 2.0))
             best = None
             for i in range(args.reps + 1):
                 film.zero_()
@@ -54,7 +60,7 @@ def main():
                     best = st
             f = best["camera_fetches"] + best["shadow_fetches"]
             bpf = {"octet16": 16, "brick16": 20}.get(layout, 32)
-            print(json.dumps({"layout": layout, "exact": int(exact), "sampler": args.sampler, "env": dict(zip(names, vals)),
+            print(json.dumps({"layout": layout, "exact": int(exact), "sampler": args.sampler, "filter": args.filter, "env": dict(zip(names, vals)),
                               "kernel_ms": round(best["kernel_ms"], 2),
                               "Msamples_s": round(W * H * args.spp / best["kernel_ms"] / 1e3, 2),
                               "fetches": f, "GBs": round((f * bpf + best["segments"] * 4) / best["kernel_ms"] / 1e6, 1),

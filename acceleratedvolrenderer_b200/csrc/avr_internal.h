@@ -53,7 +53,8 @@ struct avr_ctx {
     float *d_filter = nullptr;
     size_t d_filter_floats = 0;
     std::vector<float> h_filter;
-    float4 *d_fsamples = nullptr;  // filter sample {p.x, p.y, weight, 0} per pixel sample of the current launch
+    float4 *d_fsamples = nullptr;  // {filter p.x, p.y, weight, zsobol wavelength draw} per pixel sample of the current launch
+    bool ev0_recorded = false;     // fill_render_params started the kernel timer before its pre-pass
     size_t d_fsamples_count = 0;
 };
 

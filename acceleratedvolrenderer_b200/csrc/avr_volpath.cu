@@ -94,7 +94,7 @@ AVR_DEV void write_sample(const RenderParams &rp, const PathLane<TR> &ln, double
     // RGBFilm::AddSample: rgbSum[c] += weight * rgb[c] (a float product), weightSum += weight.  Box filter: weight 1
     // (adding +-0 leaves a sum unchanged); the tabulated-filter case is a branch of its own so that the common one
     // carries no weight at all
-    if (__builtin_expect(rp.fsamples != nullptr, 0)) {
+    if (__builtin_expect(rp.fweighted != 0, 0)) {
         const float w = rp.fsamples[sample_slot(rp, ln.px, ln.py, ln.samp)].z;
         atomicAdd(px + 0, (double)(w * rgb[0]));
         atomicAdd(px + 1, (double)(w * rgb[1]));
@@ -124,21 +124,30 @@ AVR_DEV bool start_path(const MediumView &mv, const RenderParams &rp, PathLane<T
     ln.px = px; ln.py = py; ln.samp = s;
     PathSamplerRef<TR::ZSOBOL> smp{rp.smp, ln.srng, px, py, s};
     smp.start_pixel_sample();
-    float lu = smp.get1d();
+    float lu, fx, fy;
+    const bool pre = rp.fsamples != nullptr;
+    if (TR::ZSOBOL && pre) {
+        // zsobol: the pre-pass drew the wavelength sample and the film offset of every pixel sample of the launch
+        // (three sample-index computations per path, at full lanes there instead of here)
+        lu = rp.fsamples[sample_slot(rp, px, py, s)].w;
+        smp.skip(3);
+    } else
+        lu = smp.get1d();
     float pdf[4];
     sample_visible_wavelengths<TR::EXACT>(lu, ln.lambda, pdf);
     lc = make_lambda_ctx<TR::NCH>(mv, ln.lambda);
-    float f0, f1;
-    smp.get2d(&f0, &f1);  // GetCameraSample: GetPixel2D, samplers.h:797-814
-    float fx, fy;
-    if (__builtin_expect(rp.fsamples != nullptr, 0)) {
-        // tabulated filter (FilterSampler::Sample): sampled by the pre-pass from these same two draws
+    if (!(TR::ZSOBOL && pre)) {
+        float f0, f1;
+        smp.get2d(&f0, &f1);  // GetCameraSample: GetPixel2D, samplers.h:797-814
+        fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx);  // BoxFilter::Sample, filters.h:67-70
+        fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
+    }
+    if (__builtin_expect(pre, TR::ZSOBOL)) {
+        // tabulated / triangle filter (FilterSampler::Sample), or zsobol's box offsets: sampled by the pre-pass from
+        // these same two draws (a second read of the entry: cheaper than two registers held across the wavelength code)
         const float4 fs = rp.fsamples[sample_slot(rp, px, py, s)];
         fx = fs.x;
         fy = fs.y;
-    } else {
-        fx = lerp_exact(f0, -rp.filter_rx, rp.filter_rx);  // BoxFilter::Sample, filters.h:67-70
-        fy = lerp_exact(f1, -rp.filter_ry, rp.filter_ry);
     }
     float pfx = (float(px) + fx) + 0.5f, pfy = (float(py) + fy) + 0.5f;
     smp.skip(3);          // time (Get1D), lens (Get2D): a pinhole camera reads neither

@@ -23,7 +23,8 @@ struct RenderParams {
     int fnx, fny;
     // ... sampled for every pixel sample of the launch by a pre-pass (k_filter_prepass): {p.x, p.y, weight, 0} at
     // sample_slot(px, py, samp); the render kernels only load it (no binary search in their instruction stream)
-    const float4 *fsamples;
+    const float4 *fsamples;   // per pixel sample of the launch: {filter p.x, p.y, weight, zsobol wavelength draw}, or NULL
+    int fweighted;            // the film adds weight * rgb (a tabulated filter); 0: weight 1
     float cfr[16];   // cameraFromRaster (projective)
     float rfc[12];   // renderFromCamera (affine rows)
     float light_dir[3];

@@ -70,11 +70,11 @@ def test_gaussian_table_helper_is_the_reference_table(ref):
     assert np.allclose(mine, t, rtol=5e-3, atol=1e-7)
 
 
-def test_camera_rays_and_weights_under_a_gaussian_filter(orc, ref):
-    """EvaluatePixelSample's prologue with the REAL PerspectiveCamera and GaussianFilter: rays of the restatement
-    bit-equal (fed with the reference's matrices), weights bit-equal to Filter::Sample's."""
-    cfg = FILTERS["gaussian"]
-    table = ref.filter_table(cfg)
+@pytest.mark.parametrize("name", ["gaussian", "mitchell", "triangle"])
+def test_camera_rays_and_weights_under_a_filter(orc, ref, name):
+    """EvaluatePixelSample's prologue with the REAL PerspectiveCamera and the reference's own filter object: rays of the
+    restatement bit-equal (fed with the reference's matrices), weights bit-equal to Filter::Sample's."""
+    cfg = (4, 2.0, 2.0, 0.0, 0.0) if name == "triangle" else FILTERS[name]
     W, H, fov, eye, seed = golden_cases.camera_configs()[0]
     aspect = W / H
     sw = (-aspect, -1, aspect, 1) if aspect > 1 else (-1, -1 / aspect, 1, 1 / aspect)
@@ -86,14 +86,24 @@ def test_camera_rays_and_weights_under_a_gaussian_filter(orc, ref):
     for k in range(16):
         rd.c.camera_from_raster[k] = float(mats[0].ravel()[k])
         rd.c.render_from_camera[k] = float(mats[1].ravel()[k])
-    rg = rd.with_filter(table, cfg[1:3])
+    rg = rd.with_filter("triangle" if name == "triangle" else ref.filter_table(cfg), cfg[1:3])
     m = orc.medium_uniformgrid(gd)
     _, mine = m.camera_rays(rg, samples)
     _, boxed = m.camera_rays(rd, samples)
     m.close()
     assert np.array_equal(mine.view(np.uint32), rays.view(np.uint32))
     assert not np.array_equal(mine, boxed)
-    assert weights.min() > 0
+    if name == "gaussian":
+        assert weights.min() > 0
+    elif name == "triangle":
+        assert np.all(weights == 1)
+    else:
+        assert (weights < 0).any()
+    # the restatement's CameraSample::filterWeight of the same samples (full-frame order: pick the tested ones)
+    x0, y0, x1, y1, s0, s1 = rg.ranges()
+    w_all = orc.camera_weights(rg).reshape(y1 - y0, x1 - x0, s1 - s0)
+    mine_w = w_all[samples[:, 1] - y0, samples[:, 0] - x0, samples[:, 2] - s0]
+    assert np.array_equal(mine_w.view(np.uint32), weights.view(np.uint32))
 
 
 @pytest.mark.gpu
